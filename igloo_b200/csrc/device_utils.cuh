@@ -1,0 +1,142 @@
+// device_utils.cuh — sm_100a device helpers: mbarrier, 1-D bulk async copies
+// (TMA engine, SASS UBLKCP), named barriers, streaming loads/stores, hashing and
+// the single-pass ordered scan ("decoupled look-back") used by every kernel that
+// compacts rows.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace igl {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+// ---- mbarrier ---------------------------------------------------------------
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    while (!mbar_try_wait(bar, parity)) {
+    }
+}
+
+// ---- bulk async copy global -> shared (TMA engine, no tensor map needed) -----
+// dst, src 16-byte aligned; bytes a multiple of 16.
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+            smem_u32(smem_dst)),
+        "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+
+// ---- named barriers (producer/consumer split inside one CTA) -----------------
+__device__ __forceinline__ void bar_sync(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+__device__ __forceinline__ void bar_arrive(int id, int nthreads) {
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// ---- streaming global access --------------------------------------------------
+__device__ __forceinline__ uint64_t ld_volatile_u64(const uint64_t* p) {
+    uint64_t v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_volatile_u64(uint64_t* p, uint64_t v) {
+    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void st_cs_u32(void* p, uint32_t v) {
+    asm volatile("st.global.cs.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void st_cs_u64(void* p, uint64_t v) {
+    asm volatile("st.global.cs.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ ulonglong2 ld_nc_u64x2(const void* p) {
+    ulonglong2 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
+    return v;
+}
+
+// ---- hashing ------------------------------------------------------------------
+__host__ __device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+// Join / partition hash: one multiply-xorshift round pair (cheaper than the full
+// splitmix, still avalanches the high bits the table index is taken from).
+__host__ __device__ __forceinline__ uint64_t mix64(uint64_t k) {
+    k ^= k >> 32;
+    k *= 0xD6E8FEB86659FD93ull;
+    k ^= k >> 32;
+    k *= 0xD6E8FEB86659FD93ull;
+    k ^= k >> 32;
+    return k;
+}
+
+// ---- ordered single-pass scan: tile status words -----------------------------
+// status[t] = flag << 62 | value ; flag 1 = this tile's own count is known,
+// flag 2 = the inclusive prefix up to and including this tile is known.
+constexpr uint64_t kFlagAggregate = 1ull << 62;
+constexpr uint64_t kFlagPrefix = 2ull << 62;
+constexpr uint64_t kValueMask = (1ull << 62) - 1;
+
+// Called by one full warp.  Publishes `count` for `tile`, walks back over the
+// predecessors 32 at a time until it meets a known prefix, publishes this tile's
+// inclusive prefix and returns the exclusive one (same value in every lane).
+__device__ __forceinline__ uint64_t lookback_exclusive(uint64_t* status, int64_t tile, uint64_t count, int lane) {
+    if (tile == 0) {
+        if (lane == 0) st_volatile_u64(status, kFlagPrefix | count);
+        return 0;
+    }
+    if (lane == 0) st_volatile_u64(status + tile, kFlagAggregate | count);
+    uint64_t excl = 0;
+    int64_t idx = tile - 1;
+    while (true) {
+        int64_t mine = idx - lane;
+        uint64_t w;
+        do {
+            w = (mine >= 0) ? ld_volatile_u64(status + mine) : kFlagPrefix;  // before tile 0: prefix 0
+        } while (__any_sync(0xffffffffu, (w >> 62) == 0));
+        uint32_t is_prefix = __ballot_sync(0xffffffffu, (w >> 62) == 2);
+        uint64_t v = w & kValueMask;
+        if (is_prefix) {
+            int first = __ffs(is_prefix) - 1;  // nearest predecessor holding a prefix
+            if (lane > first) v = 0;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        excl += v;
+        if (is_prefix) break;
+        idx -= 32;
+    }
+    if (lane == 0) st_volatile_u64(status + tile, kFlagPrefix | (excl + count));
+    return excl;
+}
+
+}  // namespace igl

@@ -1,0 +1,652 @@
+// filter_project.cu — K1/K2/K3: fused predicate -> stream compaction ->
+// projection over device-resident Arrow columns.
+//
+// Reference semantics implemented (crates/engine/src/operators/):
+//   filter.rs:39-68      mask = predicate(batch); keep rows whose mask is valid
+//                        AND true on every column, order preserved
+//   projection.rs:48-72  one output column per expression, literals broadcast
+// and the planner-side fusion of Projection(Filter(x)) (physical_planner.rs:52-94).
+//
+// Kernel shape (one persistent CTA = 8 compute warps + 1 control warp):
+//   * the control warp takes tile tickets in order, streams each tile's
+//     referenced column slices into a shared-memory ring with 1-D bulk async
+//     copies (TMA engine, mbarrier complete_tx), and runs the ordered
+//     single-pass scan (decoupled look-back) that turns per-tile survivor
+//     counts into global output offsets;
+//   * compute warps interpret the fused three-address program on 4 rows per
+//     lane held in registers (lane i owns rows i, i+32, i+64, i+96 of its warp's
+//     128-row group, so every ballot covers 32 consecutive rows and compacted
+//     stores are contiguous per instruction), count survivors with
+//     __ballot_sync/__popc, and write the projected columns straight to their
+//     final positions.  No intermediate array ever reaches HBM.
+// HBM traffic = referenced input columns once + surviving output rows once.
+#include "expr_ir.h"
+#include "kernels.h"
+#include "tile_pipe.cuh"
+
+#include <cstring>
+
+namespace igl {
+
+constexpr int kMaxOut = 16;
+
+enum : uint32_t { ERRF_DIV_ZERO = 1, ERRF_OVERFLOW = 2, ERRF_CAST = 4 };
+
+struct FpParams {
+    Instr code[kMaxInstr];
+    uint8_t expr_first[kMaxExprs], expr_count[kMaxExprs], expr_reg[kMaxExprs];
+    uint8_t n_out, pad0[3];
+    PipeCols T;                    // staged input columns + scan state
+    void* out_data[kMaxOut];
+    uint8_t* out_valid[kMaxOut];   // byte-per-row validity (packed afterwards) or NULL
+    uint8_t out_shift[kMaxOut];    // 2 / 3, or 0 = byte per row (boolean, packed afterwards)
+};
+
+struct V {
+    uint64_t v[4];
+    uint32_t ok;  // bit r = row r is valid (non-null)
+};
+
+#define REG_READ(dst, idx)            \
+    switch (idx) {                    \
+        case 0: dst = r0; break;      \
+        case 1: dst = r1; break;      \
+        case 2: dst = r2; break;      \
+        default: dst = r3; break;     \
+    }
+#define REG_WRITE(idx, src)           \
+    switch (idx) {                    \
+        case 0: r0 = src; break;      \
+        case 1: r1 = src; break;      \
+        case 2: r2 = src; break;      \
+        default: r3 = src; break;     \
+    }
+static_assert(kMaxRegs == 4, "REG_READ / REG_WRITE enumerate the value registers");
+
+__device__ __forceinline__ int64_t total_order_key(uint64_t bits) {
+    int64_t b = (int64_t)bits;
+    return b ^ (int64_t)(((uint64_t)(b >> 63)) >> 1);
+}
+
+template <bool HAS_NULLS>
+__device__ __forceinline__ V load_col(const FpParams& P, int slot, const uint8_t* stage, int row0) {
+    V x;
+    x.ok = 0xF;
+    const uint8_t* base = stage + P.T.smem_off[slot];
+    const int sh = P.T.shift[slot];
+    if (sh == 2) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) x.v[r] = *reinterpret_cast<const uint32_t*>(base + ((row0 + r * 32) << 2));
+    } else if (sh == 3) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) x.v[r] = *reinterpret_cast<const uint64_t*>(base + ((row0 + r * 32) << 3));
+    } else {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            int row = row0 + r * 32;
+            x.v[r] = (base[row >> 3] >> (row & 7)) & 1;
+        }
+    }
+    if (HAS_NULLS && P.T.valid[slot] != nullptr) {
+        const uint8_t* vb = stage + P.T.valid_off[slot];
+        uint32_t ok = 0;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            int row = row0 + r * 32;
+            ok |= ((vb[row >> 3] >> (row & 7)) & 1u) << r;
+        }
+        x.ok = ok;
+    }
+    return x;
+}
+
+template <bool HAS_NULLS>
+__device__ __forceinline__ V exec_op(const Instr& in, const V& a, const V& b, unsigned int* err_flags) {
+    V d;
+    d.ok = HAS_NULLS ? (a.ok & b.ok) : 0xF;
+    const int op = in.op, ty = in.type;
+    switch (op) {
+        case IOP_MOV:
+            d = a;
+            break;
+        case IGL_OP_EQ: case IGL_OP_NE: case IGL_OP_LT: case IGL_OP_LE: case IGL_OP_GT: case IGL_OP_GE: {
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                int64_t x, y;
+                if (ty == IGL_T_I32) { x = (int32_t)a.v[r]; y = (int32_t)b.v[r]; }
+                else if (ty == IGL_T_F64) { x = total_order_key(a.v[r]); y = total_order_key(b.v[r]); }
+                else if (ty == IGL_T_BOOL) { x = (int64_t)(a.v[r] & 1); y = (int64_t)(b.v[r] & 1); }
+                else { x = (int64_t)a.v[r]; y = (int64_t)b.v[r]; }
+                bool c;
+                switch (op) {
+                    case IGL_OP_EQ: c = x == y; break;
+                    case IGL_OP_NE: c = x != y; break;
+                    case IGL_OP_LT: c = x < y; break;
+                    case IGL_OP_LE: c = x <= y; break;
+                    case IGL_OP_GT: c = x > y; break;
+                    default: c = x >= y; break;
+                }
+                d.v[r] = c ? 1 : 0;
+            }
+            break;
+        }
+        case IGL_OP_ADD: case IGL_OP_SUB: case IGL_OP_MUL: {
+            if (ty == IGL_T_F64) {
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    double x = __longlong_as_double((long long)a.v[r]), y = __longlong_as_double((long long)b.v[r]);
+                    // explicit round-to-nearest intrinsics: never contracted into an FMA
+                    double z = op == IGL_OP_ADD ? __dadd_rn(x, y) : op == IGL_OP_SUB ? __dsub_rn(x, y) : __dmul_rn(x, y);
+                    d.v[r] = (uint64_t)__double_as_longlong(z);
+                }
+            } else {  // two's-complement wrap; I32 lives in the low 32 bits
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+                    d.v[r] = op == IGL_OP_ADD ? a.v[r] + b.v[r] : op == IGL_OP_SUB ? a.v[r] - b.v[r]
+                             : (ty == IGL_T_I32 ? (uint64_t)((uint32_t)a.v[r] * (uint32_t)b.v[r]) : a.v[r] * b.v[r]);
+            }
+            break;
+        }
+        case IGL_OP_DIV: case IGL_OP_MOD: {
+            if (ty == IGL_T_F64) {
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    double x = __longlong_as_double((long long)a.v[r]), y = __longlong_as_double((long long)b.v[r]);
+                    double z = op == IGL_OP_DIV ? __ddiv_rn(x, y) : fmod(x, y);
+                    d.v[r] = (uint64_t)__double_as_longlong(z);
+                }
+            } else {
+                uint32_t ef = 0;
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    int64_t x = ty == IGL_T_I32 ? (int64_t)(int32_t)a.v[r] : (int64_t)a.v[r];
+                    int64_t y = ty == IGL_T_I32 ? (int64_t)(int32_t)b.v[r] : (int64_t)b.v[r];
+                    const bool live = (d.ok >> r) & 1;  // arrow evaluates valid slots only
+                    const int64_t mn = ty == IGL_T_I32 ? (int64_t)INT32_MIN : INT64_MIN;
+                    int64_t z = 0;
+                    if (y == 0) { if (live) ef |= ERRF_DIV_ZERO; }
+                    else if (y == -1) {
+                        if (op == IGL_OP_DIV) { if (x == mn) { if (live) ef |= ERRF_OVERFLOW; } else z = -x; }
+                    } else z = op == IGL_OP_DIV ? x / y : x % y;
+                    d.v[r] = (uint64_t)z;
+                }
+                if (ef) atomicOr(err_flags, ef);
+            }
+            break;
+        }
+        case IGL_OP_NEG: {
+            d.ok = a.ok;
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+                d.v[r] = ty == IGL_T_F64 ? (a.v[r] ^ 0x8000000000000000ull) : (0ull - a.v[r]);
+            break;
+        }
+        case IGL_OP_AND: case IGL_OP_OR: {  // Kleene
+            uint32_t ok = 0;
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const bool av = (a.ok >> r) & 1, bv = (b.ok >> r) & 1;
+                const bool x = av && (a.v[r] & 1), y = bv && (b.v[r] & 1);
+                bool val, known;
+                if (op == IGL_OP_AND) { const bool kf = (av && !x) || (bv && !y); known = kf || (av && bv); val = !kf && av && bv; }
+                else { const bool kt = x || y; known = kt || (av && bv); val = kt; }
+                d.v[r] = val ? 1 : 0;
+                ok |= (known ? 1u : 0u) << r;
+            }
+            d.ok = HAS_NULLS ? ok : 0xF;
+            break;
+        }
+        case IGL_OP_NOT:
+            d.ok = a.ok;
+#pragma unroll
+            for (int r = 0; r < 4; ++r) d.v[r] = (a.v[r] & 1) ^ 1;
+            break;
+        case IGL_OP_IS_NULL: case IGL_OP_IS_NOT_NULL:
+            d.ok = 0xF;
+#pragma unroll
+            for (int r = 0; r < 4; ++r) d.v[r] = (((a.ok >> r) & 1) != 0) == (op == IGL_OP_IS_NOT_NULL) ? 1 : 0;
+            break;
+        case IGL_OP_CAST: {
+            d.ok = a.ok;
+            const int to = in.aux;
+            uint32_t ef = 0;
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const bool live = (a.ok >> r) & 1;
+                uint64_t z = 0;
+                if (ty == IGL_T_I32 && to == IGL_T_I64) z = (uint64_t)(int64_t)(int32_t)a.v[r];
+                else if (ty == IGL_T_I32 && to == IGL_T_F64) z = (uint64_t)__double_as_longlong((double)(int32_t)a.v[r]);
+                else if (ty == IGL_T_I64 && to == IGL_T_F64) z = (uint64_t)__double_as_longlong(__ll2double_rn((long long)a.v[r]));
+                else if (ty == IGL_T_I64 && to == IGL_T_I32) {
+                    int64_t x = (int64_t)a.v[r];
+                    if (x < INT32_MIN || x > INT32_MAX) { if (live) ef |= ERRF_CAST; } else z = (uint64_t)(uint32_t)(int32_t)x;
+                } else if (ty == IGL_T_F64 && to == IGL_T_I32) {
+                    double t = trunc(__longlong_as_double((long long)a.v[r]));
+                    if (!(t >= -2147483648.0 && t <= 2147483647.0)) { if (live) ef |= ERRF_CAST; } else z = (uint64_t)(uint32_t)(int32_t)t;
+                } else if (ty == IGL_T_F64 && to == IGL_T_I64) {
+                    double t = trunc(__longlong_as_double((long long)a.v[r]));
+                    if (!(t >= -9223372036854775808.0 && t < 9223372036854775808.0)) { if (live) ef |= ERRF_CAST; } else z = (uint64_t)(int64_t)t;
+                } else z = a.v[r];
+                d.v[r] = z;
+            }
+            if (ef) atomicOr(err_flags, ef);
+            break;
+        }
+        default:
+            d = a;
+            break;
+    }
+    return d;
+}
+
+template <bool HAS_NULLS>
+__device__ __forceinline__ V fetch(const FpParams& P, uint8_t kind, uint8_t idx, uint64_t lit, bool lit_null,
+                                   const uint8_t* stage, int row0, const V& r0, const V& r1, const V& r2,
+                                   const V& r3) {
+    V x;
+    if (kind == OPK_REG) {
+        REG_READ(x, idx)
+    } else if (kind == OPK_COL) {
+        x = load_col<HAS_NULLS>(P, idx, stage, row0);
+    } else {
+        x.v[0] = x.v[1] = x.v[2] = x.v[3] = lit;
+        x.ok = (HAS_NULLS && lit_null) ? 0 : 0xF;
+    }
+    return x;
+}
+
+// Runs expression `e` of the fused program on this lane's 4 rows.
+template <bool HAS_NULLS>
+__device__ __forceinline__ V run_expr(const FpParams& P, int e, const uint8_t* stage, int row0) {
+    V r0, r1, r2, r3;
+    r0.ok = r1.ok = r2.ok = r3.ok = 0xF;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) r0.v[r] = r1.v[r] = r2.v[r] = r3.v[r] = 0;
+    const int first = P.expr_first[e], last = first + P.expr_count[e];
+    for (int pc = first; pc < last; ++pc) {
+        const Instr& in = P.code[pc];
+        const bool is_cast = in.op == IGL_OP_CAST;
+        V a = fetch<HAS_NULLS>(P, in.a_kind, in.a_idx, in.a_lit, !is_cast && (in.aux & AUX_A_NULL), stage, row0, r0, r1, r2, r3);
+        V b = a;
+        if (in.b_kind != OPK_NONE)
+            b = fetch<HAS_NULLS>(P, in.b_kind, in.b_idx, in.b_lit, !is_cast && (in.aux & AUX_B_NULL), stage, row0, r0, r1, r2, r3);
+        V d = exec_op<HAS_NULLS>(in, a, b, &P.T.hdr->err_flags);
+        REG_WRITE(in.dst, d)
+    }
+    V out;
+    REG_READ(out, P.expr_reg[e])
+    return out;
+}
+
+template <int SUBS, bool HAS_PRED, bool HAS_NULLS>
+__global__ void __launch_bounds__(kPipeThreads, 2) fp_kernel(const __grid_constant__ FpParams P) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ PipeShared<SUBS> sh;
+    TilePipe<SUBS, HAS_PRED, HAS_NULLS> pipe(P.T, sh, smem);
+    pipe.init();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp == kPipeComputeWarps) {
+        pipe.control_loop();
+        return;
+    }
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    for (int it = 0;; ++it) {
+        const uint8_t* stage;
+        long long row_begin;
+        int rows_in_tile;
+        if (!pipe.acquire(it, stage, row_begin, rows_in_tile)) break;
+
+        uint32_t keep[SUBS][4];   // ballots: bit = lane whose row (r*32 + lane) survives
+        long long wcount[SUBS];
+#pragma unroll
+        for (int sub = 0; sub < SUBS; ++sub) {
+            const int row0 = sub * kPipeRowsPerSub + warp * 128 + lane;
+            V m;
+            if (HAS_PRED) m = run_expr<HAS_NULLS>(P, 0, stage, row0);
+            wcount[sub] = 0;
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                bool k = (row0 + r * 32) < rows_in_tile;
+                if (HAS_PRED) k = k && ((m.ok >> r) & 1) && (m.v[r] & 1);   // null mask => row dropped
+                keep[sub][r] = __ballot_sync(0xffffffffu, k);
+                wcount[sub] += __popc(keep[sub][r]);
+            }
+        }
+        long long wbase[SUBS];
+        if (HAS_PRED) {
+            pipe.offsets(it, warp, wcount, wbase);
+        } else {
+#pragma unroll
+            for (int sub = 0; sub < SUBS; ++sub) wbase[sub] = row_begin + sub * kPipeRowsPerSub + warp * 128;
+        }
+
+        const int e0 = HAS_PRED ? 1 : 0;
+        for (int j = 0; j < P.n_out; ++j) {
+            uint8_t* od = reinterpret_cast<uint8_t*>(P.out_data[j]);
+            uint8_t* ov = HAS_NULLS ? P.out_valid[j] : nullptr;
+            const int osh = P.out_shift[j];
+#pragma unroll
+            for (int sub = 0; sub < SUBS; ++sub) {
+                if (wcount[sub] == 0) continue;   // warp-uniform
+                const int row0 = sub * kPipeRowsPerSub + warp * 128 + lane;
+                const V val = run_expr<HAS_NULLS>(P, e0 + j, stage, row0);
+                long long pos = wbase[sub];
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    const uint32_t kb = keep[sub][r];
+                    if ((kb >> lane) & 1u) {
+                        const long long p = pos + __popc(kb & lt_mask);
+                        if (osh == 2) st_cs_u32(od + (p << 2), (uint32_t)val.v[r]);
+                        else if (osh == 3) st_cs_u64(od + (p << 3), val.v[r]);
+                        else od[p] = (uint8_t)(val.v[r] & 1);
+                        if (HAS_NULLS && ov) ov[p] = (uint8_t)((val.ok >> r) & 1u);
+                    }
+                    pos += __popc(kb);
+                }
+            }
+        }
+        pipe.release(it);
+    }
+}
+
+// byte-per-row {0,1} -> Arrow bitmap; n is read from the device-side row count.
+__global__ void pack_bits_kernel(const uint8_t* __restrict__ bytes, uint32_t* __restrict__ bits,
+                                 const long long* n_ptr, long long n_fixed) {
+    const long long n = n_ptr ? *n_ptr : n_fixed;
+    const long long nwords = (n + 31) >> 5;
+    const int lane = threadIdx.x & 31;
+    for (long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < nwords;
+         w += ((long long)gridDim.x * blockDim.x) >> 5) {
+        const long long i = (w << 5) + lane;
+        const bool b = i < n && bytes[i] != 0;
+        const uint32_t word = __ballot_sync(0xffffffffu, b);
+        if (lane == 0) bits[w] = word;
+    }
+}
+
+cudaError_t launch_pack_bits(const uint8_t* bytes, uint32_t* bits, const long long* n_ptr, long long n_fixed,
+                             long long cap_rows, int sm_count, cudaStream_t st) {
+    long long blocks = (cap_rows + 255) / 256;
+    if (blocks < 1) blocks = 1;
+    if (blocks > (long long)sm_count * 8) blocks = (long long)sm_count * 8;
+    pack_bits_kernel<<<(int)blocks, 256, 0, st>>>(bytes, bits, n_ptr, n_fixed);
+    return cudaGetLastError();
+}
+
+}  // namespace igl
+
+using namespace igl;
+
+struct igl_fp {
+    igl_ctx* ctx = nullptr;
+    FpParams params{};
+    bool has_pred = false, has_nulls = false;
+    int subs = 2;
+    int n_in = 0;
+    std::vector<int> in_types;
+    std::vector<int> slot_of_col;            // schema column -> staged slot, -1 = not read
+    std::vector<int> out_types;
+    std::vector<uint8_t> out_nullable;
+    size_t smem_bytes = 0;
+    int grid_cap = 0;
+    // scratch (grow-only): header + tile status words; temp byte planes for bit outputs
+    void* scratch = nullptr;
+    size_t scratch_bytes = 0;
+    std::vector<void*> tmp_bytes;            // per output: boolean byte plane
+    std::vector<void*> tmp_valid;            // per output: validity byte plane
+    int64_t tmp_rows = 0;
+    std::vector<igl_dev_col> last_out;
+    int64_t last_nrows = 0;
+    PipeHeader* host_hdr = nullptr;          // pinned
+    bool launched = false;
+};
+
+namespace {
+
+typedef void (*fp_kernel_t)(const FpParams);
+
+fp_kernel_t pick_kernel(int subs, bool pred, bool nulls) {
+    if (subs == 2) {
+        if (pred) return nulls ? fp_kernel<2, true, true> : fp_kernel<2, true, false>;
+        return nulls ? fp_kernel<2, false, true> : fp_kernel<2, false, false>;
+    }
+    if (pred) return nulls ? fp_kernel<1, true, true> : fp_kernel<1, true, false>;
+    return nulls ? fp_kernel<1, false, true> : fp_kernel<1, false, false>;
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t igl_fp_create(igl_ctx* ctx, const int32_t* in_types, const uint8_t* in_nullable, int32_t n_in,
+                      const igl_expr* pred, const igl_expr* const* proj, int32_t nproj, igl_fp** out) {
+    if (!ctx || !out || n_in <= 0 || !in_types) return fail(IGL_ERR_INVALID_ARG, "igl_fp_create: bad arguments");
+    *out = nullptr;
+    if (nproj < 0 || (nproj > 0 && !proj)) return fail(IGL_ERR_INVALID_ARG, "igl_fp_create: bad projection list");
+    if (pred && pred->type != IGL_T_BOOL)
+        return fail(IGL_ERR_PREDICATE_NOT_BOOLEAN, "Filter predicate must return boolean array");  // filter.rs:50-55
+    auto fp = std::make_unique<igl_fp>();
+    fp->ctx = ctx;
+    fp->n_in = n_in;
+    fp->in_types.assign(in_types, in_types + n_in);
+    fp->has_pred = pred != nullptr;
+
+    // FilterExec: nproj == 0 passes every input column through.
+    std::vector<std::unique_ptr<igl_expr>> owned;
+    std::vector<const igl_expr*> outs;
+    if (nproj == 0) {
+        for (int c = 0; c < n_in; ++c) {
+            uint8_t bc[3] = {IGL_OP_COL, (uint8_t)(c & 0xFF), (uint8_t)(c >> 8)};
+            igl_expr* e = nullptr;
+            IGL_TRY(igl_expr_compile(ctx, bc, 3, in_types, in_nullable, n_in, &e));
+            owned.emplace_back(e);
+            outs.push_back(e);
+        }
+    } else {
+        for (int j = 0; j < nproj; ++j) {
+            if (!proj[j]) return fail(IGL_ERR_INVALID_ARG, "igl_fp_create: projection %d is NULL", j);
+            outs.push_back(proj[j]);
+        }
+    }
+    if ((int)outs.size() > kMaxOut) return fail(IGL_ERR_UNSUPPORTED, "more than %d output columns", kMaxOut);
+    for (auto* e : outs) {
+        if (e->ncols != n_in) return fail(IGL_ERR_INVALID_ARG, "expression compiled against a different schema");
+        if (e->type == IGL_T_UTF8) return fail(IGL_ERR_UNSUPPORTED, "Utf8 output columns go through the operator API (gather by row index)");
+    }
+
+    // which columns are read
+    std::vector<bool> used(n_in, false);
+    if (pred) referenced_columns(*pred, used);
+    for (auto* e : outs) referenced_columns(*e, used);
+    fp->slot_of_col.assign(n_in, -1);
+    FpParams& P = fp->params;
+    uint8_t shifts[kMaxCols] = {};
+    int nslots = 0;
+    for (int c = 0; c < n_in; ++c) {
+        if (!used[c]) continue;
+        if (nslots >= kMaxCols) return fail(IGL_ERR_UNSUPPORTED, "more than %d input columns referenced", kMaxCols);
+        int t = in_types[c];
+        if (t == IGL_T_UTF8) return fail(IGL_ERR_UNSUPPORTED, "Utf8 columns cannot be read by device expressions");
+        shifts[nslots] = t == IGL_T_BOOL ? 0xFF : (t == IGL_T_I32 ? 2 : 3);
+        fp->slot_of_col[c] = nslots++;
+        if (in_nullable && in_nullable[c]) fp->has_nulls = true;
+    }
+    if (pred && pred->nullable) fp->has_nulls = true;
+    for (auto* e : outs) if (e->nullable) fp->has_nulls = true;
+
+    // lower: expression 0 = predicate (if any), then the outputs
+    std::vector<Instr> code;
+    std::vector<const igl_expr*> all;
+    if (pred) all.push_back(pred);
+    for (auto* e : outs) all.push_back(e);
+    for (size_t i = 0; i < all.size(); ++i) {
+        LoweredExpr le;
+        IGL_TRY(lower_expr(*all[i], code, le));
+        P.expr_first[i] = (uint8_t)le.first;
+        P.expr_count[i] = (uint8_t)le.count;
+        P.expr_reg[i] = (uint8_t)le.result_reg;
+    }
+    for (auto& in : code) {  // schema column index -> staged slot
+        if (in.a_kind == OPK_COL) in.a_idx = (uint8_t)fp->slot_of_col[in.a_idx];
+        if (in.b_kind == OPK_COL) in.b_idx = (uint8_t)fp->slot_of_col[in.b_idx];
+    }
+    memcpy(P.code, code.data(), code.size() * sizeof(Instr));
+    P.n_out = (uint8_t)outs.size();
+    for (size_t j = 0; j < outs.size(); ++j) {
+        fp->out_types.push_back(outs[j]->type);
+        fp->out_nullable.push_back(outs[j]->nullable ? 1 : 0);
+        P.out_shift[j] = outs[j]->type == IGL_T_BOOL ? 0 : (outs[j]->type == IGL_T_I32 ? 2 : 3);
+    }
+
+    // shared-memory ring geometry
+    PipeGeometry geo = pipe_geometry(shifts, nslots, P.T);
+    if (!geo.ok) return fail(IGL_ERR_UNSUPPORTED, "referenced columns need %u bytes per tile; too wide for one pass", geo.stage_bytes);
+    fp->subs = geo.subs;
+    fp->smem_bytes = (size_t)geo.stage_bytes * geo.stages;
+
+    DeviceGuard g(ctx->device);
+    fp_kernel_t k = pick_kernel(fp->subs, fp->has_pred, fp->has_nulls);
+    IGL_CUDA_OK(cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fp->smem_bytes));
+    int per_sm = 0;
+    IGL_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)k, kPipeThreads, fp->smem_bytes));
+    if (per_sm < 1) return fail(IGL_ERR_INTERNAL, "filter/project kernel does not fit on an SM (smem %zu)", fp->smem_bytes);
+    fp->grid_cap = per_sm * ctx->sm_count;
+    IGL_CUDA_OK(cudaHostAlloc((void**)&fp->host_hdr, sizeof(PipeHeader), cudaHostAllocDefault));
+    fp->tmp_bytes.assign(outs.size(), nullptr);
+    fp->tmp_valid.assign(outs.size(), nullptr);
+    *out = fp.release();
+    return IGL_OK;
+}
+
+int32_t igl_fp_num_outputs(const igl_fp* fp) { return fp ? (int32_t)fp->out_types.size() : 0; }
+
+int32_t igl_fp_output_type(const igl_fp* fp, int32_t j, int32_t* type, int32_t* nullable) {
+    if (!fp || j < 0 || j >= (int)fp->out_types.size()) return fail(IGL_ERR_INVALID_ARG, "igl_fp_output_type: bad index");
+    if (type) *type = fp->out_types[j];
+    if (nullable) *nullable = fp->out_nullable[j];
+    return IGL_OK;
+}
+
+int32_t igl_fp_launch(igl_fp* fp, const igl_dev_col* in, int64_t nrows, igl_dev_col* out, void* stream) {
+    if (!fp || !in || !out || nrows < 0) return fail(IGL_ERR_INVALID_ARG, "igl_fp_launch: bad arguments");
+    igl_ctx* ctx = fp->ctx;
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = pick_stream(ctx, stream);
+    FpParams P = fp->params;
+    const int TILE = fp->subs * kPipeRowsPerSub;
+    P.T.nrows = nrows;
+    P.T.ntiles = (nrows + TILE - 1) / TILE;
+    for (int c = 0; c < fp->n_in; ++c) {
+        int s = fp->slot_of_col[c];
+        if (s < 0) continue;
+        if (in[c].type != fp->in_types[c]) return fail(IGL_ERR_INVALID_ARG, "input column %d has type %d, plan expects %d", c, in[c].type, fp->in_types[c]);
+        if (((uintptr_t)in[c].data & 15) || ((uintptr_t)in[c].validity & 15))
+            return fail(IGL_ERR_INVALID_ARG, "input column %d is not 16-byte aligned", c);
+        P.T.data[s] = (const uint8_t*)in[c].data;
+        P.T.valid[s] = fp->has_nulls ? in[c].validity : nullptr;
+    }
+    // scratch: header + status words
+    size_t need = 256 + (size_t)std::max<int64_t>(P.T.ntiles, 1) * 8;
+    if (need > fp->scratch_bytes) {
+        if (fp->scratch) pool_free(ctx, fp->scratch);
+        fp->scratch = nullptr; fp->scratch_bytes = 0;
+        IGL_TRY(pool_alloc(ctx, need, &fp->scratch));
+        fp->scratch_bytes = need;
+    }
+    P.T.hdr = (PipeHeader*)fp->scratch;
+    P.T.status = (uint64_t*)((uint8_t*)fp->scratch + 256);
+    IGL_CUDA_OK(cudaMemsetAsync(fp->scratch, 0, fp->has_pred ? need : 256, st));
+    // outputs (+ byte planes for bit-packed results)
+    const size_t nout = fp->out_types.size();
+    bool any_tmp = false;
+    for (size_t j = 0; j < nout; ++j) {
+        const bool want_valid = fp->has_nulls && fp->out_nullable[j];
+        if (!out[j].data) return fail(IGL_ERR_INVALID_ARG, "output column %zu has no data buffer", j);
+        if (want_valid && !out[j].validity) return fail(IGL_ERR_INVALID_ARG, "output column %zu is nullable but has no validity buffer", j);
+        if (fp->out_types[j] == IGL_T_BOOL || want_valid) any_tmp = true;
+    }
+    if (any_tmp && nrows > fp->tmp_rows) {
+        for (size_t j = 0; j < nout; ++j) {
+            if (fp->tmp_bytes[j]) { pool_free(ctx, fp->tmp_bytes[j]); fp->tmp_bytes[j] = nullptr; }
+            if (fp->tmp_valid[j]) { pool_free(ctx, fp->tmp_valid[j]); fp->tmp_valid[j] = nullptr; }
+        }
+        fp->tmp_rows = 0;
+    }
+    for (size_t j = 0; j < nout; ++j) {
+        const bool want_valid = fp->has_nulls && fp->out_nullable[j];
+        if (fp->out_types[j] == IGL_T_BOOL) {
+            if (!fp->tmp_bytes[j]) IGL_TRY(pool_alloc(ctx, (size_t)std::max<int64_t>(nrows, 1), &fp->tmp_bytes[j]));
+            P.out_data[j] = fp->tmp_bytes[j];
+        } else {
+            P.out_data[j] = out[j].data;
+        }
+        if (want_valid) {
+            if (!fp->tmp_valid[j]) IGL_TRY(pool_alloc(ctx, (size_t)std::max<int64_t>(nrows, 1), &fp->tmp_valid[j]));
+            P.out_valid[j] = (uint8_t*)fp->tmp_valid[j];
+        } else {
+            P.out_valid[j] = nullptr;
+        }
+    }
+    if (any_tmp) fp->tmp_rows = std::max(fp->tmp_rows, nrows);
+    fp->last_out.assign(out, out + nout);
+    fp->last_nrows = nrows;
+    fp->launched = true;
+    if (nrows == 0) return IGL_OK;
+
+    fp_kernel_t k = pick_kernel(fp->subs, fp->has_pred, fp->has_nulls);
+    int grid = (int)std::min<int64_t>(P.T.ntiles, fp->grid_cap);
+    k<<<grid, kPipeThreads, fp->smem_bytes, st>>>(P);
+    IGL_CUDA_OK(cudaGetLastError());
+    ctx->launches++;
+    const long long* n_ptr = fp->has_pred ? &P.T.hdr->out_count : nullptr;
+    for (size_t j = 0; j < nout; ++j) {
+        const bool want_valid = fp->has_nulls && fp->out_nullable[j];
+        if (fp->out_types[j] == IGL_T_BOOL) {
+            IGL_CUDA_OK(launch_pack_bits((const uint8_t*)fp->tmp_bytes[j], (uint32_t*)out[j].data, n_ptr, nrows, nrows, ctx->sm_count, st));
+            ctx->launches++;
+        }
+        if (want_valid) {
+            IGL_CUDA_OK(launch_pack_bits((const uint8_t*)fp->tmp_valid[j], (uint32_t*)out[j].validity, n_ptr, nrows, nrows, ctx->sm_count, st));
+            ctx->launches++;
+        }
+    }
+    return IGL_OK;
+}
+
+int32_t igl_fp_finish(igl_fp* fp, int64_t* out_rows, void* stream) {
+    if (!fp || !fp->launched) return fail(IGL_ERR_INVALID_ARG, "igl_fp_finish: nothing launched");
+    igl_ctx* ctx = fp->ctx;
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = pick_stream(ctx, stream);
+    fp->launched = false;
+    if (fp->last_nrows == 0) {
+        IGL_CUDA_OK(cudaStreamSynchronize(st));
+        if (out_rows) *out_rows = 0;
+        return IGL_OK;
+    }
+    IGL_CUDA_OK(cudaMemcpyAsync(fp->host_hdr, fp->scratch, sizeof(PipeHeader), cudaMemcpyDeviceToHost, st));
+    IGL_CUDA_OK(cudaStreamSynchronize(st));
+    const unsigned int ef = fp->host_hdr->err_flags;
+    if (ef & ERRF_DIV_ZERO) return fail(IGL_ERR_DIV_BY_ZERO, "Divide by zero error");
+    if (ef & ERRF_OVERFLOW) return fail(IGL_ERR_ARITH_OVERFLOW, "Arithmetic overflow: Overflow happened on division");
+    if (ef & ERRF_CAST) return fail(IGL_ERR_CAST, "Cast error: Can't cast value to the target integer type");
+    if (out_rows) *out_rows = fp->has_pred ? (int64_t)fp->host_hdr->out_count : fp->last_nrows;
+    return IGL_OK;
+}
+
+int32_t igl_fp_run(igl_fp* fp, const igl_dev_col* in, int64_t nrows, igl_dev_col* out, int64_t* out_rows, void* stream) {
+    IGL_TRY(igl_fp_launch(fp, in, nrows, out, stream));
+    return igl_fp_finish(fp, out_rows, stream);
+}
+
+void igl_fp_destroy(igl_fp* fp) {
+    if (!fp) return;
+    DeviceGuard g(fp->ctx->device);
+    if (fp->scratch) pool_free(fp->ctx, fp->scratch);
+    for (void* p : fp->tmp_bytes) if (p) pool_free(fp->ctx, p);
+    for (void* p : fp->tmp_valid) if (p) pool_free(fp->ctx, p);
+    if (fp->host_hdr) cudaFreeHost(fp->host_hdr);
+    delete fp;
+}
+
+}  // extern "C"

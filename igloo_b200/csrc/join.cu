@@ -1,0 +1,737 @@
+// join.cu — K5 build / K6 probe / K7 materialise for the hash join on
+// device-resident columns.
+//
+// Reference semantics implemented (crates/engine/src/operators/hash_join.rs):
+//   :35-76    output schema = left fields ++ right fields
+//   :100-128  build: the right child is drained into the table, duplicates kept
+//   :131-213  probe: per left row, one output row per stored right row with the
+//             same key; Left/Full: an unmatched left row is emitted once with a
+//             null per right field; Right == Inner, Full == Left (no unmatched
+//             right rows are ever produced, :189, :263-276)
+//   :117-122  key identity is the printed form: NULL == NULL, NaN == NaN,
+//             -0.0 != 0.0, keys of different Arrow types never match.
+// The reference keys a std HashMap by a heap string per row and emits 1-row
+// batches; here the key is its canonical 64-bit identity and rows are emitted in
+// bulk.
+//
+// Table: open addressing, linear probing, 16-byte slots {key, val}, claimed with
+// atomicCAS on the key word.  Two layouts, chosen by what the build side holds:
+//   unique keys (the optimistic first pass; any duplicate raises a flag and the
+//   build is redone)   val = the 8-byte payload itself when the right side is
+//                      (key, one fixed-width non-null column), else the row id
+//   duplicate keys     val = {count, run end}: a CSR of build row ids grouped by
+//                      key (count pass -> run allocation -> fill pass), so a
+//                      heavy key's matches are one contiguous run that a whole
+//                      warp walks together.
+// NULL keys and the one key value that equals the empty-slot sentinel live in
+// two side entries.
+//
+// Probe kernels reuse the tile pipeline (tile_pipe.cuh): left column tiles are
+// staged by bulk async copies, each lane looks up 4 keys with all first-slot
+// loads in flight together, output offsets come from the ordered look-back scan,
+// and output rows (left columns from shared memory ++ right payload) are written
+// once, to their final place.
+#include "internal.h"
+#include "kernels.h"
+#include "tile_pipe.cuh"
+
+#include <algorithm>
+#include <cstring>
+#include <memory>
+
+namespace igl {
+
+constexpr uint64_t kEmptyKey = 0x8000000000000000ull;
+constexpr uint32_t kNoRow = 0xFFFFFFFFu;
+constexpr int kJoinMaxCols = 16;
+
+struct Slot {
+    unsigned long long key;
+    unsigned long long val;
+};
+
+struct JoinSide {          // side entries: [0] NULL key, [1] key == kEmptyKey
+    unsigned int count[2];
+    unsigned int run_end[2];
+    unsigned long long val[2];
+    unsigned int dup_flag;
+    unsigned int pad;
+    unsigned long long cursor;   // CSR run allocator
+};
+
+struct JoinTable {
+    Slot* slots;
+    uint64_t mask;
+    int shift;               // 64 - log2(capacity)
+    JoinSide* side;
+    const uint32_t* rowids;  // CSR runs (duplicate layout)
+};
+
+__device__ __forceinline__ uint64_t canon_key(int type, uint64_t raw) {
+    switch (type) {
+        case IGL_T_I32: return (uint64_t)(int64_t)(int32_t)raw;
+        case IGL_T_F64: {
+            // every NaN prints as "NaN"; everything else round-trips its bits
+            const bool nan = (raw & 0x7FFFFFFFFFFFFFFFull) > 0x7FF0000000000000ull;
+            return nan ? 0x7FF8000000000000ull : raw;
+        }
+        case IGL_T_BOOL: return raw & 1;
+        default: return raw;
+    }
+}
+
+__device__ __forceinline__ uint64_t load_key_global(const void* keys, int type, long long i) {
+    if (type == IGL_T_I32) return (uint32_t)((const int32_t*)keys)[i];
+    if (type == IGL_T_BOOL) return (((const uint8_t*)keys)[i >> 3] >> (i & 7)) & 1;
+    return ((const uint64_t*)keys)[i];
+}
+
+__device__ __forceinline__ bool bit_at(const uint8_t* bm, long long i) { return (bm[i >> 3] >> (i & 7)) & 1; }
+
+// ---- table init ---------------------------------------------------------------------
+__global__ void join_init_kernel(Slot* slots, uint64_t capacity, JoinSide* side) {
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    ulonglong2 e; e.x = kEmptyKey; e.y = 0;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < capacity; i += stride)
+        *reinterpret_cast<ulonglong2*>(slots + i) = e;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        side->count[0] = side->count[1] = 0; side->run_end[0] = side->run_end[1] = 0;
+        side->val[0] = side->val[1] = 0; side->dup_flag = 0; side->cursor = 0;
+    }
+}
+
+// ---- K5 build, unique layout ---------------------------------------------------------
+// payload_shift: 2 / 3 = width of the inlined payload column, 0xFF = store the row id.
+__global__ void join_build_unique_kernel(const void* __restrict__ keys, int key_type, const uint8_t* __restrict__ key_valid,
+                                         const void* __restrict__ payload, int payload_shift, long long n, JoinTable t) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        unsigned long long val = payload_shift == 0xFF ? (unsigned long long)i
+                                 : payload_shift == 2 ? (unsigned long long)((const uint32_t*)payload)[i]
+                                                      : ((const unsigned long long*)payload)[i];
+        const bool valid = !key_valid || bit_at(key_valid, i);
+        const uint64_t k = valid ? canon_key(key_type, load_key_global(keys, key_type, i)) : 0;
+        if (!valid || k == kEmptyKey) {
+            const int sidx = valid ? 1 : 0;
+            if (atomicAdd(&t.side->count[sidx], 1u) == 0) t.side->val[sidx] = val;
+            else t.side->dup_flag = 1;
+            continue;
+        }
+        uint64_t h = mix64(k) >> t.shift;
+        while (true) {
+            const unsigned long long prev = atomicCAS(&t.slots[h].key, (unsigned long long)kEmptyKey, (unsigned long long)k);
+            if (prev == kEmptyKey) { t.slots[h].val = val; break; }
+            if (prev == k) { t.side->dup_flag = 1; break; }
+            h = (h + 1) & t.mask;
+        }
+    }
+}
+
+// ---- K5 build, duplicate layout: count, allocate runs, fill --------------------------------
+__global__ void join_build_count_kernel(const void* __restrict__ keys, int key_type, const uint8_t* __restrict__ key_valid,
+                                        long long n, JoinTable t) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const bool valid = !key_valid || bit_at(key_valid, i);
+        const uint64_t k = valid ? canon_key(key_type, load_key_global(keys, key_type, i)) : 0;
+        if (!valid || k == kEmptyKey) { atomicAdd(&t.side->count[valid ? 1 : 0], 1u); continue; }
+        uint64_t h = mix64(k) >> t.shift;
+        while (true) {
+            const unsigned long long prev = atomicCAS(&t.slots[h].key, (unsigned long long)kEmptyKey, (unsigned long long)k);
+            if (prev == kEmptyKey || prev == k) { atomicAdd(&t.slots[h].val, 1ull << 32); break; }
+            h = (h + 1) & t.mask;
+        }
+    }
+}
+
+__global__ void join_build_runs_kernel(JoinTable t, uint64_t capacity) {
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    const int lane = threadIdx.x & 31;
+    for (uint64_t i0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) - lane; i0 < capacity; i0 += stride) {
+        const uint64_t i = i0 + lane;
+        unsigned long long cnt = 0;
+        if (i < capacity && t.slots[i].key != kEmptyKey) cnt = t.slots[i].val >> 32;
+        // one atomic per warp: warp-scan the counts, lane 31 reserves the warp's block of runs
+        unsigned long long inc = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long nb = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += nb;
+        }
+        unsigned long long base = 0;
+        if (lane == 31 && inc) base = atomicAdd(&t.side->cursor, inc);
+        base = __shfl_sync(0xffffffffu, base, 31);
+        if (cnt) t.slots[i].val = (cnt << 32) | (base + inc - cnt);   // low word: run start, advanced by the fill pass
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        for (int s = 0; s < 2; ++s)
+            if (t.side->count[s]) t.side->run_end[s] = (unsigned int)atomicAdd(&t.side->cursor, (unsigned long long)t.side->count[s]);
+    }
+}
+
+__global__ void join_build_fill_kernel(const void* __restrict__ keys, int key_type, const uint8_t* __restrict__ key_valid,
+                                       long long n, JoinTable t, uint32_t* __restrict__ rowids) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const bool valid = !key_valid || bit_at(key_valid, i);
+        const uint64_t k = valid ? canon_key(key_type, load_key_global(keys, key_type, i)) : 0;
+        unsigned int pos;
+        if (!valid || k == kEmptyKey) pos = atomicAdd(&t.side->run_end[valid ? 1 : 0], 1u);
+        else {
+            uint64_t h = mix64(k) >> t.shift;
+            while (t.slots[h].key != k) h = (h + 1) & t.mask;
+            pos = atomicAdd(reinterpret_cast<unsigned int*>(&t.slots[h].val), 1u);   // little endian: the low word
+        }
+        rowids[pos] = (uint32_t)i;   // after this pass the low word / run_end is the END of the run
+    }
+}
+
+// ---- probe ---------------------------------------------------------------------------------
+struct JoinProbeParams {
+    PipeCols T;                       // every left column, staged
+    JoinTable table;
+    int key_slot, key_type;           // left key column
+    int never_match;                  // left / right key types differ: nothing can match
+    int n_left, n_right;
+    int right_key_col;                // index among the right columns
+    int payload_col;                  // unique layout with inlined payload: that right column; else -1
+    int left_join;
+    void* out_data[2 * kJoinMaxCols];
+    uint8_t* out_valid[2 * kJoinMaxCols];   // byte-per-row validity planes (packed afterwards) or NULL
+    uint8_t out_shift[2 * kJoinMaxCols];
+    const uint8_t* right_data[kJoinMaxCols];
+    const uint8_t* right_valid[kJoinMaxCols];
+};
+
+struct Match {
+    unsigned long long val;   // unique: payload or row id;  duplicate: {count, run end}
+    bool hit;
+};
+
+// Looks up this lane's 4 keys; all first-slot loads are issued before any is used.
+template <bool HAS_NULLS>
+__device__ __forceinline__ void lookup4(const JoinProbeParams& P, const uint8_t* stage, int row0, int rows_in_tile,
+                                        uint64_t (&raw)[4], Match (&m)[4]) {
+    const uint8_t* kb = stage + P.T.smem_off[P.key_slot];
+    const int ksh = P.T.shift[P.key_slot];
+    uint64_t k[4], h[4];
+    Slot s[4];
+    int kind[4];   // 0 = regular, 1 = side entry, 2 = no lookup
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const int row = row0 + r * 32;
+        raw[r] = ksh == 2 ? (uint64_t) * reinterpret_cast<const uint32_t*>(kb + (row << 2))
+                 : ksh == 3 ? *reinterpret_cast<const uint64_t*>(kb + (row << 3))
+                            : (uint64_t)((kb[row >> 3] >> (row & 7)) & 1);
+        bool valid = true;
+        if (HAS_NULLS && P.T.valid[P.key_slot]) valid = bit_at(stage + P.T.valid_off[P.key_slot], row);
+        k[r] = canon_key(P.key_type, raw[r]);
+        kind[r] = (row >= rows_in_tile || P.never_match) ? 2 : (!valid ? 1 : (k[r] == kEmptyKey ? 1 : 0));
+        m[r].hit = false; m[r].val = 0;
+        if (kind[r] == 1) {
+            const int sidx = valid ? 1 : 0;
+            if (P.table.side->count[sidx]) {
+                m[r].hit = true;
+                m[r].val = P.table.rowids ? (((unsigned long long)P.table.side->count[sidx] << 32) | P.table.side->run_end[sidx])
+                                          : P.table.side->val[sidx];
+            }
+        }
+        h[r] = mix64(k[r]) >> P.table.shift;
+        if (kind[r] == 0) {
+            const ulonglong2 v = ld_nc_u64x2(P.table.slots + h[r]);
+            s[r].key = v.x; s[r].val = v.y;
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        if (kind[r] != 0) continue;
+        while (s[r].key != k[r] && s[r].key != kEmptyKey) {
+            h[r] = (h[r] + 1) & P.table.mask;
+            const ulonglong2 v = ld_nc_u64x2(P.table.slots + h[r]);
+            s[r].key = v.x; s[r].val = v.y;
+        }
+        if (s[r].key == k[r]) { m[r].hit = true; m[r].val = s[r].val; }
+    }
+}
+
+// Writes one output row: left columns from the staged tile, right columns from
+// the inlined payload (unique layout) or gathered by build row id.
+template <bool HAS_NULLS>
+__device__ __forceinline__ void emit_row(const JoinProbeParams& P, const uint8_t* stage, int row, long long pos,
+                                         bool matched, unsigned long long val, uint64_t raw_key) {
+    for (int c = 0; c < P.n_left; ++c) {
+        const uint8_t* src = stage + P.T.smem_off[c];
+        if (P.out_shift[c] == 2) st_cs_u32((uint8_t*)P.out_data[c] + (pos << 2), *reinterpret_cast<const uint32_t*>(src + (row << 2)));
+        else st_cs_u64((uint8_t*)P.out_data[c] + (pos << 3), *reinterpret_cast<const uint64_t*>(src + (row << 3)));
+        if (HAS_NULLS && P.out_valid[c]) P.out_valid[c][pos] = P.T.valid[c] ? (uint8_t)bit_at(stage + P.T.valid_off[c], row) : (uint8_t)1;
+    }
+    for (int c = 0; c < P.n_right; ++c) {
+        const int oc = P.n_left + c;
+        uint64_t v = 0;
+        uint8_t ok = matched ? 1 : 0;
+        if (matched) {
+            if (P.payload_col >= 0) {
+                v = c == P.payload_col ? val : raw_key;   // inlined payload; the key column is the probe key itself
+            } else {
+                const uint32_t rid = (uint32_t)val;
+                v = P.out_shift[oc] == 2 ? (uint64_t)((const uint32_t*)P.right_data[c])[rid] : ((const uint64_t*)P.right_data[c])[rid];
+                if (HAS_NULLS && P.right_valid[c]) ok = (uint8_t)bit_at(P.right_valid[c], rid);
+            }
+        }
+        if (P.out_shift[oc] == 2) st_cs_u32((uint8_t*)P.out_data[oc] + (pos << 2), (uint32_t)v);
+        else st_cs_u64((uint8_t*)P.out_data[oc] + (pos << 3), v);
+        if (HAS_NULLS && P.out_valid[oc]) P.out_valid[oc][pos] = ok;
+    }
+}
+
+// K6/K7, unique layout: at most one output row per probe row.
+template <int SUBS, bool HAS_NULLS>
+__global__ void __launch_bounds__(kPipeThreads, 2) join_probe_unique_kernel(const __grid_constant__ JoinProbeParams P) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ PipeShared<SUBS> sh;
+    TilePipe<SUBS, true, HAS_NULLS> pipe(P.T, sh, smem);
+    pipe.init();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp == kPipeComputeWarps) { pipe.control_loop(); return; }
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    for (int it = 0;; ++it) {
+        const uint8_t* stage; long long row_begin; int rows_in_tile;
+        if (!pipe.acquire(it, stage, row_begin, rows_in_tile)) break;
+        uint32_t keep[SUBS][4], hitb[SUBS][4];
+        unsigned long long val[SUBS][4];
+        uint64_t raw[SUBS][4];
+        long long wcount[SUBS];
+#pragma unroll
+        for (int sub = 0; sub < SUBS; ++sub) {
+            const int row0 = sub * kPipeRowsPerSub + warp * 128 + lane;
+            Match m[4];
+            lookup4<HAS_NULLS>(P, stage, row0, rows_in_tile, raw[sub], m);
+            wcount[sub] = 0;
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const bool inr = (row0 + r * 32) < rows_in_tile;
+                val[sub][r] = m[r].val;
+                hitb[sub][r] = __ballot_sync(0xffffffffu, m[r].hit);
+                keep[sub][r] = __ballot_sync(0xffffffffu, inr && (m[r].hit || P.left_join));
+                wcount[sub] += __popc(keep[sub][r]);
+            }
+        }
+        long long wbase[SUBS];
+        pipe.offsets(it, warp, wcount, wbase);
+#pragma unroll
+        for (int sub = 0; sub < SUBS; ++sub) {
+            const int row0 = sub * kPipeRowsPerSub + warp * 128 + lane;
+            long long pos = wbase[sub];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const uint32_t kb = keep[sub][r];
+                if ((kb >> lane) & 1u)
+                    emit_row<HAS_NULLS>(P, stage, row0 + r * 32, pos + __popc(kb & lt_mask), (hitb[sub][r] >> lane) & 1u,
+                                        val[sub][r], raw[sub][r]);
+                pos += __popc(kb);
+            }
+        }
+        pipe.release(it);
+    }
+}
+
+// K6/K7, duplicate layout: a probe row emits `count` rows; runs longer than a
+// warp are walked by the whole warp.
+template <int SUBS, bool HAS_NULLS>
+__global__ void __launch_bounds__(kPipeThreads, 2) join_probe_multi_kernel(const __grid_constant__ JoinProbeParams P) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ PipeShared<SUBS> sh;
+    TilePipe<SUBS, true, HAS_NULLS> pipe(P.T, sh, smem);
+    pipe.init();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp == kPipeComputeWarps) { pipe.control_loop(); return; }
+    for (int it = 0;; ++it) {
+        const uint8_t* stage; long long row_begin; int rows_in_tile;
+        if (!pipe.acquire(it, stage, row_begin, rows_in_tile)) break;
+        uint32_t cnt[SUBS][4], excl[SUBS][4], rend[SUBS][4];
+        uint32_t hitb[SUBS][4];
+        long long wcount[SUBS];
+#pragma unroll
+        for (int sub = 0; sub < SUBS; ++sub) {
+            const int row0 = sub * kPipeRowsPerSub + warp * 128 + lane;
+            Match m[4];
+            uint64_t raw[4];
+            lookup4<HAS_NULLS>(P, stage, row0, rows_in_tile, raw, m);
+            uint32_t running = 0;
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const bool inr = (row0 + r * 32) < rows_in_tile;
+                uint32_t c = m[r].hit ? (uint32_t)(m[r].val >> 32) : ((inr && P.left_join) ? 1u : 0u);
+                if (!inr) c = 0;
+                hitb[sub][r] = __ballot_sync(0xffffffffu, m[r].hit);
+                rend[sub][r] = (uint32_t)m[r].val;
+                uint32_t inc = c;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t nb = __shfl_up_sync(0xffffffffu, inc, o);
+                    if (lane >= o) inc += nb;
+                }
+                cnt[sub][r] = c;
+                excl[sub][r] = running + inc - c;
+                running += __shfl_sync(0xffffffffu, inc, 31);
+            }
+            wcount[sub] = (long long)running;
+        }
+        long long wbase[SUBS];
+        pipe.offsets(it, warp, wcount, wbase);
+#pragma unroll
+        for (int sub = 0; sub < SUBS; ++sub) {
+            const int row0 = sub * kPipeRowsPerSub + warp * 128 + lane;
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const int row = row0 + r * 32;
+                const uint32_t c = cnt[sub][r];
+                const bool hit = (hitb[sub][r] >> lane) & 1u;
+                const long long pos = wbase[sub] + excl[sub][r];
+                const bool heavy = c > 32;
+                if (c && !heavy) {
+                    if (!hit) emit_row<HAS_NULLS>(P, stage, row, pos, false, 0, 0);
+                    else
+                        for (uint32_t j = 0; j < c; ++j)
+                            emit_row<HAS_NULLS>(P, stage, row, pos + j, true, P.table.rowids[rend[sub][r] - c + j], 0);
+                }
+                uint32_t hv = __ballot_sync(0xffffffffu, heavy);
+                while (hv) {   // warp-cooperative walk of one long run
+                    const int src = __ffs(hv) - 1;
+                    hv &= hv - 1;
+                    const uint32_t hc = __shfl_sync(0xffffffffu, c, src);
+                    const uint32_t he = __shfl_sync(0xffffffffu, rend[sub][r], src);
+                    const long long hp = __shfl_sync(0xffffffffu, pos, src);
+                    const int hrow = row - lane + src;
+                    for (uint32_t j = lane; j < hc; j += 32)
+                        emit_row<HAS_NULLS>(P, stage, hrow, hp + j, true, P.table.rowids[he - hc + j], 0);
+                }
+            }
+        }
+        pipe.release(it);
+    }
+}
+
+// Exact output row count of a probe call (needed to size the output of the
+// duplicate layout; also serves igl_join_probe_count for the unique layout).
+__global__ void join_probe_count_kernel(const void* __restrict__ keys, int key_type, const uint8_t* __restrict__ key_valid,
+                                        long long n, JoinTable t, int csr, int left_join, int never_match,
+                                        unsigned long long* total) {
+    unsigned long long local = 0;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        unsigned long long c = 0;
+        if (!never_match) {
+            const bool valid = !key_valid || bit_at(key_valid, i);
+            const uint64_t k = valid ? canon_key(key_type, load_key_global(keys, key_type, i)) : 0;
+            if (!valid || k == kEmptyKey) c = csr ? t.side->count[valid ? 1 : 0] : (t.side->count[valid ? 1 : 0] ? 1 : 0);
+            else {
+                uint64_t h = mix64(k) >> t.shift;
+                while (true) {
+                    const ulonglong2 v = ld_nc_u64x2(t.slots + h);
+                    if (v.x == k) { c = csr ? (v.y >> 32) : 1; break; }
+                    if (v.x == kEmptyKey) break;
+                    h = (h + 1) & t.mask;
+                }
+            }
+        }
+        if (c == 0 && left_join) c = 1;
+        local += c;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+    if ((threadIdx.x & 31) == 0 && local) atomicAdd(total, local);
+}
+
+}  // namespace igl
+
+using namespace igl;
+
+struct igl_join {
+    igl_ctx* ctx = nullptr;
+    int join_type = 0;
+    bool left_join = false;
+    std::vector<int> lt, rt;
+    std::vector<uint8_t> ln, rn;
+    int lkey = 0, rkey = 0;
+    bool never_match = false;
+    // build state
+    bool built = false, csr = false;
+    int payload_col = -1;
+    JoinTable table{};
+    uint64_t capacity = 0;
+    void* d_slots = nullptr;
+    void* d_side = nullptr;
+    void* d_rowids = nullptr;
+    std::vector<igl_dev_col> right;
+    int64_t n_right_rows = 0;
+    // probe scratch
+    void* scratch = nullptr;
+    size_t scratch_bytes = 0;
+    std::vector<void*> valid_planes;
+    int64_t plane_rows = 0;
+    PipeHeader* host_hdr = nullptr;
+    JoinSide* host_side = nullptr;
+    PipeCols T{};
+    PipeGeometry geo;
+    bool has_nulls = false;
+    size_t smem_bytes = 0;
+    int grid_cap_u = 0, grid_cap_m = 0;
+};
+
+namespace {
+
+typedef void (*probe_kernel_t)(const JoinProbeParams);
+probe_kernel_t pick_probe(bool csr, int subs, bool nulls) {
+    if (csr) {
+        if (subs == 2) return nulls ? join_probe_multi_kernel<2, true> : join_probe_multi_kernel<2, false>;
+        return nulls ? join_probe_multi_kernel<1, true> : join_probe_multi_kernel<1, false>;
+    }
+    if (subs == 2) return nulls ? join_probe_unique_kernel<2, true> : join_probe_unique_kernel<2, false>;
+    return nulls ? join_probe_unique_kernel<1, true> : join_probe_unique_kernel<1, false>;
+}
+
+bool fixed_width(int t) { return t == IGL_T_I32 || t == IGL_T_I64 || t == IGL_T_F64; }
+
+}  // namespace
+
+extern "C" {
+
+int32_t igl_join_create(igl_ctx* ctx, int32_t join_type, const int32_t* left_types, const uint8_t* left_nullable,
+                        int32_t n_left, const int32_t* right_types, const uint8_t* right_nullable, int32_t n_right,
+                        const igl_expr* left_key, const igl_expr* right_key, igl_join** out) {
+    if (!ctx || !out || !left_types || !right_types || !left_key || !right_key || n_left <= 0 || n_right <= 0)
+        return fail(IGL_ERR_INVALID_ARG, "igl_join_create: bad arguments");
+    *out = nullptr;
+    if (join_type < IGL_JOIN_INNER || join_type > IGL_JOIN_FULL)
+        return fail(IGL_ERR_UNSUPPORTED, "Join type %d not implemented", join_type);   // physical_planner.rs:127-129
+    if (n_left > kJoinMaxCols || n_right > kJoinMaxCols) return fail(IGL_ERR_UNSUPPORTED, "more than %d columns on one join side", kJoinMaxCols);
+    if (!left_key->is_plain_col() || !right_key->is_plain_col())
+        return fail(IGL_ERR_UNSUPPORTED, "device join keys must be column references; project computed keys first");
+    auto j = std::make_unique<igl_join>();
+    j->ctx = ctx;
+    j->join_type = join_type;
+    // Right == Inner and Full == Left: the reference never emits unmatched right rows.
+    j->left_join = join_type == IGL_JOIN_LEFT || join_type == IGL_JOIN_FULL;
+    j->lt.assign(left_types, left_types + n_left);
+    j->rt.assign(right_types, right_types + n_right);
+    j->ln.assign(n_left, 0); j->rn.assign(n_right, 0);
+    if (left_nullable) j->ln.assign(left_nullable, left_nullable + n_left);
+    if (right_nullable) j->rn.assign(right_nullable, right_nullable + n_right);
+    j->lkey = left_key->nodes[0].col;
+    j->rkey = right_key->nodes[0].col;
+    if (j->lkey >= n_left || j->rkey >= n_right) return fail(IGL_ERR_INVALID_ARG, "join key column out of range");
+    for (int t : j->lt) if (!fixed_width(t)) return fail(IGL_ERR_UNSUPPORTED, "device join columns must be Int32/Int64/Float64 (got type %d)", t);
+    for (int t : j->rt) if (!fixed_width(t)) return fail(IGL_ERR_UNSUPPORTED, "device join columns must be Int32/Int64/Float64 (got type %d)", t);
+    j->never_match = j->lt[j->lkey] != j->rt[j->rkey];   // the Arrow type name is part of the printed key
+    j->has_nulls = j->left_join;
+    for (auto v : j->ln) if (v) j->has_nulls = true;
+    for (auto v : j->rn) if (v) j->has_nulls = true;
+    uint8_t shifts[kJoinMaxCols];
+    for (int c = 0; c < n_left; ++c) shifts[c] = j->lt[c] == IGL_T_I32 ? 2 : 3;
+    j->geo = pipe_geometry(shifts, n_left, j->T);
+    if (!j->geo.ok) return fail(IGL_ERR_UNSUPPORTED, "left side too wide for one tile (%u bytes)", j->geo.stage_bytes);
+    j->smem_bytes = (size_t)j->geo.stage_bytes * j->geo.stages;
+    DeviceGuard g(ctx->device);
+    for (int csr = 0; csr < 2; ++csr) {
+        probe_kernel_t k = pick_probe(csr, j->geo.subs, j->has_nulls);
+        IGL_CUDA_OK(cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)j->smem_bytes));
+        int per_sm = 0;
+        IGL_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)k, kPipeThreads, j->smem_bytes));
+        if (per_sm < 1) return fail(IGL_ERR_INTERNAL, "join probe kernel does not fit on an SM");
+        (csr ? j->grid_cap_m : j->grid_cap_u) = per_sm * ctx->sm_count;
+    }
+    IGL_CUDA_OK(cudaHostAlloc((void**)&j->host_hdr, sizeof(PipeHeader), cudaHostAllocDefault));
+    IGL_CUDA_OK(cudaHostAlloc((void**)&j->host_side, sizeof(JoinSide), cudaHostAllocDefault));
+    j->valid_planes.assign(n_left + n_right, nullptr);
+    *out = j.release();
+    return IGL_OK;
+}
+
+int32_t igl_join_build(igl_join* j, const igl_dev_col* right, int64_t nrows, void* stream) {
+    if (!j || !right || nrows < 0) return fail(IGL_ERR_INVALID_ARG, "igl_join_build: bad arguments");
+    if (nrows >= (int64_t)kNoRow) return fail(IGL_ERR_UNSUPPORTED, "build side limited to 2^32-2 rows per table");
+    igl_ctx* ctx = j->ctx;
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = pick_stream(ctx, stream);
+    const int nr = (int)j->rt.size();
+    for (int c = 0; c < nr; ++c)
+        if (right[c].type != j->rt[c]) return fail(IGL_ERR_INVALID_ARG, "right column %d has type %d, join expects %d", c, right[c].type, j->rt[c]);
+    j->right.assign(right, right + nr);
+    j->n_right_rows = nrows;
+    // capacity: power of two >= rows / load factor
+    uint64_t cap = 1024;
+    while ((double)cap * ctx->cfg.hash_load_factor < (double)nrows) cap <<= 1;
+    if (j->d_slots && cap != j->capacity) { pool_free(ctx, j->d_slots); j->d_slots = nullptr; }
+    if (!j->d_slots) IGL_TRY(pool_alloc(ctx, cap * sizeof(Slot), &j->d_slots));
+    if (!j->d_side) IGL_TRY(pool_alloc(ctx, sizeof(JoinSide), &j->d_side));
+    if (j->d_rowids) { pool_free(ctx, j->d_rowids); j->d_rowids = nullptr; }
+    j->capacity = cap;
+    int lg = 0; while ((1ull << lg) < cap) ++lg;
+    j->table.slots = (Slot*)j->d_slots;
+    j->table.mask = cap - 1;
+    j->table.shift = 64 - lg;
+    j->table.side = (JoinSide*)j->d_side;
+    j->table.rowids = nullptr;
+    const int grid = ctx->sm_count * 8;
+    const igl_dev_col& kc = right[j->rkey];
+    // payload inlining: (key, one non-null fixed-width column), integer key (exact round trip)
+    j->payload_col = -1;
+    if (nr == 2 && !j->rn[0] && !j->rn[1] && !right[0].validity && !right[1].validity &&
+        (j->rt[j->rkey] == IGL_T_I32 || j->rt[j->rkey] == IGL_T_I64))
+        j->payload_col = 1 - j->rkey;
+    join_init_kernel<<<grid, 256, 0, st>>>((Slot*)j->d_slots, cap, (JoinSide*)j->d_side);
+    IGL_CUDA_OK(cudaGetLastError());
+    ctx->launches++;
+    if (nrows > 0) {
+        const void* payload = j->payload_col >= 0 ? right[j->payload_col].data : nullptr;
+        const int pshift = j->payload_col >= 0 ? (j->rt[j->payload_col] == IGL_T_I32 ? 2 : 3) : 0xFF;
+        join_build_unique_kernel<<<grid, 256, 0, st>>>(kc.data, j->rt[j->rkey], kc.validity, payload, pshift, nrows, j->table);
+        IGL_CUDA_OK(cudaGetLastError());
+        ctx->launches++;
+    }
+    IGL_CUDA_OK(cudaMemcpyAsync(j->host_side, j->d_side, sizeof(JoinSide), cudaMemcpyDeviceToHost, st));
+    IGL_CUDA_OK(cudaStreamSynchronize(st));
+    j->csr = j->host_side->dup_flag != 0;
+    if (j->csr) {   // duplicates: rebuild as CSR runs
+        j->payload_col = -1;
+        IGL_TRY(pool_alloc(ctx, (size_t)nrows * 4, &j->d_rowids));
+        join_init_kernel<<<grid, 256, 0, st>>>((Slot*)j->d_slots, cap, (JoinSide*)j->d_side);
+        join_build_count_kernel<<<grid, 256, 0, st>>>(kc.data, j->rt[j->rkey], kc.validity, nrows, j->table);
+        join_build_runs_kernel<<<grid, 256, 0, st>>>(j->table, cap);
+        join_build_fill_kernel<<<grid, 256, 0, st>>>(kc.data, j->rt[j->rkey], kc.validity, nrows, j->table, (uint32_t*)j->d_rowids);
+        IGL_CUDA_OK(cudaGetLastError());
+        ctx->launches += 4;
+        j->table.rowids = (const uint32_t*)j->d_rowids;
+        IGL_CUDA_OK(cudaStreamSynchronize(st));
+    }
+    j->built = true;
+    return IGL_OK;
+}
+
+int32_t igl_join_has_duplicates(const igl_join* j) { return j && j->csr ? 1 : 0; }
+
+int32_t igl_join_probe_count(igl_join* j, const igl_dev_col* left, int64_t nrows, int64_t* out_rows, void* stream) {
+    if (!j || !left || !out_rows || nrows < 0) return fail(IGL_ERR_INVALID_ARG, "igl_join_probe_count: bad arguments");
+    if (!j->built) return fail(IGL_ERR_INVALID_ARG, "igl_join_probe_count: build side not finished");
+    igl_ctx* ctx = j->ctx;
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = pick_stream(ctx, stream);
+    if (nrows == 0) { *out_rows = 0; return IGL_OK; }
+    if (!j->scratch) { IGL_TRY(pool_alloc(ctx, 256, &j->scratch)); j->scratch_bytes = 256; }
+    IGL_CUDA_OK(cudaMemsetAsync(j->scratch, 0, 256, st));
+    PipeHeader* hdr = (PipeHeader*)j->scratch;
+    const igl_dev_col& kc = left[j->lkey];
+    join_probe_count_kernel<<<ctx->sm_count * 8, 256, 0, st>>>(kc.data, j->lt[j->lkey], kc.validity, nrows, j->table, j->csr ? 1 : 0,
+                                                               j->left_join ? 1 : 0, j->never_match ? 1 : 0, &hdr->aux[0]);
+    IGL_CUDA_OK(cudaGetLastError());
+    ctx->launches++;
+    IGL_CUDA_OK(cudaMemcpyAsync(j->host_hdr, j->scratch, sizeof(PipeHeader), cudaMemcpyDeviceToHost, st));
+    IGL_CUDA_OK(cudaStreamSynchronize(st));
+    *out_rows = (int64_t)j->host_hdr->aux[0];
+    return IGL_OK;
+}
+
+int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_dev_col* out, int64_t out_capacity,
+                       int64_t* out_rows, void* stream) {
+    if (!j || !left || !out || nrows < 0) return fail(IGL_ERR_INVALID_ARG, "igl_join_probe: bad arguments");
+    if (!j->built) return fail(IGL_ERR_INVALID_ARG, "igl_join_probe: build side not finished");
+    igl_ctx* ctx = j->ctx;
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = pick_stream(ctx, stream);
+    const int nl = (int)j->lt.size(), nr = (int)j->rt.size();
+    if (nrows == 0) { if (out_rows) *out_rows = 0; return IGL_OK; }
+    // capacity check: unique layout emits at most one row per probe row
+    if (!j->csr && out_capacity < nrows) {
+        int64_t need = 0;
+        IGL_TRY(igl_join_probe_count(j, left, nrows, &need, stream));
+        if (out_capacity < need) return fail(IGL_ERR_INVALID_ARG, "output capacity %lld < %lld rows", (long long)out_capacity, (long long)need);
+    } else if (j->csr) {
+        int64_t need = 0;
+        IGL_TRY(igl_join_probe_count(j, left, nrows, &need, stream));
+        if (out_capacity < need) return fail(IGL_ERR_INVALID_ARG, "output capacity %lld < %lld rows", (long long)out_capacity, (long long)need);
+    }
+    JoinProbeParams P{};
+    P.T = j->T;
+    const int TILE = j->geo.subs * kPipeRowsPerSub;
+    P.T.nrows = nrows;
+    P.T.ntiles = (nrows + TILE - 1) / TILE;
+    for (int c = 0; c < nl; ++c) {
+        if (left[c].type != j->lt[c]) return fail(IGL_ERR_INVALID_ARG, "left column %d has type %d, join expects %d", c, left[c].type, j->lt[c]);
+        if (((uintptr_t)left[c].data & 15) || ((uintptr_t)left[c].validity & 15)) return fail(IGL_ERR_INVALID_ARG, "left column %d is not 16-byte aligned", c);
+        P.T.data[c] = (const uint8_t*)left[c].data;
+        P.T.valid[c] = j->has_nulls ? left[c].validity : nullptr;
+    }
+    size_t need = 256 + (size_t)P.T.ntiles * 8;
+    if (need > j->scratch_bytes) {
+        if (j->scratch) pool_free(ctx, j->scratch);
+        j->scratch = nullptr; j->scratch_bytes = 0;
+        IGL_TRY(pool_alloc(ctx, need, &j->scratch));
+        j->scratch_bytes = need;
+    }
+    P.T.hdr = (PipeHeader*)j->scratch;
+    P.T.status = (uint64_t*)((uint8_t*)j->scratch + 256);
+    IGL_CUDA_OK(cudaMemsetAsync(j->scratch, 0, need, st));
+    P.table = j->table;
+    P.key_slot = j->lkey;
+    P.key_type = j->lt[j->lkey];
+    P.never_match = j->never_match ? 1 : 0;
+    P.n_left = nl; P.n_right = nr;
+    P.right_key_col = j->rkey;
+    P.payload_col = j->payload_col;
+    P.left_join = j->left_join ? 1 : 0;
+    // validity planes: a left column that has a bitmap; every right column when it
+    // can be null (source nullable, or null-extended by a Left/Full join)
+    const int64_t cap_rows = std::max<int64_t>(out_capacity, 1);
+    if (cap_rows > j->plane_rows) {
+        for (auto& p : j->valid_planes) if (p) { pool_free(ctx, p); p = nullptr; }
+        j->plane_rows = cap_rows;
+    }
+    for (int c = 0; c < nl + nr; ++c) {
+        const bool is_left = c < nl;
+        const int t = is_left ? j->lt[c] : j->rt[c - nl];
+        P.out_shift[c] = t == IGL_T_I32 ? 2 : 3;
+        if (!out[c].data) return fail(IGL_ERR_INVALID_ARG, "output column %d has no data buffer", c);
+        P.out_data[c] = out[c].data;
+        bool want = is_left ? (left[c].validity != nullptr) : (j->left_join || j->right[c - nl].validity != nullptr);
+        if (!j->has_nulls) want = false;
+        if (want && !out[c].validity) return fail(IGL_ERR_INVALID_ARG, "output column %d can hold nulls but has no validity buffer", c);
+        if (want) {
+            if (!j->valid_planes[c]) IGL_TRY(pool_alloc(ctx, (size_t)j->plane_rows, &j->valid_planes[c]));
+            P.out_valid[c] = (uint8_t*)j->valid_planes[c];
+        } else P.out_valid[c] = nullptr;
+        if (!is_left) {
+            P.right_data[c - nl] = (const uint8_t*)j->right[c - nl].data;
+            P.right_valid[c - nl] = j->right[c - nl].validity;
+        }
+    }
+    probe_kernel_t k = pick_probe(j->csr, j->geo.subs, j->has_nulls);
+    const int grid = (int)std::min<int64_t>(P.T.ntiles, j->csr ? j->grid_cap_m : j->grid_cap_u);
+    k<<<grid, kPipeThreads, j->smem_bytes, st>>>(P);
+    IGL_CUDA_OK(cudaGetLastError());
+    ctx->launches++;
+    for (int c = 0; c < nl + nr; ++c) {
+        if (!P.out_valid[c]) continue;
+        IGL_CUDA_OK(launch_pack_bits(P.out_valid[c], (uint32_t*)out[c].validity, &P.T.hdr->out_count, 0, out_capacity, ctx->sm_count, st));
+        ctx->launches++;
+    }
+    IGL_CUDA_OK(cudaMemcpyAsync(j->host_hdr, j->scratch, sizeof(PipeHeader), cudaMemcpyDeviceToHost, st));
+    IGL_CUDA_OK(cudaStreamSynchronize(st));
+    if (out_rows) *out_rows = (int64_t)j->host_hdr->out_count;
+    return IGL_OK;
+}
+
+void igl_join_destroy(igl_join* j) {
+    if (!j) return;
+    DeviceGuard g(j->ctx->device);
+    pool_free(j->ctx, j->d_slots);
+    pool_free(j->ctx, j->d_side);
+    pool_free(j->ctx, j->d_rowids);
+    pool_free(j->ctx, j->scratch);
+    for (void* p : j->valid_planes) pool_free(j->ctx, p);
+    if (j->host_hdr) cudaFreeHost(j->host_hdr);
+    if (j->host_side) cudaFreeHost(j->host_side);
+    delete j;
+}
+
+}  // extern "C"

@@ -1,0 +1,182 @@
+// partition.cu — K4: hash repartition of a column set, the data-plane half of
+// the multi-GPU join's "worker fragment exchange".
+//
+// The reference only declares this step (FragmentType::Shuffle is never built,
+// crates/coordinator/src/fragment.rs:8-13; GetDataForTask returns empty bytes,
+// crates/worker/src/service.rs:26-32; the join fragment is simply pinned to the
+// coordinator, crates/coordinator/src/distributed_planner.rs:65-92).  Here both
+// join sides are split by dest = hash(key) so that equal keys meet on one GPU.
+//
+// Two passes: a histogram (so every (source, destination) pair knows its exact
+// slab offset after one tiny count exchange) and a scatter that writes rows
+// straight to their final place.  Destination pointers may be peer device
+// pointers mapped over NVLink (CUDA IPC): the scatter then IS the exchange — no
+// send buffer, no second copy.
+//
+// dest uses the LOW 32 bits of mix64(key); the local hash table indexes with the
+// TOP bits, so partitioning does not correlate with slot placement.  NULL keys
+// all go to partition 0 (they must meet: NULL == NULL in the reference).
+#include "device_utils.cuh"
+#include "internal.h"
+
+namespace igl {
+
+constexpr int kPartMaxParts = 16;
+constexpr int kPartMaxCols = 16;
+constexpr int kPartThreads = 256;
+constexpr int kPartRowsPerThread = 8;
+constexpr int kPartTile = kPartThreads * kPartRowsPerThread;
+
+__device__ __forceinline__ uint64_t part_canon(int type, uint64_t raw) {
+    if (type == IGL_T_I32) return (uint64_t)(int64_t)(int32_t)raw;
+    if (type == IGL_T_F64) return ((raw & 0x7FFFFFFFFFFFFFFFull) > 0x7FF0000000000000ull) ? 0x7FF8000000000000ull : raw;
+    return raw;
+}
+
+__device__ __forceinline__ int part_dest(const void* keys, int type, const uint8_t* valid, long long i, int nparts) {
+    if (valid && !((valid[i >> 3] >> (i & 7)) & 1)) return 0;
+    const uint64_t raw = type == IGL_T_I32 ? (uint64_t)(uint32_t)((const int32_t*)keys)[i] : ((const uint64_t*)keys)[i];
+    const uint64_t h = mix64(part_canon(type, raw)) & 0xFFFFFFFFull;
+    return (int)((h * (uint64_t)nparts) >> 32);
+}
+
+__global__ void partition_hist_kernel(const void* __restrict__ keys, int type, const uint8_t* __restrict__ valid,
+                                      long long n, int nparts, unsigned long long* hist) {
+    __shared__ unsigned int s_hist[kPartMaxParts];
+    if (threadIdx.x < kPartMaxParts) s_hist[threadIdx.x] = 0;
+    __syncthreads();
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    unsigned int local[kPartMaxParts];
+#pragma unroll
+    for (int p = 0; p < kPartMaxParts; ++p) local[p] = 0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const int d = part_dest(keys, type, valid, i, nparts);
+#pragma unroll
+        for (int p = 0; p < kPartMaxParts; ++p) local[p] += (d == p);
+    }
+#pragma unroll
+    for (int p = 0; p < kPartMaxParts; ++p) {
+        unsigned int v = local[p];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0 && v) atomicAdd(&s_hist[p], v);
+    }
+    __syncthreads();
+    if (threadIdx.x < nparts && s_hist[threadIdx.x]) atomicAdd(&hist[threadIdx.x], (unsigned long long)s_hist[threadIdx.x]);
+}
+
+struct ScatterParams {
+    const uint8_t* src[kPartMaxCols];
+    uint8_t shift[kPartMaxCols];
+    uint8_t* dst[kPartMaxParts * kPartMaxCols];   // [part][col], already offset to this source's slab
+    int ncols, nparts, key_col, key_type;
+    const uint8_t* key_valid;
+    long long n;
+    unsigned long long* cursor;   // [nparts] rows already written per destination
+};
+
+__global__ void __launch_bounds__(kPartThreads) partition_scatter_kernel(const __grid_constant__ ScatterParams P) {
+    __shared__ unsigned int s_cnt[kPartMaxParts];
+    __shared__ unsigned long long s_base[kPartMaxParts];
+    const long long ntiles = (P.n + kPartTile - 1) / kPartTile;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        if (threadIdx.x < kPartMaxParts) s_cnt[threadIdx.x] = 0;
+        __syncthreads();
+        const long long row0 = tile * kPartTile;
+        int dest[kPartRowsPerThread];
+        unsigned int rank[kPartRowsPerThread];
+#pragma unroll
+        for (int r = 0; r < kPartRowsPerThread; ++r) {
+            const long long i = row0 + r * kPartThreads + threadIdx.x;
+            dest[r] = -1;
+            if (i < P.n) {
+                dest[r] = part_dest(P.src[P.key_col], P.key_type, P.key_valid, i, P.nparts);
+                rank[r] = atomicAdd(&s_cnt[dest[r]], 1u);   // shared-memory atomic: position inside this tile's run
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x < P.nparts)
+            s_base[threadIdx.x] = s_cnt[threadIdx.x] ? atomicAdd(&P.cursor[threadIdx.x], (unsigned long long)s_cnt[threadIdx.x]) : 0ull;
+        __syncthreads();
+        for (int c = 0; c < P.ncols; ++c) {
+            const int sh = P.shift[c];
+#pragma unroll
+            for (int r = 0; r < kPartRowsPerThread; ++r) {
+                if (dest[r] < 0) continue;
+                const long long i = row0 + r * kPartThreads + threadIdx.x;
+                const unsigned long long o = s_base[dest[r]] + rank[r];
+                uint8_t* d = P.dst[dest[r] * kPartMaxCols + c];
+                if (sh == 2) reinterpret_cast<uint32_t*>(d)[o] = reinterpret_cast<const uint32_t*>(P.src[c])[i];
+                else reinterpret_cast<uint64_t*>(d)[o] = reinterpret_cast<const uint64_t*>(P.src[c])[i];
+            }
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace igl
+
+using namespace igl;
+
+extern "C" {
+
+int32_t igl_partition_histogram(igl_ctx* ctx, const igl_dev_col* key, int64_t nrows, int32_t nparts, int64_t* dev_hist,
+                                void* stream) {
+    if (!ctx || !key || !dev_hist || nrows < 0) return fail(IGL_ERR_INVALID_ARG, "igl_partition_histogram: bad arguments");
+    if (nparts < 1 || nparts > kPartMaxParts) return fail(IGL_ERR_UNSUPPORTED, "nparts must be in [1, %d]", kPartMaxParts);
+    if (key->type != IGL_T_I32 && key->type != IGL_T_I64 && key->type != IGL_T_F64)
+        return fail(IGL_ERR_UNSUPPORTED, "partition key must be Int32/Int64/Float64");
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = pick_stream(ctx, stream);
+    IGL_CUDA_OK(cudaMemsetAsync(dev_hist, 0, sizeof(int64_t) * nparts, st));
+    if (nrows == 0) return IGL_OK;
+    const int grid = (int)std::min<int64_t>((nrows + 255) / 256, (int64_t)ctx->sm_count * 8);
+    partition_hist_kernel<<<grid, 256, 0, st>>>(key->data, key->type, key->validity, nrows, nparts, (unsigned long long*)dev_hist);
+    IGL_CUDA_OK(cudaGetLastError());
+    ctx->launches++;
+    return IGL_OK;
+}
+
+int32_t igl_partition_scatter(igl_ctx* ctx, const igl_dev_col* cols, int32_t ncols, int32_t key_col, int64_t nrows,
+                              int32_t nparts, void* const* dst, const int64_t* dst_row_offset, void* stream) {
+    if (!ctx || !cols || !dst || !dst_row_offset || nrows < 0) return fail(IGL_ERR_INVALID_ARG, "igl_partition_scatter: bad arguments");
+    if (nparts < 1 || nparts > kPartMaxParts) return fail(IGL_ERR_UNSUPPORTED, "nparts must be in [1, %d]", kPartMaxParts);
+    if (ncols < 1 || ncols > kPartMaxCols || key_col < 0 || key_col >= ncols) return fail(IGL_ERR_INVALID_ARG, "igl_partition_scatter: bad column set");
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = pick_stream(ctx, stream);
+    ScatterParams P{};
+    P.ncols = ncols; P.nparts = nparts; P.key_col = key_col; P.key_type = cols[key_col].type;
+    P.key_valid = cols[key_col].validity;
+    P.n = nrows;
+    for (int c = 0; c < ncols; ++c) {
+        const int t = cols[c].type;
+        if (t != IGL_T_I32 && t != IGL_T_I64 && t != IGL_T_F64) return fail(IGL_ERR_UNSUPPORTED, "partitioned columns must be Int32/Int64/Float64");
+        if (cols[c].validity && c != key_col) return fail(IGL_ERR_UNSUPPORTED, "nullable payload columns are not repartitioned yet");
+        P.src[c] = (const uint8_t*)cols[c].data;
+        P.shift[c] = t == IGL_T_I32 ? 2 : 3;
+    }
+    for (int p = 0; p < nparts; ++p)
+        for (int c = 0; c < ncols; ++c) {
+            if (!dst[p * ncols + c]) return fail(IGL_ERR_INVALID_ARG, "destination pointer [%d][%d] is NULL", p, c);
+            P.dst[p * kPartMaxCols + c] = (uint8_t*)dst[p * ncols + c] + ((size_t)dst_row_offset[p] << P.shift[c]);
+        }
+    if (nrows == 0) return IGL_OK;
+    void* cursor = nullptr;
+    IGL_TRY(pool_alloc(ctx, sizeof(unsigned long long) * kPartMaxParts, &cursor));
+    cudaError_t e = cudaMemsetAsync(cursor, 0, sizeof(unsigned long long) * kPartMaxParts, st);
+    P.cursor = (unsigned long long*)cursor;
+    if (e == cudaSuccess) {
+        const int64_t ntiles = (nrows + kPartTile - 1) / kPartTile;
+        const int grid = (int)std::min<int64_t>(ntiles, (int64_t)ctx->sm_count * 8);
+        partition_scatter_kernel<<<grid, kPartThreads, 0, st>>>(P);
+        e = cudaGetLastError();
+        ctx->launches++;
+    }
+    // the cursor block returns to the pool only after the kernel has consumed it
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    pool_free(ctx, cursor);
+    if (e != cudaSuccess) return fail(IGL_ERR_CUDA, "igl_partition_scatter: %s", cudaGetErrorString(e));
+    return IGL_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,253 @@
+/*
+ * igloo_cuda.h — C ABI of libigloo_cuda.so: B200 (sm_100a) replacements for
+ * Igloo's Filter / Projection / HashJoin physical operators.
+ *
+ * This is the surface a Rust `igloo-cuda` crate binds with `extern "C"`
+ * (INTEGRATION.md shows the binding).  The reference defines no FFI of its own;
+ * each entry point cites the reference interface it stands in for, all under
+ * /root/reference/crates/engine/src/.
+ *
+ * Conventions
+ *   - every call returns int32_t: 0 = IGL_OK, > 0 = status, < 0 = error class;
+ *     the message is igl_last_error() (thread-local).  Nothing throws or aborts
+ *     across the ABI.  Rust maps errors to DataFusionError (External / Internal /
+ *     NotImplemented) the way the operators return `DataFusionResult`
+ *     (filter.rs:39, hash_join.rs:41).
+ *   - handles are opaque and single-owner: one thread at a time per handle
+ *     (`Send`, not `Sync`), any thread may call.  *_destroy(NULL) is a no-op.
+ *   - "dev" pointers are CUDA device pointers on the context's device.  Column
+ *     buffers must be 16-byte aligned and readable up to the next multiple of
+ *     64 bytes (the padding Arrow recommends and igl_dev_alloc guarantees):
+ *     tiles are staged with 16-byte-granular bulk copies.
+ *   - there is no CPU fallback: without a CUDA device igl_ctx_create fails.
+ */
+#ifndef IGLOO_CUDA_H
+#define IGLOO_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include "igloo_expr.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- Arrow C Data Interface (verbatim ABI; what arrow-rs `arrow::ffi` and
+ *      pyarrow `_export_to_c` / `_import_from_c` exchange).  Stands in for
+ *      `arrow::record_batch::RecordBatch` at the operator boundary
+ *      (physical_plan.rs:13). ---------------------------------------------- */
+#ifndef ARROW_C_DATA_INTERFACE
+#define ARROW_C_DATA_INTERFACE
+#define ARROW_FLAG_DICTIONARY_ORDERED 1
+#define ARROW_FLAG_NULLABLE 2
+#define ARROW_FLAG_MAP_KEYS_SORTED 4
+struct ArrowSchema {
+    const char* format;
+    const char* name;
+    const char* metadata;
+    int64_t flags;
+    int64_t n_children;
+    struct ArrowSchema** children;
+    struct ArrowSchema* dictionary;
+    void (*release)(struct ArrowSchema*);
+    void* private_data;
+};
+struct ArrowArray {
+    int64_t length;
+    int64_t null_count;
+    int64_t offset;
+    int64_t n_buffers;
+    int64_t n_children;
+    const void** buffers;
+    struct ArrowArray** children;
+    struct ArrowArray* dictionary;
+    void (*release)(struct ArrowArray*);
+    void* private_data;
+};
+#endif
+
+/* ---- status / error classes ---------------------------------------------- */
+enum igl_status {
+    IGL_OK = 0,
+    IGL_AGAIN = 1, /* pull: nothing ready yet, push more or finish input */
+    IGL_EOS = 2,   /* pull: stream finished                              */
+    IGL_ERR_INVALID_ARG = -1,
+    IGL_ERR_UNSUPPORTED = -2, /* DataFusionError::NotImplemented           */
+    IGL_ERR_OOM = -3,
+    IGL_ERR_CUDA = -4,
+    IGL_ERR_NCCL = -5,
+    IGL_ERR_DIV_BY_ZERO = -6,           /* ArrowError::DivideByZero         */
+    IGL_ERR_PREDICATE_NOT_BOOLEAN = -7, /* filter.rs:50-55                  */
+    IGL_ERR_ARITH_OVERFLOW = -8,        /* ArrowError::ArithmeticOverflow   */
+    IGL_ERR_CAST = -9,                  /* ArrowError::CastError            */
+    IGL_ERR_INTERNAL = -10
+};
+
+/* Thread-local message of the last failing call on this thread. */
+const char* igl_last_error(void);
+int32_t igl_version(void);
+
+/* ---- context: device, streams, device buffer pool, pinned staging ring.
+ *      New (the reference has no device); its knobs replace the literals
+ *      batch size 1024 / channel depth 10 (parquet_scan.rs:44,54). --------- */
+typedef struct igl_ctx igl_ctx;
+typedef struct igl_config {
+    int32_t device;           /* CUDA ordinal                                */
+    int32_t flags;            /* reserved, 0                                 */
+    int64_t coalesce_rows;    /* host batches are coalesced to this many rows
+                                 per device chunk; 0 = default (4 Mi)        */
+    double hash_load_factor;  /* join table fill; 0 = default (0.5)          */
+    int64_t pinned_ring_bytes;/* staging ring size; 0 = default (256 MiB)    */
+} igl_config;
+
+int32_t igl_ctx_create(const igl_config* cfg, igl_ctx** out);
+void igl_ctx_destroy(igl_ctx* ctx);
+int32_t igl_ctx_device(const igl_ctx* ctx);
+/* Number of kernels this context has launched (bench.py "gpu_launches"). */
+int64_t igl_ctx_launch_count(const igl_ctx* ctx);
+
+/* Device-resident batch buffer pool and pinned host memory (north_star:
+ * "pinned-memory batch upload path", "device-resident batch buffer pool"). */
+int32_t igl_dev_alloc(igl_ctx* ctx, size_t bytes, void** out);
+int32_t igl_dev_free(igl_ctx* ctx, void* ptr);
+int32_t igl_host_alloc_pinned(igl_ctx* ctx, size_t bytes, void** out);
+int32_t igl_host_free_pinned(igl_ctx* ctx, void* ptr);
+int32_t igl_memcpy_h2d(igl_ctx* ctx, void* dev_dst, const void* host_src, size_t bytes, void* stream);
+int32_t igl_memcpy_d2h(igl_ctx* ctx, void* host_dst, const void* dev_src, size_t bytes, void* stream);
+int32_t igl_stream_sync(igl_ctx* ctx, void* stream);
+
+/* ---- expressions: `Arc<dyn PhysicalExpr>` (physical_planner.rs:60-64,86-90,
+ *      107-116) as compiled bytecode.  col_types / col_nullable describe the
+ *      child's schema the expression is lowered against. ------------------- */
+typedef struct igl_expr igl_expr;
+int32_t igl_expr_compile(igl_ctx* ctx, const uint8_t* bytecode, size_t len,
+                         const int32_t* col_types, const uint8_t* col_nullable, int32_t ncols,
+                         igl_expr** out);
+/* PhysicalExpr::data_type / ::nullable (physical_planner.rs:69-70). */
+int32_t igl_expr_type(const igl_expr* e, int32_t* type, int32_t* nullable);
+void igl_expr_destroy(igl_expr* e);
+
+/* ---- device-resident columns --------------------------------------------- */
+typedef struct igl_dev_col {
+    int32_t type;      /* igl_type                                            */
+    int32_t reserved;
+    void* data;        /* values; BOOL: Arrow bit-packed; UTF8: bytes         */
+    uint8_t* validity; /* Arrow validity bitmap (LSB first) or NULL           */
+    int32_t* offsets;  /* UTF8 only: length+1 offsets                         */
+} igl_dev_col;
+
+/* ---- fused Filter + Projection on device-resident columns.
+ *      FilterExec::execute (filter.rs:39-68): pred != NULL, nproj == 0 keeps
+ *        every input column, rows where the mask is valid AND true.
+ *      ProjectionExec::execute (projection.rs:48-72): pred == NULL.
+ *      Projection(Filter(x)) fused by the planner: both.
+ *      Row order is preserved. -------------------------------------------- */
+typedef struct igl_fp igl_fp;
+int32_t igl_fp_create(igl_ctx* ctx, const int32_t* in_types, const uint8_t* in_nullable, int32_t n_in,
+                      const igl_expr* pred, const igl_expr* const* proj, int32_t nproj, igl_fp** out);
+int32_t igl_fp_num_outputs(const igl_fp* fp);
+int32_t igl_fp_output_type(const igl_fp* fp, int32_t j, int32_t* type, int32_t* nullable);
+/* Runs on `stream` (NULL = the context's stream) and returns after the stream
+ * has drained.  out[j].data (and .validity when output j is nullable) must hold
+ * `nrows` rows.  *out_rows receives the surviving row count.  A FilterExec that
+ * keeps 0 rows reports 0: the caller drops the batch (filter.rs:59-63). */
+int32_t igl_fp_run(igl_fp* fp, const igl_dev_col* in, int64_t nrows, igl_dev_col* out,
+                   int64_t* out_rows, void* stream);
+/* Same launch without the trailing synchronise / error read-back, for timing
+ * with CUDA events: counts and error flags are fetched by igl_fp_finish. */
+int32_t igl_fp_launch(igl_fp* fp, const igl_dev_col* in, int64_t nrows, igl_dev_col* out, void* stream);
+int32_t igl_fp_finish(igl_fp* fp, int64_t* out_rows, void* stream);
+void igl_fp_destroy(igl_fp* fp);
+
+/* ---- hash join on device-resident columns.
+ *      HashJoinExec::new (hash_join.rs:35-76): schema = left ++ right.
+ *      build  (hash_join.rs:100-128): right side drained into the table.
+ *      probe  (hash_join.rs:131-213): left rows looked up; Inner emits one row
+ *        per (left row, matching right row); Left/Full add the null-extended
+ *        row for an unmatched left row; Right == Inner and Full == Left because
+ *        the reference never emits unmatched right rows (:189, :263-276).
+ *      Key identity follows the printed form the reference hashes (:117-122):
+ *      NULL == NULL, NaN == NaN, -0.0 != 0.0, differing key types never match.
+ *      Output row order within one call is probe order (matches of one probe
+ *      row in unspecified order); parity is on row multisets. -------------- */
+enum igl_join_type { IGL_JOIN_INNER = 0, IGL_JOIN_LEFT = 1, IGL_JOIN_RIGHT = 2, IGL_JOIN_FULL = 3 };
+typedef struct igl_join igl_join;
+int32_t igl_join_create(igl_ctx* ctx, int32_t join_type,
+                        const int32_t* left_types, const uint8_t* left_nullable, int32_t n_left,
+                        const int32_t* right_types, const uint8_t* right_nullable, int32_t n_right,
+                        const igl_expr* left_key, const igl_expr* right_key, igl_join** out);
+/* Build from the complete right side.  The columns are borrowed until
+ * igl_join_destroy (right payload is gathered from them by row id). */
+int32_t igl_join_build(igl_join* j, const igl_dev_col* right, int64_t nrows, void* stream);
+/* Exact number of rows igl_join_probe will emit for this left chunk. */
+int32_t igl_join_probe_count(igl_join* j, const igl_dev_col* left, int64_t nrows, int64_t* out_rows, void* stream);
+/* out has n_left + n_right columns of capacity `out_capacity` rows; right-side
+ * columns need .validity for Left/Full joins or when the source is nullable. */
+int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_dev_col* out,
+                       int64_t out_capacity, int64_t* out_rows, void* stream);
+/* 1 when the build side held duplicate keys (chain walks), else 0. */
+int32_t igl_join_has_duplicates(const igl_join* j);
+void igl_join_destroy(igl_join* j);
+
+/* ---- hash repartition for the multi-GPU join (the "worker fragment exchange":
+ *      FragmentType::Shuffle is declared but never built in the reference,
+ *      crates/coordinator/src/fragment.rs:8-13; GetDataForTask returns empty
+ *      bytes, crates/worker/src/service.rs:26-32).  dest = top bits of
+ *      mix64(key), disjoint from the bits the local table uses. ------------ */
+int32_t igl_partition_histogram(igl_ctx* ctx, const igl_dev_col* key, int64_t nrows, int32_t nparts,
+                                int64_t* dev_hist /* [nparts] */, void* stream);
+/* Scatters every column of `cols` to dst[p * ncols + c] + dst_row_offset[p] rows;
+ * dst pointers may be peer (NVLink-mapped) device pointers. */
+int32_t igl_partition_scatter(igl_ctx* ctx, const igl_dev_col* cols, int32_t ncols, int32_t key_col,
+                              int64_t nrows, int32_t nparts, void* const* dst /* host [nparts*ncols] */,
+                              const int64_t* dst_row_offset /* host [nparts] */, void* stream);
+/* CUDA IPC plumbing so one process per GPU can map its peers' receive slabs. */
+int32_t igl_ipc_export(igl_ctx* ctx, void* dev_ptr, uint8_t handle_out[64]);
+int32_t igl_ipc_open(igl_ctx* ctx, const uint8_t handle[64], void** dev_ptr_out);
+int32_t igl_ipc_close(igl_ctx* ctx, void* dev_ptr);
+
+/* ---- synthetic data + multiset digest (SURVEY.md §8d generator), device side */
+enum igl_gen_kind {
+    IGL_GEN_I32_UNIFORM = 1, /* mulhi64(u, m)                                  */
+    IGL_GEN_I64_UNIFORM = 2, /* mulhi64(u, m); m == 0 => raw u                 */
+    IGL_GEN_F64_UNIT = 3,    /* (u >> 11) * 2^-53                              */
+    IGL_GEN_I64_PERM = 4,    /* bijection of row index on [0, 2^bits)          */
+    IGL_GEN_I64_LOOKUP = 5   /* u(seed, col, perm^-1(key[i])): the generated
+                                value of the build row holding key[i]          */
+};
+int32_t igl_gen_column(igl_ctx* ctx, int32_t kind, uint64_t seed, uint64_t col_id, int64_t row0,
+                       int64_t n, uint64_t m, int32_t bits, const int64_t* dev_keys, void* dev_out,
+                       void* stream);
+int32_t igl_digest_rows(igl_ctx* ctx, const igl_dev_col* cols, int32_t ncols, int64_t nrows,
+                        uint64_t out[3], void* stream);
+
+/* ---- streaming operators on host Arrow batches (push / pull).
+ *      `trait ExecutionPlan::execute() -> BoxStream<RecordBatch>`
+ *      (physical_plan.rs:10-17): the Rust operator's stream polls igl_op_pull
+ *      and feeds igl_op_push from its child stream.  Input batches are struct
+ *      arrays borrowed for the duration of the call; output batches are owned
+ *      by the caller through their `release` callbacks. -------------------- */
+typedef struct igl_op igl_op;
+int32_t igl_op_filter_project_create(igl_ctx* ctx, const struct ArrowSchema* in_schema,
+                                     const uint8_t* pred, size_t pred_len,
+                                     const uint8_t* const* proj, const size_t* proj_len,
+                                     const char* const* proj_names, int32_t nproj, igl_op** out);
+int32_t igl_op_hash_join_create(igl_ctx* ctx, int32_t join_type,
+                                const struct ArrowSchema* left_schema, const struct ArrowSchema* right_schema,
+                                const uint8_t* left_key, size_t left_key_len,
+                                const uint8_t* right_key, size_t right_key_len, igl_op** out);
+/* ExecutionPlan::schema (physical_plan.rs:16). */
+int32_t igl_op_schema(igl_op* op, struct ArrowSchema* out);
+/* Join only: right (build) child batches, then finish_build (hash_join.rs:100-128). */
+int32_t igl_op_push_build(igl_op* op, const struct ArrowArray* batch);
+int32_t igl_op_finish_build(igl_op* op);
+int32_t igl_op_push(igl_op* op, const struct ArrowArray* batch);
+int32_t igl_op_finish_input(igl_op* op);
+int32_t igl_op_pull(igl_op* op, struct ArrowArray* out);
+void igl_op_destroy(igl_op* op);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IGLOO_CUDA_H */

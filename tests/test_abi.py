@@ -1,0 +1,87 @@
+"""CPU tests of the drop-in boundary: libigloo_cuda.so loads and exports every
+symbol include/igloo_cuda.h declares; no compute calls are made (no GPU here)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    src = open(os.path.join(ROOT, "include", "igloo_cuda.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(igl_[a-z0-9_]+)\s*\(", src)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    import __graft_entry__ as ge
+    ge.build()
+    return ctypes.CDLL(os.path.join(ROOT, "igloo_b200", "libigloo_cuda.so"))
+
+
+def test_header_declares_the_expected_surface():
+    syms = declared_symbols()
+    for must in ("igl_ctx_create", "igl_expr_compile", "igl_fp_run", "igl_join_build", "igl_join_probe",
+                 "igl_partition_scatter", "igl_op_push", "igl_op_pull", "igl_last_error"):
+        assert must in syms
+
+
+def test_library_exports_every_declared_symbol(lib):
+    missing = [s for s in declared_symbols() if not hasattr(lib, s)]
+    assert not missing, missing
+
+
+def test_no_device_means_loud_failure_not_fallback(lib):
+    """Without a GPU, igl_ctx_create must fail with a message (this box has none;
+    on the GPU box the call succeeds and the handle is destroyed again)."""
+    h = ctypes.c_void_p()
+    lib.igl_ctx_create.restype = ctypes.c_int32
+    lib.igl_last_error.restype = ctypes.c_char_p
+    rc = lib.igl_ctx_create(None, ctypes.byref(h))
+    if rc == 0:
+        lib.igl_ctx_destroy.argtypes = [ctypes.c_void_p]
+        lib.igl_ctx_destroy(h)
+    else:
+        assert rc == -4 and b"no CPU fallback" in lib.igl_last_error()
+
+
+def test_expr_compile_type_rules_without_device(lib):
+    """igl_expr_compile is pure host code: DataFusion's type rules are enforced."""
+    from igloo_b200.expr import Field, col, lit, lower, T_BOOL, T_I32, T_I64, T_F64
+    lib.igl_expr_compile.restype = ctypes.c_int32
+    lib.igl_expr_compile.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_int32),
+                                     ctypes.c_char_p, ctypes.c_int32, ctypes.POINTER(ctypes.c_void_p)]
+    lib.igl_expr_type.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]
+    lib.igl_expr_destroy.argtypes = [ctypes.c_void_p]
+    lib.igl_last_error.restype = ctypes.c_char_p
+    schema = [Field("a", T_I32), Field("c", T_I64, True), Field("x", T_F64)]
+    types = (ctypes.c_int32 * 3)(T_I32, T_I64, T_F64)
+    nulls = bytes([0, 1, 0])
+
+    def compile_(bc):
+        h = ctypes.c_void_p()
+        rc = lib.igl_expr_compile(None, bc, len(bc), types, nulls, 3, ctypes.byref(h))
+        return rc, h
+    for e, want_t, want_n in [(col("a") < 5, T_BOOL, 0), (col("a") + col("a"), T_I32, 0), (col("c") * 2, T_I64, 1),
+                              (col("x") * 1.5 + 0.25, T_F64, 0), (col("c").is_null(), T_BOOL, 0),
+                              ((col("a") + col("c")) > 0, T_BOOL, 1)]:
+        bc, t, nl = lower(e, schema)
+        rc, h = compile_(bc)
+        assert rc == 0, lib.igl_last_error()
+        tt, nn = ctypes.c_int32(), ctypes.c_int32()
+        lib.igl_expr_type(h, ctypes.byref(tt), ctypes.byref(nn))
+        assert (tt.value, nn.value) == (want_t, want_n) == (t, int(nl))
+        lib.igl_expr_destroy(h)
+    # mixed types are rejected, not coerced (the planner owns coercion)
+    bad = bytes([0x01, 0, 0, 0x01, 1, 0, 0x20])   # a(i32) + c(i64)
+    rc, _ = compile_(bad)
+    assert rc == -1 and b"different types" in lib.igl_last_error()
+    rc, _ = compile_(bytes([0x01, 9, 0]))
+    assert rc == -1
+    rc, _ = compile_(bytes([0x20]))
+    assert rc == -1
+    rc, _ = compile_(bytes([0x01, 0, 0, 0x01, 0, 0]))
+    assert rc == -1 and b"exactly one" in lib.igl_last_error()

@@ -1,0 +1,182 @@
+"""GPU parity: hash join build/probe kernels (through the C ABI) vs the CPU oracle.
+
+Join row sets are compared as sorted multisets (BASELINE.json north_star)."""
+import numpy as np
+import pyarrow as pa
+import pytest
+
+from igloo_b200.expr import Field, col, lower, T_I32, T_I64, T_F64
+from oracle import oracle as orc
+from tests.util import arrow_to_columns, assert_same_multiset, columns_to_arrow, tight_fields
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from igloo_b200.device import Context
+    c = Context(0)
+    yield c
+    c.close()
+
+
+def gpu_join(ctx, left, right, lk, rk, jt=0):
+    from igloo_b200.device import DeviceColumn, HashJoin
+    lf, rf = tight_fields(left), tight_fields(right)
+    lc = [DeviceColumn.from_arrow(left.column(i), ctx.device) for i in range(left.num_columns)]
+    rc = [DeviceColumn.from_arrow(right.column(i), ctx.device) for i in range(right.num_columns)]
+    j = HashJoin(ctx, jt, lf, rf, col(lk), col(rk))
+    j.build(rc, right.num_rows)
+    want_n = j.probe_count(lc, left.num_rows)
+    out, n = j.probe(lc, left.num_rows)
+    assert n == want_n
+    fields = j.out_fields
+    arrays = [c.to_arrow(n) for c in out]
+    sch = pa.schema([pa.field(f.name, a.type, True) for f, a in zip(fields, arrays)])
+    return pa.Table.from_arrays(arrays, schema=sch), j
+
+
+def oracle_join(left, right, lk, rk, jt=0, mode=1):
+    lf, rf = tight_fields(left), tight_fields(right)
+    L = orc.Table.scan(arrow_to_columns(left))
+    R = orc.Table.scan(arrow_to_columns(right))
+    J = L.hash_join(R, [lower(col(lk), lf)[0]], [lower(col(rk), rf)[0]], jt, mode, 4)
+    t = columns_to_arrow(J.columns())
+    return t.cast(pa.schema([pa.field(f.name, f.type, True) for f in t.schema]))
+
+
+def check(ctx, left, right, lk, rk, jt=0, mode=1):
+    got, j = gpu_join(ctx, left, right, lk, rk, jt)
+    want = oracle_join(left, right, lk, rk, jt, mode)
+    assert got.schema.names == want.schema.names
+    assert_same_multiset(got, want)
+    return got, j
+
+
+@pytest.mark.parametrize("jt", [0, 1, 2, 3])
+def test_known_answers_all_join_types(ctx, jt):
+    left = pa.table({"k": pa.array([1, 2, 3, 2, 5], pa.int64()), "w": pa.array([10, 20, 30, 40, 50], pa.int64())})
+    right = pa.table({"k": pa.array([2, 9, 2, 1], pa.int64()), "v": pa.array([200, 900, 201, 100], pa.int64())})
+    got, j = check(ctx, left, right, "k", "k", jt, mode=0)
+    assert got.schema.names == ["k", "w", "right_k", "v"]      # hash_join.rs:54-63
+    assert j.has_duplicates
+    assert got.num_rows == (5 if jt in (0, 2) else 7)           # Right == Inner, Full == Left
+
+
+def test_unique_inline_payload_c3_shape(ctx):
+    """C3 shape at 1/1024 scale: unique permuted build keys, uniform probe keys."""
+    seed, bits, nprobe = 0x16100003, 17, 1_000_003
+    nb = 1 << bits
+    right = pa.table({"k": orc.gen_perm_pow2(0, nb, bits), "v": orc.gen_i64_uniform(seed, 1, 0, nb)})
+    left = pa.table({"k": orc.gen_i64_uniform(seed, 2, 0, nprobe, nb), "w": orc.gen_i64_uniform(seed, 3, 0, nprobe)})
+    got, j = check(ctx, left, right, "k", "k")
+    assert not j.has_duplicates and got.num_rows == nprobe
+    # 50 % match rate variant (C3')
+    left2 = pa.table({"k": orc.gen_i64_uniform(seed, 2, 0, nprobe, 2 * nb), "w": left.column("w")})
+    got2, _ = check(ctx, left2, right, "k", "k")
+    assert abs(got2.num_rows / nprobe - 0.5) < 0.01
+    check(ctx, left2, right, "k", "k", 1)
+
+
+def test_rowid_gather_wide_build_side(ctx):
+    """C4 shape, small: unique i64 key, three payload columns of mixed width."""
+    rng = np.random.default_rng(2)
+    nb, nl = 50_000, 400_000
+    right = pa.table({"o_orderkey": rng.permutation(nb * 4)[:nb].astype(np.int64), "o_custkey": rng.integers(1, 15_000_000, nb),
+                      "o_totalprice": rng.random(nb) * 1e5, "o_orderdate": rng.integers(0, 2500, nb).astype(np.int32)})
+    left = pa.table({"l_orderkey": rng.integers(0, nb * 4, nl), "l_partkey": rng.integers(0, 1 << 40, nl),
+                     "l_quantity": rng.random(nl), "l_extendedprice": rng.random(nl), "l_shipdate": rng.integers(0, 2500, nl).astype(np.int32)})
+    got, j = check(ctx, left, right, "l_orderkey", "o_orderkey")
+    assert not j.has_duplicates
+    check(ctx, left, right, "l_orderkey", "o_orderkey", 1)
+
+
+def test_duplicates_both_sides_and_heavy_key(ctx):
+    rng = np.random.default_rng(9)
+    nb, nl = 30_000, 60_000
+    rk = rng.integers(0, 5000, nb)
+    rk[:3000] = 77                      # one heavy key: a run longer than a warp
+    right = pa.table({"k": rk.astype(np.int64), "v": rng.integers(0, 1 << 50, nb), "z": rng.random(nb)})
+    lk = rng.integers(0, 6000, nl)
+    lk[::1000] = 77
+    left = pa.table({"k": lk.astype(np.int64), "w": rng.integers(0, 1 << 50, nl)})
+    got, j = check(ctx, left, right, "k", "k")
+    assert j.has_duplicates
+    check(ctx, left, right, "k", "k", 1)
+
+
+def test_null_keys_match_sentinel_key_and_nullable_payload(ctx):
+    rng = np.random.default_rng(4)
+    nb, nl = 4000, 9000
+    int_min = -2**63                    # equals the table's empty-slot sentinel
+    rk = rng.integers(0, 3000, nb).astype(np.int64); rk[5] = int_min
+    lk = rng.integers(0, 3500, nl).astype(np.int64); lk[7] = int_min; lk[9] = int_min
+    right = pa.table({"k": pa.array(rk, pa.int64(), mask=rng.random(nb) < 0.01),
+                      "v": pa.array(rng.integers(0, 100, nb), pa.int64(), mask=rng.random(nb) < 0.2)})
+    left = pa.table({"k": pa.array(lk, pa.int64(), mask=rng.random(nl) < 0.01),
+                     "w": pa.array(rng.random(nl), pa.float64(), mask=rng.random(nl) < 0.2)})
+    check(ctx, left, right, "k", "k", 0)
+    check(ctx, left, right, "k", "k", 1)
+    # unique build side with exactly one NULL key and one sentinel key
+    ru = pa.table({"k": pa.array([1, None, int_min, 4], pa.int64()), "v": pa.array([10, 20, 30, 40], pa.int64())})
+    lu = pa.table({"k": pa.array([None, int_min, 4, 5, None], pa.int64()), "w": pa.array([1, 2, 3, 4, 5], pa.int64())})
+    got, j = check(ctx, lu, ru, "k", "k", 0, mode=0)
+    assert not j.has_duplicates and sorted(got.column("v").to_pylist()) == [20, 20, 30, 40]
+    check(ctx, lu, ru, "k", "k", 1, mode=0)
+
+
+def test_float_and_int32_keys_and_type_mismatch(ctx):
+    nan = float("nan")
+    lf = pa.table({"k": pa.array([nan, 0.0, -0.0, 1.5, -nan], pa.float64()), "w": pa.array([1, 2, 3, 4, 5], pa.int64())})
+    rf = pa.table({"k": pa.array([nan, -0.0, 1.5], pa.float64()), "v": pa.array([10, 20, 30], pa.int64())})
+    got, _ = check(ctx, lf, rf, "k", "k", 0, mode=0)
+    assert sorted(got.column("w").to_pylist()) == [1, 3, 4, 5]          # NaN == NaN (any payload), -0.0 != 0.0
+    rng = np.random.default_rng(1)
+    l32 = pa.table({"k": rng.integers(-100, 100, 5000).astype(np.int32), "w": rng.random(5000)})
+    r32 = pa.table({"j": np.arange(-50, 50, dtype=np.int32), "v": rng.integers(0, 9, 100).astype(np.int32)})
+    check(ctx, l32, r32, "k", "j", 0)
+    check(ctx, l32, r32, "k", "j", 1)
+    # Int32 vs Int64 keys: the type name is part of the printed key -> nothing matches
+    r64 = pa.table({"j": np.arange(-50, 50, dtype=np.int64), "v": rng.integers(0, 9, 100)})
+    got, _ = check(ctx, l32, r64, "k", "j", 0)
+    assert got.num_rows == 0
+    got, _ = check(ctx, l32, r64, "k", "j", 1)
+    assert got.num_rows == 5000 and got.column("v").null_count == 5000
+
+
+@pytest.mark.parametrize("nl,nb", [(0, 10), (10, 0), (1, 1), (895, 3), (1793, 1792)])
+def test_empty_and_ragged(ctx, nl, nb):
+    rng = np.random.default_rng(nl * 7 + nb)
+    left = pa.table({"k": rng.integers(0, 8, nl), "w": rng.integers(0, 99, nl)})
+    right = pa.table({"k": rng.integers(0, 8, nb), "v": rng.integers(0, 99, nb)})
+    check(ctx, left, right, "k", "k", 0)
+    check(ctx, left, right, "k", "k", 1)
+
+
+def test_full_scale_property_c3_digest(ctx):
+    """C3 at 1/8 scale on the device generator (16 Mi x 128 Mi rows): the join
+    output's multiset digest must equal the digest of (k, w, k, v(k)) recomputed
+    row by row from the generator definition, without any hash table."""
+    from igloo_b200.device import HashJoin
+    seed, bits, nprobe = 0x16100003, 24, 1 << 27
+    nb = 1 << bits
+    rk = ctx.gen(4, 0, 0, 0, nb, bits=bits)
+    rv = ctx.gen(2, seed, 1, 0, nb)
+    lk = ctx.gen(2, seed, 2, 0, nprobe, m=nb)
+    lw = ctx.gen(2, seed, 3, 0, nprobe)
+    f = [Field("k", T_I64), Field("w", T_I64)]
+    g = [Field("k", T_I64), Field("v", T_I64)]
+    j = HashJoin(ctx, 0, f, g, col("k"), col("k"))
+    j.build([rk, rv], nb)
+    assert not j.has_duplicates
+    out, n = j.probe([lk, lw], nprobe, capacity=nprobe)
+    assert n == nprobe
+    expect_v = ctx.gen(5, seed, 1, 0, nprobe, bits=bits, keys=lk)     # v of the build row holding each probe key
+    assert ctx.digest(out, n) == ctx.digest([lk, lw, lk, expect_v], nprobe)
+    # oracle spot check on the first tile-aligned 200k probe rows (order is preserved for unique builds)
+    m = 200_000
+    hk = orc.gen_i64_uniform(seed, 2, 0, m, nb)
+    assert np.array_equal(out[0].data[:m].cpu().numpy(), hk)
+    inv = np.array([orc.lib().orc_perm_pow2_inv(int(k), bits) for k in hk[:2000]], dtype=np.uint64)
+    hv = np.array([orc.gen_i64_uniform(seed, 1, int(i), 1)[0] for i in inv], dtype=np.int64)
+    assert np.array_equal(out[3].data[:2000].cpu().numpy(), hv)

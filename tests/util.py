@@ -107,3 +107,11 @@ def assert_same_multiset(got, want, float_rel: float = 0.0):
                 assert math.isnan(a) and math.isnan(b)
             else:
                 assert abs(a - b) <= float_rel * max(abs(a), abs(b)), (a, b)
+
+
+def tight_fields(tbl):
+    """Fields whose nullable flag is true only where nulls actually occur, so
+    the no-null kernel variants get exercised (pyarrow marks everything nullable)."""
+    from igloo_b200.arrow import PA_TO_T
+    from igloo_b200.expr import Field
+    return [Field(f.name, PA_TO_T[f.type], tbl.column(f.name).null_count > 0) for f in tbl.schema]
