@@ -101,7 +101,7 @@ __device__ __forceinline__ V load_col(const FpParams& P, int slot, const uint8_t
 }
 
 template <bool HAS_NULLS>
-__device__ __forceinline__ V exec_op(const Instr& in, const V& a, const V& b, unsigned int* err_flags) {
+__device__ __forceinline__ V exec_op(const Instr& in, const V& a, const V& b, uint32_t inrange, unsigned int* err_flags) {
     V d;
     d.ok = HAS_NULLS ? (a.ok & b.ok) : 0xF;
     const int op = in.op, ty = in.type;
@@ -161,7 +161,7 @@ __device__ __forceinline__ V exec_op(const Instr& in, const V& a, const V& b, un
                 for (int r = 0; r < 4; ++r) {
                     int64_t x = ty == IGL_T_I32 ? (int64_t)(int32_t)a.v[r] : (int64_t)a.v[r];
                     int64_t y = ty == IGL_T_I32 ? (int64_t)(int32_t)b.v[r] : (int64_t)b.v[r];
-                    const bool live = (d.ok >> r) & 1;  // arrow evaluates valid slots only
+                    const bool live = ((d.ok & inrange) >> r) & 1;  // arrow evaluates valid slots only; rows past the end do not exist
                     const int64_t mn = ty == IGL_T_I32 ? (int64_t)INT32_MIN : INT64_MIN;
                     int64_t z = 0;
                     if (y == 0) { if (live) ef |= ERRF_DIV_ZERO; }
@@ -212,7 +212,7 @@ __device__ __forceinline__ V exec_op(const Instr& in, const V& a, const V& b, un
             uint32_t ef = 0;
 #pragma unroll
             for (int r = 0; r < 4; ++r) {
-                const bool live = (a.ok >> r) & 1;
+                const bool live = ((a.ok & inrange) >> r) & 1;
                 uint64_t z = 0;
                 if (ty == IGL_T_I32 && to == IGL_T_I64) z = (uint64_t)(int64_t)(int32_t)a.v[r];
                 else if (ty == IGL_T_I32 && to == IGL_T_F64) z = (uint64_t)__double_as_longlong((double)(int32_t)a.v[r]);
@@ -257,7 +257,10 @@ __device__ __forceinline__ V fetch(const FpParams& P, uint8_t kind, uint8_t idx,
 
 // Runs expression `e` of the fused program on this lane's 4 rows.
 template <bool HAS_NULLS>
-__device__ __forceinline__ V run_expr(const FpParams& P, int e, const uint8_t* stage, int row0) {
+__device__ __forceinline__ V run_expr(const FpParams& P, int e, const uint8_t* stage, int row0, int rows_in_tile) {
+    uint32_t inrange = 0;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) inrange |= ((row0 + r * 32) < rows_in_tile ? 1u : 0u) << r;
     V r0, r1, r2, r3;
     r0.ok = r1.ok = r2.ok = r3.ok = 0xF;
 #pragma unroll
@@ -270,7 +273,7 @@ __device__ __forceinline__ V run_expr(const FpParams& P, int e, const uint8_t* s
         V b = a;
         if (in.b_kind != OPK_NONE)
             b = fetch<HAS_NULLS>(P, in.b_kind, in.b_idx, in.b_lit, !is_cast && (in.aux & AUX_B_NULL), stage, row0, r0, r1, r2, r3);
-        V d = exec_op<HAS_NULLS>(in, a, b, &P.T.hdr->err_flags);
+        V d = exec_op<HAS_NULLS>(in, a, b, inrange, &P.T.hdr->err_flags);
         REG_WRITE(in.dst, d)
     }
     V out;
@@ -302,7 +305,7 @@ __global__ void __launch_bounds__(kPipeThreads, 2) fp_kernel(const __grid_consta
         for (int sub = 0; sub < SUBS; ++sub) {
             const int row0 = sub * kPipeRowsPerSub + warp * 128 + lane;
             V m;
-            if (HAS_PRED) m = run_expr<HAS_NULLS>(P, 0, stage, row0);
+            if (HAS_PRED) m = run_expr<HAS_NULLS>(P, 0, stage, row0, rows_in_tile);
             wcount[sub] = 0;
 #pragma unroll
             for (int r = 0; r < 4; ++r) {
@@ -329,7 +332,7 @@ __global__ void __launch_bounds__(kPipeThreads, 2) fp_kernel(const __grid_consta
             for (int sub = 0; sub < SUBS; ++sub) {
                 if (wcount[sub] == 0) continue;   // warp-uniform
                 const int row0 = sub * kPipeRowsPerSub + warp * 128 + lane;
-                const V val = run_expr<HAS_NULLS>(P, e0 + j, stage, row0);
+                const V val = run_expr<HAS_NULLS>(P, e0 + j, stage, row0, rows_in_tile);
                 long long pos = wbase[sub];
 #pragma unroll
                 for (int r = 0; r < 4; ++r) {

@@ -387,6 +387,19 @@ Arr eval(const Node& nd, const BatchView& bv) {
     fail("bad expression node");
 }
 
+// Static result type (PhysicalExpr::data_type): the schema of a stream that
+// carries no batch at all still comes from the planner (projection.rs:19-29).
+int infer_type(const Node& nd, const std::vector<Arr>& cols) {
+    switch (nd.op) {
+        case IGL_OP_COL: return (nd.col >= 0 && nd.col < (int)cols.size()) ? cols[nd.col].type : 0;
+        case IGL_OP_LIT_BOOL: case IGL_OP_LIT_I32: case IGL_OP_LIT_I64: case IGL_OP_LIT_F64: case IGL_OP_LIT_NULL: return nd.lit_type;
+        case IGL_OP_EQ: case IGL_OP_NE: case IGL_OP_LT: case IGL_OP_LE: case IGL_OP_GT: case IGL_OP_GE:
+        case IGL_OP_AND: case IGL_OP_OR: case IGL_OP_NOT: case IGL_OP_IS_NULL: case IGL_OP_IS_NOT_NULL: return IGL_T_BOOL;
+        case IGL_OP_CAST: return nd.cast_to;
+        default: return infer_type(*nd.a, cols);
+    }
+}
+
 // ----------------------------------------------------------------------------
 // Operators
 // ----------------------------------------------------------------------------
@@ -443,6 +456,7 @@ Table* op_project(const Table& in, const std::vector<std::unique_ptr<Node>>& exp
     }
     for (size_t e = 0; e < exprs.size(); ++e) {
         out->cols[e].name = names[e];
+        if (first) out->cols[e].type = infer_type(*exprs[e], in.cols);
         if (out->cols[e].type == IGL_T_UTF8 && out->cols[e].off.empty()) out->cols[e].off.push_back(0);
     }
     return out.release();
