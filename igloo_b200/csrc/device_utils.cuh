@@ -106,34 +106,54 @@ constexpr uint64_t kFlagAggregate = 1ull << 62;
 constexpr uint64_t kFlagPrefix = 2ull << 62;
 constexpr uint64_t kValueMask = (1ull << 62) - 1;
 
-// Called by one full warp.  Publishes `count` for `tile`, walks back over the
-// predecessors 32 at a time until it meets a known prefix, publishes this tile's
-// inclusive prefix and returns the exclusive one (same value in every lane).
+// Publishes a tile's own count (one lane).  Tile 0's count is already a prefix.
+__device__ __forceinline__ void lookback_publish(uint64_t* status, int64_t tile, uint64_t count) {
+    st_volatile_u64(status + tile, (tile == 0 ? kFlagPrefix : kFlagAggregate) | count);
+}
+
+// Called by one full warp after lookback_publish.  Walks back over the
+// predecessors 128 at a time until it meets a known prefix, publishes this
+// tile's inclusive prefix and returns the exclusive one (same value in every
+// lane).  Word j of lane l is predecessor idx - (32*j + l): every load
+// instruction reads 32 consecutive words, i.e. 8 sector requests instead of 32 —
+// hundreds of control warps poll the same few lines of L2, and that traffic, not
+// latency, is what bounds the scan.  A failed poll backs off with nanosleep.
 __device__ __forceinline__ uint64_t lookback_exclusive(uint64_t* status, int64_t tile, uint64_t count, int lane) {
-    if (tile == 0) {
-        if (lane == 0) st_volatile_u64(status, kFlagPrefix | count);
-        return 0;
-    }
-    if (lane == 0) st_volatile_u64(status + tile, kFlagAggregate | count);
+    if (tile == 0) return 0;
     uint64_t excl = 0;
-    int64_t idx = tile - 1;
+    int64_t idx = tile - 1;   // nearest predecessor not yet accounted for
     while (true) {
-        int64_t mine = idx - lane;
-        uint64_t w;
-        do {
-            w = (mine >= 0) ? ld_volatile_u64(status + mine) : kFlagPrefix;  // before tile 0: prefix 0
-        } while (__any_sync(0xffffffffu, (w >> 62) == 0));
-        uint32_t is_prefix = __ballot_sync(0xffffffffu, (w >> 62) == 2);
-        uint64_t v = w & kValueMask;
-        if (is_prefix) {
-            int first = __ffs(is_prefix) - 1;  // nearest predecessor holding a prefix
-            if (lane > first) v = 0;
+        uint64_t w[4];
+        bool pending;
+        unsigned ns = 32;
+        while (true) {
+            pending = false;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int64_t i = idx - (32 * j + lane);
+                w[j] = (i >= 0) ? ld_volatile_u64(status + i) : kFlagPrefix;   // before tile 0: prefix 0
+                pending |= (w[j] >> 62) == 0;
+            }
+            if (!__any_sync(0xffffffffu, pending)) break;
+            __nanosleep(ns);
+            if (ns < 256) ns <<= 1;
         }
+        // nearest known prefix in (j, lane) order
+        int jstar = 4, lstar = 32;
+#pragma unroll
+        for (int j = 3; j >= 0; --j) {
+            const uint32_t b = __ballot_sync(0xffffffffu, (w[j] >> 62) == 2);
+            if (b) { jstar = j; lstar = __ffs(b) - 1; }
+        }
+        uint64_t v = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (j < jstar || (j == jstar && lane <= lstar)) v += w[j] & kValueMask;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
         excl += v;
-        if (is_prefix) break;
-        idx -= 32;
+        if (jstar < 4) break;
+        idx -= 128;
     }
     if (lane == 0) st_volatile_u64(status + tile, kFlagPrefix | (excl + count));
     return excl;

@@ -128,42 +128,58 @@ extern "C" void igl_expr_destroy(igl_expr* e) { delete e; }
 namespace igl {
 
 namespace {
-struct Operand { uint8_t kind; uint8_t idx; uint64_t lit; bool lit_null; };
+struct Operand { uint8_t kind; uint8_t idx; uint64_t lit; bool lit_null; int producer; };
 
 struct Lowerer {
     const igl_expr& e;
     std::vector<Instr>& code;
-    bool reg_used[kMaxRegs] = {};
+    bool tmp_used[kMaxTmp] = {};
+    int max_tmp = 0;
     int32_t err = IGL_OK;
 
-    int alloc() {
-        for (int i = 0; i < kMaxRegs; ++i) if (!reg_used[i]) { reg_used[i] = true; return i; }
+    bool is_leaf(int ni) const {
+        const int op = e.nodes[ni].op;
+        return op == IGL_OP_COL || (op >= IGL_OP_LIT_BOOL && op <= IGL_OP_LIT_NULL);
+    }
+    int alloc_tmp() {
+        for (int i = 0; i < kMaxTmp; ++i)
+            if (!tmp_used[i]) { tmp_used[i] = true; if (i + 1 > max_tmp) max_tmp = i + 1; return i; }
         return -1;
     }
-    void release(const Operand& o) { if (o.kind == OPK_REG) reg_used[o.idx] = false; }
+    void release(const Operand& o) { if (o.kind == OPK_TMP) tmp_used[o.idx] = false; }
 
     Operand lower(int ni) {
         const ExprNode& n = e.nodes[ni];
-        if (n.op == IGL_OP_COL) return {OPK_COL, (uint8_t)n.col, 0, false};
-        if (n.op >= IGL_OP_LIT_BOOL && n.op <= IGL_OP_LIT_NULL) return {OPK_LIT, 0, n.lit_bits, n.lit_null};
-        Operand a{OPK_NONE, 0, 0, false}, b{OPK_NONE, 0, 0, false};
+        if (n.op == IGL_OP_COL) return {OPK_COL, (uint8_t)n.col, 0, false, -1};
+        if (n.op >= IGL_OP_LIT_BOOL && n.op <= IGL_OP_LIT_NULL) return {OPK_LIT, 0, n.lit_bits, n.lit_null, -1};
+        Operand a{OPK_NONE, 0, 0, false, -1}, b{OPK_NONE, 0, 0, false, -1};
         if (n.a >= 0) { a = lower(n.a); if (err < 0) return a; }
-        if (n.b >= 0) { b = lower(n.b); if (err < 0) return b; }
+        if (n.b >= 0) {
+            if (a.kind == OPK_ACC && !is_leaf(n.b)) {
+                // the right subtree will overwrite the accumulator: park the left
+                // result in a temporary by retargeting the instruction that made it
+                const int t = alloc_tmp();
+                if (t < 0) { err = fail(IGL_ERR_UNSUPPORTED, "expression needs more than %d parked temporaries", kMaxTmp); return a; }
+                code[a.producer].dst_kind = OPK_TMP;
+                code[a.producer].dst_idx = (uint8_t)t;
+                a.kind = OPK_TMP; a.idx = (uint8_t)t;
+            }
+            b = lower(n.b);
+            if (err < 0) return b;
+        }
         release(a); release(b);
-        int d = alloc();
-        if (d < 0) { err = fail(IGL_ERR_UNSUPPORTED, "expression needs more than %d live temporaries", kMaxRegs); return a; }
         Instr in{};
         in.op = (uint8_t)n.op;
         in.type = (uint8_t)(n.a >= 0 ? e.nodes[n.a].type : n.type);  // operand type
-        in.dst = (uint8_t)d;
         in.a_kind = a.kind; in.a_idx = a.idx; in.a_lit = a.lit;
         in.b_kind = b.kind; in.b_idx = b.idx; in.b_lit = b.lit;
+        in.dst_kind = OPK_ACC;
         in.aux = (n.op == IGL_OP_CAST) ? (uint8_t)n.cast_to : (uint8_t)((a.lit_null ? AUX_A_NULL : 0) | (b.lit_null ? AUX_B_NULL : 0));
         if (n.op == IGL_OP_CAST && a.lit_null) {  // CAST(NULL) stays NULL: lower as a null literal move
             in.op = IOP_MOV; in.type = (uint8_t)n.type; in.aux = AUX_A_NULL;
         }
         code.push_back(in);
-        return {OPK_REG, (uint8_t)d, 0, false};
+        return {OPK_ACC, 0, 0, false, (int)code.size() - 1};
     }
 };
 }  // namespace
@@ -173,17 +189,16 @@ int32_t lower_expr(const igl_expr& e, std::vector<Instr>& code, LoweredExpr& out
     out.first = (int)code.size();
     Operand r = L.lower((int)e.nodes.size() - 1);
     if (L.err < 0) return L.err;
-    if (r.kind != OPK_REG) {  // a bare column or literal: one MOV so the result sits in a register
+    if (r.kind != OPK_ACC) {  // a bare column or literal: one MOV so the result sits in the accumulator
         Instr in{};
-        in.op = IOP_MOV; in.type = (uint8_t)e.type; in.dst = 0;
+        in.op = IOP_MOV; in.type = (uint8_t)e.type;
         in.a_kind = r.kind; in.a_idx = r.idx; in.a_lit = r.lit;
+        in.dst_kind = OPK_ACC;
         in.aux = r.lit_null ? AUX_A_NULL : 0;
         code.push_back(in);
-        out.result_reg = 0;
-    } else {
-        out.result_reg = r.idx;
     }
     out.count = (int)code.size() - out.first;
+    out.n_tmp = L.max_tmp;
     out.type = e.type;
     out.nullable = e.nullable;
     if ((int)code.size() > kMaxInstr) return fail(IGL_ERR_UNSUPPORTED, "fused operator exceeds %d instructions", kMaxInstr);

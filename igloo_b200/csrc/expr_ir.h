@@ -11,7 +11,7 @@ namespace igl {
 struct LoweredExpr {
     int first = 0;       // index of the first instruction in the fused program
     int count = 0;       // number of instructions
-    int result_reg = 0;  // register holding the value after the last instruction
+    int n_tmp = 0;       // shared-memory temporaries the expression needs
     int type = 0;
     bool nullable = false;
 };

@@ -7,19 +7,21 @@
 //   projection.rs:48-72  one output column per expression, literals broadcast
 // and the planner-side fusion of Projection(Filter(x)) (physical_planner.rs:52-94).
 //
-// Kernel shape (one persistent CTA = 8 compute warps + 1 control warp):
-//   * the control warp takes tile tickets in order, streams each tile's
-//     referenced column slices into a shared-memory ring with 1-D bulk async
-//     copies (TMA engine, mbarrier complete_tx), and runs the ordered
-//     single-pass scan (decoupled look-back) that turns per-tile survivor
-//     counts into global output offsets;
-//   * compute warps interpret the fused three-address program on 4 rows per
-//     lane held in registers (lane i owns rows i, i+32, i+64, i+96 of its warp's
-//     128-row group, so every ballot covers 32 consecutive rows and compacted
-//     stores are contiguous per instruction), count survivors with
-//     __ballot_sync/__popc, and write the projected columns straight to their
-//     final positions.  No intermediate array ever reaches HBM.
-// HBM traffic = referenced input columns once + surviving output rows once.
+// Kernel shape (tile_pipe.cuh: one persistent CTA = compute warps + 1 control warp):
+//   * the control warp streams each tile's referenced column slices into a
+//     shared-memory ring with 1-D bulk async copies (TMA engine, mbarrier
+//     complete_tx) and runs the ordered single-pass scan (decoupled look-back)
+//     that turns per-warp survivor counts into global output offsets;
+//   * compute warps interpret the fused program (an accumulator machine whose
+//     operands are staged columns, literals or per-warp shared-memory
+//     temporaries) on 4 rows per lane held in registers — lane i owns rows
+//     i, i+32, i+64, i+96 of its warp's 128-row group, so every ballot covers 32
+//     consecutive rows and compacted stores are contiguous per instruction —
+//     count survivors with __ballot_sync/__popc and write the projected columns
+//     straight to their final positions.  The predicate of tile t+1 is evaluated
+//     before the outputs of tile t are written, hiding the scan latency.
+// HBM traffic = referenced input columns once + surviving output rows once;
+// no intermediate array ever reaches HBM.
 #include "expr_ir.h"
 #include "kernels.h"
 #include "tile_pipe.cuh"
@@ -28,61 +30,48 @@
 
 namespace igl {
 
-constexpr int kMaxOut = 16;
+constexpr int kMaxOut = 17;   // 16 expressions + the optional row-id column
 
 enum : uint32_t { ERRF_DIV_ZERO = 1, ERRF_OVERFLOW = 2, ERRF_CAST = 4 };
 
 struct FpParams {
     Instr code[kMaxInstr];
-    uint8_t expr_first[kMaxExprs], expr_count[kMaxExprs], expr_reg[kMaxExprs];
-    uint8_t n_out, pad0[3];
+    uint8_t expr_first[kMaxExprs], expr_count[kMaxExprs];
+    uint8_t n_out, n_tmp, pad0[2];
+    uint32_t tmp_off;              // byte offset of the per-warp temporaries in dynamic shared memory
     PipeCols T;                    // staged input columns + scan state
     void* out_data[kMaxOut];
     uint8_t* out_valid[kMaxOut];   // byte-per-row validity (packed afterwards) or NULL
     uint8_t out_shift[kMaxOut];    // 2 / 3, or 0 = byte per row (boolean, packed afterwards)
 };
 
+template <int R>
 struct V {
-    uint64_t v[4];
+    uint64_t v[R];
     uint32_t ok;  // bit r = row r is valid (non-null)
 };
-
-#define REG_READ(dst, idx)            \
-    switch (idx) {                    \
-        case 0: dst = r0; break;      \
-        case 1: dst = r1; break;      \
-        case 2: dst = r2; break;      \
-        default: dst = r3; break;     \
-    }
-#define REG_WRITE(idx, src)           \
-    switch (idx) {                    \
-        case 0: r0 = src; break;      \
-        case 1: r1 = src; break;      \
-        case 2: r2 = src; break;      \
-        default: r3 = src; break;     \
-    }
-static_assert(kMaxRegs == 4, "REG_READ / REG_WRITE enumerate the value registers");
+template <int R> struct FullMask { static constexpr uint32_t value = (1u << R) - 1u; };
 
 __device__ __forceinline__ int64_t total_order_key(uint64_t bits) {
     int64_t b = (int64_t)bits;
     return b ^ (int64_t)(((uint64_t)(b >> 63)) >> 1);
 }
 
-template <bool HAS_NULLS>
-__device__ __forceinline__ V load_col(const FpParams& P, int slot, const uint8_t* stage, int row0) {
-    V x;
-    x.ok = 0xF;
+template <int R, bool HAS_NULLS>
+__device__ __forceinline__ V<R> load_col(const FpParams& P, int slot, const uint8_t* stage, int row0) {
+    V<R> x;
+    x.ok = FullMask<R>::value;
     const uint8_t* base = stage + P.T.smem_off[slot];
     const int sh = P.T.shift[slot];
     if (sh == 2) {
 #pragma unroll
-        for (int r = 0; r < 4; ++r) x.v[r] = *reinterpret_cast<const uint32_t*>(base + ((row0 + r * 32) << 2));
+        for (int r = 0; r < R; ++r) x.v[r] = *reinterpret_cast<const uint32_t*>(base + ((row0 + r * 32) << 2));
     } else if (sh == 3) {
 #pragma unroll
-        for (int r = 0; r < 4; ++r) x.v[r] = *reinterpret_cast<const uint64_t*>(base + ((row0 + r * 32) << 3));
+        for (int r = 0; r < R; ++r) x.v[r] = *reinterpret_cast<const uint64_t*>(base + ((row0 + r * 32) << 3));
     } else {
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
+        for (int r = 0; r < R; ++r) {
             int row = row0 + r * 32;
             x.v[r] = (base[row >> 3] >> (row & 7)) & 1;
         }
@@ -91,7 +80,7 @@ __device__ __forceinline__ V load_col(const FpParams& P, int slot, const uint8_t
         const uint8_t* vb = stage + P.T.valid_off[slot];
         uint32_t ok = 0;
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
+        for (int r = 0; r < R; ++r) {
             int row = row0 + r * 32;
             ok |= ((vb[row >> 3] >> (row & 7)) & 1u) << r;
         }
@@ -100,10 +89,10 @@ __device__ __forceinline__ V load_col(const FpParams& P, int slot, const uint8_t
     return x;
 }
 
-template <bool HAS_NULLS>
-__device__ __forceinline__ V exec_op(const Instr& in, const V& a, const V& b, uint32_t inrange, unsigned int* err_flags) {
-    V d;
-    d.ok = HAS_NULLS ? (a.ok & b.ok) : 0xF;
+template <int R, bool HAS_NULLS>
+__device__ __forceinline__ V<R> exec_op(const Instr& in, const V<R>& a, const V<R>& b, uint32_t inrange, unsigned int* err_flags) {
+    V<R> d;
+    d.ok = HAS_NULLS ? (a.ok & b.ok) : FullMask<R>::value;
     const int op = in.op, ty = in.type;
     switch (op) {
         case IOP_MOV:
@@ -111,7 +100,7 @@ __device__ __forceinline__ V exec_op(const Instr& in, const V& a, const V& b, ui
             break;
         case IGL_OP_EQ: case IGL_OP_NE: case IGL_OP_LT: case IGL_OP_LE: case IGL_OP_GT: case IGL_OP_GE: {
 #pragma unroll
-            for (int r = 0; r < 4; ++r) {
+            for (int r = 0; r < R; ++r) {
                 int64_t x, y;
                 if (ty == IGL_T_I32) { x = (int32_t)a.v[r]; y = (int32_t)b.v[r]; }
                 else if (ty == IGL_T_F64) { x = total_order_key(a.v[r]); y = total_order_key(b.v[r]); }
@@ -133,7 +122,7 @@ __device__ __forceinline__ V exec_op(const Instr& in, const V& a, const V& b, ui
         case IGL_OP_ADD: case IGL_OP_SUB: case IGL_OP_MUL: {
             if (ty == IGL_T_F64) {
 #pragma unroll
-                for (int r = 0; r < 4; ++r) {
+                for (int r = 0; r < R; ++r) {
                     double x = __longlong_as_double((long long)a.v[r]), y = __longlong_as_double((long long)b.v[r]);
                     // explicit round-to-nearest intrinsics: never contracted into an FMA
                     double z = op == IGL_OP_ADD ? __dadd_rn(x, y) : op == IGL_OP_SUB ? __dsub_rn(x, y) : __dmul_rn(x, y);
@@ -141,7 +130,7 @@ __device__ __forceinline__ V exec_op(const Instr& in, const V& a, const V& b, ui
                 }
             } else {  // two's-complement wrap; I32 lives in the low 32 bits
 #pragma unroll
-                for (int r = 0; r < 4; ++r)
+                for (int r = 0; r < R; ++r)
                     d.v[r] = op == IGL_OP_ADD ? a.v[r] + b.v[r] : op == IGL_OP_SUB ? a.v[r] - b.v[r]
                              : (ty == IGL_T_I32 ? (uint64_t)((uint32_t)a.v[r] * (uint32_t)b.v[r]) : a.v[r] * b.v[r]);
             }
@@ -150,7 +139,7 @@ __device__ __forceinline__ V exec_op(const Instr& in, const V& a, const V& b, ui
         case IGL_OP_DIV: case IGL_OP_MOD: {
             if (ty == IGL_T_F64) {
 #pragma unroll
-                for (int r = 0; r < 4; ++r) {
+                for (int r = 0; r < R; ++r) {
                     double x = __longlong_as_double((long long)a.v[r]), y = __longlong_as_double((long long)b.v[r]);
                     double z = op == IGL_OP_DIV ? __ddiv_rn(x, y) : fmod(x, y);
                     d.v[r] = (uint64_t)__double_as_longlong(z);
@@ -158,7 +147,7 @@ __device__ __forceinline__ V exec_op(const Instr& in, const V& a, const V& b, ui
             } else {
                 uint32_t ef = 0;
 #pragma unroll
-                for (int r = 0; r < 4; ++r) {
+                for (int r = 0; r < R; ++r) {
                     int64_t x = ty == IGL_T_I32 ? (int64_t)(int32_t)a.v[r] : (int64_t)a.v[r];
                     int64_t y = ty == IGL_T_I32 ? (int64_t)(int32_t)b.v[r] : (int64_t)b.v[r];
                     const bool live = ((d.ok & inrange) >> r) & 1;  // arrow evaluates valid slots only; rows past the end do not exist
@@ -177,14 +166,14 @@ __device__ __forceinline__ V exec_op(const Instr& in, const V& a, const V& b, ui
         case IGL_OP_NEG: {
             d.ok = a.ok;
 #pragma unroll
-            for (int r = 0; r < 4; ++r)
+            for (int r = 0; r < R; ++r)
                 d.v[r] = ty == IGL_T_F64 ? (a.v[r] ^ 0x8000000000000000ull) : (0ull - a.v[r]);
             break;
         }
         case IGL_OP_AND: case IGL_OP_OR: {  // Kleene
             uint32_t ok = 0;
 #pragma unroll
-            for (int r = 0; r < 4; ++r) {
+            for (int r = 0; r < R; ++r) {
                 const bool av = (a.ok >> r) & 1, bv = (b.ok >> r) & 1;
                 const bool x = av && (a.v[r] & 1), y = bv && (b.v[r] & 1);
                 bool val, known;
@@ -193,25 +182,25 @@ __device__ __forceinline__ V exec_op(const Instr& in, const V& a, const V& b, ui
                 d.v[r] = val ? 1 : 0;
                 ok |= (known ? 1u : 0u) << r;
             }
-            d.ok = HAS_NULLS ? ok : 0xF;
+            d.ok = HAS_NULLS ? ok : FullMask<R>::value;
             break;
         }
         case IGL_OP_NOT:
             d.ok = a.ok;
 #pragma unroll
-            for (int r = 0; r < 4; ++r) d.v[r] = (a.v[r] & 1) ^ 1;
+            for (int r = 0; r < R; ++r) d.v[r] = (a.v[r] & 1) ^ 1;
             break;
         case IGL_OP_IS_NULL: case IGL_OP_IS_NOT_NULL:
-            d.ok = 0xF;
+            d.ok = FullMask<R>::value;
 #pragma unroll
-            for (int r = 0; r < 4; ++r) d.v[r] = (((a.ok >> r) & 1) != 0) == (op == IGL_OP_IS_NOT_NULL) ? 1 : 0;
+            for (int r = 0; r < R; ++r) d.v[r] = (((a.ok >> r) & 1) != 0) == (op == IGL_OP_IS_NOT_NULL) ? 1 : 0;
             break;
         case IGL_OP_CAST: {
             d.ok = a.ok;
             const int to = in.aux;
             uint32_t ef = 0;
 #pragma unroll
-            for (int r = 0; r < 4; ++r) {
+            for (int r = 0; r < R; ++r) {
                 const bool live = ((a.ok & inrange) >> r) & 1;
                 uint64_t z = 0;
                 if (ty == IGL_T_I32 && to == IGL_T_I64) z = (uint64_t)(int64_t)(int32_t)a.v[r];
@@ -239,116 +228,165 @@ __device__ __forceinline__ V exec_op(const Instr& in, const V& a, const V& b, ui
     return d;
 }
 
-template <bool HAS_NULLS>
-__device__ __forceinline__ V fetch(const FpParams& P, uint8_t kind, uint8_t idx, uint64_t lit, bool lit_null,
-                                   const uint8_t* stage, int row0, const V& r0, const V& r1, const V& r2,
-                                   const V& r3) {
-    V x;
-    if (kind == OPK_REG) {
-        REG_READ(x, idx)
+// Per-warp temporaries: kMaxTmp x 128 rows x 8 bytes, then one validity nibble per lane.
+struct WarpTmp {
+    uint64_t* vals;   // [n_tmp][128]
+    uint8_t* oks;     // [n_tmp][32]
+};
+
+template <int R, bool HAS_NULLS>
+__device__ __forceinline__ V<R> fetch(const FpParams& P, uint8_t kind, uint8_t idx, uint64_t lit, bool lit_null,
+                                   const uint8_t* stage, int row0, const V<R>& acc, const WarpTmp& tmp, int lane) {
+    V<R> x;
+    if (kind == OPK_ACC) {
+        x = acc;
     } else if (kind == OPK_COL) {
-        x = load_col<HAS_NULLS>(P, idx, stage, row0);
+        x = load_col<R, HAS_NULLS>(P, idx, stage, row0);
+    } else if (kind == OPK_TMP) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) x.v[r] = tmp.vals[idx * (32 * R) + r * 32 + lane];
+        x.ok = HAS_NULLS ? tmp.oks[idx * 32 + lane] : FullMask<R>::value;
     } else {
-        x.v[0] = x.v[1] = x.v[2] = x.v[3] = lit;
-        x.ok = (HAS_NULLS && lit_null) ? 0 : 0xF;
+        #pragma unroll
+        for (int r = 0; r < R; ++r) x.v[r] = lit;
+        x.ok = (HAS_NULLS && lit_null) ? 0 : FullMask<R>::value;
     }
     return x;
 }
 
 // Runs expression `e` of the fused program on this lane's 4 rows.
-template <bool HAS_NULLS>
-__device__ __forceinline__ V run_expr(const FpParams& P, int e, const uint8_t* stage, int row0, int rows_in_tile) {
+template <int R, bool HAS_NULLS>
+__device__ __forceinline__ V<R> run_expr(const FpParams& P, int e, const uint8_t* stage, int row0, int rows_in_tile,
+                                      long long grow0, const WarpTmp& tmp, int lane) {
     uint32_t inrange = 0;
 #pragma unroll
-    for (int r = 0; r < 4; ++r) inrange |= ((row0 + r * 32) < rows_in_tile ? 1u : 0u) << r;
-    V r0, r1, r2, r3;
-    r0.ok = r1.ok = r2.ok = r3.ok = 0xF;
+    for (int r = 0; r < R; ++r) inrange |= ((row0 + r * 32) < rows_in_tile ? 1u : 0u) << r;
+    V<R> acc;
+    acc.ok = FullMask<R>::value;
 #pragma unroll
-    for (int r = 0; r < 4; ++r) r0.v[r] = r1.v[r] = r2.v[r] = r3.v[r] = 0;
+    for (int r = 0; r < R; ++r) acc.v[r] = 0;
     const int first = P.expr_first[e], last = first + P.expr_count[e];
     for (int pc = first; pc < last; ++pc) {
         const Instr& in = P.code[pc];
-        const bool is_cast = in.op == IGL_OP_CAST;
-        V a = fetch<HAS_NULLS>(P, in.a_kind, in.a_idx, in.a_lit, !is_cast && (in.aux & AUX_A_NULL), stage, row0, r0, r1, r2, r3);
-        V b = a;
-        if (in.b_kind != OPK_NONE)
-            b = fetch<HAS_NULLS>(P, in.b_kind, in.b_idx, in.b_lit, !is_cast && (in.aux & AUX_B_NULL), stage, row0, r0, r1, r2, r3);
-        V d = exec_op<HAS_NULLS>(in, a, b, inrange, &P.T.hdr->err_flags);
-        REG_WRITE(in.dst, d)
+        V<R> d;
+        if (in.op == IOP_ROWID) {
+            d.ok = FullMask<R>::value;
+#pragma unroll
+            for (int r = 0; r < R; ++r) d.v[r] = (uint64_t)(grow0 + r * 32);
+        } else {
+            const bool is_cast = in.op == IGL_OP_CAST;
+            const V<R> a = fetch<R, HAS_NULLS>(P, in.a_kind, in.a_idx, in.a_lit, !is_cast && (in.aux & AUX_A_NULL), stage, row0, acc, tmp, lane);
+            V<R> b = a;
+            if (in.b_kind != OPK_NONE)
+                b = fetch<R, HAS_NULLS>(P, in.b_kind, in.b_idx, in.b_lit, !is_cast && (in.aux & AUX_B_NULL), stage, row0, acc, tmp, lane);
+            d = exec_op<R, HAS_NULLS>(in, a, b, inrange, &P.T.hdr->err_flags);
+        }
+        if (in.dst_kind == OPK_TMP) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) tmp.vals[in.dst_idx * (32 * R) + r * 32 + lane] = d.v[r];
+            if (HAS_NULLS) tmp.oks[in.dst_idx * 32 + lane] = (uint8_t)d.ok;
+        } else {
+            acc = d;
+        }
     }
-    V out;
-    REG_READ(out, P.expr_reg[e])
-    return out;
+    return acc;
 }
 
-template <int SUBS, bool HAS_PRED, bool HAS_NULLS>
-__global__ void __launch_bounds__(kPipeThreads, 2) fp_kernel(const __grid_constant__ FpParams P) {
+template <int R>
+struct FpTile {
+    const uint8_t* stage;
+    long long row_begin;
+    int rows;
+    uint32_t keep[R];   // ballots: bit = lane whose row (r*32 + lane) survives
+    int count;
+};
+
+template <int R, bool HAS_PRED, bool HAS_NULLS>
+__device__ __forceinline__ void fp_count(const FpParams& P, FpTile<R>& t, int warp, int lane, const WarpTmp& tmp) {
+    const int row0 = warp * (32 * R) + lane;
+    V<R> m;
+    const bool owner = warp < P.T.active_warps;   // warp-uniform
+    if (HAS_PRED && owner) m = run_expr<R, HAS_NULLS>(P, 0, t.stage, row0, t.rows, t.row_begin + row0, tmp, lane);
+    t.count = 0;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        bool k = owner && (row0 + r * 32) < t.rows;
+        if (HAS_PRED) k = k && ((m.ok >> r) & 1) && (m.v[r] & 1);   // null mask => row dropped
+        t.keep[r] = __ballot_sync(0xffffffffu, k);
+        t.count += __popc(t.keep[r]);
+    }
+}
+
+template <int R, bool HAS_PRED, bool HAS_NULLS>
+__device__ __forceinline__ void fp_write(const FpParams& P, const FpTile<R>& t, long long wbase, int warp, int lane,
+                                         const WarpTmp& tmp) {
+    if (t.count == 0) return;   // warp-uniform
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const int row0 = warp * (32 * R) + lane;
+    const int e0 = HAS_PRED ? 1 : 0;
+    for (int j = 0; j < P.n_out; ++j) {
+        uint8_t* od = reinterpret_cast<uint8_t*>(P.out_data[j]);
+        uint8_t* ov = HAS_NULLS ? P.out_valid[j] : nullptr;
+        const int osh = P.out_shift[j];
+        const V<R> val = run_expr<R, HAS_NULLS>(P, e0 + j, t.stage, row0, t.rows, t.row_begin + row0, tmp, lane);
+        long long pos = wbase;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const uint32_t kb = t.keep[r];
+            if ((kb >> lane) & 1u) {
+                const long long p = pos + __popc(kb & lt_mask);
+                if (osh == 2) st_cs_u32(od + (p << 2), (uint32_t)val.v[r]);
+                else if (osh == 3) st_cs_u64(od + (p << 3), val.v[r]);
+                else od[p] = (uint8_t)(val.v[r] & 1);
+                if (HAS_NULLS && ov) ov[p] = (uint8_t)((val.ok >> r) & 1u);
+            }
+            pos += __popc(kb);
+        }
+    }
+}
+
+template <int R, bool HAS_PRED, bool HAS_NULLS>
+__global__ void __launch_bounds__(kPipeThreads, kPipeMinCtas) fp_kernel(const __grid_constant__ FpParams P) {
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ PipeShared<SUBS> sh;
-    TilePipe<SUBS, HAS_PRED, HAS_NULLS> pipe(P.T, sh, smem);
+    __shared__ PipeShared sh;
+    TilePipe<HAS_PRED, HAS_NULLS> pipe(P.T, sh, smem);
     pipe.init();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (warp == kPipeComputeWarps) {
         pipe.control_loop();
         return;
     }
-    const uint32_t lt_mask = (1u << lane) - 1u;
+    WarpTmp tmp;
+    tmp.vals = reinterpret_cast<uint64_t*>(smem + P.tmp_off) + (size_t)warp * P.n_tmp * (32 * R);
+    tmp.oks = smem + P.tmp_off + (size_t)kPipeComputeWarps * P.n_tmp * 1024 + (size_t)warp * P.n_tmp * 32;
+
+    if (!HAS_PRED) {   // nothing to scan: output position == input position
+        for (int it = 0;; ++it) {
+            FpTile<R> t;
+            if (!pipe.acquire(it, t.stage, t.row_begin, t.rows)) break;
+            fp_count<R, false, HAS_NULLS>(P, t, warp, lane, tmp);
+            fp_write<R, false, HAS_NULLS>(P, t, t.row_begin + warp * (32 * R), warp, lane, tmp);
+            pipe.release(it);
+        }
+        return;
+    }
+    // software pipeline: count(t+1) is issued before write(t)
+    FpTile<R> cur;
+    if (!pipe.acquire(0, cur.stage, cur.row_begin, cur.rows)) return;
+    fp_count<R, true, HAS_NULLS>(P, cur, warp, lane, tmp);
+    pipe.post_count(0, warp, cur.count);
     for (int it = 0;; ++it) {
-        const uint8_t* stage;
-        long long row_begin;
-        int rows_in_tile;
-        if (!pipe.acquire(it, stage, row_begin, rows_in_tile)) break;
-
-        uint32_t keep[SUBS][4];   // ballots: bit = lane whose row (r*32 + lane) survives
-        long long wcount[SUBS];
-#pragma unroll
-        for (int sub = 0; sub < SUBS; ++sub) {
-            const int row0 = sub * kPipeRowsPerSub + warp * 128 + lane;
-            V m;
-            if (HAS_PRED) m = run_expr<HAS_NULLS>(P, 0, stage, row0, rows_in_tile);
-            wcount[sub] = 0;
-#pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                bool k = (row0 + r * 32) < rows_in_tile;
-                if (HAS_PRED) k = k && ((m.ok >> r) & 1) && (m.v[r] & 1);   // null mask => row dropped
-                keep[sub][r] = __ballot_sync(0xffffffffu, k);
-                wcount[sub] += __popc(keep[sub][r]);
-            }
+        FpTile<R> nxt;
+        const bool has_next = pipe.acquire(it + 1, nxt.stage, nxt.row_begin, nxt.rows);
+        if (has_next) {
+            fp_count<R, true, HAS_NULLS>(P, nxt, warp, lane, tmp);
+            pipe.post_count(it + 1, warp, nxt.count);
         }
-        long long wbase[SUBS];
-        if (HAS_PRED) {
-            pipe.offsets(it, warp, wcount, wbase);
-        } else {
-#pragma unroll
-            for (int sub = 0; sub < SUBS; ++sub) wbase[sub] = row_begin + sub * kPipeRowsPerSub + warp * 128;
-        }
-
-        const int e0 = HAS_PRED ? 1 : 0;
-        for (int j = 0; j < P.n_out; ++j) {
-            uint8_t* od = reinterpret_cast<uint8_t*>(P.out_data[j]);
-            uint8_t* ov = HAS_NULLS ? P.out_valid[j] : nullptr;
-            const int osh = P.out_shift[j];
-#pragma unroll
-            for (int sub = 0; sub < SUBS; ++sub) {
-                if (wcount[sub] == 0) continue;   // warp-uniform
-                const int row0 = sub * kPipeRowsPerSub + warp * 128 + lane;
-                const V val = run_expr<HAS_NULLS>(P, e0 + j, stage, row0, rows_in_tile);
-                long long pos = wbase[sub];
-#pragma unroll
-                for (int r = 0; r < 4; ++r) {
-                    const uint32_t kb = keep[sub][r];
-                    if ((kb >> lane) & 1u) {
-                        const long long p = pos + __popc(kb & lt_mask);
-                        if (osh == 2) st_cs_u32(od + (p << 2), (uint32_t)val.v[r]);
-                        else if (osh == 3) st_cs_u64(od + (p << 3), val.v[r]);
-                        else od[p] = (uint8_t)(val.v[r] & 1);
-                        if (HAS_NULLS && ov) ov[p] = (uint8_t)((val.ok >> r) & 1u);
-                    }
-                    pos += __popc(kb);
-                }
-            }
-        }
+        const long long wbase = pipe.wait_base(it, warp);
+        fp_write<R, true, HAS_NULLS>(P, cur, wbase, warp, lane, tmp);
         pipe.release(it);
+        if (!has_next) break;
+        cur = nxt;
     }
 }
 
@@ -384,7 +422,7 @@ struct igl_fp {
     igl_ctx* ctx = nullptr;
     FpParams params{};
     bool has_pred = false, has_nulls = false;
-    int subs = 2;
+    int rows_per_lane = 4;
     int n_in = 0;
     std::vector<int> in_types;
     std::vector<int> slot_of_col;            // schema column -> staged slot, -1 = not read
@@ -408,10 +446,10 @@ namespace {
 
 typedef void (*fp_kernel_t)(const FpParams);
 
-fp_kernel_t pick_kernel(int subs, bool pred, bool nulls) {
-    if (subs == 2) {
-        if (pred) return nulls ? fp_kernel<2, true, true> : fp_kernel<2, true, false>;
-        return nulls ? fp_kernel<2, false, true> : fp_kernel<2, false, false>;
+fp_kernel_t pick_kernel(int rows_per_lane, bool pred, bool nulls) {
+    if (rows_per_lane == 4) {
+        if (pred) return nulls ? fp_kernel<4, true, true> : fp_kernel<4, true, false>;
+        return nulls ? fp_kernel<4, false, true> : fp_kernel<4, false, false>;
     }
     if (pred) return nulls ? fp_kernel<1, true, true> : fp_kernel<1, true, false>;
     return nulls ? fp_kernel<1, false, true> : fp_kernel<1, false, false>;
@@ -423,6 +461,16 @@ extern "C" {
 
 int32_t igl_fp_create(igl_ctx* ctx, const int32_t* in_types, const uint8_t* in_nullable, int32_t n_in,
                       const igl_expr* pred, const igl_expr* const* proj, int32_t nproj, igl_fp** out) {
+    return igl::fp_create_ex(ctx, in_types, in_nullable, n_in, pred, proj, nproj, nullptr, false, out);
+}
+
+}  // extern "C"
+
+// `skip` (optional, n_in flags): input columns a pass-through FilterExec must not
+// emit on the device (Utf8 columns, gathered afterwards through the row ids).
+int32_t igl::fp_create_ex(igl_ctx* ctx, const int32_t* in_types, const uint8_t* in_nullable, int32_t n_in,
+                          const igl_expr* pred, const igl_expr* const* proj, int32_t nproj, const uint8_t* skip,
+                          bool with_rowid, igl_fp** out) {
     if (!ctx || !out || n_in <= 0 || !in_types) return fail(IGL_ERR_INVALID_ARG, "igl_fp_create: bad arguments");
     *out = nullptr;
     if (nproj < 0 || (nproj > 0 && !proj)) return fail(IGL_ERR_INVALID_ARG, "igl_fp_create: bad projection list");
@@ -439,6 +487,7 @@ int32_t igl_fp_create(igl_ctx* ctx, const int32_t* in_types, const uint8_t* in_n
     std::vector<const igl_expr*> outs;
     if (nproj == 0) {
         for (int c = 0; c < n_in; ++c) {
+            if (skip && skip[c]) continue;
             uint8_t bc[3] = {IGL_OP_COL, (uint8_t)(c & 0xFF), (uint8_t)(c >> 8)};
             igl_expr* e = nullptr;
             IGL_TRY(igl_expr_compile(ctx, bc, 3, in_types, in_nullable, n_in, &e));
@@ -451,7 +500,7 @@ int32_t igl_fp_create(igl_ctx* ctx, const int32_t* in_types, const uint8_t* in_n
             outs.push_back(proj[j]);
         }
     }
-    if ((int)outs.size() > kMaxOut) return fail(IGL_ERR_UNSUPPORTED, "more than %d output columns", kMaxOut);
+    if ((int)outs.size() > kMaxOut - 1) return fail(IGL_ERR_UNSUPPORTED, "more than %d output columns", kMaxOut - 1);
     for (auto* e : outs) {
         if (e->ncols != n_in) return fail(IGL_ERR_INVALID_ARG, "expression compiled against a different schema");
         if (e->type == IGL_T_UTF8) return fail(IGL_ERR_UNSUPPORTED, "Utf8 output columns go through the operator API (gather by row index)");
@@ -480,6 +529,7 @@ int32_t igl_fp_create(igl_ctx* ctx, const int32_t* in_types, const uint8_t* in_n
     // lower: expression 0 = predicate (if any), then the outputs
     std::vector<Instr> code;
     std::vector<const igl_expr*> all;
+    int n_tmp = 0;
     if (pred) all.push_back(pred);
     for (auto* e : outs) all.push_back(e);
     for (size_t i = 0; i < all.size(); ++i) {
@@ -487,28 +537,44 @@ int32_t igl_fp_create(igl_ctx* ctx, const int32_t* in_types, const uint8_t* in_n
         IGL_TRY(lower_expr(*all[i], code, le));
         P.expr_first[i] = (uint8_t)le.first;
         P.expr_count[i] = (uint8_t)le.count;
-        P.expr_reg[i] = (uint8_t)le.result_reg;
+        n_tmp = std::max(n_tmp, le.n_tmp);
+    }
+    if (with_rowid) {   // extra Int32 output: the input row index of every surviving row
+        Instr in{};
+        in.op = IOP_ROWID; in.type = IGL_T_I32; in.dst_kind = OPK_ACC;
+        P.expr_first[all.size()] = (uint8_t)code.size();
+        P.expr_count[all.size()] = 1;
+        code.push_back(in);
+        if ((int)code.size() > kMaxInstr) return fail(IGL_ERR_UNSUPPORTED, "fused operator exceeds %d instructions", kMaxInstr);
     }
     for (auto& in : code) {  // schema column index -> staged slot
         if (in.a_kind == OPK_COL) in.a_idx = (uint8_t)fp->slot_of_col[in.a_idx];
         if (in.b_kind == OPK_COL) in.b_idx = (uint8_t)fp->slot_of_col[in.b_idx];
     }
     memcpy(P.code, code.data(), code.size() * sizeof(Instr));
-    P.n_out = (uint8_t)outs.size();
+    P.n_out = (uint8_t)(outs.size() + (with_rowid ? 1 : 0));
     for (size_t j = 0; j < outs.size(); ++j) {
         fp->out_types.push_back(outs[j]->type);
         fp->out_nullable.push_back(outs[j]->nullable ? 1 : 0);
         P.out_shift[j] = outs[j]->type == IGL_T_BOOL ? 0 : (outs[j]->type == IGL_T_I32 ? 2 : 3);
     }
+    if (with_rowid) {
+        fp->out_types.push_back(IGL_T_I32);
+        fp->out_nullable.push_back(0);
+        P.out_shift[outs.size()] = 2;
+    }
 
-    // shared-memory ring geometry
-    PipeGeometry geo = pipe_geometry(shifts, nslots, P.T);
+    // shared-memory ring geometry (+ per-warp temporaries behind the ring)
+    const uint32_t tmp_bytes = (uint32_t)n_tmp * kPipeComputeWarps * (1024 + 32);
+    PipeGeometry geo = pipe_geometry(shifts, nslots, P.T, tmp_bytes);
     if (!geo.ok) return fail(IGL_ERR_UNSUPPORTED, "referenced columns need %u bytes per tile; too wide for one pass", geo.stage_bytes);
-    fp->subs = geo.subs;
-    fp->smem_bytes = (size_t)geo.stage_bytes * geo.stages;
+    fp->rows_per_lane = geo.rows_per_lane;
+    P.n_tmp = (uint8_t)n_tmp;
+    P.tmp_off = geo.stage_bytes * geo.stages;
+    fp->smem_bytes = (size_t)geo.stage_bytes * geo.stages + tmp_bytes;
 
     DeviceGuard g(ctx->device);
-    fp_kernel_t k = pick_kernel(fp->subs, fp->has_pred, fp->has_nulls);
+    fp_kernel_t k = pick_kernel(fp->rows_per_lane, fp->has_pred, fp->has_nulls);
     IGL_CUDA_OK(cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fp->smem_bytes));
     int per_sm = 0;
     IGL_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)k, kPipeThreads, fp->smem_bytes));
@@ -520,6 +586,8 @@ int32_t igl_fp_create(igl_ctx* ctx, const int32_t* in_types, const uint8_t* in_n
     *out = fp.release();
     return IGL_OK;
 }
+
+extern "C" {
 
 int32_t igl_fp_num_outputs(const igl_fp* fp) { return fp ? (int32_t)fp->out_types.size() : 0; }
 
@@ -536,9 +604,8 @@ int32_t igl_fp_launch(igl_fp* fp, const igl_dev_col* in, int64_t nrows, igl_dev_
     DeviceGuard g(ctx->device);
     cudaStream_t st = pick_stream(ctx, stream);
     FpParams P = fp->params;
-    const int TILE = fp->subs * kPipeRowsPerSub;
     P.T.nrows = nrows;
-    P.T.ntiles = (nrows + TILE - 1) / TILE;
+    P.T.ntiles = (nrows + P.T.tile_rows - 1) / P.T.tile_rows;
     for (int c = 0; c < fp->n_in; ++c) {
         int s = fp->slot_of_col[c];
         if (s < 0) continue;
@@ -596,7 +663,7 @@ int32_t igl_fp_launch(igl_fp* fp, const igl_dev_col* in, int64_t nrows, igl_dev_
     fp->launched = true;
     if (nrows == 0) return IGL_OK;
 
-    fp_kernel_t k = pick_kernel(fp->subs, fp->has_pred, fp->has_nulls);
+    fp_kernel_t k = pick_kernel(fp->rows_per_lane, fp->has_pred, fp->has_nulls);
     int grid = (int)std::min<int64_t>(P.T.ntiles, fp->grid_cap);
     k<<<grid, kPipeThreads, fp->smem_bytes, st>>>(P);
     IGL_CUDA_OK(cudaGetLastError());

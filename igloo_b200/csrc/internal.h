@@ -36,26 +36,30 @@ int32_t fail(int32_t code, const char* fmt, ...);
     } while (0)
 
 // ---- expression IR -----------------------------------------------------------
-// Three-address code with operand modes: a leaf (column or literal) is an
+// Accumulator machine with operand modes.  A leaf (column or literal) is an
 // operand of its consumer, never an instruction of its own, so `a < 250` is one
-// instruction and `x * 1.5 + 0.25` is two.
-enum : uint8_t { OPK_NONE = 0, OPK_REG = 1, OPK_COL = 2, OPK_LIT = 3 };
-enum : uint8_t { IOP_MOV = 0x50 };  // besides the igl_opcode values
+// instruction and `x * 1.5 + 0.25` is two.  An inner result lives in the
+// accumulator (registers); when the right subtree is itself an expression the
+// left result is parked in a per-warp shared-memory temporary instead.
+enum : uint8_t { OPK_NONE = 0, OPK_ACC = 1, OPK_COL = 2, OPK_LIT = 3, OPK_TMP = 4 };
+enum : uint8_t { IOP_MOV = 0x50, IOP_ROWID = 0x51 };  // besides the igl_opcode values
 
-constexpr int kMaxRegs = 4;     // value registers of the in-kernel interpreter
+constexpr int kMaxTmp = 4;      // shared-memory temporaries per warp
 constexpr int kMaxInstr = 48;   // per fused operator (predicate + all outputs)
-constexpr int kMaxExprs = 17;   // predicate + 16 outputs
+constexpr int kMaxExprs = 18;   // predicate + 16 outputs + row id
 constexpr int kMaxCols = 16;    // staged input columns per operator
 
-struct Instr {            // 24 bytes
-    uint8_t op;           // igl_opcode or IOP_MOV
+struct Instr {            // 32 bytes
+    uint8_t op;           // igl_opcode, IOP_MOV or IOP_ROWID
     uint8_t type;         // operand type (igl_type) the operation is carried out in
-    uint8_t dst;          // destination register
-    uint8_t a_kind, a_idx, b_kind, b_idx;
-    uint8_t aux;          // CAST: target type.  bit7 of a_idx/b_idx unused.
-    uint64_t a_lit, b_lit;  // literal bits when *_kind == OPK_LIT (null literal: type 0 in aux bits)
+    uint8_t a_kind, b_kind;
+    uint8_t a_idx, b_idx;     // COL: staged slot; TMP: temporary index
+    uint8_t dst_kind, dst_idx;  // OPK_ACC or OPK_TMP k
+    uint8_t aux;          // CAST: target type; else AUX_*_NULL flags of literal operands
+    uint8_t pad[7];
+    uint64_t a_lit, b_lit;  // literal bits when *_kind == OPK_LIT
 };
-static_assert(sizeof(Instr) == 24, "Instr layout");
+static_assert(sizeof(Instr) == 32, "Instr layout");
 
 // literal flags carried in `aux` for non-CAST ops
 enum : uint8_t { AUX_A_NULL = 1, AUX_B_NULL = 2 };

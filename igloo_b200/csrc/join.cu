@@ -208,17 +208,17 @@ struct Match {
     bool hit;
 };
 
-// Looks up this lane's 4 keys; all first-slot loads are issued before any is used.
-template <bool HAS_NULLS>
-__device__ __forceinline__ void lookup4(const JoinProbeParams& P, const uint8_t* stage, int row0, int rows_in_tile,
-                                        uint64_t (&raw)[4], Match (&m)[4]) {
+// Looks up this lane's R keys; all first-slot loads are issued before any is used.
+template <int R, bool HAS_NULLS>
+__device__ __forceinline__ void lookup_rows(const JoinProbeParams& P, const uint8_t* stage, int row0, int rows_in_tile,
+                                            uint64_t (&raw)[R], Match (&m)[R]) {
     const uint8_t* kb = stage + P.T.smem_off[P.key_slot];
     const int ksh = P.T.shift[P.key_slot];
-    uint64_t k[4], h[4];
-    Slot s[4];
-    int kind[4];   // 0 = regular, 1 = side entry, 2 = no lookup
+    uint64_t k[R], h[R];
+    Slot s[R];
+    int kind[R];   // 0 = regular, 1 = side entry, 2 = no lookup
 #pragma unroll
-    for (int r = 0; r < 4; ++r) {
+    for (int r = 0; r < R; ++r) {
         const int row = row0 + r * 32;
         raw[r] = ksh == 2 ? (uint64_t) * reinterpret_cast<const uint32_t*>(kb + (row << 2))
                  : ksh == 3 ? *reinterpret_cast<const uint64_t*>(kb + (row << 3))
@@ -243,7 +243,7 @@ __device__ __forceinline__ void lookup4(const JoinProbeParams& P, const uint8_t*
         }
     }
 #pragma unroll
-    for (int r = 0; r < 4; ++r) {
+    for (int r = 0; r < R; ++r) {
         if (kind[r] != 0) continue;
         while (s[r].key != k[r] && s[r].key != kEmptyKey) {
             h[r] = (h[r] + 1) & P.table.mask;
@@ -284,131 +284,177 @@ __device__ __forceinline__ void emit_row(const JoinProbeParams& P, const uint8_t
     }
 }
 
-// K6/K7, unique layout: at most one output row per probe row.
-template <int SUBS, bool HAS_NULLS>
-__global__ void __launch_bounds__(kPipeThreads, 2) join_probe_unique_kernel(const __grid_constant__ JoinProbeParams P) {
+// K6/K7, unique layout: at most one output row per probe row.  The lookups of
+// tile t+1 are issued before the rows of tile t are written, so the scan of tile
+// t and the table's DRAM latency overlap with useful work.
+template <int R>
+struct UniqueTile {
+    const uint8_t* stage;
+    long long row_begin;
+    int rows;
+    uint32_t keep[R], hitb[R];
+    unsigned long long val[R];
+    int count;
+};
+
+template <int R, bool HAS_NULLS>
+__device__ __forceinline__ void unique_lookup(const JoinProbeParams& P, UniqueTile<R>& t, int warp, int lane) {
+    const int row0 = warp * (32 * R) + lane;
+    Match m[R];
+    uint64_t raw[R];
+    lookup_rows<R, HAS_NULLS>(P, t.stage, row0, warp < P.T.active_warps ? t.rows : 0, raw, m);
+    t.count = 0;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const bool inr = warp < P.T.active_warps && (row0 + r * 32) < t.rows;
+        t.val[r] = m[r].val;
+        t.hitb[r] = __ballot_sync(0xffffffffu, m[r].hit);
+        t.keep[r] = __ballot_sync(0xffffffffu, inr && (m[r].hit || P.left_join));
+        t.count += __popc(t.keep[r]);
+    }
+}
+
+template <int R, bool HAS_NULLS>
+__device__ __forceinline__ void unique_emit(const JoinProbeParams& P, const UniqueTile<R>& t, long long wbase, int warp, int lane) {
+    if (t.count == 0) return;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const int row0 = warp * (32 * R) + lane;
+    const uint8_t* kb = t.stage + P.T.smem_off[P.key_slot];
+    const int ksh = P.T.shift[P.key_slot];
+    long long pos = wbase;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const uint32_t kbits = t.keep[r];
+        if ((kbits >> lane) & 1u) {
+            const int row = row0 + r * 32;
+            const uint64_t raw = ksh == 2 ? (uint64_t) * reinterpret_cast<const uint32_t*>(kb + (row << 2))
+                                          : *reinterpret_cast<const uint64_t*>(kb + (row << 3));
+            emit_row<HAS_NULLS>(P, t.stage, row, pos + __popc(kbits & lt_mask), (t.hitb[r] >> lane) & 1u, t.val[r], raw);
+        }
+        pos += __popc(kbits);
+    }
+}
+
+template <int R, bool HAS_NULLS>
+__global__ void __launch_bounds__(kPipeThreads, kPipeMinCtas) join_probe_unique_kernel(const __grid_constant__ JoinProbeParams P) {
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ PipeShared<SUBS> sh;
-    TilePipe<SUBS, true, HAS_NULLS> pipe(P.T, sh, smem);
+    __shared__ PipeShared sh;
+    TilePipe<true, HAS_NULLS> pipe(P.T, sh, smem);
     pipe.init();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (warp == kPipeComputeWarps) { pipe.control_loop(); return; }
-    const uint32_t lt_mask = (1u << lane) - 1u;
+    UniqueTile<R> cur;
+    if (!pipe.acquire(0, cur.stage, cur.row_begin, cur.rows)) return;
+    unique_lookup<R, HAS_NULLS>(P, cur, warp, lane);
+    pipe.post_count(0, warp, cur.count);
     for (int it = 0;; ++it) {
-        const uint8_t* stage; long long row_begin; int rows_in_tile;
-        if (!pipe.acquire(it, stage, row_begin, rows_in_tile)) break;
-        uint32_t keep[SUBS][4], hitb[SUBS][4];
-        unsigned long long val[SUBS][4];
-        uint64_t raw[SUBS][4];
-        long long wcount[SUBS];
-#pragma unroll
-        for (int sub = 0; sub < SUBS; ++sub) {
-            const int row0 = sub * kPipeRowsPerSub + warp * 128 + lane;
-            Match m[4];
-            lookup4<HAS_NULLS>(P, stage, row0, rows_in_tile, raw[sub], m);
-            wcount[sub] = 0;
-#pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                const bool inr = (row0 + r * 32) < rows_in_tile;
-                val[sub][r] = m[r].val;
-                hitb[sub][r] = __ballot_sync(0xffffffffu, m[r].hit);
-                keep[sub][r] = __ballot_sync(0xffffffffu, inr && (m[r].hit || P.left_join));
-                wcount[sub] += __popc(keep[sub][r]);
-            }
+        UniqueTile<R> nxt;
+        const bool has_next = pipe.acquire(it + 1, nxt.stage, nxt.row_begin, nxt.rows);
+        if (has_next) {
+            unique_lookup<R, HAS_NULLS>(P, nxt, warp, lane);
+            pipe.post_count(it + 1, warp, nxt.count);
         }
-        long long wbase[SUBS];
-        pipe.offsets(it, warp, wcount, wbase);
-#pragma unroll
-        for (int sub = 0; sub < SUBS; ++sub) {
-            const int row0 = sub * kPipeRowsPerSub + warp * 128 + lane;
-            long long pos = wbase[sub];
-#pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                const uint32_t kb = keep[sub][r];
-                if ((kb >> lane) & 1u)
-                    emit_row<HAS_NULLS>(P, stage, row0 + r * 32, pos + __popc(kb & lt_mask), (hitb[sub][r] >> lane) & 1u,
-                                        val[sub][r], raw[sub][r]);
-                pos += __popc(kb);
-            }
-        }
+        const long long wbase = pipe.wait_base(it, warp);
+        unique_emit<R, HAS_NULLS>(P, cur, wbase, warp, lane);
         pipe.release(it);
+        if (!has_next) break;
+        cur = nxt;
     }
 }
 
 // K6/K7, duplicate layout: a probe row emits `count` rows; runs longer than a
 // warp are walked by the whole warp.
-template <int SUBS, bool HAS_NULLS>
-__global__ void __launch_bounds__(kPipeThreads, 2) join_probe_multi_kernel(const __grid_constant__ JoinProbeParams P) {
+template <int R>
+struct MultiTile {
+    const uint8_t* stage;
+    long long row_begin;
+    int rows;
+    uint32_t cnt[R], excl[R], rend[R], hitb[R];
+    long long count;
+};
+
+template <int R, bool HAS_NULLS>
+__device__ __forceinline__ void multi_lookup(const JoinProbeParams& P, MultiTile<R>& t, int warp, int lane) {
+    const int row0 = warp * (32 * R) + lane;
+    Match m[R];
+    uint64_t raw[R];
+    lookup_rows<R, HAS_NULLS>(P, t.stage, row0, warp < P.T.active_warps ? t.rows : 0, raw, m);
+    uint32_t running = 0;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const bool inr = warp < P.T.active_warps && (row0 + r * 32) < t.rows;
+        uint32_t c = m[r].hit ? (uint32_t)(m[r].val >> 32) : ((inr && P.left_join) ? 1u : 0u);
+        if (!inr) c = 0;
+        t.hitb[r] = __ballot_sync(0xffffffffu, m[r].hit);
+        t.rend[r] = (uint32_t)m[r].val;
+        uint32_t inc = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t nb = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += nb;
+        }
+        t.cnt[r] = c;
+        t.excl[r] = running + inc - c;
+        running += __shfl_sync(0xffffffffu, inc, 31);
+    }
+    t.count = (long long)running;
+}
+
+template <int R, bool HAS_NULLS>
+__device__ __forceinline__ void multi_emit(const JoinProbeParams& P, const MultiTile<R>& t, long long wbase, int warp, int lane) {
+    if (t.count == 0) return;
+    const int row0 = warp * (32 * R) + lane;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int row = row0 + r * 32;
+        const uint32_t c = t.cnt[r];
+        const bool hit = (t.hitb[r] >> lane) & 1u;
+        const long long pos = wbase + t.excl[r];
+        const bool heavy = c > 32;
+        if (c && !heavy) {
+            if (!hit) emit_row<HAS_NULLS>(P, t.stage, row, pos, false, 0, 0);
+            else
+                for (uint32_t j = 0; j < c; ++j)
+                    emit_row<HAS_NULLS>(P, t.stage, row, pos + j, true, P.table.rowids[t.rend[r] - c + j], 0);
+        }
+        uint32_t hv = __ballot_sync(0xffffffffu, heavy);
+        while (hv) {   // warp-cooperative walk of one long run
+            const int src = __ffs(hv) - 1;
+            hv &= hv - 1;
+            const uint32_t hc = __shfl_sync(0xffffffffu, c, src);
+            const uint32_t he = __shfl_sync(0xffffffffu, t.rend[r], src);
+            const long long hp = __shfl_sync(0xffffffffu, pos, src);
+            const int hrow = row - lane + src;
+            for (uint32_t j = lane; j < hc; j += 32)
+                emit_row<HAS_NULLS>(P, t.stage, hrow, hp + j, true, P.table.rowids[he - hc + j], 0);
+        }
+    }
+}
+
+template <int R, bool HAS_NULLS>
+__global__ void __launch_bounds__(kPipeThreads, kPipeMinCtas) join_probe_multi_kernel(const __grid_constant__ JoinProbeParams P) {
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ PipeShared<SUBS> sh;
-    TilePipe<SUBS, true, HAS_NULLS> pipe(P.T, sh, smem);
+    __shared__ PipeShared sh;
+    TilePipe<true, HAS_NULLS> pipe(P.T, sh, smem);
     pipe.init();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (warp == kPipeComputeWarps) { pipe.control_loop(); return; }
+    MultiTile<R> cur;
+    if (!pipe.acquire(0, cur.stage, cur.row_begin, cur.rows)) return;
+    multi_lookup<R, HAS_NULLS>(P, cur, warp, lane);
+    pipe.post_count(0, warp, cur.count);
     for (int it = 0;; ++it) {
-        const uint8_t* stage; long long row_begin; int rows_in_tile;
-        if (!pipe.acquire(it, stage, row_begin, rows_in_tile)) break;
-        uint32_t cnt[SUBS][4], excl[SUBS][4], rend[SUBS][4];
-        uint32_t hitb[SUBS][4];
-        long long wcount[SUBS];
-#pragma unroll
-        for (int sub = 0; sub < SUBS; ++sub) {
-            const int row0 = sub * kPipeRowsPerSub + warp * 128 + lane;
-            Match m[4];
-            uint64_t raw[4];
-            lookup4<HAS_NULLS>(P, stage, row0, rows_in_tile, raw, m);
-            uint32_t running = 0;
-#pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                const bool inr = (row0 + r * 32) < rows_in_tile;
-                uint32_t c = m[r].hit ? (uint32_t)(m[r].val >> 32) : ((inr && P.left_join) ? 1u : 0u);
-                if (!inr) c = 0;
-                hitb[sub][r] = __ballot_sync(0xffffffffu, m[r].hit);
-                rend[sub][r] = (uint32_t)m[r].val;
-                uint32_t inc = c;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const uint32_t nb = __shfl_up_sync(0xffffffffu, inc, o);
-                    if (lane >= o) inc += nb;
-                }
-                cnt[sub][r] = c;
-                excl[sub][r] = running + inc - c;
-                running += __shfl_sync(0xffffffffu, inc, 31);
-            }
-            wcount[sub] = (long long)running;
+        MultiTile<R> nxt;
+        const bool has_next = pipe.acquire(it + 1, nxt.stage, nxt.row_begin, nxt.rows);
+        if (has_next) {
+            multi_lookup<R, HAS_NULLS>(P, nxt, warp, lane);
+            pipe.post_count(it + 1, warp, nxt.count);
         }
-        long long wbase[SUBS];
-        pipe.offsets(it, warp, wcount, wbase);
-#pragma unroll
-        for (int sub = 0; sub < SUBS; ++sub) {
-            const int row0 = sub * kPipeRowsPerSub + warp * 128 + lane;
-#pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                const int row = row0 + r * 32;
-                const uint32_t c = cnt[sub][r];
-                const bool hit = (hitb[sub][r] >> lane) & 1u;
-                const long long pos = wbase[sub] + excl[sub][r];
-                const bool heavy = c > 32;
-                if (c && !heavy) {
-                    if (!hit) emit_row<HAS_NULLS>(P, stage, row, pos, false, 0, 0);
-                    else
-                        for (uint32_t j = 0; j < c; ++j)
-                            emit_row<HAS_NULLS>(P, stage, row, pos + j, true, P.table.rowids[rend[sub][r] - c + j], 0);
-                }
-                uint32_t hv = __ballot_sync(0xffffffffu, heavy);
-                while (hv) {   // warp-cooperative walk of one long run
-                    const int src = __ffs(hv) - 1;
-                    hv &= hv - 1;
-                    const uint32_t hc = __shfl_sync(0xffffffffu, c, src);
-                    const uint32_t he = __shfl_sync(0xffffffffu, rend[sub][r], src);
-                    const long long hp = __shfl_sync(0xffffffffu, pos, src);
-                    const int hrow = row - lane + src;
-                    for (uint32_t j = lane; j < hc; j += 32)
-                        emit_row<HAS_NULLS>(P, stage, hrow, hp + j, true, P.table.rowids[he - hc + j], 0);
-                }
-            }
-        }
+        const long long wbase = pipe.wait_base(it, warp);
+        multi_emit<R, HAS_NULLS>(P, cur, wbase, warp, lane);
         pipe.release(it);
+        if (!has_next) break;
+        cur = nxt;
     }
 }
 
@@ -482,12 +528,12 @@ struct igl_join {
 namespace {
 
 typedef void (*probe_kernel_t)(const JoinProbeParams);
-probe_kernel_t pick_probe(bool csr, int subs, bool nulls) {
-    if (csr) {
-        if (subs == 2) return nulls ? join_probe_multi_kernel<2, true> : join_probe_multi_kernel<2, false>;
-        return nulls ? join_probe_multi_kernel<1, true> : join_probe_multi_kernel<1, false>;
+probe_kernel_t pick_probe(bool csr, int rows_per_lane, bool nulls) {
+    if (rows_per_lane == 4) {
+        if (csr) return nulls ? join_probe_multi_kernel<4, true> : join_probe_multi_kernel<4, false>;
+        return nulls ? join_probe_unique_kernel<4, true> : join_probe_unique_kernel<4, false>;
     }
-    if (subs == 2) return nulls ? join_probe_unique_kernel<2, true> : join_probe_unique_kernel<2, false>;
+    if (csr) return nulls ? join_probe_multi_kernel<1, true> : join_probe_multi_kernel<1, false>;
     return nulls ? join_probe_unique_kernel<1, true> : join_probe_unique_kernel<1, false>;
 }
 
@@ -534,7 +580,7 @@ int32_t igl_join_create(igl_ctx* ctx, int32_t join_type, const int32_t* left_typ
     j->smem_bytes = (size_t)j->geo.stage_bytes * j->geo.stages;
     DeviceGuard g(ctx->device);
     for (int csr = 0; csr < 2; ++csr) {
-        probe_kernel_t k = pick_probe(csr, j->geo.subs, j->has_nulls);
+        probe_kernel_t k = pick_probe(csr, j->geo.rows_per_lane, j->has_nulls);
         IGL_CUDA_OK(cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)j->smem_bytes));
         int per_sm = 0;
         IGL_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)k, kPipeThreads, j->smem_bytes));
@@ -653,9 +699,8 @@ int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_
     }
     JoinProbeParams P{};
     P.T = j->T;
-    const int TILE = j->geo.subs * kPipeRowsPerSub;
     P.T.nrows = nrows;
-    P.T.ntiles = (nrows + TILE - 1) / TILE;
+    P.T.ntiles = (nrows + P.T.tile_rows - 1) / P.T.tile_rows;
     for (int c = 0; c < nl; ++c) {
         if (left[c].type != j->lt[c]) return fail(IGL_ERR_INVALID_ARG, "left column %d has type %d, join expects %d", c, left[c].type, j->lt[c]);
         if (((uintptr_t)left[c].data & 15) || ((uintptr_t)left[c].validity & 15)) return fail(IGL_ERR_INVALID_ARG, "left column %d is not 16-byte aligned", c);
@@ -705,7 +750,7 @@ int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_
             P.right_valid[c - nl] = j->right[c - nl].validity;
         }
     }
-    probe_kernel_t k = pick_probe(j->csr, j->geo.subs, j->has_nulls);
+    probe_kernel_t k = pick_probe(j->csr, j->geo.rows_per_lane, j->has_nulls);
     const int grid = (int)std::min<int64_t>(P.T.ntiles, j->csr ? j->grid_cap_m : j->grid_cap_u);
     k<<<grid, kPipeThreads, j->smem_bytes, st>>>(P);
     IGL_CUDA_OK(cudaGetLastError());

@@ -1,5 +1,5 @@
 // tile_pipe.cuh — the CTA skeleton shared by every row-streaming kernel
-// (filter/project, join probe, join probe-count):
+// (filter/project, join probe):
 //
 //   control warp  : takes tile tickets in order, streams each tile's column
 //                   slices into a shared-memory ring with 1-D bulk async copies
@@ -12,6 +12,13 @@
 //                   group), hand their counts to the control warp, receive their
 //                   output base, write, release the stage.
 //
+// Scanning kernels are software-pipelined: a compute warp runs the counting
+// phase of tile t+1 BEFORE the writing phase of tile t, so the look-back of
+// tile t (a chain of L2 round trips behind every tile in flight on the GPU)
+// overlaps useful work instead of stalling the CTA at a barrier.  The named
+// barriers alternate by tile parity so a warp that is one tile ahead cannot
+// alias the previous tile's handshake.
+//
 // Tiles are claimed with an atomic ticket, so a tile's predecessors are always
 // owned by CTAs that are already running: the look-back cannot deadlock however
 // many CTAs are resident.
@@ -21,11 +28,20 @@
 
 namespace igl {
 
-constexpr int kPipeComputeWarps = 7;   // + 1 control warp = 256 threads: 2 CTAs/SM at <= 128 registers
+#ifndef IGL_PIPE_COMPUTE_WARPS
+#define IGL_PIPE_COMPUTE_WARPS 15
+#endif
+#ifndef IGL_PIPE_MIN_CTAS
+#define IGL_PIPE_MIN_CTAS 2
+#endif
+constexpr int kPipeComputeWarps = IGL_PIPE_COMPUTE_WARPS;   // + 1 control warp
 constexpr int kPipeThreads = (kPipeComputeWarps + 1) * 32;
-constexpr int kPipeRowsPerSub = kPipeComputeWarps * 128;   // 896: a multiple of 128 keeps bitmap slices 16-B aligned
+// rows per tile = compute warps * 32 lanes * R rows per lane (R = 4, or 1 for very wide
+// tables); always a multiple of 128 rows so bitmap slices stay 16-byte aligned
+constexpr int kPipeMinCtas = IGL_PIPE_MIN_CTAS;
 constexpr int kPipeMaxStages = 4;
 constexpr int kPipeMaxCols = 16;
+static_assert(kPipeComputeWarps <= 32, "per-tile warp counts are scanned by one warp");
 
 struct PipeHeader {   // first 256 bytes of a kernel's scratch block; zeroed before every launch
     unsigned int ticket;
@@ -42,32 +58,31 @@ struct PipeCols {
     uint8_t shift[kPipeMaxCols];   // log2(bytes per row); 0xFF = bit-packed boolean
     uint8_t n_cols, n_stages, pad[2];
     uint32_t stage_bytes;
+    int tile_rows;                 // active warps * 32 * rows-per-lane, a multiple of 128
+    int active_warps;              // compute warps that own rows (all of them at 4 rows per lane)
     long long nrows, ntiles;
     PipeHeader* hdr;
     uint64_t* status;              // one word per tile (only when SCAN)
 };
 
-template <int SUBS>
 struct PipeShared {
     uint64_t full_bar[kPipeMaxStages], empty_bar[kPipeMaxStages];
     long long tile_of_stage[kPipeMaxStages];
-    long long counts[2][SUBS * kPipeComputeWarps];
-    long long local[2][SUBS * kPipeComputeWarps];
+    long long counts[2][kPipeComputeWarps];
+    long long local[2][kPipeComputeWarps];
     unsigned long long base[2];
 };
 
-template <int SUBS, bool SCAN, bool HAS_NULLS>
-struct TilePipe {
-    static constexpr int TILE = SUBS * kPipeRowsPerSub;
-    static constexpr int NC = SUBS * kPipeComputeWarps;
-    static_assert(NC <= 32, "per-tile warp counts are scanned by one warp");
+enum { kBarCounts = 1, kBarBase = 3 };   // named barrier ids (+ tile parity)
 
+template <bool SCAN, bool HAS_NULLS>
+struct TilePipe {
     const PipeCols& T;
-    PipeShared<SUBS>& sh;
+    PipeShared& sh;
     uint8_t* smem;
     int lane;
 
-    __device__ TilePipe(const PipeCols& t, PipeShared<SUBS>& s, uint8_t* dyn_smem)
+    __device__ TilePipe(const PipeCols& t, PipeShared& s, uint8_t* dyn_smem)
         : T(t), sh(s), smem(dyn_smem), lane(threadIdx.x & 31) {}
 
     __device__ void init() {   // whole CTA
@@ -79,16 +94,23 @@ struct TilePipe {
     }
 
     // ---- control warp ---------------------------------------------------------
-    __device__ void issue(int s) {   // one lane
-        const long long t = (long long)atomicAdd(&T.hdr->ticket, 1u);
+    // Tile claims.  The first n_stages tiles of a CTA are taken round-robin
+    // (stage s of CTA c = tile s * gridDim + c) and later ones from an atomic
+    // ticket as stages free up: consecutive tiles then always sit on different
+    // CTAs that reach them at about the same time.  (Claiming a CTA's first
+    // stages as consecutive tickets would make its neighbour's first tile wait
+    // for this CTA's LAST prefetched tile — a scan chain as long as the grid.)
+    __device__ void issue(int s, bool prologue) {   // one lane
+        const long long t = prologue ? (long long)s * gridDim.x + blockIdx.x
+                                     : (long long)T.n_stages * gridDim.x + (long long)atomicAdd(&T.hdr->ticket, 1u);
         if (t >= T.ntiles) {
             sh.tile_of_stage[s] = -1;
             mbar_arrive(&sh.full_bar[s]);
             return;
         }
         sh.tile_of_stage[s] = t;
-        const long long row_begin = t * TILE;
-        const long long rows = min((long long)TILE, T.nrows - row_begin);
+        const long long row_begin = t * T.tile_rows;
+        const long long rows = min((long long)T.tile_rows, T.nrows - row_begin);
         uint8_t* stage = smem + (size_t)s * T.stage_bytes;
         const uint32_t bit_bytes = ((uint32_t)((rows + 7) >> 3) + 15u) & ~15u;
         auto col_bytes = [&](int c) {
@@ -107,40 +129,53 @@ struct TilePipe {
         }
     }
 
+    // Scans this tile's per-warp counts (in sh.counts[it & 1]) and publishes the
+    // tile's own count; returns {inclusive per-warp scan, tile total}.
+    __device__ void take_counts(int it, long long tile, long long& c, long long& inc, long long& total) {
+        bar_sync(kBarCounts + (it & 1), kPipeThreads);
+        c = lane < kPipeComputeWarps ? sh.counts[it & 1][lane] : 0;
+        inc = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const long long n = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += n;
+        }
+        total = __shfl_sync(0xffffffffu, inc, 31);
+        if (lane == 0) lookback_publish(T.status, tile, (uint64_t)total);
+    }
+
     __device__ void control_loop() {   // the whole control warp
         const int S = T.n_stages;
         if (lane == 0)
-            for (int s = 0; s < S; ++s) issue(s);
+            for (int s = 0; s < S; ++s) issue(s, true);
         __syncwarp();
-        for (int it = 0;; ++it) {
+        long long c = 0, inc = 0, total = 0;
+        long long tile = *reinterpret_cast<volatile long long*>(&sh.tile_of_stage[0]);
+        if (SCAN && tile >= 0) take_counts(0, tile, c, inc, total);
+        for (int it = 0; tile >= 0; ++it) {
             const int s = it % S;
             const uint32_t ph = (uint32_t)(it / S) & 1u;
-            const long long tile = *reinterpret_cast<volatile long long*>(&sh.tile_of_stage[s]);
-            if (tile < 0) break;
             if (SCAN) {
-                bar_sync(1, kPipeThreads);   // this tile's per-warp counts are in sh.counts[it & 1]
-                const long long c = lane < NC ? sh.counts[it & 1][lane] : 0;
-                long long inc = c;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const long long n = __shfl_up_sync(0xffffffffu, inc, o);
-                    if (lane >= o) inc += n;
-                }
-                const long long total = __shfl_sync(0xffffffffu, inc, 31);
                 const uint64_t base = lookback_exclusive(T.status, tile, (uint64_t)total, lane);
-                if (lane < NC) sh.local[it & 1][lane] = inc - c;
+                if (lane < kPipeComputeWarps) sh.local[it & 1][lane] = inc - c;
                 if (lane == 0) {
                     sh.base[it & 1] = base;
                     if (tile == T.ntiles - 1) T.hdr->out_count = (long long)(base + (uint64_t)total);
                 }
                 __syncwarp();
-                bar_arrive(2, kPipeThreads);
+                bar_arrive(kBarBase + (it & 1), kPipeThreads);
             }
+            // The compute warps post the counts of tile it+1 before they write tile
+            // it: publish that count now, a whole write phase before its turn, so
+            // the neighbours' look-backs rarely find it missing.
+            const long long next_tile = *reinterpret_cast<volatile long long*>(&sh.tile_of_stage[(it + 1) % S]);
+            if (SCAN && next_tile >= 0) take_counts(it + 1, next_tile, c, inc, total);
             if (lane == 0) {
                 mbar_wait(&sh.empty_bar[s], ph);   // every compute warp has finished reading stage s
-                issue(s);
+                issue(s, false);
             }
             __syncwarp();
+            tile = next_tile;
         }
     }
 
@@ -152,23 +187,22 @@ struct TilePipe {
         const long long tile = sh.tile_of_stage[s];
         if (tile < 0) return false;
         stage = smem + (size_t)s * T.stage_bytes;
-        row_begin = tile * TILE;
-        rows_in_tile = (int)min((long long)TILE, T.nrows - row_begin);
+        row_begin = tile * T.tile_rows;
+        rows_in_tile = (int)min((long long)T.tile_rows, T.nrows - row_begin);
         return true;
     }
 
-    // Per-warp output counts in, per-warp global output base out (ordered).
-    __device__ void offsets(int it, int warp, const long long (&wcount)[SUBS], long long (&wbase)[SUBS]) {
-        if (lane == 0) {
-#pragma unroll
-            for (int sub = 0; sub < SUBS; ++sub) sh.counts[it & 1][sub * kPipeComputeWarps + warp] = wcount[sub];
-        }
+    // This warp's output count for tile `it` (does not block).
+    __device__ void post_count(int it, int warp, long long wcount) {
+        if (lane == 0) sh.counts[it & 1][warp] = wcount;
         __syncwarp();
-        bar_arrive(1, kPipeThreads);
-        bar_sync(2, kPipeThreads);
-        const unsigned long long base = sh.base[it & 1];
-#pragma unroll
-        for (int sub = 0; sub < SUBS; ++sub) wbase[sub] = (long long)base + sh.local[it & 1][sub * kPipeComputeWarps + warp];
+        bar_arrive(kBarCounts + (it & 1), kPipeThreads);
+    }
+
+    // This warp's global output base for tile `it` (ordered).
+    __device__ long long wait_base(int it, int warp) {
+        bar_sync(kBarBase + (it & 1), kPipeThreads);
+        return (long long)sh.base[it & 1] + sh.local[it & 1][warp];
     }
 
     __device__ void release(int it) {
@@ -179,40 +213,42 @@ struct TilePipe {
 
 // ---- host-side ring geometry ------------------------------------------------------
 struct PipeGeometry {
-    int subs = 2, stages = 2;
+    int stages = 2;
+    int rows_per_lane = 4;
     uint32_t stage_bytes = 128;
     bool ok = true;
 };
 
 // shift[c] per staged column; every column reserves a validity slice too.
-inline PipeGeometry pipe_geometry(const uint8_t* shift, int ncols, PipeCols& T, uint32_t budget = 100u << 10) {
-    auto stage_bytes_for = [&](int subs) {
+// `extra` = other dynamic shared memory the kernel needs per CTA.  Picks 4 rows
+// per lane when two stages fit (two CTAs per SM if possible), else 1 row per lane.
+inline PipeGeometry pipe_geometry(const uint8_t* shift, int ncols, PipeCols& T, uint32_t extra = 0) {
+    PipeGeometry g;
+    const uint32_t budget2 = (226u << 10) / kPipeMinCtas - 2048u;   // per CTA when kPipeMinCtas share an SM
+    const uint32_t budget1 = 220u << 10;                             // one CTA per SM
+    for (int R : {4, 1}) {
+        // 1 row per lane: only a multiple of 4 warps own rows, so the tile stays a multiple of 128 rows
+        const int active = R == 4 ? kPipeComputeWarps : (kPipeComputeWarps / 4) * 4;
+        const uint32_t rows = (uint32_t)active * 32u * R;
+        T.active_warps = active;
         uint32_t off = 0;
         for (int c = 0; c < ncols; ++c) {
-            const uint32_t rows = subs * kPipeRowsPerSub;
             const uint32_t b = shift[c] == 0xFF ? rows / 8 : rows << shift[c];
-            off += (b + 127u) & ~127u;
-            off += ((rows / 8) + 127u) & ~127u;
+            T.shift[c] = shift[c];
+            T.smem_off[c] = off; off += (b + 127u) & ~127u;
+            T.valid_off[c] = off; off += ((rows / 8) + 127u) & ~127u;
         }
-        return off ? off : 128u;
-    };
-    PipeGeometry g;
-    g.stage_bytes = stage_bytes_for(2);
-    if (g.stage_bytes * 3 <= budget) g.stages = (int)(budget / g.stage_bytes < (uint32_t)kPipeMaxStages ? budget / g.stage_bytes : kPipeMaxStages);
-    else {
-        g.subs = 1;
-        g.stage_bytes = stage_bytes_for(1);
-        if (g.stage_bytes * 2 <= budget) g.stages = (int)(budget / g.stage_bytes < (uint32_t)kPipeMaxStages ? budget / g.stage_bytes : kPipeMaxStages);
-        else if (g.stage_bytes * 2 <= (200u << 10)) g.stages = 2;
-        else g.ok = false;
-    }
-    uint32_t off = 0;
-    for (int c = 0; c < ncols; ++c) {
-        const uint32_t rows = g.subs * kPipeRowsPerSub;
-        const uint32_t b = shift[c] == 0xFF ? rows / 8 : rows << shift[c];
-        T.shift[c] = shift[c];
-        T.smem_off[c] = off; off += (b + 127u) & ~127u;
-        T.valid_off[c] = off; off += ((rows / 8) + 127u) & ~127u;
+        g.stage_bytes = off ? off : 128u;
+        g.rows_per_lane = R;
+        T.tile_rows = (int)rows;
+        if (g.stage_bytes * 2 + extra <= budget2) {
+            const uint32_t st = (budget2 - extra) / g.stage_bytes;
+            g.stages = (int)(st < (uint32_t)kPipeMaxStages ? st : kPipeMaxStages);
+            g.ok = true;
+            break;
+        }
+        if (g.stage_bytes * 2 + extra <= budget1) { g.stages = 2; g.ok = true; break; }
+        g.ok = false;
     }
     T.n_cols = (uint8_t)ncols;
     T.n_stages = (uint8_t)g.stages;

@@ -53,7 +53,10 @@ class Context:
 
     def stream(self) -> int:
         torch = _torch()
-        return torch.cuda.current_stream(self.device).cuda_stream
+        # torch's default stream is the legacy default stream (handle 0); the C ABI
+        # reads a NULL stream as "the context's own stream", so name it explicitly
+        # (cudaStreamLegacy == 0x1) to keep kernels on the stream torch events see.
+        return torch.cuda.current_stream(self.device).cuda_stream or 1
 
     def compile(self, e: Expr, schema: Sequence[Field]) -> "CompiledExpr":
         return CompiledExpr(self, e, schema)
