@@ -4,6 +4,7 @@
 // pool" and "pinned-memory batch upload path" BASELINE.json's north_star names.
 #include "internal.h"
 
+#include <cstdlib>
 #include <cstring>
 
 namespace igl {
@@ -121,6 +122,13 @@ int32_t igl_ctx_create(const igl_config* cfg, igl_ctx** out) {
     if (prop.major < 10)
         return fail(IGL_ERR_UNSUPPORTED, "device %d is sm_%d%d; this library is built for sm_100a only", dev,
                     prop.major, prop.minor);
+    // Experiment knob only: cudaLimitMaxL2FetchGranularity.  Measured on B200: no
+    // effect on the ~128 B of HBM traffic each random 16-byte table read costs
+    // (profiles/README.md), so nothing is set unless the variable is present.
+    if (const char* env = getenv("IGL_L2_FETCH_GRANULARITY")) {
+        (void)cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(env));
+        (void)cudaGetLastError();
+    }
     igl_ctx* c = new igl_ctx();
     c->device = dev;
     c->sm_count = prop.multiProcessorCount;
