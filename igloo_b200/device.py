@@ -188,9 +188,10 @@ class FilterProject:
             self.out_fields.append(Field(name, t.value, bool(nl.value)))
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        # a handle must not outlive its context (igl_fp_destroy returns blocks to the pool)
+        if getattr(self, "_h", None) and getattr(self.ctx, "_h", None):
             lib.igl_fp_destroy(self._h)
-            self._h = None
+        self._h = None
 
     def alloc_outputs(self, nrows: int) -> List[DeviceColumn]:
         return [DeviceColumn.empty(f.type, nrows, self.ctx.device, nullable=f.nullable) for f in self.out_fields]
@@ -253,9 +254,9 @@ class HashJoin:
         self.left_join = join_type in (JOIN_LEFT, JOIN_FULL)
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and getattr(self.ctx, "_h", None):
             lib.igl_join_destroy(self._h)
-            self._h = None
+        self._h = None
 
     def build(self, cols: Sequence[DeviceColumn], nrows: int):
         self._right_cols = list(cols)  # borrowed by the library until destroy
