@@ -720,3 +720,109 @@ void igl_fp_destroy(igl_fp* fp) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------
+// igl_fp_run_static: the same fused Filter/Projection launch as igl_fp_run, for
+// callers that are not allowed to allocate device memory while they run.
+//
+// Who that is: an engine that carves its whole HBM budget up front and treats
+// any later cudaMalloc as a bug (a worker sharing its GPU with other tenants, a
+// latency-sensitive stream where an allocation's implicit device synchronisation
+// would stall unrelated work), or code running at a point where the CUDA
+// allocator must not be entered at all.  igl_fp_run grows a per-plan scratch
+// block from the context's pool on demand; this entry point never touches the
+// pool, cudaMalloc or cudaFree.  The caller still provides inputs and outputs.
+//
+// The scan scratch (256-byte header + one status word per tile) lives in the
+// file-scope device array below instead: kFpStaticScratchBytes (88 KiB) of
+// device memory held by every GPU that loads the library, until the process
+// exits.  That bounds a call to kFpStaticMaxRows rows.
+//
+// Rules that follow from sharing one array:
+//   * every call clears the header and the status words it is about to use, so
+//     a call never sees what the previous one left behind;
+//   * two calls whose kernels overlap on the same GPU (different streams or
+//     threads) race on the array — serialise them, or use igl_fp_run;
+//   * the first call on each device looks the array's device address up
+//     (cudaGetSymbolAddress, with that device current) and caches it; make that
+//     first call before starting any stream capture.
+// Plans with boolean or nullable outputs need per-row byte planes that only the
+// pool can provide and are rejected here.
+// ---------------------------------------------------------------------------
+namespace igl {
+constexpr long long kFpStaticMaxRows = 4ll << 20;   // == the default coalesce_rows chunk
+constexpr size_t kFpStaticScratchBytes = 88u << 10;  // 256 + 8 * ceil(kFpStaticMaxRows / 384 rows per narrowest tile)
+static_assert(256 + 8 * ((kFpStaticMaxRows + 383) / 384) <= (long long)kFpStaticScratchBytes, "static scratch too small");
+static __device__ __align__(256) unsigned char g_fp_static_scratch[kFpStaticScratchBytes];
+
+// In host code `g_fp_static_scratch` is only a handle for the runtime, never a
+// device pointer: the address a kernel may use comes from cudaGetSymbolAddress.
+static std::mutex g_fp_static_mu;
+static void* g_fp_static_ptr[64] = {};
+
+static int32_t fp_static_scratch_ptr(int device, void** out) {
+    if (device < 0 || device >= 64) return fail(IGL_ERR_UNSUPPORTED, "igl_fp_run_static: device ordinal %d not supported", device);
+    std::lock_guard<std::mutex> g(g_fp_static_mu);
+    if (!g_fp_static_ptr[device]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_fp_static_scratch);   // the caller made `device` current
+        if (e != cudaSuccess || !p)
+            return fail(IGL_ERR_CUDA, "igl_fp_run_static: cudaGetSymbolAddress failed on device %d: %s", device, cudaGetErrorString(e));
+        g_fp_static_ptr[device] = p;
+    }
+    *out = g_fp_static_ptr[device];
+    return IGL_OK;
+}
+}  // namespace igl
+
+extern "C" int32_t igl_fp_run_static(igl_fp* fp, const igl_dev_col* in, int64_t nrows, igl_dev_col* out,
+                                     int64_t* out_rows, void* stream) {
+    if (!fp || !in || !out || nrows < 0) return fail(IGL_ERR_INVALID_ARG, "igl_fp_run_static: bad arguments");
+    if (nrows > kFpStaticMaxRows)
+        return fail(IGL_ERR_INVALID_ARG, "igl_fp_run_static: %lld rows exceed the static scratch limit of %lld rows per call; "
+                    "split the batch or use igl_fp_run", (long long)nrows, kFpStaticMaxRows);
+    const size_t nout = fp->out_types.size();
+    for (size_t j = 0; j < nout; ++j)
+        if (fp->out_types[j] == IGL_T_BOOL || (fp->has_nulls && fp->out_nullable[j]))
+            return fail(IGL_ERR_UNSUPPORTED, "igl_fp_run_static: output %zu is boolean or nullable and needs pooled byte planes; use igl_fp_run", j);
+    igl_ctx* ctx = fp->ctx;
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = pick_stream(ctx, stream);
+    void* scratch = nullptr;
+    IGL_TRY(fp_static_scratch_ptr(ctx->device, &scratch));
+    FpParams P = fp->params;
+    P.T.nrows = nrows;
+    P.T.ntiles = (nrows + P.T.tile_rows - 1) / P.T.tile_rows;
+    for (int c = 0; c < fp->n_in; ++c) {
+        const int s = fp->slot_of_col[c];
+        if (s < 0) continue;
+        if (in[c].type != fp->in_types[c]) return fail(IGL_ERR_INVALID_ARG, "input column %d has type %d, plan expects %d", c, in[c].type, fp->in_types[c]);
+        if (((uintptr_t)in[c].data & 15) || ((uintptr_t)in[c].validity & 15)) return fail(IGL_ERR_INVALID_ARG, "input column %d is not 16-byte aligned", c);
+        P.T.data[s] = (const uint8_t*)in[c].data;
+        P.T.valid[s] = fp->has_nulls ? in[c].validity : nullptr;
+    }
+    for (size_t j = 0; j < nout; ++j) {
+        if (!out[j].data) return fail(IGL_ERR_INVALID_ARG, "output column %zu has no data buffer", j);
+        P.out_data[j] = out[j].data;
+        P.out_valid[j] = nullptr;
+    }
+    if (nrows == 0) { if (out_rows) *out_rows = 0; return IGL_OK; }
+    const size_t need = 256 + (size_t)P.T.ntiles * 8;   // <= kFpStaticScratchBytes by the row limit
+    P.T.hdr = (PipeHeader*)scratch;
+    P.T.status = (uint64_t*)((uint8_t*)scratch + 256);
+    IGL_CUDA_OK(cudaMemsetAsync(scratch, 0, need, st));   // ticket, error flags, count and every status word start at zero
+    fp_kernel_t k = pick_kernel(fp->rows_per_lane, fp->has_pred, fp->has_nulls);
+    const int grid = (int)std::min<int64_t>(P.T.ntiles, fp->grid_cap);
+    k<<<grid, kPipeThreads, fp->smem_bytes, st>>>(P);
+    IGL_CUDA_OK(cudaGetLastError());
+    ctx->launches++;
+    IGL_CUDA_OK(cudaMemcpyAsync(fp->host_hdr, scratch, sizeof(PipeHeader), cudaMemcpyDeviceToHost, st));
+    IGL_CUDA_OK(cudaStreamSynchronize(st));
+    const unsigned int ef = fp->host_hdr->err_flags;
+    if (ef & ERRF_DIV_ZERO) return fail(IGL_ERR_DIV_BY_ZERO, "Divide by zero error");
+    if (ef & ERRF_OVERFLOW) return fail(IGL_ERR_ARITH_OVERFLOW, "Arithmetic overflow: Overflow happened on division");
+    if (ef & ERRF_CAST) return fail(IGL_ERR_CAST, "Cast error: Can't cast value to the target integer type");
+    if (out_rows) *out_rows = fp->has_pred ? (int64_t)fp->host_hdr->out_count : nrows;
+    return IGL_OK;
+}
+

@@ -159,6 +159,18 @@ int32_t igl_fp_run(igl_fp* fp, const igl_dev_col* in, int64_t nrows, igl_dev_col
 int32_t igl_fp_launch(igl_fp* fp, const igl_dev_col* in, int64_t nrows, igl_dev_col* out, void* stream);
 int32_t igl_fp_finish(igl_fp* fp, int64_t* out_rows, void* stream);
 void igl_fp_destroy(igl_fp* fp);
+/* No counterpart in the reference.  igl_fp_run for callers that must not
+ * allocate device memory while running (engines that reserve all of their HBM up
+ * front, latency-critical streams that cannot absorb an allocation's implicit
+ * synchronisation): the scan scratch is a fixed 88 KiB device array inside the
+ * library instead of a pooled block, so no cudaMalloc / cudaFree / pool call is
+ * made.  Limits: at most 4,194,304 rows per call (IGL_ERR_INVALID_ARG beyond);
+ * plans with boolean or nullable outputs are rejected (IGL_ERR_UNSUPPORTED).
+ * All calls on a GPU share that array: calls that overlap on the GPU race, so
+ * serialise them.  The first call on each device resolves the array's address;
+ * make it before any stream capture begins. */
+int32_t igl_fp_run_static(igl_fp* fp, const igl_dev_col* in, int64_t nrows, igl_dev_col* out,
+                          int64_t* out_rows, void* stream);
 
 /* ---- hash join on device-resident columns.
  *      HashJoinExec::new (hash_join.rs:35-76): schema = left ++ right.
