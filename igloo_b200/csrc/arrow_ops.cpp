@@ -1,26 +1,774 @@
-// arrow_ops.cpp — streaming operators over host Arrow batches (push / pull).
-// PLACEHOLDER: replaced by the real implementation in the next milestone; every
-// entry point reports IGL_ERR_UNSUPPORTED so nothing silently falls back.
+// arrow_ops.cpp — streaming operators over host Arrow batches (push / pull):
+// the C-ABI form of `ExecutionPlan::execute() -> BoxStream<RecordBatch>`
+// (crates/engine/src/physical_plan.rs:10-17) for
+//   FilterExec / ProjectionExec   (operators/filter.rs:39-68, projection.rs:48-72)
+//   HashJoinExec                  (operators/hash_join.rs:100-213)
+//
+// Host batches arrive as Arrow C Data Interface struct arrays (what arrow-rs
+// `arrow::ffi::to_ffi` exports).  The reference's upstream granularity is
+// 1024-row batches (parquet_scan.rs:54); they are coalesced in a pinned staging
+// chunk (igl_config.coalesce_rows, default 4 Mi rows), uploaded with
+// cudaMemcpyAsync, run through the device operators and copied back into pinned
+// buffers that are handed out as Arrow arrays whose release callback recycles
+// them.  Row multisets, schema and error behaviour follow the reference; batch
+// boundaries follow the coalescing (one output batch per chunk; a FilterExec
+// chunk that keeps no row emits nothing, filter.rs:59-63).
+#include <algorithm>
+#include <cstring>
+#include <deque>
+#include <memory>
+
 #include "internal.h"
+#include "kernels.h"
 
 using namespace igl;
 
+namespace {
+
+// ---- process-wide pinned buffer pool (outlives any context: exported arrays
+//      may be released after their operator and context are gone) -------------
+struct PinnedPool {
+    std::mutex mu;
+    std::map<size_t, std::vector<void*>> free_lists;
+    std::map<void*, size_t> live;
+    static size_t bucket(size_t b) { size_t s = 4096; while (s < b) s <<= 1; return s; }
+    void* get(size_t bytes) {
+        const size_t b = bucket(bytes ? bytes : 1);
+        {
+            std::lock_guard<std::mutex> g(mu);
+            auto it = free_lists.find(b);
+            if (it != free_lists.end() && !it->second.empty()) {
+                void* p = it->second.back(); it->second.pop_back(); live[p] = b; return p;
+            }
+        }
+        void* p = nullptr;
+        if (cudaHostAlloc(&p, b, cudaHostAllocDefault) != cudaSuccess) { (void)cudaGetLastError(); return nullptr; }
+        std::lock_guard<std::mutex> g(mu);
+        live[p] = b;
+        return p;
+    }
+    void put(void* p) {
+        if (!p) return;
+        std::lock_guard<std::mutex> g(mu);
+        auto it = live.find(p);
+        if (it == live.end()) return;
+        const size_t b = it->second;
+        live.erase(it);
+        if (b > (256ull << 20)) { cudaFreeHost(p); return; }   // keep the pool modest
+        free_lists[b].push_back(p);
+    }
+};
+PinnedPool& pinned_pool() { static PinnedPool* p = new PinnedPool(); return *p; }
+
+struct FieldMeta { std::string name; int type; bool nullable; };
+
+int type_of_format(const char* f) {
+    if (!f) return 0;
+    if (!strcmp(f, "b")) return IGL_T_BOOL;
+    if (!strcmp(f, "i")) return IGL_T_I32;
+    if (!strcmp(f, "l")) return IGL_T_I64;
+    if (!strcmp(f, "g")) return IGL_T_F64;
+    if (!strcmp(f, "u")) return IGL_T_UTF8;
+    return 0;
+}
+const char* format_of_type(int t) {
+    switch (t) { case IGL_T_BOOL: return "b"; case IGL_T_I32: return "i"; case IGL_T_I64: return "l";
+                 case IGL_T_F64: return "g"; case IGL_T_UTF8: return "u"; }
+    return "n";
+}
+
+int32_t import_schema(const ArrowSchema* s, std::vector<FieldMeta>& out) {
+    if (!s || !s->format || strcmp(s->format, "+s")) return fail(IGL_ERR_INVALID_ARG, "schema must be a struct (\"+s\") of columns");
+    for (int64_t i = 0; i < s->n_children; ++i) {
+        const ArrowSchema* c = s->children[i];
+        const int t = type_of_format(c->format);
+        if (!t) return fail(IGL_ERR_UNSUPPORTED, "Arrow format \"%s\" of column %lld is not supported (Boolean, Int32, Int64, Float64, Utf8)",
+                            c->format ? c->format : "?", (long long)i);
+        out.push_back({c->name ? c->name : "", t, (c->flags & ARROW_FLAG_NULLABLE) != 0});
+    }
+    return IGL_OK;
+}
+
+void copy_bits(uint8_t* dst, int64_t dst_off, const uint8_t* src, int64_t src_off, int64_t n) {
+    if (n <= 0) return;
+    if ((dst_off & 7) == 0 && (src_off & 7) == 0) {
+        memcpy(dst + (dst_off >> 3), src + (src_off >> 3), (size_t)(n >> 3));
+        for (int64_t i = n & ~7ll; i < n; ++i) {
+            const int b = (src[(src_off + i) >> 3] >> ((src_off + i) & 7)) & 1;
+            uint8_t& d = dst[(dst_off + i) >> 3];
+            d = (uint8_t)((d & ~(1u << ((dst_off + i) & 7))) | (b << ((dst_off + i) & 7)));
+        }
+        return;
+    }
+    for (int64_t i = 0; i < n; ++i) {
+        const int b = (src[(src_off + i) >> 3] >> ((src_off + i) & 7)) & 1;
+        uint8_t& d = dst[(dst_off + i) >> 3];
+        d = (uint8_t)((d & ~(1u << ((dst_off + i) & 7))) | (b << ((dst_off + i) & 7)));
+    }
+}
+int64_t count_zero_bits(const uint8_t* bm, int64_t n) {
+    int64_t ones = 0;
+    for (int64_t i = 0; i < (n >> 3); ++i) ones += __builtin_popcount(bm[i]);
+    for (int64_t i = n & ~7ll; i < n; ++i) ones += (bm[i >> 3] >> (i & 7)) & 1;
+    return n - ones;
+}
+size_t pad64(size_t b) { return (b + 63) / 64 * 64 + 64; }
+
+// ---- one side's staging: pinned host chunk + device copy ---------------------
+struct StagedCol {
+    int type = 0; bool nullable = false;
+    uint8_t* h_data = nullptr; size_t h_data_cap = 0;   // values / utf8 bytes (pinned)
+    uint8_t* h_valid = nullptr;                          // bitmap for chunk_rows (pinned)
+    int32_t* h_off = nullptr;                            // utf8 offsets (pinned)
+    size_t utf8_used = 0;
+    void* d_data = nullptr; size_t d_data_cap = 0;
+    uint8_t* d_valid = nullptr; int32_t* d_off = nullptr;
+};
+
+struct Staging {
+    igl_ctx* ctx = nullptr;
+    std::vector<FieldMeta> fields;
+    std::vector<StagedCol> cols;
+    std::vector<uint8_t> wanted;   // which columns are staged at all
+    int64_t chunk_rows = 0, rows = 0;
+
+    int32_t init(igl_ctx* c, const std::vector<FieldMeta>& f, int64_t chunk) {
+        ctx = c; fields = f; chunk_rows = chunk; cols.resize(f.size()); wanted.assign(f.size(), 1);
+        for (size_t i = 0; i < f.size(); ++i) { cols[i].type = f[i].type; cols[i].nullable = f[i].nullable; }
+        return IGL_OK;
+    }
+    int32_t ensure_host(StagedCol& c, size_t data_bytes) {
+        if (data_bytes > c.h_data_cap) {
+            size_t cap = std::max<size_t>(data_bytes, c.h_data_cap * 2);
+            uint8_t* p = (uint8_t*)pinned_pool().get(pad64(cap));
+            if (!p) return fail(IGL_ERR_OOM, "pinned staging allocation of %zu bytes failed", cap);
+            if (c.h_data) { memcpy(p, c.h_data, c.type == IGL_T_UTF8 ? c.utf8_used : c.h_data_cap); pinned_pool().put(c.h_data); }
+            c.h_data = p; c.h_data_cap = cap;
+        }
+        if (c.nullable && !c.h_valid) {
+            c.h_valid = (uint8_t*)pinned_pool().get(pad64((size_t)(chunk_rows + 7) / 8));
+            if (!c.h_valid) return fail(IGL_ERR_OOM, "pinned staging allocation failed");
+            memset(c.h_valid, 0, pad64((size_t)(chunk_rows + 7) / 8));
+        }
+        if (c.type == IGL_T_UTF8 && !c.h_off) {
+            c.h_off = (int32_t*)pinned_pool().get(pad64((size_t)(chunk_rows + 1) * 4));
+            if (!c.h_off) return fail(IGL_ERR_OOM, "pinned staging allocation failed");
+            c.h_off[0] = 0;
+        }
+        return IGL_OK;
+    }
+    // Appends rows [from, from + n) of the batch.
+    int32_t append(const ArrowArray* batch, int64_t from, int64_t n) {
+        if ((size_t)batch->n_children != fields.size())
+            return fail(IGL_ERR_INVALID_ARG, "batch has %lld columns, schema has %zu", (long long)batch->n_children, fields.size());
+        for (size_t j = 0; j < fields.size(); ++j) {
+            if (!wanted[j]) continue;
+            StagedCol& c = cols[j];
+            const ArrowArray* a = batch->children[j];
+            const int64_t off = a->offset + batch->offset + from;
+            const uint8_t* valid = (const uint8_t*)a->buffers[0];
+            if (c.type == IGL_T_UTF8) {
+                if (a->n_buffers < 3) return fail(IGL_ERR_INVALID_ARG, "Utf8 column %zu needs 3 buffers", j);
+                const int32_t* so = (const int32_t*)a->buffers[1];
+                const uint8_t* sb = (const uint8_t*)a->buffers[2];
+                const int32_t b0 = so[off], b1 = so[off + n];
+                IGL_TRY(ensure_host(c, c.utf8_used + (size_t)(b1 - b0)));
+                if (b1 > b0) memcpy(c.h_data + c.utf8_used, sb + b0, (size_t)(b1 - b0));
+                const int32_t base = (int32_t)c.utf8_used - b0;
+                for (int64_t i = 1; i <= n; ++i) c.h_off[rows + i] = so[off + i] + base;
+                c.utf8_used += (size_t)(b1 - b0);
+            } else if (c.type == IGL_T_BOOL) {
+                IGL_TRY(ensure_host(c, (size_t)(rows + n + 7) / 8 + 8));
+                copy_bits(c.h_data, rows, (const uint8_t*)a->buffers[1], off, n);
+            } else {
+                const int w = type_width(c.type);
+                IGL_TRY(ensure_host(c, (size_t)(rows + n) * w));
+                memcpy(c.h_data + (size_t)rows * w, (const uint8_t*)a->buffers[1] + (size_t)off * w, (size_t)n * w);
+            }
+            if (c.nullable) {
+                if (valid && a->null_count != 0) copy_bits(c.h_valid, rows, valid, off, n);
+                else { // clear then set: the target bytes may hold stale bits from the previous chunk
+                    for (int64_t i = 0; i < n; ++i) c.h_valid[(rows + i) >> 3] |= (uint8_t)(1u << ((rows + i) & 7));
+                }
+            } else if (valid && a->null_count > 0) {
+                return fail(IGL_ERR_INVALID_ARG, "column %zu is declared non-nullable but the batch carries nulls", j);
+            }
+        }
+        rows += n;
+        return IGL_OK;
+    }
+    // Uploads the staged chunk; device pointers valid until the next upload.
+    int32_t upload(cudaStream_t st, std::vector<igl_dev_col>& dev) {
+        dev.assign(fields.size(), igl_dev_col{});
+        for (size_t j = 0; j < fields.size(); ++j) {
+            dev[j].type = fields[j].type;
+            if (!wanted[j]) continue;
+            StagedCol& c = cols[j];
+            size_t bytes = c.type == IGL_T_UTF8 ? c.utf8_used : c.type == IGL_T_BOOL ? (size_t)(rows + 7) / 8 : (size_t)rows * type_width(c.type);
+            if (pad64(bytes) > c.d_data_cap) {
+                if (c.d_data) pool_free(ctx, c.d_data);
+                c.d_data = nullptr; c.d_data_cap = 0;
+                IGL_TRY(pool_alloc(ctx, pad64(bytes), &c.d_data));
+                c.d_data_cap = pad64(bytes);
+            }
+            if (bytes) IGL_CUDA_OK(cudaMemcpyAsync(c.d_data, c.h_data, bytes, cudaMemcpyHostToDevice, st));
+            dev[j].data = c.d_data;
+            if (c.nullable) {
+                if (!c.d_valid) { void* p = nullptr; IGL_TRY(pool_alloc(ctx, pad64((size_t)(chunk_rows + 7) / 8), &p)); c.d_valid = (uint8_t*)p; }
+                IGL_CUDA_OK(cudaMemcpyAsync(c.d_valid, c.h_valid, (size_t)(rows + 7) / 8, cudaMemcpyHostToDevice, st));
+                dev[j].validity = c.d_valid;
+            }
+            if (c.type == IGL_T_UTF8) {
+                if (!c.d_off) { void* p = nullptr; IGL_TRY(pool_alloc(ctx, pad64((size_t)(chunk_rows + 1) * 4), &p)); c.d_off = (int32_t*)p; }
+                IGL_CUDA_OK(cudaMemcpyAsync(c.d_off, c.h_off, (size_t)(rows + 1) * 4, cudaMemcpyHostToDevice, st));
+                dev[j].offsets = c.d_off;
+            }
+        }
+        return IGL_OK;
+    }
+    void reset() {
+        rows = 0;
+        for (auto& c : cols) {
+            c.utf8_used = 0;
+            if (c.h_valid) memset(c.h_valid, 0, (size_t)(chunk_rows + 7) / 8);
+        }
+    }
+    void destroy() {
+        for (auto& c : cols) {
+            pinned_pool().put(c.h_data); pinned_pool().put(c.h_valid); pinned_pool().put(c.h_off);
+            pool_free(ctx, c.d_data); pool_free(ctx, c.d_valid); pool_free(ctx, c.d_off);
+            c = StagedCol{};
+        }
+    }
+};
+
+// ---- output batches ------------------------------------------------------------
+struct OutCol { int type = 0; void* data = nullptr; uint8_t* valid = nullptr; int32_t* off = nullptr; int64_t null_count = 0; };
+struct OutBatch { int64_t nrows = 0; std::vector<OutCol> cols; };
+
+struct ExportHolder {
+    std::vector<void*> pinned;
+    std::vector<ArrowArray> children;
+    std::vector<ArrowArray*> child_ptrs;
+    std::vector<std::vector<const void*>> buffers;
+    const void* top_buffers[1] = {nullptr};
+};
+void release_child(ArrowArray* a) { a->release = nullptr; }
+void release_top(ArrowArray* a) {
+    ExportHolder* h = (ExportHolder*)a->private_data;
+    for (auto& c : h->children) if (c.release) c.release(&c);
+    for (void* p : h->pinned) pinned_pool().put(p);
+    delete h;
+    a->release = nullptr;
+}
+void export_batch(OutBatch&& b, ArrowArray* out) {
+    ExportHolder* h = new ExportHolder();
+    const size_t n = b.cols.size();
+    h->children.resize(n); h->child_ptrs.resize(n); h->buffers.resize(n);
+    for (size_t j = 0; j < n; ++j) {
+        OutCol& c = b.cols[j];
+        ArrowArray& a = h->children[j];
+        memset(&a, 0, sizeof a);
+        a.length = b.nrows; a.null_count = c.null_count; a.offset = 0;
+        if (c.type == IGL_T_UTF8) h->buffers[j] = {c.null_count ? c.valid : nullptr, c.off, c.data};
+        else h->buffers[j] = {c.null_count ? c.valid : nullptr, c.data};
+        a.n_buffers = (int64_t)h->buffers[j].size();
+        a.buffers = h->buffers[j].data();
+        a.release = release_child;
+        h->child_ptrs[j] = &a;
+        h->pinned.push_back(c.data); h->pinned.push_back(c.valid); h->pinned.push_back(c.off);
+    }
+    memset(out, 0, sizeof *out);
+    out->length = b.nrows; out->null_count = 0; out->offset = 0;
+    out->n_buffers = 1; out->buffers = h->top_buffers;
+    out->n_children = (int64_t)n; out->children = h->child_ptrs.data();
+    out->release = release_top; out->private_data = h;
+}
+
+struct SchemaHolder {
+    std::vector<ArrowSchema> children; std::vector<ArrowSchema*> ptrs; std::vector<std::string> names;
+};
+void release_schema_child(ArrowSchema* s) { s->release = nullptr; }
+void release_schema_top(ArrowSchema* s) { delete (SchemaHolder*)s->private_data; s->release = nullptr; }
+void export_schema(const std::vector<FieldMeta>& f, ArrowSchema* out) {
+    SchemaHolder* h = new SchemaHolder();
+    h->children.resize(f.size()); h->ptrs.resize(f.size()); h->names.resize(f.size());
+    for (size_t j = 0; j < f.size(); ++j) {
+        h->names[j] = f[j].name;
+        ArrowSchema& c = h->children[j];
+        memset(&c, 0, sizeof c);
+        c.format = format_of_type(f[j].type); c.name = h->names[j].c_str();
+        c.flags = f[j].nullable ? ARROW_FLAG_NULLABLE : 0; c.release = release_schema_child;
+        h->ptrs[j] = &c;
+    }
+    memset(out, 0, sizeof *out);
+    out->format = "+s"; out->name = ""; out->n_children = (int64_t)f.size(); out->children = h->ptrs.data();
+    out->release = release_schema_top; out->private_data = h;
+}
+
+}  // namespace
+
+// ---- the operator --------------------------------------------------------------
+struct igl_op {
+    igl_ctx* ctx = nullptr;
+    bool is_join = false;
+    std::vector<FieldMeta> out_fields;
+    std::deque<OutBatch> ready;
+    bool input_done = false;
+    // filter / projection
+    Staging in;
+    igl_expr* pred = nullptr;
+    std::vector<igl_expr*> proj_exprs;       // device expressions (owned)
+    igl_fp* fp = nullptr;
+    bool has_pred = false, need_rowid = false;
+    struct OutSpec { bool utf8_pass; int index; };   // index: fp output # or input column #
+    std::vector<OutSpec> out_spec;
+    int n_fp_out = 0;
+    // join
+    Staging build;
+    igl_join* join = nullptr;
+    igl_expr *lkey = nullptr, *rkey = nullptr;
+    bool build_done = false, left_join = false;
+    int n_left = 0, n_right = 0;
+    std::vector<void*> build_dev;            // grown device columns of the whole build side
+    std::vector<size_t> build_cap;
+    std::vector<uint8_t*> build_valid;
+    int64_t build_rows = 0, build_rows_cap = 0;
+};
+
+namespace {
+
+int32_t d2h_col(igl_ctx* ctx, cudaStream_t st, OutCol& oc, const void* d_data, const uint8_t* d_valid, int64_t n, bool nullable) {
+    const size_t bytes = oc.type == IGL_T_BOOL ? (size_t)(n + 7) / 8 : (size_t)n * type_width(oc.type);
+    oc.data = pinned_pool().get(pad64(bytes));
+    if (!oc.data) return fail(IGL_ERR_OOM, "pinned output allocation of %zu bytes failed", bytes);
+    if (bytes) IGL_CUDA_OK(cudaMemcpyAsync(oc.data, d_data, bytes, cudaMemcpyDeviceToHost, st));
+    if (nullable && d_valid) {
+        oc.valid = (uint8_t*)pinned_pool().get(pad64((size_t)(n + 7) / 8));
+        if (!oc.valid) return fail(IGL_ERR_OOM, "pinned output allocation failed");
+        IGL_CUDA_OK(cudaMemcpyAsync(oc.valid, d_valid, (size_t)(n + 7) / 8, cudaMemcpyDeviceToHost, st));
+    }
+    (void)ctx;
+    return IGL_OK;
+}
+
+// Runs one staged chunk of a filter / projection operator.
+int32_t fp_flush(igl_op* op) {
+    Staging& S = op->in;
+    const int64_t n = S.rows;
+    if (n == 0) return IGL_OK;
+    igl_ctx* ctx = op->ctx;
+    cudaStream_t st = ctx->stream;
+    std::vector<igl_dev_col> dev;
+    IGL_TRY(S.upload(st, dev));
+    // device outputs
+    const int nfo = op->n_fp_out + (op->need_rowid ? 1 : 0);
+    std::vector<igl_dev_col> dout(nfo);
+    std::vector<void*> to_free;
+    auto cleanup = [&]() { for (void* p : to_free) pool_free(ctx, p); };
+    int64_t n_out = n;
+    if (op->fp) {
+        for (int j = 0; j < nfo; ++j) {
+            int32_t t = 0, nl = 0;
+            igl_fp_output_type(op->fp, j, &t, &nl);
+            dout[j].type = t;
+            const size_t bytes = t == IGL_T_BOOL ? (size_t)(n + 7) / 8 : (size_t)n * type_width(t);
+            void* p = nullptr;
+            int32_t rc = pool_alloc(ctx, pad64(bytes), &p);
+            if (rc < 0) { cleanup(); return rc; }
+            to_free.push_back(p); dout[j].data = p;
+            if (nl) {
+                rc = pool_alloc(ctx, pad64((size_t)(n + 7) / 8), &p);
+                if (rc < 0) { cleanup(); return rc; }
+                to_free.push_back(p); dout[j].validity = (uint8_t*)p;
+            }
+        }
+        int32_t rc = igl_fp_run(op->fp, dev.data(), n, dout.data(), &n_out, st);
+        if (rc < 0) { cleanup(); return rc; }
+    }
+    S.reset();
+    if (n_out == 0 && op->has_pred) { cleanup(); return IGL_OK; }   // filter.rs:59-63: empty results are dropped
+    OutBatch ob;
+    ob.nrows = n_out;
+    ob.cols.resize(op->out_spec.size());
+    const int32_t* d_rowid = op->need_rowid ? (const int32_t*)dout[op->n_fp_out].data : nullptr;
+    std::vector<std::pair<size_t, int32_t*>> utf8_pending;   // (output index, device offsets)
+    std::vector<uint8_t*> utf8_valid_bytes(op->out_spec.size(), nullptr);
+    int32_t rc = IGL_OK;
+    for (size_t j = 0; j < op->out_spec.size() && rc >= 0; ++j) {
+        OutCol& oc = ob.cols[j];
+        const auto& sp = op->out_spec[j];
+        oc.type = op->out_fields[j].type;
+        if (!sp.utf8_pass) {
+            rc = d2h_col(ctx, st, oc, dout[sp.index].data, dout[sp.index].validity, n_out, op->out_fields[j].nullable);
+        } else {
+            // K2s: offsets (lengths + scan) now, bytes once the total is known
+            const igl_dev_col& src = dev[sp.index];
+            void* d_off = nullptr; void* scratch = nullptr; void* vbytes = nullptr;
+            const size_t sbytes = 256 + ((size_t)n_out / 2048 + 2) * 8;
+            rc = pool_alloc(ctx, pad64((size_t)(n_out + 1) * 4), &d_off);
+            if (rc >= 0) { to_free.push_back(d_off); rc = pool_alloc(ctx, sbytes, &scratch); }
+            if (rc >= 0) { to_free.push_back(scratch); if (src.validity) { rc = pool_alloc(ctx, pad64((size_t)n_out + 1), &vbytes); if (rc >= 0) to_free.push_back(vbytes); } }
+            if (rc >= 0) rc = utf8_gather_offsets(ctx, src.offsets, src.validity, d_rowid, n_out, (int32_t*)d_off, (uint8_t*)vbytes, scratch, sbytes, st);
+            if (rc >= 0) {
+                oc.off = (int32_t*)pinned_pool().get(pad64((size_t)(n_out + 1) * 4));
+                if (!oc.off) rc = fail(IGL_ERR_OOM, "pinned output allocation failed");
+            }
+            if (rc >= 0 && cudaMemcpyAsync(oc.off, d_off, (size_t)(n_out + 1) * 4, cudaMemcpyDeviceToHost, st) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "offset copy failed");
+            utf8_pending.push_back({j, (int32_t*)d_off});
+            utf8_valid_bytes[j] = (uint8_t*)vbytes;
+        }
+    }
+    if (rc >= 0 && cudaStreamSynchronize(st) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "stream synchronise failed: %s", cudaGetErrorString(cudaGetLastError()));
+    for (auto& pr : utf8_pending) {
+        if (rc < 0) break;
+        const size_t j = pr.first;
+        OutCol& oc = ob.cols[j];
+        const igl_dev_col& src = dev[op->out_spec[j].index];
+        const size_t total = (size_t)oc.off[n_out];
+        void* d_bytes = nullptr;
+        rc = pool_alloc(ctx, pad64(total), &d_bytes);
+        if (rc < 0) break;
+        to_free.push_back(d_bytes);
+        rc = utf8_gather_bytes(ctx, src.offsets, (const uint8_t*)src.data, d_rowid, n_out, pr.second, (uint8_t*)d_bytes, st);
+        if (rc < 0) break;
+        oc.data = pinned_pool().get(pad64(total));
+        if (!oc.data) { rc = fail(IGL_ERR_OOM, "pinned output allocation failed"); break; }
+        if (total && cudaMemcpyAsync(oc.data, d_bytes, total, cudaMemcpyDeviceToHost, st) != cudaSuccess) { rc = fail(IGL_ERR_CUDA, "string copy failed"); break; }
+        if (utf8_valid_bytes[j]) {   // validity gathered as bytes -> bitmap on the device, then down
+            void* d_bits = nullptr;
+            rc = pool_alloc(ctx, pad64((size_t)(n_out + 7) / 8 + 4), &d_bits);
+            if (rc < 0) break;
+            to_free.push_back(d_bits);
+            if (launch_pack_bits(utf8_valid_bytes[j], (uint32_t*)d_bits, nullptr, n_out, n_out, ctx->sm_count, st) != cudaSuccess) { rc = fail(IGL_ERR_CUDA, "validity pack failed"); break; }
+            ctx->launches++;
+            oc.valid = (uint8_t*)pinned_pool().get(pad64((size_t)(n_out + 7) / 8 + 4));
+            if (!oc.valid) { rc = fail(IGL_ERR_OOM, "pinned output allocation failed"); break; }
+            if (cudaMemcpyAsync(oc.valid, d_bits, (size_t)(n_out + 7) / 8, cudaMemcpyDeviceToHost, st) != cudaSuccess) { rc = fail(IGL_ERR_CUDA, "validity copy failed"); break; }
+        }
+    }
+    if (rc >= 0 && !utf8_pending.empty() && cudaStreamSynchronize(st) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "stream synchronise failed");
+    cleanup();
+    if (rc < 0) {
+        for (auto& c : ob.cols) { pinned_pool().put(c.data); pinned_pool().put(c.valid); pinned_pool().put(c.off); }
+        return rc;
+    }
+    for (auto& c : ob.cols) c.null_count = c.valid ? count_zero_bits(c.valid, n_out) : 0;
+    op->ready.push_back(std::move(ob));
+    return IGL_OK;
+}
+
+// Appends the staged build chunk to the device-resident build side.
+int32_t join_build_flush(igl_op* op) {
+    Staging& S = op->build;
+    const int64_t n = S.rows;
+    if (n == 0) return IGL_OK;
+    igl_ctx* ctx = op->ctx;
+    cudaStream_t st = ctx->stream;
+    if (op->build_rows + n > op->build_rows_cap) {   // grow every column (doubling)
+        const int64_t cap = std::max<int64_t>(op->build_rows + n, op->build_rows_cap * 2);
+        for (int c = 0; c < op->n_right; ++c) {
+            const int w = type_width(S.fields[c].type);
+            void* p = nullptr;
+            IGL_TRY(pool_alloc(ctx, pad64((size_t)cap * w), &p));
+            if (op->build_dev[c]) {
+                IGL_CUDA_OK(cudaMemcpyAsync(p, op->build_dev[c], (size_t)op->build_rows * w, cudaMemcpyDeviceToDevice, st));
+                IGL_CUDA_OK(cudaStreamSynchronize(st));
+                pool_free(ctx, op->build_dev[c]);
+            }
+            op->build_dev[c] = p;
+            if (S.fields[c].nullable) {
+                void* v = nullptr;
+                IGL_TRY(pool_alloc(ctx, pad64((size_t)(cap + 7) / 8 + 8), &v));
+                IGL_CUDA_OK(cudaMemsetAsync(v, 0, pad64((size_t)(cap + 7) / 8 + 8), st));
+                if (op->build_valid[c]) {
+                    IGL_CUDA_OK(cudaMemcpyAsync(v, op->build_valid[c], (size_t)(op->build_rows + 7) / 8, cudaMemcpyDeviceToDevice, st));
+                    IGL_CUDA_OK(cudaStreamSynchronize(st));
+                    pool_free(ctx, op->build_valid[c]);
+                }
+                op->build_valid[c] = (uint8_t*)v;
+            }
+        }
+        op->build_rows_cap = cap;
+    }
+    if ((op->build_rows & 7) != 0) {
+        // validity bitmaps are appended bytewise: keep chunk boundaries byte aligned
+        for (int c = 0; c < op->n_right; ++c)
+            if (S.fields[c].nullable) return fail(IGL_ERR_UNSUPPORTED, "nullable build columns need coalesce_rows to be a multiple of 8");
+    }
+    for (int c = 0; c < op->n_right; ++c) {
+        const int w = type_width(S.fields[c].type);
+        IGL_CUDA_OK(cudaMemcpyAsync((uint8_t*)op->build_dev[c] + (size_t)op->build_rows * w, S.cols[c].h_data, (size_t)n * w, cudaMemcpyHostToDevice, st));
+        if (S.fields[c].nullable)
+            IGL_CUDA_OK(cudaMemcpyAsync(op->build_valid[c] + (op->build_rows >> 3), S.cols[c].h_valid, (size_t)(n + 7) / 8, cudaMemcpyHostToDevice, st));
+    }
+    IGL_CUDA_OK(cudaStreamSynchronize(st));
+    op->build_rows += n;
+    S.reset();
+    return IGL_OK;
+}
+
+int32_t join_probe_flush(igl_op* op) {
+    Staging& S = op->in;
+    const int64_t n = S.rows;
+    if (n == 0) return IGL_OK;
+    igl_ctx* ctx = op->ctx;
+    cudaStream_t st = ctx->stream;
+    std::vector<igl_dev_col> dev;
+    IGL_TRY(S.upload(st, dev));
+    int64_t cap = n;
+    if (igl_join_has_duplicates(op->join)) IGL_TRY(igl_join_probe_count(op->join, dev.data(), n, &cap, st));
+    const int nc = op->n_left + op->n_right;
+    std::vector<igl_dev_col> dout(nc);
+    std::vector<void*> to_free;
+    auto cleanup = [&]() { for (void* p : to_free) pool_free(ctx, p); };
+    for (int c = 0; c < nc; ++c) {
+        dout[c].type = op->out_fields[c].type;
+        void* p = nullptr;
+        int32_t rc = pool_alloc(ctx, pad64((size_t)std::max<int64_t>(cap, 1) * type_width(dout[c].type)), &p);
+        if (rc < 0) { cleanup(); return rc; }
+        to_free.push_back(p); dout[c].data = p;
+        rc = pool_alloc(ctx, pad64((size_t)(cap + 7) / 8 + 8), &p);
+        if (rc < 0) { cleanup(); return rc; }
+        to_free.push_back(p); dout[c].validity = (uint8_t*)p;
+    }
+    int64_t n_out = 0;
+    int32_t rc = igl_join_probe(op->join, dev.data(), n, dout.data(), cap, &n_out, st);
+    S.reset();
+    if (rc < 0) { cleanup(); return rc; }
+    if (n_out == 0) { cleanup(); return IGL_OK; }
+    OutBatch ob;
+    ob.nrows = n_out;
+    ob.cols.resize(nc);
+    for (int c = 0; c < nc && rc >= 0; ++c) {
+        ob.cols[c].type = dout[c].type;
+        // igl_join_probe writes a validity bitmap for a left column that has one and
+        // for a right column that can be null (source nullable, or null-extended)
+        const bool is_left = c < op->n_left;
+        const bool wrote_valid = is_left ? dev[c].validity != nullptr
+                                         : (op->left_join || op->build_valid[c - op->n_left] != nullptr);
+        rc = d2h_col(ctx, st, ob.cols[c], dout[c].data, wrote_valid ? dout[c].validity : nullptr, n_out, true);
+    }
+    if (rc >= 0 && cudaStreamSynchronize(st) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "stream synchronise failed");
+    cleanup();
+    if (rc < 0) {
+        for (auto& c : ob.cols) { pinned_pool().put(c.data); pinned_pool().put(c.valid); }
+        return rc;
+    }
+    for (auto& c : ob.cols) c.null_count = c.valid ? count_zero_bits(c.valid, n_out) : 0;
+    op->ready.push_back(std::move(ob));
+    return IGL_OK;
+}
+
+int32_t push_rows(igl_op* op, Staging& S, const ArrowArray* batch, int32_t (*flush)(igl_op*)) {
+    if (!batch) return fail(IGL_ERR_INVALID_ARG, "batch is NULL");
+    int64_t done = 0;
+    while (done < batch->length) {
+        const int64_t take = std::min<int64_t>(batch->length - done, S.chunk_rows - S.rows);
+        IGL_TRY(S.append(batch, done, take));
+        done += take;
+        if (S.rows == S.chunk_rows) IGL_TRY(flush(op));
+    }
+    return IGL_OK;
+}
+
+bool is_bare_col(const uint8_t* bc, size_t len, int* col) {
+    if (len == 3 && bc[0] == IGL_OP_COL) { *col = bc[1] | (bc[2] << 8); return true; }
+    return false;
+}
+
+}  // namespace
+
 extern "C" {
-int32_t igl_op_filter_project_create(igl_ctx*, const struct ArrowSchema*, const uint8_t*, size_t, const uint8_t* const*,
-                                     const size_t*, const char* const*, int32_t, igl_op** out) {
-    if (out) *out = nullptr;
-    return fail(IGL_ERR_UNSUPPORTED, "igl_op_filter_project_create: not built yet");
+
+int32_t igl_op_filter_project_create(igl_ctx* ctx, const struct ArrowSchema* in_schema, const uint8_t* pred, size_t pred_len,
+                                     const uint8_t* const* proj, const size_t* proj_len, const char* const* proj_names,
+                                     int32_t nproj, igl_op** out) {
+    if (!ctx || !out) return fail(IGL_ERR_INVALID_ARG, "igl_op_filter_project_create: NULL argument");
+    *out = nullptr;
+    std::vector<FieldMeta> fields;
+    IGL_TRY(import_schema(in_schema, fields));
+    if (fields.empty()) return fail(IGL_ERR_INVALID_ARG, "input schema has no columns");
+    auto op = std::make_unique<igl_op>();
+    op->ctx = ctx;
+    DeviceGuard g(ctx->device);
+    op->in.init(ctx, fields, ctx->cfg.coalesce_rows);
+    const int n_in = (int)fields.size();
+    std::vector<int32_t> types(n_in); std::vector<uint8_t> nulls(n_in);
+    for (int i = 0; i < n_in; ++i) { types[i] = fields[i].type; nulls[i] = fields[i].nullable; }
+    auto destroy_partial = [&]() { igl_op_destroy(op.release()); };
+    if (pred && pred_len) {
+        int32_t rc = igl_expr_compile(ctx, pred, pred_len, types.data(), nulls.data(), n_in, &op->pred);
+        if (rc < 0) { destroy_partial(); return rc; }
+        op->has_pred = true;
+    }
+    std::vector<uint8_t> skip(n_in, 0);
+    std::vector<uint8_t> wanted(n_in, 0);
+    std::vector<bool> used(n_in, false);
+    if (nproj == 0) {   // FilterExec: schema = input schema (filter.rs:70-72)
+        for (int c = 0; c < n_in; ++c) {
+            op->out_fields.push_back(fields[c]);
+            if (fields[c].type == IGL_T_UTF8) { skip[c] = 1; op->out_spec.push_back({true, c}); }
+            else op->out_spec.push_back({false, op->n_fp_out++});
+            wanted[c] = 1;
+        }
+    } else {
+        for (int j = 0; j < nproj; ++j) {
+            int c = -1;
+            const char* nm = proj_names && proj_names[j] ? proj_names[j] : "";
+            if (is_bare_col(proj[j], proj_len[j], &c) && c < n_in && fields[c].type == IGL_T_UTF8) {
+                op->out_spec.push_back({true, c});
+                op->out_fields.push_back({nm, IGL_T_UTF8, fields[c].nullable});
+                wanted[c] = 1;
+                continue;
+            }
+            igl_expr* e = nullptr;
+            int32_t rc = igl_expr_compile(ctx, proj[j], proj_len[j], types.data(), nulls.data(), n_in, &e);
+            if (rc < 0) { destroy_partial(); return rc; }
+            op->proj_exprs.push_back(e);
+            op->out_spec.push_back({false, op->n_fp_out++});
+            op->out_fields.push_back({nm, e->type, e->nullable});
+            for (auto& nd : e->nodes) if (nd.op == IGL_OP_COL) wanted[nd.col] = 1;
+        }
+    }
+    if (op->pred) for (auto& nd : op->pred->nodes) if (nd.op == IGL_OP_COL) wanted[nd.col] = 1;
+    op->in.wanted = wanted;
+    bool any_utf8 = false;
+    for (auto& sp : op->out_spec) any_utf8 |= sp.utf8_pass;
+    op->need_rowid = any_utf8 && op->has_pred;
+    if (op->n_fp_out > 0 || op->has_pred) {
+        std::vector<const igl_expr*> pe(op->proj_exprs.begin(), op->proj_exprs.end());
+        // a filter whose only outputs are strings still needs the row ids: give it a plan with no value outputs
+        int32_t rc;
+        if (nproj == 0) rc = fp_create_ex(ctx, types.data(), nulls.data(), n_in, op->pred, nullptr, 0, skip.data(), op->need_rowid, &op->fp);
+        else if (!pe.empty()) rc = fp_create_ex(ctx, types.data(), nulls.data(), n_in, op->pred, pe.data(), (int32_t)pe.size(), nullptr, op->need_rowid, &op->fp);
+        else {   // projection of string columns only, under a predicate
+            std::fill(skip.begin(), skip.end(), 1);
+            rc = fp_create_ex(ctx, types.data(), nulls.data(), n_in, op->pred, nullptr, 0, skip.data(), op->need_rowid, &op->fp);
+        }
+        if (rc < 0) { destroy_partial(); return rc; }
+    }
+    *out = op.release();
+    return IGL_OK;
 }
-int32_t igl_op_hash_join_create(igl_ctx*, int32_t, const struct ArrowSchema*, const struct ArrowSchema*, const uint8_t*,
-                                size_t, const uint8_t*, size_t, igl_op** out) {
-    if (out) *out = nullptr;
-    return fail(IGL_ERR_UNSUPPORTED, "igl_op_hash_join_create: not built yet");
+
+int32_t igl_op_hash_join_create(igl_ctx* ctx, int32_t join_type, const struct ArrowSchema* left_schema,
+                                const struct ArrowSchema* right_schema, const uint8_t* left_key, size_t left_key_len,
+                                const uint8_t* right_key, size_t right_key_len, igl_op** out) {
+    if (!ctx || !out || !left_key || !right_key) return fail(IGL_ERR_INVALID_ARG, "igl_op_hash_join_create: NULL argument");
+    *out = nullptr;
+    std::vector<FieldMeta> lf, rf;
+    IGL_TRY(import_schema(left_schema, lf));
+    IGL_TRY(import_schema(right_schema, rf));
+    auto op = std::make_unique<igl_op>();
+    op->ctx = ctx; op->is_join = true;
+    DeviceGuard g(ctx->device);
+    op->n_left = (int)lf.size(); op->n_right = (int)rf.size();
+    op->in.init(ctx, lf, ctx->cfg.coalesce_rows);
+    op->build.init(ctx, rf, ctx->cfg.coalesce_rows);
+    std::vector<int32_t> lt, rt; std::vector<uint8_t> ln, rn;
+    for (auto& f : lf) { lt.push_back(f.type); ln.push_back(f.nullable); }
+    for (auto& f : rf) { rt.push_back(f.type); rn.push_back(f.nullable); }
+    auto destroy_partial = [&]() { igl_op_destroy(op.release()); };
+    int32_t rc = igl_expr_compile(ctx, left_key, left_key_len, lt.data(), ln.data(), op->n_left, &op->lkey);
+    if (rc >= 0) rc = igl_expr_compile(ctx, right_key, right_key_len, rt.data(), rn.data(), op->n_right, &op->rkey);
+    if (rc >= 0) rc = igl_join_create(ctx, join_type, lt.data(), ln.data(), op->n_left, rt.data(), rn.data(), op->n_right, op->lkey, op->rkey, &op->join);
+    if (rc < 0) { destroy_partial(); return rc; }
+    // output schema: hash_join.rs:35-76 (left fields, right fields, clashes renamed right_<name>)
+    op->left_join = join_type == IGL_JOIN_LEFT || join_type == IGL_JOIN_FULL;
+    for (auto& f : lf) op->out_fields.push_back(f);
+    for (auto& f : rf) {
+        FieldMeta o = f;
+        for (auto& l : lf) if (l.name == f.name) { o.name = "right_" + f.name; break; }
+        // The reference keeps the declared nullability (hash_join.rs:57-61), so its
+        // null-extended rows of a Left/Full join fail RecordBatch::try_new when the
+        // right field was declared non-nullable.  Here such fields become nullable.
+        if (op->left_join) o.nullable = true;
+        op->out_fields.push_back(o);
+    }
+    op->build_dev.assign(op->n_right, nullptr);
+    op->build_cap.assign(op->n_right, 0);
+    op->build_valid.assign(op->n_right, nullptr);
+    *out = op.release();
+    return IGL_OK;
 }
-int32_t igl_op_schema(igl_op*, struct ArrowSchema*) { return fail(IGL_ERR_UNSUPPORTED, "igl_op_schema: not built yet"); }
-int32_t igl_op_push_build(igl_op*, const struct ArrowArray*) { return fail(IGL_ERR_UNSUPPORTED, "igl_op_push_build: not built yet"); }
-int32_t igl_op_finish_build(igl_op*) { return fail(IGL_ERR_UNSUPPORTED, "igl_op_finish_build: not built yet"); }
-int32_t igl_op_push(igl_op*, const struct ArrowArray*) { return fail(IGL_ERR_UNSUPPORTED, "igl_op_push: not built yet"); }
-int32_t igl_op_finish_input(igl_op*) { return fail(IGL_ERR_UNSUPPORTED, "igl_op_finish_input: not built yet"); }
-int32_t igl_op_pull(igl_op*, struct ArrowArray*) { return fail(IGL_ERR_UNSUPPORTED, "igl_op_pull: not built yet"); }
-void igl_op_destroy(igl_op*) {}
+
+int32_t igl_op_schema(igl_op* op, struct ArrowSchema* out) {
+    if (!op || !out) return fail(IGL_ERR_INVALID_ARG, "igl_op_schema: NULL argument");
+    export_schema(op->out_fields, out);
+    return IGL_OK;
 }
+
+int32_t igl_op_push_build(igl_op* op, const struct ArrowArray* batch) {
+    if (!op || !op->is_join) return fail(IGL_ERR_INVALID_ARG, "igl_op_push_build: not a join operator");
+    if (op->build_done) return fail(IGL_ERR_INVALID_ARG, "igl_op_push_build: build side already finished");
+    DeviceGuard g(op->ctx->device);
+    return push_rows(op, op->build, batch, join_build_flush);
+}
+
+int32_t igl_op_finish_build(igl_op* op) {
+    if (!op || !op->is_join) return fail(IGL_ERR_INVALID_ARG, "igl_op_finish_build: not a join operator");
+    if (op->build_done) return IGL_OK;
+    DeviceGuard g(op->ctx->device);
+    IGL_TRY(join_build_flush(op));
+    std::vector<igl_dev_col> cols(op->n_right);
+    for (int c = 0; c < op->n_right; ++c) {
+        cols[c].type = op->build.fields[c].type;
+        if (!op->build_dev[c]) { void* p = nullptr; IGL_TRY(pool_alloc(op->ctx, 256, &p)); op->build_dev[c] = p; }
+        cols[c].data = op->build_dev[c];
+        cols[c].validity = op->build_valid[c];
+    }
+    IGL_TRY(igl_join_build(op->join, cols.data(), op->build_rows, op->ctx->stream));
+    op->build_done = true;
+    return IGL_OK;
+}
+
+int32_t igl_op_push(igl_op* op, const struct ArrowArray* batch) {
+    if (!op) return fail(IGL_ERR_INVALID_ARG, "igl_op_push: NULL operator");
+    if (op->input_done) return fail(IGL_ERR_INVALID_ARG, "igl_op_push: input already finished");
+    DeviceGuard g(op->ctx->device);
+    if (op->is_join) {
+        if (!op->build_done) return fail(IGL_ERR_INVALID_ARG, "igl_op_push: finish the build side first (hash_join.rs:100-128 drains the right child before probing)");
+        return push_rows(op, op->in, batch, join_probe_flush);
+    }
+    return push_rows(op, op->in, batch, fp_flush);
+}
+
+int32_t igl_op_finish_input(igl_op* op) {
+    if (!op) return fail(IGL_ERR_INVALID_ARG, "igl_op_finish_input: NULL operator");
+    if (op->input_done) return IGL_OK;
+    DeviceGuard g(op->ctx->device);
+    if (op->is_join) {
+        if (!op->build_done) IGL_TRY(igl_op_finish_build(op));
+        IGL_TRY(join_probe_flush(op));
+    } else IGL_TRY(fp_flush(op));
+    op->input_done = true;
+    return IGL_OK;
+}
+
+int32_t igl_op_pull(igl_op* op, struct ArrowArray* out) {
+    if (!op || !out) return fail(IGL_ERR_INVALID_ARG, "igl_op_pull: NULL argument");
+    if (op->ready.empty()) return op->input_done ? IGL_EOS : IGL_AGAIN;
+    OutBatch b = std::move(op->ready.front());
+    op->ready.pop_front();
+    export_batch(std::move(b), out);
+    return IGL_OK;
+}
+
+void igl_op_destroy(igl_op* op) {
+    if (!op) return;
+    DeviceGuard g(op->ctx->device);
+    for (auto& b : op->ready) for (auto& c : b.cols) { pinned_pool().put(c.data); pinned_pool().put(c.valid); pinned_pool().put(c.off); }
+    op->in.destroy();
+    op->build.destroy();
+    if (op->fp) igl_fp_destroy(op->fp);
+    if (op->join) igl_join_destroy(op->join);
+    igl_expr_destroy(op->pred);
+    for (auto* e : op->proj_exprs) igl_expr_destroy(e);
+    igl_expr_destroy(op->lkey); igl_expr_destroy(op->rkey);
+    for (void* p : op->build_dev) pool_free(op->ctx, p);
+    for (uint8_t* p : op->build_valid) pool_free(op->ctx, p);
+    delete op;
+}
+
+}  // extern "C"

@@ -21,4 +21,11 @@ int32_t fp_create_ex(igl_ctx* ctx, const int32_t* in_types, const uint8_t* in_nu
                      const igl_expr* pred, const igl_expr* const* proj, int32_t nproj, const uint8_t* skip,
                      bool with_rowid, igl_fp** out);
 
+// Utf8 gather by row ids (utf8.cu): offsets (lengths + ordered scan), then bytes.
+int32_t utf8_gather_offsets(igl_ctx* ctx, const int32_t* src_off, const uint8_t* src_valid, const int32_t* rowid,
+                            long long n, int32_t* out_off, uint8_t* out_valid_bytes, void* scratch, size_t scratch_bytes,
+                            cudaStream_t st);
+int32_t utf8_gather_bytes(igl_ctx* ctx, const int32_t* src_off, const uint8_t* src_bytes, const int32_t* rowid,
+                          long long n, const int32_t* out_off, uint8_t* out_bytes, cudaStream_t st);
+
 }  // namespace igl

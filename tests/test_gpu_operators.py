@@ -1,0 +1,155 @@
+"""GPU parity through the streaming operator API (Arrow C Data Interface push/pull),
+written like the reference's own integration test (crates/engine/tests/integration_test.rs)."""
+import json
+import os
+
+import numpy as np
+import pyarrow as pa
+import pytest
+
+from igloo_b200.expr import Field, col, lit, lower, T_BOOL, T_F64, T_I32, T_I64
+from oracle import oracle as orc
+from tests.util import arrow_to_columns, assert_same_multiset, columns_to_arrow
+
+pytestmark = pytest.mark.gpu
+GOLD = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "users.json")))
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from igloo_b200.device import Context
+    c = Context(0, coalesce_rows=4096)   # small chunks: every test crosses chunk boundaries
+    yield c
+    c.close()
+
+
+def users():
+    r = GOLD["rows"]
+    return pa.table({"id": pa.array(r["id"], pa.int32()), "name": pa.array(r["name"], pa.string()), "age": pa.array(r["age"], pa.int32())},
+                    schema=pa.schema([pa.field("id", pa.int32(), False), pa.field("name", pa.string(), False), pa.field("age", pa.int32(), False)]))
+
+
+def collect(plan):
+    batches = list(plan.execute())
+    return pa.Table.from_batches(batches, schema=plan.schema()), batches
+
+
+def test_c1_select_name_age_where_age_gt(ctx):
+    """BASELINE.json configs[0] on the integration_test.rs rows, via the planner:
+    SELECT name, age FROM users WHERE age > 25 -> 4 rows; WHERE age > 30 -> (Eve,32),(Charlie,35)."""
+    from igloo_b200.physical_planner import Filter, MemoryCatalog, PhysicalPlanner, Projection, TableScan
+    cat = MemoryCatalog()
+    cat.register_table("users", users())
+    for fuse in (True, False):
+        planner = PhysicalPlanner(cat, ctx, fuse=fuse)
+        for case in GOLD["cases"]:
+            plan = planner.create_physical_plan(Projection(Filter(TableScan("users", [1, 2]), col("age") > case["threshold"]),
+                                                           [col("name"), col("age")]))
+            t, _ = collect(plan)
+            assert t.schema.names == ["name", "age"] and t.schema.field("age").type == pa.int32()
+            rows = sorted(zip(t.column("name").to_pylist(), t.column("age").to_pylist()), key=lambda x: x[1])
+            assert [list(r) for r in rows] == case["expect_sorted_by_age"]
+
+
+def test_filter_exec_streams_and_drops_empty_chunks(ctx):
+    from igloo_b200.operators import FilterExec, MemoryScanExec
+    n = 20_000
+    rng = np.random.default_rng(0)
+    tbl = pa.table({"a": np.arange(n, dtype=np.int32), "s": pa.array([f"row{i % 97}" * (i % 3) for i in range(n)]),
+                    "x": pa.array(rng.random(n), pa.float64(), mask=rng.random(n) < 0.1)},
+                   schema=pa.schema([pa.field("a", pa.int32(), False), pa.field("s", pa.string(), False), pa.field("x", pa.float64(), True)]))
+    f = FilterExec(MemoryScanExec(tbl), (col("a") < 6000) | (col("a") >= 19_000), ctx)
+    got, batches = collect(f)
+    keep = (np.arange(n) < 6000) | (np.arange(n) >= 19_000)
+    assert got.schema == tbl.schema
+    assert got.equals(tbl.filter(pa.array(keep)))             # order preserved, strings gathered, nulls kept
+    assert all(b.num_rows > 0 for b in batches) and len(batches) == 3   # chunks 0,1 and 4 survive; 2,3 are dropped
+    none, nb = collect(FilterExec(MemoryScanExec(tbl), col("a") < 0, ctx))
+    assert none.num_rows == 0 and nb == []
+    # oracle agreement on the numeric + string columns
+    o = orc.Table.scan(arrow_to_columns(tbl))
+    fields = [Field("a", T_I32), Field("s", 5), Field("x", T_F64, True)]
+    want = columns_to_arrow(o.filter(lower((col("a") < 6000) | (col("a") >= 19_000), fields)[0]).columns())
+    assert_same_multiset(got.cast(want.schema), want)
+
+
+def test_projection_exec_matches_oracle_and_pair_equals_fused(ctx):
+    from igloo_b200.operators import FilterExec, FusedFilterProjectExec, MemoryScanExec, ProjectionExec
+    n = 50_000
+    a = orc.gen_i32_uniform(0x16100002, 0, 0, n, 1000); b = orc.gen_i32_uniform(0x16100002, 1, 0, n, 1 << 31); x = orc.gen_f64_unit(0x16100002, 2, 0, n)
+    sch = pa.schema([pa.field("a", pa.int32(), False), pa.field("b", pa.int32(), False), pa.field("x", pa.float64(), False)])
+    tbl = pa.table({"a": a, "b": b, "x": x}, schema=sch)
+    exprs = [((col("b") + col("a")).alias("s"), "s"), ((col("x") * 1.5 + 0.25).alias("y"), "y")]
+    out_schema = pa.schema([pa.field("s", pa.int32(), False), pa.field("y", pa.float64(), False)])
+    pair = ProjectionExec(FilterExec(MemoryScanExec(tbl), col("a") < 250, ctx), exprs, out_schema, ctx)
+    fused = FusedFilterProjectExec(MemoryScanExec(tbl), col("a") < 250, exprs, out_schema, ctx)
+    t1, _ = collect(pair)
+    t2, _ = collect(fused)
+    assert t1.equals(t2)
+    m = a < 250
+    assert np.array_equal(t1.column("s").to_numpy(), (b[m].astype(np.int64) + a[m]).astype(np.int32))
+    assert np.array_equal(t1.column("y").to_numpy(), x[m] * 1.5 + 0.25)
+    # SELECT 42 AS answer (lib.rs:160-183): literal projection over a one-row relation
+    one = pa.table({"d": pa.array([0], pa.int32())})
+    t, _ = collect(ProjectionExec(MemoryScanExec(one), [(lit(42).alias("answer"), "answer")], pa.schema([pa.field("answer", pa.int64(), False)]), ctx))
+    assert t.column("answer").to_pylist() == [42]
+
+
+def test_stream_error_is_surfaced(ctx):
+    from igloo_b200._lib import IglooCudaError
+    from igloo_b200.operators import MemoryScanExec, ProjectionExec
+    tbl = pa.table({"a": pa.array([1, 2, 0, 4], pa.int32())}, schema=pa.schema([pa.field("a", pa.int32(), False)]))
+    p = ProjectionExec(MemoryScanExec(tbl), [((lit(10, T_I32) / col("a")).alias("q"), "q")], pa.schema([pa.field("q", pa.int32(), False)]), ctx)
+    with pytest.raises(IglooCudaError) as e:
+        collect(p)
+    assert e.value.code == -6 and "Divide by zero" in e.value.message
+
+
+@pytest.mark.parametrize("jt", [0, 1])
+def test_hash_join_exec_streaming(ctx, jt):
+    from igloo_b200.operators import HashJoinExec, MemoryScanExec
+    rng = np.random.default_rng(5)
+    nb, nl = 9_000, 30_000
+    right = pa.table({"k": rng.permutation(20_000)[:nb].astype(np.int64), "v": rng.integers(0, 1 << 40, nb)},
+                     schema=pa.schema([pa.field("k", pa.int64(), False), pa.field("v", pa.int64(), False)]))
+    left = pa.table({"k": rng.integers(0, 20_000, nl), "w": rng.random(nl)},
+                    schema=pa.schema([pa.field("k", pa.int64(), False), pa.field("w", pa.float64(), False)]))
+    j = HashJoinExec(MemoryScanExec(left), MemoryScanExec(right), [col("k")], [col("k")], jt, ctx)
+    assert j.schema().names == ["k", "w", "right_k", "v"]
+    got, _ = collect(j)
+    L = orc.Table.scan(arrow_to_columns(left)); R = orc.Table.scan(arrow_to_columns(right))
+    key = lower(col("k"), [Field("k", T_I64)])[0]
+    want = columns_to_arrow(L.hash_join(R, [key], [key], jt, 1, 2).columns())
+    assert_same_multiset(got.cast(pa.schema([pa.field(f.name, f.type, True) for f in got.schema])),
+                         want.cast(pa.schema([pa.field(f.name, f.type, True) for f in want.schema])))
+
+
+def test_hash_join_duplicates_and_nullable_columns_streaming(ctx):
+    from igloo_b200.operators import HashJoinExec, MemoryScanExec
+    rng = np.random.default_rng(6)
+    nb, nl = 8_192, 12_000
+    right = pa.table({"k": pa.array(rng.integers(0, 500, nb), pa.int64(), mask=rng.random(nb) < 0.01),
+                      "v": pa.array(rng.integers(0, 99, nb), pa.int32(), mask=rng.random(nb) < 0.3)})
+    left = pa.table({"k": pa.array(rng.integers(0, 600, nl), pa.int64(), mask=rng.random(nl) < 0.01), "w": pa.array(rng.random(nl))})
+    for jt in (0, 1):
+        got, _ = collect(HashJoinExec(MemoryScanExec(left), MemoryScanExec(right), [col("k")], [col("k")], jt, ctx))
+        L = orc.Table.scan(arrow_to_columns(left)); R = orc.Table.scan(arrow_to_columns(right))
+        key = lower(col("k"), [Field("k", T_I64, True)])[0]
+        want = columns_to_arrow(L.hash_join(R, [key], [key], jt, 1, 2).columns())
+        assert_same_multiset(got.cast(pa.schema([pa.field(f.name, f.type, True) for f in got.schema])),
+                             want.cast(pa.schema([pa.field(f.name, f.type, True) for f in want.schema])))
+
+
+def test_planner_join_of_filtered_scans(ctx):
+    from igloo_b200.physical_planner import Filter, Join, MemoryCatalog, PhysicalPlanner, Projection, TableScan
+    rng = np.random.default_rng(8)
+    orders = pa.table({"o_orderkey": np.arange(1, 5001, dtype=np.int64), "o_total": rng.random(5000)})
+    items = pa.table({"l_orderkey": rng.integers(1, 6000, 40_000), "l_qty": rng.integers(1, 50, 40_000).astype(np.int32)})
+    cat = MemoryCatalog(); cat.register_table("orders", orders); cat.register_table("lineitem", items)
+    plan = PhysicalPlanner(cat, ctx).create_physical_plan(
+        Join(Filter(TableScan("lineitem"), col("l_qty") > 10), TableScan("orders"), [(col("l_orderkey"), col("o_orderkey"))], "Inner"))
+    got, _ = collect(plan)
+    m = (items.column("l_qty").to_numpy() > 10) & (items.column("l_orderkey").to_numpy() <= 5000)
+    assert got.num_rows == int(m.sum()) and got.schema.names == ["l_orderkey", "l_qty", "o_orderkey", "o_total"]
+    assert np.array_equal(np.sort(got.column("l_orderkey").to_numpy()), np.sort(items.column("l_orderkey").to_numpy()[m]))
+    assert np.array_equal(got.column("l_orderkey").to_numpy(), got.column("o_orderkey").to_numpy())
