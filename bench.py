@@ -190,7 +190,7 @@ def run_ours(args):
 
     if world > 1:
         from igloo_b200.shuffle import PartitionedJoin
-        pj = PartitionedJoin(ctx, rank, world, lf, rf, 0, 0)
+        pj = PartitionedJoin(ctx, rank, world, lf, rf, 0, 0, mode=args.exchange)
         # row-range shard of both sides, as after a parallel scan
         b0, b1 = nb_total * rank // world, nb_total * (rank + 1) // world
         p0, p1 = np_total * rank // world, np_total * (rank + 1) // world
@@ -258,7 +258,7 @@ def run_ours(args):
             "vs_baseline": None, "dtype": "int64", "data": "synthetic",
             "config": {"workload": f"C3 inner hash join: build 2^{bits} (k,v) x probe {np_total} (k,w), int64 uniform keys, 1 match per probe row",
                        "l2_policy": "inputs (>= 18 GB) and the 4 GiB table are far larger than the 126 MB L2",
-                       "parallelism": f"hash-partitioned over {world} GPU(s)" if world > 1 else "1 GPU"},
+                       "parallelism": f"hash-partitioned over {world} GPUs, exchange={args.exchange}" if world > 1 else "1 GPU"},
             "gpu_launches": launches, "clocks": clocks}
     if rank != 0:
         return
@@ -342,6 +342,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--scale", type=int, default=1, help="divide the workload by this power of two (development only)")
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
+                    help="multi-GPU row exchange: partition kernel storing into peer HBM over NVLink (p2p) or NCCL all-to-all")
     ap.add_argument("--skip-fp", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--ref-build-bits", type=int, default=21)
