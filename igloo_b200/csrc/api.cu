@@ -87,7 +87,7 @@ void pool_free(igl_ctx* ctx, void* p) {
     if (it == ctx->live.end()) return;
     size_t b = it->second;
     ctx->live.erase(it);
-    if (b > (1ull << 30)) {  // do not cache multi-GB blocks
+    if (b > (40ull << 30)) {  // very large blocks go straight back (cached blocks are released on OOM anyway)
         ctx->pool_bytes -= b;
         cudaFree(p);
         return;

@@ -81,6 +81,14 @@ __device__ __forceinline__ ulonglong2 ld_nc_u64x2(const void* p) {
     return v;
 }
 
+// One 32-byte sector (a two-slot bucket of the join table) in a single request.
+__device__ __forceinline__ ulonglong4 ld_nc_u64x4(const void* p) {
+    ulonglong4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u64 {%0, %1, %2, %3}, [%4];"
+                 : "=l"(v.x), "=l"(v.y), "=l"(v.z), "=l"(v.w) : "l"(p));
+    return v;
+}
+
 // ---- hashing ------------------------------------------------------------------
 __host__ __device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
     x += 0x9E3779B97F4A7C15ull;

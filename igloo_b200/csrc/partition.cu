@@ -114,6 +114,193 @@ __global__ void __launch_bounds__(kPartThreads) partition_scatter_kernel(const _
     }
 }
 
+// ---------------------------------------------------------------------------
+// High-fanout radix partition (up to 1024 parts) by the TOP bits of mix64(key) —
+// the same bits the join table is indexed with, so rows sorted by partition walk
+// the table region by region and every region (16 MB) stays L2-resident while
+// it is built and probed.  Each random 16-byte table access otherwise costs about
+// a 128-byte line of HBM traffic (profiles/README.md).
+//
+// Pass 1: per-CTA shared-memory histogram -> global counts -> one-block scan.
+// Pass 2: every tile is counting-sorted by partition in shared memory first, so
+// the write-out stores runs of consecutive rows per partition (coalesced) instead
+// of one scattered store per row.
+// ---------------------------------------------------------------------------
+constexpr int kRadixMaxParts = 1024;
+constexpr int kRadixThreads = 512;
+constexpr int kRadixRowsPerThread = 8;
+constexpr int kRadixTile = kRadixThreads * kRadixRowsPerThread;   // 4096 rows
+
+__device__ __forceinline__ int radix_part(const void* keys, int type, long long i, int log2_parts) {
+    const uint64_t raw = type == IGL_T_I32 ? (uint64_t)(uint32_t)((const int32_t*)keys)[i] : ((const uint64_t*)keys)[i];
+    return (int)(mix64(part_canon(type, raw)) >> (64 - log2_parts));
+}
+
+__global__ void __launch_bounds__(kRadixThreads) radix_hist_kernel(const void* __restrict__ keys, int type, long long n,
+                                                                   int log2_parts, unsigned long long* hist) {
+    __shared__ unsigned int s_hist[kRadixMaxParts];
+    const int nparts = 1 << log2_parts;
+    for (int p = threadIdx.x; p < nparts; p += blockDim.x) s_hist[p] = 0;
+    __syncthreads();
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+        atomicAdd(&s_hist[radix_part(keys, type, i, log2_parts)], 1u);
+    __syncthreads();
+    for (int p = threadIdx.x; p < nparts; p += blockDim.x)
+        if (s_hist[p]) atomicAdd(&hist[p], (unsigned long long)s_hist[p]);
+}
+
+// offsets[p] = sum of hist[0..p) ; offsets[nparts] = total ; cursor[] zeroed.
+__global__ void radix_scan_kernel(const unsigned long long* hist, unsigned long long* offsets, unsigned long long* cursor, int nparts) {
+    __shared__ unsigned long long s[kRadixMaxParts];
+    const int t = threadIdx.x;
+    unsigned long long v = t < nparts ? hist[t] : 0;
+    s[t] = v;
+    __syncthreads();
+    for (int o = 1; o < kRadixMaxParts; o <<= 1) {
+        unsigned long long add = t >= o ? s[t - o] : 0;
+        __syncthreads();
+        s[t] += add;
+        __syncthreads();
+    }
+    if (t < nparts) { offsets[t] = s[t] - v; cursor[t] = 0; }
+    if (t == nparts - 1) offsets[nparts] = s[t];
+}
+
+struct RadixParams {
+    const uint8_t* src[kPartMaxCols];
+    uint8_t* dst[kPartMaxCols];
+    uint8_t shift[kPartMaxCols];
+    uint32_t stage_off[kPartMaxCols];   // byte offset of each column's staging area in dynamic shared memory
+    int ncols, key_col, key_type, log2_parts;
+    long long n;
+    const unsigned long long* offsets;  // [nparts + 1]
+    unsigned long long* cursor;         // [nparts]
+};
+
+__global__ void __launch_bounds__(kRadixThreads, 2) radix_scatter_kernel(const __grid_constant__ RadixParams P) {
+    extern __shared__ __align__(16) uint8_t stage[];
+    __shared__ unsigned int s_cnt[kRadixMaxParts];     // count, then exclusive start
+    __shared__ unsigned long long s_gbase[kRadixMaxParts];
+    __shared__ unsigned short s_part[kRadixTile];       // partition of each staged slot
+    __shared__ unsigned int s_warp_tot[kRadixThreads / 32];
+    const int nparts = 1 << P.log2_parts;
+    const long long ntiles = (P.n + kRadixTile - 1) / kRadixTile;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        for (int p = threadIdx.x; p < nparts; p += kRadixThreads) s_cnt[p] = 0;
+        __syncthreads();
+        const long long row0 = tile * kRadixTile;
+        const int rows = (int)min((long long)kRadixTile, P.n - row0);
+        int part[kRadixRowsPerThread];
+        unsigned int rank[kRadixRowsPerThread];
+#pragma unroll
+        for (int r = 0; r < kRadixRowsPerThread; ++r) {
+            const int li = r * kRadixThreads + threadIdx.x;
+            part[r] = -1;
+            if (li < rows) {
+                part[r] = radix_part(P.src[P.key_col], P.key_type, row0 + li, P.log2_parts);
+                rank[r] = atomicAdd(&s_cnt[part[r]], 1u);
+            }
+        }
+        __syncthreads();
+        // exclusive scan of s_cnt[0..nparts) by the CTA (nparts <= 1024 = 2 per thread) + global reservation
+        {
+            const int i0 = threadIdx.x * 2;
+            const unsigned int c0 = i0 < nparts ? s_cnt[i0] : 0, c1 = i0 + 1 < nparts ? s_cnt[i0 + 1] : 0;
+            unsigned int inc = c0 + c1;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned int t = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += t;
+            }
+            if (lane == 31) s_warp_tot[warp] = inc;
+            __syncthreads();
+            unsigned int wpre = 0;
+            for (int w = 0; w < warp; ++w) wpre += s_warp_tot[w];
+            const unsigned int ex = wpre + inc - (c0 + c1);
+            if (i0 < nparts) {
+                s_cnt[i0] = ex;
+                s_gbase[i0] = c0 ? P.offsets[i0] + atomicAdd(&P.cursor[i0], (unsigned long long)c0) : 0ull;
+            }
+            if (i0 + 1 < nparts) {
+                s_cnt[i0 + 1] = ex + c0;
+                s_gbase[i0 + 1] = c1 ? P.offsets[i0 + 1] + atomicAdd(&P.cursor[i0 + 1], (unsigned long long)c1) : 0ull;
+            }
+        }
+        __syncthreads();
+        // stage: rows land grouped by partition
+#pragma unroll
+        for (int r = 0; r < kRadixRowsPerThread; ++r) {
+            if (part[r] < 0) continue;
+            const long long i = row0 + r * kRadixThreads + threadIdx.x;
+            const unsigned int slot = s_cnt[part[r]] + rank[r];
+            s_part[slot] = (unsigned short)part[r];
+            for (int c = 0; c < P.ncols; ++c) {
+                if (P.shift[c] == 2) reinterpret_cast<uint32_t*>(stage + P.stage_off[c])[slot] = reinterpret_cast<const uint32_t*>(P.src[c])[i];
+                else reinterpret_cast<uint64_t*>(stage + P.stage_off[c])[slot] = reinterpret_cast<const uint64_t*>(P.src[c])[i];
+            }
+        }
+        __syncthreads();
+        // write-out: consecutive threads -> consecutive slots -> runs of consecutive destination rows
+        for (int slot = threadIdx.x; slot < rows; slot += kRadixThreads) {
+            const int p = s_part[slot];
+            const unsigned long long d = s_gbase[p] + (slot - s_cnt[p]);
+            for (int c = 0; c < P.ncols; ++c) {
+                if (P.shift[c] == 2) reinterpret_cast<uint32_t*>(P.dst[c])[d] = reinterpret_cast<const uint32_t*>(stage + P.stage_off[c])[slot];
+                else reinterpret_cast<uint64_t*>(P.dst[c])[d] = reinterpret_cast<const uint64_t*>(stage + P.stage_off[c])[slot];
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// Partitions `cols` (no validity) into dst[c] (capacity nrows each) by the top
+// log2_parts bits of the join hash.  `scratch` holds 3 * (nparts + 1) u64.
+int32_t radix_partition(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int key_col, long long nrows, int log2_parts,
+                        void* const* dst, void* scratch, cudaStream_t st) {
+    if (ncols < 1 || ncols > kPartMaxCols || log2_parts < 1 || (1 << log2_parts) > kRadixMaxParts)
+        return fail(IGL_ERR_INVALID_ARG, "radix_partition: bad arguments");
+    const int nparts = 1 << log2_parts;
+    unsigned long long* hist = (unsigned long long*)scratch;
+    unsigned long long* offsets = hist + (nparts + 1);
+    unsigned long long* cursor = offsets + (nparts + 1);
+    IGL_CUDA_OK(cudaMemsetAsync(hist, 0, sizeof(unsigned long long) * (nparts + 1), st));
+    RadixParams P{};
+    P.ncols = ncols; P.key_col = key_col; P.key_type = cols[key_col].type; P.log2_parts = log2_parts; P.n = nrows;
+    P.offsets = offsets; P.cursor = cursor;
+    uint32_t off = 0;
+    for (int c = 0; c < ncols; ++c) {
+        const int t = cols[c].type;
+        if (t != IGL_T_I32 && t != IGL_T_I64 && t != IGL_T_F64) return fail(IGL_ERR_UNSUPPORTED, "radix_partition: fixed-width columns only");
+        if (cols[c].validity) return fail(IGL_ERR_UNSUPPORTED, "radix_partition: nullable columns are not partitioned");
+        P.src[c] = (const uint8_t*)cols[c].data; P.dst[c] = (uint8_t*)dst[c];
+        P.shift[c] = t == IGL_T_I32 ? 2 : 3;
+        P.stage_off[c] = off;
+        off += (uint32_t)kRadixTile << P.shift[c];
+    }
+    if (off > (96u << 10)) return fail(IGL_ERR_UNSUPPORTED, "radix_partition: row too wide (%u bytes of staging)", off);
+    const int grid = ctx->sm_count * 2;
+    if (nrows > 0) {
+        radix_hist_kernel<<<grid, kRadixThreads, 0, st>>>(cols[key_col].data, P.key_type, nrows, log2_parts, hist);
+        IGL_CUDA_OK(cudaGetLastError());
+    }
+    radix_scan_kernel<<<1, kRadixMaxParts, 0, st>>>(hist, offsets, cursor, nparts);
+    IGL_CUDA_OK(cudaGetLastError());
+    ctx->launches += 2;
+    if (nrows > 0) {
+        static bool attr_set = false;
+        if (!attr_set) {
+            IGL_CUDA_OK(cudaFuncSetAttribute((const void*)radix_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 << 10));
+            attr_set = true;
+        }
+        radix_scatter_kernel<<<grid, kRadixThreads, off, st>>>(P);
+        IGL_CUDA_OK(cudaGetLastError());
+        ctx->launches++;
+    }
+    return IGL_OK;
+}
+
 }  // namespace igl
 
 using namespace igl;

@@ -85,3 +85,13 @@ def test_expr_compile_type_rules_without_device(lib):
     assert rc == -1
     rc, _ = compile_(bytes([0x01, 0, 0, 0x01, 0, 0]))
     assert rc == -1 and b"exactly one" in lib.igl_last_error()
+
+
+def test_cpp_host_mirror_compiles_and_links_against_the_abi(lib, tmp_path):
+    """igloo_b200/host/igloo_operators.hpp (FilterExec / ProjectionExec / HashJoinExec
+    over the C ABI) must type-check and link against libigloo_cuda.so."""
+    import subprocess
+    exe = tmp_path / "host_mirror_check"
+    subprocess.check_call(["g++", "-std=c++17", "-Wall", "-Werror", "-o", str(exe), os.path.join(ROOT, "tests", "host_mirror_check.cpp"),
+                           "-L", os.path.join(ROOT, "igloo_b200"), "-ligloo_cuda", f"-Wl,-rpath,{os.path.join(ROOT, 'igloo_b200')}"])
+    subprocess.check_call([str(exe)])

@@ -173,10 +173,12 @@ def test_full_scale_property_c3_digest(ctx):
     assert n == nprobe
     expect_v = ctx.gen(5, seed, 1, 0, nprobe, bits=bits, keys=lk)     # v of the build row holding each probe key
     assert ctx.digest(out, n) == ctx.digest([lk, lw, lk, expect_v], nprobe)
-    # oracle spot check on the first tile-aligned 200k probe rows (order is preserved for unique builds)
-    m = 200_000
-    hk = orc.gen_i64_uniform(seed, 2, 0, m, nb)
-    assert np.array_equal(out[0].data[:m].cpu().numpy(), hk)
-    inv = np.array([orc.lib().orc_perm_pow2_inv(int(k), bits) for k in hk[:2000]], dtype=np.uint64)
+    # large build sides are radix-partitioned, so the output is in partition order:
+    # spot-check rows wherever they landed — (k, w) must be a generated probe row's
+    # pair is covered by the digest; here v and right_k are recomputed from k alone
+    m = 4096
+    hk = out[0].data[:m].cpu().numpy()
+    assert np.array_equal(out[2].data[:m].cpu().numpy(), hk)                 # right_k == k
+    inv = np.array([orc.lib().orc_perm_pow2_inv(int(k), bits) for k in hk], dtype=np.uint64)
     hv = np.array([orc.gen_i64_uniform(seed, 1, int(i), 1)[0] for i in inv], dtype=np.int64)
-    assert np.array_equal(out[3].data[:2000].cpu().numpy(), hv)
+    assert np.array_equal(out[3].data[:m].cpu().numpy(), hv)
