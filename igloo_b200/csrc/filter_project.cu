@@ -89,207 +89,301 @@ __device__ __forceinline__ V<R> load_col(const FpParams& P, int slot, const uint
     return x;
 }
 
+// ---- one IR instruction on R rows ---------------------------------------------
+// Everything that is uniform across rows (operator, type, operand kinds) is
+// resolved ONCE per instruction, outside the per-row loops: the type selects a
+// template instantiation, comparison operators become three uniform masks, and
+// the operand kinds select a `step` instantiation so operands are read straight
+// into the registers the operation consumes (no struct copies, no per-row
+// switches).  Per-row code is then the arithmetic itself.
+template <int TY> struct TypeTag {};
+
+template <int R, int TY>
+__device__ __forceinline__ void cmp_rows(int op, const uint64_t (&a)[R], const uint64_t (&b)[R], uint64_t (&d)[R]) {
+    const bool m_lt = op == IGL_OP_LT || op == IGL_OP_LE || op == IGL_OP_NE;
+    const bool m_eq = op == IGL_OP_EQ || op == IGL_OP_LE || op == IGL_OP_GE;
+    const bool m_gt = op == IGL_OP_GT || op == IGL_OP_GE || op == IGL_OP_NE;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        bool lt, eq;
+        if (TY == IGL_T_I32) { const int32_t x = (int32_t)a[r], y = (int32_t)b[r]; lt = x < y; eq = x == y; }
+        else if (TY == IGL_T_F64) { const int64_t x = total_order_key(a[r]), y = total_order_key(b[r]); lt = x < y; eq = x == y; }
+        else if (TY == IGL_T_BOOL) { const uint32_t x = (uint32_t)a[r] & 1u, y = (uint32_t)b[r] & 1u; lt = x < y; eq = x == y; }
+        else { const int64_t x = (int64_t)a[r], y = (int64_t)b[r]; lt = x < y; eq = x == y; }
+        d[r] = ((lt && m_lt) || (eq && m_eq) || (!lt && !eq && m_gt)) ? 1 : 0;
+    }
+}
+
+template <int R, int TY>
+__device__ __forceinline__ void arith_rows(int op, const uint64_t (&a)[R], const uint64_t (&b)[R], uint64_t (&d)[R]) {
+    if (TY == IGL_T_F64) {
+        // explicit round-to-nearest intrinsics: never contracted into an FMA
+        if (op == IGL_OP_ADD) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) d[r] = (uint64_t)__double_as_longlong(__dadd_rn(__longlong_as_double((long long)a[r]), __longlong_as_double((long long)b[r])));
+        } else if (op == IGL_OP_SUB) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) d[r] = (uint64_t)__double_as_longlong(__dsub_rn(__longlong_as_double((long long)a[r]), __longlong_as_double((long long)b[r])));
+        } else {
+#pragma unroll
+            for (int r = 0; r < R; ++r) d[r] = (uint64_t)__double_as_longlong(__dmul_rn(__longlong_as_double((long long)a[r]), __longlong_as_double((long long)b[r])));
+        }
+    } else if (TY == IGL_T_I32) {   // two's-complement wrap; I32 lives in the low 32 bits
+        if (op == IGL_OP_ADD) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) d[r] = (uint32_t)a[r] + (uint32_t)b[r];
+        } else if (op == IGL_OP_SUB) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) d[r] = (uint32_t)a[r] - (uint32_t)b[r];
+        } else {
+#pragma unroll
+            for (int r = 0; r < R; ++r) d[r] = (uint32_t)a[r] * (uint32_t)b[r];
+        }
+    } else {
+        if (op == IGL_OP_ADD) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) d[r] = a[r] + b[r];
+        } else if (op == IGL_OP_SUB) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) d[r] = a[r] - b[r];
+        } else {
+#pragma unroll
+            for (int r = 0; r < R; ++r) d[r] = a[r] * b[r];
+        }
+    }
+}
+
+// The rare operators (division, casts, boolean logic, null tests, negation).
 template <int R, bool HAS_NULLS>
-__device__ __forceinline__ V<R> exec_op(const Instr& in, const V<R>& a, const V<R>& b, uint32_t inrange, unsigned int* err_flags) {
-    V<R> d;
-    d.ok = HAS_NULLS ? (a.ok & b.ok) : FullMask<R>::value;
+__device__ __noinline__ void slow_rows(const Instr& in, const uint64_t (&a)[R], uint32_t aok, const uint64_t (&b)[R], uint32_t bok,
+                                       uint32_t inrange, unsigned int* err_flags, uint64_t (&d)[R], uint32_t& dok) {
     const int op = in.op, ty = in.type;
+    constexpr uint32_t FULL = FullMask<R>::value;
+    dok = HAS_NULLS ? (aok & bok) : FULL;
     switch (op) {
-        case IOP_MOV:
-            d = a;
-            break;
-        case IGL_OP_EQ: case IGL_OP_NE: case IGL_OP_LT: case IGL_OP_LE: case IGL_OP_GT: case IGL_OP_GE: {
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                int64_t x, y;
-                if (ty == IGL_T_I32) { x = (int32_t)a.v[r]; y = (int32_t)b.v[r]; }
-                else if (ty == IGL_T_F64) { x = total_order_key(a.v[r]); y = total_order_key(b.v[r]); }
-                else if (ty == IGL_T_BOOL) { x = (int64_t)(a.v[r] & 1); y = (int64_t)(b.v[r] & 1); }
-                else { x = (int64_t)a.v[r]; y = (int64_t)b.v[r]; }
-                bool c;
-                switch (op) {
-                    case IGL_OP_EQ: c = x == y; break;
-                    case IGL_OP_NE: c = x != y; break;
-                    case IGL_OP_LT: c = x < y; break;
-                    case IGL_OP_LE: c = x <= y; break;
-                    case IGL_OP_GT: c = x > y; break;
-                    default: c = x >= y; break;
-                }
-                d.v[r] = c ? 1 : 0;
-            }
-            break;
-        }
-        case IGL_OP_ADD: case IGL_OP_SUB: case IGL_OP_MUL: {
-            if (ty == IGL_T_F64) {
-#pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    double x = __longlong_as_double((long long)a.v[r]), y = __longlong_as_double((long long)b.v[r]);
-                    // explicit round-to-nearest intrinsics: never contracted into an FMA
-                    double z = op == IGL_OP_ADD ? __dadd_rn(x, y) : op == IGL_OP_SUB ? __dsub_rn(x, y) : __dmul_rn(x, y);
-                    d.v[r] = (uint64_t)__double_as_longlong(z);
-                }
-            } else {  // two's-complement wrap; I32 lives in the low 32 bits
-#pragma unroll
-                for (int r = 0; r < R; ++r)
-                    d.v[r] = op == IGL_OP_ADD ? a.v[r] + b.v[r] : op == IGL_OP_SUB ? a.v[r] - b.v[r]
-                             : (ty == IGL_T_I32 ? (uint64_t)((uint32_t)a.v[r] * (uint32_t)b.v[r]) : a.v[r] * b.v[r]);
-            }
-            break;
-        }
         case IGL_OP_DIV: case IGL_OP_MOD: {
             if (ty == IGL_T_F64) {
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
-                    double x = __longlong_as_double((long long)a.v[r]), y = __longlong_as_double((long long)b.v[r]);
-                    double z = op == IGL_OP_DIV ? __ddiv_rn(x, y) : fmod(x, y);
-                    d.v[r] = (uint64_t)__double_as_longlong(z);
+                    const double x = __longlong_as_double((long long)a[r]), y = __longlong_as_double((long long)b[r]);
+                    d[r] = (uint64_t)__double_as_longlong(op == IGL_OP_DIV ? __ddiv_rn(x, y) : fmod(x, y));
                 }
             } else {
                 uint32_t ef = 0;
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
-                    int64_t x = ty == IGL_T_I32 ? (int64_t)(int32_t)a.v[r] : (int64_t)a.v[r];
-                    int64_t y = ty == IGL_T_I32 ? (int64_t)(int32_t)b.v[r] : (int64_t)b.v[r];
-                    const bool live = ((d.ok & inrange) >> r) & 1;  // arrow evaluates valid slots only; rows past the end do not exist
+                    const int64_t x = ty == IGL_T_I32 ? (int64_t)(int32_t)a[r] : (int64_t)a[r];
+                    const int64_t y = ty == IGL_T_I32 ? (int64_t)(int32_t)b[r] : (int64_t)b[r];
+                    const bool live = ((dok & inrange) >> r) & 1;  // arrow evaluates valid slots only; rows past the end do not exist
                     const int64_t mn = ty == IGL_T_I32 ? (int64_t)INT32_MIN : INT64_MIN;
                     int64_t z = 0;
                     if (y == 0) { if (live) ef |= ERRF_DIV_ZERO; }
                     else if (y == -1) {
                         if (op == IGL_OP_DIV) { if (x == mn) { if (live) ef |= ERRF_OVERFLOW; } else z = -x; }
                     } else z = op == IGL_OP_DIV ? x / y : x % y;
-                    d.v[r] = (uint64_t)z;
+                    d[r] = (uint64_t)z;
                 }
                 if (ef) atomicOr(err_flags, ef);
             }
             break;
         }
-        case IGL_OP_NEG: {
-            d.ok = a.ok;
+        case IGL_OP_NEG:
+            dok = aok;
 #pragma unroll
-            for (int r = 0; r < R; ++r)
-                d.v[r] = ty == IGL_T_F64 ? (a.v[r] ^ 0x8000000000000000ull) : (0ull - a.v[r]);
+            for (int r = 0; r < R; ++r) d[r] = ty == IGL_T_F64 ? (a[r] ^ 0x8000000000000000ull) : (0ull - a[r]);
             break;
-        }
         case IGL_OP_AND: case IGL_OP_OR: {  // Kleene
             uint32_t ok = 0;
 #pragma unroll
             for (int r = 0; r < R; ++r) {
-                const bool av = (a.ok >> r) & 1, bv = (b.ok >> r) & 1;
-                const bool x = av && (a.v[r] & 1), y = bv && (b.v[r] & 1);
+                const bool av = (aok >> r) & 1, bv = (bok >> r) & 1;
+                const bool x = av && (a[r] & 1), y = bv && (b[r] & 1);
                 bool val, known;
                 if (op == IGL_OP_AND) { const bool kf = (av && !x) || (bv && !y); known = kf || (av && bv); val = !kf && av && bv; }
                 else { const bool kt = x || y; known = kt || (av && bv); val = kt; }
-                d.v[r] = val ? 1 : 0;
+                d[r] = val ? 1 : 0;
                 ok |= (known ? 1u : 0u) << r;
             }
-            d.ok = HAS_NULLS ? ok : FullMask<R>::value;
+            dok = HAS_NULLS ? ok : FULL;
             break;
         }
         case IGL_OP_NOT:
-            d.ok = a.ok;
+            dok = aok;
 #pragma unroll
-            for (int r = 0; r < R; ++r) d.v[r] = (a.v[r] & 1) ^ 1;
+            for (int r = 0; r < R; ++r) d[r] = (a[r] & 1) ^ 1;
             break;
         case IGL_OP_IS_NULL: case IGL_OP_IS_NOT_NULL:
-            d.ok = FullMask<R>::value;
+            dok = FULL;
 #pragma unroll
-            for (int r = 0; r < R; ++r) d.v[r] = (((a.ok >> r) & 1) != 0) == (op == IGL_OP_IS_NOT_NULL) ? 1 : 0;
+            for (int r = 0; r < R; ++r) d[r] = (((aok >> r) & 1) != 0) == (op == IGL_OP_IS_NOT_NULL) ? 1 : 0;
             break;
         case IGL_OP_CAST: {
-            d.ok = a.ok;
+            dok = aok;
             const int to = in.aux;
             uint32_t ef = 0;
 #pragma unroll
             for (int r = 0; r < R; ++r) {
-                const bool live = ((a.ok & inrange) >> r) & 1;
+                const bool live = ((aok & inrange) >> r) & 1;
                 uint64_t z = 0;
-                if (ty == IGL_T_I32 && to == IGL_T_I64) z = (uint64_t)(int64_t)(int32_t)a.v[r];
-                else if (ty == IGL_T_I32 && to == IGL_T_F64) z = (uint64_t)__double_as_longlong((double)(int32_t)a.v[r]);
-                else if (ty == IGL_T_I64 && to == IGL_T_F64) z = (uint64_t)__double_as_longlong(__ll2double_rn((long long)a.v[r]));
+                if (ty == IGL_T_I32 && to == IGL_T_I64) z = (uint64_t)(int64_t)(int32_t)a[r];
+                else if (ty == IGL_T_I32 && to == IGL_T_F64) z = (uint64_t)__double_as_longlong((double)(int32_t)a[r]);
+                else if (ty == IGL_T_I64 && to == IGL_T_F64) z = (uint64_t)__double_as_longlong(__ll2double_rn((long long)a[r]));
                 else if (ty == IGL_T_I64 && to == IGL_T_I32) {
-                    int64_t x = (int64_t)a.v[r];
+                    const int64_t x = (int64_t)a[r];
                     if (x < INT32_MIN || x > INT32_MAX) { if (live) ef |= ERRF_CAST; } else z = (uint64_t)(uint32_t)(int32_t)x;
                 } else if (ty == IGL_T_F64 && to == IGL_T_I32) {
-                    double t = trunc(__longlong_as_double((long long)a.v[r]));
+                    const double t = trunc(__longlong_as_double((long long)a[r]));
                     if (!(t >= -2147483648.0 && t <= 2147483647.0)) { if (live) ef |= ERRF_CAST; } else z = (uint64_t)(uint32_t)(int32_t)t;
                 } else if (ty == IGL_T_F64 && to == IGL_T_I64) {
-                    double t = trunc(__longlong_as_double((long long)a.v[r]));
+                    const double t = trunc(__longlong_as_double((long long)a[r]));
                     if (!(t >= -9223372036854775808.0 && t < 9223372036854775808.0)) { if (live) ef |= ERRF_CAST; } else z = (uint64_t)(int64_t)t;
-                } else z = a.v[r];
-                d.v[r] = z;
+                } else z = a[r];
+                d[r] = z;
             }
             if (ef) atomicOr(err_flags, ef);
             break;
         }
-        default:
-            d = a;
+        default:   // IOP_MOV
+            dok = aok;
+#pragma unroll
+            for (int r = 0; r < R; ++r) d[r] = a[r];
             break;
     }
-    return d;
 }
 
-// Per-warp temporaries: kMaxTmp x 128 rows x 8 bytes, then one validity nibble per lane.
+// Per-warp temporaries: kMaxTmp x 32R rows x 8 bytes, then one validity nibble per lane.
 struct WarpTmp {
-    uint64_t* vals;   // [n_tmp][128]
+    uint64_t* vals;   // [n_tmp][32 * R]
     uint8_t* oks;     // [n_tmp][32]
 };
 
-template <int R, bool HAS_NULLS>
-__device__ __forceinline__ V<R> fetch(const FpParams& P, uint8_t kind, uint8_t idx, uint64_t lit, bool lit_null,
-                                   const uint8_t* stage, int row0, const V<R>& acc, const WarpTmp& tmp, int lane) {
-    V<R> x;
-    if (kind == OPK_ACC) {
-        x = acc;
-    } else if (kind == OPK_COL) {
-        x = load_col<R, HAS_NULLS>(P, idx, stage, row0);
-    } else if (kind == OPK_TMP) {
+// Reads one operand of statically known kind into (v, ok).
+template <int R, bool HAS_NULLS, int KIND>
+__device__ __forceinline__ void read_operand(const FpParams& P, int idx, uint64_t lit, bool lit_null, const uint8_t* stage, int row0,
+                                             const uint64_t (&acc)[R], uint32_t acc_ok, const WarpTmp& tmp, int lane,
+                                             uint64_t (&v)[R], uint32_t& ok) {
+    constexpr uint32_t FULL = FullMask<R>::value;
+    if (KIND == OPK_ACC) {
 #pragma unroll
-        for (int r = 0; r < R; ++r) x.v[r] = tmp.vals[idx * (32 * R) + r * 32 + lane];
-        x.ok = HAS_NULLS ? tmp.oks[idx * 32 + lane] : FullMask<R>::value;
+        for (int r = 0; r < R; ++r) v[r] = acc[r];
+        ok = acc_ok;
+    } else if (KIND == OPK_COL) {
+        const V<R> x = load_col<R, HAS_NULLS>(P, idx, stage, row0);
+#pragma unroll
+        for (int r = 0; r < R; ++r) v[r] = x.v[r];
+        ok = x.ok;
+    } else if (KIND == OPK_TMP) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) v[r] = tmp.vals[idx * (32 * R) + r * 32 + lane];
+        ok = HAS_NULLS ? tmp.oks[idx * 32 + lane] : FULL;
     } else {
-        #pragma unroll
-        for (int r = 0; r < R; ++r) x.v[r] = lit;
-        x.ok = (HAS_NULLS && lit_null) ? 0 : FullMask<R>::value;
+#pragma unroll
+        for (int r = 0; r < R; ++r) v[r] = lit;
+        ok = (HAS_NULLS && lit_null) ? 0 : FULL;
     }
-    return x;
 }
 
-// Runs expression `e` of the fused program on this lane's 4 rows.
+template <int R, bool HAS_NULLS, int AK, int BK>
+__device__ __forceinline__ void step(const FpParams& P, const Instr& in, const uint8_t* stage, int row0, uint32_t inrange,
+                                     const WarpTmp& tmp, int lane, uint64_t (&acc)[R], uint32_t& acc_ok) {
+    constexpr uint32_t FULL = FullMask<R>::value;
+    const bool is_cast = in.op == IGL_OP_CAST;
+    uint64_t a[R], b[R], d[R];
+    uint32_t aok, bok, dok;
+    read_operand<R, HAS_NULLS, AK>(P, in.a_idx, in.a_lit, !is_cast && (in.aux & AUX_A_NULL), stage, row0, acc, acc_ok, tmp, lane, a, aok);
+    if (BK == OPK_NONE) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) b[r] = a[r];
+        bok = aok;
+    } else {
+        read_operand<R, HAS_NULLS, BK>(P, in.b_idx, in.b_lit, !is_cast && (in.aux & AUX_B_NULL), stage, row0, acc, acc_ok, tmp, lane, b, bok);
+    }
+    const int op = in.op, ty = in.type;
+    if (op >= IGL_OP_EQ && op <= IGL_OP_GE) {
+        dok = HAS_NULLS ? (aok & bok) : FULL;
+        if (ty == IGL_T_I32) cmp_rows<R, IGL_T_I32>(op, a, b, d);
+        else if (ty == IGL_T_F64) cmp_rows<R, IGL_T_F64>(op, a, b, d);
+        else if (ty == IGL_T_I64) cmp_rows<R, IGL_T_I64>(op, a, b, d);
+        else cmp_rows<R, IGL_T_BOOL>(op, a, b, d);
+    } else if (op >= IGL_OP_ADD && op <= IGL_OP_MUL) {
+        dok = HAS_NULLS ? (aok & bok) : FULL;
+        if (ty == IGL_T_I32) arith_rows<R, IGL_T_I32>(op, a, b, d);
+        else if (ty == IGL_T_F64) arith_rows<R, IGL_T_F64>(op, a, b, d);
+        else arith_rows<R, IGL_T_I64>(op, a, b, d);
+    } else if (op == IOP_MOV) {
+        dok = aok;
+#pragma unroll
+        for (int r = 0; r < R; ++r) d[r] = a[r];
+    } else {
+        // out-of-line: hand it copies, so a / b / d themselves never need an address
+        uint64_t sa[R], sb[R], sd[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) { sa[r] = a[r]; sb[r] = b[r]; }
+        slow_rows<R, HAS_NULLS>(in, sa, aok, sb, bok, inrange, &P.T.hdr->err_flags, sd, dok);
+#pragma unroll
+        for (int r = 0; r < R; ++r) d[r] = sd[r];
+    }
+    if (in.dst_kind == OPK_TMP) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) tmp.vals[in.dst_idx * (32 * R) + r * 32 + lane] = d[r];
+        if (HAS_NULLS) tmp.oks[in.dst_idx * 32 + lane] = (uint8_t)dok;
+    } else {
+#pragma unroll
+        for (int r = 0; r < R; ++r) acc[r] = d[r];
+        acc_ok = dok;
+    }
+}
+
+// Runs expression `e` of the fused program on this lane's R rows.
 template <int R, bool HAS_NULLS>
 __device__ __forceinline__ V<R> run_expr(const FpParams& P, int e, const uint8_t* stage, int row0, int rows_in_tile,
-                                      long long grow0, const WarpTmp& tmp, int lane) {
+                                         long long grow0, const WarpTmp& tmp, int lane) {
     uint32_t inrange = 0;
 #pragma unroll
     for (int r = 0; r < R; ++r) inrange |= ((row0 + r * 32) < rows_in_tile ? 1u : 0u) << r;
-    V<R> acc;
-    acc.ok = FullMask<R>::value;
+    uint64_t acc[R];
+    uint32_t acc_ok = FullMask<R>::value;
 #pragma unroll
-    for (int r = 0; r < R; ++r) acc.v[r] = 0;
+    for (int r = 0; r < R; ++r) acc[r] = 0;
     const int first = P.expr_first[e], last = first + P.expr_count[e];
     for (int pc = first; pc < last; ++pc) {
         const Instr& in = P.code[pc];
-        V<R> d;
         if (in.op == IOP_ROWID) {
-            d.ok = FullMask<R>::value;
 #pragma unroll
-            for (int r = 0; r < R; ++r) d.v[r] = (uint64_t)(grow0 + r * 32);
-        } else {
-            const bool is_cast = in.op == IGL_OP_CAST;
-            const V<R> a = fetch<R, HAS_NULLS>(P, in.a_kind, in.a_idx, in.a_lit, !is_cast && (in.aux & AUX_A_NULL), stage, row0, acc, tmp, lane);
-            V<R> b = a;
-            if (in.b_kind != OPK_NONE)
-                b = fetch<R, HAS_NULLS>(P, in.b_kind, in.b_idx, in.b_lit, !is_cast && (in.aux & AUX_B_NULL), stage, row0, acc, tmp, lane);
-            d = exec_op<R, HAS_NULLS>(in, a, b, inrange, &P.T.hdr->err_flags);
+            for (int r = 0; r < R; ++r) acc[r] = (uint64_t)(grow0 + r * 32);
+            acc_ok = FullMask<R>::value;
+            continue;
         }
-        if (in.dst_kind == OPK_TMP) {
-#pragma unroll
-            for (int r = 0; r < R; ++r) tmp.vals[in.dst_idx * (32 * R) + r * 32 + lane] = d.v[r];
-            if (HAS_NULLS) tmp.oks[in.dst_idx * 32 + lane] = (uint8_t)d.ok;
-        } else {
-            acc = d;
+#define IGL_STEP(AK, BK) step<R, HAS_NULLS, AK, BK>(P, in, stage, row0, inrange, tmp, lane, acc, acc_ok)
+        switch (in.a_kind * 8 + in.b_kind) {
+            case OPK_COL * 8 + OPK_LIT: IGL_STEP(OPK_COL, OPK_LIT); break;
+            case OPK_COL * 8 + OPK_COL: IGL_STEP(OPK_COL, OPK_COL); break;
+            case OPK_ACC * 8 + OPK_LIT: IGL_STEP(OPK_ACC, OPK_LIT); break;
+            case OPK_ACC * 8 + OPK_COL: IGL_STEP(OPK_ACC, OPK_COL); break;
+            case OPK_COL * 8 + OPK_NONE: IGL_STEP(OPK_COL, OPK_NONE); break;
+            case OPK_ACC * 8 + OPK_NONE: IGL_STEP(OPK_ACC, OPK_NONE); break;
+            case OPK_LIT * 8 + OPK_NONE: IGL_STEP(OPK_LIT, OPK_NONE); break;
+            case OPK_TMP * 8 + OPK_ACC: IGL_STEP(OPK_TMP, OPK_ACC); break;
+            case OPK_TMP * 8 + OPK_COL: IGL_STEP(OPK_TMP, OPK_COL); break;
+            case OPK_TMP * 8 + OPK_LIT: IGL_STEP(OPK_TMP, OPK_LIT); break;
+            case OPK_TMP * 8 + OPK_TMP: IGL_STEP(OPK_TMP, OPK_TMP); break;
+            case OPK_TMP * 8 + OPK_NONE: IGL_STEP(OPK_TMP, OPK_NONE); break;
+            case OPK_COL * 8 + OPK_ACC: IGL_STEP(OPK_COL, OPK_ACC); break;
+            case OPK_COL * 8 + OPK_TMP: IGL_STEP(OPK_COL, OPK_TMP); break;
+            case OPK_LIT * 8 + OPK_COL: IGL_STEP(OPK_LIT, OPK_COL); break;
+            case OPK_LIT * 8 + OPK_ACC: IGL_STEP(OPK_LIT, OPK_ACC); break;
+            case OPK_LIT * 8 + OPK_LIT: IGL_STEP(OPK_LIT, OPK_LIT); break;
+            case OPK_LIT * 8 + OPK_TMP: IGL_STEP(OPK_LIT, OPK_TMP); break;
+            case OPK_ACC * 8 + OPK_TMP: IGL_STEP(OPK_ACC, OPK_TMP); break;
+            default: IGL_STEP(OPK_ACC, OPK_ACC); break;
         }
+#undef IGL_STEP
     }
-    return acc;
+    V<R> out;
+#pragma unroll
+    for (int r = 0; r < R; ++r) out.v[r] = acc[r];
+    out.ok = acc_ok;
+    return out;
 }
 
 template <int R>
