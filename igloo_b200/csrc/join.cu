@@ -58,6 +58,8 @@ struct JoinSide {          // side entries: [0] NULL key, [1] key == kEmptyKey
     unsigned int dup_flag;
     unsigned int pad;
     unsigned long long cursor;   // CSR run allocator
+    unsigned int ticket;         // build kernels: chunk claims
+    unsigned int pad2;
 };
 
 struct JoinTable {
@@ -97,24 +99,39 @@ __global__ void join_init_kernel(Slot* slots, uint64_t capacity, JoinSide* side)
         *reinterpret_cast<ulonglong2*>(slots + i) = e;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         side->count[0] = side->count[1] = 0; side->run_end[0] = side->run_end[1] = 0;
-        side->val[0] = side->val[1] = 0; side->dup_flag = 0; side->cursor = 0;
+        side->val[0] = side->val[1] = 0; side->dup_flag = 0; side->cursor = 0; side->ticket = 0;
     }
 }
 
 // ---- K5 build, unique layout ---------------------------------------------------------
 // payload_shift: 2 / 3 = width of the inlined payload column, 0xFF = store the row id.
-__global__ void join_build_unique_kernel(const void* __restrict__ keys, int key_type, const uint8_t* __restrict__ key_valid,
-                                         const void* __restrict__ payload, int payload_shift, long long n, JoinTable t) {
-    // 4 rows per thread per iteration, claimed concurrently: 4 independent atomics in flight
-    constexpr int U = 4;
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += stride * U) {
+constexpr int kBuildThreads = 256;
+constexpr int kBuildU = 4;                                   // rows per thread per chunk: 4 independent atomics in flight
+constexpr int kBuildChunk = kBuildThreads * kBuildU;
+
+// Chunks are claimed from an atomic ticket (not a static grid stride): all CTAs
+// then work on one moving frontier of the input, so when the build side has been
+// radix-partitioned the table region being filled stays L2-resident.
+__global__ void __launch_bounds__(kBuildThreads) join_build_unique_kernel(const void* __restrict__ keys, int key_type,
+                                                                           const uint8_t* __restrict__ key_valid,
+                                                                           const void* __restrict__ payload, int payload_shift,
+                                                                           long long n, JoinTable t, unsigned int* ticket) {
+    constexpr int U = kBuildU;
+    __shared__ long long s_chunk;
+    const long long nchunks = (n + kBuildChunk - 1) / kBuildChunk;
+    while (true) {
+        if (threadIdx.x == 0) s_chunk = (long long)atomicAdd(ticket, 1u);
+        __syncthreads();
+        const long long chunk = s_chunk;
+        __syncthreads();
+        if (chunk >= nchunks) break;
+        const long long i0 = chunk * kBuildChunk + threadIdx.x;
         uint64_t k[U], h[U];
         unsigned long long val[U];
         uint32_t pend = 0;
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            const long long i = i0 + u * stride;
+            const long long i = i0 + u * kBuildThreads;
             if (i >= n) continue;
             val[u] = payload_shift == 0xFF ? (unsigned long long)i
                      : payload_shift == 2 ? (unsigned long long)((const uint32_t*)payload)[i]
@@ -342,24 +359,72 @@ __device__ __forceinline__ void unique_lookup(const JoinProbeParams& P, UniqueTi
     }
 }
 
+// Column by column: width / source tests are uniform per column, the row loop is
+// straight predicated code.
 template <int R, bool HAS_NULLS>
 __device__ __forceinline__ void unique_emit(const JoinProbeParams& P, const UniqueTile<R>& t, long long wbase, int warp, int lane) {
     if (t.count == 0) return;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const int row0 = warp * (32 * R) + lane;
+    long long p[R];
+    uint32_t mine = 0, hitm = 0;
+    {
+        long long pos = wbase;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            p[r] = pos + __popc(t.keep[r] & lt_mask);
+            pos += __popc(t.keep[r]);
+            mine |= ((t.keep[r] >> lane) & 1u) << r;
+            hitm |= ((t.hitb[r] >> lane) & 1u) << r;
+        }
+    }
+    if (!mine) return;
+    for (int c = 0; c < P.n_left; ++c) {
+        const uint8_t* src = t.stage + P.T.smem_off[c];
+        uint8_t* dst = (uint8_t*)P.out_data[c];
+        if (P.out_shift[c] == 3) {
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                if ((mine >> r) & 1u) st_cs_u64(dst + (p[r] << 3), *reinterpret_cast<const uint64_t*>(src + ((row0 + r * 32) << 3)));
+        } else {
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                if ((mine >> r) & 1u) st_cs_u32(dst + (p[r] << 2), *reinterpret_cast<const uint32_t*>(src + ((row0 + r * 32) << 2)));
+        }
+        if (HAS_NULLS && P.out_valid[c]) {
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                if ((mine >> r) & 1u)
+                    P.out_valid[c][p[r]] = P.T.valid[c] ? (uint8_t)bit_at(t.stage + P.T.valid_off[c], row0 + r * 32) : (uint8_t)1;
+        }
+    }
     const uint8_t* kb = t.stage + P.T.smem_off[P.key_slot];
     const int ksh = P.T.shift[P.key_slot];
-    long long pos = wbase;
+    for (int c = 0; c < P.n_right; ++c) {
+        const int oc = P.n_left + c;
+        uint8_t* dst = (uint8_t*)P.out_data[oc];
+        const int mode = P.payload_col < 0 ? 2 : (c == P.payload_col ? 0 : 1);   // 0 inlined payload, 1 the probe key, 2 gather by row id
 #pragma unroll
-    for (int r = 0; r < R; ++r) {
-        const uint32_t kbits = t.keep[r];
-        if ((kbits >> lane) & 1u) {
-            const int row = row0 + r * 32;
-            const uint64_t raw = ksh == 2 ? (uint64_t) * reinterpret_cast<const uint32_t*>(kb + (row << 2))
-                                          : *reinterpret_cast<const uint64_t*>(kb + (row << 3));
-            emit_row<HAS_NULLS>(P, t.stage, row, pos + __popc(kbits & lt_mask), (t.hitb[r] >> lane) & 1u, t.val[r], raw);
+        for (int r = 0; r < R; ++r) {
+            if (!((mine >> r) & 1u)) continue;
+            const bool matched = (hitm >> r) & 1u;
+            uint64_t v = 0;
+            uint8_t ok = matched ? 1 : 0;
+            if (matched) {
+                if (mode == 0) v = t.val[r];
+                else if (mode == 1) {
+                    const int row = row0 + r * 32;
+                    v = ksh == 2 ? (uint64_t) * reinterpret_cast<const uint32_t*>(kb + (row << 2)) : *reinterpret_cast<const uint64_t*>(kb + (row << 3));
+                } else {
+                    const uint32_t rid = (uint32_t)t.val[r];
+                    v = P.out_shift[oc] == 2 ? (uint64_t)((const uint32_t*)P.right_data[c])[rid] : ((const uint64_t*)P.right_data[c])[rid];
+                    if (HAS_NULLS && P.right_valid[c]) ok = (uint8_t)bit_at(P.right_valid[c], rid);
+                }
+            }
+            if (P.out_shift[oc] == 2) st_cs_u32(dst + (p[r] << 2), (uint32_t)v);
+            else st_cs_u64(dst + (p[r] << 3), v);
+            if (HAS_NULLS && P.out_valid[oc]) P.out_valid[oc][p[r]] = ok;
         }
-        pos += __popc(kbits);
     }
 }
 
@@ -497,6 +562,7 @@ __global__ void __launch_bounds__(kPipeThreads, kPipeMinCtas) join_probe_multi_k
 constexpr int kFlatThreads = 256;
 constexpr int kFlatRows = 4;
 constexpr int kFlatChunk = kFlatThreads * kFlatRows;   // 1024 rows per CTA iteration
+constexpr int kFlatClaim = 4;                          // consecutive chunks claimed per ticket
 
 struct FlatProbeParams {
     const uint8_t* left[kJoinMaxCols];
@@ -507,18 +573,29 @@ struct FlatProbeParams {
     JoinTable table;
     long long nrows;
     unsigned long long* out_counter;
+    unsigned int* ticket;   // chunks are claimed in order, so all CTAs work on one moving frontier of the
+                            // (partitioned) input and the table region they touch stays L2-resident
 };
 
+template <int KEY_TYPE>
 __global__ void __launch_bounds__(kFlatThreads, 3) join_probe_flat_kernel(const __grid_constant__ FlatProbeParams P) {
     __shared__ unsigned int s_wcnt[kFlatThreads / 32];
     __shared__ unsigned long long s_base;
+    __shared__ long long s_chunk;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint64_t bmask = P.table.mask >> 1;
     const long long nchunks = (P.nrows + kFlatChunk - 1) / kFlatChunk;
     const uint8_t* keys = P.left[P.key_col];
-    const int ksh = P.lshift[P.key_col];
-    for (long long chunk = blockIdx.x; chunk < nchunks; chunk += gridDim.x) {
+    const Slot* slots = P.table.slots;
+    const int tshift = P.table.shift;
+    for (long long it = 0;; ++it) {
+        if ((it % kFlatClaim) == 0) {
+            if (threadIdx.x == 0) s_chunk = (long long)atomicAdd(P.ticket, 1u) * kFlatClaim;
+            __syncthreads();
+        }
+        const long long chunk = s_chunk + (it % kFlatClaim);
+        if (chunk >= nchunks) break;   // claims only grow: nothing is left for this CTA
         const long long row0 = chunk * kFlatChunk + warp * (32 * kFlatRows) + lane;
         uint64_t raw[kFlatRows], k[kFlatRows], b[kFlatRows];
         unsigned long long val[kFlatRows];
@@ -527,27 +604,37 @@ __global__ void __launch_bounds__(kFlatThreads, 3) join_probe_flat_kernel(const 
 #pragma unroll
         for (int r = 0; r < kFlatRows; ++r) {
             const long long row = row0 + r * 32;
+            raw[r] = 0; k[r] = kEmptyKey;
             if (row < P.nrows) {
-                raw[r] = ksh == 2 ? (uint64_t)((const uint32_t*)keys)[row] : ((const uint64_t*)keys)[row];
-                k[r] = canon_key(P.key_type, raw[r]);
-                if (k[r] == kEmptyKey) {   // the one key equal to the sentinel lives in a side entry
-                    if (P.table.side->count[1]) { hit |= 1u << r; val[r] = P.table.side->val[1]; }
-                } else {
-                    b[r] = (mix64(k[r]) >> P.table.shift) >> 1;
-                    q[r] = ld_nc_u64x4(P.table.slots + 2 * b[r]);
-                    pend |= 1u << r;
-                }
+                raw[r] = KEY_TYPE == IGL_T_I32 ? (uint64_t)((const uint32_t*)keys)[row] : ((const uint64_t*)keys)[row];
+                k[r] = canon_key(KEY_TYPE, raw[r]);
+                pend |= (k[r] != kEmptyKey ? 1u : 0u) << r;
+            }
+            b[r] = (mix64(k[r]) >> tshift) >> 1;
+        }
+#pragma unroll
+        for (int r = 0; r < kFlatRows; ++r)
+            if ((pend >> r) & 1u) q[r] = ld_nc_u64x4(slots + 2 * b[r]);
+        // the one key equal to the empty-slot sentinel lives in a side entry (rare: checked once per lane)
+        {
+            bool any_special = false;
+#pragma unroll
+            for (int r = 0; r < kFlatRows; ++r) any_special |= (row0 + r * 32 < P.nrows) && k[r] == kEmptyKey;
+            if (any_special && P.table.side->count[1]) {
+#pragma unroll
+                for (int r = 0; r < kFlatRows; ++r)
+                    if ((row0 + r * 32 < P.nrows) && k[r] == kEmptyKey) { hit |= 1u << r; val[r] = P.table.side->val[1]; }
             }
         }
         while (pend) {
 #pragma unroll
             for (int r = 0; r < kFlatRows; ++r) {
                 if (!((pend >> r) & 1u)) continue;
-                if (q[r].x == k[r]) { hit |= 1u << r; val[r] = q[r].y; pend &= ~(1u << r); }
-                else if (q[r].x == kEmptyKey) pend &= ~(1u << r);
-                else if (q[r].z == k[r]) { hit |= 1u << r; val[r] = q[r].w; pend &= ~(1u << r); }
-                else if (q[r].z == kEmptyKey) pend &= ~(1u << r);
-                else { b[r] = (b[r] + 1) & bmask; q[r] = ld_nc_u64x4(P.table.slots + 2 * b[r]); }
+                const bool h0 = q[r].x == k[r], h1 = q[r].z == k[r];
+                const bool e0 = q[r].x == kEmptyKey, e1 = q[r].z == kEmptyKey;
+                if (h0 || (!e0 && h1)) { hit |= 1u << r; val[r] = h0 ? q[r].y : q[r].w; pend &= ~(1u << r); }
+                else if (e0 || e1) pend &= ~(1u << r);
+                else { b[r] = (b[r] + 1) & bmask; q[r] = ld_nc_u64x4(slots + 2 * b[r]); }
             }
         }
         uint32_t hb[kFlatRows];
@@ -566,27 +653,40 @@ __global__ void __launch_bounds__(kFlatThreads, 3) join_probe_flat_kernel(const 
         unsigned long long pos = s_base;
         for (int w = 0; w < warp; ++w) pos += s_wcnt[w];
         __syncthreads();   // s_wcnt / s_base are rewritten by the next chunk
+        // output positions of this lane's rows (only meaningful where hit)
+        unsigned long long p[kFlatRows];
 #pragma unroll
-        for (int r = 0; r < kFlatRows; ++r) {
-            if ((hb[r] >> lane) & 1u) {
-                const unsigned long long p = pos + __popc(hb[r] & lt_mask);
-                const long long row = row0 + r * 32;
-                for (int c = 0; c < P.n_left; ++c) {
-                    if (P.lshift[c] == 2) st_cs_u32((uint8_t*)P.out[c] + (p << 2), c == P.key_col ? (uint32_t)raw[r] : ((const uint32_t*)P.left[c])[row]);
-                    else st_cs_u64((uint8_t*)P.out[c] + (p << 3), c == P.key_col ? raw[r] : ((const uint64_t*)P.left[c])[row]);
-                }
-                for (int c = 0; c < P.n_right; ++c) {
-                    uint64_t v;
-                    if (P.payload_col >= 0) v = c == P.payload_col ? val[r] : raw[r];
-                    else {
-                        const uint32_t rid = (uint32_t)val[r];
-                        v = P.rshift[c] == 2 ? (uint64_t)((const uint32_t*)P.right_data[c])[rid] : ((const uint64_t*)P.right_data[c])[rid];
-                    }
-                    if (P.rshift[c] == 2) st_cs_u32((uint8_t*)P.out[P.n_left + c] + (p << 2), (uint32_t)v);
-                    else st_cs_u64((uint8_t*)P.out[P.n_left + c] + (p << 3), v);
-                }
+        for (int r = 0; r < kFlatRows; ++r) { p[r] = pos + __popc(hb[r] & lt_mask); pos += __popc(hb[r]); }
+        // column by column: the width test is uniform per column, the row loop is branch-free predication
+        for (int c = 0; c < P.n_left; ++c) {
+            const uint8_t* src = P.left[c];
+            uint8_t* dst = (uint8_t*)P.out[c];
+            const bool is_key = c == P.key_col;
+            if (P.lshift[c] == 3) {
+#pragma unroll
+                for (int r = 0; r < kFlatRows; ++r)
+                    if ((hit >> r) & 1u) st_cs_u64(dst + (p[r] << 3), is_key ? raw[r] : ((const uint64_t*)src)[row0 + r * 32]);
+            } else {
+#pragma unroll
+                for (int r = 0; r < kFlatRows; ++r)
+                    if ((hit >> r) & 1u) st_cs_u32(dst + (p[r] << 2), is_key ? (uint32_t)raw[r] : ((const uint32_t*)src)[row0 + r * 32]);
             }
-            pos += __popc(hb[r]);
+        }
+        for (int c = 0; c < P.n_right; ++c) {
+            uint8_t* dst = (uint8_t*)P.out[P.n_left + c];
+            const uint8_t* src = P.right_data[c];
+            const int mode = P.payload_col < 0 ? 2 : (c == P.payload_col ? 0 : 1);   // 0 inlined payload, 1 the key itself, 2 gather by row id
+            if (P.rshift[c] == 3) {
+#pragma unroll
+                for (int r = 0; r < kFlatRows; ++r)
+                    if ((hit >> r) & 1u)
+                        st_cs_u64(dst + (p[r] << 3), mode == 0 ? val[r] : mode == 1 ? raw[r] : ((const uint64_t*)src)[(uint32_t)val[r]]);
+            } else {
+#pragma unroll
+                for (int r = 0; r < kFlatRows; ++r)
+                    if ((hit >> r) & 1u)
+                        st_cs_u32(dst + (p[r] << 2), mode == 0 ? (uint32_t)val[r] : mode == 1 ? (uint32_t)raw[r] : ((const uint32_t*)src)[(uint32_t)val[r]]);
+            }
         }
     }
 }
@@ -765,11 +865,9 @@ int32_t igl_join_build(igl_join* j, const igl_dev_col* right, int64_t nrows, voi
     j->part_right.clear();
     j->log2_parts = 0;
     {
-        // Off unless IGL_JOIN_PARTITION=1: measured on B200 (profiles/README.md) the
-        // partitioned probe is 1.7x faster (table reads served by L2) but the extra
-        // pass over the probe side still costs more than it saves.
+        // IGL_JOIN_PARTITION=0 switches it off (A/B measurements in profiles/README.md).
         const char* env = getenv("IGL_JOIN_PARTITION");
-        bool want = (env && env[0] == '1') && cap * sizeof(Slot) >= (64ull << 20) && nrows > 0;
+        bool want = !(env && env[0] == '0') && cap * sizeof(Slot) >= (64ull << 20) && nrows > 0;
         for (int c = 0; c < nr; ++c) if (right[c].validity) want = false;
         if (want) {
             int lp = 0;
@@ -801,7 +899,8 @@ int32_t igl_join_build(igl_join* j, const igl_dev_col* right, int64_t nrows, voi
     if (nrows > 0) {
         const void* payload = j->payload_col >= 0 ? right[j->payload_col].data : nullptr;
         const int pshift = j->payload_col >= 0 ? (j->rt[j->payload_col] == IGL_T_I32 ? 2 : 3) : 0xFF;
-        join_build_unique_kernel<<<grid, 256, 0, st>>>(kc.data, j->rt[j->rkey], kc.validity, payload, pshift, nrows, j->table);
+        join_build_unique_kernel<<<grid, kBuildThreads, 0, st>>>(kc.data, j->rt[j->rkey], kc.validity, payload, pshift, nrows, j->table,
+                                                                  &((JoinSide*)j->d_side)->ticket);
         IGL_CUDA_OK(cudaGetLastError());
         ctx->launches++;
     }
@@ -907,9 +1006,12 @@ int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_
             if (!j->scratch) { IGL_TRY(pool_alloc(ctx, 256, &j->scratch)); j->scratch_bytes = 256; }
             IGL_CUDA_OK(cudaMemsetAsync(j->scratch, 0, 256, st));
             F.out_counter = &((PipeHeader*)j->scratch)->aux[1];
+            F.ticket = &((PipeHeader*)j->scratch)->ticket;
             const long long nchunks = (nrows + kFlatChunk - 1) / kFlatChunk;
             const int grid = (int)std::min<long long>(nchunks, (long long)ctx->sm_count * 6);
-            join_probe_flat_kernel<<<grid, kFlatThreads, 0, st>>>(F);
+            if (F.key_type == IGL_T_I32) join_probe_flat_kernel<IGL_T_I32><<<grid, kFlatThreads, 0, st>>>(F);
+            else if (F.key_type == IGL_T_F64) join_probe_flat_kernel<IGL_T_F64><<<grid, kFlatThreads, 0, st>>>(F);
+            else join_probe_flat_kernel<IGL_T_I64><<<grid, kFlatThreads, 0, st>>>(F);
             IGL_CUDA_OK(cudaGetLastError());
             ctx->launches++;
             IGL_CUDA_OK(cudaMemcpyAsync(j->host_hdr, j->scratch, sizeof(PipeHeader), cudaMemcpyDeviceToHost, st));

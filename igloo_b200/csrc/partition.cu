@@ -129,14 +129,14 @@ __global__ void __launch_bounds__(kPartThreads) partition_scatter_kernel(const _
 constexpr int kRadixMaxParts = 1024;
 constexpr int kRadixThreads = 512;
 constexpr int kRadixRowsPerThread = 8;
-constexpr int kRadixTile = kRadixThreads * kRadixRowsPerThread;   // 4096 rows
+constexpr int kRadixTile = kRadixThreads * kRadixRowsPerThread;   // 4096 rows per tile: long write runs per partition
 
 __device__ __forceinline__ int radix_part(const void* keys, int type, long long i, int log2_parts) {
     const uint64_t raw = type == IGL_T_I32 ? (uint64_t)(uint32_t)((const int32_t*)keys)[i] : ((const uint64_t*)keys)[i];
     return (int)(mix64(part_canon(type, raw)) >> (64 - log2_parts));
 }
 
-__global__ void __launch_bounds__(kRadixThreads) radix_hist_kernel(const void* __restrict__ keys, int type, long long n,
+__global__ void __launch_bounds__(512) radix_hist_kernel(const void* __restrict__ keys, int type, long long n,
                                                                    int log2_parts, unsigned long long* hist) {
     __shared__ unsigned int s_hist[kRadixMaxParts];
     const int nparts = 1 << log2_parts;
@@ -194,12 +194,21 @@ __global__ void __launch_bounds__(kRadixThreads, 2) radix_scatter_kernel(const _
         const int rows = (int)min((long long)kRadixTile, P.n - row0);
         int part[kRadixRowsPerThread];
         unsigned int rank[kRadixRowsPerThread];
+        uint64_t keyraw[kRadixRowsPerThread];
+        const void* keys = P.src[P.key_col];
+#pragma unroll
+        for (int r = 0; r < kRadixRowsPerThread; ++r) {   // all key loads first: 8 independent requests in flight per thread
+            const int li = r * kRadixThreads + threadIdx.x;
+            keyraw[r] = 0;
+            if (li < rows)
+                keyraw[r] = P.key_type == IGL_T_I32 ? (uint64_t)(uint32_t)((const int32_t*)keys)[row0 + li] : ((const uint64_t*)keys)[row0 + li];
+        }
 #pragma unroll
         for (int r = 0; r < kRadixRowsPerThread; ++r) {
             const int li = r * kRadixThreads + threadIdx.x;
             part[r] = -1;
             if (li < rows) {
-                part[r] = radix_part(P.src[P.key_col], P.key_type, row0 + li, P.log2_parts);
+                part[r] = (int)(mix64(part_canon(P.key_type, keyraw[r])) >> (64 - P.log2_parts));
                 rank[r] = atomicAdd(&s_cnt[part[r]], 1u);
             }
         }
@@ -207,8 +216,11 @@ __global__ void __launch_bounds__(kRadixThreads, 2) radix_scatter_kernel(const _
         // exclusive scan of s_cnt[0..nparts) by the CTA (nparts <= 1024 = 2 per thread) + global reservation
         {
             const int i0 = threadIdx.x * 2;
-            const unsigned int c0 = i0 < nparts ? s_cnt[i0] : 0, c1 = i0 + 1 < nparts ? s_cnt[i0 + 1] : 0;
-            unsigned int inc = c0 + c1;
+            unsigned int c[2];
+            unsigned int sum = 0;
+#pragma unroll
+            for (int q = 0; q < 2; ++q) { c[q] = (i0 + q < nparts) ? s_cnt[i0 + q] : 0; sum += c[q]; }
+            unsigned int inc = sum;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 const unsigned int t = __shfl_up_sync(0xffffffffu, inc, o);
@@ -216,39 +228,66 @@ __global__ void __launch_bounds__(kRadixThreads, 2) radix_scatter_kernel(const _
             }
             if (lane == 31) s_warp_tot[warp] = inc;
             __syncthreads();
-            unsigned int wpre = 0;
-            for (int w = 0; w < warp; ++w) wpre += s_warp_tot[w];
-            const unsigned int ex = wpre + inc - (c0 + c1);
-            if (i0 < nparts) {
-                s_cnt[i0] = ex;
-                s_gbase[i0] = c0 ? P.offsets[i0] + atomicAdd(&P.cursor[i0], (unsigned long long)c0) : 0ull;
-            }
-            if (i0 + 1 < nparts) {
-                s_cnt[i0 + 1] = ex + c0;
-                s_gbase[i0 + 1] = c1 ? P.offsets[i0 + 1] + atomicAdd(&P.cursor[i0 + 1], (unsigned long long)c1) : 0ull;
+            unsigned int ex = inc - sum;
+            for (int w = 0; w < warp; ++w) ex += s_warp_tot[w];
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                if (i0 + q < nparts) {
+                    s_cnt[i0 + q] = ex;
+                    s_gbase[i0 + q] = c[q] ? P.offsets[i0 + q] + atomicAdd(&P.cursor[i0 + q], (unsigned long long)c[q]) : 0ull;
+                }
+                ex += c[q];
             }
         }
         __syncthreads();
-        // stage: rows land grouped by partition
+        // stage: rows land grouped by partition.  Column by column, so the width test is
+        // uniform and the row loop is straight predicated code.
+        unsigned int slot[kRadixRowsPerThread];
 #pragma unroll
         for (int r = 0; r < kRadixRowsPerThread; ++r) {
-            if (part[r] < 0) continue;
-            const long long i = row0 + r * kRadixThreads + threadIdx.x;
-            const unsigned int slot = s_cnt[part[r]] + rank[r];
-            s_part[slot] = (unsigned short)part[r];
-            for (int c = 0; c < P.ncols; ++c) {
-                if (P.shift[c] == 2) reinterpret_cast<uint32_t*>(stage + P.stage_off[c])[slot] = reinterpret_cast<const uint32_t*>(P.src[c])[i];
-                else reinterpret_cast<uint64_t*>(stage + P.stage_off[c])[slot] = reinterpret_cast<const uint64_t*>(P.src[c])[i];
+            slot[r] = 0;
+            if (part[r] >= 0) { slot[r] = s_cnt[part[r]] + rank[r]; s_part[slot[r]] = (unsigned short)part[r]; }
+        }
+        for (int c = 0; c < P.ncols; ++c) {
+            const bool is_key = c == P.key_col;
+            if (P.shift[c] == 3) {
+                uint64_t* sc = reinterpret_cast<uint64_t*>(stage + P.stage_off[c]);
+                const uint64_t* src = reinterpret_cast<const uint64_t*>(P.src[c]) + row0 + threadIdx.x;
+                uint64_t v[kRadixRowsPerThread];
+#pragma unroll
+                for (int r = 0; r < kRadixRowsPerThread; ++r) v[r] = (part[r] >= 0 && !is_key) ? src[r * kRadixThreads] : keyraw[r];
+#pragma unroll
+                for (int r = 0; r < kRadixRowsPerThread; ++r) if (part[r] >= 0) sc[slot[r]] = v[r];
+            } else {
+                uint32_t* sc = reinterpret_cast<uint32_t*>(stage + P.stage_off[c]);
+                const uint32_t* src = reinterpret_cast<const uint32_t*>(P.src[c]) + row0 + threadIdx.x;
+                uint32_t v[kRadixRowsPerThread];
+#pragma unroll
+                for (int r = 0; r < kRadixRowsPerThread; ++r) v[r] = (part[r] >= 0 && !is_key) ? src[r * kRadixThreads] : (uint32_t)keyraw[r];
+#pragma unroll
+                for (int r = 0; r < kRadixRowsPerThread; ++r) if (part[r] >= 0) sc[slot[r]] = v[r];
             }
         }
         __syncthreads();
         // write-out: consecutive threads -> consecutive slots -> runs of consecutive destination rows
-        for (int slot = threadIdx.x; slot < rows; slot += kRadixThreads) {
-            const int p = s_part[slot];
-            const unsigned long long d = s_gbase[p] + (slot - s_cnt[p]);
-            for (int c = 0; c < P.ncols; ++c) {
-                if (P.shift[c] == 2) reinterpret_cast<uint32_t*>(P.dst[c])[d] = reinterpret_cast<const uint32_t*>(stage + P.stage_off[c])[slot];
-                else reinterpret_cast<uint64_t*>(P.dst[c])[d] = reinterpret_cast<const uint64_t*>(stage + P.stage_off[c])[slot];
+        unsigned long long d[kRadixRowsPerThread];
+#pragma unroll
+        for (int r = 0; r < kRadixRowsPerThread; ++r) {
+            const int sl = r * kRadixThreads + threadIdx.x;
+            d[r] = 0;
+            if (sl < rows) { const int p = s_part[sl]; d[r] = s_gbase[p] + (unsigned)(sl - s_cnt[p]); }
+        }
+        for (int c = 0; c < P.ncols; ++c) {
+            if (P.shift[c] == 3) {
+                const uint64_t* sc = reinterpret_cast<const uint64_t*>(stage + P.stage_off[c]) + threadIdx.x;
+                uint64_t* dst = reinterpret_cast<uint64_t*>(P.dst[c]);
+#pragma unroll
+                for (int r = 0; r < kRadixRowsPerThread; ++r) if (r * kRadixThreads + (int)threadIdx.x < rows) dst[d[r]] = sc[r * kRadixThreads];
+            } else {
+                const uint32_t* sc = reinterpret_cast<const uint32_t*>(stage + P.stage_off[c]) + threadIdx.x;
+                uint32_t* dst = reinterpret_cast<uint32_t*>(P.dst[c]);
+#pragma unroll
+                for (int r = 0; r < kRadixRowsPerThread; ++r) if (r * kRadixThreads + (int)threadIdx.x < rows) dst[d[r]] = sc[r * kRadixThreads];
             }
         }
         __syncthreads();
@@ -282,7 +321,7 @@ int32_t radix_partition(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int ke
     if (off > (96u << 10)) return fail(IGL_ERR_UNSUPPORTED, "radix_partition: row too wide (%u bytes of staging)", off);
     const int grid = ctx->sm_count * 2;
     if (nrows > 0) {
-        radix_hist_kernel<<<grid, kRadixThreads, 0, st>>>(cols[key_col].data, P.key_type, nrows, log2_parts, hist);
+        radix_hist_kernel<<<grid * 2, 512, 0, st>>>(cols[key_col].data, P.key_type, nrows, log2_parts, hist);
         IGL_CUDA_OK(cudaGetLastError());
     }
     radix_scan_kernel<<<1, kRadixMaxParts, 0, st>>>(hist, offsets, cursor, nparts);
