@@ -334,6 +334,68 @@ __device__ __forceinline__ void step(const FpParams& P, const Instr& in, const u
     }
 }
 
+// ---- fast handlers ----------------------------------------------------------------
+// The common instructions (column/accumulator against column/literal; compare, add,
+// subtract, multiply; Int32 / Int64 / Float64; no nulls anywhere) get one fully
+// specialised handler each, selected by a dense id computed on the host: one
+// jump-table branch per instruction, native-width operands, no per-row tests.
+template <int TY> struct NativeOf { using type = uint64_t; };
+template <> struct NativeOf<FP_TY_I32> { using type = uint32_t; };
+
+template <int R, int PAIR, int CLS, int TY>
+__device__ __forceinline__ void fast_step(const FpParams& P, const Instr& in, const uint8_t* stage, int row0, uint64_t (&acc)[R]) {
+    using T = typename NativeOf<TY>::type;
+    T a[R], b[R];
+    if (PAIR == FP_PAIR_COL_LIT || PAIR == FP_PAIR_COL_COL) {
+        const T* ca = reinterpret_cast<const T*>(stage + P.T.smem_off[in.a_idx]) + row0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) a[r] = ca[r * 32];
+    } else {
+#pragma unroll
+        for (int r = 0; r < R; ++r) a[r] = (T)acc[r];
+    }
+    if (PAIR == FP_PAIR_COL_COL || PAIR == FP_PAIR_ACC_COL) {
+        const T* cb = reinterpret_cast<const T*>(stage + P.T.smem_off[in.b_idx]) + row0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) b[r] = cb[r * 32];
+    } else {
+        const T lit = (T)in.b_lit;
+#pragma unroll
+        for (int r = 0; r < R; ++r) b[r] = lit;
+    }
+    if (CLS == FP_CLS_CMP) {
+        const int op = in.op;
+        const bool m_lt = op == IGL_OP_LT || op == IGL_OP_LE || op == IGL_OP_NE;
+        const bool m_eq = op == IGL_OP_EQ || op == IGL_OP_LE || op == IGL_OP_GE;
+        const bool m_gt = op == IGL_OP_GT || op == IGL_OP_GE || op == IGL_OP_NE;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            bool lt, eq;
+            if (TY == FP_TY_I32) { lt = (int32_t)a[r] < (int32_t)b[r]; eq = a[r] == b[r]; }
+            else if (TY == FP_TY_I64) { lt = (int64_t)a[r] < (int64_t)b[r]; eq = a[r] == b[r]; }
+            else { const int64_t x = total_order_key((uint64_t)a[r]), y = total_order_key((uint64_t)b[r]); lt = x < y; eq = x == y; }
+            acc[r] = ((lt && m_lt) || (eq && m_eq) || (!lt && !eq && m_gt)) ? 1 : 0;
+        }
+    } else if (TY == FP_TY_F64) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const double x = __longlong_as_double((long long)a[r]), y = __longlong_as_double((long long)b[r]);
+            const double z = CLS == FP_CLS_ADD ? __dadd_rn(x, y) : CLS == FP_CLS_SUB ? __dsub_rn(x, y) : __dmul_rn(x, y);   // never an FMA
+            acc[r] = (uint64_t)__double_as_longlong(z);
+        }
+    } else {
+#pragma unroll
+        for (int r = 0; r < R; ++r) acc[r] = (uint64_t)(T)(CLS == FP_CLS_ADD ? a[r] + b[r] : CLS == FP_CLS_SUB ? a[r] - b[r] : a[r] * b[r]);
+    }
+}
+
+template <int R, class T>
+__device__ __forceinline__ void fast_mov(const FpParams& P, const Instr& in, const uint8_t* stage, int row0, uint64_t (&acc)[R]) {
+    const T* ca = reinterpret_cast<const T*>(stage + P.T.smem_off[in.a_idx]) + row0;
+#pragma unroll
+    for (int r = 0; r < R; ++r) acc[r] = (uint64_t)ca[r * 32];
+}
+
 // Runs expression `e` of the fused program on this lane's R rows.
 template <int R, bool HAS_NULLS>
 __device__ __forceinline__ V<R> run_expr(const FpParams& P, int e, const uint8_t* stage, int row0, int rows_in_tile,
@@ -352,6 +414,28 @@ __device__ __forceinline__ V<R> run_expr(const FpParams& P, int e, const uint8_t
 #pragma unroll
             for (int r = 0; r < R; ++r) acc[r] = (uint64_t)(grow0 + r * 32);
             acc_ok = FullMask<R>::value;
+            continue;
+        }
+        if (!HAS_NULLS && in.fast) {   // dense id -> jump table -> specialised straight-line handler
+#define IGL_FAST3(PAIR, CLS, BASE)                                                              \
+            case BASE + 0: fast_step<R, PAIR, CLS, FP_TY_I32>(P, in, stage, row0, acc); break;   \
+            case BASE + 1: fast_step<R, PAIR, CLS, FP_TY_I64>(P, in, stage, row0, acc); break;   \
+            case BASE + 2: fast_step<R, PAIR, CLS, FP_TY_F64>(P, in, stage, row0, acc); break;
+#define IGL_FAST_PAIR(PAIR)                                  \
+            IGL_FAST3(PAIR, FP_CLS_CMP, 1 + (PAIR * 4 + 0) * 3) \
+            IGL_FAST3(PAIR, FP_CLS_ADD, 1 + (PAIR * 4 + 1) * 3) \
+            IGL_FAST3(PAIR, FP_CLS_SUB, 1 + (PAIR * 4 + 2) * 3) \
+            IGL_FAST3(PAIR, FP_CLS_MUL, 1 + (PAIR * 4 + 3) * 3)
+            switch (in.fast) {
+                IGL_FAST_PAIR(FP_PAIR_COL_LIT)
+                IGL_FAST_PAIR(FP_PAIR_COL_COL)
+                IGL_FAST_PAIR(FP_PAIR_ACC_LIT)
+                IGL_FAST_PAIR(FP_PAIR_ACC_COL)
+                case kFastMov32: fast_mov<R, uint32_t>(P, in, stage, row0, acc); break;
+                default: fast_mov<R, uint64_t>(P, in, stage, row0, acc); break;
+            }
+#undef IGL_FAST_PAIR
+#undef IGL_FAST3
             continue;
         }
 #define IGL_STEP(AK, BK) step<R, HAS_NULLS, AK, BK>(P, in, stage, row0, inrange, tmp, lane, acc, acc_ok)
@@ -418,23 +502,38 @@ __device__ __forceinline__ void fp_write(const FpParams& P, const FpTile<R>& t, 
     const uint32_t lt_mask = (1u << lane) - 1u;
     const int row0 = warp * (32 * R) + lane;
     const int e0 = HAS_PRED ? 1 : 0;
-    for (int j = 0; j < P.n_out; ++j) {
-        uint8_t* od = reinterpret_cast<uint8_t*>(P.out_data[j]);
-        uint8_t* ov = HAS_NULLS ? P.out_valid[j] : nullptr;
-        const int osh = P.out_shift[j];
-        const V<R> val = run_expr<R, HAS_NULLS>(P, e0 + j, t.stage, row0, t.rows, t.row_begin + row0, tmp, lane);
-        long long pos = wbase;
+    // 32-bit offsets inside this warp's output run, computed once for all output columns
+    uint32_t off[R];
+    uint32_t mine = 0;
+    {
+        uint32_t run = 0;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            const uint32_t kb = t.keep[r];
-            if ((kb >> lane) & 1u) {
-                const long long p = pos + __popc(kb & lt_mask);
-                if (osh == 2) st_cs_u32(od + (p << 2), (uint32_t)val.v[r]);
-                else if (osh == 3) st_cs_u64(od + (p << 3), val.v[r]);
-                else od[p] = (uint8_t)(val.v[r] & 1);
-                if (HAS_NULLS && ov) ov[p] = (uint8_t)((val.ok >> r) & 1u);
-            }
-            pos += __popc(kb);
+            off[r] = run + __popc(t.keep[r] & lt_mask);
+            run += __popc(t.keep[r]);
+            mine |= ((t.keep[r] >> lane) & 1u) << r;
+        }
+    }
+    for (int j = 0; j < P.n_out; ++j) {
+        const int osh = P.out_shift[j];
+        const V<R> val = run_expr<R, HAS_NULLS>(P, e0 + j, t.stage, row0, t.rows, t.row_begin + row0, tmp, lane);
+        if (osh == 3) {
+            uint64_t* od = reinterpret_cast<uint64_t*>(P.out_data[j]) + wbase;
+#pragma unroll
+            for (int r = 0; r < R; ++r) if ((mine >> r) & 1u) st_cs_u64(od + off[r], val.v[r]);
+        } else if (osh == 2) {
+            uint32_t* od = reinterpret_cast<uint32_t*>(P.out_data[j]) + wbase;
+#pragma unroll
+            for (int r = 0; r < R; ++r) if ((mine >> r) & 1u) st_cs_u32(od + off[r], (uint32_t)val.v[r]);
+        } else {
+            uint8_t* od = reinterpret_cast<uint8_t*>(P.out_data[j]) + wbase;
+#pragma unroll
+            for (int r = 0; r < R; ++r) if ((mine >> r) & 1u) od[off[r]] = (uint8_t)(val.v[r] & 1);
+        }
+        if (HAS_NULLS && P.out_valid[j]) {
+            uint8_t* ov = P.out_valid[j] + wbase;
+#pragma unroll
+            for (int r = 0; r < R; ++r) if ((mine >> r) & 1u) ov[off[r]] = (uint8_t)((val.ok >> r) & 1u);
         }
     }
 }
@@ -446,10 +545,7 @@ __global__ void __launch_bounds__(kPipeThreads, kPipeMinCtas) fp_kernel(const __
     TilePipe<HAS_PRED, HAS_NULLS> pipe(P.T, sh, smem);
     pipe.init();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (warp == kPipeComputeWarps) {
-        pipe.control_loop();
-        return;
-    }
+    if (warp == kPipeComputeWarps) { pipe.control_loop(); return; }
     WarpTmp tmp;
     tmp.vals = reinterpret_cast<uint64_t*>(smem + P.tmp_off) + (size_t)warp * P.n_tmp * (32 * R);
     tmp.oks = smem + P.tmp_off + (size_t)kPipeComputeWarps * P.n_tmp * 1024 + (size_t)warp * P.n_tmp * 32;
@@ -644,6 +740,27 @@ int32_t igl::fp_create_ex(igl_ctx* ctx, const int32_t* in_types, const uint8_t* 
     for (auto& in : code) {  // schema column index -> staged slot
         if (in.a_kind == OPK_COL) in.a_idx = (uint8_t)fp->slot_of_col[in.a_idx];
         if (in.b_kind == OPK_COL) in.b_idx = (uint8_t)fp->slot_of_col[in.b_idx];
+    }
+    // fast-handler ids (only used by the no-null kernels; see fast_step)
+    for (auto& in : code) {
+        in.fast = 0;
+        if (in.dst_kind != OPK_ACC) continue;
+        int pair = -1;
+        if (in.a_kind == OPK_COL && in.b_kind == OPK_LIT) pair = FP_PAIR_COL_LIT;
+        else if (in.a_kind == OPK_COL && in.b_kind == OPK_COL) pair = FP_PAIR_COL_COL;
+        else if (in.a_kind == OPK_ACC && in.b_kind == OPK_LIT) pair = FP_PAIR_ACC_LIT;
+        else if (in.a_kind == OPK_ACC && in.b_kind == OPK_COL) pair = FP_PAIR_ACC_COL;
+        const int ty = in.type == IGL_T_I32 ? FP_TY_I32 : in.type == IGL_T_I64 ? FP_TY_I64 : in.type == IGL_T_F64 ? FP_TY_F64 : -1;
+        int cls = -1;
+        if (in.op >= IGL_OP_EQ && in.op <= IGL_OP_GE) cls = FP_CLS_CMP;
+        else if (in.op == IGL_OP_ADD) cls = FP_CLS_ADD;
+        else if (in.op == IGL_OP_SUB) cls = FP_CLS_SUB;
+        else if (in.op == IGL_OP_MUL) cls = FP_CLS_MUL;
+        if (pair >= 0 && ty >= 0 && cls >= 0 && !(in.aux & (AUX_A_NULL | AUX_B_NULL))) in.fast = (uint8_t)(1 + (pair * 4 + cls) * 3 + ty);
+        else if (in.op == IOP_MOV && in.a_kind == OPK_COL && in.b_kind == OPK_NONE && !(in.aux & AUX_A_NULL)) {
+            const int sh = shifts[in.a_idx];
+            if (sh == 2) in.fast = kFastMov32; else if (sh == 3) in.fast = kFastMov64;
+        }
     }
     memcpy(P.code, code.data(), code.size() * sizeof(Instr));
     P.n_out = (uint8_t)(outs.size() + (with_rowid ? 1 : 0));

@@ -56,10 +56,17 @@ struct Instr {            // 32 bytes
     uint8_t a_idx, b_idx;     // COL: staged slot; TMP: temporary index
     uint8_t dst_kind, dst_idx;  // OPK_ACC or OPK_TMP k
     uint8_t aux;          // CAST: target type; else AUX_*_NULL flags of literal operands
-    uint8_t pad[7];
+    uint8_t fast;         // 0 = generic step; else 1 + ((pair * 4 + class) * 3 + type): a fully specialised handler
+    uint8_t pad[6];
     uint64_t a_lit, b_lit;  // literal bits when *_kind == OPK_LIT
 };
 static_assert(sizeof(Instr) == 32, "Instr layout");
+
+// Fast handlers (filter_project.cu): operand pair x operator class x type, results in the accumulator.
+enum : uint8_t { FP_PAIR_COL_LIT = 0, FP_PAIR_COL_COL = 1, FP_PAIR_ACC_LIT = 2, FP_PAIR_ACC_COL = 3 };
+enum : uint8_t { FP_CLS_CMP = 0, FP_CLS_ADD = 1, FP_CLS_SUB = 2, FP_CLS_MUL = 3 };
+enum : uint8_t { FP_TY_I32 = 0, FP_TY_I64 = 1, FP_TY_F64 = 2 };
+constexpr uint8_t kFastMov32 = 49, kFastMov64 = 50;   // bare column pass-through, by width
 
 // literal flags carried in `aux` for non-CAST ops
 enum : uint8_t { AUX_A_NULL = 1, AUX_B_NULL = 2 };

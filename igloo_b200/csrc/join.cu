@@ -586,9 +586,9 @@ __global__ void __launch_bounds__(kFlatThreads, 3) join_probe_flat_kernel(const 
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint64_t bmask = P.table.mask >> 1;
     const long long nchunks = (P.nrows + kFlatChunk - 1) / kFlatChunk;
-    const uint8_t* keys = P.left[P.key_col];
     const Slot* slots = P.table.slots;
-    const int tshift = P.table.shift;
+    const int tshift = P.table.shift + 1;   // slot index -> bucket index
+    const int lrow = warp * (32 * kFlatRows) + lane;   // this lane's first row inside a chunk
     for (long long it = 0;; ++it) {
         if ((it % kFlatClaim) == 0) {
             if (threadIdx.x == 0) s_chunk = (long long)atomicAdd(P.ticket, 1u) * kFlatClaim;
@@ -596,45 +596,60 @@ __global__ void __launch_bounds__(kFlatThreads, 3) join_probe_flat_kernel(const 
         }
         const long long chunk = s_chunk + (it % kFlatClaim);
         if (chunk >= nchunks) break;   // claims only grow: nothing is left for this CTA
-        const long long row0 = chunk * kFlatChunk + warp * (32 * kFlatRows) + lane;
-        uint64_t raw[kFlatRows], k[kFlatRows], b[kFlatRows];
+        const long long cbase = chunk * kFlatChunk;                       // uniform
+        const int nvalid = (int)min((long long)kFlatChunk, P.nrows - cbase);   // rows of this chunk that exist
+        uint64_t raw[kFlatRows], k[kFlatRows];
         unsigned long long val[kFlatRows];
         ulonglong4 q[kFlatRows];
-        uint32_t pend = 0, hit = 0;
-#pragma unroll
-        for (int r = 0; r < kFlatRows; ++r) {
-            const long long row = row0 + r * 32;
-            raw[r] = 0; k[r] = kEmptyKey;
-            if (row < P.nrows) {
-                raw[r] = KEY_TYPE == IGL_T_I32 ? (uint64_t)((const uint32_t*)keys)[row] : ((const uint64_t*)keys)[row];
-                k[r] = canon_key(KEY_TYPE, raw[r]);
-                pend |= (k[r] != kEmptyKey ? 1u : 0u) << r;
-            }
-            b[r] = (mix64(k[r]) >> tshift) >> 1;
-        }
-#pragma unroll
-        for (int r = 0; r < kFlatRows; ++r)
-            if ((pend >> r) & 1u) q[r] = ld_nc_u64x4(slots + 2 * b[r]);
-        // the one key equal to the empty-slot sentinel lives in a side entry (rare: checked once per lane)
+        uint32_t live = 0;
         {
-            bool any_special = false;
-#pragma unroll
-            for (int r = 0; r < kFlatRows; ++r) any_special |= (row0 + r * 32 < P.nrows) && k[r] == kEmptyKey;
-            if (any_special && P.table.side->count[1]) {
-#pragma unroll
-                for (int r = 0; r < kFlatRows; ++r)
-                    if ((row0 + r * 32 < P.nrows) && k[r] == kEmptyKey) { hit |= 1u << r; val[r] = P.table.side->val[1]; }
-            }
-        }
-        while (pend) {
+            const uint8_t* kc = P.left[P.key_col] + (KEY_TYPE == IGL_T_I32 ? (cbase << 2) : (cbase << 3));   // uniform base, 32-bit offsets below
 #pragma unroll
             for (int r = 0; r < kFlatRows; ++r) {
-                if (!((pend >> r) & 1u)) continue;
-                const bool h0 = q[r].x == k[r], h1 = q[r].z == k[r];
-                const bool e0 = q[r].x == kEmptyKey, e1 = q[r].z == kEmptyKey;
-                if (h0 || (!e0 && h1)) { hit |= 1u << r; val[r] = h0 ? q[r].y : q[r].w; pend &= ~(1u << r); }
-                else if (e0 || e1) pend &= ~(1u << r);
-                else { b[r] = (b[r] + 1) & bmask; q[r] = ld_nc_u64x4(slots + 2 * b[r]); }
+                const int i = min(lrow + r * 32, nvalid - 1);   // clamped: the load is unconditional, the row just does not count
+                raw[r] = KEY_TYPE == IGL_T_I32 ? (uint64_t)((const uint32_t*)kc)[i] : ((const uint64_t*)kc)[i];
+                live |= ((lrow + r * 32) < nvalid ? 1u : 0u) << r;
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < kFlatRows; ++r) {
+            k[r] = canon_key(KEY_TYPE, raw[r]);
+            const uint64_t b = mix64(k[r]) >> tshift;
+            q[r] = ld_nc_u64x4(slots + 2 * b);
+        }
+        // first bucket, branch-free: most rows are decided here
+        uint32_t hit = 0, pend = 0;
+#pragma unroll
+        for (int r = 0; r < kFlatRows; ++r) {
+            const bool h0 = q[r].x == k[r], h1 = q[r].z == k[r];
+            const bool e0 = q[r].x == kEmptyKey, e1 = q[r].z == kEmptyKey;
+            const bool found = h0 || (h1 && !e0);
+            val[r] = h0 ? q[r].y : q[r].w;
+            hit |= (found ? 1u : 0u) << r;
+            pend |= ((found || e0 || e1) ? 0u : 1u) << r;
+        }
+        const uint32_t special = (k[0] == kEmptyKey) | ((k[1] == kEmptyKey) << 1) | ((k[2] == kEmptyKey) << 2) | ((k[3] == kEmptyKey) << 3);
+        hit &= live & ~special;
+        pend &= live & ~special;
+        if (special & live) {   // the key equal to the empty-slot sentinel lives in a side entry (rare)
+            if (P.table.side->count[1]) {
+#pragma unroll
+                for (int r = 0; r < kFlatRows; ++r)
+                    if (((special & live) >> r) & 1u) { hit |= 1u << r; val[r] = P.table.side->val[1]; }
+            }
+        }
+        if (pend) {   // collisions beyond the home bucket (rare at load factor 0.5)
+#pragma unroll
+            for (int r = 0; r < kFlatRows; ++r) {
+                uint64_t b = (mix64(k[r]) >> tshift);
+                while ((pend >> r) & 1u) {
+                    b = (b + 1) & bmask;
+                    const ulonglong4 n = ld_nc_u64x4(slots + 2 * b);
+                    if (n.x == k[r]) { hit |= 1u << r; val[r] = n.y; pend &= ~(1u << r); }
+                    else if (n.x == kEmptyKey) pend &= ~(1u << r);
+                    else if (n.z == k[r]) { hit |= 1u << r; val[r] = n.w; pend &= ~(1u << r); }
+                    else if (n.z == kEmptyKey) pend &= ~(1u << r);
+                }
             }
         }
         uint32_t hb[kFlatRows];
@@ -650,42 +665,49 @@ __global__ void __launch_bounds__(kFlatThreads, 3) join_probe_flat_kernel(const 
             s_base = tot ? atomicAdd(P.out_counter, (unsigned long long)tot) : 0ull;
         }
         __syncthreads();
-        unsigned long long pos = s_base;
-        for (int w = 0; w < warp; ++w) pos += s_wcnt[w];
+        const unsigned long long obase = s_base;   // uniform
+        unsigned int lpos = 0;
+        for (int w = 0; w < warp; ++w) lpos += s_wcnt[w];
         __syncthreads();   // s_wcnt / s_base are rewritten by the next chunk
-        // output positions of this lane's rows (only meaningful where hit)
-        unsigned long long p[kFlatRows];
+        // 32-bit output offsets inside this chunk's reservation
+        unsigned int p[kFlatRows];
 #pragma unroll
-        for (int r = 0; r < kFlatRows; ++r) { p[r] = pos + __popc(hb[r] & lt_mask); pos += __popc(hb[r]); }
-        // column by column: the width test is uniform per column, the row loop is branch-free predication
+        for (int r = 0; r < kFlatRows; ++r) { p[r] = lpos + __popc(hb[r] & lt_mask); lpos += __popc(hb[r]); }
+        // column by column: uniform width test, unconditional (clamped) loads, predicated stores
         for (int c = 0; c < P.n_left; ++c) {
-            const uint8_t* src = P.left[c];
-            uint8_t* dst = (uint8_t*)P.out[c];
             const bool is_key = c == P.key_col;
             if (P.lshift[c] == 3) {
+                const uint64_t* src = (const uint64_t*)P.left[c] + cbase;
+                uint64_t* dst = (uint64_t*)P.out[c] + obase;
+                uint64_t v[kFlatRows];
 #pragma unroll
-                for (int r = 0; r < kFlatRows; ++r)
-                    if ((hit >> r) & 1u) st_cs_u64(dst + (p[r] << 3), is_key ? raw[r] : ((const uint64_t*)src)[row0 + r * 32]);
+                for (int r = 0; r < kFlatRows; ++r) v[r] = is_key ? raw[r] : src[min(lrow + r * 32, nvalid - 1)];
+#pragma unroll
+                for (int r = 0; r < kFlatRows; ++r) if ((hit >> r) & 1u) st_cs_u64(dst + p[r], v[r]);
             } else {
+                const uint32_t* src = (const uint32_t*)P.left[c] + cbase;
+                uint32_t* dst = (uint32_t*)P.out[c] + obase;
+                uint32_t v[kFlatRows];
 #pragma unroll
-                for (int r = 0; r < kFlatRows; ++r)
-                    if ((hit >> r) & 1u) st_cs_u32(dst + (p[r] << 2), is_key ? (uint32_t)raw[r] : ((const uint32_t*)src)[row0 + r * 32]);
+                for (int r = 0; r < kFlatRows; ++r) v[r] = is_key ? (uint32_t)raw[r] : src[min(lrow + r * 32, nvalid - 1)];
+#pragma unroll
+                for (int r = 0; r < kFlatRows; ++r) if ((hit >> r) & 1u) st_cs_u32(dst + p[r], v[r]);
             }
         }
         for (int c = 0; c < P.n_right; ++c) {
-            uint8_t* dst = (uint8_t*)P.out[P.n_left + c];
-            const uint8_t* src = P.right_data[c];
             const int mode = P.payload_col < 0 ? 2 : (c == P.payload_col ? 0 : 1);   // 0 inlined payload, 1 the key itself, 2 gather by row id
             if (P.rshift[c] == 3) {
+                const uint64_t* src = (const uint64_t*)P.right_data[c];
+                uint64_t* dst = (uint64_t*)P.out[P.n_left + c] + obase;
 #pragma unroll
                 for (int r = 0; r < kFlatRows; ++r)
-                    if ((hit >> r) & 1u)
-                        st_cs_u64(dst + (p[r] << 3), mode == 0 ? val[r] : mode == 1 ? raw[r] : ((const uint64_t*)src)[(uint32_t)val[r]]);
+                    if ((hit >> r) & 1u) st_cs_u64(dst + p[r], mode == 0 ? val[r] : mode == 1 ? raw[r] : src[(uint32_t)val[r]]);
             } else {
+                const uint32_t* src = (const uint32_t*)P.right_data[c];
+                uint32_t* dst = (uint32_t*)P.out[P.n_left + c] + obase;
 #pragma unroll
                 for (int r = 0; r < kFlatRows; ++r)
-                    if ((hit >> r) & 1u)
-                        st_cs_u32(dst + (p[r] << 2), mode == 0 ? (uint32_t)val[r] : mode == 1 ? (uint32_t)raw[r] : ((const uint32_t*)src)[(uint32_t)val[r]]);
+                    if ((hit >> r) & 1u) st_cs_u32(dst + p[r], mode == 0 ? (uint32_t)val[r] : mode == 1 ? (uint32_t)raw[r] : src[(uint32_t)val[r]]);
             }
         }
     }

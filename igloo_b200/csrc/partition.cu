@@ -178,6 +178,116 @@ struct RadixParams {
     unsigned long long* cursor;         // [nparts]
 };
 
+// One tile.  FULL = every one of the 4096 rows exists (all tiles but the last):
+// no per-row existence predicates, hence no divergence blocks in the hot loops.
+template <bool FULL>
+__device__ __forceinline__ void radix_tile(const RadixParams& P, uint8_t* stage, unsigned int* s_cnt, unsigned long long* s_gbase,
+                                           unsigned short* s_part, unsigned int* s_warp_tot, long long row0, int rows) {
+    const int nparts = 1 << P.log2_parts;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tid = threadIdx.x;
+    int part[kRadixRowsPerThread];
+    unsigned int rank[kRadixRowsPerThread];
+    uint64_t keyraw[kRadixRowsPerThread];
+    {
+        const uint8_t* kbase = P.src[P.key_col] + (P.key_type == IGL_T_I32 ? (row0 << 2) : (row0 << 3));   // uniform base, 32-bit offsets
+#pragma unroll
+        for (int r = 0; r < kRadixRowsPerThread; ++r) {   // all key loads first: 8 independent requests in flight per thread
+            const int li = FULL ? r * kRadixThreads + tid : min(r * kRadixThreads + tid, rows - 1);
+            keyraw[r] = P.key_type == IGL_T_I32 ? (uint64_t)((const uint32_t*)kbase)[li] : ((const uint64_t*)kbase)[li];
+        }
+    }
+    const int pshift = 64 - P.log2_parts;
+#pragma unroll
+    for (int r = 0; r < kRadixRowsPerThread; ++r) {
+        const bool ok = FULL || (r * kRadixThreads + tid) < rows;
+        part[r] = (int)(mix64(part_canon(P.key_type, keyraw[r])) >> pshift);
+        rank[r] = 0;
+        if (ok) rank[r] = atomicAdd(&s_cnt[part[r]], 1u);
+        else part[r] = -1;
+    }
+    __syncthreads();
+    // exclusive scan of s_cnt[0..nparts) by the CTA (nparts <= 1024 = 2 per thread) + global reservation
+    {
+        const int i0 = tid * 2;
+        unsigned int c[2];
+        unsigned int sum = 0;
+#pragma unroll
+        for (int q = 0; q < 2; ++q) { c[q] = (i0 + q < nparts) ? s_cnt[i0 + q] : 0; sum += c[q]; }
+        unsigned int inc = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_warp_tot[warp] = inc;
+        __syncthreads();
+        unsigned int ex = inc - sum;
+        for (int w = 0; w < warp; ++w) ex += s_warp_tot[w];
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            if (i0 + q < nparts) {
+                s_cnt[i0 + q] = ex;
+                s_gbase[i0 + q] = c[q] ? P.offsets[i0 + q] + atomicAdd(&P.cursor[i0 + q], (unsigned long long)c[q]) : 0ull;
+            }
+            ex += c[q];
+        }
+    }
+    __syncthreads();
+    // stage: rows land grouped by partition.  Column by column, so the width test is uniform.
+    unsigned int slot[kRadixRowsPerThread];
+#pragma unroll
+    for (int r = 0; r < kRadixRowsPerThread; ++r) {
+        slot[r] = 0;
+        if (FULL || part[r] >= 0) { slot[r] = s_cnt[part[r]] + rank[r]; s_part[slot[r]] = (unsigned short)part[r]; }
+    }
+    for (int c = 0; c < P.ncols; ++c) {
+        const bool is_key = c == P.key_col;
+        if (P.shift[c] == 3) {
+            uint64_t* sc = reinterpret_cast<uint64_t*>(stage + P.stage_off[c]);
+            const uint64_t* src = reinterpret_cast<const uint64_t*>(P.src[c]) + row0;
+            uint64_t v[kRadixRowsPerThread];
+#pragma unroll
+            for (int r = 0; r < kRadixRowsPerThread; ++r)
+                v[r] = is_key ? keyraw[r] : src[FULL ? r * kRadixThreads + tid : min(r * kRadixThreads + tid, rows - 1)];
+#pragma unroll
+            for (int r = 0; r < kRadixRowsPerThread; ++r) if (FULL || part[r] >= 0) sc[slot[r]] = v[r];
+        } else {
+            uint32_t* sc = reinterpret_cast<uint32_t*>(stage + P.stage_off[c]);
+            const uint32_t* src = reinterpret_cast<const uint32_t*>(P.src[c]) + row0;
+            uint32_t v[kRadixRowsPerThread];
+#pragma unroll
+            for (int r = 0; r < kRadixRowsPerThread; ++r)
+                v[r] = is_key ? (uint32_t)keyraw[r] : src[FULL ? r * kRadixThreads + tid : min(r * kRadixThreads + tid, rows - 1)];
+#pragma unroll
+            for (int r = 0; r < kRadixRowsPerThread; ++r) if (FULL || part[r] >= 0) sc[slot[r]] = v[r];
+        }
+    }
+    __syncthreads();
+    // write-out: consecutive threads -> consecutive slots -> runs of consecutive destination rows
+    unsigned long long d[kRadixRowsPerThread];
+#pragma unroll
+    for (int r = 0; r < kRadixRowsPerThread; ++r) {
+        const int sl = r * kRadixThreads + tid;
+        d[r] = 0;
+        if (FULL || sl < rows) { const int p = s_part[sl]; d[r] = s_gbase[p] + (unsigned)(sl - s_cnt[p]); }
+    }
+    for (int c = 0; c < P.ncols; ++c) {
+        if (P.shift[c] == 3) {
+            const uint64_t* sc = reinterpret_cast<const uint64_t*>(stage + P.stage_off[c]) + tid;
+            uint64_t* dst = reinterpret_cast<uint64_t*>(P.dst[c]);
+#pragma unroll
+            for (int r = 0; r < kRadixRowsPerThread; ++r) if (FULL || r * kRadixThreads + tid < rows) dst[d[r]] = sc[r * kRadixThreads];
+        } else {
+            const uint32_t* sc = reinterpret_cast<const uint32_t*>(stage + P.stage_off[c]) + tid;
+            uint32_t* dst = reinterpret_cast<uint32_t*>(P.dst[c]);
+#pragma unroll
+            for (int r = 0; r < kRadixRowsPerThread; ++r) if (FULL || r * kRadixThreads + tid < rows) dst[d[r]] = sc[r * kRadixThreads];
+        }
+    }
+    __syncthreads();
+}
+
 __global__ void __launch_bounds__(kRadixThreads, 2) radix_scatter_kernel(const __grid_constant__ RadixParams P) {
     extern __shared__ __align__(16) uint8_t stage[];
     __shared__ unsigned int s_cnt[kRadixMaxParts];     // count, then exclusive start
@@ -186,111 +296,13 @@ __global__ void __launch_bounds__(kRadixThreads, 2) radix_scatter_kernel(const _
     __shared__ unsigned int s_warp_tot[kRadixThreads / 32];
     const int nparts = 1 << P.log2_parts;
     const long long ntiles = (P.n + kRadixTile - 1) / kRadixTile;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         for (int p = threadIdx.x; p < nparts; p += kRadixThreads) s_cnt[p] = 0;
         __syncthreads();
         const long long row0 = tile * kRadixTile;
         const int rows = (int)min((long long)kRadixTile, P.n - row0);
-        int part[kRadixRowsPerThread];
-        unsigned int rank[kRadixRowsPerThread];
-        uint64_t keyraw[kRadixRowsPerThread];
-        const void* keys = P.src[P.key_col];
-#pragma unroll
-        for (int r = 0; r < kRadixRowsPerThread; ++r) {   // all key loads first: 8 independent requests in flight per thread
-            const int li = r * kRadixThreads + threadIdx.x;
-            keyraw[r] = 0;
-            if (li < rows)
-                keyraw[r] = P.key_type == IGL_T_I32 ? (uint64_t)(uint32_t)((const int32_t*)keys)[row0 + li] : ((const uint64_t*)keys)[row0 + li];
-        }
-#pragma unroll
-        for (int r = 0; r < kRadixRowsPerThread; ++r) {
-            const int li = r * kRadixThreads + threadIdx.x;
-            part[r] = -1;
-            if (li < rows) {
-                part[r] = (int)(mix64(part_canon(P.key_type, keyraw[r])) >> (64 - P.log2_parts));
-                rank[r] = atomicAdd(&s_cnt[part[r]], 1u);
-            }
-        }
-        __syncthreads();
-        // exclusive scan of s_cnt[0..nparts) by the CTA (nparts <= 1024 = 2 per thread) + global reservation
-        {
-            const int i0 = threadIdx.x * 2;
-            unsigned int c[2];
-            unsigned int sum = 0;
-#pragma unroll
-            for (int q = 0; q < 2; ++q) { c[q] = (i0 + q < nparts) ? s_cnt[i0 + q] : 0; sum += c[q]; }
-            unsigned int inc = sum;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const unsigned int t = __shfl_up_sync(0xffffffffu, inc, o);
-                if (lane >= o) inc += t;
-            }
-            if (lane == 31) s_warp_tot[warp] = inc;
-            __syncthreads();
-            unsigned int ex = inc - sum;
-            for (int w = 0; w < warp; ++w) ex += s_warp_tot[w];
-#pragma unroll
-            for (int q = 0; q < 2; ++q) {
-                if (i0 + q < nparts) {
-                    s_cnt[i0 + q] = ex;
-                    s_gbase[i0 + q] = c[q] ? P.offsets[i0 + q] + atomicAdd(&P.cursor[i0 + q], (unsigned long long)c[q]) : 0ull;
-                }
-                ex += c[q];
-            }
-        }
-        __syncthreads();
-        // stage: rows land grouped by partition.  Column by column, so the width test is
-        // uniform and the row loop is straight predicated code.
-        unsigned int slot[kRadixRowsPerThread];
-#pragma unroll
-        for (int r = 0; r < kRadixRowsPerThread; ++r) {
-            slot[r] = 0;
-            if (part[r] >= 0) { slot[r] = s_cnt[part[r]] + rank[r]; s_part[slot[r]] = (unsigned short)part[r]; }
-        }
-        for (int c = 0; c < P.ncols; ++c) {
-            const bool is_key = c == P.key_col;
-            if (P.shift[c] == 3) {
-                uint64_t* sc = reinterpret_cast<uint64_t*>(stage + P.stage_off[c]);
-                const uint64_t* src = reinterpret_cast<const uint64_t*>(P.src[c]) + row0 + threadIdx.x;
-                uint64_t v[kRadixRowsPerThread];
-#pragma unroll
-                for (int r = 0; r < kRadixRowsPerThread; ++r) v[r] = (part[r] >= 0 && !is_key) ? src[r * kRadixThreads] : keyraw[r];
-#pragma unroll
-                for (int r = 0; r < kRadixRowsPerThread; ++r) if (part[r] >= 0) sc[slot[r]] = v[r];
-            } else {
-                uint32_t* sc = reinterpret_cast<uint32_t*>(stage + P.stage_off[c]);
-                const uint32_t* src = reinterpret_cast<const uint32_t*>(P.src[c]) + row0 + threadIdx.x;
-                uint32_t v[kRadixRowsPerThread];
-#pragma unroll
-                for (int r = 0; r < kRadixRowsPerThread; ++r) v[r] = (part[r] >= 0 && !is_key) ? src[r * kRadixThreads] : (uint32_t)keyraw[r];
-#pragma unroll
-                for (int r = 0; r < kRadixRowsPerThread; ++r) if (part[r] >= 0) sc[slot[r]] = v[r];
-            }
-        }
-        __syncthreads();
-        // write-out: consecutive threads -> consecutive slots -> runs of consecutive destination rows
-        unsigned long long d[kRadixRowsPerThread];
-#pragma unroll
-        for (int r = 0; r < kRadixRowsPerThread; ++r) {
-            const int sl = r * kRadixThreads + threadIdx.x;
-            d[r] = 0;
-            if (sl < rows) { const int p = s_part[sl]; d[r] = s_gbase[p] + (unsigned)(sl - s_cnt[p]); }
-        }
-        for (int c = 0; c < P.ncols; ++c) {
-            if (P.shift[c] == 3) {
-                const uint64_t* sc = reinterpret_cast<const uint64_t*>(stage + P.stage_off[c]) + threadIdx.x;
-                uint64_t* dst = reinterpret_cast<uint64_t*>(P.dst[c]);
-#pragma unroll
-                for (int r = 0; r < kRadixRowsPerThread; ++r) if (r * kRadixThreads + (int)threadIdx.x < rows) dst[d[r]] = sc[r * kRadixThreads];
-            } else {
-                const uint32_t* sc = reinterpret_cast<const uint32_t*>(stage + P.stage_off[c]) + threadIdx.x;
-                uint32_t* dst = reinterpret_cast<uint32_t*>(P.dst[c]);
-#pragma unroll
-                for (int r = 0; r < kRadixRowsPerThread; ++r) if (r * kRadixThreads + (int)threadIdx.x < rows) dst[d[r]] = sc[r * kRadixThreads];
-            }
-        }
-        __syncthreads();
+        if (rows == kRadixTile) radix_tile<true>(P, stage, s_cnt, s_gbase, s_part, s_warp_tot, row0, rows);
+        else radix_tile<false>(P, stage, s_cnt, s_gbase, s_part, s_warp_tot, row0, rows);
     }
 }
 
