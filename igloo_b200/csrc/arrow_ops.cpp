@@ -405,7 +405,7 @@ int32_t fp_flush(igl_op* op) {
             // K2s: offsets (lengths + scan) now, bytes once the total is known
             const igl_dev_col& src = dev[sp.index];
             void* d_off = nullptr; void* scratch = nullptr; void* vbytes = nullptr;
-            const size_t sbytes = 256 + ((size_t)n_out / 2048 + 2) * 8;
+            const size_t sbytes = 256 + ((size_t)n_out / 2048 + 8) * 8;
             rc = pool_alloc(ctx, pad64((size_t)(n_out + 1) * 4), &d_off);
             if (rc >= 0) { to_free.push_back(d_off); rc = pool_alloc(ctx, sbytes, &scratch); }
             if (rc >= 0) { to_free.push_back(scratch); if (src.validity) { rc = pool_alloc(ctx, pad64((size_t)n_out + 1), &vbytes); if (rc >= 0) to_free.push_back(vbytes); } }

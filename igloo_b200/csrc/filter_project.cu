@@ -827,7 +827,7 @@ int32_t igl_fp_launch(igl_fp* fp, const igl_dev_col* in, int64_t nrows, igl_dev_
         P.T.valid[s] = fp->has_nulls ? in[c].validity : nullptr;
     }
     // scratch: header + status words
-    size_t need = 256 + (size_t)std::max<int64_t>(P.T.ntiles, 1) * 8;
+    size_t need = 256 + (size_t)scan_scratch_words(P.T.ntiles) * 8;
     if (need > fp->scratch_bytes) {
         if (fp->scratch) pool_free(ctx, fp->scratch);
         fp->scratch = nullptr; fp->scratch_bytes = 0;
@@ -1018,7 +1018,7 @@ extern "C" int32_t igl_fp_run_static(igl_fp* fp, const igl_dev_col* in, int64_t 
         P.out_valid[j] = nullptr;
     }
     if (nrows == 0) { if (out_rows) *out_rows = 0; return IGL_OK; }
-    const size_t need = 256 + (size_t)P.T.ntiles * 8;   // <= kFpStaticScratchBytes by the row limit
+    const size_t need = 256 + (size_t)scan_scratch_words(P.T.ntiles) * 8;   // <= kFpStaticScratchBytes by the row limit
     P.T.hdr = (PipeHeader*)scratch;
     P.T.status = (uint64_t*)((uint8_t*)scratch + 256);
     IGL_CUDA_OK(cudaMemsetAsync(scratch, 0, need, st));   // ticket, error flags, count and every status word start at zero

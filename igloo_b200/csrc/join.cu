@@ -1052,7 +1052,7 @@ int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_
         P.T.data[c] = (const uint8_t*)left[c].data;
         P.T.valid[c] = j->has_nulls ? left[c].validity : nullptr;
     }
-    size_t need = 256 + (size_t)P.T.ntiles * 8;
+    size_t need = 256 + (size_t)scan_scratch_words(P.T.ntiles) * 8;
     if (need > j->scratch_bytes) {
         if (j->scratch) pool_free(ctx, j->scratch);
         j->scratch = nullptr; j->scratch_bytes = 0;
@@ -1107,6 +1107,8 @@ int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_
     }
     IGL_CUDA_OK(cudaMemcpyAsync(j->host_hdr, j->scratch, sizeof(PipeHeader), cudaMemcpyDeviceToHost, st));
     IGL_CUDA_OK(cudaStreamSynchronize(st));
+    if (j->host_hdr->err_flags & 0x80000000u)
+        return fail(IGL_ERR_UNSUPPORTED, "one probe tile expands to more than 2^31 output rows (extreme key skew on both sides); probe in smaller chunks");
     if (out_rows) *out_rows = (int64_t)j->host_hdr->out_count;
     return IGL_OK;
 }

@@ -66,9 +66,9 @@ __global__ void __launch_bounds__(kScanThreads) scan_offsets_kernel(int32_t* v, 
             total += warp_sums[w];
         }
         if (warp == 0) {
-            if (lane == 0) lookback_publish(status, tile, (uint64_t)total);
+            if (lane == 0) scan_publish(status, ntiles, tile, (uint64_t)total);
             __syncwarp();
-            const uint64_t b = lookback_exclusive(status, tile, (uint64_t)total, lane);
+            const uint64_t b = scan_exclusive(status, ntiles, tile, (uint64_t)total, lane);
             if (lane == 0) s_base = (long long)b;
         }
         __syncthreads();
@@ -102,7 +102,7 @@ int32_t utf8_gather_offsets(igl_ctx* ctx, const int32_t* src_off, const uint8_t*
                             long long n, int32_t* out_off, uint8_t* out_valid_bytes, void* scratch, size_t scratch_bytes,
                             cudaStream_t st) {
     const long long ntiles = (n + kScanTile - 1) / kScanTile;
-    const size_t need = 256 + (size_t)ntiles * 8;
+    const size_t need = 256 + (size_t)scan_scratch_words(ntiles) * 8;
     if (scratch_bytes < need) return fail(IGL_ERR_INTERNAL, "utf8 gather scratch too small");
     IGL_CUDA_OK(cudaMemsetAsync(scratch, 0, need, st));
     const int grid = (int)std::min<long long>((n + 255) / 256 + 1, (long long)ctx->sm_count * 8);

@@ -26,3 +26,6 @@ timeit("copy a only (proj)", None, [col("a")], lambda s: 8)
 timeit("filter+project T=500", col("a") < 500, proj, lambda s: 16 + 12 * s)
 timeit("filter+project T=10", col("a") < 10, proj, lambda s: 16 + 12 * s)
 timeit("filter only T=500", col("a") < 500, [], lambda s: 16 + 16 * s)
+timeit("proj a,b (S=4)", None, [col("a"), col("b")], lambda s: 16)
+timeit("filter a<500 -> a,b (S=4)", col("a") < 500, [col("a"), col("b")], lambda s: 8 + 8 * s)
+timeit("filter a<1000 -> a,b (all)", col("a") < 1000, [col("a"), col("b")], lambda s: 8 + 8 * s)
