@@ -141,7 +141,10 @@ struct TilePipe {
             if (lane >= o) inc += n;
         }
         total = __shfl_sync(0xffffffffu, inc, 31);
-        if (lane == 0) lookback_publish(T.status, tile, (uint64_t)total);
+        if (lane == 0) {
+            if (total >> 31) atomicOr(&T.hdr->err_flags, 0x80000000u);   // tile counts are published in 31 bits
+            scan_publish(T.status, T.ntiles, tile, (uint32_t)total);
+        }
     }
 
     __device__ void control_loop() {   // the whole control warp
@@ -156,7 +159,7 @@ struct TilePipe {
             const int s = it % S;
             const uint32_t ph = (uint32_t)(it / S) & 1u;
             if (SCAN) {
-                const uint64_t base = lookback_exclusive(T.status, tile, (uint64_t)total, lane);
+                const uint64_t base = scan_exclusive(T.status, T.ntiles, tile, (uint32_t)total, lane);
                 if (lane < kPipeComputeWarps) sh.local[it & 1][lane] = inc - c;
                 if (lane == 0) {
                     sh.base[it & 1] = base;
