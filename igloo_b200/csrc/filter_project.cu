@@ -43,7 +43,18 @@ struct FpParams {
     void* out_data[kMaxOut];
     uint8_t* out_valid[kMaxOut];   // byte-per-row validity (packed afterwards) or NULL
     uint8_t out_shift[kMaxOut];    // 2 / 3, or 0 = byte per row (boolean, packed afterwards)
+    // two-pass filter (FP_MASK writes, FP_APPLY reads): survivor bitmap in input row order, one
+    // bit per row, padded to whole tiles; exclusive output offset of every tile
+    uint8_t mask_slot;             // FP_APPLY: staged slot holding the tile's slice of the bitmap
+    uint32_t* mask_words;
 };
+
+// What one launch of fp_kernel does.
+//   FP_PROJECT  no predicate: output position == input position
+//   FP_SCAN     predicate + outputs in one pass, ordered by the in-kernel tile scan
+//   FP_MASK     predicate only: writes the survivor bitmap          (pass 1 of 2)
+//   FP_APPLY    outputs only: reads the bitmap and the tile offsets  (pass 2 of 2)
+enum FpMode : int { FP_PROJECT = 0, FP_SCAN = 1, FP_MASK = 2, FP_APPLY = 3 };
 
 template <int R>
 struct V {
@@ -398,11 +409,8 @@ __device__ __forceinline__ void fast_mov(const FpParams& P, const Instr& in, con
 
 // Runs expression `e` of the fused program on this lane's R rows.
 template <int R, bool HAS_NULLS>
-__device__ __forceinline__ V<R> run_expr(const FpParams& P, int e, const uint8_t* stage, int row0, int rows_in_tile,
+__device__ __forceinline__ V<R> run_expr(const FpParams& P, int e, const uint8_t* stage, int row0, uint32_t inrange,
                                          long long grow0, const WarpTmp& tmp, int lane) {
-    uint32_t inrange = 0;
-#pragma unroll
-    for (int r = 0; r < R; ++r) inrange |= ((row0 + r * 32) < rows_in_tile ? 1u : 0u) << r;
     uint64_t acc[R];
     uint32_t acc_ok = FullMask<R>::value;
 #pragma unroll
@@ -473,35 +481,73 @@ __device__ __forceinline__ V<R> run_expr(const FpParams& P, int e, const uint8_t
 template <int R>
 struct FpTile {
     const uint8_t* stage;
-    long long row_begin;
-    int rows;
+    long long row_begin;   // first row of the staged tile
+    int rows;              // rows in the staged tile
+    int row_off;           // first row of the sub-tile being worked on, relative to row_begin
     uint32_t keep[R];   // ballots: bit = lane whose row (r*32 + lane) survives
     int count;
 };
 
+// Bit r of the result = row (row0 + 32 r) exists in this tile.
+template <int R>
+__device__ __forceinline__ uint32_t rows_in_range(int row0, int rows_in_tile) {
+    uint32_t m = 0;
+#pragma unroll
+    for (int r = 0; r < R; ++r) m |= ((row0 + r * 32) < rows_in_tile ? 1u : 0u) << r;
+    return m;
+}
+
 template <int R, bool HAS_PRED, bool HAS_NULLS>
 __device__ __forceinline__ void fp_count(const FpParams& P, FpTile<R>& t, int warp, int lane, const WarpTmp& tmp) {
-    const int row0 = warp * (32 * R) + lane;
+    const int row0 = t.row_off + warp * (32 * R) + lane;
     V<R> m;
     const bool owner = warp < P.T.active_warps;   // warp-uniform
-    if (HAS_PRED && owner) m = run_expr<R, HAS_NULLS>(P, 0, t.stage, row0, t.rows, t.row_begin + row0, tmp, lane);
+    const uint32_t inrange = rows_in_range<R>(row0, t.rows);
+    if (HAS_PRED && owner) m = run_expr<R, HAS_NULLS>(P, 0, t.stage, row0, inrange, t.row_begin + row0, tmp, lane);
     t.count = 0;
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-        bool k = owner && (row0 + r * 32) < t.rows;
+        bool k = owner && ((inrange >> r) & 1u);
         if (HAS_PRED) k = k && ((m.ok >> r) & 1) && (m.v[r] & 1);   // null mask => row dropped
         t.keep[r] = __ballot_sync(0xffffffffu, k);
         t.count += __popc(t.keep[r]);
     }
 }
 
-template <int R, bool HAS_PRED, bool HAS_NULLS>
+// FP_APPLY: the ballots come from the staged slice of the survivor bitmap (word w of the
+// slice = rows 32w .. 32w+31 of the tile = row group w % R of warp w / R).  Returns this
+// warp's offset inside the tile's output run.
+template <int R>
+__device__ __forceinline__ int fp_take_mask(const FpParams& P, FpTile<R>& t, int warp, int lane) {
+    const uint32_t* mw = reinterpret_cast<const uint32_t*>(t.stage + P.T.smem_off[P.mask_slot]) + (t.row_off >> 5);
+    // a short last tile copies only the bitmap bytes that exist: clip every word to the rows present
+    auto word = [&](int w) -> uint32_t {
+        const int left = t.rows - t.row_off - w * 32;
+        if (left <= 0) return 0u;
+        const uint32_t x = mw[w];
+        return left >= 32 ? x : (x & ((1u << left) - 1u));
+    };
+    const int first = warp * R;       // this warp's first word
+    int before = 0;
+    for (int w = lane; w < first; w += 32) before += __popc(word(w));
+    before = __reduce_add_sync(0xffffffffu, before);
+    t.count = 0;
+    const bool owner = warp < P.T.active_warps;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        t.keep[r] = owner ? word(first + r) : 0u;
+        t.count += __popc(t.keep[r]);
+    }
+    return before;
+}
+
+// E0 = index of the first output expression in the program.
+template <int R, int E0, bool HAS_NULLS>
 __device__ __forceinline__ void fp_write(const FpParams& P, const FpTile<R>& t, long long wbase, int warp, int lane,
                                          const WarpTmp& tmp) {
     if (t.count == 0) return;   // warp-uniform
     const uint32_t lt_mask = (1u << lane) - 1u;
-    const int row0 = warp * (32 * R) + lane;
-    const int e0 = HAS_PRED ? 1 : 0;
+    const int row0 = t.row_off + warp * (32 * R) + lane;
     // 32-bit offsets inside this warp's output run, computed once for all output columns
     uint32_t off[R];
     uint32_t mine = 0;
@@ -516,7 +562,9 @@ __device__ __forceinline__ void fp_write(const FpParams& P, const FpTile<R>& t, 
     }
     for (int j = 0; j < P.n_out; ++j) {
         const int osh = P.out_shift[j];
-        const V<R> val = run_expr<R, HAS_NULLS>(P, e0 + j, t.stage, row0, t.rows, t.row_begin + row0, tmp, lane);
+        // ProjectionExec only ever sees the rows FilterExec kept (physical_planner.rs:52-94):
+        // an output expression cannot fail on a row the predicate dropped
+        const V<R> val = run_expr<R, HAS_NULLS>(P, E0 + j, t.stage, row0, mine, t.row_begin + row0, tmp, lane);
         if (osh == 3) {
             uint64_t* od = reinterpret_cast<uint64_t*>(P.out_data[j]) + wbase;
 #pragma unroll
@@ -538,11 +586,11 @@ __device__ __forceinline__ void fp_write(const FpParams& P, const FpTile<R>& t, 
     }
 }
 
-template <int R, bool HAS_PRED, bool HAS_NULLS>
+template <int R, int MODE, bool HAS_NULLS>
 __global__ void __launch_bounds__(kPipeThreads, kPipeMinCtas) fp_kernel(const __grid_constant__ FpParams P) {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ PipeShared sh;
-    TilePipe<HAS_PRED, HAS_NULLS> pipe(P.T, sh, smem);
+    TilePipe<MODE == FP_SCAN, HAS_NULLS> pipe(P.T, sh, smem);
     pipe.init();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (warp == kPipeComputeWarps) { pipe.control_loop(); return; }
@@ -550,33 +598,146 @@ __global__ void __launch_bounds__(kPipeThreads, kPipeMinCtas) fp_kernel(const __
     tmp.vals = reinterpret_cast<uint64_t*>(smem + P.tmp_off) + (size_t)warp * P.n_tmp * (32 * R);
     tmp.oks = smem + P.tmp_off + (size_t)kPipeComputeWarps * P.n_tmp * 1024 + (size_t)warp * P.n_tmp * 32;
 
-    if (!HAS_PRED) {   // nothing to scan: output position == input position
+    if (MODE == FP_PROJECT) {   // nothing to scan: output position == input position
         for (int it = 0;; ++it) {
             FpTile<R> t;
             if (!pipe.acquire(it, t.stage, t.row_begin, t.rows)) break;
-            fp_count<R, false, HAS_NULLS>(P, t, warp, lane, tmp);
-            fp_write<R, false, HAS_NULLS>(P, t, t.row_begin + warp * (32 * R), warp, lane, tmp);
+            for (t.row_off = 0; t.row_off < t.rows; t.row_off += P.T.sub_rows) {
+                fp_count<R, false, HAS_NULLS>(P, t, warp, lane, tmp);
+                fp_write<R, 0, HAS_NULLS>(P, t, t.row_begin + t.row_off + warp * (32 * R), warp, lane, tmp);
+            }
             pipe.release(it);
         }
         return;
     }
-    // software pipeline: count(t+1) is issued before write(t)
+    if (MODE == FP_MASK) {      // pass 1: the predicate's ballots ARE the bitmap words
+        for (int it = 0;; ++it) {
+            FpTile<R> t;
+            if (!pipe.acquire(it, t.stage, t.row_begin, t.rows)) break;
+            for (t.row_off = 0; t.row_off < t.rows; t.row_off += P.T.sub_rows) {
+                fp_count<R, true, HAS_NULLS>(P, t, warp, lane, tmp);
+                if (warp < P.T.active_warps && lane < R) {
+                    uint32_t w = t.keep[0];
+#pragma unroll
+                    for (int r = 1; r < R; ++r) w = lane == r ? t.keep[r] : w;
+                    P.mask_words[((t.row_begin + t.row_off) >> 5) + warp * R + lane] = w;
+                }
+            }
+            pipe.release(it);
+        }
+        return;
+    }
+    if (MODE == FP_APPLY) {     // pass 2: every tile knows where its output starts
+        for (int it = 0;; ++it) {
+            FpTile<R> t;
+            if (!pipe.acquire(it, t.stage, t.row_begin, t.rows)) break;
+            // the tile's output offsets arrived with its columns (PipeCols::aux_table)
+            const unsigned long long* offs = reinterpret_cast<const unsigned long long*>(t.stage + P.T.aux_smem) +
+                                             ((t.row_begin / P.T.sub_rows) & 1);
+            int k = 0;
+            for (t.row_off = 0; t.row_off < t.rows; t.row_off += P.T.sub_rows, ++k) {
+                const unsigned long long tbase = offs[k];
+                const int before = fp_take_mask<R>(P, t, warp, lane);
+                fp_write<R, 0, HAS_NULLS>(P, t, (long long)tbase + before, warp, lane, tmp);
+            }
+            pipe.release(it);
+        }
+        return;
+    }
+    // FP_SCAN, software pipeline: count(t+1) is issued before write(t)
     FpTile<R> cur;
+    cur.row_off = 0;
     if (!pipe.acquire(0, cur.stage, cur.row_begin, cur.rows)) return;
     fp_count<R, true, HAS_NULLS>(P, cur, warp, lane, tmp);
     pipe.post_count(0, warp, cur.count);
     for (int it = 0;; ++it) {
         FpTile<R> nxt;
+        nxt.row_off = 0;
         const bool has_next = pipe.acquire(it + 1, nxt.stage, nxt.row_begin, nxt.rows);
         if (has_next) {
             fp_count<R, true, HAS_NULLS>(P, nxt, warp, lane, tmp);
             pipe.post_count(it + 1, warp, nxt.count);
         }
         const long long wbase = pipe.wait_base(it, warp);
-        fp_write<R, true, HAS_NULLS>(P, cur, wbase, warp, lane, tmp);
+        fp_write<R, 1, HAS_NULLS>(P, cur, wbase, warp, lane, tmp);
         pipe.release(it);
         if (!has_next) break;
         cur = nxt;
+    }
+}
+
+// Between the two passes: popcount of every tile's slice of the survivor bitmap ->
+// exclusive offsets (off[ntiles] = surviving rows, also left in the header).  1024 tiles
+// per CTA iteration, ordered across CTAs by the block-prefix scan.
+constexpr int kToThreads = 256;
+constexpr int kToPerThread = 4;
+constexpr int kToTile = kToThreads * kToPerThread;
+
+__global__ void __launch_bounds__(kToThreads) fp_tile_offsets_kernel(const uint4* __restrict__ mask, int quads_per_tile,
+                                                                     long long ntiles, unsigned long long* __restrict__ off,
+                                                                     PipeHeader* hdr, unsigned int* ticket, uint64_t* status) {
+    __shared__ unsigned int warp_sums[kToThreads / 32];
+    __shared__ unsigned long long s_base;
+    __shared__ long long s_tile;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long long nscan = (ntiles + kToTile - 1) / kToTile;
+    while (true) {
+        if (threadIdx.x == 0) s_tile = (long long)atomicAdd(ticket, 1u);
+        __syncthreads();
+        const long long st = s_tile;
+        if (st >= nscan) break;
+        const long long base_i = st * kToTile + (long long)threadIdx.x * kToPerThread;
+        unsigned int x[kToPerThread];
+        unsigned int run = 0;
+#pragma unroll
+        for (int k = 0; k < kToPerThread; ++k) {
+            const long long i = base_i + k;
+            unsigned int c = 0;
+            if (i < ntiles) {
+                const uint4* q = mask + i * quads_per_tile;
+                for (int j = 0; j < quads_per_tile; ++j) {
+                    const uint4 v = q[j];
+                    c += __popc(v.x) + __popc(v.y) + __popc(v.z) + __popc(v.w);
+                }
+            }
+            x[k] = run;      // exclusive inside the thread
+            run += c;
+        }
+        unsigned int inc = run;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) warp_sums[warp] = inc;
+        __syncthreads();
+        unsigned int wprefix = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < kToThreads / 32; ++w) {
+            if (w < warp) wprefix += warp_sums[w];
+            total += warp_sums[w];
+        }
+        if (warp == 0) {
+            if (lane == 0) scan_publish(status, nscan, st, total);
+            __syncwarp();
+            const uint64_t b = scan_exclusive(status, nscan, st, total, lane);
+            if (lane == 0) {
+                s_base = b;
+                if (st == nscan - 1) {
+                    off[ntiles] = b + total;
+                    hdr->out_count = (long long)(b + total);
+                    hdr->ticket = 0;      // pass 1 is over; pass 2 claims its tiles from zero again
+                }
+            }
+        }
+        __syncthreads();
+        const unsigned long long o0 = s_base + wprefix + (inc - run);
+#pragma unroll
+        for (int k = 0; k < kToPerThread; ++k) {
+            const long long i = base_i + k;
+            if (i < ntiles) off[i] = o0 + x[k];
+        }
+        __syncthreads();
     }
 }
 
@@ -608,19 +769,28 @@ cudaError_t launch_pack_bits(const uint8_t* bytes, uint32_t* bits, const long lo
 
 using namespace igl;
 
-struct igl_fp {
-    igl_ctx* ctx = nullptr;
-    FpParams params{};
-    bool has_pred = false, has_nulls = false;
-    int rows_per_lane = 4;
-    int n_in = 0;
-    std::vector<int> in_types;
+// One compiled launch shape: the lowered program, its staged columns and ring geometry.
+struct FpProgram {
+    FpParams P{};
+    int mode = FP_PROJECT;
     std::vector<int> slot_of_col;            // schema column -> staged slot, -1 = not read
-    std::vector<int> out_types;
-    std::vector<uint8_t> out_nullable;
+    int rows_per_lane = 4;
     size_t smem_bytes = 0;
     int grid_cap = 0;
-    // scratch (grow-only): header + tile status words; temp byte planes for bit outputs
+};
+
+struct igl_fp {
+    igl_ctx* ctx = nullptr;
+    FpProgram one;                           // FP_PROJECT, or FP_SCAN: predicate and outputs in one pass
+    FpProgram mask, apply;                   // FP_MASK + FP_APPLY: the two-pass form of the same operator
+    bool two_pass_ok = false;
+    int two_pass_mode = -1;                  // IGL_FP_TWO_PASS: 0 never, 1 whenever possible, -1 by input size
+    bool has_pred = false, has_nulls = false;
+    int n_in = 0;
+    std::vector<int> in_types;
+    std::vector<int> out_types;
+    std::vector<uint8_t> out_nullable;
+    // scratch (grow-only): header + scan words (+ tile offsets and survivor bitmap); byte planes for bit outputs
     void* scratch = nullptr;
     size_t scratch_bytes = 0;
     std::vector<void*> tmp_bytes;            // per output: boolean byte plane
@@ -636,14 +806,143 @@ namespace {
 
 typedef void (*fp_kernel_t)(const FpParams);
 
-fp_kernel_t pick_kernel(int rows_per_lane, bool pred, bool nulls) {
-    if (rows_per_lane == 4) {
-        if (pred) return nulls ? fp_kernel<4, true, true> : fp_kernel<4, true, false>;
-        return nulls ? fp_kernel<4, false, true> : fp_kernel<4, false, false>;
+template <int R, bool NULLS>
+fp_kernel_t pick_mode(int mode) {
+    switch (mode) {
+        case FP_PROJECT: return fp_kernel<R, FP_PROJECT, NULLS>;
+        case FP_SCAN: return fp_kernel<R, FP_SCAN, NULLS>;
+        case FP_MASK: return fp_kernel<R, FP_MASK, NULLS>;
+        default: return fp_kernel<R, FP_APPLY, NULLS>;
     }
-    if (pred) return nulls ? fp_kernel<1, true, true> : fp_kernel<1, true, false>;
-    return nulls ? fp_kernel<1, false, true> : fp_kernel<1, false, false>;
 }
+
+fp_kernel_t pick_kernel(int rows_per_lane, int mode, bool nulls) {
+    if (rows_per_lane == 4) return nulls ? pick_mode<4, true>(mode) : pick_mode<4, false>(mode);
+    return nulls ? pick_mode<1, true>(mode) : pick_mode<1, false>(mode);
+}
+
+// Lowers `exprs` (expression 0.. in order; the outputs start at `first_out`) against the
+// input schema and lays out the shared-memory ring.  `mask_col` stages one more bit-packed
+// column (the survivor bitmap) behind the referenced inputs.  `force_r` = 0 lets the
+// geometry pick rows per lane.  Returns IGL_ERR_UNSUPPORTED when the shape does not fit.
+int32_t build_program(igl_ctx* ctx, const int32_t* in_types, const uint8_t* in_nullable, int n_in,
+                      const std::vector<const igl_expr*>& exprs, size_t first_out, bool with_rowid, bool mask_col,
+                      int force_r, bool has_nulls, int mode, FpProgram& prog) {
+    prog.mode = mode;
+    FpParams& P = prog.P;
+    std::vector<bool> used(n_in, false);
+    for (auto* e : exprs) referenced_columns(*e, used);
+    prog.slot_of_col.assign(n_in, -1);
+    uint8_t shifts[kMaxCols + 1] = {};
+    int nslots = 0;
+    for (int c = 0; c < n_in; ++c) {
+        if (!used[c]) continue;
+        if (nslots >= kMaxCols) return fail(IGL_ERR_UNSUPPORTED, "more than %d input columns referenced", kMaxCols);
+        const int t = in_types[c];
+        if (t == IGL_T_UTF8) return fail(IGL_ERR_UNSUPPORTED, "Utf8 columns cannot be read by device expressions");
+        shifts[nslots] = t == IGL_T_BOOL ? 0xFF : (t == IGL_T_I32 ? 2 : 3);
+        prog.slot_of_col[c] = nslots++;
+    }
+    (void)in_nullable;
+    if (mask_col) {
+        if (nslots >= kMaxCols) return fail(IGL_ERR_UNSUPPORTED, "no staged slot left for the survivor bitmap");
+        shifts[nslots] = 0xFF;
+        P.mask_slot = (uint8_t)nslots++;
+    }
+
+    std::vector<Instr> code;
+    int n_tmp = 0;
+    for (size_t i = 0; i < exprs.size(); ++i) {
+        LoweredExpr le;
+        IGL_TRY(lower_expr(*exprs[i], code, le));
+        P.expr_first[i] = (uint8_t)le.first;
+        P.expr_count[i] = (uint8_t)le.count;
+        n_tmp = std::max(n_tmp, le.n_tmp);
+    }
+    const size_t n_out_exprs = exprs.size() - first_out;
+    if (with_rowid) {   // extra Int32 output: the input row index of every surviving row
+        Instr in{};
+        in.op = IOP_ROWID; in.type = IGL_T_I32; in.dst_kind = OPK_ACC;
+        P.expr_first[exprs.size()] = (uint8_t)code.size();
+        P.expr_count[exprs.size()] = 1;
+        code.push_back(in);
+    }
+    if ((int)code.size() > kMaxInstr) return fail(IGL_ERR_UNSUPPORTED, "fused operator exceeds %d instructions", kMaxInstr);
+    for (auto& in : code) {  // schema column index -> staged slot
+        if (in.a_kind == OPK_COL) in.a_idx = (uint8_t)prog.slot_of_col[in.a_idx];
+        if (in.b_kind == OPK_COL) in.b_idx = (uint8_t)prog.slot_of_col[in.b_idx];
+    }
+    // fast-handler ids (only used by the no-null kernels; see fast_step)
+    for (auto& in : code) {
+        in.fast = 0;
+        if (in.dst_kind != OPK_ACC) continue;
+        int pair = -1;
+        if (in.a_kind == OPK_COL && in.b_kind == OPK_LIT) pair = FP_PAIR_COL_LIT;
+        else if (in.a_kind == OPK_COL && in.b_kind == OPK_COL) pair = FP_PAIR_COL_COL;
+        else if (in.a_kind == OPK_ACC && in.b_kind == OPK_LIT) pair = FP_PAIR_ACC_LIT;
+        else if (in.a_kind == OPK_ACC && in.b_kind == OPK_COL) pair = FP_PAIR_ACC_COL;
+        const int ty = in.type == IGL_T_I32 ? FP_TY_I32 : in.type == IGL_T_I64 ? FP_TY_I64 : in.type == IGL_T_F64 ? FP_TY_F64 : -1;
+        int cls = -1;
+        if (in.op >= IGL_OP_EQ && in.op <= IGL_OP_GE) cls = FP_CLS_CMP;
+        else if (in.op == IGL_OP_ADD) cls = FP_CLS_ADD;
+        else if (in.op == IGL_OP_SUB) cls = FP_CLS_SUB;
+        else if (in.op == IGL_OP_MUL) cls = FP_CLS_MUL;
+        if (pair >= 0 && ty >= 0 && cls >= 0 && !(in.aux & (AUX_A_NULL | AUX_B_NULL))) in.fast = (uint8_t)(1 + (pair * 4 + cls) * 3 + ty);
+        else if (in.op == IOP_MOV && in.a_kind == OPK_COL && in.b_kind == OPK_NONE && !(in.aux & AUX_A_NULL)) {
+            const int sh = shifts[in.a_idx];
+            if (sh == 2) in.fast = kFastMov32; else if (sh == 3) in.fast = kFastMov64;
+        }
+    }
+    memcpy(P.code, code.data(), code.size() * sizeof(Instr));
+    P.n_out = (uint8_t)(n_out_exprs + (with_rowid ? 1 : 0));
+    for (size_t j = 0; j < n_out_exprs; ++j) {
+        const int t = exprs[first_out + j]->type;
+        P.out_shift[j] = t == IGL_T_BOOL ? 0 : (t == IGL_T_I32 ? 2 : 3);
+    }
+    if (with_rowid) P.out_shift[n_out_exprs] = 2;
+
+    // shared-memory ring geometry (+ per-warp temporaries behind the ring)
+    const uint32_t tmp_bytes = (uint32_t)n_tmp * kPipeComputeWarps * (1024 + 32);
+    PipeGeometry geo = pipe_geometry(shifts, nslots, P.T, tmp_bytes, force_r, mode == FP_SCAN ? 1 : 8);
+    if (!geo.ok) return fail(IGL_ERR_UNSUPPORTED, "referenced columns need %u bytes per tile; too wide for one pass", geo.stage_bytes);
+    prog.rows_per_lane = geo.rows_per_lane;
+    P.n_tmp = (uint8_t)n_tmp;
+    P.tmp_off = geo.stage_bytes * geo.stages;
+    prog.smem_bytes = (size_t)geo.stage_bytes * geo.stages + tmp_bytes;
+
+    fp_kernel_t k = pick_kernel(prog.rows_per_lane, mode, has_nulls);
+    IGL_CUDA_OK(cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)prog.smem_bytes));
+    int per_sm = 0;
+    IGL_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)k, kPipeThreads, prog.smem_bytes));
+    if (per_sm < 1) return fail(IGL_ERR_INTERNAL, "filter/project kernel does not fit on an SM (smem %zu)", prog.smem_bytes);
+    prog.grid_cap = per_sm * ctx->sm_count;
+    return IGL_OK;
+}
+
+// Points a program's staged slots at this call's input columns.
+int32_t bind_inputs(const igl_fp* fp, const FpProgram& prog, const igl_dev_col* in, FpParams& P) {
+    for (int c = 0; c < fp->n_in; ++c) {
+        const int s = prog.slot_of_col[c];
+        if (s < 0) continue;
+        if (in[c].type != fp->in_types[c]) return fail(IGL_ERR_INVALID_ARG, "input column %d has type %d, plan expects %d", c, in[c].type, fp->in_types[c]);
+        if (((uintptr_t)in[c].data & 15) || ((uintptr_t)in[c].validity & 15))
+            return fail(IGL_ERR_INVALID_ARG, "input column %d is not 16-byte aligned", c);
+        P.T.data[s] = (const uint8_t*)in[c].data;
+        P.T.valid[s] = fp->has_nulls ? in[c].validity : nullptr;
+    }
+    return IGL_OK;
+}
+
+int32_t launch_program(igl_ctx* ctx, const FpProgram& prog, const FpParams& P, bool has_nulls, cudaStream_t st) {
+    fp_kernel_t k = pick_kernel(prog.rows_per_lane, prog.mode, has_nulls);
+    const int grid = (int)std::min<int64_t>(P.T.ntiles, prog.grid_cap);
+    k<<<grid, kPipeThreads, prog.smem_bytes, st>>>(P);
+    IGL_CUDA_OK(cudaGetLastError());
+    ctx->launches++;
+    return IGL_OK;
+}
+
+inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 }  // namespace
 
@@ -695,102 +994,49 @@ int32_t igl::fp_create_ex(igl_ctx* ctx, const int32_t* in_types, const uint8_t* 
         if (e->ncols != n_in) return fail(IGL_ERR_INVALID_ARG, "expression compiled against a different schema");
         if (e->type == IGL_T_UTF8) return fail(IGL_ERR_UNSUPPORTED, "Utf8 output columns go through the operator API (gather by row index)");
     }
+    if (pred && pred->ncols != n_in) return fail(IGL_ERR_INVALID_ARG, "predicate compiled against a different schema");
 
-    // which columns are read
-    std::vector<bool> used(n_in, false);
-    if (pred) referenced_columns(*pred, used);
-    for (auto* e : outs) referenced_columns(*e, used);
-    fp->slot_of_col.assign(n_in, -1);
-    FpParams& P = fp->params;
-    uint8_t shifts[kMaxCols] = {};
-    int nslots = 0;
-    for (int c = 0; c < n_in; ++c) {
-        if (!used[c]) continue;
-        if (nslots >= kMaxCols) return fail(IGL_ERR_UNSUPPORTED, "more than %d input columns referenced", kMaxCols);
-        int t = in_types[c];
-        if (t == IGL_T_UTF8) return fail(IGL_ERR_UNSUPPORTED, "Utf8 columns cannot be read by device expressions");
-        shifts[nslots] = t == IGL_T_BOOL ? 0xFF : (t == IGL_T_I32 ? 2 : 3);
-        fp->slot_of_col[c] = nslots++;
-        if (in_nullable && in_nullable[c]) fp->has_nulls = true;
+    // nulls anywhere (a nullable referenced column or a nullable result) select the null-aware kernels
+    {
+        std::vector<bool> used(n_in, false);
+        if (pred) referenced_columns(*pred, used);
+        for (auto* e : outs) referenced_columns(*e, used);
+        for (int c = 0; c < n_in; ++c) if (used[c] && in_nullable && in_nullable[c]) fp->has_nulls = true;
+        if (pred && pred->nullable) fp->has_nulls = true;
+        for (auto* e : outs) if (e->nullable) fp->has_nulls = true;
     }
-    if (pred && pred->nullable) fp->has_nulls = true;
-    for (auto* e : outs) if (e->nullable) fp->has_nulls = true;
-
-    // lower: expression 0 = predicate (if any), then the outputs
-    std::vector<Instr> code;
-    std::vector<const igl_expr*> all;
-    int n_tmp = 0;
-    if (pred) all.push_back(pred);
-    for (auto* e : outs) all.push_back(e);
-    for (size_t i = 0; i < all.size(); ++i) {
-        LoweredExpr le;
-        IGL_TRY(lower_expr(*all[i], code, le));
-        P.expr_first[i] = (uint8_t)le.first;
-        P.expr_count[i] = (uint8_t)le.count;
-        n_tmp = std::max(n_tmp, le.n_tmp);
-    }
-    if (with_rowid) {   // extra Int32 output: the input row index of every surviving row
-        Instr in{};
-        in.op = IOP_ROWID; in.type = IGL_T_I32; in.dst_kind = OPK_ACC;
-        P.expr_first[all.size()] = (uint8_t)code.size();
-        P.expr_count[all.size()] = 1;
-        code.push_back(in);
-        if ((int)code.size() > kMaxInstr) return fail(IGL_ERR_UNSUPPORTED, "fused operator exceeds %d instructions", kMaxInstr);
-    }
-    for (auto& in : code) {  // schema column index -> staged slot
-        if (in.a_kind == OPK_COL) in.a_idx = (uint8_t)fp->slot_of_col[in.a_idx];
-        if (in.b_kind == OPK_COL) in.b_idx = (uint8_t)fp->slot_of_col[in.b_idx];
-    }
-    // fast-handler ids (only used by the no-null kernels; see fast_step)
-    for (auto& in : code) {
-        in.fast = 0;
-        if (in.dst_kind != OPK_ACC) continue;
-        int pair = -1;
-        if (in.a_kind == OPK_COL && in.b_kind == OPK_LIT) pair = FP_PAIR_COL_LIT;
-        else if (in.a_kind == OPK_COL && in.b_kind == OPK_COL) pair = FP_PAIR_COL_COL;
-        else if (in.a_kind == OPK_ACC && in.b_kind == OPK_LIT) pair = FP_PAIR_ACC_LIT;
-        else if (in.a_kind == OPK_ACC && in.b_kind == OPK_COL) pair = FP_PAIR_ACC_COL;
-        const int ty = in.type == IGL_T_I32 ? FP_TY_I32 : in.type == IGL_T_I64 ? FP_TY_I64 : in.type == IGL_T_F64 ? FP_TY_F64 : -1;
-        int cls = -1;
-        if (in.op >= IGL_OP_EQ && in.op <= IGL_OP_GE) cls = FP_CLS_CMP;
-        else if (in.op == IGL_OP_ADD) cls = FP_CLS_ADD;
-        else if (in.op == IGL_OP_SUB) cls = FP_CLS_SUB;
-        else if (in.op == IGL_OP_MUL) cls = FP_CLS_MUL;
-        if (pair >= 0 && ty >= 0 && cls >= 0 && !(in.aux & (AUX_A_NULL | AUX_B_NULL))) in.fast = (uint8_t)(1 + (pair * 4 + cls) * 3 + ty);
-        else if (in.op == IOP_MOV && in.a_kind == OPK_COL && in.b_kind == OPK_NONE && !(in.aux & AUX_A_NULL)) {
-            const int sh = shifts[in.a_idx];
-            if (sh == 2) in.fast = kFastMov32; else if (sh == 3) in.fast = kFastMov64;
-        }
-    }
-    memcpy(P.code, code.data(), code.size() * sizeof(Instr));
-    P.n_out = (uint8_t)(outs.size() + (with_rowid ? 1 : 0));
-    for (size_t j = 0; j < outs.size(); ++j) {
-        fp->out_types.push_back(outs[j]->type);
-        fp->out_nullable.push_back(outs[j]->nullable ? 1 : 0);
-        P.out_shift[j] = outs[j]->type == IGL_T_BOOL ? 0 : (outs[j]->type == IGL_T_I32 ? 2 : 3);
+    for (auto* e : outs) {
+        fp->out_types.push_back(e->type);
+        fp->out_nullable.push_back(e->nullable ? 1 : 0);
     }
     if (with_rowid) {
         fp->out_types.push_back(IGL_T_I32);
         fp->out_nullable.push_back(0);
-        P.out_shift[outs.size()] = 2;
     }
 
-    // shared-memory ring geometry (+ per-warp temporaries behind the ring)
-    const uint32_t tmp_bytes = (uint32_t)n_tmp * kPipeComputeWarps * (1024 + 32);
-    PipeGeometry geo = pipe_geometry(shifts, nslots, P.T, tmp_bytes);
-    if (!geo.ok) return fail(IGL_ERR_UNSUPPORTED, "referenced columns need %u bytes per tile; too wide for one pass", geo.stage_bytes);
-    fp->rows_per_lane = geo.rows_per_lane;
-    P.n_tmp = (uint8_t)n_tmp;
-    P.tmp_off = geo.stage_bytes * geo.stages;
-    fp->smem_bytes = (size_t)geo.stage_bytes * geo.stages + tmp_bytes;
-
     DeviceGuard g(ctx->device);
-    fp_kernel_t k = pick_kernel(fp->rows_per_lane, fp->has_pred, fp->has_nulls);
-    IGL_CUDA_OK(cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fp->smem_bytes));
-    int per_sm = 0;
-    IGL_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)k, kPipeThreads, fp->smem_bytes));
-    if (per_sm < 1) return fail(IGL_ERR_INTERNAL, "filter/project kernel does not fit on an SM (smem %zu)", fp->smem_bytes);
-    fp->grid_cap = per_sm * ctx->sm_count;
+    std::vector<const igl_expr*> all;
+    if (pred) all.push_back(pred);
+    for (auto* e : outs) all.push_back(e);
+    IGL_TRY(build_program(ctx, in_types, in_nullable, n_in, all, pred ? 1 : 0, with_rowid, false, 0, fp->has_nulls,
+                          pred ? FP_SCAN : FP_PROJECT, fp->one));
+    if (pred) {
+        // Two-pass form: the predicate alone writes a survivor bitmap, a small kernel turns the
+        // bitmap into tile offsets, the outputs are then written with no ordering between CTAs.
+        // Both passes must cut the input into the same tiles.
+        if (const char* e = getenv("IGL_FP_TWO_PASS")) fp->two_pass_mode = atoi(e) ? 1 : 0;
+        std::vector<const igl_expr*> pe{pred};
+        int32_t r1 = build_program(ctx, in_types, in_nullable, n_in, pe, 1, false, false, 0, fp->has_nulls, FP_MASK, fp->mask);
+        int32_t r2 = r1 < 0 ? r1 : build_program(ctx, in_types, in_nullable, n_in, outs, 0, with_rowid, true, 0, fp->has_nulls, FP_APPLY, fp->apply);
+        if (r1 >= 0 && r2 >= 0 && fp->mask.rows_per_lane != fp->apply.rows_per_lane) {
+            FpProgram& wide = fp->mask.rows_per_lane == 4 ? fp->mask : fp->apply;
+            wide = FpProgram{};
+            const bool is_mask = &wide == &fp->mask;
+            r1 = is_mask ? build_program(ctx, in_types, in_nullable, n_in, pe, 1, false, false, 1, fp->has_nulls, FP_MASK, fp->mask)
+                         : build_program(ctx, in_types, in_nullable, n_in, outs, 0, with_rowid, true, 1, fp->has_nulls, FP_APPLY, fp->apply);
+        }
+        fp->two_pass_ok = r1 >= 0 && r2 >= 0 && fp->mask.P.T.sub_rows == fp->apply.P.T.sub_rows;
+    }
     IGL_CUDA_OK(cudaHostAlloc((void**)&fp->host_hdr, sizeof(PipeHeader), cudaHostAllocDefault));
     fp->tmp_bytes.assign(outs.size(), nullptr);
     fp->tmp_valid.assign(outs.size(), nullptr);
@@ -814,29 +1060,42 @@ int32_t igl_fp_launch(igl_fp* fp, const igl_dev_col* in, int64_t nrows, igl_dev_
     igl_ctx* ctx = fp->ctx;
     DeviceGuard g(ctx->device);
     cudaStream_t st = pick_stream(ctx, stream);
-    FpParams P = fp->params;
+    const int tile_rows = fp->one.P.T.tile_rows;
+    const long long ntiles1 = (nrows + tile_rows - 1) / tile_rows;
+    // One pass keeps every CTA in step with the slowest tile ahead of it; two passes stream at
+    // full speed but launch three kernels.  Small inputs stay on one pass.
+    bool two = fp->has_pred && fp->two_pass_ok &&
+               (fp->two_pass_mode == 1 || (fp->two_pass_mode < 0 && ntiles1 >= 4ll * fp->one.grid_cap));
+    const FpProgram& body = two ? fp->apply : fp->one;
+    FpParams P = body.P;
     P.T.nrows = nrows;
     P.T.ntiles = (nrows + P.T.tile_rows - 1) / P.T.tile_rows;
-    for (int c = 0; c < fp->n_in; ++c) {
-        int s = fp->slot_of_col[c];
-        if (s < 0) continue;
-        if (in[c].type != fp->in_types[c]) return fail(IGL_ERR_INVALID_ARG, "input column %d has type %d, plan expects %d", c, in[c].type, fp->in_types[c]);
-        if (((uintptr_t)in[c].data & 15) || ((uintptr_t)in[c].validity & 15))
-            return fail(IGL_ERR_INVALID_ARG, "input column %d is not 16-byte aligned", c);
-        P.T.data[s] = (const uint8_t*)in[c].data;
-        P.T.valid[s] = fp->has_nulls ? in[c].validity : nullptr;
+    IGL_TRY(bind_inputs(fp, body, in, P));
+    FpParams PM{};
+    if (two) {
+        PM = fp->mask.P;
+        PM.T.nrows = nrows;
+        PM.T.ntiles = (nrows + PM.T.tile_rows - 1) / PM.T.tile_rows;
+        IGL_TRY(bind_inputs(fp, fp->mask, in, PM));
     }
-    // scratch: header + status words
-    size_t need = 256 + (size_t)scan_scratch_words(P.T.ntiles) * 8;
+    // scratch: [header 256][offsets-kernel header 256][scan words][tile offsets][survivor bitmap]
+    // (the bitmap and the offsets are kept per sub-tile: the two passes may stage different numbers of them)
+    const long long nsub = (nrows + P.T.sub_rows - 1) / P.T.sub_rows;
+    const long long nscan = two ? (nsub + kToTile - 1) / kToTile : P.T.ntiles;
+    const size_t scan_bytes = align256((size_t)scan_scratch_words(nscan) * 8);
+    const size_t off_bytes = two ? align256((size_t)(nsub + 1) * 8 + 128) : 0;   // + slack: a stage copies up to 9 entries
+    const size_t mask_bytes = two ? align256((size_t)nsub * (P.T.sub_rows / 8) + 16) : 0;
+    const size_t need = 512 + scan_bytes + off_bytes + mask_bytes;
     if (need > fp->scratch_bytes) {
         if (fp->scratch) pool_free(ctx, fp->scratch);
         fp->scratch = nullptr; fp->scratch_bytes = 0;
         IGL_TRY(pool_alloc(ctx, need, &fp->scratch));
         fp->scratch_bytes = need;
     }
-    P.T.hdr = (PipeHeader*)fp->scratch;
-    P.T.status = (uint64_t*)((uint8_t*)fp->scratch + 256);
-    IGL_CUDA_OK(cudaMemsetAsync(fp->scratch, 0, fp->has_pred ? need : 256, st));
+    uint8_t* sb = (uint8_t*)fp->scratch;
+    P.T.hdr = (PipeHeader*)sb;
+    P.T.status = (uint64_t*)(sb + 512);
+    IGL_CUDA_OK(cudaMemsetAsync(fp->scratch, 0, fp->has_pred ? 512 + scan_bytes : 256, st));
     // outputs (+ byte planes for bit-packed results)
     const size_t nout = fp->out_types.size();
     bool any_tmp = false;
@@ -874,11 +1133,25 @@ int32_t igl_fp_launch(igl_fp* fp, const igl_dev_col* in, int64_t nrows, igl_dev_
     fp->launched = true;
     if (nrows == 0) return IGL_OK;
 
-    fp_kernel_t k = pick_kernel(fp->rows_per_lane, fp->has_pred, fp->has_nulls);
-    int grid = (int)std::min<int64_t>(P.T.ntiles, fp->grid_cap);
-    k<<<grid, kPipeThreads, fp->smem_bytes, st>>>(P);
-    IGL_CUDA_OK(cudaGetLastError());
-    ctx->launches++;
+    if (two) {
+        PipeHeader* hdr2 = (PipeHeader*)(sb + 256);
+        unsigned long long* tile_off = (unsigned long long*)(sb + 512 + scan_bytes);
+        uint8_t* mask = sb + 512 + scan_bytes + off_bytes;
+        PM.T.hdr = P.T.hdr;
+        PM.T.status = nullptr;
+        PM.mask_words = (uint32_t*)mask;
+        IGL_TRY(launch_program(ctx, fp->mask, PM, fp->has_nulls, st));
+        const int ogrid = (int)std::min<long long>(nscan, (long long)ctx->sm_count * 2);
+        fp_tile_offsets_kernel<<<ogrid, kToThreads, 0, st>>>((const uint4*)mask, P.T.sub_rows / 128, nsub, tile_off, P.T.hdr,
+                                                             &hdr2->ticket, P.T.status);
+        IGL_CUDA_OK(cudaGetLastError());
+        ctx->launches++;
+        P.T.aux_table = tile_off;
+        P.T.data[P.mask_slot] = mask;
+        P.T.valid[P.mask_slot] = nullptr;
+        P.T.status = nullptr;
+    }
+    IGL_TRY(launch_program(ctx, body, P, fp->has_nulls, st));
     const long long* n_ptr = fp->has_pred ? &P.T.hdr->out_count : nullptr;
     for (size_t j = 0; j < nout; ++j) {
         const bool want_valid = fp->has_nulls && fp->out_nullable[j];
@@ -1001,17 +1274,10 @@ extern "C" int32_t igl_fp_run_static(igl_fp* fp, const igl_dev_col* in, int64_t 
     cudaStream_t st = pick_stream(ctx, stream);
     void* scratch = nullptr;
     IGL_TRY(fp_static_scratch_ptr(ctx->device, &scratch));
-    FpParams P = fp->params;
+    FpParams P = fp->one.P;   // always the one-pass form: its scratch is bounded by the row limit alone
     P.T.nrows = nrows;
     P.T.ntiles = (nrows + P.T.tile_rows - 1) / P.T.tile_rows;
-    for (int c = 0; c < fp->n_in; ++c) {
-        const int s = fp->slot_of_col[c];
-        if (s < 0) continue;
-        if (in[c].type != fp->in_types[c]) return fail(IGL_ERR_INVALID_ARG, "input column %d has type %d, plan expects %d", c, in[c].type, fp->in_types[c]);
-        if (((uintptr_t)in[c].data & 15) || ((uintptr_t)in[c].validity & 15)) return fail(IGL_ERR_INVALID_ARG, "input column %d is not 16-byte aligned", c);
-        P.T.data[s] = (const uint8_t*)in[c].data;
-        P.T.valid[s] = fp->has_nulls ? in[c].validity : nullptr;
-    }
+    IGL_TRY(bind_inputs(fp, fp->one, in, P));
     for (size_t j = 0; j < nout; ++j) {
         if (!out[j].data) return fail(IGL_ERR_INVALID_ARG, "output column %zu has no data buffer", j);
         P.out_data[j] = out[j].data;
@@ -1022,11 +1288,7 @@ extern "C" int32_t igl_fp_run_static(igl_fp* fp, const igl_dev_col* in, int64_t 
     P.T.hdr = (PipeHeader*)scratch;
     P.T.status = (uint64_t*)((uint8_t*)scratch + 256);
     IGL_CUDA_OK(cudaMemsetAsync(scratch, 0, need, st));   // ticket, error flags, count and every status word start at zero
-    fp_kernel_t k = pick_kernel(fp->rows_per_lane, fp->has_pred, fp->has_nulls);
-    const int grid = (int)std::min<int64_t>(P.T.ntiles, fp->grid_cap);
-    k<<<grid, kPipeThreads, fp->smem_bytes, st>>>(P);
-    IGL_CUDA_OK(cudaGetLastError());
-    ctx->launches++;
+    IGL_TRY(launch_program(ctx, fp->one, P, fp->has_nulls, st));
     IGL_CUDA_OK(cudaMemcpyAsync(fp->host_hdr, scratch, sizeof(PipeHeader), cudaMemcpyDeviceToHost, st));
     IGL_CUDA_OK(cudaStreamSynchronize(st));
     const unsigned int ef = fp->host_hdr->err_flags;

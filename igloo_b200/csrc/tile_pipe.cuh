@@ -39,7 +39,7 @@ constexpr int kPipeThreads = (kPipeComputeWarps + 1) * 32;
 // rows per tile = compute warps * 32 lanes * R rows per lane (R = 4, or 1 for very wide
 // tables); always a multiple of 128 rows so bitmap slices stay 16-byte aligned
 constexpr int kPipeMinCtas = IGL_PIPE_MIN_CTAS;
-constexpr int kPipeMaxStages = 4;
+constexpr int kPipeMaxStages = 8;
 constexpr int kPipeMaxCols = 16;
 static_assert(kPipeComputeWarps <= 32, "per-tile warp counts are scanned by one warp");
 
@@ -56,11 +56,17 @@ struct PipeCols {
     uint32_t smem_off[kPipeMaxCols];
     uint32_t valid_off[kPipeMaxCols];
     uint8_t shift[kPipeMaxCols];   // log2(bytes per row); 0xFF = bit-packed boolean
-    uint8_t n_cols, n_stages, pad[2];
+    uint8_t n_cols, n_stages, sub_tiles, pad;
     uint32_t stage_bytes;
-    int tile_rows;                 // active warps * 32 * rows-per-lane, a multiple of 128
+    int sub_rows;                  // active warps * 32 * rows-per-lane, a multiple of 128: what the CTA works on at a time
+    int tile_rows;                 // sub_tiles * sub_rows: what one stage (one round of bulk copies) holds
     int active_warps;              // compute warps that own rows (all of them at 4 rows per lane)
     long long nrows, ntiles;
+    // optional per-sub-tile table (8 bytes per sub-tile, e.g. output offsets) whose entries for a
+    // tile are copied into the stage with the columns: aux_smem = stage offset of the copy, which
+    // starts at the even entry at or below the tile's first one
+    const unsigned long long* aux_table;
+    uint32_t aux_smem;
     PipeHeader* hdr;
     uint64_t* status;              // one word per tile (only when SCAN)
 };
@@ -100,9 +106,14 @@ struct TilePipe {
     // CTAs that reach them at about the same time.  (Claiming a CTA's first
     // stages as consecutive tickets would make its neighbour's first tile wait
     // for this CTA's LAST prefetched tile — a scan chain as long as the grid.)
+    // The ticket for the NEXT refill is drawn as soon as the current one is used, so the
+    // atomic's round trip to L2 overlaps the wait for a free stage.
+    unsigned int next_ticket = 0;
+
     __device__ void issue(int s, bool prologue) {   // one lane
         const long long t = prologue ? (long long)s * gridDim.x + blockIdx.x
-                                     : (long long)T.n_stages * gridDim.x + (long long)atomicAdd(&T.hdr->ticket, 1u);
+                                     : (long long)T.n_stages * gridDim.x + (long long)next_ticket;
+        if (!prologue || s == T.n_stages - 1) next_ticket = atomicAdd(&T.hdr->ticket, 1u);
         if (t >= T.ntiles) {
             sh.tile_of_stage[s] = -1;
             mbar_arrive(&sh.full_bar[s]);
@@ -119,7 +130,11 @@ struct TilePipe {
         };
         uint32_t total = 0;
         for (int c = 0; c < T.n_cols; ++c) total += col_bytes(c) + ((HAS_NULLS && T.valid[c]) ? bit_bytes : 0u);
+        const long long aux_first = (t * T.sub_tiles) & ~1ll;
+        const uint32_t aux_bytes = T.aux_table ? ((uint32_t)(T.sub_tiles + 1) * 8u + 15u) & ~15u : 0u;
+        total += aux_bytes;
         mbar_arrive_expect_tx(&sh.full_bar[s], total);
+        if (T.aux_table) bulk_g2s(stage + T.aux_smem, T.aux_table + aux_first, aux_bytes, &sh.full_bar[s]);
         for (int c = 0; c < T.n_cols; ++c) {
             const int shf = T.shift[c];
             const size_t goff = shf == 0xFF ? (size_t)(row_begin >> 3) : ((size_t)row_begin << shf);
@@ -225,25 +240,39 @@ struct PipeGeometry {
 // shift[c] per staged column; every column reserves a validity slice too.
 // `extra` = other dynamic shared memory the kernel needs per CTA.  Picks 4 rows
 // per lane when two stages fit (two CTAs per SM if possible), else 1 row per lane.
-inline PipeGeometry pipe_geometry(const uint8_t* shift, int ncols, PipeCols& T, uint32_t extra = 0) {
+// `max_sub` > 1 lets a narrow stage hold several sub-tiles, so the fixed cost of a stage
+// hand-over (ticket, copies, barriers) is paid once per sub_tiles * sub_rows rows.
+inline PipeGeometry pipe_geometry(const uint8_t* shift, int ncols, PipeCols& T, uint32_t extra = 0, int force_r = 0,
+                                  int max_sub = 1) {
     PipeGeometry g;
     const uint32_t budget2 = (226u << 10) / kPipeMinCtas - 2048u;   // per CTA when kPipeMinCtas share an SM
     const uint32_t budget1 = 220u << 10;                             // one CTA per SM
     for (int R : {4, 1}) {
+        if (force_r && R != force_r) continue;
         // 1 row per lane: only a multiple of 4 warps own rows, so the tile stays a multiple of 128 rows
         const int active = R == 4 ? kPipeComputeWarps : (kPipeComputeWarps / 4) * 4;
-        const uint32_t rows = (uint32_t)active * 32u * R;
+        const uint32_t sub_rows = (uint32_t)active * 32u * R;
         T.active_warps = active;
-        uint32_t off = 0;
-        for (int c = 0; c < ncols; ++c) {
-            const uint32_t b = shift[c] == 0xFF ? rows / 8 : rows << shift[c];
-            T.shift[c] = shift[c];
-            T.smem_off[c] = off; off += (b + 127u) & ~127u;
-            T.valid_off[c] = off; off += ((rows / 8) + 127u) & ~127u;
-        }
-        g.stage_bytes = off ? off : 128u;
+        T.sub_rows = (int)sub_rows;
+        auto layout = [&](uint32_t rows) {
+            uint32_t off = 0;
+            for (int c = 0; c < ncols; ++c) {
+                const uint32_t b = shift[c] == 0xFF ? rows / 8 : rows << shift[c];
+                T.shift[c] = shift[c];
+                T.smem_off[c] = off; off += (b + 127u) & ~127u;
+                T.valid_off[c] = off; off += ((rows / 8) + 127u) & ~127u;
+            }
+            return off ? off : 128u;
+        };
+        int sub = 1;
+        for (int k = max_sub; k > 1; k >>= 1)   // the most sub-tiles that still leave three stages for two CTAs per SM
+            if ((layout(sub_rows * k) + 128u) * 3 + extra <= budget2) { sub = k; break; }
+        g.stage_bytes = layout(sub_rows * sub);
+        T.aux_smem = g.stage_bytes;      // 128 bytes behind the columns, used when aux_table is set
+        g.stage_bytes += 128u;
         g.rows_per_lane = R;
-        T.tile_rows = (int)rows;
+        T.sub_tiles = (uint8_t)sub;
+        T.tile_rows = (int)(sub_rows * sub);
         if (g.stage_bytes * 2 + extra <= budget2) {
             const uint32_t st = (budget2 - extra) / g.stage_bytes;
             g.stages = (int)(st < (uint32_t)kPipeMaxStages ? st : kPipeMaxStages);

@@ -25,12 +25,22 @@ def _fields(tbl):
     return tight_fields(tbl)
 
 
-def gpu_filter_project(ctx, tbl, pred, proj):
+def gpu_filter_project(ctx, tbl, pred, proj, two_pass=None):
+    """two_pass: None = the library's own choice by input size; False / True force the one-pass
+    (in-kernel ordered scan) or two-pass (survivor bitmap + tile offsets) form of the filter."""
     from igloo_b200.device import DeviceColumn, FilterProject
     from igloo_b200.arrow import schema_of
     fields = _fields(tbl)
     cols = [DeviceColumn.from_arrow(tbl.column(i), ctx.device) for i in range(tbl.num_columns)]
-    fp = FilterProject(ctx, fields, pred, proj)
+    old = os.environ.pop("IGL_FP_TWO_PASS", None)
+    try:
+        if two_pass is not None:
+            os.environ["IGL_FP_TWO_PASS"] = "1" if two_pass else "0"
+        fp = FilterProject(ctx, fields, pred, proj)   # the switch is read when the plan is created
+    finally:
+        os.environ.pop("IGL_FP_TWO_PASS", None)
+        if old is not None:
+            os.environ["IGL_FP_TWO_PASS"] = old
     out, n = fp.run(cols, tbl.num_rows)
     arrays = [c.to_arrow(n) for c in out]
     return pa.Table.from_arrays(arrays, schema=schema_of(fp.out_fields))
@@ -47,8 +57,13 @@ def oracle_filter_project(tbl, pred, proj):
 
 
 def check(ctx, tbl, pred, proj, exact_order=True):
-    got = gpu_filter_project(ctx, tbl, pred, proj)
     want, _ = oracle_filter_project(tbl, pred, proj)
+    for two_pass in ([False, True] if pred is not None else [None]):
+        got = _check_one(gpu_filter_project(ctx, tbl, pred, proj, two_pass), want, exact_order)
+    return got
+
+
+def _check_one(got, want, exact_order):
     assert got.num_rows == want.num_rows
     assert [f.type for f in got.schema] == [f.type for f in want.schema]
     assert got.schema.names == want.schema.names
@@ -150,6 +165,22 @@ def test_wrapping_division_cast(ctx):
     # a null divisor row is not evaluated
     tn = pa.table({"a": pa.array([1, 2], pa.int32()), "b": pa.array([None, 1], pa.int32())})
     check(ctx, tn, None, [(col("a") / col("b")).alias("q")])
+
+
+def test_projection_sees_only_rows_the_filter_kept(ctx):
+    """Projection(Filter(x)): projection.rs evaluates its expressions on the batches filter.rs
+    already compacted, so `a / b WHERE b <> 0` succeeds although b holds zeros."""
+    from igloo_b200._lib import IglooCudaError
+    rng = np.random.default_rng(11)
+    n = 70_001
+    t = pa.table({"a": rng.integers(-1000, 1000, n).astype(np.int32), "b": rng.integers(-3, 4, n).astype(np.int32),
+                  "c": rng.integers(-2**40, 2**40, n).astype(np.int64)})
+    check(ctx, t, col("b") != lit(0, T_I32), [(col("a") / col("b")).alias("q"), (col("a") % col("b")).alias("r")])
+    check(ctx, t, (col("c") < lit(2**31, T_I64)) & (col("c") >= lit(-2**31, T_I64)), [col("c").cast(T_I32).alias("i")])
+    for two_pass in (False, True):   # ... and still fails when a kept row divides by zero
+        with pytest.raises(IglooCudaError) as e:
+            gpu_filter_project(ctx, t, col("b") >= lit(0, T_I32), [(col("a") / col("b")).alias("q")], two_pass)
+        assert e.value.code == -6
 
 
 def test_predicate_must_be_boolean(ctx):

@@ -23,9 +23,17 @@ def timeit(name, pred, pr, bytes_fn):
     print(f"{name:28s} kept={kept/n:.3f} ms={ms:.3f} GB/s={gb/ms*1e3:.0f} rows/s={n/ms/1e6:.1f}G", flush=True)
 timeit("projection only", None, proj, lambda s: 16 + 12)
 timeit("copy a only (proj)", None, [col("a")], lambda s: 8)
-timeit("filter+project T=500", col("a") < 500, proj, lambda s: 16 + 12 * s)
-timeit("filter+project T=10", col("a") < 10, proj, lambda s: 16 + 12 * s)
-timeit("filter only T=500", col("a") < 500, [], lambda s: 16 + 16 * s)
-timeit("proj a,b (S=4)", None, [col("a"), col("b")], lambda s: 16)
-timeit("filter a<500 -> a,b (S=4)", col("a") < 500, [col("a"), col("b")], lambda s: 8 + 8 * s)
-timeit("filter a<1000 -> a,b (all)", col("a") < 1000, [col("a"), col("b")], lambda s: 8 + 8 * s)
+for tp in ("0", "1"):
+    os.environ["IGL_FP_TWO_PASS"] = tp
+    print("IGL_FP_TWO_PASS=" + tp)
+    timeit("filter+project T=500", col("a") < 500, proj, lambda s: 16 + 12 * s)
+    timeit("filter+project T=10", col("a") < 10, proj, lambda s: 16 + 12 * s)
+    timeit("filter+project T=1000", col("a") < 1000, proj, lambda s: 16 + 12 * s)
+    timeit("filter only T=500", col("a") < 500, [], lambda s: 16 + 16 * s)
+    timeit("filter a<500 -> a,b", col("a") < 500, [col("a"), col("b")], lambda s: 8 + 8 * s)
+if len(sys.argv) > 2:
+    for m in (1 << 20, 1 << 22, 1 << 24, 1 << 26):
+        n = m
+        for tp in ("0", "1"):
+            os.environ["IGL_FP_TWO_PASS"] = tp
+            timeit(f"n={m} two_pass={tp} T=500", col("a") < 500, proj, lambda s: 16 + 12 * s)
