@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libigloo_cuda.so")
+# IGLOO_CUDA_LIB: load another build of the same library (kernel A/B experiments)
+LIB_PATH = os.environ.get("IGLOO_CUDA_LIB") or os.path.join(_HERE, "libigloo_cuda.so")
 
 IGL_OK, IGL_AGAIN, IGL_EOS = 0, 1, 2
 ERR_NAMES = {-1: "INVALID_ARG", -2: "UNSUPPORTED", -3: "OOM", -4: "CUDA", -5: "NCCL", -6: "DIV_BY_ZERO",

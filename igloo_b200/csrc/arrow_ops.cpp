@@ -243,7 +243,10 @@ struct Staging {
 };
 
 // ---- output batches ------------------------------------------------------------
-struct OutCol { int type = 0; void* data = nullptr; uint8_t* valid = nullptr; int32_t* off = nullptr; int64_t null_count = 0; };
+struct OutCol {
+    int type = 0; void* data = nullptr; uint8_t* valid = nullptr; int32_t* off = nullptr; int64_t null_count = 0;
+    bool alias = false;   // `data` belongs to another column of the same batch (two columns, one host buffer)
+};
 struct OutBatch { int64_t nrows = 0; std::vector<OutCol> cols; };
 
 struct ExportHolder {
@@ -276,7 +279,8 @@ void export_batch(OutBatch&& b, ArrowArray* out) {
         a.buffers = h->buffers[j].data();
         a.release = release_child;
         h->child_ptrs[j] = &a;
-        h->pinned.push_back(c.data); h->pinned.push_back(c.valid); h->pinned.push_back(c.off);
+        if (!c.alias) h->pinned.push_back(c.data);
+        h->pinned.push_back(c.valid); h->pinned.push_back(c.off);
     }
     memset(out, 0, sizeof *out);
     out->length = b.nrows; out->null_count = 0; out->offset = 0;
@@ -330,6 +334,10 @@ struct igl_op {
     igl_expr *lkey = nullptr, *rkey = nullptr;
     bool build_done = false, left_join = false;
     int n_left = 0, n_right = 0;
+    // Inner equi-join on integer keys of one type, neither side nullable: every output row's
+    // right key equals its left key bit for bit, so the right key column is not copied back
+    // over PCIe — the exported batch's two key columns share one host buffer.
+    int alias_right_key = -1, alias_left_key = -1;
     std::vector<void*> build_dev;            // grown device columns of the whole build side
     std::vector<size_t> build_cap;
     std::vector<uint8_t*> build_valid;
@@ -542,6 +550,12 @@ int32_t join_probe_flush(igl_op* op) {
     ob.cols.resize(nc);
     for (int c = 0; c < nc && rc >= 0; ++c) {
         ob.cols[c].type = dout[c].type;
+        if (op->alias_right_key >= 0 && c == op->n_left + op->alias_right_key && dev[op->alias_left_key].validity == nullptr &&
+            op->build_valid[op->alias_right_key] == nullptr) {   // no NULL keys on either side in this chunk
+            ob.cols[c].data = ob.cols[op->alias_left_key].data;   // left columns come first: already set
+            ob.cols[c].alias = true;
+            continue;
+        }
         // igl_join_probe writes a validity bitmap for a left column that has one and
         // for a right column that can be null (source nullable, or null-extended)
         const bool is_left = c < op->n_left;
@@ -552,7 +566,7 @@ int32_t join_probe_flush(igl_op* op) {
     if (rc >= 0 && cudaStreamSynchronize(st) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "stream synchronise failed");
     cleanup();
     if (rc < 0) {
-        for (auto& c : ob.cols) { pinned_pool().put(c.data); pinned_pool().put(c.valid); }
+        for (auto& c : ob.cols) { if (!c.alias) pinned_pool().put(c.data); pinned_pool().put(c.valid); }
         return rc;
     }
     for (auto& c : ob.cols) c.null_count = c.valid ? count_zero_bits(c.valid, n_out) : 0;
@@ -685,6 +699,10 @@ int32_t igl_op_hash_join_create(igl_ctx* ctx, int32_t join_type, const struct Ar
         // right field was declared non-nullable.  Here such fields become nullable.
         if (op->left_join) o.nullable = true;
         op->out_fields.push_back(o);
+    }
+    if (!op->left_join && op->lkey->is_plain_col() && op->rkey->is_plain_col()) {
+        const int lc = op->lkey->nodes[0].col, rc2 = op->rkey->nodes[0].col;
+        if (lt[lc] == rt[rc2] && (lt[lc] == IGL_T_I32 || lt[lc] == IGL_T_I64)) { op->alias_left_key = lc; op->alias_right_key = rc2; }
     }
     op->build_dev.assign(op->n_right, nullptr);
     op->build_cap.assign(op->n_right, 0);

@@ -756,6 +756,16 @@ __global__ void pack_bits_kernel(const uint8_t* __restrict__ bytes, uint32_t* __
     }
 }
 
+// status must hold scan_scratch_words(ceil(ntiles / 1024)) zeroed words, *ticket must be zero.
+cudaError_t launch_tile_offsets(const void* bitmap, int rows_per_tile, long long ntiles, unsigned long long* off,
+                                PipeHeader* hdr, unsigned int* ticket, uint64_t* status, int sm_count, cudaStream_t st) {
+    const long long nscan = (ntiles + kToTile - 1) / kToTile;
+    const int grid = (int)std::min<long long>(std::max<long long>(nscan, 1), (long long)sm_count * 2);
+    fp_tile_offsets_kernel<<<grid, kToThreads, 0, st>>>((const uint4*)bitmap, rows_per_tile / 128, ntiles, off, hdr, ticket, status);
+    return cudaGetLastError();
+}
+long long tile_offsets_scan_tiles(long long ntiles) { return (ntiles + kToTile - 1) / kToTile; }
+
 cudaError_t launch_pack_bits(const uint8_t* bytes, uint32_t* bits, const long long* n_ptr, long long n_fixed,
                              long long cap_rows, int sm_count, cudaStream_t st) {
     long long blocks = (cap_rows + 255) / 256;
@@ -1141,10 +1151,7 @@ int32_t igl_fp_launch(igl_fp* fp, const igl_dev_col* in, int64_t nrows, igl_dev_
         PM.T.status = nullptr;
         PM.mask_words = (uint32_t*)mask;
         IGL_TRY(launch_program(ctx, fp->mask, PM, fp->has_nulls, st));
-        const int ogrid = (int)std::min<long long>(nscan, (long long)ctx->sm_count * 2);
-        fp_tile_offsets_kernel<<<ogrid, kToThreads, 0, st>>>((const uint4*)mask, P.T.sub_rows / 128, nsub, tile_off, P.T.hdr,
-                                                             &hdr2->ticket, P.T.status);
-        IGL_CUDA_OK(cudaGetLastError());
+        IGL_CUDA_OK(launch_tile_offsets(mask, P.T.sub_rows, nsub, tile_off, P.T.hdr, &hdr2->ticket, P.T.status, ctx->sm_count, st));
         ctx->launches++;
         P.T.aux_table = tile_off;
         P.T.data[P.mask_slot] = mask;

@@ -560,7 +560,13 @@ __global__ void __launch_bounds__(kPipeThreads, kPipeMinCtas) join_probe_multi_k
 // input) and HBM latency no longer hides them.
 // ---------------------------------------------------------------------------
 constexpr int kFlatThreads = 256;
-constexpr int kFlatRows = 4;
+#ifndef IGL_FLAT_ROWS
+#define IGL_FLAT_ROWS 4
+#endif
+#ifndef IGL_FLAT_CTAS
+#define IGL_FLAT_CTAS 3
+#endif
+constexpr int kFlatRows = IGL_FLAT_ROWS;
 constexpr int kFlatChunk = kFlatThreads * kFlatRows;   // 1024 rows per CTA iteration
 constexpr int kFlatClaim = 4;                          // consecutive chunks claimed per ticket
 
@@ -575,13 +581,23 @@ struct FlatProbeParams {
     unsigned long long* out_counter;
     unsigned int* ticket;   // chunks are claimed in order, so all CTAs work on one moving frontier of the
                             // (partitioned) input and the table region they touch stays L2-resident
+    uint32_t stage_off[kJoinMaxCols];   // byte offset of each left column's chunk slice inside a stage
+    uint32_t stage_bytes;
 };
 
+constexpr int kFlatStages = 3;   // chunks in flight per CTA: the one being probed + two on their way from HBM
+
+// The left columns of every chunk reach shared memory through a ring of bulk async
+// copies issued by thread 0 two chunks ahead (the threads themselves only have four
+// rows each in flight, far too few bytes to cover HBM latency); table buckets are
+// read directly (L2-resident region) and the output is stored straight from registers.
 template <int KEY_TYPE>
-__global__ void __launch_bounds__(kFlatThreads, 3) join_probe_flat_kernel(const __grid_constant__ FlatProbeParams P) {
+__global__ void __launch_bounds__(kFlatThreads, IGL_FLAT_CTAS) join_probe_flat_kernel(const __grid_constant__ FlatProbeParams P) {
+    extern __shared__ __align__(128) uint8_t fsmem[];
+    __shared__ uint64_t s_full[kFlatStages];
+    __shared__ long long s_chunk_of[kFlatStages];
     __shared__ unsigned int s_wcnt[kFlatThreads / 32];
     __shared__ unsigned long long s_base;
-    __shared__ long long s_chunk;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint64_t bmask = P.table.mask >> 1;
@@ -589,13 +605,41 @@ __global__ void __launch_bounds__(kFlatThreads, 3) join_probe_flat_kernel(const 
     const Slot* slots = P.table.slots;
     const int tshift = P.table.shift + 1;   // slot index -> bucket index
     const int lrow = warp * (32 * kFlatRows) + lane;   // this lane's first row inside a chunk
-    for (long long it = 0;; ++it) {
-        if ((it % kFlatClaim) == 0) {
-            if (threadIdx.x == 0) s_chunk = (long long)atomicAdd(P.ticket, 1u) * kFlatClaim;
-            __syncthreads();
+    // ---- producer state (thread 0 only) ----
+    long long grp_base = 0;
+    int grp_used = kFlatClaim;
+    unsigned int pending = 0;
+    auto refill = [&](int s) {   // claim the next chunk and start its copies into stage s
+        if (grp_used == kFlatClaim) {
+            grp_base = (long long)pending * kFlatClaim;
+            pending = atomicAdd(P.ticket, 1u);   // for the group after this one: its round trip is hidden
+            grp_used = 0;
         }
-        const long long chunk = s_chunk + (it % kFlatClaim);
-        if (chunk >= nchunks) break;   // claims only grow: nothing is left for this CTA
+        const long long chunk = grp_base + grp_used++;
+        if (chunk >= nchunks) { s_chunk_of[s] = -1; mbar_arrive(&s_full[s]); return; }
+        s_chunk_of[s] = chunk;
+        const long long cb = chunk * kFlatChunk;
+        const uint32_t rows = (uint32_t)min((long long)kFlatChunk, P.nrows - cb);
+        uint32_t total = 0;
+        for (int c = 0; c < P.n_left; ++c) total += ((rows << P.lshift[c]) + 15u) & ~15u;
+        mbar_arrive_expect_tx(&s_full[s], total);
+        uint8_t* st = fsmem + (size_t)s * P.stage_bytes;
+        for (int c = 0; c < P.n_left; ++c)
+            bulk_g2s(st + P.stage_off[c], P.left[c] + ((size_t)cb << P.lshift[c]), ((rows << P.lshift[c]) + 15u) & ~15u, &s_full[s]);
+    };
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kFlatStages; ++s) mbar_init(&s_full[s], 1);
+        mbar_fence_init();
+        pending = atomicAdd(P.ticket, 1u);
+        for (int s = 0; s < kFlatStages; ++s) refill(s);
+    }
+    __syncthreads();
+    for (int it = 0;; ++it) {
+        const int sidx = it % kFlatStages;
+        mbar_wait(&s_full[sidx], (uint32_t)(it / kFlatStages) & 1u);
+        const long long chunk = s_chunk_of[sidx];
+        if (chunk < 0) break;   // claims only grow: nothing is left for this CTA
+        const uint8_t* stage = fsmem + (size_t)sidx * P.stage_bytes;
         const long long cbase = chunk * kFlatChunk;                       // uniform
         const int nvalid = (int)min((long long)kFlatChunk, P.nrows - cbase);   // rows of this chunk that exist
         uint64_t raw[kFlatRows], k[kFlatRows];
@@ -603,10 +647,10 @@ __global__ void __launch_bounds__(kFlatThreads, 3) join_probe_flat_kernel(const 
         ulonglong4 q[kFlatRows];
         uint32_t live = 0;
         {
-            const uint8_t* kc = P.left[P.key_col] + (KEY_TYPE == IGL_T_I32 ? (cbase << 2) : (cbase << 3));   // uniform base, 32-bit offsets below
+            const uint8_t* kc = stage + P.stage_off[P.key_col];
 #pragma unroll
             for (int r = 0; r < kFlatRows; ++r) {
-                const int i = min(lrow + r * 32, nvalid - 1);   // clamped: the load is unconditional, the row just does not count
+                const int i = lrow + r * 32;   // rows past nvalid read stale shared memory and do not count
                 raw[r] = KEY_TYPE == IGL_T_I32 ? (uint64_t)((const uint32_t*)kc)[i] : ((const uint64_t*)kc)[i];
                 live |= ((lrow + r * 32) < nvalid ? 1u : 0u) << r;
             }
@@ -628,7 +672,9 @@ __global__ void __launch_bounds__(kFlatThreads, 3) join_probe_flat_kernel(const 
             hit |= (found ? 1u : 0u) << r;
             pend |= ((found || e0 || e1) ? 0u : 1u) << r;
         }
-        const uint32_t special = (k[0] == kEmptyKey) | ((k[1] == kEmptyKey) << 1) | ((k[2] == kEmptyKey) << 2) | ((k[3] == kEmptyKey) << 3);
+        uint32_t special = 0;
+#pragma unroll
+        for (int r = 0; r < kFlatRows; ++r) special |= (k[r] == kEmptyKey ? 1u : 0u) << r;
         hit &= live & ~special;
         pend &= live & ~special;
         if (special & live) {   // the key equal to the empty-slot sentinel lives in a side entry (rare)
@@ -638,17 +684,39 @@ __global__ void __launch_bounds__(kFlatThreads, 3) join_probe_flat_kernel(const 
                     if (((special & live) >> r) & 1u) { hit |= 1u << r; val[r] = P.table.side->val[1]; }
             }
         }
-        if (pend) {   // collisions beyond the home bucket (rare at load factor 0.5)
+        if (pend) {
+            // About one row in ten is not decided by its home bucket (load factor 0.5, two
+            // slots per bucket), so nearly every warp comes here: fetch the next bucket of
+            // ALL this lane's undecided rows at once — one L2 round trip, not one per row.
+            uint64_t b[kFlatRows];
 #pragma unroll
             for (int r = 0; r < kFlatRows; ++r) {
-                uint64_t b = (mix64(k[r]) >> tshift);
-                while ((pend >> r) & 1u) {
-                    b = (b + 1) & bmask;
-                    const ulonglong4 n = ld_nc_u64x4(slots + 2 * b);
-                    if (n.x == k[r]) { hit |= 1u << r; val[r] = n.y; pend &= ~(1u << r); }
-                    else if (n.x == kEmptyKey) pend &= ~(1u << r);
-                    else if (n.z == k[r]) { hit |= 1u << r; val[r] = n.w; pend &= ~(1u << r); }
-                    else if (n.z == kEmptyKey) pend &= ~(1u << r);
+                b[r] = ((mix64(k[r]) >> tshift) + 1) & bmask;
+                if ((pend >> r) & 1u) q[r] = ld_nc_u64x4(slots + 2 * b[r]);
+            }
+#pragma unroll
+            for (int r = 0; r < kFlatRows; ++r) {
+                if ((pend >> r) & 1u) {
+                    if (q[r].x == k[r]) { hit |= 1u << r; val[r] = q[r].y; pend &= ~(1u << r); }
+                    else if (q[r].x == kEmptyKey) pend &= ~(1u << r);
+                    else if (q[r].z == k[r]) { hit |= 1u << r; val[r] = q[r].w; pend &= ~(1u << r); }
+                    else if (q[r].z == kEmptyKey) pend &= ~(1u << r);
+                }
+            }
+            while (pend) {   // longer walks (about one row in a hundred): again all undecided rows per round trip
+#pragma unroll
+                for (int r = 0; r < kFlatRows; ++r) {
+                    b[r] = (b[r] + 1) & bmask;
+                    if ((pend >> r) & 1u) q[r] = ld_nc_u64x4(slots + 2 * b[r]);
+                }
+#pragma unroll
+                for (int r = 0; r < kFlatRows; ++r) {
+                    if ((pend >> r) & 1u) {
+                        if (q[r].x == k[r]) { hit |= 1u << r; val[r] = q[r].y; pend &= ~(1u << r); }
+                        else if (q[r].x == kEmptyKey) pend &= ~(1u << r);
+                        else if (q[r].z == k[r]) { hit |= 1u << r; val[r] = q[r].w; pend &= ~(1u << r); }
+                        else if (q[r].z == kEmptyKey) pend &= ~(1u << r);
+                    }
                 }
             }
         }
@@ -657,8 +725,9 @@ __global__ void __launch_bounds__(kFlatThreads, 3) join_probe_flat_kernel(const 
 #pragma unroll
         for (int r = 0; r < kFlatRows; ++r) { hb[r] = __ballot_sync(0xffffffffu, (hit >> r) & 1u); wcnt += __popc(hb[r]); }
         if (lane == 0) s_wcnt[warp] = wcnt;
-        __syncthreads();
+        __syncthreads();   // every thread is also done with the previous chunk's stage
         if (threadIdx.x == 0) {
+            if (it > 0) refill((it - 1) % kFlatStages);
             unsigned int tot = 0;
 #pragma unroll
             for (int w = 0; w < kFlatThreads / 32; ++w) tot += s_wcnt[w];
@@ -677,19 +746,19 @@ __global__ void __launch_bounds__(kFlatThreads, 3) join_probe_flat_kernel(const 
         for (int c = 0; c < P.n_left; ++c) {
             const bool is_key = c == P.key_col;
             if (P.lshift[c] == 3) {
-                const uint64_t* src = (const uint64_t*)P.left[c] + cbase;
+                const uint64_t* src = (const uint64_t*)(stage + P.stage_off[c]);
                 uint64_t* dst = (uint64_t*)P.out[c] + obase;
                 uint64_t v[kFlatRows];
 #pragma unroll
-                for (int r = 0; r < kFlatRows; ++r) v[r] = is_key ? raw[r] : src[min(lrow + r * 32, nvalid - 1)];
+                for (int r = 0; r < kFlatRows; ++r) v[r] = is_key ? raw[r] : src[lrow + r * 32];
 #pragma unroll
                 for (int r = 0; r < kFlatRows; ++r) if ((hit >> r) & 1u) st_cs_u64(dst + p[r], v[r]);
             } else {
-                const uint32_t* src = (const uint32_t*)P.left[c] + cbase;
+                const uint32_t* src = (const uint32_t*)(stage + P.stage_off[c]);
                 uint32_t* dst = (uint32_t*)P.out[c] + obase;
                 uint32_t v[kFlatRows];
 #pragma unroll
-                for (int r = 0; r < kFlatRows; ++r) v[r] = is_key ? (uint32_t)raw[r] : src[min(lrow + r * 32, nvalid - 1)];
+                for (int r = 0; r < kFlatRows; ++r) v[r] = is_key ? (uint32_t)raw[r] : src[lrow + r * 32];
 #pragma unroll
                 for (int r = 0; r < kFlatRows; ++r) if ((hit >> r) & 1u) st_cs_u32(dst + p[r], v[r]);
             }
@@ -1008,10 +1077,15 @@ int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_
     {
         const char* env = getenv("IGL_JOIN_FLAT");
         bool flat = !(env && env[0] == '0') && !j->csr && !j->left_join && !j->never_match;
-        for (int c = 0; c < nl && flat; ++c) if (left[c].validity) flat = false;
+        for (int c = 0; c < nl && flat; ++c) if (left[c].validity || ((uintptr_t)left[c].data & 15)) flat = false;
         for (int c = 0; c < nr && flat; ++c) if (j->right[c].validity) flat = false;
+        uint32_t flat_stage = 0;
+        for (int c = 0; c < nl; ++c) flat_stage += (uint32_t)kFlatChunk << (j->lt[c] == IGL_T_I32 ? 2 : 3);
+        if ((size_t)flat_stage * kFlatStages > (200u << 10)) flat = false;   // very wide probe rows take the tiled kernels
         if (flat) {
             FlatProbeParams F{};
+            F.stage_bytes = flat_stage;
+            for (uint32_t c = 0, off = 0; c < (uint32_t)nl; ++c) { F.stage_off[c] = off; off += (uint32_t)kFlatChunk << (j->lt[c] == IGL_T_I32 ? 2 : 3); }
             F.n_left = nl; F.n_right = nr; F.key_col = j->lkey; F.key_type = j->lt[j->lkey];
             F.right_key_col = j->rkey; F.payload_col = j->payload_col; F.table = j->table; F.nrows = nrows;
             for (int c = 0; c < nl; ++c) {
@@ -1030,10 +1104,16 @@ int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_
             F.out_counter = &((PipeHeader*)j->scratch)->aux[1];
             F.ticket = &((PipeHeader*)j->scratch)->ticket;
             const long long nchunks = (nrows + kFlatChunk - 1) / kFlatChunk;
-            const int grid = (int)std::min<long long>(nchunks, (long long)ctx->sm_count * 6);
-            if (F.key_type == IGL_T_I32) join_probe_flat_kernel<IGL_T_I32><<<grid, kFlatThreads, 0, st>>>(F);
-            else if (F.key_type == IGL_T_F64) join_probe_flat_kernel<IGL_T_F64><<<grid, kFlatThreads, 0, st>>>(F);
-            else join_probe_flat_kernel<IGL_T_I64><<<grid, kFlatThreads, 0, st>>>(F);
+            const void* kfn = F.key_type == IGL_T_I32 ? (const void*)join_probe_flat_kernel<IGL_T_I32>
+                            : F.key_type == IGL_T_F64 ? (const void*)join_probe_flat_kernel<IGL_T_F64>
+                                                      : (const void*)join_probe_flat_kernel<IGL_T_I64>;
+            const size_t fsmem = (size_t)F.stage_bytes * kFlatStages;
+            IGL_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
+            int per_sm = 0;
+            IGL_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, kFlatThreads, fsmem));
+            const int grid = (int)std::min<long long>(nchunks, (long long)ctx->sm_count * std::max(per_sm, 1));
+            void* kargs[] = {&F};
+            IGL_CUDA_OK(cudaLaunchKernel(kfn, dim3(grid), dim3(kFlatThreads), kargs, fsmem, st));
             IGL_CUDA_OK(cudaGetLastError());
             ctx->launches++;
             IGL_CUDA_OK(cudaMemcpyAsync(j->host_hdr, j->scratch, sizeof(PipeHeader), cudaMemcpyDeviceToHost, st));

@@ -14,6 +14,15 @@ namespace igl {
 cudaError_t launch_pack_bits(const uint8_t* bytes, uint32_t* bits, const long long* n_ptr, long long n_fixed,
                              long long cap_rows, int sm_count, cudaStream_t st);
 
+// Popcount of every tile's slice of a row bitmap -> exclusive offsets (filter_project.cu):
+// off[t] = set bits before tile t, off[ntiles] = hdr->out_count = all set bits; resets
+// hdr->ticket.  `status` = scan_scratch_words(tile_offsets_scan_tiles(ntiles)) zeroed words,
+// *ticket zero.  rows_per_tile is a multiple of 128; the bitmap is padded to whole tiles.
+struct PipeHeader;
+cudaError_t launch_tile_offsets(const void* bitmap, int rows_per_tile, long long ntiles, unsigned long long* off,
+                                PipeHeader* hdr, unsigned int* ticket, uint64_t* status, int sm_count, cudaStream_t st);
+long long tile_offsets_scan_tiles(long long ntiles);
+
 // igl_fp_create with two internal extras used by the streaming operators: `skip`
 // hides input columns from a pass-through filter, `with_rowid` appends an Int32
 // output holding the input row index of each surviving row.
