@@ -30,6 +30,10 @@ sys.path.insert(0, ROOT)
 SEED_C2, SEED_C3 = 0x16100002, 0x16100003
 
 
+# join_probe_flat_kernel at C3 full scale: 21.30 GB read + 31.95 GB written (profiles/launches_r1c_join_full.csv)
+NCU_PROBE_TRAFFIC_BYTES = 53_243_975_680
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -210,12 +214,9 @@ def run_ours(args):
         probe_ms = []
 
         def step():
-            e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
             join.build([rk, rv], nb_total)
-            e0.record()
             _, n = join.probe([lk, lw], np_total, out=out, capacity=np_total)
-            e1.record()
-            probe_ms.append((e0, e1))
+            probe_ms.append(join.phase_ms())   # CUDA events recorded by the library on the launching stream
             return n
         rows_per_step = nb_total + np_total
 
@@ -260,15 +261,25 @@ def run_ours(args):
                        "l2_policy": "inputs (>= 18 GB) and the 4 GiB table are far larger than the 126 MB L2",
                        "parallelism": f"hash-partitioned over {world} GPUs, exchange={args.exchange}" if world > 1 else "1 GPU"},
             "gpu_launches": launches, "clocks": clocks}
+    if world > 1:
+        phases = [None] * world
+        dist.all_gather_object(phases, pj.phase_ms())
+        line["phases_ms_per_rank"] = phases
     if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
         return
     if world == 1:
-        pm = statistics.median(a.elapsed_time(b) for a, b in probe_ms)
+        ph = [statistics.median(p[i] for p in probe_ms) for i in range(4)]
+        pm = ph[3]
         probe_bytes = np_total * 16 + n_out * 32
-        line["roofline"] = {"bound": "hbm", "kernel": "join_probe_unique_kernel<2,false>", "achieved": probe_bytes / pm / 1e6,
-                            "peak": peak, "unit": "GB/s", "frac": probe_bytes / pm / 1e6 / peak, "traffic": None,
+        # traffic: dram__bytes_read.sum + dram__bytes_write.sum of this kernel at this size (ncu, profiles/README.md)
+        traffic = NCU_PROBE_TRAFFIC_BYTES if scale == 1 else None
+        line["roofline"] = {"bound": "hbm", "kernel": "join_probe_flat_kernel<3>", "achieved": probe_bytes / pm / 1e6,
+                            "peak": peak, "unit": "GB/s", "frac": probe_bytes / pm / 1e6 / peak, "traffic": traffic,
                             "peak_source": peak_src, "kernel_ms": pm,
                             "algorithmic_bytes_per_launch": probe_bytes,
+                            "phases_ms": {"build_partition": ph[0], "build": ph[1], "probe_partition": ph[2], "probe_kernel": ph[3]},
                             "whole_join": {"algorithmic_gb": (nb_total * 16 + np_total * 16 + n_out * 32) / 1e9,
                                            "gb_per_s": (nb_total * 16 + np_total * 16 + n_out * 32) / ms_step / 1e6,
                                            "frac": (nb_total * 16 + np_total * 16 + n_out * 32) / ms_step / 1e6 / peak}}

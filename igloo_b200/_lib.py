@@ -100,9 +100,14 @@ _sig("igl_join_build", _i32, _vp, _P(DevCol), _i64, _vp)
 _sig("igl_join_probe_count", _i32, _vp, _P(DevCol), _i64, _P(_i64), _vp)
 _sig("igl_join_probe", _i32, _vp, _P(DevCol), _i64, _P(DevCol), _i64, _P(_i64), _vp)
 _sig("igl_join_has_duplicates", _i32, _vp)
+_sig("igl_join_partition_bits", _i32, _vp, _i64)
+_sig("igl_join_phase_ms", _i32, _vp, _P(C.c_double))
+_sig("igl_join_set_prepartitioned", _i32, _vp, _i32)
 _sig("igl_join_destroy", None, _vp)
 _sig("igl_partition_histogram", _i32, _vp, _P(DevCol), _i64, _i32, _vp, _vp)
 _sig("igl_partition_scatter", _i32, _vp, _P(DevCol), _i32, _i32, _i64, _i32, _P(_vp), _P(_i64), _vp)
+_sig("igl_partition_histogram_radix", _i32, _vp, _P(DevCol), _i64, _i32, _i32, _vp, _vp)
+_sig("igl_partition_scatter_radix", _i32, _vp, _P(DevCol), _i32, _i32, _i64, _i32, _i32, _P(_vp), _P(_i64), _vp)
 _sig("igl_ipc_export", _i32, _vp, _vp, C.c_char_p)
 _sig("igl_ipc_open", _i32, _vp, C.c_char_p, _P(_vp))
 _sig("igl_ipc_close", _i32, _vp, _vp)

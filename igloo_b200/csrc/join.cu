@@ -838,6 +838,7 @@ struct igl_join {
     // radix partitioning (large build sides): both sides are reordered by the top
     // bits of the hash so each 16 MB table region is built and probed while L2-resident
     int log2_parts = 0;
+    bool prepartitioned = false;             // both sides arrive ordered by the top hash bits: skip the radix passes
     std::vector<void*> part_right;           // partitioned build columns (owned)
     std::vector<void*> part_left;            // partitioned probe columns (owned, grow-only)
     int64_t part_left_rows = 0;
@@ -848,6 +849,10 @@ struct igl_join {
     std::vector<void*> valid_planes;
     int64_t plane_rows = 0;
     PipeHeader* host_hdr = nullptr;
+    // device-timeline marks of the last build / probe (igl_join_phase_ms): [0] build start, [1] after its
+    // partitioning, [2] build end, [3] probe start, [4] after its partitioning, [5] probe kernel end
+    cudaEvent_t ev[6] = {};
+    bool ev_build = false, ev_probe = false;
     JoinSide* host_side = nullptr;
     PipeCols T{};
     PipeGeometry geo;
@@ -919,9 +924,32 @@ int32_t igl_join_create(igl_ctx* ctx, int32_t join_type, const int32_t* left_typ
         (csr ? j->grid_cap_m : j->grid_cap_u) = per_sm * ctx->sm_count;
     }
     IGL_CUDA_OK(cudaHostAlloc((void**)&j->host_hdr, sizeof(PipeHeader), cudaHostAllocDefault));
+    for (auto& e : j->ev) IGL_CUDA_OK(cudaEventCreate(&e));
     IGL_CUDA_OK(cudaHostAlloc((void**)&j->host_side, sizeof(JoinSide), cudaHostAllocDefault));
     j->valid_planes.assign(n_left + n_right, nullptr);
     *out = j.release();
+    return IGL_OK;
+}
+
+// The radix fan-out igl_join_build would pick for a build side of `build_rows` rows (0 = it
+// would not partition): callers that partition during the exchange use the same value.
+int32_t igl_join_partition_bits(igl_ctx* ctx, int64_t build_rows) {
+    if (!ctx || build_rows <= 0) return 0;
+    const char* env = getenv("IGL_JOIN_PARTITION");
+    if (env && env[0] == '0') return 0;
+    uint64_t cap = 1024;
+    while ((double)cap * ctx->cfg.hash_load_factor < (double)build_rows) cap <<= 1;
+    if (cap * sizeof(Slot) < (64ull << 20)) return 0;
+    const char* pmb = getenv("IGL_PART_MB");
+    const uint64_t target = (uint64_t)(pmb ? atoi(pmb) : 16) << 20;
+    int lp = 0;
+    while (((cap * sizeof(Slot)) >> lp) > target && lp < 10) ++lp;
+    return lp < 4 ? 4 : lp;
+}
+
+int32_t igl_join_set_prepartitioned(igl_join* j, int32_t on) {
+    if (!j) return fail(IGL_ERR_INVALID_ARG, "igl_join_set_prepartitioned: NULL join");
+    j->prepartitioned = on != 0;
     return IGL_OK;
 }
 
@@ -951,6 +979,7 @@ int32_t igl_join_build(igl_join* j, const igl_dev_col* right, int64_t nrows, voi
     j->table.side = (JoinSide*)j->d_side;
     j->table.rowids = nullptr;
     const int grid = ctx->sm_count * 8;
+    cudaEventRecord(j->ev[0], st);
     // Large tables: reorder the build side by the top hash bits (partition.cu).
     for (void* p : j->part_right) pool_free(ctx, p);
     j->part_right.clear();
@@ -958,7 +987,7 @@ int32_t igl_join_build(igl_join* j, const igl_dev_col* right, int64_t nrows, voi
     {
         // IGL_JOIN_PARTITION=0 switches it off (A/B measurements in profiles/README.md).
         const char* env = getenv("IGL_JOIN_PARTITION");
-        bool want = !(env && env[0] == '0') && cap * sizeof(Slot) >= (64ull << 20) && nrows > 0;
+        bool want = !(env && env[0] == '0') && cap * sizeof(Slot) >= (64ull << 20) && nrows > 0 && !j->prepartitioned;
         for (int c = 0; c < nr; ++c) if (right[c].validity) want = false;
         if (want) {
             int lp = 0;
@@ -978,6 +1007,7 @@ int32_t igl_join_build(igl_join* j, const igl_dev_col* right, int64_t nrows, voi
         }
     }
     right = j->right.data();
+    cudaEventRecord(j->ev[1], st);
     const igl_dev_col& kc = right[j->rkey];
     // payload inlining: (key, one non-null fixed-width column), integer key (exact round trip)
     j->payload_col = -1;
@@ -995,6 +1025,8 @@ int32_t igl_join_build(igl_join* j, const igl_dev_col* right, int64_t nrows, voi
         IGL_CUDA_OK(cudaGetLastError());
         ctx->launches++;
     }
+    cudaEventRecord(j->ev[2], st);
+    j->ev_build = true;
     IGL_CUDA_OK(cudaMemcpyAsync(j->host_side, j->d_side, sizeof(JoinSide), cudaMemcpyDeviceToHost, st));
     IGL_CUDA_OK(cudaStreamSynchronize(st));
     j->csr = j->host_side->dup_flag != 0;
@@ -1057,6 +1089,8 @@ int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_
         if (out_capacity < need) return fail(IGL_ERR_INVALID_ARG, "output capacity %lld < %lld rows", (long long)out_capacity, (long long)need);
     }
     std::vector<igl_dev_col> pleft;
+    cudaEventRecord(j->ev[3], st);
+    j->ev_probe = false;
     if (j->log2_parts > 0) {   // reorder the probe chunk the same way, so it walks the table region by region
         bool ok = true;
         for (int c = 0; c < nl; ++c) if (left[c].validity) ok = false;
@@ -1113,7 +1147,10 @@ int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_
             IGL_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, kFlatThreads, fsmem));
             const int grid = (int)std::min<long long>(nchunks, (long long)ctx->sm_count * std::max(per_sm, 1));
             void* kargs[] = {&F};
+            cudaEventRecord(j->ev[4], st);
             IGL_CUDA_OK(cudaLaunchKernel(kfn, dim3(grid), dim3(kFlatThreads), kargs, fsmem, st));
+            cudaEventRecord(j->ev[5], st);
+            j->ev_probe = true;
             IGL_CUDA_OK(cudaGetLastError());
             ctx->launches++;
             IGL_CUDA_OK(cudaMemcpyAsync(j->host_hdr, j->scratch, sizeof(PipeHeader), cudaMemcpyDeviceToHost, st));
@@ -1193,6 +1230,25 @@ int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_
     return IGL_OK;
 }
 
+// Device time of the last igl_join_build / igl_join_probe on this join, in milliseconds:
+// out[0] build-side partitioning, out[1] table init + build kernels, out[2] probe-side
+// partitioning, out[3] the probe kernel (fast path only; -1 where nothing was recorded).
+int32_t igl_join_phase_ms(igl_join* j, double out[4]) {
+    if (!j || !out) return fail(IGL_ERR_INVALID_ARG, "igl_join_phase_ms: NULL argument");
+    DeviceGuard g(j->ctx->device);
+    for (int i = 0; i < 4; ++i) out[i] = -1.0;
+    float ms = 0.f;
+    if (j->ev_build && cudaEventSynchronize(j->ev[2]) == cudaSuccess) {
+        if (cudaEventElapsedTime(&ms, j->ev[0], j->ev[1]) == cudaSuccess) out[0] = ms;
+        if (cudaEventElapsedTime(&ms, j->ev[1], j->ev[2]) == cudaSuccess) out[1] = ms;
+    }
+    if (j->ev_probe && cudaEventSynchronize(j->ev[5]) == cudaSuccess) {
+        if (cudaEventElapsedTime(&ms, j->ev[3], j->ev[4]) == cudaSuccess) out[2] = ms;
+        if (cudaEventElapsedTime(&ms, j->ev[4], j->ev[5]) == cudaSuccess) out[3] = ms;
+    }
+    return IGL_OK;
+}
+
 void igl_join_destroy(igl_join* j) {
     if (!j) return;
     DeviceGuard g(j->ctx->device);
@@ -1206,6 +1262,7 @@ void igl_join_destroy(igl_join* j) {
     for (void* p : j->valid_planes) pool_free(j->ctx, p);
     if (j->host_hdr) cudaFreeHost(j->host_hdr);
     if (j->host_side) cudaFreeHost(j->host_side);
+    for (auto& e : j->ev) if (e) cudaEventDestroy(e);
     delete j;
 }
 

@@ -131,20 +131,27 @@ constexpr int kRadixThreads = 512;
 constexpr int kRadixRowsPerThread = 8;
 constexpr int kRadixTile = kRadixThreads * kRadixRowsPerThread;   // 4096 rows per tile: long write runs per partition
 
-__device__ __forceinline__ int radix_part(const void* keys, int type, long long i, int log2_parts) {
+// bin = destination * 2^log2_parts + partition: destination from the LOW 32 hash bits (as
+// part_dest), partition from the TOP bits (as the join table).  ndest == 1: partition only.
+__device__ __forceinline__ int radix_bin_of(uint64_t h, int ndest, int log2_parts) {
+    const int part = log2_parts ? (int)(h >> (64 - log2_parts)) : 0;
+    const int dest = ndest > 1 ? (int)(((h & 0xFFFFFFFFull) * (uint64_t)ndest) >> 32) : 0;
+    return (dest << log2_parts) | part;
+}
+__device__ __forceinline__ int radix_part(const void* keys, int type, long long i, int ndest, int log2_parts) {
     const uint64_t raw = type == IGL_T_I32 ? (uint64_t)(uint32_t)((const int32_t*)keys)[i] : ((const uint64_t*)keys)[i];
-    return (int)(mix64(part_canon(type, raw)) >> (64 - log2_parts));
+    return radix_bin_of(mix64(part_canon(type, raw)), ndest, log2_parts);
 }
 
-__global__ void __launch_bounds__(512) radix_hist_kernel(const void* __restrict__ keys, int type, long long n,
+__global__ void __launch_bounds__(512) radix_hist_kernel(const void* __restrict__ keys, int type, long long n, int ndest,
                                                                    int log2_parts, unsigned long long* hist) {
     __shared__ unsigned int s_hist[kRadixMaxParts];
-    const int nparts = 1 << log2_parts;
+    const int nparts = ndest << log2_parts;
     for (int p = threadIdx.x; p < nparts; p += blockDim.x) s_hist[p] = 0;
     __syncthreads();
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
-        atomicAdd(&s_hist[radix_part(keys, type, i, log2_parts)], 1u);
+        atomicAdd(&s_hist[radix_part(keys, type, i, ndest, log2_parts)], 1u);
     __syncthreads();
     for (int p = threadIdx.x; p < nparts; p += blockDim.x)
         if (s_hist[p]) atomicAdd(&hist[p], (unsigned long long)s_hist[p]);
@@ -169,13 +176,13 @@ __global__ void radix_scan_kernel(const unsigned long long* hist, unsigned long 
 
 struct RadixParams {
     const uint8_t* src[kPartMaxCols];
-    uint8_t* dst[kPartMaxCols];
+    uint8_t* dst[kPartMaxParts][kPartMaxCols];   // per destination (one when partitioning locally)
     uint8_t shift[kPartMaxCols];
     uint32_t stage_off[kPartMaxCols];   // byte offset of each column's staging area in dynamic shared memory
-    int ncols, key_col, key_type, log2_parts;
+    int ncols, key_col, key_type, log2_parts, ndest;
     long long n;
-    const unsigned long long* offsets;  // [nparts + 1]
-    unsigned long long* cursor;         // [nparts]
+    const unsigned long long* offsets;  // [bins]: first row of the bin inside its destination's buffer
+    unsigned long long* cursor;         // [bins]
 };
 
 // One tile.  FULL = every one of the 4096 rows exists (all tiles but the last):
@@ -183,7 +190,7 @@ struct RadixParams {
 template <bool FULL>
 __device__ __forceinline__ void radix_tile(const RadixParams& P, uint8_t* stage, unsigned int* s_cnt, unsigned long long* s_gbase,
                                            unsigned short* s_part, unsigned int* s_warp_tot, long long row0, int rows) {
-    const int nparts = 1 << P.log2_parts;
+    const int nparts = P.ndest << P.log2_parts;   // bins
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int tid = threadIdx.x;
     int part[kRadixRowsPerThread];
@@ -197,11 +204,10 @@ __device__ __forceinline__ void radix_tile(const RadixParams& P, uint8_t* stage,
             keyraw[r] = P.key_type == IGL_T_I32 ? (uint64_t)((const uint32_t*)kbase)[li] : ((const uint64_t*)kbase)[li];
         }
     }
-    const int pshift = 64 - P.log2_parts;
 #pragma unroll
     for (int r = 0; r < kRadixRowsPerThread; ++r) {
         const bool ok = FULL || (r * kRadixThreads + tid) < rows;
-        part[r] = (int)(mix64(part_canon(P.key_type, keyraw[r])) >> pshift);
+        part[r] = radix_bin_of(mix64(part_canon(P.key_type, keyraw[r])), P.ndest, P.log2_parts);
         rank[r] = 0;
         if (ok) rank[r] = atomicAdd(&s_cnt[part[r]], 1u);
         else part[r] = -1;
@@ -266,23 +272,24 @@ __device__ __forceinline__ void radix_tile(const RadixParams& P, uint8_t* stage,
     __syncthreads();
     // write-out: consecutive threads -> consecutive slots -> runs of consecutive destination rows
     unsigned long long d[kRadixRowsPerThread];
+    int dq[kRadixRowsPerThread];   // destination of each staged slot (0 when partitioning locally)
 #pragma unroll
     for (int r = 0; r < kRadixRowsPerThread; ++r) {
         const int sl = r * kRadixThreads + tid;
-        d[r] = 0;
-        if (FULL || sl < rows) { const int p = s_part[sl]; d[r] = s_gbase[p] + (unsigned)(sl - s_cnt[p]); }
+        d[r] = 0; dq[r] = 0;
+        if (FULL || sl < rows) { const int p = s_part[sl]; d[r] = s_gbase[p] + (unsigned)(sl - s_cnt[p]); dq[r] = p >> P.log2_parts; }
     }
     for (int c = 0; c < P.ncols; ++c) {
         if (P.shift[c] == 3) {
             const uint64_t* sc = reinterpret_cast<const uint64_t*>(stage + P.stage_off[c]) + tid;
-            uint64_t* dst = reinterpret_cast<uint64_t*>(P.dst[c]);
 #pragma unroll
-            for (int r = 0; r < kRadixRowsPerThread; ++r) if (FULL || r * kRadixThreads + tid < rows) dst[d[r]] = sc[r * kRadixThreads];
+            for (int r = 0; r < kRadixRowsPerThread; ++r)
+                if (FULL || r * kRadixThreads + tid < rows) reinterpret_cast<uint64_t*>(P.dst[dq[r]][c])[d[r]] = sc[r * kRadixThreads];
         } else {
             const uint32_t* sc = reinterpret_cast<const uint32_t*>(stage + P.stage_off[c]) + tid;
-            uint32_t* dst = reinterpret_cast<uint32_t*>(P.dst[c]);
 #pragma unroll
-            for (int r = 0; r < kRadixRowsPerThread; ++r) if (FULL || r * kRadixThreads + tid < rows) dst[d[r]] = sc[r * kRadixThreads];
+            for (int r = 0; r < kRadixRowsPerThread; ++r)
+                if (FULL || r * kRadixThreads + tid < rows) reinterpret_cast<uint32_t*>(P.dst[dq[r]][c])[d[r]] = sc[r * kRadixThreads];
         }
     }
     __syncthreads();
@@ -294,7 +301,7 @@ __global__ void __launch_bounds__(kRadixThreads, 2) radix_scatter_kernel(const _
     __shared__ unsigned long long s_gbase[kRadixMaxParts];
     __shared__ unsigned short s_part[kRadixTile];       // partition of each staged slot
     __shared__ unsigned int s_warp_tot[kRadixThreads / 32];
-    const int nparts = 1 << P.log2_parts;
+    const int nparts = P.ndest << P.log2_parts;
     const long long ntiles = (P.n + kRadixTile - 1) / kRadixTile;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         for (int p = threadIdx.x; p < nparts; p += kRadixThreads) s_cnt[p] = 0;
@@ -318,14 +325,14 @@ int32_t radix_partition(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int ke
     unsigned long long* cursor = offsets + (nparts + 1);
     IGL_CUDA_OK(cudaMemsetAsync(hist, 0, sizeof(unsigned long long) * (nparts + 1), st));
     RadixParams P{};
-    P.ncols = ncols; P.key_col = key_col; P.key_type = cols[key_col].type; P.log2_parts = log2_parts; P.n = nrows;
+    P.ncols = ncols; P.key_col = key_col; P.key_type = cols[key_col].type; P.log2_parts = log2_parts; P.ndest = 1; P.n = nrows;
     P.offsets = offsets; P.cursor = cursor;
     uint32_t off = 0;
     for (int c = 0; c < ncols; ++c) {
         const int t = cols[c].type;
         if (t != IGL_T_I32 && t != IGL_T_I64 && t != IGL_T_F64) return fail(IGL_ERR_UNSUPPORTED, "radix_partition: fixed-width columns only");
         if (cols[c].validity) return fail(IGL_ERR_UNSUPPORTED, "radix_partition: nullable columns are not partitioned");
-        P.src[c] = (const uint8_t*)cols[c].data; P.dst[c] = (uint8_t*)dst[c];
+        P.src[c] = (const uint8_t*)cols[c].data; P.dst[0][c] = (uint8_t*)dst[c];
         P.shift[c] = t == IGL_T_I32 ? 2 : 3;
         P.stage_off[c] = off;
         off += (uint32_t)kRadixTile << P.shift[c];
@@ -333,7 +340,7 @@ int32_t radix_partition(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int ke
     if (off > (96u << 10)) return fail(IGL_ERR_UNSUPPORTED, "radix_partition: row too wide (%u bytes of staging)", off);
     const int grid = ctx->sm_count * 2;
     if (nrows > 0) {
-        radix_hist_kernel<<<grid * 2, 512, 0, st>>>(cols[key_col].data, P.key_type, nrows, log2_parts, hist);
+        radix_hist_kernel<<<grid * 2, 512, 0, st>>>(cols[key_col].data, P.key_type, nrows, 1, log2_parts, hist);
         IGL_CUDA_OK(cudaGetLastError());
     }
     radix_scan_kernel<<<1, kRadixMaxParts, 0, st>>>(hist, offsets, cursor, nparts);
@@ -414,6 +421,77 @@ int32_t igl_partition_scatter(igl_ctx* ctx, const igl_dev_col* cols, int32_t nco
     if (e == cudaSuccess) e = cudaStreamSynchronize(st);
     pool_free(ctx, cursor);
     if (e != cudaSuccess) return fail(IGL_ERR_CUDA, "igl_partition_scatter: %s", cudaGetErrorString(e));
+    return IGL_OK;
+}
+
+// ---- exchange fused with the join's own partitioning ---------------------------------
+// Bins = ndest * 2^log2_parts, destination-major.  A receiver lays its slab out partition by
+// partition (inside a partition: source by source), so what arrives is already in the order
+// igl_join_build / igl_join_probe want (igl_join_set_prepartitioned) and rows cross NVLink as
+// runs staged in shared memory, not as single 8-byte stores.
+int32_t igl_partition_histogram_radix(igl_ctx* ctx, const igl_dev_col* key, int64_t nrows, int32_t ndest, int32_t log2_parts,
+                                      int64_t* dev_hist, void* stream) {
+    if (!ctx || !key || !dev_hist || nrows < 0) return fail(IGL_ERR_INVALID_ARG, "igl_partition_histogram_radix: bad arguments");
+    if (ndest < 1 || ndest > kPartMaxParts || log2_parts < 0 || (ndest << log2_parts) > kRadixMaxParts)
+        return fail(IGL_ERR_UNSUPPORTED, "ndest in [1, %d] and ndest << log2_parts <= %d", kPartMaxParts, kRadixMaxParts);
+    if (key->type != IGL_T_I32 && key->type != IGL_T_I64 && key->type != IGL_T_F64)
+        return fail(IGL_ERR_UNSUPPORTED, "partition key must be Int32/Int64/Float64");
+    if (key->validity) return fail(IGL_ERR_UNSUPPORTED, "nullable keys take igl_partition_histogram / igl_partition_scatter");
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = pick_stream(ctx, stream);
+    IGL_CUDA_OK(cudaMemsetAsync(dev_hist, 0, sizeof(int64_t) * ((size_t)ndest << log2_parts), st));
+    if (nrows == 0) return IGL_OK;
+    radix_hist_kernel<<<ctx->sm_count * 4, 512, 0, st>>>(key->data, key->type, nrows, ndest, log2_parts, (unsigned long long*)dev_hist);
+    IGL_CUDA_OK(cudaGetLastError());
+    ctx->launches++;
+    return IGL_OK;
+}
+
+int32_t igl_partition_scatter_radix(igl_ctx* ctx, const igl_dev_col* cols, int32_t ncols, int32_t key_col, int64_t nrows,
+                                    int32_t ndest, int32_t log2_parts, void* const* dst, const int64_t* bin_row_offset,
+                                    void* stream) {
+    if (!ctx || !cols || !dst || !bin_row_offset || nrows < 0) return fail(IGL_ERR_INVALID_ARG, "igl_partition_scatter_radix: bad arguments");
+    if (ndest < 1 || ndest > kPartMaxParts || log2_parts < 0 || (ndest << log2_parts) > kRadixMaxParts)
+        return fail(IGL_ERR_UNSUPPORTED, "ndest in [1, %d] and ndest << log2_parts <= %d", kPartMaxParts, kRadixMaxParts);
+    if (ncols < 1 || ncols > kPartMaxCols || key_col < 0 || key_col >= ncols) return fail(IGL_ERR_INVALID_ARG, "igl_partition_scatter_radix: bad column set");
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = pick_stream(ctx, stream);
+    const int bins = ndest << log2_parts;
+    RadixParams P{};
+    P.ncols = ncols; P.key_col = key_col; P.key_type = cols[key_col].type; P.log2_parts = log2_parts; P.ndest = ndest; P.n = nrows;
+    uint32_t off = 0;
+    for (int c = 0; c < ncols; ++c) {
+        const int t = cols[c].type;
+        if (t != IGL_T_I32 && t != IGL_T_I64 && t != IGL_T_F64) return fail(IGL_ERR_UNSUPPORTED, "partitioned columns must be Int32/Int64/Float64");
+        if (cols[c].validity) return fail(IGL_ERR_UNSUPPORTED, "nullable columns take igl_partition_scatter");
+        P.src[c] = (const uint8_t*)cols[c].data;
+        P.shift[c] = t == IGL_T_I32 ? 2 : 3;
+        P.stage_off[c] = off;
+        off += (uint32_t)kRadixTile << P.shift[c];
+        for (int d = 0; d < ndest; ++d) {
+            if (!dst[d * ncols + c]) return fail(IGL_ERR_INVALID_ARG, "destination pointer [%d][%d] is NULL", d, c);
+            P.dst[d][c] = (uint8_t*)dst[d * ncols + c];
+        }
+    }
+    if (off > (96u << 10)) return fail(IGL_ERR_UNSUPPORTED, "row too wide (%u bytes of staging)", off);
+    if (nrows == 0) return IGL_OK;
+    // device copy of the offsets + zeroed cursors; handed back to the pool once the kernel is done
+    void* scratch = nullptr;
+    IGL_TRY(pool_alloc(ctx, sizeof(unsigned long long) * 2 * kRadixMaxParts, &scratch));
+    unsigned long long* offsets = (unsigned long long*)scratch;
+    unsigned long long* cursor = offsets + kRadixMaxParts;
+    cudaError_t e = cudaMemcpyAsync(offsets, bin_row_offset, sizeof(int64_t) * bins, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemsetAsync(cursor, 0, sizeof(unsigned long long) * bins, st);
+    P.offsets = offsets; P.cursor = cursor;
+    if (e == cudaSuccess) e = cudaFuncSetAttribute((const void*)radix_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 << 10);
+    if (e == cudaSuccess) {
+        radix_scatter_kernel<<<ctx->sm_count * 2, kRadixThreads, off, st>>>(P);
+        e = cudaGetLastError();
+        ctx->launches++;
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    pool_free(ctx, scratch);
+    if (e != cudaSuccess) return fail(IGL_ERR_CUDA, "igl_partition_scatter_radix: %s", cudaGetErrorString(e));
     return IGL_OK;
 }
 

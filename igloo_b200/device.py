@@ -273,6 +273,12 @@ class HashJoin:
         check(lib.igl_join_probe_count(self._h, a, nrows, C.byref(n), self.ctx.stream()))
         return n.value
 
+    def phase_ms(self):
+        """Device time of the last build / probe: build partitioning, build, probe partitioning, probe kernel."""
+        out = (C.c_double * 4)()
+        check(lib.igl_join_phase_ms(self._h, out))
+        return [float(x) for x in out]
+
     def alloc_outputs(self, capacity: int, left_cols: Sequence[DeviceColumn]) -> List[DeviceColumn]:
         out = []
         nl = len(self.left)

@@ -54,6 +54,33 @@ class ExchangePlan:
         return ExchangePlan(rank, world, send, recv, roff, dst_off, int(sum(recv)))
 
 
+@dataclass
+class RadixExchangePlan:
+    """Bookkeeping of the exchange fused with the join's radix partitioning.
+
+    counts[src][dest * parts + part] = rows of source `src` that belong to partition
+    `part` of destination `dest`.  A destination's slab is laid out partition by
+    partition and, inside a partition, source by source — so the rows a GPU receives are
+    already ordered by the top bits of the join hash, the order its local build and
+    probe want (igl_join_set_prepartitioned)."""
+    rank: int
+    world: int
+    parts: int
+    bin_row_offset: List[int]   # [world * parts]: where THIS rank's rows of each bin start in the destination's slab
+    send_counts: List[int]      # rows this rank sends to each destination
+    total_recv: int             # rows this rank receives
+
+    @staticmethod
+    def from_counts(counts, rank: int, world: int, parts: int) -> "RadixExchangePlan":
+        c = np.asarray(counts, dtype=np.int64).reshape(world, world, parts)      # [src][dest][part]
+        per_part = c.sum(axis=0)                                                  # [dest][part]
+        part_start = np.cumsum(per_part, axis=1) - per_part                       # first row of a partition in its slab
+        before_me = c[:rank].sum(axis=0)                                          # rows of lower-ranked sources, per bin
+        off = (part_start + before_me).reshape(-1)
+        return RadixExchangePlan(rank, world, parts, [int(x) for x in off], [int(x) for x in c[rank].sum(axis=1)],
+                                 int(per_part[rank].sum()))
+
+
 class RawBuffer:
     """A pool block from igl_dev_alloc (its own cudaMalloc, so IPC-exportable)."""
 
@@ -96,6 +123,9 @@ class PartitionedJoin:
         self.out_capacity = 0
         import torch
         self._hist = torch.zeros(2, world, dtype=torch.int64, device=f"cuda:{ctx.device}")
+        # p2p: the exchange also does the join's radix partitioning (set in prepare())
+        self.log2_parts = 0
+        self.fused = False
 
     # ---- set-up --------------------------------------------------------------
     def prepare(self, right_cols, n_right, left_cols, n_left, slack: float = 1.10):
@@ -107,6 +137,13 @@ class PartitionedJoin:
         self.L.cols, self.L.nrows = list(left_cols), n_left
         tot = torch.tensor([n_right, n_left], dtype=torch.int64, device=f"cuda:{self.ctx.device}")
         dist.all_reduce(tot)
+        if self.mode == "p2p":
+            # the fan-out the local join would use for its share of the build side
+            self.log2_parts = int(lib.igl_join_partition_bits(self.ctx._h, int(tot[0]) // self.world))
+            self.fused = (self.world << self.log2_parts) <= 1024 and all(c.validity is None for c in self.R.cols + self.L.cols)
+            if self.fused:
+                self._hist = torch.zeros(2, self.world << self.log2_parts, dtype=torch.int64, device=f"cuda:{self.ctx.device}")
+            check(lib.igl_join_set_prepartitioned(self.join._h, 1 if self.fused else 0))
         for side, total in ((self.R, int(tot[0])), (self.L, int(tot[1]))):
             side.capacity = int(total / self.world * slack) + 4096
             side.slabs = [RawBuffer(self.ctx, side.capacity * _W[f.type] + 256) for f in side.fields]
@@ -147,6 +184,15 @@ class PartitionedJoin:
         from .device import DeviceColumn
         ctx, W = self.ctx, self.world
         st = ctx.stream()
+        marks = []
+
+        def mark(name):   # phase boundaries on the device timeline (read back by phase_ms())
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            marks.append((name, ev))
+        mark("start")
+        if self.fused:
+            return self._run_fused(mark, marks)
         # 1. histograms
         for i, side in enumerate((self.R, self.L)):
             key = side.cols[side.key_idx].c_struct()
@@ -155,6 +201,7 @@ class PartitionedJoin:
         allh = torch.empty(W, 2, W, dtype=torch.int64, device=self._hist.device)
         dist.all_gather_into_tensor(allh.view(-1), self._hist.view(-1))
         counts = allh.cpu().numpy()
+        mark("histogram+counts")
         plans = [ExchangePlan.from_counts(counts[:, i, :].tolist(), self.rank) for i in range(2)]
         for side, plan in zip((self.R, self.L), plans):
             if plan.total_recv > side.capacity:
@@ -181,18 +228,72 @@ class PartitionedJoin:
                     src = _as_tensor(side.send[c].ptr, sum(plan.send_counts), dt, ctx.device)
                     dstt = _as_tensor(side.slabs[c].ptr, plan.total_recv, dt, ctx.device)
                     dist.all_to_all_single(dstt, src, plan.recv_counts, plan.send_counts)
+        mark("exchange")
         # 4. local join on what arrived
         nr, nl = plans[0].total_recv, plans[1].total_recv
         rcols = [DeviceColumn(f.type, nr, self.R.slabs[i]) for i, f in enumerate(self.R.fields)]
         lcols = [DeviceColumn(f.type, nl, self.L.slabs[i]) for i, f in enumerate(self.L.fields)]
         self.join.build(rcols, nr)
+        mark("build")
         cap = self.join.probe_count(lcols, nl) if self.join.has_duplicates else nl
         if self.out is None or cap > self.out_capacity:
             self.out_capacity = int(cap * 1.05) + 1024
             self.out = self.join.alloc_outputs(self.out_capacity, lcols)
         _, n = self.join.probe(lcols, nl, out=self.out, capacity=self.out_capacity)
+        mark("probe")
         self.last_plans = plans
+        self._marks = marks
         return n
+
+    def _run_fused(self, mark, marks) -> int:
+        """p2p with the radix partitioning folded into the exchange: rows are sorted by
+        (destination, partition) in shared memory and stored to the peers as runs."""
+        import torch
+        import torch.distributed as dist
+        from .device import DeviceColumn
+        ctx, W, lp = self.ctx, self.world, self.log2_parts
+        st = ctx.stream()
+        bins = W << lp
+        for i, side in enumerate((self.R, self.L)):
+            key = side.cols[side.key_idx].c_struct()
+            check(lib.igl_partition_histogram_radix(ctx._h, C.byref(key), side.nrows, W, lp, self._hist[i].data_ptr(), st))
+        allh = torch.empty(W, 2, bins, dtype=torch.int64, device=self._hist.device)
+        dist.all_gather_into_tensor(allh.view(-1), self._hist.view(-1))
+        counts = allh.cpu().numpy()
+        mark("histogram+counts")
+        plans = [RadixExchangePlan.from_counts(counts[:, i, :], self.rank, W, 1 << lp) for i in range(2)]
+        for side, plan in zip((self.R, self.L), plans):
+            if plan.total_recv > side.capacity:
+                raise RuntimeError(f"receive slab too small: {plan.total_recv} rows > capacity {side.capacity} (skewed keys: raise slack)")
+        dist.barrier()                       # peers are done reading their slabs from the previous join
+        for side, plan in zip((self.R, self.L), plans):
+            nc = len(side.fields)
+            dst = (C.c_void_p * (W * nc))(*[side.peer_ptrs[p][c] for p in range(W) for c in range(nc)])
+            off = (C.c_int64 * bins)(*plan.bin_row_offset)
+            check(lib.igl_partition_scatter_radix(ctx._h, self._devcols(side), nc, side.key_idx, side.nrows, W, lp, dst, off, st))
+        torch.cuda.synchronize()
+        dist.barrier()                       # every rank's stores have landed
+        mark("exchange")
+        nr, nl = plans[0].total_recv, plans[1].total_recv
+        rcols = [DeviceColumn(f.type, nr, self.R.slabs[i]) for i, f in enumerate(self.R.fields)]
+        lcols = [DeviceColumn(f.type, nl, self.L.slabs[i]) for i, f in enumerate(self.L.fields)]
+        self.join.build(rcols, nr)
+        mark("build")
+        cap = self.join.probe_count(lcols, nl) if self.join.has_duplicates else nl
+        if self.out is None or cap > self.out_capacity:
+            self.out_capacity = int(cap * 1.05) + 1024
+            self.out = self.join.alloc_outputs(self.out_capacity, lcols)
+        _, n = self.join.probe(lcols, nl, out=self.out, capacity=self.out_capacity)
+        mark("probe")
+        self.last_plans = plans
+        self._marks = marks
+        return n
+
+    def phase_ms(self):
+        """Device time of each phase of the last run() on this rank."""
+        import torch
+        torch.cuda.synchronize()
+        return {b[0]: round(a[1].elapsed_time(b[1]), 3) for a, b in zip(self._marks, self._marks[1:])}
 
 
 def _as_tensor(ptr: int, n: int, dtype, device: int):

@@ -200,6 +200,18 @@ int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_
                        int64_t out_capacity, int64_t* out_rows, void* stream);
 /* 1 when the build side held duplicate keys (chain walks), else 0. */
 int32_t igl_join_has_duplicates(const igl_join* j);
+/* Large build sides are reordered by the top bits of the join hash before the table is
+ * built, and every probe chunk likewise, so each 16 MB region of the table is filled and
+ * probed while it is L2-resident.  igl_join_partition_bits: log2 of the fan-out
+ * igl_join_build would use for `build_rows` rows (0 = none).  A caller whose rows already
+ * arrive in that order (igl_partition_scatter_radix) switches the join's own reordering
+ * off with igl_join_set_prepartitioned(j, 1).  No counterpart in the reference. */
+int32_t igl_join_partition_bits(igl_ctx* ctx, int64_t build_rows);
+int32_t igl_join_set_prepartitioned(igl_join* j, int32_t on);
+/* Device time (ms, CUDA events on the call's stream) of the last build and probe of `j`:
+ * out[0] build-side partitioning, out[1] table init + build kernels, out[2] probe-side
+ * partitioning, out[3] the probe kernel (-1 where nothing was recorded).  Measurement aid. */
+int32_t igl_join_phase_ms(igl_join* j, double out[4]);
 void igl_join_destroy(igl_join* j);
 
 /* ---- hash repartition for the multi-GPU join (the "worker fragment exchange":
@@ -214,6 +226,19 @@ int32_t igl_partition_histogram(igl_ctx* ctx, const igl_dev_col* key, int64_t nr
 int32_t igl_partition_scatter(igl_ctx* ctx, const igl_dev_col* cols, int32_t ncols, int32_t key_col,
                               int64_t nrows, int32_t nparts, void* const* dst /* host [nparts*ncols] */,
                               const int64_t* dst_row_offset /* host [nparts] */, void* stream);
+/* The same exchange fused with the join's radix partitioning: bins = ndest << log2_parts,
+ * bin = dest * 2^log2_parts + (top log2_parts bits of the join hash).  The histogram counts
+ * rows per bin; the scatter sorts each 4096-row tile by bin in shared memory and stores runs
+ * to dst[dest * ncols + c] + bin_row_offset[bin] rows, so a receiver that lays its slab out
+ * partition by partition gets its rows in the order igl_join_build / igl_join_probe want.
+ * Non-nullable columns only. */
+int32_t igl_partition_histogram_radix(igl_ctx* ctx, const igl_dev_col* key, int64_t nrows, int32_t ndest,
+                                      int32_t log2_parts, int64_t* dev_hist /* [ndest << log2_parts] */,
+                                      void* stream);
+int32_t igl_partition_scatter_radix(igl_ctx* ctx, const igl_dev_col* cols, int32_t ncols, int32_t key_col,
+                                    int64_t nrows, int32_t ndest, int32_t log2_parts,
+                                    void* const* dst /* host [ndest*ncols] */,
+                                    const int64_t* bin_row_offset /* host [ndest << log2_parts] */, void* stream);
 /* CUDA IPC plumbing so one process per GPU can map its peers' receive slabs. */
 int32_t igl_ipc_export(igl_ctx* ctx, void* dev_ptr, uint8_t handle_out[64]);
 int32_t igl_ipc_open(igl_ctx* ctx, const uint8_t handle[64], void** dev_ptr_out);

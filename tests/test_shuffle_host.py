@@ -10,7 +10,7 @@ import textwrap
 import numpy as np
 import pytest
 
-from igloo_b200.shuffle import ExchangePlan
+from igloo_b200.shuffle import ExchangePlan, RadixExchangePlan
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
@@ -25,6 +25,23 @@ def test_exchange_plan_offsets_are_a_partition_of_each_slab():
         assert plans[p].recv_counts == [counts[s][p] for s in range(3)]
         assert plans[p].recv_offsets == [plans[s].dst_row_offset[p] for s in range(3)]
     assert [pl.send_counts for pl in plans] == counts
+
+
+def test_radix_exchange_plan_lays_slabs_out_partition_by_partition():
+    rng = np.random.default_rng(3)
+    world, parts = 3, 4
+    counts = rng.integers(0, 50, (world, world * parts))          # [src][dest * parts + part]
+    plans = [RadixExchangePlan.from_counts(counts, r, world, parts) for r in range(world)]
+    c = counts.reshape(world, world, parts)
+    for d in range(world):
+        # walking the destination's slab: partition 0 of source 0, of source 1, ..., then partition 1, ...
+        pos = 0
+        for part in range(parts):
+            for src in range(world):
+                assert plans[src].bin_row_offset[d * parts + part] == pos
+                pos += int(c[src][d][part])
+        assert pos == plans[d].total_recv
+    assert [pl.send_counts for pl in plans] == [[int(c[s][d].sum()) for d in range(world)] for s in range(world)]
 
 
 WORKER = textwrap.dedent('''
