@@ -4,8 +4,12 @@
 // compacts rows.
 #pragma once
 
+#ifdef __CUDACC_RTC__
+#include "stdint.h"   // supplied by fp_jit.cpp: NVRTC has no system headers
+#else
 #include <cuda_runtime.h>
 #include <stdint.h>
+#endif
 
 namespace igl {
 

@@ -229,6 +229,7 @@ struct TilePipe {
     }
 };
 
+#ifndef __CUDACC_RTC__
 // ---- host-side ring geometry ------------------------------------------------------
 struct PipeGeometry {
     int stages = 2;
@@ -287,5 +288,7 @@ inline PipeGeometry pipe_geometry(const uint8_t* shift, int ncols, PipeCols& T, 
     T.stage_bytes = g.stage_bytes;
     return g;
 }
+
+#endif  // !__CUDACC_RTC__
 
 }  // namespace igl

@@ -193,6 +193,11 @@ class FilterProject:
             lib.igl_fp_destroy(self._h)
         self._h = None
 
+    @property
+    def is_specialised(self) -> bool:
+        """True once the plan runs on kernels compiled for it at run time (igl_fp_is_specialised)."""
+        return bool(lib.igl_fp_is_specialised(self._h))
+
     def alloc_outputs(self, nrows: int) -> List[DeviceColumn]:
         return [DeviceColumn.empty(f.type, nrows, self.ctx.device, nullable=f.nullable) for f in self.out_fields]
 

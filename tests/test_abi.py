@@ -95,3 +95,19 @@ def test_cpp_host_mirror_compiles_and_links_against_the_abi(lib, tmp_path):
     subprocess.check_call(["g++", "-std=c++17", "-Wall", "-Werror", "-o", str(exe), os.path.join(ROOT, "tests", "host_mirror_check.cpp"),
                            "-L", os.path.join(ROOT, "igloo_b200"), "-ligloo_cuda", f"-Wl,-rpath,{os.path.join(ROOT, 'igloo_b200')}"])
     subprocess.check_call([str(exe)])
+
+
+def test_device_sources_compile_with_nvrtc_for_sm_100a():
+    """fp_jit.cpp: the embedded device headers plus a generated operator build with NVRTC on a machine
+    without a GPU (three hand-built operators; see igl_jit_selftest)."""
+    import ctypes as C
+    from igloo_b200._lib import lib
+    n = C.c_int64(0)
+    rc = lib.igl_jit_selftest(C.byref(n))
+    if rc < 0:
+        lib.igl_last_error.restype = C.c_char_p
+        msg = lib.igl_last_error().decode()
+        if "NVRTC is not available" in msg:
+            pytest.skip(msg)
+        raise AssertionError(msg)
+    assert n.value > 10_000

@@ -25,7 +25,7 @@ def _fields(tbl):
     return tight_fields(tbl)
 
 
-def gpu_filter_project(ctx, tbl, pred, proj, two_pass=None):
+def gpu_filter_project(ctx, tbl, pred, proj, two_pass=None, expect_specialised=None):
     """two_pass: None = the library's own choice by input size; False / True force the one-pass
     (in-kernel ordered scan) or two-pass (survivor bitmap + tile offsets) form of the filter."""
     from igloo_b200.device import DeviceColumn, FilterProject
@@ -42,6 +42,8 @@ def gpu_filter_project(ctx, tbl, pred, proj, two_pass=None):
         if old is not None:
             os.environ["IGL_FP_TWO_PASS"] = old
     out, n = fp.run(cols, tbl.num_rows)
+    if expect_specialised is not None and tbl.num_rows > 0:
+        assert fp.is_specialised == expect_specialised
     arrays = [c.to_arrow(n) for c in out]
     return pa.Table.from_arrays(arrays, schema=schema_of(fp.out_fields))
 
@@ -181,6 +183,33 @@ def test_projection_sees_only_rows_the_filter_kept(ctx):
         with pytest.raises(IglooCudaError) as e:
             gpu_filter_project(ctx, t, col("b") >= lit(0, T_I32), [(col("a") / col("b")).alias("q")], two_pass)
         assert e.value.code == -6
+
+
+def test_run_time_specialised_kernels_match_the_interpreter_and_the_oracle(ctx, monkeypatch):
+    """IGL_FP_JIT=1: every pass is compiled for the plan with NVRTC (fp_jit.cpp).  Same cases as the
+    interpreter gets — fast handlers, generic null-aware steps, temporaries, division errors."""
+    from igloo_b200._lib import IglooCudaError
+    monkeypatch.setenv("IGL_FP_JIT", "1")
+    t = c2_table(100_003)
+    want, _ = oracle_filter_project(t, col("a") < 250, [(col("b") + col("a")).alias("s"), (col("x") * 1.5 + 0.25).alias("y")])
+    for two_pass in (False, True):
+        got = gpu_filter_project(ctx, t, col("a") < 250, [(col("b") + col("a")).alias("s"), (col("x") * 1.5 + 0.25).alias("y")],
+                                 two_pass, expect_specialised=True)
+        _check_one(got, want, True)
+    rng = np.random.default_rng(17)
+    n = 40_000
+    tn = pa.table({"a": pa.array(rng.integers(-50, 50, n), pa.int32(), mask=rng.random(n) < 0.2),
+                   "b": pa.array(rng.random(n) < 0.5, pa.bool_(), mask=rng.random(n) < 0.3),
+                   "c": pa.array(rng.integers(-2**40, 2**40, n), pa.int64(), mask=rng.random(n) < 0.1),
+                   "x": pa.array(rng.random(n) * 100 - 50)})
+    check(ctx, tn, (col("a") > 0) | col("b"), [col("a").is_null().alias("n"), (col("a").cast(T_I64) + col("c")).alias("s"),
+                                               ((col("x") + 1.0) * (col("x") - 1.0)).alias("p"), (col("c") % lit(7, T_I64)).alias("m")])
+    check(ctx, tn, None, [(-col("a")).alias("neg"), (col("x") / lit(0.0)).alias("q"), col("x").cast(T_I32).alias("i")])
+    with pytest.raises(IglooCudaError) as e:
+        gpu_filter_project(ctx, tn, None, [(col("a") / lit(0, T_I32)).alias("q")])
+    assert e.value.code == -6
+    monkeypatch.setenv("IGL_FP_JIT", "0")
+    gpu_filter_project(ctx, t, col("a") < 250, [col("b")], True, expect_specialised=False)
 
 
 def test_predicate_must_be_boolean(ctx):
