@@ -106,7 +106,10 @@ __global__ void join_init_kernel(Slot* slots, uint64_t capacity, JoinSide* side)
 // ---- K5 build, unique layout ---------------------------------------------------------
 // payload_shift: 2 / 3 = width of the inlined payload column, 0xFF = store the row id.
 constexpr int kBuildThreads = 256;
-constexpr int kBuildU = 4;                                   // rows per thread per chunk: 4 independent atomics in flight
+#ifndef IGL_BUILD_U
+#define IGL_BUILD_U 4
+#endif
+constexpr int kBuildU = IGL_BUILD_U;                                   // rows per thread per chunk: 4 independent atomics in flight
 constexpr int kBuildChunk = kBuildThreads * kBuildU;
 
 // Chunks are claimed from an atomic ticket (not a static grid stride): all CTAs
@@ -117,14 +120,15 @@ __global__ void __launch_bounds__(kBuildThreads) join_build_unique_kernel(const 
                                                                            const void* __restrict__ payload, int payload_shift,
                                                                            long long n, JoinTable t, unsigned int* ticket) {
     constexpr int U = kBuildU;
-    __shared__ long long s_chunk;
+    __shared__ long long s_chunk[2];
     const long long nchunks = (n + kBuildChunk - 1) / kBuildChunk;
-    while (true) {
-        if (threadIdx.x == 0) s_chunk = (long long)atomicAdd(ticket, 1u);
-        __syncthreads();
-        const long long chunk = s_chunk;
-        __syncthreads();
+    // the ticket for the NEXT chunk is drawn while this one is inserted: its L2 round trip is hidden
+    if (threadIdx.x == 0) s_chunk[0] = (long long)atomicAdd(ticket, 1u);
+    __syncthreads();
+    for (int it = 0;; ++it) {
+        const long long chunk = s_chunk[it & 1];
         if (chunk >= nchunks) break;
+        if (threadIdx.x == 0) s_chunk[(it + 1) & 1] = (long long)atomicAdd(ticket, 1u);
         const long long i0 = chunk * kBuildChunk + threadIdx.x;
         uint64_t k[U], h[U];
         unsigned long long val[U];
@@ -160,6 +164,7 @@ __global__ void __launch_bounds__(kBuildThreads) join_build_unique_kernel(const 
                 else h[u] = (h[u] + 1) & t.mask;
             }
         }
+        __syncthreads();   // s_chunk[(it + 1) & 1] is written; s_chunk[it & 1] may be overwritten next round
     }
 }
 
@@ -559,12 +564,15 @@ __global__ void __launch_bounds__(kPipeThreads, kPipeMinCtas) join_probe_multi_k
 // pipeline, which matters once the table is L2-resident (radix-partitioned
 // input) and HBM latency no longer hides them.
 // ---------------------------------------------------------------------------
-constexpr int kFlatThreads = 256;
+#ifndef IGL_FLAT_THREADS
+#define IGL_FLAT_THREADS 32
+#endif
+constexpr int kFlatThreads = IGL_FLAT_THREADS;
 #ifndef IGL_FLAT_ROWS
 #define IGL_FLAT_ROWS 4
 #endif
 #ifndef IGL_FLAT_CTAS
-#define IGL_FLAT_CTAS 3
+#define IGL_FLAT_CTAS 24
 #endif
 constexpr int kFlatRows = IGL_FLAT_ROWS;
 constexpr int kFlatChunk = kFlatThreads * kFlatRows;   // 1024 rows per CTA iteration
@@ -583,6 +591,9 @@ struct FlatProbeParams {
                             // (partitioned) input and the table region they touch stays L2-resident
     uint32_t stage_off[kJoinMaxCols];   // byte offset of each left column's chunk slice inside a stage
     uint32_t stage_bytes;
+    // DENSE form: matched rows keep their input position, the warps leave a hit bitmap
+    uint32_t* hit_words;                // bit i = probe row i matched; padded to whole 1024-row tiles, zero-filled
+    unsigned long long* miss_counter;
 };
 
 constexpr int kFlatStages = 3;   // chunks in flight per CTA: the one being probed + two on their way from HBM
@@ -591,7 +602,17 @@ constexpr int kFlatStages = 3;   // chunks in flight per CTA: the one being prob
 // copies issued by thread 0 two chunks ahead (the threads themselves only have four
 // rows each in flight, far too few bytes to cover HBM latency); table buckets are
 // read directly (L2-resident region) and the output is stored straight from registers.
-template <int KEY_TYPE>
+//
+// One warp per CTA (24 CTAs per SM): measured, the probe's speed follows the number of
+// independent chunk chains per SM, not the rows in flight (256-thread CTAs 19.5 ms, 128: 17.6,
+// 64: 16.0, 32: 14.9 for C3).  With one output reservation per 128-row chunk the shared
+// cursor then becomes the limit (same-address atomics top out near 0.55 G/s), so the
+// DENSE form drops the cursor: an inner join against a unique table yields one row or
+// none per probe row — nearly always one in the foreign-key joins this path exists for —
+// and matched rows are written at their INPUT position.  If any row missed, dense_fix
+// afterwards moves matched rows from the tail into the holes (output order carries no
+// meaning here: the partitioned probe is already unordered).
+template <int KEY_TYPE, bool DENSE>
 __global__ void __launch_bounds__(kFlatThreads, IGL_FLAT_CTAS) join_probe_flat_kernel(const __grid_constant__ FlatProbeParams P) {
     extern __shared__ __align__(128) uint8_t fsmem[];
     __shared__ uint64_t s_full[kFlatStages];
@@ -605,6 +626,7 @@ __global__ void __launch_bounds__(kFlatThreads, IGL_FLAT_CTAS) join_probe_flat_k
     const Slot* slots = P.table.slots;
     const int tshift = P.table.shift + 1;   // slot index -> bucket index
     const int lrow = warp * (32 * kFlatRows) + lane;   // this lane's first row inside a chunk
+    unsigned int misses = 0;
     // ---- producer state (thread 0 only) ----
     long long grp_base = 0;
     int grp_used = kFlatClaim;
@@ -724,24 +746,38 @@ __global__ void __launch_bounds__(kFlatThreads, IGL_FLAT_CTAS) join_probe_flat_k
         unsigned int wcnt = 0;
 #pragma unroll
         for (int r = 0; r < kFlatRows; ++r) { hb[r] = __ballot_sync(0xffffffffu, (hit >> r) & 1u); wcnt += __popc(hb[r]); }
-        if (lane == 0) s_wcnt[warp] = wcnt;
-        __syncthreads();   // every thread is also done with the previous chunk's stage
-        if (threadIdx.x == 0) {
-            if (it > 0) refill((it - 1) % kFlatStages);
-            unsigned int tot = 0;
+        unsigned long long obase;
+        unsigned int p[kFlatRows];   // 32-bit output offsets from obase
+        if (DENSE) {
+            uint32_t mine = 0;   // the ballots are the bitmap words of this warp's rows
 #pragma unroll
-            for (int w = 0; w < kFlatThreads / 32; ++w) tot += s_wcnt[w];
-            s_base = tot ? atomicAdd(P.out_counter, (unsigned long long)tot) : 0ull;
+            for (int r = 0; r < kFlatRows; ++r) {
+                misses += __popc(__ballot_sync(0xffffffffu, (live >> r) & 1u)) - __popc(hb[r]);
+                mine = lane == r ? hb[r] : mine;
+                p[r] = (unsigned int)(lrow + r * 32);
+            }
+            if (lane < kFlatRows) P.hit_words[(cbase >> 5) + warp * kFlatRows + lane] = mine;
+            __syncthreads();   // every thread is done with the previous chunk's stage
+            if (threadIdx.x == 0 && it > 0) refill((it - 1) % kFlatStages);
+            obase = (unsigned long long)cbase;
+        } else {
+            if (lane == 0) s_wcnt[warp] = wcnt;
+            __syncthreads();   // every thread is also done with the previous chunk's stage
+            if (threadIdx.x == 0) {
+                if (it > 0) refill((it - 1) % kFlatStages);
+                unsigned int tot = 0;
+#pragma unroll
+                for (int w = 0; w < kFlatThreads / 32; ++w) tot += s_wcnt[w];
+                s_base = tot ? atomicAdd(P.out_counter, (unsigned long long)tot) : 0ull;
+            }
+            __syncthreads();
+            obase = s_base;   // uniform
+            unsigned int lpos = 0;
+            for (int w = 0; w < warp; ++w) lpos += s_wcnt[w];
+            __syncthreads();   // s_wcnt / s_base are rewritten by the next chunk
+#pragma unroll
+            for (int r = 0; r < kFlatRows; ++r) { p[r] = lpos + __popc(hb[r] & lt_mask); lpos += __popc(hb[r]); }
         }
-        __syncthreads();
-        const unsigned long long obase = s_base;   // uniform
-        unsigned int lpos = 0;
-        for (int w = 0; w < warp; ++w) lpos += s_wcnt[w];
-        __syncthreads();   // s_wcnt / s_base are rewritten by the next chunk
-        // 32-bit output offsets inside this chunk's reservation
-        unsigned int p[kFlatRows];
-#pragma unroll
-        for (int r = 0; r < kFlatRows; ++r) { p[r] = lpos + __popc(hb[r] & lt_mask); lpos += __popc(hb[r]); }
         // column by column: uniform width test, unconditional (clamped) loads, predicated stores
         for (int c = 0; c < P.n_left; ++c) {
             const bool is_key = c == P.key_col;
@@ -777,6 +813,55 @@ __global__ void __launch_bounds__(kFlatThreads, IGL_FLAT_CTAS) join_probe_flat_k
 #pragma unroll
                 for (int r = 0; r < kFlatRows; ++r)
                     if ((hit >> r) & 1u) st_cs_u32(dst + p[r], mode == 0 ? (uint32_t)val[r] : mode == 1 ? (uint32_t)raw[r] : src[(uint32_t)val[r]]);
+            }
+        }
+    }
+    if (DENSE && lane == 0 && misses) atomicAdd(P.miss_counter, (unsigned long long)misses);
+}
+
+// Hole filling after a dense probe with misses.  H = matched rows in total; the output is
+// dense once every unmatched position below H holds a matched row taken from at or above H.
+// One warp per 32-row bitmap word; tile_off[] (per `tile_rows` rows) gives the matched rows
+// before each tile.  The j-th hole (from the front) receives the matched tail row that has
+// j matched rows after it.
+struct DenseFixParams {
+    const uint32_t* hit_words;
+    const unsigned long long* tile_off;   // [ntiles + 1]
+    int tile_rows;
+    long long nrows;
+    uint32_t* holes;                      // [misses]
+    void* out[2 * kJoinMaxCols];
+    uint8_t shift[2 * kJoinMaxCols];
+    int ncols;
+};
+
+template <bool FILL>
+__global__ void __launch_bounds__(256) dense_fix_kernel(const __grid_constant__ DenseFixParams P) {
+    const int lane = threadIdx.x & 31;
+    const long long nwords = (P.nrows + 31) >> 5;
+    const long long ntiles = (P.nrows + P.tile_rows - 1) / P.tile_rows;
+    const unsigned long long H = P.tile_off[ntiles];
+    const int wpt = P.tile_rows >> 5;
+    const long long warps = ((long long)gridDim.x * blockDim.x) >> 5;
+    // the fill pass walks the words at or above H's word, the hole pass the words up to it
+    const long long w_lo = FILL ? (long long)(H >> 5) : 0, w_hi = FILL ? nwords : (long long)((H + 31) >> 5);
+    for (long long w = w_lo + (((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5); w < w_hi; w += warps) {
+        const long long tile = w / wpt;
+        const int j = (int)(w - tile * wpt);
+        int c = 0;
+        for (int i = lane; i < j; i += 32) c += __popc(P.hit_words[tile * wpt + i]);
+        c = __reduce_add_sync(0xffffffffu, c);
+        const uint32_t word = P.hit_words[w];
+        const long long i = (w << 5) + lane;
+        const bool bit = (word >> lane) & 1u;
+        const unsigned long long hb = P.tile_off[tile] + (unsigned)c + __popc(word & ((1u << lane) - 1u));   // matched rows before row i
+        if (!FILL) {
+            if (i < (long long)H && !bit) P.holes[(unsigned long long)i - hb] = (uint32_t)i;
+        } else if (i >= (long long)H && i < P.nrows && bit) {
+            const uint32_t dst = P.holes[H - hb - 1];
+            for (int col = 0; col < P.ncols; ++col) {
+                if (P.shift[col] == 3) ((uint64_t*)P.out[col])[dst] = ((const uint64_t*)P.out[col])[i];
+                else ((uint32_t*)P.out[col])[dst] = ((const uint32_t*)P.out[col])[i];
             }
         }
     }
@@ -1133,28 +1218,74 @@ int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_
                 if (!out[nl + c].data) return fail(IGL_ERR_INVALID_ARG, "output column %d has no data buffer", nl + c);
                 F.out[nl + c] = out[nl + c].data;
             }
-            if (!j->scratch) { IGL_TRY(pool_alloc(ctx, 256, &j->scratch)); j->scratch_bytes = 256; }
-            IGL_CUDA_OK(cudaMemsetAsync(j->scratch, 0, 256, st));
+            // DENSE form (see the kernel): needs room for every probe row and 32-bit row numbers
+            const char* denv = getenv("IGL_JOIN_DENSE");
+            const bool dense = !(denv && denv[0] == '0') && out_capacity >= nrows && nrows < (1ll << 32);
+            constexpr int kFixTile = 1024;   // rows per tile of the hole-filling pass
+            const long long ntiles = (nrows + kFixTile - 1) / kFixTile;
+            const size_t scan_bytes = (((size_t)scan_scratch_words(tile_offsets_scan_tiles(ntiles)) * 8) + 255) & ~(size_t)255;
+            const size_t off_bytes = (((size_t)(ntiles + 1) * 8) + 255) & ~(size_t)255;
+            const size_t bm_bytes = (size_t)ntiles * (kFixTile / 8) + 256;
+            // scratch: [header][offsets-kernel header][scan words][tile offsets][hit bitmap]
+            const size_t need = dense ? 512 + scan_bytes + off_bytes + bm_bytes : 256;
+            if (need > j->scratch_bytes) {
+                if (j->scratch) pool_free(ctx, j->scratch);
+                j->scratch = nullptr; j->scratch_bytes = 0;
+                IGL_TRY(pool_alloc(ctx, need, &j->scratch));
+                j->scratch_bytes = need;
+            }
+            uint8_t* sb = (uint8_t*)j->scratch;
+            IGL_CUDA_OK(cudaMemsetAsync(sb, 0, dense ? 512 + scan_bytes : 256, st));
+            if (dense) IGL_CUDA_OK(cudaMemsetAsync(sb + 512 + scan_bytes + off_bytes, 0, bm_bytes, st));
             F.out_counter = &((PipeHeader*)j->scratch)->aux[1];
             F.ticket = &((PipeHeader*)j->scratch)->ticket;
+            F.hit_words = dense ? (uint32_t*)(sb + 512 + scan_bytes + off_bytes) : nullptr;
+            F.miss_counter = &((PipeHeader*)j->scratch)->aux[2];
             const long long nchunks = (nrows + kFlatChunk - 1) / kFlatChunk;
-            const void* kfn = F.key_type == IGL_T_I32 ? (const void*)join_probe_flat_kernel<IGL_T_I32>
-                            : F.key_type == IGL_T_F64 ? (const void*)join_probe_flat_kernel<IGL_T_F64>
-                                                      : (const void*)join_probe_flat_kernel<IGL_T_I64>;
+            const int kt = F.key_type;
+            const void* kfn = dense ? (kt == IGL_T_I32 ? (const void*)join_probe_flat_kernel<IGL_T_I32, true>
+                                       : kt == IGL_T_F64 ? (const void*)join_probe_flat_kernel<IGL_T_F64, true>
+                                                         : (const void*)join_probe_flat_kernel<IGL_T_I64, true>)
+                                    : (kt == IGL_T_I32 ? (const void*)join_probe_flat_kernel<IGL_T_I32, false>
+                                       : kt == IGL_T_F64 ? (const void*)join_probe_flat_kernel<IGL_T_F64, false>
+                                                         : (const void*)join_probe_flat_kernel<IGL_T_I64, false>);
             const size_t fsmem = (size_t)F.stage_bytes * kFlatStages;
             IGL_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
             int per_sm = 0;
             IGL_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, kFlatThreads, fsmem));
+            if (const char* e = getenv("IGL_FLAT_CTAS_PER_SM")) per_sm = std::min(per_sm, std::max(1, atoi(e)));   // experiments
             const int grid = (int)std::min<long long>(nchunks, (long long)ctx->sm_count * std::max(per_sm, 1));
             void* kargs[] = {&F};
             cudaEventRecord(j->ev[4], st);
             IGL_CUDA_OK(cudaLaunchKernel(kfn, dim3(grid), dim3(kFlatThreads), kargs, fsmem, st));
             cudaEventRecord(j->ev[5], st);
             j->ev_probe = true;
-            IGL_CUDA_OK(cudaGetLastError());
             ctx->launches++;
             IGL_CUDA_OK(cudaMemcpyAsync(j->host_hdr, j->scratch, sizeof(PipeHeader), cudaMemcpyDeviceToHost, st));
             IGL_CUDA_OK(cudaStreamSynchronize(st));
+            if (dense) {
+                const int64_t misses = (int64_t)j->host_hdr->aux[2];
+                if (misses > 0 && misses < nrows) {   // fill the holes below the matched-row count from the tail
+                    void* holes = nullptr;
+                    IGL_TRY(pool_alloc(ctx, (size_t)misses * 4 + 256, &holes));
+                    unsigned long long* tile_off = (unsigned long long*)(sb + 512 + scan_bytes);
+                    cudaError_t e = launch_tile_offsets(F.hit_words, kFixTile, ntiles, tile_off, (PipeHeader*)sb,
+                                                        &((PipeHeader*)(sb + 256))->ticket, (uint64_t*)(sb + 512), ctx->sm_count, st);
+                    DenseFixParams X{};
+                    X.hit_words = F.hit_words; X.tile_off = tile_off; X.tile_rows = kFixTile; X.nrows = nrows;
+                    X.holes = (uint32_t*)holes; X.ncols = nl + nr;
+                    for (int c = 0; c < nl + nr; ++c) { X.out[c] = F.out[c]; X.shift[c] = c < nl ? F.lshift[c] : F.rshift[c - nl]; }
+                    const int fgrid = (int)std::min<long long>(((nrows + 31) / 32 + 7) / 8, (long long)ctx->sm_count * 8);
+                    if (e == cudaSuccess) { dense_fix_kernel<false><<<fgrid, 256, 0, st>>>(X); e = cudaGetLastError(); }
+                    if (e == cudaSuccess) { dense_fix_kernel<true><<<fgrid, 256, 0, st>>>(X); e = cudaGetLastError(); }
+                    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+                    pool_free(ctx, holes);
+                    if (e != cudaSuccess) return fail(IGL_ERR_CUDA, "probe hole filling failed: %s", cudaGetErrorString(e));
+                    ctx->launches += 3;
+                }
+                if (out_rows) *out_rows = nrows - misses;
+                return IGL_OK;
+            }
             if (out_rows) *out_rows = (int64_t)j->host_hdr->aux[1];
             return IGL_OK;
         }

@@ -127,7 +127,15 @@ __global__ void __launch_bounds__(kPartThreads) partition_scatter_kernel(const _
 // of one scattered store per row.
 // ---------------------------------------------------------------------------
 constexpr int kRadixMaxParts = 1024;
-constexpr int kRadixThreads = 512;
+#ifndef IGL_RADIX_THREADS
+#define IGL_RADIX_THREADS 512
+#endif
+#ifndef IGL_RADIX_CTAS
+#define IGL_RADIX_CTAS 2
+#endif
+constexpr int kRadixThreads = IGL_RADIX_THREADS;
+constexpr int kRadixBinsPerThread = kRadixMaxParts / kRadixThreads;
+constexpr unsigned kRadixMaxStage = (IGL_RADIX_CTAS == 1 ? 176u : 96u) << 10;   // dynamic shared memory for the staged tile
 constexpr int kRadixRowsPerThread = 8;
 constexpr int kRadixTile = kRadixThreads * kRadixRowsPerThread;   // 4096 rows per tile: long write runs per partition
 
@@ -215,11 +223,11 @@ __device__ __forceinline__ void radix_tile(const RadixParams& P, uint8_t* stage,
     __syncthreads();
     // exclusive scan of s_cnt[0..nparts) by the CTA (nparts <= 1024 = 2 per thread) + global reservation
     {
-        const int i0 = tid * 2;
-        unsigned int c[2];
+        const int i0 = tid * kRadixBinsPerThread;
+        unsigned int c[kRadixBinsPerThread];
         unsigned int sum = 0;
 #pragma unroll
-        for (int q = 0; q < 2; ++q) { c[q] = (i0 + q < nparts) ? s_cnt[i0 + q] : 0; sum += c[q]; }
+        for (int q = 0; q < kRadixBinsPerThread; ++q) { c[q] = (i0 + q < nparts) ? s_cnt[i0 + q] : 0; sum += c[q]; }
         unsigned int inc = sum;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -231,7 +239,7 @@ __device__ __forceinline__ void radix_tile(const RadixParams& P, uint8_t* stage,
         unsigned int ex = inc - sum;
         for (int w = 0; w < warp; ++w) ex += s_warp_tot[w];
 #pragma unroll
-        for (int q = 0; q < 2; ++q) {
+        for (int q = 0; q < kRadixBinsPerThread; ++q) {
             if (i0 + q < nparts) {
                 s_cnt[i0 + q] = ex;
                 s_gbase[i0 + q] = c[q] ? P.offsets[i0 + q] + atomicAdd(&P.cursor[i0 + q], (unsigned long long)c[q]) : 0ull;
@@ -295,7 +303,7 @@ __device__ __forceinline__ void radix_tile(const RadixParams& P, uint8_t* stage,
     __syncthreads();
 }
 
-__global__ void __launch_bounds__(kRadixThreads, 2) radix_scatter_kernel(const __grid_constant__ RadixParams P) {
+__global__ void __launch_bounds__(kRadixThreads, IGL_RADIX_CTAS) radix_scatter_kernel(const __grid_constant__ RadixParams P) {
     extern __shared__ __align__(16) uint8_t stage[];
     __shared__ unsigned int s_cnt[kRadixMaxParts];     // count, then exclusive start
     __shared__ unsigned long long s_gbase[kRadixMaxParts];
@@ -337,10 +345,10 @@ int32_t radix_partition(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int ke
         P.stage_off[c] = off;
         off += (uint32_t)kRadixTile << P.shift[c];
     }
-    if (off > (96u << 10)) return fail(IGL_ERR_UNSUPPORTED, "radix_partition: row too wide (%u bytes of staging)", off);
-    const int grid = ctx->sm_count * 2;
+    if (off > kRadixMaxStage) return fail(IGL_ERR_UNSUPPORTED, "radix_partition: row too wide (%u bytes of staging)", off);
+    const int grid = ctx->sm_count * IGL_RADIX_CTAS;
     if (nrows > 0) {
-        radix_hist_kernel<<<grid * 2, 512, 0, st>>>(cols[key_col].data, P.key_type, nrows, 1, log2_parts, hist);
+        radix_hist_kernel<<<ctx->sm_count * 4, 512, 0, st>>>(cols[key_col].data, P.key_type, nrows, 1, log2_parts, hist);
         IGL_CUDA_OK(cudaGetLastError());
     }
     radix_scan_kernel<<<1, kRadixMaxParts, 0, st>>>(hist, offsets, cursor, nparts);
@@ -349,7 +357,7 @@ int32_t radix_partition(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int ke
     if (nrows > 0) {
         static bool attr_set = false;
         if (!attr_set) {
-            IGL_CUDA_OK(cudaFuncSetAttribute((const void*)radix_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 << 10));
+            IGL_CUDA_OK(cudaFuncSetAttribute((const void*)radix_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRadixMaxStage));
             attr_set = true;
         }
         radix_scatter_kernel<<<grid, kRadixThreads, off, st>>>(P);
@@ -473,7 +481,7 @@ int32_t igl_partition_scatter_radix(igl_ctx* ctx, const igl_dev_col* cols, int32
             P.dst[d][c] = (uint8_t*)dst[d * ncols + c];
         }
     }
-    if (off > (96u << 10)) return fail(IGL_ERR_UNSUPPORTED, "row too wide (%u bytes of staging)", off);
+    if (off > kRadixMaxStage) return fail(IGL_ERR_UNSUPPORTED, "row too wide (%u bytes of staging)", off);
     if (nrows == 0) return IGL_OK;
     // device copy of the offsets + zeroed cursors; handed back to the pool once the kernel is done
     void* scratch = nullptr;
@@ -483,9 +491,9 @@ int32_t igl_partition_scatter_radix(igl_ctx* ctx, const igl_dev_col* cols, int32
     cudaError_t e = cudaMemcpyAsync(offsets, bin_row_offset, sizeof(int64_t) * bins, cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) e = cudaMemsetAsync(cursor, 0, sizeof(unsigned long long) * bins, st);
     P.offsets = offsets; P.cursor = cursor;
-    if (e == cudaSuccess) e = cudaFuncSetAttribute((const void*)radix_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 << 10);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute((const void*)radix_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRadixMaxStage);
     if (e == cudaSuccess) {
-        radix_scatter_kernel<<<ctx->sm_count * 2, kRadixThreads, off, st>>>(P);
+        radix_scatter_kernel<<<ctx->sm_count * IGL_RADIX_CTAS, kRadixThreads, off, st>>>(P);
         e = cudaGetLastError();
         ctx->launches++;
     }
