@@ -30,8 +30,8 @@ sys.path.insert(0, ROOT)
 SEED_C2, SEED_C3 = 0x16100002, 0x16100003
 
 
-# join_probe_flat_kernel at C3 full scale: 21.30 GB read + 31.95 GB written (profiles/launches_r1c_join_full.csv)
-NCU_PROBE_TRAFFIC_BYTES = 53_243_975_680
+# join_probe_flat_kernel at C3 full scale: 21.51 GB read + 32.07 GB written (profiles/ncu_summary_r1h_join_probe_full.txt)
+NCU_PROBE_TRAFFIC_BYTES = 53_579_546_000
 
 
 def load_peaks():
