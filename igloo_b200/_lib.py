@@ -109,6 +109,7 @@ _sig("igl_join_set_prepartitioned", _i32, _vp, _i32)
 _sig("igl_join_destroy", None, _vp)
 _sig("igl_partition_histogram", _i32, _vp, _P(DevCol), _i64, _i32, _vp, _vp)
 _sig("igl_partition_scatter", _i32, _vp, _P(DevCol), _i32, _i32, _i64, _i32, _P(_vp), _P(_i64), _vp)
+_sig("igl_partition_radix_supported", _i32, _P(DevCol), _i32)
 _sig("igl_partition_histogram_radix", _i32, _vp, _P(DevCol), _i64, _i32, _i32, _vp, _vp)
 _sig("igl_partition_scatter_radix", _i32, _vp, _P(DevCol), _i32, _i32, _i64, _i32, _i32, _P(_vp), _P(_i64), _vp)
 _sig("igl_ipc_export", _i32, _vp, _vp, C.c_char_p)

@@ -1073,7 +1073,7 @@ int32_t igl_join_build(igl_join* j, const igl_dev_col* right, int64_t nrows, voi
         // IGL_JOIN_PARTITION=0 switches it off (A/B measurements in profiles/README.md).
         const char* env = getenv("IGL_JOIN_PARTITION");
         bool want = !(env && env[0] == '0') && cap * sizeof(Slot) >= (64ull << 20) && nrows > 0 && !j->prepartitioned;
-        for (int c = 0; c < nr; ++c) if (right[c].validity) want = false;
+        if (!radix_partition_supported(right, nr)) want = false;   // nullable or very wide rows: one big table, unordered probes
         if (want) {
             int lp = 0;
             const char* pmb = getenv("IGL_PART_MB");
@@ -1177,9 +1177,7 @@ int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_
     cudaEventRecord(j->ev[3], st);
     j->ev_probe = false;
     if (j->log2_parts > 0) {   // reorder the probe chunk the same way, so it walks the table region by region
-        bool ok = true;
-        for (int c = 0; c < nl; ++c) if (left[c].validity) ok = false;
-        if (ok) {
+        if (radix_partition_supported(left, nl)) {
             if (nrows > j->part_left_rows) {
                 for (void* p : j->part_left) pool_free(ctx, p);
                 j->part_left.assign(nl, nullptr);

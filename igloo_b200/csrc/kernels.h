@@ -39,6 +39,7 @@ int32_t utf8_gather_bytes(igl_ctx* ctx, const int32_t* src_off, const uint8_t* s
 
 // Radix partition of a column set by the top bits of the join hash (partition.cu).
 // dst[c]: device buffers of nrows rows; scratch: 3 * ((1 << log2_parts) + 1) * 8 bytes.
+bool radix_partition_supported(const igl_dev_col* cols, int ncols);
 int32_t radix_partition(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int key_col, long long nrows, int log2_parts,
                         void* const* dst, void* scratch, cudaStream_t st);
 

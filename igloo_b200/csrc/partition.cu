@@ -321,6 +321,169 @@ __global__ void __launch_bounds__(kRadixThreads, IGL_RADIX_CTAS) radix_scatter_k
     }
 }
 
+// ---- scatter, bulk-copy form -----------------------------------------------------------
+// One 1024-thread CTA per SM.  A tile's columns arrive in shared memory through bulk async
+// copies (double-buffered: the next tile travels while this one is sorted), so no global
+// load sits on the tile's critical path and no row value passes through registers twice:
+// rows are ranked by bin with shared-memory atomics, a permutation (slot -> row) is built,
+// and the write-out reads each column through the permutation and stores runs of
+// consecutive destination rows.  Used when the tile fits (2 x 4096 rows x row bytes <= 190 KB,
+// or one buffer for wider rows) and the columns are 16-byte aligned.
+constexpr int kRtThreads = 1024;
+constexpr int kRtRows = 4;
+constexpr int kRtTile = kRtThreads * kRtRows;          // 4096 rows
+constexpr unsigned kRtMaxDyn = 190u << 10;
+
+__global__ void __launch_bounds__(kRtThreads, 1) radix_scatter_bulk_kernel(const __grid_constant__ RadixParams P, int n_buf, uint32_t tile_bytes) {
+    extern __shared__ __align__(128) uint8_t in_tiles[];
+    __shared__ unsigned int s_cnt[2][kRadixMaxParts];      // by tile parity: count, then exclusive start
+    __shared__ unsigned long long s_gbase[kRadixMaxParts];
+    __shared__ unsigned short s_perm[kRtTile];              // slot -> row of the tile
+    __shared__ unsigned short s_part[kRtTile];              // slot -> bin
+    __shared__ unsigned int s_warp_tot[kRtThreads / 32];
+    __shared__ uint64_t s_full[2];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nbins = P.ndest << P.log2_parts;
+    const long long ntiles = (P.n + kRtTile - 1) / kRtTile;
+    auto issue = [&](long long tile, int buf) {   // thread 0
+        if (tile >= ntiles) return;
+        const long long row0 = tile * kRtTile;
+        const uint32_t rows = (uint32_t)min((long long)kRtTile, P.n - row0);
+        uint32_t total = 0;
+        for (int c = 0; c < P.ncols; ++c) total += ((rows << P.shift[c]) + 15u) & ~15u;
+        mbar_arrive_expect_tx(&s_full[buf], total);
+        uint8_t* dst = in_tiles + (size_t)buf * tile_bytes;
+        for (int c = 0; c < P.ncols; ++c)
+            bulk_g2s(dst + P.stage_off[c], P.src[c] + ((size_t)row0 << P.shift[c]), ((rows << P.shift[c]) + 15u) & ~15u, &s_full[buf]);
+    };
+    if (tid == 0) {
+        mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1);
+        mbar_fence_init();
+        for (int b = 0; b < n_buf; ++b) issue((long long)blockIdx.x + (long long)b * gridDim.x, b);
+    }
+    s_cnt[0][tid] = 0; s_cnt[1][tid] = 0;
+    __syncthreads();
+    int it = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        const int buf = n_buf == 2 ? (it & 1) : 0;
+        const uint32_t phase = n_buf == 2 ? ((uint32_t)(it >> 1) & 1u) : ((uint32_t)it & 1u);
+        unsigned int* cnt = s_cnt[it & 1];
+        const long long row0 = tile * kRtTile;
+        const int rows = (int)min((long long)kRtTile, P.n - row0);
+        const uint8_t* in = in_tiles + (size_t)buf * tile_bytes;
+        mbar_wait(&s_full[buf], phase);
+        int bin[kRtRows];
+        unsigned int rank[kRtRows];
+        {
+            const uint8_t* kc = in + P.stage_off[P.key_col];
+#pragma unroll
+            for (int r = 0; r < kRtRows; ++r) {
+                const int i = r * kRtThreads + tid;
+                bin[r] = -1;
+                if (i < rows) {
+                    const uint64_t raw = P.key_type == IGL_T_I32 ? (uint64_t)((const uint32_t*)kc)[i] : ((const uint64_t*)kc)[i];
+                    bin[r] = radix_bin_of(mix64(part_canon(P.key_type, raw)), P.ndest, P.log2_parts);
+                    rank[r] = atomicAdd(&cnt[bin[r]], 1u);
+                }
+            }
+        }
+        s_cnt[(it + 1) & 1][tid] = 0;   // the other parity's counters: last read before the previous tile's final barrier
+        __syncthreads();
+        {   // exclusive scan of the bin counts (one bin per thread) + global reservation
+            const unsigned int c = tid < nbins ? cnt[tid] : 0;
+            unsigned int inc = c;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned int t = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += t;
+            }
+            if (lane == 31) s_warp_tot[warp] = inc;
+            __syncthreads();
+            unsigned int ex = inc - c;
+            for (int w = 0; w < warp; ++w) ex += s_warp_tot[w];
+            if (tid < nbins) {
+                cnt[tid] = ex;
+                s_gbase[tid] = c ? P.offsets[tid] + atomicAdd(&P.cursor[tid], (unsigned long long)c) : 0ull;
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < kRtRows; ++r) {
+            if (bin[r] >= 0) {
+                const unsigned int slot = cnt[bin[r]] + rank[r];
+                s_perm[slot] = (unsigned short)(r * kRtThreads + tid);
+                s_part[slot] = (unsigned short)bin[r];
+            }
+        }
+        __syncthreads();
+        // write-out: consecutive threads -> consecutive slots -> runs of consecutive destination rows
+        unsigned long long d[kRtRows];
+        int src_row[kRtRows], dq[kRtRows];
+#pragma unroll
+        for (int r = 0; r < kRtRows; ++r) {
+            const int sl = r * kRtThreads + tid;
+            d[r] = 0; src_row[r] = 0; dq[r] = 0;
+            if (sl < rows) {
+                const int p = s_part[sl];
+                d[r] = s_gbase[p] + (unsigned)(sl - cnt[p]);
+                src_row[r] = s_perm[sl];
+                dq[r] = p >> P.log2_parts;
+            }
+        }
+        for (int c = 0; c < P.ncols; ++c) {
+            if (P.shift[c] == 3) {
+                const uint64_t* sc = reinterpret_cast<const uint64_t*>(in + P.stage_off[c]);
+#pragma unroll
+                for (int r = 0; r < kRtRows; ++r)
+                    if (r * kRtThreads + tid < rows) reinterpret_cast<uint64_t*>(P.dst[dq[r]][c])[d[r]] = sc[src_row[r]];
+            } else {
+                const uint32_t* sc = reinterpret_cast<const uint32_t*>(in + P.stage_off[c]);
+#pragma unroll
+                for (int r = 0; r < kRtRows; ++r)
+                    if (r * kRtThreads + tid < rows) reinterpret_cast<uint32_t*>(P.dst[dq[r]][c])[d[r]] = sc[src_row[r]];
+            }
+        }
+        __syncthreads();   // the tile buffer, s_perm, s_part and s_gbase are free again
+        if (tid == 0) issue(tile + (long long)n_buf * gridDim.x, buf);
+    }
+}
+
+// Whether a column set can go through radix_partition / igl_partition_scatter_radix: fixed-width
+// non-null columns whose 4096-row tile fits one of the two scatter forms.
+bool radix_partition_supported(const igl_dev_col* cols, int ncols) {
+    if (ncols < 1 || ncols > kPartMaxCols) return false;
+    uint32_t off = 0;
+    bool aligned = true;
+    for (int c = 0; c < ncols; ++c) {
+        const int t = cols[c].type;
+        if (t != IGL_T_I32 && t != IGL_T_I64 && t != IGL_T_F64) return false;
+        if (cols[c].validity) return false;
+        if ((uintptr_t)cols[c].data & 15) aligned = false;
+        off += (uint32_t)kRtTile << (t == IGL_T_I32 ? 2 : 3);
+    }
+    return off <= kRadixMaxStage || (aligned && off <= kRtMaxDyn);
+}
+
+// Launches the scatter pass for `P` (offsets and cursor already set): bulk-copy form when it applies.
+static cudaError_t launch_radix_scatter(igl_ctx* ctx, const RadixParams& P, uint32_t tile_bytes_4096, cudaStream_t st) {
+    bool aligned = true;
+    for (int c = 0; c < P.ncols; ++c) if ((uintptr_t)P.src[c] & 15) aligned = false;
+    const char* env = getenv("IGL_RADIX_BULK");
+    if (aligned && tile_bytes_4096 <= kRtMaxDyn && (!(env && env[0] == '0') || tile_bytes_4096 > kRadixMaxStage)) {
+        const int n_buf = 2u * tile_bytes_4096 <= kRtMaxDyn ? 2 : 1;
+        const size_t dyn = (size_t)n_buf * tile_bytes_4096;
+        cudaError_t e = cudaFuncSetAttribute((const void*)radix_scatter_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRtMaxDyn);
+        if (e != cudaSuccess) return e;
+        radix_scatter_bulk_kernel<<<ctx->sm_count, kRtThreads, dyn, st>>>(P, n_buf, tile_bytes_4096);
+        return cudaGetLastError();
+    }
+    cudaError_t e = cudaFuncSetAttribute((const void*)radix_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRadixMaxStage);
+    if (e != cudaSuccess) return e;
+    static_assert(kRadixTile == kRtTile, "both scatter forms stage 4096-row tiles");
+    radix_scatter_kernel<<<ctx->sm_count * IGL_RADIX_CTAS, kRadixThreads, tile_bytes_4096, st>>>(P);
+    return cudaGetLastError();
+}
+
 // Partitions `cols` (no validity) into dst[c] (capacity nrows each) by the top
 // log2_parts bits of the join hash.  `scratch` holds 3 * (nparts + 1) u64.
 int32_t radix_partition(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int key_col, long long nrows, int log2_parts,
@@ -345,8 +508,7 @@ int32_t radix_partition(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int ke
         P.stage_off[c] = off;
         off += (uint32_t)kRadixTile << P.shift[c];
     }
-    if (off > kRadixMaxStage) return fail(IGL_ERR_UNSUPPORTED, "radix_partition: row too wide (%u bytes of staging)", off);
-    const int grid = ctx->sm_count * IGL_RADIX_CTAS;
+    if (!radix_partition_supported(cols, ncols)) return fail(IGL_ERR_UNSUPPORTED, "radix_partition: row too wide (%u bytes of staging)", off);
     if (nrows > 0) {
         radix_hist_kernel<<<ctx->sm_count * 4, 512, 0, st>>>(cols[key_col].data, P.key_type, nrows, 1, log2_parts, hist);
         IGL_CUDA_OK(cudaGetLastError());
@@ -355,13 +517,7 @@ int32_t radix_partition(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int ke
     IGL_CUDA_OK(cudaGetLastError());
     ctx->launches += 2;
     if (nrows > 0) {
-        static bool attr_set = false;
-        if (!attr_set) {
-            IGL_CUDA_OK(cudaFuncSetAttribute((const void*)radix_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRadixMaxStage));
-            attr_set = true;
-        }
-        radix_scatter_kernel<<<grid, kRadixThreads, off, st>>>(P);
-        IGL_CUDA_OK(cudaGetLastError());
+        IGL_CUDA_OK(launch_radix_scatter(ctx, P, off, st));
         ctx->launches++;
     }
     return IGL_OK;
@@ -455,6 +611,10 @@ int32_t igl_partition_histogram_radix(igl_ctx* ctx, const igl_dev_col* key, int6
     return IGL_OK;
 }
 
+int32_t igl_partition_radix_supported(const igl_dev_col* cols, int32_t ncols) {
+    return cols && radix_partition_supported(cols, ncols) ? 1 : 0;
+}
+
 int32_t igl_partition_scatter_radix(igl_ctx* ctx, const igl_dev_col* cols, int32_t ncols, int32_t key_col, int64_t nrows,
                                     int32_t ndest, int32_t log2_parts, void* const* dst, const int64_t* bin_row_offset,
                                     void* stream) {
@@ -481,7 +641,7 @@ int32_t igl_partition_scatter_radix(igl_ctx* ctx, const igl_dev_col* cols, int32
             P.dst[d][c] = (uint8_t*)dst[d * ncols + c];
         }
     }
-    if (off > kRadixMaxStage) return fail(IGL_ERR_UNSUPPORTED, "row too wide (%u bytes of staging)", off);
+    if (!radix_partition_supported(cols, ncols)) return fail(IGL_ERR_UNSUPPORTED, "row too wide (%u bytes of staging)", off);
     if (nrows == 0) return IGL_OK;
     // device copy of the offsets + zeroed cursors; handed back to the pool once the kernel is done
     void* scratch = nullptr;
@@ -491,10 +651,8 @@ int32_t igl_partition_scatter_radix(igl_ctx* ctx, const igl_dev_col* cols, int32
     cudaError_t e = cudaMemcpyAsync(offsets, bin_row_offset, sizeof(int64_t) * bins, cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) e = cudaMemsetAsync(cursor, 0, sizeof(unsigned long long) * bins, st);
     P.offsets = offsets; P.cursor = cursor;
-    if (e == cudaSuccess) e = cudaFuncSetAttribute((const void*)radix_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRadixMaxStage);
     if (e == cudaSuccess) {
-        radix_scatter_kernel<<<ctx->sm_count * IGL_RADIX_CTAS, kRadixThreads, off, st>>>(P);
-        e = cudaGetLastError();
+        e = launch_radix_scatter(ctx, P, off, st);
         ctx->launches++;
     }
     if (e == cudaSuccess) e = cudaStreamSynchronize(st);

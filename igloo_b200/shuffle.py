@@ -145,7 +145,8 @@ class PartitionedJoin:
             # per exchange), so the fan-out is capped at 128 bins; regions of up to 32 MB still sit in L2.
             while self.log2_parts > 0 and (self.world << self.log2_parts) > 128:
                 self.log2_parts -= 1
-            self.fused = (self.world << self.log2_parts) <= 1024 and all(c.validity is None for c in self.R.cols + self.L.cols)
+            self.fused = ((self.world << self.log2_parts) <= 1024 and all(c.validity is None for c in self.R.cols + self.L.cols)
+                          and all(lib.igl_partition_radix_supported(self._devcols(side), len(side.fields)) == 1 for side in (self.R, self.L)))
             if self.fused:
                 self._hist = torch.zeros(2, self.world << self.log2_parts, dtype=torch.int64, device=f"cuda:{self.ctx.device}")
             check(lib.igl_join_set_prepartitioned(self.join._h, 1 if self.fused else 0))

@@ -242,7 +242,9 @@ int32_t igl_partition_scatter(igl_ctx* ctx, const igl_dev_col* cols, int32_t nco
  * rows per bin; the scatter sorts each 4096-row tile by bin in shared memory and stores runs
  * to dst[dest * ncols + c] + bin_row_offset[bin] rows, so a receiver that lays its slab out
  * partition by partition gets its rows in the order igl_join_build / igl_join_probe want.
- * Non-nullable columns only. */
+ * Non-nullable fixed-width columns of at most 46 bytes per row (16-byte aligned; 24 bytes
+ * per row otherwise): igl_partition_radix_supported tells. */
+int32_t igl_partition_radix_supported(const igl_dev_col* cols, int32_t ncols);
 int32_t igl_partition_histogram_radix(igl_ctx* ctx, const igl_dev_col* key, int64_t nrows, int32_t ndest,
                                       int32_t log2_parts, int64_t* dev_hist /* [ndest << log2_parts] */,
                                       void* stream);

@@ -182,3 +182,38 @@ def test_full_scale_property_c3_digest(ctx):
     inv = np.array([orc.lib().orc_perm_pow2_inv(int(k), bits) for k in hk], dtype=np.uint64)
     hv = np.array([orc.gen_i64_uniform(seed, 1, int(i), 1)[0] for i in inv], dtype=np.int64)
     assert np.array_equal(out[3].data[:m].cpu().numpy(), hv)
+
+
+def test_partitioned_row_id_gather_c4_shape_digest(ctx):
+    """C4 shape at 1/18 scale on the device generator: a build side wider than (key, payload) is
+    joined through row ids, and at 2^23 rows its 256 MB table is radix-partitioned, so the row ids
+    index the partitioned copy.  Expected right columns are recomputed from the generator."""
+    from igloo_b200.device import HashJoin
+    seed, bits, nprobe = 0x16100004, 23, 40_000_000
+    nb = 1 << bits
+    rk = ctx.gen(4, 0, 0, 0, nb, bits=bits)
+    rv = [ctx.gen(2, seed, c, 0, nb) for c in (1, 2, 3)]
+    lk = ctx.gen(2, seed, 7, 0, nprobe, m=nb)
+    lw = ctx.gen(2, seed, 8, 0, nprobe)
+    f = [Field("k", T_I64), Field("w", T_I64)]
+    g = [Field("k", T_I64), Field("v1", T_I64), Field("v2", T_I64), Field("v3", T_I64)]
+    j = HashJoin(ctx, 0, f, g, col("k"), col("k"))
+    j.build([rk] + rv, nb)
+    assert not j.has_duplicates
+    out, n = j.probe([lk, lw], nprobe, capacity=nprobe)
+    assert n == nprobe
+    expect = [ctx.gen(5, seed, c, 0, nprobe, bits=bits, keys=lk) for c in (1, 2, 3)]
+    assert ctx.digest(out, n) == ctx.digest([lk, lw, lk] + expect, nprobe)
+    # half of the probe keys outside the build domain: the dense probe has holes to fill
+    lk2 = ctx.gen(2, seed, 9, 0, nprobe, m=2 * nb)
+    out2, n2 = j.probe([lk2, lw], nprobe, capacity=nprobe)
+    hk = lk2.data[:nprobe]
+    keep = hk < nb
+    assert n2 == int(keep.sum().item())
+    from igloo_b200.device import DeviceColumn
+    import torch
+    idx = torch.nonzero(keep).flatten()
+    sel = lambda c: DeviceColumn(3, n2, c.data[:nprobe][idx].contiguous(), None)   # noqa: E731
+    lk_in = sel(lk2)
+    expect2 = [ctx.gen(5, seed, c, 0, n2, bits=bits, keys=lk_in) for c in (1, 2, 3)]
+    assert ctx.digest(out2, n2) == ctx.digest([lk_in, sel(lw), lk_in] + expect2, n2)
