@@ -169,18 +169,28 @@ __global__ void __launch_bounds__(kBuildThreads) join_build_unique_kernel(const 
 }
 
 // ---- K5 build, duplicate layout: count, allocate runs, fill --------------------------------
+// Lanes of a warp that hold the same key act as one: the first of them walks to the key's slot
+// and adds the whole group's count.  With skewed build keys (C5b: one key owns a fifth of the
+// rows) this cuts the atomics on the hot slot 32-fold.
 __global__ void join_build_count_kernel(const void* __restrict__ keys, int key_type, const uint8_t* __restrict__ key_valid,
                                         long long n, JoinTable t) {
     const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const bool valid = !key_valid || bit_at(key_valid, i);
-        const uint64_t k = valid ? canon_key(key_type, load_key_global(keys, key_type, i)) : 0;
-        if (!valid || k == kEmptyKey) { atomicAdd(&t.side->count[valid ? 1 : 0], 1u); continue; }
-        uint64_t h = (mix64(k) >> t.shift) & ~1ull;   // homes are even: a bucket is one 32-byte sector
-        while (true) {
-            const unsigned long long prev = atomicCAS(&t.slots[h].key, (unsigned long long)kEmptyKey, (unsigned long long)k);
-            if (prev == kEmptyKey || prev == k) { atomicAdd(&t.slots[h].val, 1ull << 32); break; }
-            h = (h + 1) & t.mask;
+    const int lane = threadIdx.x & 31;
+    for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x - lane; i0 < n; i0 += stride) {   // warp-uniform trip count
+        const long long i = i0 + lane;
+        const bool in = i < n;
+        const bool valid = in && (!key_valid || bit_at(key_valid, i));
+        const uint64_t k = valid ? canon_key(key_type, load_key_global(keys, key_type, i)) : kEmptyKey;
+        const bool normal = valid && k != kEmptyKey;
+        if (in && !normal) atomicAdd(&t.side->count[valid ? 1 : 0], 1u);
+        const unsigned peers = __match_any_sync(0xffffffffu, k);   // side-entry lanes all carry kEmptyKey and skip below
+        if (normal && lane == __ffs(peers) - 1) {
+            uint64_t h = (mix64(k) >> t.shift) & ~1ull;   // homes are even: a bucket is one 32-byte sector
+            while (true) {
+                const unsigned long long prev = atomicCAS(&t.slots[h].key, (unsigned long long)kEmptyKey, (unsigned long long)k);
+                if (prev == kEmptyKey || prev == k) { atomicAdd(&t.slots[h].val, (unsigned long long)__popc(peers) << 32); break; }
+                h = (h + 1) & t.mask;
+            }
         }
     }
 }
@@ -213,17 +223,25 @@ __global__ void join_build_runs_kernel(JoinTable t, uint64_t capacity) {
 __global__ void join_build_fill_kernel(const void* __restrict__ keys, int key_type, const uint8_t* __restrict__ key_valid,
                                        long long n, JoinTable t, uint32_t* __restrict__ rowids) {
     const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const bool valid = !key_valid || bit_at(key_valid, i);
-        const uint64_t k = valid ? canon_key(key_type, load_key_global(keys, key_type, i)) : 0;
-        unsigned int pos;
-        if (!valid || k == kEmptyKey) pos = atomicAdd(&t.side->run_end[valid ? 1 : 0], 1u);
-        else {
+    const int lane = threadIdx.x & 31;
+    for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x - lane; i0 < n; i0 += stride) {   // warp-uniform trip count
+        const long long i = i0 + lane;
+        const bool in = i < n;
+        const bool valid = in && (!key_valid || bit_at(key_valid, i));
+        const uint64_t k = valid ? canon_key(key_type, load_key_global(keys, key_type, i)) : kEmptyKey;
+        const bool normal = valid && k != kEmptyKey;
+        const unsigned peers = __match_any_sync(0xffffffffu, k);
+        const int leader = __ffs(peers) - 1;
+        unsigned int base = 0;
+        if (normal && lane == leader) {   // one reservation in the key's run for the whole group
             uint64_t h = (mix64(k) >> t.shift) & ~1ull;   // homes are even: a bucket is one 32-byte sector
             while (t.slots[h].key != k) h = (h + 1) & t.mask;
-            pos = atomicAdd(reinterpret_cast<unsigned int*>(&t.slots[h].val), 1u);   // little endian: the low word
+            base = atomicAdd(reinterpret_cast<unsigned int*>(&t.slots[h].val), (unsigned int)__popc(peers));   // little endian: the low word
         }
-        rowids[pos] = (uint32_t)i;   // after this pass the low word / run_end is the END of the run
+        base = __shfl_sync(0xffffffffu, base, leader);
+        unsigned int pos = base + __popc(peers & ((1u << lane) - 1u));
+        if (in && !normal) pos = atomicAdd(&t.side->run_end[valid ? 1 : 0], 1u);
+        if (in) rowids[pos] = (uint32_t)i;   // after this pass the low word / run_end is the END of the run
     }
 }
 
@@ -242,7 +260,15 @@ struct JoinProbeParams {
     uint8_t out_shift[2 * kJoinMaxCols];
     const uint8_t* right_data[kJoinMaxCols];
     const uint8_t* right_valid[kJoinMaxCols];
+    // duplicate layout: runs longer than kGiantRun are not walked by the probing warp (one warp
+    // would emit millions of rows alone) but listed here as {left row, run end, count, output
+    // position} and expanded afterwards by the whole grid (join_expand_giant_kernel)
+    unsigned long long* giant_list;
+    unsigned long long* giant_count;
+    unsigned int giant_cap;
 };
+
+constexpr uint32_t kGiantRun = 8192;
 
 struct Match {
     unsigned long long val;   // unique: payload or row id;  duplicate: {count, run end}
@@ -522,6 +548,18 @@ __device__ __forceinline__ void multi_emit(const JoinProbeParams& P, const Multi
             const uint32_t he = __shfl_sync(0xffffffffu, t.rend[r], src);
             const long long hp = __shfl_sync(0xffffffffu, pos, src);
             const int hrow = row - lane + src;
+            if (hc > kGiantRun && P.giant_list) {   // warp-uniform
+                unsigned long long slot = 0;
+                if (lane == 0) slot = atomicAdd(P.giant_count, 1ull);
+                slot = __shfl_sync(0xffffffffu, slot, 0);
+                if (slot < P.giant_cap) {
+                    if (lane == 0) {
+                        unsigned long long* e = P.giant_list + 4 * slot;
+                        e[0] = (unsigned long long)(t.row_begin + hrow); e[1] = he; e[2] = hc; e[3] = (unsigned long long)hp;
+                    }
+                    continue;
+                }
+            }
             for (uint32_t j = lane; j < hc; j += 32)
                 emit_row<HAS_NULLS>(P, t.stage, hrow, hp + j, true, P.table.rowids[he - hc + j], 0);
         }
@@ -577,6 +615,42 @@ constexpr int kFlatThreads = IGL_FLAT_THREADS;
 constexpr int kFlatRows = IGL_FLAT_ROWS;
 constexpr int kFlatChunk = kFlatThreads * kFlatRows;   // 1024 rows per CTA iteration
 constexpr int kFlatClaim = 4;                          // consecutive chunks claimed per ticket
+
+// Expands the listed giant runs: every CTA takes a slice of every run.  The left row's values
+// are read once per thread from the (global) left columns; right columns are gathered by row id.
+template <bool HAS_NULLS>
+__global__ void __launch_bounds__(256) join_expand_giant_kernel(const __grid_constant__ JoinProbeParams P) {
+    const unsigned long long n = min(*P.giant_count, (unsigned long long)P.giant_cap);
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (unsigned long long e = 0; e < n; ++e) {
+        const unsigned long long* ent = P.giant_list + 4 * e;
+        const long long lrow = (long long)ent[0];
+        const uint32_t rend = (uint32_t)ent[1], cnt = (uint32_t)ent[2];
+        const long long pos0 = (long long)ent[3];
+        uint64_t lv[kJoinMaxCols];
+        uint8_t lok[kJoinMaxCols];
+        for (int c = 0; c < P.n_left; ++c) {
+            lv[c] = P.out_shift[c] == 2 ? (uint64_t)((const uint32_t*)P.T.data[c])[lrow] : ((const uint64_t*)P.T.data[c])[lrow];
+            lok[c] = (HAS_NULLS && P.T.valid[c]) ? (uint8_t)bit_at(P.T.valid[c], lrow) : (uint8_t)1;
+        }
+        for (long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x; j < (long long)cnt; j += stride) {
+            const long long pos = pos0 + j;
+            const uint32_t rid = P.table.rowids[rend - cnt + (uint32_t)j];
+            for (int c = 0; c < P.n_left; ++c) {
+                if (P.out_shift[c] == 2) st_cs_u32((uint8_t*)P.out_data[c] + (pos << 2), (uint32_t)lv[c]);
+                else st_cs_u64((uint8_t*)P.out_data[c] + (pos << 3), lv[c]);
+                if (HAS_NULLS && P.out_valid[c]) P.out_valid[c][pos] = lok[c];
+            }
+            for (int c = 0; c < P.n_right; ++c) {
+                const int oc = P.n_left + c;
+                const uint64_t v = P.out_shift[oc] == 2 ? (uint64_t)((const uint32_t*)P.right_data[c])[rid] : ((const uint64_t*)P.right_data[c])[rid];
+                if (P.out_shift[oc] == 2) st_cs_u32((uint8_t*)P.out_data[oc] + (pos << 2), (uint32_t)v);
+                else st_cs_u64((uint8_t*)P.out_data[oc] + (pos << 3), v);
+                if (HAS_NULLS && P.out_valid[oc]) P.out_valid[oc][pos] = P.right_valid[c] ? (uint8_t)bit_at(P.right_valid[c], rid) : (uint8_t)1;
+            }
+        }
+    }
+}
 
 struct FlatProbeParams {
     const uint8_t* left[kJoinMaxCols];
@@ -1298,7 +1372,9 @@ int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_
         P.T.data[c] = (const uint8_t*)left[c].data;
         P.T.valid[c] = j->has_nulls ? left[c].validity : nullptr;
     }
-    size_t need = 256 + (size_t)scan_scratch_words(P.T.ntiles) * 8;
+    constexpr unsigned int kGiantCap = 4096;   // listed giant runs per probe call; more are walked in place
+    const size_t scan_part = (256 + (size_t)scan_scratch_words(P.T.ntiles) * 8 + 255) & ~(size_t)255;
+    size_t need = scan_part + (j->csr ? (size_t)kGiantCap * 32 : 0);
     if (need > j->scratch_bytes) {
         if (j->scratch) pool_free(ctx, j->scratch);
         j->scratch = nullptr; j->scratch_bytes = 0;
@@ -1307,7 +1383,12 @@ int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_
     }
     P.T.hdr = (PipeHeader*)j->scratch;
     P.T.status = (uint64_t*)((uint8_t*)j->scratch + 256);
-    IGL_CUDA_OK(cudaMemsetAsync(j->scratch, 0, need, st));
+    IGL_CUDA_OK(cudaMemsetAsync(j->scratch, 0, scan_part, st));
+    if (j->csr) {
+        P.giant_list = (unsigned long long*)((uint8_t*)j->scratch + scan_part);
+        P.giant_count = &P.T.hdr->aux[3];
+        P.giant_cap = kGiantCap;
+    }
     P.table = j->table;
     P.key_slot = j->lkey;
     P.key_type = j->lt[j->lkey];
@@ -1346,6 +1427,12 @@ int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_
     k<<<grid, kPipeThreads, j->smem_bytes, st>>>(P);
     IGL_CUDA_OK(cudaGetLastError());
     ctx->launches++;
+    if (j->csr) {
+        if (j->has_nulls) join_expand_giant_kernel<true><<<ctx->sm_count * 8, 256, 0, st>>>(P);
+        else join_expand_giant_kernel<false><<<ctx->sm_count * 8, 256, 0, st>>>(P);
+        IGL_CUDA_OK(cudaGetLastError());
+        ctx->launches++;
+    }
     for (int c = 0; c < nl + nr; ++c) {
         if (!P.out_valid[c]) continue;
         IGL_CUDA_OK(launch_pack_bits(P.out_valid[c], (uint32_t*)out[c].validity, &P.T.hdr->out_count, 0, out_capacity, ctx->sm_count, st));

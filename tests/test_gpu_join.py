@@ -105,6 +105,25 @@ def test_duplicates_both_sides_and_heavy_key(ctx):
     check(ctx, left, right, "k", "k", 1)
 
 
+def test_giant_duplicate_runs_are_expanded_by_the_grid(ctx):
+    """C5b shape, small: two build keys own runs far longer than the 8192-row limit above which the
+    probing warp lists the run and join_expand_giant_kernel emits it; nullable payload, Inner and Left."""
+    rng = np.random.default_rng(19)
+    nb, nl = 60_000, 4_000
+    rk = rng.integers(0, 3000, nb)
+    rk[:20_000] = 41
+    rk[20_000:31_000] = 1999
+    right = pa.table({"k": rk.astype(np.int64), "v": pa.array(rng.integers(0, 1 << 50, nb), pa.int64(), mask=rng.random(nb) < 0.2),
+                      "z": rng.integers(0, 99, nb).astype(np.int32)})
+    lk = rng.integers(0, 3500, nl)
+    lk[[5, 1234, 3999]] = 41
+    lk[[77, 2500]] = 1999
+    left = pa.table({"k": lk.astype(np.int64), "w": rng.random(nl)})
+    got, j = check(ctx, left, right, "k", "k")
+    assert j.has_duplicates and got.num_rows > 3 * 20_000 + 2 * 11_000
+    check(ctx, left, right, "k", "k", 1)
+
+
 def test_null_keys_match_sentinel_key_and_nullable_payload(ctx):
     rng = np.random.default_rng(4)
     nb, nl = 4000, 9000
