@@ -151,30 +151,52 @@ class PartitionedJoin:
                 self._hist = torch.zeros(2, self.world << self.log2_parts, dtype=torch.int64, device=f"cuda:{self.ctx.device}")
             check(lib.igl_join_set_prepartitioned(self.join._h, 1 if self.fused else 0))
         for side, total in ((self.R, int(tot[0])), (self.L, int(tot[1]))):
-            side.capacity = int(total / self.world * slack) + 4096
-            side.slabs = [RawBuffer(self.ctx, side.capacity * _W[f.type] + 256) for f in side.fields]
-            if self.mode == "nccl":
-                side.send = [RawBuffer(self.ctx, max(side.nrows, 1) * _W[f.type] + 256) for f in side.fields]
-            else:
-                handles = []
-                for b in side.slabs:
-                    h = C.create_string_buffer(64)
-                    check(lib.igl_ipc_export(self.ctx._h, b.ptr, h))
-                    handles.append(h.raw)
-                gathered = [None] * self.world
-                dist.all_gather_object(gathered, handles)
-                side.peer_ptrs = []
-                for p in range(self.world):
-                    if p == self.rank:
-                        side.peer_ptrs.append([b.ptr for b in side.slabs])
-                    else:
-                        ptrs = []
-                        for hraw in gathered[p]:
-                            out = C.c_void_p()
-                            check(lib.igl_ipc_open(self.ctx._h, hraw, C.byref(out)))
-                            ptrs.append(out.value)
-                        side.peer_ptrs.append(ptrs)
+            self._alloc_slabs(side, int(total / self.world * slack) + 4096)
         dist.barrier()
+
+    def _alloc_slabs(self, side, capacity: int):
+        """(Re)allocates one side's receive slabs for `capacity` rows on every rank — a collective
+        call — and, in p2p mode, maps the peers' slabs (CUDA IPC)."""
+        import torch.distributed as dist
+        if side.slabs:       # growing: drop the old mappings and blocks first
+            for p, ptrs in enumerate(getattr(side, "peer_ptrs", []) or []):
+                if p != self.rank:
+                    for q in ptrs:
+                        lib.igl_ipc_close(self.ctx._h, q)
+            dist.barrier()   # nobody still maps a block that is about to be freed
+            for b in side.slabs + (getattr(side, "send", None) or []):
+                b.free()
+        side.capacity = capacity
+        side.slabs = [RawBuffer(self.ctx, side.capacity * _W[f.type] + 256) for f in side.fields]
+        if self.mode == "nccl":
+            side.send = [RawBuffer(self.ctx, max(side.nrows, 1) * _W[f.type] + 256) for f in side.fields]
+            return
+        handles = []
+        for b in side.slabs:
+            h = C.create_string_buffer(64)
+            check(lib.igl_ipc_export(self.ctx._h, b.ptr, h))
+            handles.append(h.raw)
+        gathered = [None] * self.world
+        dist.all_gather_object(gathered, handles)
+        side.peer_ptrs = []
+        for p in range(self.world):
+            if p == self.rank:
+                side.peer_ptrs.append([b.ptr for b in side.slabs])
+            else:
+                ptrs = []
+                for hraw in gathered[p]:
+                    out = C.c_void_p()
+                    check(lib.igl_ipc_open(self.ctx._h, hraw, C.byref(out)))
+                    ptrs.append(out.value)
+                side.peer_ptrs.append(ptrs)
+
+    def _fit_slabs(self, needed_rows):
+        """Skewed keys (C5: one GPU can receive a fifth of all probe rows) outgrow slabs sized for an
+        even share.  `needed_rows[side]` = the largest number of rows any rank receives, derived from
+        the count matrix every rank holds, so all ranks take the same decision and grow together."""
+        for side, need in zip((self.R, self.L), needed_rows):
+            if need > side.capacity:
+                self._alloc_slabs(side, int(need * 1.05) + 4096)
 
     # ---- one join --------------------------------------------------------------
     def _devcols(self, side, ptrs=None, validity=None):
@@ -209,9 +231,7 @@ class PartitionedJoin:
         counts = allh.cpu().numpy()
         mark("histogram+counts")
         plans = [ExchangePlan.from_counts(counts[:, i, :].tolist(), self.rank) for i in range(2)]
-        for side, plan in zip((self.R, self.L), plans):
-            if plan.total_recv > side.capacity:
-                raise RuntimeError(f"receive slab too small: {plan.total_recv} rows > capacity {side.capacity} (skewed keys: raise slack)")
+        self._fit_slabs([int(counts[:, i, :].sum(axis=0).max()) for i in range(2)])
         # 3. rows travel once
         if self.mode == "p2p":
             dist.barrier()                       # peers are done reading their slabs from the previous join
@@ -268,9 +288,7 @@ class PartitionedJoin:
         counts = allh.cpu().numpy()
         mark("histogram+counts")
         plans = [RadixExchangePlan.from_counts(counts[:, i, :], self.rank, W, 1 << lp) for i in range(2)]
-        for side, plan in zip((self.R, self.L), plans):
-            if plan.total_recv > side.capacity:
-                raise RuntimeError(f"receive slab too small: {plan.total_recv} rows > capacity {side.capacity} (skewed keys: raise slack)")
+        self._fit_slabs([int(counts[:, i, :].reshape(W, W, 1 << lp).sum(axis=(0, 2)).max()) for i in range(2)])
         dist.barrier()                       # peers are done reading their slabs from the previous join
         for side, plan in zip((self.R, self.L), plans):
             nc = len(side.fields)

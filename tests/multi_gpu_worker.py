@@ -36,6 +36,11 @@ def main():
     p0, p1 = nprobe * rank // world, nprobe * (rank + 1) // world
     rk = ctx.gen(4, 0, 0, b0, b1 - b0, bits=bits); rv = ctx.gen(2, seed, 1, b0, b1 - b0)
     lk = ctx.gen(2, seed, 2, p0, p1 - p0, m=nb); lw = ctx.gen(2, seed, 3, p0, p1 - p0)
+    if len(sys.argv) > 3 and sys.argv[3] == "skew":
+        # 60 % of the probe rows carry one key: its destination GPU receives far more than the even
+        # share the slabs were sized for, so they must grow (on every rank) inside run()
+        hot = torch.rand(p1 - p0, device=f"cuda:{local}") < 0.6
+        lk.data[: p1 - p0][hot] = 12345 % nb
     expect_v = ctx.gen(5, seed, 1, 0, p1 - p0, bits=bits, keys=lk)
     want = combine(ctx.digest([lk, lw, lk, expect_v], p1 - p0), local)
     f = [Field("k", T_I64), Field("w", T_I64)]

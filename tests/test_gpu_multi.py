@@ -10,8 +10,8 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.mark.parametrize("bits,nprobe", [(16, 300_000), (23, 40_000_000)])
-def test_two_gpu_partitioned_join_digest(bits, nprobe):
+@pytest.mark.parametrize("bits,nprobe,extra", [(16, 300_000, ""), (23, 40_000_000, ""), (23, 20_000_000, "skew")])
+def test_two_gpu_partitioned_join_digest(bits, nprobe, extra):
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
@@ -19,7 +19,7 @@ def test_two_gpu_partitioned_join_digest(bits, nprobe):
     # takes the exchange fused with the partitioning; bits=16 takes the plain scatter
     env = dict(os.environ, IGL_PART_MB="4")
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
-                        "--master-port", "29533", os.path.join(ROOT, "tests", "multi_gpu_worker.py"), str(bits), str(nprobe)],
+                        "--master-port", "29533", os.path.join(ROOT, "tests", "multi_gpu_worker.py"), str(bits), str(nprobe)] + ([extra] if extra else []),
                        capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     assert "mode=p2p" in r.stdout and "mode=nccl" in r.stdout
