@@ -158,6 +158,7 @@ struct FpProgram {
     size_t smem_bytes = 0;
     int grid_cap = 0;
     int n_instr = 0, n_exprs = 0, n_cols = 0;
+    int64_t rows_seen = 0;                   // rows launched through this program so far
     // run-time specialised kernel (fp_jit.h): 0 not tried, 1 loaded, -1 unavailable
     int jit_state = 0;
     void* jit_kernel = nullptr;
@@ -331,8 +332,9 @@ FpJitSpec jit_spec(const FpProgram& prog, bool has_nulls) {
     return sp;
 }
 
-// IGL_FP_JIT: 0 never specialise, 1 always; unset: for launches of at least
-// IGL_FP_JIT_MIN_ROWS rows (default 64 Mi), where the compile time is repaid.
+// IGL_FP_JIT: 0 never specialise, 1 always; unset: once the plan has been given at least
+// IGL_FP_JIT_MIN_ROWS rows (default 64 Mi) over all of its launches — one large launch or a
+// stream of 4 Mi-row chunks alike — so the compile time is repaid.
 bool want_jit(int64_t nrows) {
     const char* e = getenv("IGL_FP_JIT");
     if (e) return atoi(e) != 0;
@@ -340,9 +342,10 @@ bool want_jit(int64_t nrows) {
     return nrows >= (m ? atoll(m) : (long long)1 << 26);
 }
 
-int32_t launch_program(igl_ctx* ctx, FpProgram& prog, const FpParams& P, bool has_nulls, cudaStream_t st) {
+int32_t launch_program(igl_ctx* ctx, FpProgram& prog, const FpParams& P, bool has_nulls, cudaStream_t st, bool may_compile = true) {
     const int grid = (int)std::min<int64_t>(P.T.ntiles, prog.grid_cap);
-    if (prog.jit_state == 0 && want_jit(P.T.nrows)) {
+    prog.rows_seen += P.T.nrows;
+    if (may_compile && prog.jit_state == 0 && want_jit(prog.rows_seen)) {
         void* k = nullptr;
         if (fp_jit_build(jit_spec(prog, has_nulls), &k) >= 0 &&
             cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)prog.smem_bytes) == cudaSuccess) {
@@ -731,7 +734,7 @@ extern "C" int32_t igl_fp_run_static(igl_fp* fp, const igl_dev_col* in, int64_t 
     P.T.hdr = (PipeHeader*)scratch;
     P.T.status = (uint64_t*)((uint8_t*)scratch + 256);
     IGL_CUDA_OK(cudaMemsetAsync(scratch, 0, need, st));   // ticket, error flags, count and every status word start at zero
-    IGL_TRY(launch_program(ctx, fp->one, P, fp->has_nulls, st));
+    IGL_TRY(launch_program(ctx, fp->one, P, fp->has_nulls, st, /*may_compile=*/false));   // compiling and loading a kernel allocates
     IGL_CUDA_OK(cudaMemcpyAsync(fp->host_hdr, scratch, sizeof(PipeHeader), cudaMemcpyDeviceToHost, st));
     IGL_CUDA_OK(cudaStreamSynchronize(st));
     const unsigned int ef = fp->host_hdr->err_flags;

@@ -160,9 +160,9 @@ int32_t igl_fp_launch(igl_fp* fp, const igl_dev_col* in, int64_t nrows, igl_dev_
 int32_t igl_fp_finish(igl_fp* fp, int64_t* out_rows, void* stream);
 void igl_fp_destroy(igl_fp* fp);
 /* Run-time specialisation (no counterpart in the reference; DataFusion interprets its
- * PhysicalExpr trees).  The kernels above interpret the operator's program; a launch of at
- * least IGL_FP_JIT_MIN_ROWS rows (environment, default 64 Mi; IGL_FP_JIT=0 never, =1 always)
- * first compiles the same device source with the program fixed as constants (NVRTC, sm_100a,
+ * PhysicalExpr trees).  The kernels above interpret the operator's program; once a plan has
+ * been given IGL_FP_JIT_MIN_ROWS rows in total (environment, default 64 Mi; IGL_FP_JIT=0 never,
+ * =1 always) its next launch first compiles the same device source with the program fixed as constants (NVRTC, sm_100a,
  * loaded through cudaLibraryLoadData, cached per process) and runs that instead — same
  * arithmetic, same results.  Without libnvrtc.so.12 the interpreter stays in use.
  * igl_fp_is_specialised: 1 when the plan's kernels are the specialised ones.

@@ -210,6 +210,18 @@ def test_run_time_specialised_kernels_match_the_interpreter_and_the_oracle(ctx, 
     assert e.value.code == -6
     monkeypatch.setenv("IGL_FP_JIT", "0")
     gpu_filter_project(ctx, t, col("a") < 250, [col("b")], True, expect_specialised=False)
+    # by default a plan specialises itself once it has been given enough rows in total: a stream of chunks counts
+    monkeypatch.delenv("IGL_FP_JIT")
+    monkeypatch.setenv("IGL_FP_JIT_MIN_ROWS", "250000")
+    from igloo_b200.device import DeviceColumn, FilterProject
+    cols = [DeviceColumn.from_arrow(t.column(i), ctx.device) for i in range(t.num_columns)]
+    fp = FilterProject(ctx, _fields(t), col("a") < 250, [(col("b") + col("a")).alias("s")])
+    seen = []
+    for _ in range(4):
+        out, n = fp.run(cols, t.num_rows)
+        seen.append((fp.is_specialised, n, out[0].data[:n].cpu().numpy().copy()))
+    assert [x[0] for x in seen] == [False, False, True, True]       # 100 003 rows per call, threshold 250 000
+    assert all(x[1] == seen[0][1] and np.array_equal(x[2], seen[0][2]) for x in seen)
 
 
 def test_predicate_must_be_boolean(ctx):
