@@ -1,0 +1,128 @@
+"""Fragment-exchange wire format.
+
+The reference declares the message that carries a batch between fragments,
+`RecordBatchMessage { bytes schema = 1; bytes batch_data = 2; int64 num_rows = 3; }`
+(crates/api/proto/distributed.proto:53-57), but leaves both ends as stubs:
+`serialize_plan` returns empty bytes and `deserialize_batch` fabricates a dummy batch
+(crates/coordinator/src/distributed_executor.rs:203-222).  Here the two byte fields are
+Arrow IPC (the encapsulated schema message and the encapsulated record-batch message, the
+format arrow-rs `arrow::ipc` reads and writes), and the message itself is encoded as the
+protobuf wire bytes a tonic/prost peer produces for that definition — so a batch leaving a
+GPU worker on the control path (small results, or a peer outside the NVLink domain) is
+readable by the reference's Rust side once its stub is filled in.
+
+Inside one NVLink box the join's rows do not take this path: they move GPU to GPU through
+`igloo_b200.shuffle` (FragmentType.Shuffle below names that step in a fragment plan).
+"""
+from __future__ import annotations
+
+import enum
+from dataclasses import dataclass, field
+from typing import List
+
+import pyarrow as pa
+
+
+class FragmentType(enum.Enum):
+    """crates/coordinator/src/fragment.rs:8-13."""
+    Scan = "Scan"
+    Join = "Join"
+    Compute = "Compute"
+    Shuffle = "Shuffle"
+
+
+@dataclass
+class QueryFragment:
+    """crates/coordinator/src/fragment.rs:16-23, with the plan held as this package's operator tree."""
+    id: str
+    fragment_type: FragmentType
+    physical_plan: object
+    worker_address: str = ""
+    dependencies: List[str] = field(default_factory=list)
+
+
+@dataclass
+class RecordBatchMessage:
+    schema: bytes
+    batch_data: bytes
+    num_rows: int
+
+    # ---- protobuf wire format (proto3: field 1, 2 length-delimited; field 3 varint) ----
+    def to_wire(self) -> bytes:
+        out = bytearray()
+        for tag, payload in ((0x0A, self.schema), (0x12, self.batch_data)):
+            if payload:
+                out.append(tag)
+                out += _varint(len(payload))
+                out += payload
+        if self.num_rows:
+            out.append(0x18)
+            out += _varint(self.num_rows & 0xFFFFFFFFFFFFFFFF)
+        return bytes(out)
+
+    @staticmethod
+    def from_wire(buf: bytes) -> "RecordBatchMessage":
+        schema = batch = b""
+        rows = 0
+        i, n = 0, len(buf)
+        while i < n:
+            key, i = _read_varint(buf, i)
+            fno, wt = key >> 3, key & 7
+            if wt == 2:
+                ln, i = _read_varint(buf, i)
+                if i + ln > n:
+                    raise ValueError("truncated RecordBatchMessage")
+                payload = bytes(buf[i:i + ln]); i += ln
+                if fno == 1:
+                    schema = payload
+                elif fno == 2:
+                    batch = payload
+            elif wt == 0:
+                v, i = _read_varint(buf, i)
+                if fno == 3:
+                    rows = v - (1 << 64) if v >> 63 else v
+            elif wt == 1:
+                i += 8
+            elif wt == 5:
+                i += 4
+            else:
+                raise ValueError(f"unsupported wire type {wt}")
+        return RecordBatchMessage(schema, batch, rows)
+
+
+def _varint(v: int) -> bytes:
+    out = bytearray()
+    while True:
+        b = v & 0x7F
+        v >>= 7
+        if v:
+            out.append(b | 0x80)
+        else:
+            out.append(b)
+            return bytes(out)
+
+
+def _read_varint(buf: bytes, i: int):
+    shift = v = 0
+    while True:
+        if i >= len(buf):
+            raise ValueError("truncated varint")
+        b = buf[i]; i += 1
+        v |= (b & 0x7F) << shift
+        if not b & 0x80:
+            return v, i
+        shift += 7
+
+
+def serialize_batch(batch: pa.RecordBatch) -> RecordBatchMessage:
+    """The sending half the reference never wrote (a worker's ExecuteFragment stream item)."""
+    return RecordBatchMessage(batch.schema.serialize().to_pybytes(), batch.serialize().to_pybytes(), batch.num_rows)
+
+
+def deserialize_batch(message: RecordBatchMessage) -> pa.RecordBatch:
+    """What `deserialize_batch` (distributed_executor.rs:209-222) stands in for."""
+    schema = pa.ipc.read_schema(pa.py_buffer(message.schema))
+    batch = pa.ipc.read_record_batch(pa.py_buffer(message.batch_data), schema)
+    if batch.num_rows != message.num_rows:
+        raise ValueError(f"RecordBatchMessage says {message.num_rows} rows, the batch holds {batch.num_rows}")
+    return batch
