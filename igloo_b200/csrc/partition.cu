@@ -332,29 +332,32 @@ __global__ void __launch_bounds__(kRadixThreads, IGL_RADIX_CTAS) radix_scatter_k
 constexpr int kRtThreads = 1024;
 constexpr int kRtRows = 4;
 constexpr int kRtTile = kRtThreads * kRtRows;          // 4096 rows
-constexpr unsigned kRtMaxDyn = 190u << 10;
+constexpr unsigned kRtMaxDyn = 190u << 10;   // tile buffers; the two permutation arrays (16 KB) follow them
 
+template <int ROWS>   // rows per thread: 4 (4096-row tiles) or 8 (8192-row tiles: twice the run length per bin, for the exchange)
 __global__ void __launch_bounds__(kRtThreads, 1) radix_scatter_bulk_kernel(const __grid_constant__ RadixParams P, int n_buf, uint32_t tile_bytes) {
+    constexpr int kTile = kRtThreads * ROWS;
+    constexpr uint32_t kOffScale = ROWS / kRtRows;   // P.stage_off is laid out for 4096-row tiles
     extern __shared__ __align__(128) uint8_t in_tiles[];
     __shared__ unsigned int s_cnt[2][kRadixMaxParts];      // by tile parity: count, then exclusive start
     __shared__ unsigned long long s_gbase[kRadixMaxParts];
-    __shared__ unsigned short s_perm[kRtTile];              // slot -> row of the tile
-    __shared__ unsigned short s_part[kRtTile];              // slot -> bin
+    unsigned short* s_perm = reinterpret_cast<unsigned short*>(in_tiles + (size_t)n_buf * tile_bytes);   // slot -> row of the tile
+    unsigned short* s_part = s_perm + kTile;                                                               // slot -> bin
     __shared__ unsigned int s_warp_tot[kRtThreads / 32];
     __shared__ uint64_t s_full[2];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nbins = P.ndest << P.log2_parts;
-    const long long ntiles = (P.n + kRtTile - 1) / kRtTile;
+    const long long ntiles = (P.n + kTile - 1) / kTile;
     auto issue = [&](long long tile, int buf) {   // thread 0
         if (tile >= ntiles) return;
-        const long long row0 = tile * kRtTile;
-        const uint32_t rows = (uint32_t)min((long long)kRtTile, P.n - row0);
+        const long long row0 = tile * kTile;
+        const uint32_t rows = (uint32_t)min((long long)kTile, P.n - row0);
         uint32_t total = 0;
         for (int c = 0; c < P.ncols; ++c) total += ((rows << P.shift[c]) + 15u) & ~15u;
         mbar_arrive_expect_tx(&s_full[buf], total);
         uint8_t* dst = in_tiles + (size_t)buf * tile_bytes;
         for (int c = 0; c < P.ncols; ++c)
-            bulk_g2s(dst + P.stage_off[c], P.src[c] + ((size_t)row0 << P.shift[c]), ((rows << P.shift[c]) + 15u) & ~15u, &s_full[buf]);
+            bulk_g2s(dst + P.stage_off[c] * kOffScale, P.src[c] + ((size_t)row0 << P.shift[c]), ((rows << P.shift[c]) + 15u) & ~15u, &s_full[buf]);
     };
     if (tid == 0) {
         mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1);
@@ -368,16 +371,16 @@ __global__ void __launch_bounds__(kRtThreads, 1) radix_scatter_bulk_kernel(const
         const int buf = n_buf == 2 ? (it & 1) : 0;
         const uint32_t phase = n_buf == 2 ? ((uint32_t)(it >> 1) & 1u) : ((uint32_t)it & 1u);
         unsigned int* cnt = s_cnt[it & 1];
-        const long long row0 = tile * kRtTile;
-        const int rows = (int)min((long long)kRtTile, P.n - row0);
+        const long long row0 = tile * kTile;
+        const int rows = (int)min((long long)kTile, P.n - row0);
         const uint8_t* in = in_tiles + (size_t)buf * tile_bytes;
         mbar_wait(&s_full[buf], phase);
-        int bin[kRtRows];
-        unsigned int rank[kRtRows];
+        int bin[ROWS];
+        unsigned int rank[ROWS];
         {
-            const uint8_t* kc = in + P.stage_off[P.key_col];
+            const uint8_t* kc = in + P.stage_off[P.key_col] * kOffScale;
 #pragma unroll
-            for (int r = 0; r < kRtRows; ++r) {
+            for (int r = 0; r < ROWS; ++r) {
                 const int i = r * kRtThreads + tid;
                 bin[r] = -1;
                 if (i < rows) {
@@ -408,7 +411,7 @@ __global__ void __launch_bounds__(kRtThreads, 1) radix_scatter_bulk_kernel(const
         }
         __syncthreads();
 #pragma unroll
-        for (int r = 0; r < kRtRows; ++r) {
+        for (int r = 0; r < ROWS; ++r) {
             if (bin[r] >= 0) {
                 const unsigned int slot = cnt[bin[r]] + rank[r];
                 s_perm[slot] = (unsigned short)(r * kRtThreads + tid);
@@ -417,10 +420,10 @@ __global__ void __launch_bounds__(kRtThreads, 1) radix_scatter_bulk_kernel(const
         }
         __syncthreads();
         // write-out: consecutive threads -> consecutive slots -> runs of consecutive destination rows
-        unsigned long long d[kRtRows];
-        int src_row[kRtRows], dq[kRtRows];
+        unsigned long long d[ROWS];
+        int src_row[ROWS], dq[ROWS];
 #pragma unroll
-        for (int r = 0; r < kRtRows; ++r) {
+        for (int r = 0; r < ROWS; ++r) {
             const int sl = r * kRtThreads + tid;
             d[r] = 0; src_row[r] = 0; dq[r] = 0;
             if (sl < rows) {
@@ -432,14 +435,14 @@ __global__ void __launch_bounds__(kRtThreads, 1) radix_scatter_bulk_kernel(const
         }
         for (int c = 0; c < P.ncols; ++c) {
             if (P.shift[c] == 3) {
-                const uint64_t* sc = reinterpret_cast<const uint64_t*>(in + P.stage_off[c]);
+                const uint64_t* sc = reinterpret_cast<const uint64_t*>(in + P.stage_off[c] * kOffScale);
 #pragma unroll
-                for (int r = 0; r < kRtRows; ++r)
+                for (int r = 0; r < ROWS; ++r)
                     if (r * kRtThreads + tid < rows) reinterpret_cast<uint64_t*>(P.dst[dq[r]][c])[d[r]] = sc[src_row[r]];
             } else {
-                const uint32_t* sc = reinterpret_cast<const uint32_t*>(in + P.stage_off[c]);
+                const uint32_t* sc = reinterpret_cast<const uint32_t*>(in + P.stage_off[c] * kOffScale);
 #pragma unroll
-                for (int r = 0; r < kRtRows; ++r)
+                for (int r = 0; r < ROWS; ++r)
                     if (r * kRtThreads + tid < rows) reinterpret_cast<uint32_t*>(P.dst[dq[r]][c])[d[r]] = sc[src_row[r]];
             }
         }
@@ -465,16 +468,24 @@ bool radix_partition_supported(const igl_dev_col* cols, int ncols) {
 }
 
 // Launches the scatter pass for `P` (offsets and cursor already set): bulk-copy form when it applies.
-static cudaError_t launch_radix_scatter(igl_ctx* ctx, const RadixParams& P, uint32_t tile_bytes_4096, cudaStream_t st) {
+static cudaError_t launch_radix_scatter(igl_ctx* ctx, const RadixParams& P, uint32_t tile_bytes_4096, cudaStream_t st, bool long_runs = false) {
     bool aligned = true;
     for (int c = 0; c < P.ncols; ++c) if ((uintptr_t)P.src[c] & 15) aligned = false;
     const char* env = getenv("IGL_RADIX_BULK");
     if (aligned && tile_bytes_4096 <= kRtMaxDyn && (!(env && env[0] == '0') || tile_bytes_4096 > kRadixMaxStage)) {
         const int n_buf = 2u * tile_bytes_4096 <= kRtMaxDyn ? 2 : 1;
         const size_t dyn = (size_t)n_buf * tile_bytes_4096;
-        cudaError_t e = cudaFuncSetAttribute((const void*)radix_scatter_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRtMaxDyn);
+        cudaError_t e = cudaFuncSetAttribute((const void*)radix_scatter_bulk_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kRtMaxDyn + 4u * kRtTile));
         if (e != cudaSuccess) return e;
-        radix_scatter_bulk_kernel<<<ctx->sm_count, kRtThreads, dyn, st>>>(P, n_buf, tile_bytes_4096);
+        // 8192-row tiles (one buffer) when the caller wants the longest runs and the tile fits beside 48 KB of static arrays
+        const char* lenv = getenv("IGL_RADIX_LONG");
+        if (long_runs && !(lenv && lenv[0] == '0') && 2u * tile_bytes_4096 <= (176u << 10)) {
+            e = cudaFuncSetAttribute((const void*)radix_scatter_bulk_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((176u << 10) + 8u * kRtTile));
+            if (e != cudaSuccess) return e;
+            radix_scatter_bulk_kernel<8><<<ctx->sm_count, kRtThreads, 2u * tile_bytes_4096 + 4u * 2u * kRtTile, st>>>(P, 1, 2u * tile_bytes_4096);
+            return cudaGetLastError();
+        }
+        radix_scatter_bulk_kernel<4><<<ctx->sm_count, kRtThreads, dyn + 4u * kRtTile, st>>>(P, n_buf, tile_bytes_4096);
         return cudaGetLastError();
     }
     cudaError_t e = cudaFuncSetAttribute((const void*)radix_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRadixMaxStage);
@@ -652,7 +663,7 @@ int32_t igl_partition_scatter_radix(igl_ctx* ctx, const igl_dev_col* cols, int32
     if (e == cudaSuccess) e = cudaMemsetAsync(cursor, 0, sizeof(unsigned long long) * bins, st);
     P.offsets = offsets; P.cursor = cursor;
     if (e == cudaSuccess) {
-        e = launch_radix_scatter(ctx, P, off, st);
+        e = launch_radix_scatter(ctx, P, off, st, /*long_runs=*/ndest > 1);   // run length is what NVLink efficiency hangs on
         ctx->launches++;
     }
     if (e == cudaSuccess) e = cudaStreamSynchronize(st);

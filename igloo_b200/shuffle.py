@@ -290,14 +290,16 @@ class PartitionedJoin:
         plans = [RadixExchangePlan.from_counts(counts[:, i, :], self.rank, W, 1 << lp) for i in range(2)]
         self._fit_slabs([int(counts[:, i, :].reshape(W, W, 1 << lp).sum(axis=(0, 2)).max()) for i in range(2)])
         dist.barrier()                       # peers are done reading their slabs from the previous join
+        mark("exchange:barrier")
         for side, plan in zip((self.R, self.L), plans):
             nc = len(side.fields)
             dst = (C.c_void_p * (W * nc))(*[side.peer_ptrs[p][c] for p in range(W) for c in range(nc)])
             off = (C.c_int64 * bins)(*plan.bin_row_offset)
             check(lib.igl_partition_scatter_radix(ctx._h, self._devcols(side), nc, side.key_idx, side.nrows, W, lp, dst, off, st))
+        mark("exchange:scatter")
         torch.cuda.synchronize()
         dist.barrier()                       # every rank's stores have landed
-        mark("exchange")
+        mark("exchange:landed")
         nr, nl = plans[0].total_recv, plans[1].total_recv
         rcols = [DeviceColumn(f.type, nr, self.R.slabs[i]) for i, f in enumerate(self.R.fields)]
         lcols = [DeviceColumn(f.type, nl, self.L.slabs[i]) for i, f in enumerate(self.L.fields)]
