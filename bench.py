@@ -275,7 +275,7 @@ def run_ours(args):
         probe_bytes = np_total * 16 + n_out * 32
         # traffic: dram__bytes_read.sum + dram__bytes_write.sum of this kernel at this size (ncu, profiles/README.md)
         traffic = NCU_PROBE_TRAFFIC_BYTES if scale == 1 else None
-        line["roofline"] = {"bound": "hbm", "kernel": "join_probe_flat_kernel<3>", "achieved": probe_bytes / pm / 1e6,
+        line["roofline"] = {"bound": "hbm", "kernel": "join_probe_flat_kernel<3, 1> (Int64 key, dense output)", "achieved": probe_bytes / pm / 1e6,
                             "peak": peak, "unit": "GB/s", "frac": probe_bytes / pm / 1e6 / peak, "traffic": traffic,
                             "peak_source": peak_src, "kernel_ms": pm,
                             "algorithmic_bytes_per_launch": probe_bytes,
