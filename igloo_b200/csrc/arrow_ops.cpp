@@ -346,6 +346,17 @@ struct igl_op {
     bool input_done = false;
     // filter / projection
     Staging in;
+    // Filter / projection chunks are double-buffered: when a chunk is full its upload and kernels are
+    // queued (fp_begin) and the caller goes on staging the next chunk into `in` while the GPU works on
+    // `in_alt`; the chunk is finished (count read back, outputs copied down, batch queued: fp_end) when
+    // the next one is full or the input ends.
+    Staging in_alt;
+    struct FpPending {
+        bool active = false;
+        int64_t n = 0;
+        std::vector<igl_dev_col> dev, dout;
+        std::vector<void*> to_free;
+    } pend;
     igl_expr* pred = nullptr;
     std::vector<igl_expr*> proj_exprs;       // device expressions (owned)
     igl_fp* fp = nullptr;
@@ -386,38 +397,61 @@ int32_t d2h_col(igl_ctx* ctx, cudaStream_t st, OutCol& oc, const void* d_data, c
 }
 
 // Runs one staged chunk of a filter / projection operator.
-int32_t fp_flush(igl_op* op) {
+// Queues the staged chunk: upload, output buffers, kernel launches.  Does not wait.
+int32_t fp_begin(igl_op* op) {
     Staging& S = op->in;
     const int64_t n = S.rows;
     if (n == 0) return IGL_OK;
     igl_ctx* ctx = op->ctx;
     cudaStream_t st = ctx->stream;
-    std::vector<igl_dev_col> dev;
-    IGL_TRY(S.upload(st, dev));
-    // device outputs
+    auto& PD = op->pend;
+    PD.dev.clear(); PD.dout.clear(); PD.to_free.clear();
+    IGL_TRY(S.upload(st, PD.dev));
     const int nfo = op->n_fp_out + (op->need_rowid ? 1 : 0);
-    std::vector<igl_dev_col> dout(nfo);
-    std::vector<void*> to_free;
-    auto cleanup = [&]() { for (void* p : to_free) pool_free(ctx, p); };
-    int64_t n_out = n;
+    PD.dout.assign(nfo, igl_dev_col{});
+    auto cleanup = [&]() { for (void* p : PD.to_free) pool_free(ctx, p); PD.to_free.clear(); };
     if (op->fp) {
         for (int j = 0; j < nfo; ++j) {
             int32_t t = 0, nl = 0;
             igl_fp_output_type(op->fp, j, &t, &nl);
-            dout[j].type = t;
+            PD.dout[j].type = t;
             const size_t bytes = t == IGL_T_BOOL ? (size_t)(n + 7) / 8 : (size_t)n * type_width(t);
             void* p = nullptr;
             int32_t rc = pool_alloc(ctx, pad64(bytes), &p);
             if (rc < 0) { cleanup(); return rc; }
-            to_free.push_back(p); dout[j].data = p;
+            PD.to_free.push_back(p); PD.dout[j].data = p;
             if (nl) {
                 rc = pool_alloc(ctx, pad64((size_t)(n + 7) / 8), &p);
                 if (rc < 0) { cleanup(); return rc; }
-                to_free.push_back(p); dout[j].validity = (uint8_t*)p;
+                PD.to_free.push_back(p); PD.dout[j].validity = (uint8_t*)p;
             }
         }
-        int32_t rc = igl_fp_run(op->fp, dev.data(), n, dout.data(), &n_out, st);
+        int32_t rc = igl_fp_launch(op->fp, PD.dev.data(), n, PD.dout.data(), st);
         if (rc < 0) { cleanup(); return rc; }
+    }
+    PD.n = n;
+    PD.active = true;
+    std::swap(op->in, op->in_alt);   // the queued chunk now lives in in_alt; `in` is the empty one
+    return IGL_OK;
+}
+
+// Finishes the queued chunk: waits for it, copies the outputs down, queues the batch.
+int32_t fp_end(igl_op* op) {
+    auto& PD = op->pend;
+    if (!PD.active) return IGL_OK;
+    PD.active = false;
+    Staging& S = op->in_alt;
+    const int64_t n = PD.n;
+    igl_ctx* ctx = op->ctx;
+    cudaStream_t st = ctx->stream;
+    std::vector<igl_dev_col>& dev = PD.dev;
+    std::vector<igl_dev_col>& dout = PD.dout;
+    std::vector<void*>& to_free = PD.to_free;
+    auto cleanup = [&]() { for (void* p : to_free) pool_free(ctx, p); to_free.clear(); };
+    int64_t n_out = n;
+    if (op->fp) {
+        int32_t rc = igl_fp_finish(op->fp, &n_out, st);
+        if (rc < 0) { cudaStreamSynchronize(st); S.reset(); cleanup(); return rc; }
     }
     S.reset();
     if (n_out == 0 && op->has_pred) { cleanup(); return IGL_OK; }   // filter.rs:59-63: empty results are dropped
@@ -489,6 +523,12 @@ int32_t fp_flush(igl_op* op) {
     for (auto& c : ob.cols) c.null_count = c.valid ? count_zero_bits(c.valid, n_out) : 0;
     op->ready.push_back(std::move(ob));
     return IGL_OK;
+}
+
+// A chunk is full (or the input ended): finish the chunk queued before, queue this one.
+int32_t fp_flush(igl_op* op) {
+    IGL_TRY(fp_end(op));
+    return fp_begin(op);
 }
 
 // Appends the staged build chunk to the device-resident build side.
@@ -672,6 +712,7 @@ int32_t igl_op_filter_project_create(igl_ctx* ctx, const struct ArrowSchema* in_
     }
     if (op->pred) for (auto& nd : op->pred->nodes) if (nd.op == IGL_OP_COL) wanted[nd.col] = 1;
     op->in.wanted = wanted;
+    op->in_alt = op->in;   // second (still empty) staging buffer of the same shape
     bool any_utf8 = false;
     for (auto& sp : op->out_spec) any_utf8 |= sp.utf8_pass;
     op->need_rowid = any_utf8 && op->has_pred;
@@ -784,7 +825,10 @@ int32_t igl_op_finish_input(igl_op* op) {
     if (op->is_join) {
         if (!op->build_done) IGL_TRY(igl_op_finish_build(op));
         IGL_TRY(join_probe_flush(op));
-    } else IGL_TRY(fp_flush(op));
+    } else {
+        IGL_TRY(fp_flush(op));
+        IGL_TRY(fp_end(op));
+    }
     op->input_done = true;
     return IGL_OK;
 }
@@ -802,7 +846,9 @@ void igl_op_destroy(igl_op* op) {
     if (!op) return;
     DeviceGuard g(op->ctx->device);
     for (auto& b : op->ready) for (auto& c : b.cols) { pinned_pool().put(c.data); pinned_pool().put(c.valid); pinned_pool().put(c.off); }
+    if (op->pend.active) { cudaStreamSynchronize(op->ctx->stream); for (void* p : op->pend.to_free) pool_free(op->ctx, p); }
     op->in.destroy();
+    op->in_alt.destroy();
     op->build.destroy();
     if (op->fp) igl_fp_destroy(op->fp);
     if (op->join) igl_join_destroy(op->join);
