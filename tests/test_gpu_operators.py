@@ -155,3 +155,15 @@ def test_planner_join_of_filtered_scans(ctx):
     assert got.num_rows == int(m.sum()) and got.schema.names == ["l_orderkey", "l_qty", "o_orderkey", "o_total"]
     assert np.array_equal(np.sort(got.column("l_orderkey").to_numpy()), np.sort(items.column("l_orderkey").to_numpy()[m]))
     assert np.array_equal(got.column("l_orderkey").to_numpy(), got.column("o_orderkey").to_numpy())
+
+
+def test_golden_scan_fixture_through_filter_exec(ctx):
+    """tests/golden/scan_fixture.json (the reference's test_data.csv): CSV -> MemoryScanExec -> FilterExec on
+    the GPU, the Utf8 column passing through by row id."""
+    import io
+    import pyarrow.csv as pacsv
+    from igloo_b200.operators import FilterExec, MemoryScanExec
+    g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "scan_fixture.json")))
+    tbl = pacsv.read_csv(io.BytesIO(g["csv"].encode()))
+    got, _ = collect(FilterExec(MemoryScanExec(tbl), col("col_a") > lit(1, T_I64), ctx))
+    assert got.to_pydict() == {"col_a": [2], "col_b": ["bar"]}

@@ -280,3 +280,19 @@ def test_pyarrow_second_opinion_join(mode):
         g = sorted(zip(*[got.column(c).to_pylist() for c in ("k", "w", "right_k", "v", "z")]), key=repr)
         w = sorted(zip(*[want.column(c).to_pylist() for c in ("k", "w", "rk", "v", "z")]), key=repr)
         assert g == w
+
+
+def test_golden_scan_fixture_csv():
+    """The reference's tiny scan fixture (connectors/filesystem/test_data.csv), read the way the harness
+    reads CSV (pyarrow), goes through the restated Filter: col_a > 1 keeps (2, bar)."""
+    import io
+    import json
+    import os
+    import pyarrow.csv as pacsv
+    g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "scan_fixture.json")))
+    tbl = pacsv.read_csv(io.BytesIO(g["csv"].encode()))
+    assert tbl.to_pydict() == g["rows"]
+    sch = [Field("col_a", T_I64), Field("col_b", T_UTF8)]
+    t = orc.Table.scan(arrow_to_columns(tbl))
+    out = columns_to_arrow(t.filter(lower(col("col_a") > lit(1, T_I64), sch)[0]).columns())
+    assert out.to_pydict() == {"col_a": [2], "col_b": ["bar"]}
