@@ -5,6 +5,13 @@
 // and bench.py's cpu_baseline / --impl reference legs.  Nothing in the product
 // path (igloo_b200/, libigloo_cuda.so) may include, link or call this file.
 //
+// Pinning: Filter / Projection are checked against the reference's own known answers
+// (integration_test.rs:21-29,59,72-75 and `SELECT 42`; tests/golden/users.json, and the CSV
+// scan fixture tests/golden/scan_fixture.json).  HashJoin: PARITY UNPINNED — the reference
+// holds no test, fixture or golden vector for HashJoinExec, and it cannot be built here
+// (Rust, no toolchain); the join below follows hash_join.rs line by line, with Arrow C++
+// (Acero) as a second opinion in tests/test_oracle.py.
+//
 // Reference followed (all under /root/reference/crates/engine/src/):
 //   operators/filter.rs:39-68        FilterExec::execute
 //   operators/projection.rs:48-72    ProjectionExec::execute
