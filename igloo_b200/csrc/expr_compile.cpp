@@ -25,6 +25,8 @@ extern "C" int32_t igl_expr_compile(igl_ctx* ctx, const uint8_t* bc, size_t len,
     *out = nullptr;
     if (!bc || len == 0) return fail(IGL_ERR_INVALID_ARG, "igl_expr_compile: empty bytecode");
     if (ncols < 0 || (ncols > 0 && !col_types)) return fail(IGL_ERR_INVALID_ARG, "igl_expr_compile: bad schema");
+    // the IR addresses columns with 8 bits (Instr::a_idx / b_idx): wider schemas are refused, not truncated
+    if (ncols > 256) return fail(IGL_ERR_UNSUPPORTED, "schemas of more than 256 columns are not supported (got %d)", ncols);
     auto e = std::make_unique<igl_expr>();
     e->ncols = ncols;
     e->col_types.assign(col_types, col_types + ncols);
@@ -105,6 +107,8 @@ extern "C" int32_t igl_expr_compile(igl_ctx* ctx, const uint8_t* bc, size_t len,
                 return fail(IGL_ERR_INVALID_ARG, "unknown opcode 0x%02x in expression bytecode", n.op);
         }
         N.push_back(n);
+        // lowering recurses once per node: bound the tree here, long before the host stack is at risk
+        if (N.size() > (size_t)(4 * kMaxInstr)) return fail(IGL_ERR_UNSUPPORTED, "expression has more than %d nodes", 4 * kMaxInstr);
         st.push_back((int)N.size() - 1);
     }
 #undef NEED

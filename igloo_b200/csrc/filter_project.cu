@@ -730,7 +730,11 @@ extern "C" int32_t igl_fp_run_static(igl_fp* fp, const igl_dev_col* in, int64_t 
         P.out_valid[j] = nullptr;
     }
     if (nrows == 0) { if (out_rows) *out_rows = 0; return IGL_OK; }
-    const size_t need = 256 + (size_t)scan_scratch_words(P.T.ntiles) * 8;   // <= kFpStaticScratchBytes by the row limit
+    const size_t need = 256 + (size_t)scan_scratch_words(P.T.ntiles) * 8;
+    // the row limit bounds this only while no tile is narrower than 384 rows (tile_pipe.cuh): check, never assume
+    if (need > kFpStaticScratchBytes)
+        return fail(IGL_ERR_INVALID_ARG, "igl_fp_run_static: this plan needs %zu bytes of scan scratch for %lld rows, the static array holds %zu; "
+                    "split the batch or use igl_fp_run", need, (long long)nrows, kFpStaticScratchBytes);
     P.T.hdr = (PipeHeader*)scratch;
     P.T.status = (uint64_t*)((uint8_t*)scratch + 256);
     IGL_CUDA_OK(cudaMemsetAsync(scratch, 0, need, st));   // ticket, error flags, count and every status word start at zero

@@ -502,7 +502,9 @@ __device__ __forceinline__ void multi_lookup(const JoinProbeParams& P, MultiTile
     const int row0 = warp * (32 * R) + lane;
     Match m[R];
     lookup_rows<R, HAS_NULLS>(P, t.stage, row0, warp < P.T.active_warps ? t.rows : 0, m);
-    uint32_t running = 0;
+    // sums in 64 bits: 128 probe rows that each hit a run of tens of millions of rows overflow 32;
+    // a warp total of 2^31 or more is reported as such and take_counts raises the tile-overflow flag
+    unsigned long long running = 0;
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         const bool inr = warp < P.T.active_warps && (row0 + r * 32) < t.rows;
@@ -510,14 +512,14 @@ __device__ __forceinline__ void multi_lookup(const JoinProbeParams& P, MultiTile
         if (!inr) c = 0;
         t.hitb[r] = __ballot_sync(0xffffffffu, m[r].hit);
         t.rend[r] = (uint32_t)m[r].val;
-        uint32_t inc = c;
+        unsigned long long inc = c;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t nb = __shfl_up_sync(0xffffffffu, inc, o);
+            const unsigned long long nb = __shfl_up_sync(0xffffffffu, inc, o);
             if (lane >= o) inc += nb;
         }
         t.cnt[r] = c;
-        t.excl[r] = running + inc - c;
+        t.excl[r] = (uint32_t)(running + inc - c);   // exact whenever the total below stays under 2^31 (else the call fails)
         running += __shfl_sync(0xffffffffu, inc, 31);
     }
     t.count = (long long)running;

@@ -54,14 +54,27 @@ fn stream_through(op: OpHandle, mut input: BatchStream, schema: Arc<Schema>) -> 
             while let Some(out) = pull(&op, &schema, &mut eos)? { yield out; }
         }
         check(unsafe { igl_op_finish_input(op.0) })?;
+        // after finish_input the operator drains: IGL_AGAIN now only means "a download is still in
+        // flight", so hand the executor back its thread instead of spinning on the FFI call
         while !eos {
-            if let Some(out) = pull(&op, &schema, &mut eos)? { yield out; }
+            match pull(&op, &schema, &mut eos)? {
+                Some(out) => yield out,
+                None if !eos => tokio::task::yield_now().await,
+                None => {}
+            }
         }
     })
 }
 
 // ---- Filter (filter.rs:19, 39-68), optionally with the Projection folded into it -----------
-#[derive(Debug, Clone)]
+// no derive(Debug): `dyn ExecutionPlan` has no Debug bound (physical_plan.rs:11)
+impl std::fmt::Debug for GpuFilterExec {
+    fn fmt(&self, f: &mut std::fmt::Formatter<'_>) -> std::fmt::Result {
+        f.debug_struct("GpuFilterExec").field("predicate", &self.predicate).field("fused_projection", &self.projection.is_some()).finish_non_exhaustive()
+    }
+}
+
+#[derive(Clone)]
 pub struct GpuFilterExec {
     ctx: Arc<GpuContext>,
     input: Arc<dyn ExecutionPlan>,
@@ -116,7 +129,14 @@ impl ExecutionPlan for GpuFilterExec {
 }
 
 // ---- Projection (projection.rs:19-23, 48-72) --------------------------------------------------
-#[derive(Debug, Clone)]
+// no derive(Debug): `dyn ExecutionPlan` has no Debug bound (physical_plan.rs:11)
+impl std::fmt::Debug for GpuProjectionExec {
+    fn fmt(&self, f: &mut std::fmt::Formatter<'_>) -> std::fmt::Result {
+        f.debug_struct("GpuProjectionExec").field("schema", &self.schema).finish_non_exhaustive()
+    }
+}
+
+#[derive(Clone)]
 pub struct GpuProjectionExec {
     ctx: Arc<GpuContext>,
     input: Arc<dyn ExecutionPlan>,
@@ -143,7 +163,14 @@ impl ExecutionPlan for GpuProjectionExec {
 }
 
 // ---- HashJoin (hash_join.rs:35-76, 100-213) ------------------------------------------------------
-#[derive(Debug, Clone)]
+// no derive(Debug): `dyn ExecutionPlan` has no Debug bound (physical_plan.rs:11)
+impl std::fmt::Debug for GpuHashJoinExec {
+    fn fmt(&self, f: &mut std::fmt::Formatter<'_>) -> std::fmt::Result {
+        f.debug_struct("GpuHashJoinExec").field("join_type", &self.join_type).field("schema", &self.schema).finish_non_exhaustive()
+    }
+}
+
+#[derive(Clone)]
 pub struct GpuHashJoinExec {
     ctx: Arc<GpuContext>,
     left: Arc<dyn ExecutionPlan>,

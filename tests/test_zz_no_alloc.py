@@ -60,6 +60,19 @@ def test_static_scratch_entry_point_matches_pooled_one_on_two_calls_in_a_row(ctx
         # integer column and float64 column: bit-exact, the tolerance of every parity test here
         assert torch.equal(got[0].data[:n_got], want[0].data[:n_want])
         assert torch.equal(got[1].data[:n_got].view(torch.int64), want[1].data[:n_want].view(torch.int64))
+    # and against the CPU oracle (a prefix the oracle finishes quickly; row order is preserved, so
+    # the prefix of the output is the output of the prefix)
+    from igloo_b200.expr import lower
+    from oracle import oracle as orc
+    m = 200_000
+    ha, hb, hx = (orc.gen_i32_uniform(seed, 0, 0, m, 1000), orc.gen_i32_uniform(seed, 1, 0, m, 1 << 31),
+                  orc.gen_f64_unit(seed, 2, 0, m))
+    t = orc.Table.scan([orc.Column("a", orc.T_I32, ha), orc.Column("b", orc.T_I32, hb), orc.Column("x", orc.T_F64, hx)])
+    ref = t.filter(lower(col("a") < thr, fields)[0]).project([lower(e, fields)[0] for e in proj], ["s", "y"]).columns()
+    k = len(ref[0].values)
+    assert 0 < k <= n_got
+    assert np.array_equal(got[0].data[:k].cpu().numpy(), ref[0].values)
+    assert np.array_equal(got[1].data[:k].cpu().numpy().view(np.int64), ref[1].values.view(np.int64))
     # the pooled entry point is unaffected by the static one having run in between
     again, n_again = fp.run([a, b, x], nrows)
     assert n_again == n_want and torch.equal(again[0].data[:n_again], want[0].data[:n_want])
