@@ -85,6 +85,14 @@ def test_expr_compile_type_rules_without_device(lib):
     assert rc == -1
     rc, _ = compile_(bytes([0x01, 0, 0, 0x01, 0, 0]))
     assert rc == -1 and b"exactly one" in lib.igl_last_error()
+    # the IR addresses columns with 8 bits: a 300-column schema is refused, never truncated
+    wide_t = (ctypes.c_int32 * 300)(*([T_I32] * 300))
+    h = ctypes.c_void_p()
+    rc = lib.igl_expr_compile(None, bytes([0x01, 0x2B, 0x01]), 3, wide_t, bytes(300), 300, ctypes.byref(h))   # COL 299
+    assert rc == -2 and b"256 columns" in lib.igl_last_error()
+    # a very long unary chain is refused before lowering can recurse through it
+    rc, _ = compile_(bytes([0x01, 0, 0]) + bytes([0x25]) * 100_000)    # a, then NEG x 100000
+    assert rc == -2 and b"nodes" in lib.igl_last_error()
 
 
 def test_cpp_host_mirror_compiles_and_links_against_the_abi(lib, tmp_path):
