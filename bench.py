@@ -193,7 +193,8 @@ def run_ours(args):
     rf = [Field("k", T_I64), Field("v", T_I64)]
 
     if world > 1:
-        from igloo_b200.shuffle import PartitionedJoin
+        from igloo_b200.shuffle import PartitionedJoin, init_comm
+        init_comm(ctx, rank, world)
         pj = PartitionedJoin(ctx, rank, world, lf, rf, 0, 0, mode=args.exchange)
         # row-range shard of both sides, as after a parallel scan
         b0, b1 = nb_total * rank // world, nb_total * (rank + 1) // world
@@ -251,6 +252,27 @@ def run_ours(args):
         dist.all_reduce(cnt)
         n_out = int(cnt.item())
     assert n_out == np_total, (n_out, np_total)   # every probe row matches exactly once
+    # ---- parity at the timed size, outside the timed region: the multiset digest of what the join
+    # wrote (all ranks combined) against the digest of (k, w, k, v(k)) recomputed from the generator
+    # definition alone — no hash table, no exchange involved (SURVEY.md §8d "parity check at scale")
+    if world > 1:
+        n_local, got_cols = pj.out_rows, pj.out
+    else:
+        n_local, got_cols = n_out, out
+    got = ctx.digest(got_cols, n_local)
+    n_probe_local = lk.length
+    expect_v = ctx.gen(5, SEED_C3, 1, 0, n_probe_local, bits=bits, keys=lk)
+    want = ctx.digest([lk, lw, lk, expect_v], n_probe_local)
+    del expect_v
+    if world > 1:
+        both = [None] * world
+        dist.all_gather_object(both, (got, want))
+        M = (1 << 64) - 1
+        fold = lambda ds: (sum(d[0] for d in ds) & M, __import__("functools").reduce(lambda a, b: a ^ b, (d[1] for d in ds)), sum(d[2] for d in ds) & M)  # noqa: E731
+        got, want = fold([b[0] for b in both]), fold([b[1] for b in both])
+    parity = {"digest_equal": got == want, "rows": n_out, "rows_expected": np_total,
+              "check": "sum/xor/sum2 of splitmix64 row hashes of the join output (all ranks) == the same digest of (k, w, k, v(perm^-1(k))) regenerated from the data definition"}
+    assert parity["digest_equal"], (got, want)
     ms_step = ms_total / args.steps
     value = rows_per_step / (ms_step / 1e3)
 
@@ -260,11 +282,22 @@ def run_ours(args):
             "config": {"workload": f"C3 inner hash join: build 2^{bits} (k,v) x probe {np_total} (k,w), int64 uniform keys, 1 match per probe row",
                        "l2_policy": "inputs (>= 18 GB) and the 4 GiB table are far larger than the 126 MB L2",
                        "parallelism": f"hash-partitioned over {world} GPUs, exchange={args.exchange}" if world > 1 else "1 GPU"},
-            "gpu_launches": launches, "clocks": clocks}
+            "gpu_launches": launches, "clocks": clocks, "parity": parity}
     if world > 1:
         phases = [None] * world
-        dist.all_gather_object(phases, pj.phase_ms())
-        line["phases_ms_per_rank"] = phases
+        dist.all_gather_object(phases, (pj.phase_ms(), pj.stats()))
+        line["phases_ms_per_rank"] = [p[0] for p in phases]
+        line["exchange_stats_per_rank"] = [p[1] for p in phases]
+        # NVLink: bytes each GPU read from its peers (build rows pulled + probe rows fetched by the
+        # probe kernel) over the time those reads had (build pull + probe phase), against 900 GB/s
+        per = []
+        for ph, stt in phases:
+            t = (ph["build"] + ph["probe"]) / 1e3
+            per.append(stt["bytes_read_from_peers"] / t / 1e9 if t > 0 else 0.0)
+        line["nvlink"] = {"bytes_in_per_gpu": [p[1]["bytes_read_from_peers"] for p in phases],
+                          "gb_per_s_per_gpu_over_build_and_probe_phases": [round(x, 1) for x in per],
+                          "frac_of_900": round(max(per) / 900.0, 3),
+                          "floor_ms_at_900": round(max(p[1]["bytes_read_from_peers"] for p in phases) / 900e9 * 1e3, 3)}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()

@@ -115,6 +115,16 @@ _sig("igl_partition_scatter_radix", _i32, _vp, _P(DevCol), _i32, _i32, _i64, _i3
 _sig("igl_ipc_export", _i32, _vp, _vp, C.c_char_p)
 _sig("igl_ipc_open", _i32, _vp, C.c_char_p, _P(_vp))
 _sig("igl_ipc_close", _i32, _vp, _vp)
+_sig("igl_comm_unique_id", _i32, C.c_char_p)
+_sig("igl_comm_init", _i32, _vp, _i32, _i32, C.c_char_p)
+_sig("igl_comm_rank", _i32, _vp, _P(_i32), _P(_i32))
+_sig("igl_join_shuffle_create", _i32, _vp, _i32, _P(_i32), C.c_char_p, _i32, _P(_i32), C.c_char_p, _i32, _vp, _vp, _i32, _P(_vp))
+_sig("igl_join_shuffle_run", _i32, _vp, _P(DevCol), _i64, _P(DevCol), _i64, _P(_i64), _vp)
+_sig("igl_join_shuffle_output", _i32, _vp, _P(DevCol), _P(_i64))
+_sig("igl_join_shuffle_phase_ms", _i32, _vp, _P(C.c_double))
+_sig("igl_join_shuffle_stats", _i32, _vp, _P(_i64))
+_sig("igl_join_shuffle_destroy", None, _vp)
+_sig("igl_shuffle_plan", _i32, _i32, _i32, _i32, _P(_i64), _P(_i64), _P(_i32), _P(_i64), _P(_i64), _P(_i64))
 _sig("igl_gen_column", _i32, _vp, _i32, _u64, _u64, _i64, _i64, _u64, _i32, _vp, _vp, _vp)
 _sig("igl_digest_rows", _i32, _vp, _P(DevCol), _i32, _i64, _P(_u64), _vp)
 _sig("igl_op_filter_project_create", _i32, _vp, _P(ArrowSchema), C.c_char_p, _sz, _P(C.c_char_p), _P(_sz),

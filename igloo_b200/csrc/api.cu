@@ -149,6 +149,7 @@ void igl_ctx_destroy(igl_ctx* ctx) {
     if (!ctx) return;
     DeviceGuard g(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    comm_release(ctx);
     for (auto& kv : ctx->free_lists)
         for (void* p : kv.second) cudaFree(p);
     for (auto& kv : ctx->live) cudaFree(kv.first);

@@ -72,6 +72,7 @@ struct igl_ctx {
     std::map<void*, size_t> live;      // ptr -> bucket bytes
     size_t pool_bytes = 0;
     std::map<void*, size_t> pinned;
+    void* comm = nullptr;              // igl::Comm (shuffle.cu) once igl_comm_init has run
 };
 
 namespace igl {
@@ -88,4 +89,5 @@ inline cudaStream_t pick_stream(igl_ctx* ctx, void* s) { return s ? (cudaStream_
 inline int type_width(int t) { return t == IGL_T_I32 ? 4 : (t == IGL_T_I64 || t == IGL_T_F64) ? 8 : 0; }
 int32_t pool_alloc(igl_ctx* ctx, size_t bytes, void** out);
 void pool_free(igl_ctx* ctx, void* p);
+void comm_release(igl_ctx* ctx);    // shuffle.cu: destroys the NCCL communicator of a context, if any
 }  // namespace igl

@@ -617,6 +617,7 @@ constexpr int kFlatThreads = IGL_FLAT_THREADS;
 constexpr int kFlatRows = IGL_FLAT_ROWS;
 constexpr int kFlatChunk = kFlatThreads * kFlatRows;   // 1024 rows per CTA iteration
 constexpr int kFlatClaim = 4;                          // consecutive chunks claimed per ticket
+static_assert(kFlatChunk == kSegChunkRows, "ProbeSeg::chunk0 counts chunks of the flat probe kernel");
 
 // Expands the listed giant runs: every CTA takes a slice of every run.  The left row's values
 // are read once per thread from the (global) left columns; right columns are gathered by row id.
@@ -670,6 +671,12 @@ struct FlatProbeParams {
     // DENSE form: matched rows keep their input position, the warps leave a hit bitmap
     uint32_t* hit_words;                // bit i = probe row i matched; padded to whole 1024-row tiles, zero-filled
     unsigned long long* miss_counter;
+    // SEG form (multi-GPU join): the probe rows are a list of runs spread over several source
+    // buffers — this GPU's staging buffer and the peers', read over NVLink by the same bulk
+    // copies.  `nrows` is then the virtual row count (128 per chunk, runs padded to whole chunks).
+    const ProbeSeg* segs;
+    int nsegs;
+    const uint8_t* seg_left[kSegMaxSrc][kJoinMaxCols];
 };
 
 constexpr int kFlatStages = 3;   // chunks in flight per CTA: the one being probed + two on their way from HBM
@@ -688,11 +695,20 @@ constexpr int kFlatStages = 3;   // chunks in flight per CTA: the one being prob
 // and matched rows are written at their INPUT position.  If any row missed, dense_fix
 // afterwards moves matched rows from the tail into the holes (output order carries no
 // meaning here: the partitioned probe is already unordered).
-template <int KEY_TYPE, bool DENSE>
+//
+// SEG form: the chunk a CTA claims is looked up in a list of runs (ProbeSeg) that may sit in
+// another GPU's memory; the bulk copy then crosses NVLink and lands in shared memory directly,
+// so the exchange of the probe side and the probe are one kernel: no receive buffer, and the
+// transfer of a chunk overlaps the lookups of the chunks before it.  (Plain bulk copies, never
+// multicast: TMA multicast loads here read only this GPU's memory, since on B200 a TMA
+// multicast load from another GPU's memory hung the GPU.)
+template <int KEY_TYPE, bool DENSE, bool SEG>
 __global__ void __launch_bounds__(kFlatThreads, IGL_FLAT_CTAS) join_probe_flat_kernel(const __grid_constant__ FlatProbeParams P) {
+    static_assert(!SEG || DENSE, "segmented input is only written densely");
     extern __shared__ __align__(128) uint8_t fsmem[];
     __shared__ uint64_t s_full[kFlatStages];
     __shared__ long long s_chunk_of[kFlatStages];
+    __shared__ int s_rows_of[kFlatStages];   // SEG: rows of the chunk held by each stage
     __shared__ unsigned int s_wcnt[kFlatThreads / 32];
     __shared__ unsigned long long s_base;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -707,6 +723,7 @@ __global__ void __launch_bounds__(kFlatThreads, IGL_FLAT_CTAS) join_probe_flat_k
     long long grp_base = 0;
     int grp_used = kFlatClaim;
     unsigned int pending = 0;
+    int cur_seg = 0;   // SEG: claims only grow, so the run holding a chunk is found by walking forward
     auto refill = [&](int s) {   // claim the next chunk and start its copies into stage s
         if (grp_used == kFlatClaim) {
             grp_base = (long long)pending * kFlatClaim;
@@ -716,12 +733,28 @@ __global__ void __launch_bounds__(kFlatThreads, IGL_FLAT_CTAS) join_probe_flat_k
         const long long chunk = grp_base + grp_used++;
         if (chunk >= nchunks) { s_chunk_of[s] = -1; mbar_arrive(&s_full[s]); return; }
         s_chunk_of[s] = chunk;
+        uint8_t* st = fsmem + (size_t)s * P.stage_bytes;
+        if (SEG) {
+            while (cur_seg + 1 < P.nsegs && (long long)__ldg(&P.segs[cur_seg + 1].chunk0) <= chunk) ++cur_seg;
+            const uint32_t c0 = __ldg(&P.segs[cur_seg].chunk0), srows = __ldg(&P.segs[cur_seg].rows);
+            const unsigned long long rs = __ldg(&P.segs[cur_seg].row0_src);
+            const uint32_t done = (uint32_t)(chunk - c0) * kFlatChunk;
+            const uint32_t rows = min((uint32_t)kFlatChunk, srows - done);
+            const int src = (int)(rs >> 56);
+            const size_t srow = (size_t)(rs & 0x00FFFFFFFFFFFFFFull) + done;
+            s_rows_of[s] = (int)rows;
+            uint32_t total = 0;
+            for (int c = 0; c < P.n_left; ++c) total += ((rows << P.lshift[c]) + 15u) & ~15u;
+            mbar_arrive_expect_tx(&s_full[s], total);
+            for (int c = 0; c < P.n_left; ++c)
+                bulk_g2s(st + P.stage_off[c], P.seg_left[src][c] + (srow << P.lshift[c]), ((rows << P.lshift[c]) + 15u) & ~15u, &s_full[s]);
+            return;
+        }
         const long long cb = chunk * kFlatChunk;
         const uint32_t rows = (uint32_t)min((long long)kFlatChunk, P.nrows - cb);
         uint32_t total = 0;
         for (int c = 0; c < P.n_left; ++c) total += ((rows << P.lshift[c]) + 15u) & ~15u;
         mbar_arrive_expect_tx(&s_full[s], total);
-        uint8_t* st = fsmem + (size_t)s * P.stage_bytes;
         for (int c = 0; c < P.n_left; ++c)
             bulk_g2s(st + P.stage_off[c], P.left[c] + ((size_t)cb << P.lshift[c]), ((rows << P.lshift[c]) + 15u) & ~15u, &s_full[s]);
     };
@@ -739,7 +772,7 @@ __global__ void __launch_bounds__(kFlatThreads, IGL_FLAT_CTAS) join_probe_flat_k
         if (chunk < 0) break;   // claims only grow: nothing is left for this CTA
         const uint8_t* stage = fsmem + (size_t)sidx * P.stage_bytes;
         const long long cbase = chunk * kFlatChunk;                       // uniform
-        const int nvalid = (int)min((long long)kFlatChunk, P.nrows - cbase);   // rows of this chunk that exist
+        const int nvalid = SEG ? s_rows_of[sidx] : (int)min((long long)kFlatChunk, P.nrows - cbase);   // rows of this chunk that exist
         uint64_t raw[kFlatRows], k[kFlatRows];
         unsigned long long val[kFlatRows];
         ulonglong4 q[kFlatRows];
@@ -828,7 +861,8 @@ __global__ void __launch_bounds__(kFlatThreads, IGL_FLAT_CTAS) join_probe_flat_k
             uint32_t mine = 0;   // the ballots are the bitmap words of this warp's rows
 #pragma unroll
             for (int r = 0; r < kFlatRows; ++r) {
-                misses += __popc(__ballot_sync(0xffffffffu, (live >> r) & 1u)) - __popc(hb[r]);
+                // SEG: the padding behind a run's last row is a hole like any unmatched row
+                misses += (SEG ? 32 : __popc(__ballot_sync(0xffffffffu, (live >> r) & 1u))) - __popc(hb[r]);
                 mine = lane == r ? hb[r] : mine;
                 p[r] = (unsigned int)(lrow + r * 32);
             }
@@ -1036,7 +1070,156 @@ probe_kernel_t pick_probe(bool csr, int rows_per_lane, bool nulls) {
 
 bool fixed_width(int t) { return t == IGL_T_I32 || t == IGL_T_I64 || t == IGL_T_F64; }
 
+const void* flat_kernel_for(int kt, bool dense, bool seg) {
+    if (seg)
+        return kt == IGL_T_I32 ? (const void*)join_probe_flat_kernel<IGL_T_I32, true, true>
+               : kt == IGL_T_F64 ? (const void*)join_probe_flat_kernel<IGL_T_F64, true, true>
+                                 : (const void*)join_probe_flat_kernel<IGL_T_I64, true, true>;
+    if (dense)
+        return kt == IGL_T_I32 ? (const void*)join_probe_flat_kernel<IGL_T_I32, true, false>
+               : kt == IGL_T_F64 ? (const void*)join_probe_flat_kernel<IGL_T_F64, true, false>
+                                 : (const void*)join_probe_flat_kernel<IGL_T_I64, true, false>;
+    return kt == IGL_T_I32 ? (const void*)join_probe_flat_kernel<IGL_T_I32, false, false>
+           : kt == IGL_T_F64 ? (const void*)join_probe_flat_kernel<IGL_T_F64, false, false>
+                             : (const void*)join_probe_flat_kernel<IGL_T_I64, false, false>;
+}
+
+uint32_t flat_stage_bytes(const igl_join* j) {
+    uint32_t b = 0;
+    for (int t : j->lt) b += (uint32_t)kFlatChunk << (t == IGL_T_I32 ? 2 : 3);
+    return b;
+}
+
+// The flat kernel's preconditions that do not depend on the probe columns themselves.
+bool flat_eligible(const igl_join* j) {
+    if (!j->built || j->csr || j->left_join || j->never_match) return false;
+    for (const auto& rc : j->right) if (rc.validity) return false;
+    return (size_t)flat_stage_bytes(j) * kFlatStages <= (200u << 10);   // very wide probe rows take the tiled kernels
+}
+
+// Everything of FlatProbeParams but the probe-side source pointers.
+int32_t flat_fill_params(igl_join* j, FlatProbeParams& F, igl_dev_col* out, int64_t nrows) {
+    const int nl = (int)j->lt.size(), nr = (int)j->rt.size();
+    F.stage_bytes = flat_stage_bytes(j);
+    for (uint32_t c = 0, off = 0; c < (uint32_t)nl; ++c) { F.stage_off[c] = off; off += (uint32_t)kFlatChunk << (j->lt[c] == IGL_T_I32 ? 2 : 3); }
+    F.n_left = nl; F.n_right = nr; F.key_col = j->lkey; F.key_type = j->lt[j->lkey];
+    F.right_key_col = j->rkey; F.payload_col = j->payload_col; F.table = j->table; F.nrows = nrows;
+    for (int c = 0; c < nl; ++c) {
+        F.lshift[c] = j->lt[c] == IGL_T_I32 ? 2 : 3;
+        if (!out[c].data) return fail(IGL_ERR_INVALID_ARG, "output column %d has no data buffer", c);
+        F.out[c] = out[c].data;
+    }
+    for (int c = 0; c < nr; ++c) {
+        F.right_data[c] = (const uint8_t*)j->right[c].data; F.rshift[c] = j->rt[c] == IGL_T_I32 ? 2 : 3;
+        if (!out[nl + c].data) return fail(IGL_ERR_INVALID_ARG, "output column %d has no data buffer", nl + c);
+        F.out[nl + c] = out[nl + c].data;
+    }
+    return IGL_OK;
+}
+
+// Scratch, launch, row count and (dense form) hole filling of the flat probe.  `nrows` is the
+// virtual row count when `seg`.
+int32_t flat_probe_run(igl_join* j, FlatProbeParams& F, bool seg, int64_t nrows, int64_t out_capacity, int64_t* out_rows,
+                       cudaStream_t st) {
+    igl_ctx* ctx = j->ctx;
+    const int nl = F.n_left, nr = F.n_right;
+    // DENSE form (see the kernel): needs room for every probe row and 32-bit row numbers
+    const char* denv = getenv("IGL_JOIN_DENSE");
+    const bool dense = seg || (!(denv && denv[0] == '0') && out_capacity >= nrows && nrows < (1ll << 32));
+    if (seg && !(out_capacity >= nrows && nrows < (1ll << 32)))
+        return fail(IGL_ERR_INVALID_ARG, "segmented probe needs an output capacity of %lld rows (< 2^32)", (long long)nrows);
+    constexpr int kFixTile = 1024;   // rows per tile of the hole-filling pass
+    const long long ntiles = (nrows + kFixTile - 1) / kFixTile;
+    const size_t scan_bytes = (((size_t)scan_scratch_words(tile_offsets_scan_tiles(ntiles)) * 8) + 255) & ~(size_t)255;
+    const size_t off_bytes = (((size_t)(ntiles + 1) * 8) + 255) & ~(size_t)255;
+    const size_t bm_bytes = (size_t)ntiles * (kFixTile / 8) + 256;
+    // scratch: [header][offsets-kernel header][scan words][tile offsets][hit bitmap]
+    const size_t need = dense ? 512 + scan_bytes + off_bytes + bm_bytes : 256;
+    if (need > j->scratch_bytes) {
+        if (j->scratch) pool_free(ctx, j->scratch);
+        j->scratch = nullptr; j->scratch_bytes = 0;
+        IGL_TRY(pool_alloc(ctx, need, &j->scratch));
+        j->scratch_bytes = need;
+    }
+    uint8_t* sb = (uint8_t*)j->scratch;
+    IGL_CUDA_OK(cudaMemsetAsync(sb, 0, dense ? 512 + scan_bytes : 256, st));
+    if (dense) IGL_CUDA_OK(cudaMemsetAsync(sb + 512 + scan_bytes + off_bytes, 0, bm_bytes, st));
+    F.out_counter = &((PipeHeader*)j->scratch)->aux[1];
+    F.ticket = &((PipeHeader*)j->scratch)->ticket;
+    F.hit_words = dense ? (uint32_t*)(sb + 512 + scan_bytes + off_bytes) : nullptr;
+    F.miss_counter = &((PipeHeader*)j->scratch)->aux[2];
+    const long long nchunks = (nrows + kFlatChunk - 1) / kFlatChunk;
+    const void* kfn = flat_kernel_for(F.key_type, dense, seg);
+    const size_t fsmem = (size_t)F.stage_bytes * kFlatStages;
+    IGL_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
+    int per_sm = 0;
+    IGL_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, kFlatThreads, fsmem));
+    if (const char* e = getenv("IGL_FLAT_CTAS_PER_SM")) per_sm = std::min(per_sm, std::max(1, atoi(e)));   // experiments
+    const int grid = (int)std::min<long long>(nchunks, (long long)ctx->sm_count * std::max(per_sm, 1));
+    void* kargs[] = {&F};
+    cudaEventRecord(j->ev[4], st);
+    IGL_CUDA_OK(cudaLaunchKernel(kfn, dim3(grid), dim3(kFlatThreads), kargs, fsmem, st));
+    cudaEventRecord(j->ev[5], st);
+    j->ev_probe = true;
+    ctx->launches++;
+    IGL_CUDA_OK(cudaMemcpyAsync(j->host_hdr, j->scratch, sizeof(PipeHeader), cudaMemcpyDeviceToHost, st));
+    IGL_CUDA_OK(cudaStreamSynchronize(st));
+    if (dense) {
+        const int64_t misses = (int64_t)j->host_hdr->aux[2];
+        if (misses > 0 && misses < nrows) {   // fill the holes below the matched-row count from the tail
+            void* holes = nullptr;
+            IGL_TRY(pool_alloc(ctx, (size_t)misses * 4 + 256, &holes));
+            unsigned long long* tile_off = (unsigned long long*)(sb + 512 + scan_bytes);
+            cudaError_t e = launch_tile_offsets(F.hit_words, kFixTile, ntiles, tile_off, (PipeHeader*)sb,
+                                                &((PipeHeader*)(sb + 256))->ticket, (uint64_t*)(sb + 512), ctx->sm_count, st);
+            DenseFixParams X{};
+            X.hit_words = F.hit_words; X.tile_off = tile_off; X.tile_rows = kFixTile; X.nrows = nrows;
+            X.holes = (uint32_t*)holes; X.ncols = nl + nr;
+            for (int c = 0; c < nl + nr; ++c) { X.out[c] = F.out[c]; X.shift[c] = c < nl ? F.lshift[c] : F.rshift[c - nl]; }
+            const int fgrid = (int)std::min<long long>(((nrows + 31) / 32 + 7) / 8, (long long)ctx->sm_count * 8);
+            if (e == cudaSuccess) { dense_fix_kernel<false><<<fgrid, 256, 0, st>>>(X); e = cudaGetLastError(); }
+            if (e == cudaSuccess) { dense_fix_kernel<true><<<fgrid, 256, 0, st>>>(X); e = cudaGetLastError(); }
+            if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+            pool_free(ctx, holes);
+            if (e != cudaSuccess) return fail(IGL_ERR_CUDA, "probe hole filling failed: %s", cudaGetErrorString(e));
+            ctx->launches += 3;
+        }
+        if (out_rows) *out_rows = nrows - misses;
+        return IGL_OK;
+    }
+    if (out_rows) *out_rows = (int64_t)j->host_hdr->aux[1];
+    return IGL_OK;
+}
+
 }  // namespace
+
+namespace igl {
+
+bool join_segments_eligible(const igl_join* j) { return j && flat_eligible(j); }
+
+// The probe of a segmented probe side (kernels.h): this GPU's and its peers' staging buffers,
+// walked run by run.  The output is dense, `out_rows` rows; it needs S.nchunks * 128 rows of room.
+int32_t join_probe_segments(igl_join* j, const SegSource& S, igl_dev_col* out, int64_t out_capacity, int64_t* out_rows,
+                            cudaStream_t st) {
+    if (!j || !out || S.nsrc < 1 || S.nsrc > kSegMaxSrc) return fail(IGL_ERR_INVALID_ARG, "join_probe_segments: bad arguments");
+    if (!flat_eligible(j)) return fail(IGL_ERR_UNSUPPORTED, "join_probe_segments: this join takes the general probe");
+    DeviceGuard g(j->ctx->device);
+    cudaEventRecord(j->ev[3], st);
+    j->ev_probe = false;
+    if (S.nchunks == 0 || S.nsegs == 0) { if (out_rows) *out_rows = 0; return IGL_OK; }
+    FlatProbeParams F{};
+    const int nl = (int)j->lt.size();
+    for (int s = 0; s < S.nsrc; ++s)
+        for (int c = 0; c < nl; ++c) {
+            if ((uintptr_t)S.cols[s][c] & 15) return fail(IGL_ERR_INVALID_ARG, "segment source %d column %d is not 16-byte aligned", s, c);
+            F.seg_left[s][c] = S.cols[s][c];
+        }
+    F.segs = S.dev_segs; F.nsegs = S.nsegs;
+    IGL_TRY(flat_fill_params(j, F, out, S.nchunks * kFlatChunk));
+    return flat_probe_run(j, F, /*seg=*/true, S.nchunks * kFlatChunk, out_capacity, out_rows, st);
+}
+
+}  // namespace igl
 
 extern "C" {
 
@@ -1269,99 +1452,16 @@ int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_
     // ---- fast path: inner join, unique layout, no validity anywhere ----
     {
         const char* env = getenv("IGL_JOIN_FLAT");
-        bool flat = !(env && env[0] == '0') && !j->csr && !j->left_join && !j->never_match;
+        bool flat = !(env && env[0] == '0') && flat_eligible(j);
         for (int c = 0; c < nl && flat; ++c) if (left[c].validity || ((uintptr_t)left[c].data & 15)) flat = false;
-        for (int c = 0; c < nr && flat; ++c) if (j->right[c].validity) flat = false;
-        uint32_t flat_stage = 0;
-        for (int c = 0; c < nl; ++c) flat_stage += (uint32_t)kFlatChunk << (j->lt[c] == IGL_T_I32 ? 2 : 3);
-        if ((size_t)flat_stage * kFlatStages > (200u << 10)) flat = false;   // very wide probe rows take the tiled kernels
         if (flat) {
             FlatProbeParams F{};
-            F.stage_bytes = flat_stage;
-            for (uint32_t c = 0, off = 0; c < (uint32_t)nl; ++c) { F.stage_off[c] = off; off += (uint32_t)kFlatChunk << (j->lt[c] == IGL_T_I32 ? 2 : 3); }
-            F.n_left = nl; F.n_right = nr; F.key_col = j->lkey; F.key_type = j->lt[j->lkey];
-            F.right_key_col = j->rkey; F.payload_col = j->payload_col; F.table = j->table; F.nrows = nrows;
             for (int c = 0; c < nl; ++c) {
                 if (left[c].type != j->lt[c]) return fail(IGL_ERR_INVALID_ARG, "left column %d has type %d, join expects %d", c, left[c].type, j->lt[c]);
-                F.left[c] = (const uint8_t*)left[c].data; F.lshift[c] = j->lt[c] == IGL_T_I32 ? 2 : 3;
-                if (!out[c].data) return fail(IGL_ERR_INVALID_ARG, "output column %d has no data buffer", c);
-                F.out[c] = out[c].data;
+                F.left[c] = (const uint8_t*)left[c].data;
             }
-            for (int c = 0; c < nr; ++c) {
-                F.right_data[c] = (const uint8_t*)j->right[c].data; F.rshift[c] = j->rt[c] == IGL_T_I32 ? 2 : 3;
-                if (!out[nl + c].data) return fail(IGL_ERR_INVALID_ARG, "output column %d has no data buffer", nl + c);
-                F.out[nl + c] = out[nl + c].data;
-            }
-            // DENSE form (see the kernel): needs room for every probe row and 32-bit row numbers
-            const char* denv = getenv("IGL_JOIN_DENSE");
-            const bool dense = !(denv && denv[0] == '0') && out_capacity >= nrows && nrows < (1ll << 32);
-            constexpr int kFixTile = 1024;   // rows per tile of the hole-filling pass
-            const long long ntiles = (nrows + kFixTile - 1) / kFixTile;
-            const size_t scan_bytes = (((size_t)scan_scratch_words(tile_offsets_scan_tiles(ntiles)) * 8) + 255) & ~(size_t)255;
-            const size_t off_bytes = (((size_t)(ntiles + 1) * 8) + 255) & ~(size_t)255;
-            const size_t bm_bytes = (size_t)ntiles * (kFixTile / 8) + 256;
-            // scratch: [header][offsets-kernel header][scan words][tile offsets][hit bitmap]
-            const size_t need = dense ? 512 + scan_bytes + off_bytes + bm_bytes : 256;
-            if (need > j->scratch_bytes) {
-                if (j->scratch) pool_free(ctx, j->scratch);
-                j->scratch = nullptr; j->scratch_bytes = 0;
-                IGL_TRY(pool_alloc(ctx, need, &j->scratch));
-                j->scratch_bytes = need;
-            }
-            uint8_t* sb = (uint8_t*)j->scratch;
-            IGL_CUDA_OK(cudaMemsetAsync(sb, 0, dense ? 512 + scan_bytes : 256, st));
-            if (dense) IGL_CUDA_OK(cudaMemsetAsync(sb + 512 + scan_bytes + off_bytes, 0, bm_bytes, st));
-            F.out_counter = &((PipeHeader*)j->scratch)->aux[1];
-            F.ticket = &((PipeHeader*)j->scratch)->ticket;
-            F.hit_words = dense ? (uint32_t*)(sb + 512 + scan_bytes + off_bytes) : nullptr;
-            F.miss_counter = &((PipeHeader*)j->scratch)->aux[2];
-            const long long nchunks = (nrows + kFlatChunk - 1) / kFlatChunk;
-            const int kt = F.key_type;
-            const void* kfn = dense ? (kt == IGL_T_I32 ? (const void*)join_probe_flat_kernel<IGL_T_I32, true>
-                                       : kt == IGL_T_F64 ? (const void*)join_probe_flat_kernel<IGL_T_F64, true>
-                                                         : (const void*)join_probe_flat_kernel<IGL_T_I64, true>)
-                                    : (kt == IGL_T_I32 ? (const void*)join_probe_flat_kernel<IGL_T_I32, false>
-                                       : kt == IGL_T_F64 ? (const void*)join_probe_flat_kernel<IGL_T_F64, false>
-                                                         : (const void*)join_probe_flat_kernel<IGL_T_I64, false>);
-            const size_t fsmem = (size_t)F.stage_bytes * kFlatStages;
-            IGL_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
-            int per_sm = 0;
-            IGL_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, kFlatThreads, fsmem));
-            if (const char* e = getenv("IGL_FLAT_CTAS_PER_SM")) per_sm = std::min(per_sm, std::max(1, atoi(e)));   // experiments
-            const int grid = (int)std::min<long long>(nchunks, (long long)ctx->sm_count * std::max(per_sm, 1));
-            void* kargs[] = {&F};
-            cudaEventRecord(j->ev[4], st);
-            IGL_CUDA_OK(cudaLaunchKernel(kfn, dim3(grid), dim3(kFlatThreads), kargs, fsmem, st));
-            cudaEventRecord(j->ev[5], st);
-            j->ev_probe = true;
-            ctx->launches++;
-            IGL_CUDA_OK(cudaMemcpyAsync(j->host_hdr, j->scratch, sizeof(PipeHeader), cudaMemcpyDeviceToHost, st));
-            IGL_CUDA_OK(cudaStreamSynchronize(st));
-            if (dense) {
-                const int64_t misses = (int64_t)j->host_hdr->aux[2];
-                if (misses > 0 && misses < nrows) {   // fill the holes below the matched-row count from the tail
-                    void* holes = nullptr;
-                    IGL_TRY(pool_alloc(ctx, (size_t)misses * 4 + 256, &holes));
-                    unsigned long long* tile_off = (unsigned long long*)(sb + 512 + scan_bytes);
-                    cudaError_t e = launch_tile_offsets(F.hit_words, kFixTile, ntiles, tile_off, (PipeHeader*)sb,
-                                                        &((PipeHeader*)(sb + 256))->ticket, (uint64_t*)(sb + 512), ctx->sm_count, st);
-                    DenseFixParams X{};
-                    X.hit_words = F.hit_words; X.tile_off = tile_off; X.tile_rows = kFixTile; X.nrows = nrows;
-                    X.holes = (uint32_t*)holes; X.ncols = nl + nr;
-                    for (int c = 0; c < nl + nr; ++c) { X.out[c] = F.out[c]; X.shift[c] = c < nl ? F.lshift[c] : F.rshift[c - nl]; }
-                    const int fgrid = (int)std::min<long long>(((nrows + 31) / 32 + 7) / 8, (long long)ctx->sm_count * 8);
-                    if (e == cudaSuccess) { dense_fix_kernel<false><<<fgrid, 256, 0, st>>>(X); e = cudaGetLastError(); }
-                    if (e == cudaSuccess) { dense_fix_kernel<true><<<fgrid, 256, 0, st>>>(X); e = cudaGetLastError(); }
-                    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-                    pool_free(ctx, holes);
-                    if (e != cudaSuccess) return fail(IGL_ERR_CUDA, "probe hole filling failed: %s", cudaGetErrorString(e));
-                    ctx->launches += 3;
-                }
-                if (out_rows) *out_rows = nrows - misses;
-                return IGL_OK;
-            }
-            if (out_rows) *out_rows = (int64_t)j->host_hdr->aux[1];
-            return IGL_OK;
+            IGL_TRY(flat_fill_params(j, F, out, nrows));
+            return flat_probe_run(j, F, /*seg=*/false, nrows, out_capacity, out_rows, st);
         }
     }
     JoinProbeParams P{};

@@ -43,4 +43,35 @@ bool radix_partition_supported(const igl_dev_col* cols, int ncols);
 int32_t radix_partition(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int key_col, long long nrows, int log2_parts,
                         void* const* dst, void* scratch, cudaStream_t st);
 
+// (destination x partition) split without host synchronisation (partition.cu; driven by shuffle.cu)
+int32_t radix_histogram_async(igl_ctx* ctx, const igl_dev_col* key, long long nrows, int ndest, int log2_parts,
+                              unsigned long long* dev_hist, cudaStream_t st);
+int32_t radix_scatter_bins_async(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int key_col, long long nrows, int ndest,
+                                 int log2_parts, void* const* dst, const unsigned long long* dev_offsets,
+                                 unsigned long long* dev_cursor, cudaStream_t st);
+
+// ---- segmented probe input (join.cu; used by the multi-GPU join, shuffle.cu) ---------------------
+// The probe side as a list of contiguous runs that may live in different buffers — the staging
+// buffers of this and the peer GPUs.  Runs are walked in list order; each starts on a 128-row
+// boundary of the (virtual) output, so `chunk0` is its first 128-row chunk.
+constexpr int kSegMaxSrc = 8;
+constexpr int kSegChunkRows = 128;   // rows per chunk of the flat probe kernel (join.cu asserts it)
+constexpr int kSegAlignRows = 4;     // a run starts on a multiple of this many rows of its source: 16 bytes for 4-byte columns
+struct ProbeSeg {
+    uint32_t chunk0;    // first chunk of this run in the virtual chunk space (strictly increasing, run 0 starts at 0)
+    uint32_t rows;      // > 0
+    uint64_t row0_src;  // low 56 bits: first row inside the source's columns (a multiple of 4); top 8 bits: source index
+};
+struct SegSource {
+    const uint8_t* cols[kSegMaxSrc][16];   // [source][left column]
+    int nsrc;
+    const ProbeSeg* dev_segs;
+    int nsegs;
+    long long nchunks;                     // chunks in total; the output needs nchunks * 128 rows of capacity
+};
+// True when `j` (built) can take segmented input: inner join, unique build keys, no validity.
+bool join_segments_eligible(const igl_join* j);
+int32_t join_probe_segments(igl_join* j, const SegSource& S, igl_dev_col* out, int64_t out_capacity, int64_t* out_rows,
+                            cudaStream_t st);
+
 }  // namespace igl

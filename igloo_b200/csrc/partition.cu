@@ -534,6 +534,50 @@ int32_t radix_partition(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int ke
     return IGL_OK;
 }
 
+// ---- the two halves of a (destination x partition) split, stream-ordered and without any
+// host synchronisation (shuffle.cu drives them) --------------------------------------------
+// dev_hist[ndest << log2_parts] is zeroed and filled.
+int32_t radix_histogram_async(igl_ctx* ctx, const igl_dev_col* key, long long nrows, int ndest, int log2_parts,
+                              unsigned long long* dev_hist, cudaStream_t st) {
+    if (ndest < 1 || ndest > kPartMaxParts || log2_parts < 0 || (ndest << log2_parts) > kRadixMaxParts)
+        return fail(IGL_ERR_UNSUPPORTED, "ndest in [1, %d] and ndest << log2_parts <= %d", kPartMaxParts, kRadixMaxParts);
+    if (key->type != IGL_T_I32 && key->type != IGL_T_I64 && key->type != IGL_T_F64)
+        return fail(IGL_ERR_UNSUPPORTED, "partition key must be Int32/Int64/Float64");
+    if (key->validity) return fail(IGL_ERR_UNSUPPORTED, "nullable join keys are not repartitioned across GPUs");
+    IGL_CUDA_OK(cudaMemsetAsync(dev_hist, 0, sizeof(unsigned long long) * ((size_t)ndest << log2_parts), st));
+    if (nrows == 0) return IGL_OK;
+    radix_hist_kernel<<<ctx->sm_count * 4, 512, 0, st>>>(key->data, key->type, nrows, ndest, log2_parts, dev_hist);
+    IGL_CUDA_OK(cudaGetLastError());
+    ctx->launches++;
+    return IGL_OK;
+}
+
+// Rows of `cols` are written to dst[c] (one buffer per column, all bins inside it) at
+// dev_offsets[bin] + arrival order; dev_cursor[bins] must be zero.  Bins are destination-major.
+int32_t radix_scatter_bins_async(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int key_col, long long nrows, int ndest,
+                                 int log2_parts, void* const* dst, const unsigned long long* dev_offsets,
+                                 unsigned long long* dev_cursor, cudaStream_t st) {
+    if (ndest < 1 || ndest > kPartMaxParts || log2_parts < 0 || (ndest << log2_parts) > kRadixMaxParts)
+        return fail(IGL_ERR_UNSUPPORTED, "ndest in [1, %d] and ndest << log2_parts <= %d", kPartMaxParts, kRadixMaxParts);
+    if (ncols < 1 || ncols > kPartMaxCols || key_col < 0 || key_col >= ncols) return fail(IGL_ERR_INVALID_ARG, "radix_scatter_bins: bad column set");
+    if (!radix_partition_supported(cols, ncols)) return fail(IGL_ERR_UNSUPPORTED, "columns cannot be radix-partitioned (nullable, not fixed-width, or too wide)");
+    if (nrows == 0) return IGL_OK;
+    RadixParams P{};
+    P.ncols = ncols; P.key_col = key_col; P.key_type = cols[key_col].type; P.log2_parts = log2_parts; P.ndest = ndest; P.n = nrows;
+    P.offsets = dev_offsets; P.cursor = dev_cursor;
+    uint32_t off = 0;
+    for (int c = 0; c < ncols; ++c) {
+        P.src[c] = (const uint8_t*)cols[c].data;
+        P.shift[c] = cols[c].type == IGL_T_I32 ? 2 : 3;
+        P.stage_off[c] = off;
+        off += (uint32_t)kRadixTile << P.shift[c];
+        for (int d = 0; d < ndest; ++d) P.dst[d][c] = (uint8_t*)dst[c];
+    }
+    IGL_CUDA_OK(launch_radix_scatter(ctx, P, off, st));
+    ctx->launches++;
+    return IGL_OK;
+}
+
 }  // namespace igl
 
 using namespace igl;

@@ -257,6 +257,58 @@ int32_t igl_ipc_export(igl_ctx* ctx, void* dev_ptr, uint8_t handle_out[64]);
 int32_t igl_ipc_open(igl_ctx* ctx, const uint8_t handle[64], void** dev_ptr_out);
 int32_t igl_ipc_close(igl_ctx* ctx, void* dev_ptr);
 
+/* ---- the hash join across the GPUs of one node: one process per GPU, each
+ *      holding a row-range shard of both sides.  Stands in for the exchange the reference only
+ *      declares: FragmentType::Shuffle (crates/coordinator/src/fragment.rs:8-13), the join
+ *      fragment fed by scan fragments (crates/coordinator/src/distributed_planner.rs:65-92,
+ *      distributed_executor.rs:105-166), a worker process per executor
+ *      (crates/worker/src/main.rs:14-52).
+ *      igl_comm_unique_id / igl_comm_init: rank 0 makes an id, the host distributes it (the
+ *        coordinator's registration reply, coordinator.proto:60-69, is the natural carrier),
+ *        every rank joins; NCCL is resolved with dlopen (IGL_ERR_NCCL when absent or failing).
+ *      igl_join_shuffle_run: collective — every rank calls it with its shard.  Both sides are
+ *        radix-partitioned locally by (destination GPU, partition of the join hash); counts
+ *        and buffer handles travel in one ncclAllGather; the build rows a GPU owns are pulled
+ *        from its peers' staging buffers over NVLink and the table is built; the probe kernel
+ *        then reads its probe rows straight out of the peers' staging buffers, tile by tile,
+ *        while it probes (mode IGL_EXCHANGE_P2P), or both sides first travel by grouped
+ *        ncclSend/ncclRecv (IGL_EXCHANGE_NCCL, the all-to-all-v baseline).  Equal keys meet
+ *        on one GPU; the output stays sharded, in library-owned device columns that
+ *        igl_join_shuffle_output lends until the next run or the destroy.
+ *      Non-nullable Int32/Int64/Float64 columns of at most 46 bytes per row and side; column-
+ *      reference keys.  Key semantics and join types as igl_join_*. ------------------------- */
+enum igl_exchange_mode { IGL_EXCHANGE_P2P = 0, IGL_EXCHANGE_NCCL = 1 };
+int32_t igl_comm_unique_id(uint8_t id_out[128]);
+int32_t igl_comm_init(igl_ctx* ctx, int32_t nranks, int32_t rank, const uint8_t id[128]);
+int32_t igl_comm_rank(const igl_ctx* ctx, int32_t* rank, int32_t* nranks);
+typedef struct igl_join_shuffle igl_join_shuffle;
+int32_t igl_join_shuffle_create(igl_ctx* ctx, int32_t join_type,
+                                const int32_t* left_types, const uint8_t* left_nullable, int32_t n_left,
+                                const int32_t* right_types, const uint8_t* right_nullable, int32_t n_right,
+                                const igl_expr* left_key, const igl_expr* right_key, int32_t mode,
+                                igl_join_shuffle** out);
+int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int64_t n_right,
+                             const igl_dev_col* left, int64_t n_left, int64_t* out_rows, void* stream);
+int32_t igl_join_shuffle_output(igl_join_shuffle* js, igl_dev_col* out /* [n_left + n_right] */, int64_t* rows);
+/* Device time (ms) of the phases of the last run on this rank: [0] histograms + all-gather,
+ * [1] local partitioning, [2] barrier / NCCL exchange, [3] build-side pull + table build,
+ * [4] probe (fused with the probe-side transfer in p2p mode), [5] closing barrier, [6] total,
+ * [7] the probe kernel alone.  stats: [0] build rows received, [1] probe rows received,
+ * [2] bytes read from peer GPUs, [3] log2 of the partition count, [4] 1 = fused probe,
+ * [5] output rows. */
+int32_t igl_join_shuffle_phase_ms(igl_join_shuffle* js, double out[8]);
+int32_t igl_join_shuffle_stats(igl_join_shuffle* js, int64_t out[8]);
+void igl_join_shuffle_destroy(igl_join_shuffle* js);
+/* The exchange plan as pure host arithmetic (no GPU needed; igl_join_shuffle_run uses it).
+ * counts[nranks][bins], bins = nranks << log2_parts, destination-major: rows of each source per
+ * (destination, partition).  src_offsets[nranks][bins]: first row of every bin inside its
+ * source's staging buffer (bins start on multiples of 4 rows).  For `rank`, in the order its
+ * join walks them (partition by partition, source by source): seg_src / seg_row0 / seg_rows
+ * [(nranks << log2_parts) / nranks * nranks entries = parts * nranks], and their total. */
+int32_t igl_shuffle_plan(int32_t nranks, int32_t rank, int32_t log2_parts, const int64_t* counts,
+                         int64_t* src_offsets, int32_t* seg_src, int64_t* seg_row0, int64_t* seg_rows,
+                         int64_t* total_rows);
+
 /* ---- synthetic data + multiset digest (SURVEY.md §8d generator), device side */
 enum igl_gen_kind {
     IGL_GEN_I32_UNIFORM = 1, /* mulhi64(u, m)                                  */

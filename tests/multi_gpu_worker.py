@@ -11,7 +11,7 @@ import torch.distributed as dist
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from igloo_b200.device import Context  # noqa: E402
 from igloo_b200.expr import Field, T_I64  # noqa: E402
-from igloo_b200.shuffle import PartitionedJoin  # noqa: E402
+from igloo_b200.shuffle import PartitionedJoin, init_comm  # noqa: E402
 
 M64 = (1 << 64) - 1
 
@@ -30,6 +30,7 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     ctx = Context(local)
+    init_comm(ctx, rank, world)
     seed, bits, nprobe = 0x16100003, int(sys.argv[1]), int(sys.argv[2])
     nb = 1 << bits
     b0, b1 = nb * rank // world, nb * (rank + 1) // world
@@ -37,8 +38,7 @@ def main():
     rk = ctx.gen(4, 0, 0, b0, b1 - b0, bits=bits); rv = ctx.gen(2, seed, 1, b0, b1 - b0)
     lk = ctx.gen(2, seed, 2, p0, p1 - p0, m=nb); lw = ctx.gen(2, seed, 3, p0, p1 - p0)
     if len(sys.argv) > 3 and sys.argv[3] == "skew":
-        # 60 % of the probe rows carry one key: its destination GPU receives far more than the even
-        # share the slabs were sized for, so they must grow (on every rank) inside run()
+        # 60 % of the probe rows carry one key: its destination GPU reads far more than an even share
         hot = torch.rand(p1 - p0, device=f"cuda:{local}") < 0.6
         lk.data[: p1 - p0][hot] = 12345 % nb
     expect_v = ctx.gen(5, seed, 1, 0, p1 - p0, bits=bits, keys=lk)
@@ -55,8 +55,10 @@ def main():
             dist.all_reduce(tot)
             assert int(tot.item()) == nprobe, (mode, int(tot.item()), nprobe)
             assert got == want, (mode, got, want)
+        st = pj.stats()
         if rank == 0:
-            print(f"mode={mode} fused={pj.fused} log2_parts={pj.log2_parts} OK", flush=True)
+            print(f"mode={mode} fused={bool(st['fused_probe'])} log2_parts={st['log2_parts']} OK", flush=True)
+        pj.close()
     dist.barrier()
     dist.destroy_process_group()
 
