@@ -7,6 +7,8 @@
 #include "device_utils.cuh"
 #include "internal.h"
 
+#include <cmath>
+
 namespace igl {
 
 __device__ __forceinline__ uint64_t gen_u64(uint64_t seed, uint64_t col, uint64_t row) {
@@ -40,13 +42,67 @@ __device__ __forceinline__ uint64_t perm_pow2_inv(uint64_t x, int bits, uint64_t
     return x;
 }
 
+// C4: lineitem row -> index of its order, 1-7 lines per order, addressable by
+// row.  Orders come in blocks of 7 whose line counts are a permutation of 1..7 picked by the
+// block's hash (28 lines per block, 4 per order on average); rows past the last whole block go
+// round-robin to the remaining orders and then wrap from order 0.
+__device__ __forceinline__ uint64_t line_order_index(uint64_t seed, uint64_t col, uint64_t row, uint64_t n_orders) {
+    const uint64_t nblocks = n_orders / 7;
+    const uint64_t blk = row / 28;
+    if (blk >= nblocks) return (7 * nblocks + (row - 28 * nblocks)) % n_orders;
+    const uint64_t u = gen_u64(seed, col, blk);
+    const uint32_t r = (uint32_t)(u % 7), mul = 1 + (uint32_t)((u >> 8) % 6);   // t -> (t * mul + r) mod 7 permutes 0..6
+    uint32_t q = (uint32_t)(row - blk * 28), t = 0;
+    for (; t < 6; ++t) {
+        const uint32_t c = 1 + (t * mul + r) % 7;
+        if (q < c) break;
+        q -= c;
+    }
+    return blk * 7 + t;
+}
+
+// C5: Zipf(1.1) rank in [1, m] by inverse CDF.  H(k) = sum_{i<=k} i^-s is
+// tabulated exactly for k <= kZipfHead and continued by the midpoint rule
+// H(k) = H(K) + ((K + .5)^(1-s) - (k + .5)^(1-s)) / (s - 1) (relative error < 1e-8 here).
+constexpr int kZipfHead = 1024;
+constexpr double kZipfS = 1.1;
+struct ZipfParams { const double* head; double h_total, tail_base; };   // head[k-1] = H(k); tail_base = (K + .5)^(1-s)
+__device__ __forceinline__ uint64_t zipf_rank(double u01, uint64_t m, const ZipfParams& Z) {
+    const double t = u01 * Z.h_total;
+    const int K = (int)min((uint64_t)kZipfHead, m);
+    if (t < Z.head[K - 1]) {   // first k with H(k) > t
+        int lo = 0, hi = K - 1;
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (Z.head[mid] > t) hi = mid; else lo = mid + 1; }
+        return (uint64_t)lo + 1;
+    }
+    const double y = Z.tail_base - (t - Z.head[K - 1]) * (kZipfS - 1.0);
+    double k = floor(pow(y, 1.0 / (1.0 - kZipfS)) + 0.5);
+    if (!(k >= (double)(K + 1))) k = (double)(K + 1);
+    if (k > (double)m) k = (double)m;
+    return (uint64_t)k;
+}
+
 __global__ void gen_kernel(int kind, uint64_t seed, uint64_t col, long long row0, long long n, uint64_t m, int bits,
                            const long long* __restrict__ keys, void* __restrict__ out, uint64_t i1, uint64_t i2,
-                           uint64_t i3) {
+                           uint64_t i3, ZipfParams Z) {
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const uint64_t row = (uint64_t)(row0 + i);
+        // kinds 1-3 and 6 take their row number from keys[i] when keys are given ("the value the
+        // generator gives row keys[i]": expected join payloads without a hash table)
+        const uint64_t row = (keys && kind != IGL_GEN_I64_LOOKUP) ? (uint64_t)keys[i] : (uint64_t)(row0 + i);
         switch (kind) {
+            case IGL_GEN_I64_TPCH_ORDERKEY:
+                ((int64_t*)out)[i] = (int64_t)((((row >> 3) << 5) | (row & 7)) + 1);
+                break;
+            case IGL_GEN_I64_LINE_ORDER:
+                ((int64_t*)out)[i] = (int64_t)line_order_index(seed, col, row, m);
+                break;
+            case IGL_GEN_I64_ZIPF: {
+                const double u01 = (double)(gen_u64(seed, col, row) >> 11) * 0x1.0p-53;
+                const uint64_t r = zipf_rank(u01, m, Z) - 1;
+                ((int64_t*)out)[i] = (int64_t)(bits > 0 ? perm_pow2(r, bits) : r);
+                break;
+            }
             case IGL_GEN_I32_UNIFORM:
                 ((int32_t*)out)[i] = (int32_t)__umul64hi(gen_u64(seed, col, row), m);
                 break;
@@ -118,17 +174,38 @@ extern "C" {
 int32_t igl_gen_column(igl_ctx* ctx, int32_t kind, uint64_t seed, uint64_t col_id, int64_t row0, int64_t n,
                        uint64_t m, int32_t bits, const int64_t* dev_keys, void* dev_out, void* stream) {
     if (!ctx || !dev_out || n < 0) return fail(IGL_ERR_INVALID_ARG, "igl_gen_column: bad arguments");
-    if (kind < IGL_GEN_I32_UNIFORM || kind > IGL_GEN_I64_LOOKUP) return fail(IGL_ERR_INVALID_ARG, "igl_gen_column: unknown kind %d", kind);
+    if (kind < IGL_GEN_I32_UNIFORM || kind > IGL_GEN_I64_ZIPF) return fail(IGL_ERR_INVALID_ARG, "igl_gen_column: unknown kind %d", kind);
     if ((kind == IGL_GEN_I64_PERM || kind == IGL_GEN_I64_LOOKUP) && (bits < 2 || bits > 62))
         return fail(IGL_ERR_INVALID_ARG, "igl_gen_column: bits must be in [2, 62]");
     if (kind == IGL_GEN_I64_LOOKUP && !dev_keys) return fail(IGL_ERR_INVALID_ARG, "igl_gen_column: LOOKUP needs keys");
+    if (kind == IGL_GEN_I64_LINE_ORDER && m < 1) return fail(IGL_ERR_INVALID_ARG, "igl_gen_column: LINE_ORDER needs the order count in m");
+    if (kind == IGL_GEN_I64_ZIPF && (m < 1 || bits < 0 || bits > 62 || (bits > 0 && m > (1ull << bits))))
+        return fail(IGL_ERR_INVALID_ARG, "igl_gen_column: ZIPF needs a domain size m >= 1 (and m <= 2^bits when permuted)");
     if (n == 0) return IGL_OK;
     DeviceGuard g(ctx->device);
+    cudaStream_t st = pick_stream(ctx, stream);
+    ZipfParams Z{};
+    void* head = nullptr;
+    if (kind == IGL_GEN_I64_ZIPF) {
+        std::vector<double> h(kZipfHead);
+        double acc = 0;
+        for (int k = 1; k <= kZipfHead; ++k) { acc += pow((double)k, -kZipfS); h[k - 1] = acc; }
+        const int K = (int)std::min<uint64_t>(kZipfHead, m);
+        Z.tail_base = pow((double)K + 0.5, 1.0 - kZipfS);
+        Z.h_total = m <= (uint64_t)kZipfHead ? h[m - 1] : h[K - 1] + (Z.tail_base - pow((double)m + 0.5, 1.0 - kZipfS)) / (kZipfS - 1.0);
+        IGL_TRY(pool_alloc(ctx, sizeof(double) * kZipfHead, &head));
+        cudaError_t e = cudaMemcpyAsync(head, h.data(), sizeof(double) * kZipfHead, cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);   // `h` is pageable and goes out of scope
+        if (e != cudaSuccess) { pool_free(ctx, head); return fail(IGL_ERR_CUDA, "igl_gen_column: %s", cudaGetErrorString(e)); }
+        Z.head = (const double*)head;
+    }
     int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
-    gen_kernel<<<grid, 256, 0, pick_stream(ctx, stream)>>>(kind, seed, col_id, row0, n, m, bits, (const long long*)dev_keys,
-                                                           dev_out, inv_odd(0x9E3779B97F4A7C15ull),
-                                                           inv_odd(0xBF58476D1CE4E5B9ull), inv_odd(0x94D049BB133111EBull));
-    IGL_CUDA_OK(cudaGetLastError());
+    gen_kernel<<<grid, 256, 0, st>>>(kind, seed, col_id, row0, n, m, bits, (const long long*)dev_keys,
+                                     dev_out, inv_odd(0x9E3779B97F4A7C15ull),
+                                     inv_odd(0xBF58476D1CE4E5B9ull), inv_odd(0x94D049BB133111EBull), Z);
+    cudaError_t le = cudaGetLastError();
+    if (head) { if (le == cudaSuccess) le = cudaStreamSynchronize(st); pool_free(ctx, head); }
+    if (le != cudaSuccess) return fail(IGL_ERR_CUDA, "igl_gen_column: %s", cudaGetErrorString(le));
     ctx->launches++;
     return IGL_OK;
 }

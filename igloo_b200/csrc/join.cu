@@ -673,9 +673,10 @@ struct FlatProbeParams {
     unsigned long long* miss_counter;
     // SEG form (multi-GPU join): the probe rows are a list of runs spread over several source
     // buffers — this GPU's staging buffer and the peers', read over NVLink by the same bulk
-    // copies.  `nrows` is then the virtual row count (128 per chunk, runs padded to whole chunks).
+    // copies.  `nrows` is the total over all runs.
     const ProbeSeg* segs;
     int nsegs;
+    long long seg_nchunks;
     const uint8_t* seg_left[kSegMaxSrc][kJoinMaxCols];
 };
 
@@ -709,12 +710,13 @@ __global__ void __launch_bounds__(kFlatThreads, IGL_FLAT_CTAS) join_probe_flat_k
     __shared__ uint64_t s_full[kFlatStages];
     __shared__ long long s_chunk_of[kFlatStages];
     __shared__ int s_rows_of[kFlatStages];   // SEG: rows of the chunk held by each stage
+    __shared__ unsigned long long s_obase[kFlatStages];   // SEG: output row of the chunk's first row
     __shared__ unsigned int s_wcnt[kFlatThreads / 32];
     __shared__ unsigned long long s_base;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint64_t bmask = P.table.mask >> 1;
-    const long long nchunks = (P.nrows + kFlatChunk - 1) / kFlatChunk;
+    const long long nchunks = SEG ? P.seg_nchunks : (P.nrows + kFlatChunk - 1) / kFlatChunk;
     const Slot* slots = P.table.slots;
     const int tshift = P.table.shift + 1;   // slot index -> bucket index
     const int lrow = warp * (32 * kFlatRows) + lane;   // this lane's first row inside a chunk
@@ -743,6 +745,7 @@ __global__ void __launch_bounds__(kFlatThreads, IGL_FLAT_CTAS) join_probe_flat_k
             const int src = (int)(rs >> 56);
             const size_t srow = (size_t)(rs & 0x00FFFFFFFFFFFFFFull) + done;
             s_rows_of[s] = (int)rows;
+            s_obase[s] = __ldg(&P.segs[cur_seg].out0) + done;
             uint32_t total = 0;
             for (int c = 0; c < P.n_left; ++c) total += ((rows << P.lshift[c]) + 15u) & ~15u;
             mbar_arrive_expect_tx(&s_full[s], total);
@@ -861,15 +864,33 @@ __global__ void __launch_bounds__(kFlatThreads, IGL_FLAT_CTAS) join_probe_flat_k
             uint32_t mine = 0;   // the ballots are the bitmap words of this warp's rows
 #pragma unroll
             for (int r = 0; r < kFlatRows; ++r) {
-                // SEG: the padding behind a run's last row is a hole like any unmatched row
-                misses += (SEG ? 32 : __popc(__ballot_sync(0xffffffffu, (live >> r) & 1u))) - __popc(hb[r]);
+                misses += __popc(__ballot_sync(0xffffffffu, (live >> r) & 1u)) - __popc(hb[r]);
                 mine = lane == r ? hb[r] : mine;
                 p[r] = (unsigned int)(lrow + r * 32);
             }
-            if (lane < kFlatRows) P.hit_words[(cbase >> 5) + warp * kFlatRows + lane] = mine;
+            if (SEG) {
+                // Runs are packed in the output, so a chunk starts at any row: its four ballot words
+                // land on five bitmap words.  Words wholly inside a full chunk are stored; the two
+                // edge words (and every word of a run's short last chunk) are shared with the
+                // neighbouring chunks and OR-ed in (the bitmap starts zeroed).
+                static_assert(!SEG || kFlatThreads == 32, "one warp per CTA");
+                obase = s_obase[sidx];
+                const uint32_t sh = (uint32_t)obase & 31u;
+                uint32_t prev = 0;   // hb[lane - 1]
+#pragma unroll
+                for (int r = 0; r < kFlatRows; ++r) prev = lane == r + 1 ? hb[r] : prev;
+                const uint32_t word = (lane < kFlatRows ? mine << sh : 0u) | ((sh && lane >= 1 && lane <= kFlatRows) ? prev >> (32u - sh) : 0u);
+                if (lane <= kFlatRows && word) {
+                    uint32_t* wp = P.hit_words + (obase >> 5) + lane;
+                    const bool own = nvalid == kFlatChunk && (sh == 0 ? lane < kFlatRows : (lane >= 1 && lane < kFlatRows));
+                    if (own) *wp = word; else atomicOr(wp, word);
+                }
+            } else {
+                if (lane < kFlatRows) P.hit_words[(cbase >> 5) + warp * kFlatRows + lane] = mine;
+                obase = (unsigned long long)cbase;
+            }
             __syncthreads();   // every thread is done with the previous chunk's stage
             if (threadIdx.x == 0 && it > 0) refill((it - 1) % kFlatStages);
-            obase = (unsigned long long)cbase;
         } else {
             if (lane == 0) s_wcnt[warp] = wcnt;
             __syncthreads();   // every thread is also done with the previous chunk's stage
@@ -1117,10 +1138,9 @@ int32_t flat_fill_params(igl_join* j, FlatProbeParams& F, igl_dev_col* out, int6
     return IGL_OK;
 }
 
-// Scratch, launch, row count and (dense form) hole filling of the flat probe.  `nrows` is the
-// virtual row count when `seg`.
-int32_t flat_probe_run(igl_join* j, FlatProbeParams& F, bool seg, int64_t nrows, int64_t out_capacity, int64_t* out_rows,
-                       cudaStream_t st) {
+// Scratch, launch, row count and (dense form) hole filling of the flat probe.
+int32_t flat_probe_run(igl_join* j, FlatProbeParams& F, bool seg, int64_t nrows, long long nchunks, int64_t out_capacity,
+                       int64_t* out_rows, cudaStream_t st) {
     igl_ctx* ctx = j->ctx;
     const int nl = F.n_left, nr = F.n_right;
     // DENSE form (see the kernel): needs room for every probe row and 32-bit row numbers
@@ -1148,7 +1168,6 @@ int32_t flat_probe_run(igl_join* j, FlatProbeParams& F, bool seg, int64_t nrows,
     F.ticket = &((PipeHeader*)j->scratch)->ticket;
     F.hit_words = dense ? (uint32_t*)(sb + 512 + scan_bytes + off_bytes) : nullptr;
     F.miss_counter = &((PipeHeader*)j->scratch)->aux[2];
-    const long long nchunks = (nrows + kFlatChunk - 1) / kFlatChunk;
     const void* kfn = flat_kernel_for(F.key_type, dense, seg);
     const size_t fsmem = (size_t)F.stage_bytes * kFlatStages;
     IGL_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
@@ -1198,7 +1217,7 @@ namespace igl {
 bool join_segments_eligible(const igl_join* j) { return j && flat_eligible(j); }
 
 // The probe of a segmented probe side (kernels.h): this GPU's and its peers' staging buffers,
-// walked run by run.  The output is dense, `out_rows` rows; it needs S.nchunks * 128 rows of room.
+// walked run by run.  The output is dense, `out_rows` rows; it needs S.total_rows rows of room.
 int32_t join_probe_segments(igl_join* j, const SegSource& S, igl_dev_col* out, int64_t out_capacity, int64_t* out_rows,
                             cudaStream_t st) {
     if (!j || !out || S.nsrc < 1 || S.nsrc > kSegMaxSrc) return fail(IGL_ERR_INVALID_ARG, "join_probe_segments: bad arguments");
@@ -1214,9 +1233,9 @@ int32_t join_probe_segments(igl_join* j, const SegSource& S, igl_dev_col* out, i
             if ((uintptr_t)S.cols[s][c] & 15) return fail(IGL_ERR_INVALID_ARG, "segment source %d column %d is not 16-byte aligned", s, c);
             F.seg_left[s][c] = S.cols[s][c];
         }
-    F.segs = S.dev_segs; F.nsegs = S.nsegs;
-    IGL_TRY(flat_fill_params(j, F, out, S.nchunks * kFlatChunk));
-    return flat_probe_run(j, F, /*seg=*/true, S.nchunks * kFlatChunk, out_capacity, out_rows, st);
+    F.segs = S.dev_segs; F.nsegs = S.nsegs; F.seg_nchunks = S.nchunks;
+    IGL_TRY(flat_fill_params(j, F, out, S.total_rows));
+    return flat_probe_run(j, F, /*seg=*/true, S.total_rows, S.nchunks, out_capacity, out_rows, st);
 }
 
 }  // namespace igl
@@ -1461,7 +1480,7 @@ int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_
                 F.left[c] = (const uint8_t*)left[c].data;
             }
             IGL_TRY(flat_fill_params(j, F, out, nrows));
-            return flat_probe_run(j, F, /*seg=*/false, nrows, out_capacity, out_rows, st);
+            return flat_probe_run(j, F, /*seg=*/false, nrows, (nrows + kFlatChunk - 1) / kFlatChunk, out_capacity, out_rows, st);
         }
     }
     JoinProbeParams P{};

@@ -58,16 +58,19 @@ constexpr int kSegMaxSrc = 8;
 constexpr int kSegChunkRows = 128;   // rows per chunk of the flat probe kernel (join.cu asserts it)
 constexpr int kSegAlignRows = 4;     // a run starts on a multiple of this many rows of its source: 16 bytes for 4-byte columns
 struct ProbeSeg {
-    uint32_t chunk0;    // first chunk of this run in the virtual chunk space (strictly increasing, run 0 starts at 0)
+    uint32_t chunk0;    // first chunk of this run in the chunk space (strictly increasing, run 0 starts at 0)
     uint32_t rows;      // > 0
     uint64_t row0_src;  // low 56 bits: first row inside the source's columns (a multiple of 4); top 8 bits: source index
+    uint64_t out0;      // rows of all earlier runs: where this run's rows go in the (dense) output
+    uint64_t pad;
 };
 struct SegSource {
     const uint8_t* cols[kSegMaxSrc][16];   // [source][left column]
     int nsrc;
     const ProbeSeg* dev_segs;
     int nsegs;
-    long long nchunks;                     // chunks in total; the output needs nchunks * 128 rows of capacity
+    long long nchunks;                     // chunks in total (every run rounded up to whole chunks)
+    long long total_rows;                  // rows in total: the output capacity needed
 };
 // True when `j` (built) can take segmented input: inner join, unique build keys, no validity.
 bool join_segments_eligible(const igl_join* j);

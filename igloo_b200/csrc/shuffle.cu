@@ -271,6 +271,8 @@ struct igl_join_shuffle {
     int64_t out_cap = 0;
     int64_t out_rows = 0;
     cudaEvent_t ev[7] = {};
+    cudaEvent_t ev_plan = nullptr, ev_wait = nullptr, ev_l[3] = {};   // second stream: probe-side partition start / end / barrier end
+    cudaStream_t stream2 = nullptr;
     bool timed = false;
     int64_t stats[8] = {};
     int log2_parts = 0;
@@ -378,6 +380,9 @@ int32_t igl_join_shuffle_create(igl_ctx* ctx, int32_t join_type, const int32_t* 
     if (rc >= 0) { rc = pool_alloc(ctx, 256, &p); js->d_flag = (int*)p; }
     if (rc >= 0 && cudaMemset(js->d_flag, 0, 256) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "cudaMemset failed");
     for (auto& ev : js->ev) if (rc >= 0 && cudaEventCreate(&ev) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "cudaEventCreate failed");
+    for (auto& ev : js->ev_l) if (rc >= 0 && cudaEventCreate(&ev) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "cudaEventCreate failed");
+    if (rc >= 0 && (cudaEventCreate(&js->ev_plan) != cudaSuccess || cudaEventCreate(&js->ev_wait) != cudaSuccess)) rc = fail(IGL_ERR_CUDA, "cudaEventCreate failed");
+    if (rc >= 0 && cudaStreamCreateWithFlags(&js->stream2, cudaStreamNonBlocking) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "cudaStreamCreate failed");
     if (rc < 0) { igl_join_shuffle_destroy(js.release()); return rc; }
     *out = js.release();
     return IGL_OK;
@@ -461,10 +466,20 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
         for (int b = 0; b < bins; ++b) js->h_plan[(size_t)sd * kMsgBins + b] = (unsigned long long)offs[((size_t)sd * W + me) * bins + b];
     IGL_CUDA_OK(cudaMemcpyAsync(js->d_plan, js->h_plan, sizeof(unsigned long long) * 2 * kMsgBins, cudaMemcpyHostToDevice, st));
     IGL_CUDA_OK(cudaMemsetAsync(js->d_plan + 2 * kMsgBins, 0, sizeof(unsigned long long) * 2 * kMsgBins, st));
-    // ---- 3. local radix partition of both sides into the staging buffers
+    // ---- 3. local radix partition of both sides into the staging buffers.  p2p mode: the probe side
+    // (the long one) is partitioned on a second stream, so it overlaps the build side's barrier,
+    // pull and table build; the probe kernel waits for it (and for every peer's) below.
+    const bool overlap = js->mode == IGL_EXCHANGE_P2P && !(getenv("IGL_SHUFFLE_OVERLAP") && getenv("IGL_SHUFFLE_OVERLAP")[0] == '0');
+    cudaStream_t st_l = overlap ? js->stream2 : st;
+    if (overlap) {
+        cudaEventRecord(js->ev_plan, st);
+        IGL_CUDA_OK(cudaStreamWaitEvent(st_l, js->ev_plan, 0));
+        cudaEventRecord(js->ev_l[0], st_l);
+    }
     for (int sd = 0; sd < 2; ++sd)
         IGL_TRY(radix_scatter_bins_async(ctx, in[sd], js->side[sd].ncols, js->side[sd].key, n_in[sd], W, lp, js->side[sd].staging.data(),
-                                         js->d_plan + (size_t)sd * kMsgBins, js->d_plan + (size_t)(2 + sd) * kMsgBins, st));
+                                         js->d_plan + (size_t)sd * kMsgBins, js->d_plan + (size_t)(2 + sd) * kMsgBins, sd == 1 ? st_l : st));
+    if (overlap) cudaEventRecord(js->ev_l[1], st_l);
     cudaEventRecord(js->ev[2], st);
     // ---- where the runs are read from
     const uint8_t* src_cols[2][kSegMaxSrc][16] = {};
@@ -487,8 +502,13 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
                 for (int c = 0; c < S.ncols; ++c) src_cols[sd][s][c] = (const uint8_t*)P.ptrs[c];
             }
         }
-        // ---- 4. every rank's staging is complete
+        // ---- 4. every rank's staging is complete: the build side's (on this stream) first, then the
+        // probe side's (on its own stream when overlapped) — the same order on every rank
         IGL_NCCL_OK(g_nccl.AllReduce(js->d_flag, js->d_flag, 1, kNcclInt32, kNcclSum, comm->comm, st));
+        if (overlap) {
+            IGL_NCCL_OK(g_nccl.AllReduce(js->d_flag + 8, js->d_flag + 8, 1, kNcclInt32, kNcclSum, comm->comm, st_l));
+            cudaEventRecord(js->ev_l[2], st_l);
+        }
     } else {
         // grouped send/recv of each destination's contiguous staging range (padding included)
         for (int sd = 0; sd < 2; ++sd) {
@@ -555,6 +575,7 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
                 ProbeSeg& ps = h_probe[nprobe++];
                 ps.chunk0 = (uint32_t)probe_chunks; ps.rows = (uint32_t)rows;
                 ps.row0_src = (uint64_t)row0 | ((uint64_t)s << 56);
+                ps.out0 = cs.dst_row0; ps.pad = 0;
                 probe_chunks += (rows + kSegChunkRows - 1) / kSegChunkRows;
             }
         }
@@ -573,6 +594,8 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
     IGL_TRY(igl_join_build(js->join, rcols.data(), recv_total[0], st));
     cudaEventRecord(js->ev[4], st);
     // ---- 6. probe side
+    if (overlap) IGL_CUDA_OK(cudaStreamWaitEvent(st, js->ev_l[2], 0));
+    cudaEventRecord(js->ev_wait, st);
     const int ncols_out = L.ncols + R.ncols;
     auto ensure_out = [&](int64_t rows) -> int32_t {
         if (rows <= js->out_cap && !js->out.empty()) return IGL_OK;
@@ -599,8 +622,8 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
     if (seg_probe_possible && !(segenv && segenv[0] == '0') && join_segments_eligible(js->join)) {
         SegSource SS{};
         for (int s = 0; s < W; ++s) for (int c = 0; c < L.ncols; ++c) SS.cols[s][c] = src_cols[1][s][c];
-        SS.nsrc = W; SS.dev_segs = d_probe; SS.nsegs = nprobe; SS.nchunks = probe_chunks;
-        IGL_TRY(ensure_out(probe_chunks * kSegChunkRows));
+        SS.nsrc = W; SS.dev_segs = d_probe; SS.nsegs = nprobe; SS.nchunks = probe_chunks; SS.total_rows = recv_total[1];
+        IGL_TRY(ensure_out(std::max<int64_t>(recv_total[1], 1)));
         out_cols(oc);
         IGL_TRY(join_probe_segments(js->join, SS, oc.data(), js->out_cap, &n_out, st));
         js->stats[4] = 1;
@@ -626,6 +649,12 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
     js->out_rows = n_out;
     js->stats[0] = recv_total[0]; js->stats[1] = recv_total[1]; js->stats[2] = remote_bytes; js->stats[3] = lp;
     js->stats[5] = n_out;
+    js->stats[6] = js->stats[7] = -1;   // probe-side partitioning on the second stream (us), and how long the probe waited for it (us)
+    if (overlap) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, js->ev_l[0], js->ev_l[1]) == cudaSuccess) js->stats[6] = (int64_t)(ms * 1e3);
+        if (cudaEventElapsedTime(&ms, js->ev[4], js->ev_wait) == cudaSuccess) js->stats[7] = (int64_t)(ms * 1e3);
+    }
     if (out_rows) *out_rows = n_out;
     return IGL_OK;
 }
@@ -649,6 +678,7 @@ int32_t igl_join_shuffle_phase_ms(igl_join_shuffle* js, double out[8]) {
     float ms = 0.f;
     for (int i = 0; i < 6; ++i)
         if (cudaEventElapsedTime(&ms, js->ev[i], js->ev[i + 1]) == cudaSuccess) out[i] = ms;
+    if (cudaEventElapsedTime(&ms, js->ev_wait, js->ev[5]) == cudaSuccess) out[4] = ms;   // probe, without the wait for the probe side's partitioning
     if (cudaEventElapsedTime(&ms, js->ev[0], js->ev[6]) == cudaSuccess) out[6] = ms;
     double jp[4];
     if (igl_join_phase_ms(js->join, jp) == IGL_OK) out[7] = jp[3];   // the probe kernel alone
@@ -684,6 +714,10 @@ void igl_join_shuffle_destroy(igl_join_shuffle* js) {
     if (js->h_plan) cudaFreeHost(js->h_plan);
     if (js->h_segs) cudaFreeHost(js->h_segs);
     for (auto& ev : js->ev) if (ev) cudaEventDestroy(ev);
+    for (auto& ev : js->ev_l) if (ev) cudaEventDestroy(ev);
+    if (js->ev_plan) cudaEventDestroy(js->ev_plan);
+    if (js->ev_wait) cudaEventDestroy(js->ev_wait);
+    if (js->stream2) cudaStreamDestroy(js->stream2);
     igl_join_destroy(js->join);
     delete js;
 }

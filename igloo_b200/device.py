@@ -65,7 +65,7 @@ class Context:
     def gen(self, kind: int, seed: int, col_id: int, row0: int, n: int, m: int = 0, bits: int = 0,
             keys: Optional["DeviceColumn"] = None) -> "DeviceColumn":
         torch = _torch()
-        t = {1: T_I32, 2: T_I64, 3: T_F64, 4: T_I64, 5: T_I64}[kind]
+        t = {1: T_I32, 2: T_I64, 3: T_F64}.get(kind, T_I64)   # igl_gen_kind: 4-8 are Int64 generators
         out = DeviceColumn.empty(t, n, self.device)
         check(lib.igl_gen_column(self._h, kind, seed, col_id, row0, n, m, bits,
                                  keys.data.data_ptr() if keys is not None else None,

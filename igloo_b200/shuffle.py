@@ -25,7 +25,8 @@ from .expr import Field, col
 EXCHANGE_P2P, EXCHANGE_NCCL = 0, 1
 _MODES = {"p2p": EXCHANGE_P2P, "nccl": EXCHANGE_NCCL}
 PHASES = ("counts", "partition", "exchange", "build", "probe", "closing_barrier", "total", "probe_kernel")
-STATS = ("build_rows_received", "probe_rows_received", "bytes_read_from_peers", "log2_parts", "fused_probe", "output_rows")
+STATS = ("build_rows_received", "probe_rows_received", "bytes_read_from_peers", "log2_parts", "fused_probe", "output_rows",
+         "probe_partition_us", "probe_wait_us")
 
 
 def init_comm(ctx, rank: int, world: int, broadcast=None) -> None:

@@ -291,11 +291,13 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
                              const igl_dev_col* left, int64_t n_left, int64_t* out_rows, void* stream);
 int32_t igl_join_shuffle_output(igl_join_shuffle* js, igl_dev_col* out /* [n_left + n_right] */, int64_t* rows);
 /* Device time (ms) of the phases of the last run on this rank: [0] histograms + all-gather,
- * [1] local partitioning, [2] barrier / NCCL exchange, [3] build-side pull + table build,
- * [4] probe (fused with the probe-side transfer in p2p mode), [5] closing barrier, [6] total,
- * [7] the probe kernel alone.  stats: [0] build rows received, [1] probe rows received,
- * [2] bytes read from peer GPUs, [3] log2 of the partition count, [4] 1 = fused probe,
- * [5] output rows. */
+ * [1] local partitioning on the call's stream (p2p: the build side only — the probe side is
+ * partitioned on a second stream under [2] and [3]), [2] barrier / NCCL exchange, [3] build-side
+ * pull + table build, [4] probe (fused with the probe-side transfer in p2p mode), [5] closing
+ * barrier, [6] total, [7] the probe kernel alone.  stats: [0] build rows received, [1] probe rows
+ * received, [2] bytes read from peer GPUs, [3] log2 of the partition count, [4] 1 = fused probe,
+ * [5] output rows, [6] probe-side partitioning on the second stream (us, -1 = not overlapped),
+ * [7] time the probe waited for it after the build (us). */
 int32_t igl_join_shuffle_phase_ms(igl_join_shuffle* js, double out[8]);
 int32_t igl_join_shuffle_stats(igl_join_shuffle* js, int64_t out[8]);
 void igl_join_shuffle_destroy(igl_join_shuffle* js);
@@ -315,9 +317,17 @@ enum igl_gen_kind {
     IGL_GEN_I64_UNIFORM = 2, /* mulhi64(u, m); m == 0 => raw u                 */
     IGL_GEN_F64_UNIT = 3,    /* (u >> 11) * 2^-53                              */
     IGL_GEN_I64_PERM = 4,    /* bijection of row index on [0, 2^bits)          */
-    IGL_GEN_I64_LOOKUP = 5   /* u(seed, col, perm^-1(key[i])): the generated
+    IGL_GEN_I64_LOOKUP = 5,  /* u(seed, col, perm^-1(key[i])): the generated
                                 value of the build row holding key[i]          */
+    IGL_GEN_I64_TPCH_ORDERKEY = 6, /* C4: ((row >> 3) << 5 | row & 7) + 1      */
+    IGL_GEN_I64_LINE_ORDER = 7,    /* C4: lineitem row -> index of its order (m
+                                      orders, 1-7 lines each, 4 on average)     */
+    IGL_GEN_I64_ZIPF = 8     /* C5: Zipf(1.1) rank - 1 over [0, m) by inverse
+                                CDF of u; bits > 0: mapped through the same
+                                bijection as IGL_GEN_I64_PERM                  */
 };
+/* Kinds 1-3 and 6 with dev_keys != NULL generate the value of row dev_keys[i]
+ * instead of row0 + i (expected join payloads, recomputed without a table). */
 int32_t igl_gen_column(igl_ctx* ctx, int32_t kind, uint64_t seed, uint64_t col_id, int64_t row0,
                        int64_t n, uint64_t m, int32_t bits, const int64_t* dev_keys, void* dev_out,
                        void* stream);

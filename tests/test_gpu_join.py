@@ -236,3 +236,32 @@ def test_partitioned_row_id_gather_c4_shape_digest(ctx):
     lk_in = sel(lk2)
     expect2 = [ctx.gen(5, seed, c, 0, n2, bits=bits, keys=lk_in) for c in (1, 2, 3)]
     assert ctx.digest(out2, n2) == ctx.digest([lk_in, sel(lw), lk_in] + expect2, n2)
+
+
+@pytest.mark.parametrize("workload,scale", [("c3", 512), ("c4", 256), ("c5a", 1024), ("c5b", 2048)])
+def test_bench_workloads_small_join_vs_definition_and_oracle(ctx, workload, scale):
+    """The workload shapes bench.py times (C3, C4, C5a, C5b), small: (1) the join's output digest
+    equals the digest of the answer recomputed from the data definition (what bench.py asserts at
+    full scale), and (2) the same device-generated inputs joined by the CPU oracle give the same
+    row multiset digest — so the definition-derived expectation is itself pinned to the oracle."""
+    import bench
+    from igloo_b200.device import HashJoin
+    wl = bench.WORKLOADS[workload](ctx, scale)
+    right, nr, left, nl = wl.shard(0, 1)
+    j = HashJoin(ctx, 0, wl.lf, wl.rf, col(wl.lf[wl.lkey].name), col(wl.rf[wl.rkey].name))
+    j.build(right, nr)
+    assert j.has_duplicates == (workload == "c5b")
+    out, n = j.probe(left, nl)
+    got = ctx.digest(out, n)
+    want, want_rows = wl.expected(left, nl, 0, 1)
+    assert n == want_rows and got == want
+    if workload == "c5a":   # the probe keys really are skewed: the top key holds ~1/H(N, 1.1) of the rows
+        import torch
+        top = int(torch.bincount(left[0].data[:nl] % (1 << 20)).max().item())
+        assert top / nl > 0.05
+    # oracle on the same inputs (read back from the device)
+    names_l = [f.name for f in wl.lf]; names_r = [f.name for f in wl.rf]
+    L = orc.Table.scan([orc.Column(nm, c.type, c.data[:nl].cpu().numpy()) for nm, c in zip(names_l, left)])
+    R = orc.Table.scan([orc.Column(nm, c.type, c.data[:nr].cpu().numpy()) for nm, c in zip(names_r, right)])
+    J = L.hash_join(R, [lower(col(names_l[wl.lkey]), wl.lf)[0]], [lower(col(names_r[wl.rkey]), wl.rf)[0]], 0, 1, 4)
+    assert J.nrows == n and J.digest() == got

@@ -1,5 +1,7 @@
-"""Multi-GPU parity: the hash-repartitioned join over 2 GPUs (both exchange modes) against
-the generator-defined answer.  Skipped on a single-GPU box."""
+"""Multi-GPU parity: the hash-repartitioned join over 2 GPUs (igl_join_shuffle_*, both
+exchange modes) against the answer recomputed from the data definition, for every workload
+shape bench.py times.  Skipped on a single-GPU box (bench.py --gpus N repeats the digest check
+at full scale on every N)."""
 import os
 import subprocess
 import sys
@@ -9,19 +11,27 @@ import pytest
 pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
+CASES = [
+    # workload, scale, extra, join type, must the probe be the fused (segmented) one in p2p mode
+    ("c3", 2048, "", 0, True),        # 2^16 x 488 K: one partition per destination
+    ("c3", 16, "", 0, True),          # 2^23 x 62.5 M: the local tables are radix-partitioned (IGL_PART_MB=4)
+    ("c3", 32, "skew", 0, True),      # 60 % of the probe rows carry one key
+    ("c4", 64, "", 0, True),          # 36-byte probe rows, build payload gathered by row id
+    ("c5a", 64, "", 0, True),         # Zipf(1.1) probe keys
+    ("c5b", 256, "", 0, False),       # Zipf(1.1) build keys: duplicate runs, general probe after a pull of the probe side
+    ("c3", 64, "", 1, False),         # Left join: general probe, null-extended columns
+]
 
-@pytest.mark.parametrize("bits,nprobe,extra", [(16, 300_000, ""), (23, 40_000_000, ""), (23, 20_000_000, "skew")])
-def test_two_gpu_partitioned_join_digest(bits, nprobe, extra):
+
+@pytest.mark.parametrize("workload,scale,extra,jt,fused", CASES)
+def test_two_gpu_partitioned_join_digest(workload, scale, extra, jt, fused):
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
-    # bits=23: the local table (2 x 64 MB) is large enough for the radix fan-out, so the p2p mode
-    # takes the exchange fused with the partitioning; bits=16 takes the plain scatter
-    env = dict(os.environ, IGL_PART_MB="4")
+    env = dict(os.environ, IGL_PART_MB="4", IGL_TEST_JOIN_TYPE=str(jt))
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
-                        "--master-port", "29533", os.path.join(ROOT, "tests", "multi_gpu_worker.py"), str(bits), str(nprobe)] + ([extra] if extra else []),
+                        "--master-port", "29533", os.path.join(ROOT, "tests", "multi_gpu_worker.py"), workload, str(scale)] + ([extra] if extra else []),
                        capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     assert "mode=p2p" in r.stdout and "mode=nccl" in r.stdout
-    if bits >= 23:
-        assert "mode=p2p fused=True" in r.stdout, r.stdout[-500:]
+    assert f"mode=p2p fused={fused}" in r.stdout, r.stdout[-500:]
