@@ -1069,6 +1069,11 @@ struct igl_join {
     // partitioning, [2] build end, [3] probe start, [4] after its partitioning, [5] probe kernel end
     cudaEvent_t ev[6] = {};
     bool ev_build = false, ev_probe = false;
+    // a probe that has been queued but not finished (join_probe_begin / join_probe_end)
+    int pend_kind = 0;                       // 0 none, 1 flat kernel queued, 2 already complete (pend_rows)
+    int64_t pend_rows = 0, pend_nrows = 0;
+    bool pend_dense = false;
+    std::unique_ptr<FlatProbeParams> pend_F;
     JoinSide* host_side = nullptr;
     PipeCols T{};
     PipeGeometry geo;
@@ -1138,9 +1143,9 @@ int32_t flat_fill_params(igl_join* j, FlatProbeParams& F, igl_dev_col* out, int6
     return IGL_OK;
 }
 
-// Scratch, launch, row count and (dense form) hole filling of the flat probe.
-int32_t flat_probe_run(igl_join* j, FlatProbeParams& F, bool seg, int64_t nrows, long long nchunks, int64_t out_capacity,
-                       int64_t* out_rows, cudaStream_t st) {
+// First half: scratch, launch, header copy — everything is queued on `st`, nothing waits.
+int32_t flat_probe_launch(igl_join* j, FlatProbeParams& F, bool seg, int64_t nrows, long long nchunks, int64_t out_capacity,
+                          cudaStream_t st) {
     igl_ctx* ctx = j->ctx;
     const int nl = F.n_left, nr = F.n_right;
     // DENSE form (see the kernel): needs room for every probe row and 32-bit row numbers
@@ -1182,6 +1187,24 @@ int32_t flat_probe_run(igl_join* j, FlatProbeParams& F, bool seg, int64_t nrows,
     j->ev_probe = true;
     ctx->launches++;
     IGL_CUDA_OK(cudaMemcpyAsync(j->host_hdr, j->scratch, sizeof(PipeHeader), cudaMemcpyDeviceToHost, st));
+    if (!j->pend_F) j->pend_F = std::make_unique<FlatProbeParams>();
+    *j->pend_F = F;
+    j->pend_kind = 1; j->pend_nrows = nrows; j->pend_dense = dense;
+    return IGL_OK;
+}
+
+// Second half: waits for the queued flat probe, fills the holes of a dense output, reports the rows.
+int32_t flat_probe_finish(igl_join* j, int64_t* out_rows, cudaStream_t st) {
+    igl_ctx* ctx = j->ctx;
+    const FlatProbeParams& F = *j->pend_F;
+    const int64_t nrows = j->pend_nrows;
+    const bool dense = j->pend_dense;
+    const int nl = F.n_left, nr = F.n_right;
+    j->pend_kind = 0;
+    constexpr int kFixTile = 1024;
+    const long long ntiles = (nrows + kFixTile - 1) / kFixTile;
+    const size_t scan_bytes = (((size_t)scan_scratch_words(tile_offsets_scan_tiles(ntiles)) * 8) + 255) & ~(size_t)255;
+    uint8_t* sb = (uint8_t*)j->scratch;
     IGL_CUDA_OK(cudaStreamSynchronize(st));
     if (dense) {
         const int64_t misses = (int64_t)j->host_hdr->aux[2];
@@ -1235,7 +1258,8 @@ int32_t join_probe_segments(igl_join* j, const SegSource& S, igl_dev_col* out, i
         }
     F.segs = S.dev_segs; F.nsegs = S.nsegs; F.seg_nchunks = S.nchunks;
     IGL_TRY(flat_fill_params(j, F, out, S.total_rows));
-    return flat_probe_run(j, F, /*seg=*/true, S.total_rows, S.nchunks, out_capacity, out_rows, st);
+    IGL_TRY(flat_probe_launch(j, F, /*seg=*/true, S.total_rows, S.nchunks, out_capacity, st));
+    return flat_probe_finish(j, out_rows, st);
 }
 
 }  // namespace igl
@@ -1432,15 +1456,24 @@ int32_t igl_join_probe_count(igl_join* j, const igl_dev_col* left, int64_t nrows
     return IGL_OK;
 }
 
-int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_dev_col* out, int64_t out_capacity,
-                       int64_t* out_rows, void* stream) {
+}  // extern "C"
+
+namespace igl {
+
+// igl_join_probe in two halves (kernels.h): `begin` queues everything it can on `st` — for the flat
+// fast path that is all of the work, nothing waits — and `end` waits, finishes (hole filling) and
+// reports the row count.  One probe per join may be pending.  The streaming operator puts the
+// staging of its next chunk between the two.
+int32_t join_probe_begin(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_dev_col* out, int64_t out_capacity,
+                         cudaStream_t st) {
+    void* stream = (void*)st;
     if (!j || !left || !out || nrows < 0) return fail(IGL_ERR_INVALID_ARG, "igl_join_probe: bad arguments");
     if (!j->built) return fail(IGL_ERR_INVALID_ARG, "igl_join_probe: build side not finished");
     igl_ctx* ctx = j->ctx;
     DeviceGuard g(ctx->device);
-    cudaStream_t st = pick_stream(ctx, stream);
     const int nl = (int)j->lt.size(), nr = (int)j->rt.size();
-    if (nrows == 0) { if (out_rows) *out_rows = 0; return IGL_OK; }
+    if (j->pend_kind != 0) return fail(IGL_ERR_INVALID_ARG, "igl_join_probe: the previous probe of this join has not been finished");
+    if (nrows == 0) { j->pend_kind = 2; j->pend_rows = 0; return IGL_OK; }
     // capacity check: unique layout emits at most one row per probe row
     if (!j->csr && out_capacity < nrows) {
         int64_t need = 0;
@@ -1480,7 +1513,7 @@ int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_
                 F.left[c] = (const uint8_t*)left[c].data;
             }
             IGL_TRY(flat_fill_params(j, F, out, nrows));
-            return flat_probe_run(j, F, /*seg=*/false, nrows, (nrows + kFlatChunk - 1) / kFlatChunk, out_capacity, out_rows, st);
+            return flat_probe_launch(j, F, /*seg=*/false, nrows, (nrows + kFlatChunk - 1) / kFlatChunk, out_capacity, st);
         }
     }
     JoinProbeParams P{};
@@ -1563,9 +1596,30 @@ int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_
     IGL_CUDA_OK(cudaStreamSynchronize(st));
     if (j->host_hdr->err_flags & 0x80000000u)
         return fail(IGL_ERR_UNSUPPORTED, "one probe tile expands to more than 2^31 output rows (extreme key skew on both sides); probe in smaller chunks");
-    if (out_rows) *out_rows = (int64_t)j->host_hdr->out_count;
+    j->pend_kind = 2; j->pend_rows = (int64_t)j->host_hdr->out_count;
     return IGL_OK;
 }
+
+int32_t join_probe_end(igl_join* j, int64_t* out_rows, cudaStream_t st) {
+    if (!j) return fail(IGL_ERR_INVALID_ARG, "join_probe_end: NULL join");
+    DeviceGuard g(j->ctx->device);
+    if (j->pend_kind == 1) return flat_probe_finish(j, out_rows, st);
+    if (j->pend_kind == 2) { j->pend_kind = 0; if (out_rows) *out_rows = j->pend_rows; return IGL_OK; }
+    return fail(IGL_ERR_INVALID_ARG, "join_probe_end: no probe is pending");
+}
+
+}  // namespace igl
+
+extern "C" {
+
+int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_dev_col* out, int64_t out_capacity,
+                       int64_t* out_rows, void* stream) {
+    if (!j || !left || !out || nrows < 0) return fail(IGL_ERR_INVALID_ARG, "igl_join_probe: bad arguments");
+    cudaStream_t st = pick_stream(j->ctx, stream);
+    IGL_TRY(join_probe_begin(j, left, nrows, out, out_capacity, st));
+    return join_probe_end(j, out_rows, st);
+}
+
 
 // Device time of the last igl_join_build / igl_join_probe on this join, in milliseconds:
 // out[0] build-side partitioning, out[1] table init + build kernels, out[2] probe-side

@@ -72,6 +72,11 @@ struct SegSource {
     long long nchunks;                     // chunks in total (every run rounded up to whole chunks)
     long long total_rows;                  // rows in total: the output capacity needed
 };
+// igl_join_probe in two halves: `begin` queues the probe on `st` (the flat fast path does not
+// wait for anything), `end` waits, finishes and reports the rows.  One pending probe per join.
+int32_t join_probe_begin(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_dev_col* out, int64_t out_capacity,
+                         cudaStream_t st);
+int32_t join_probe_end(igl_join* j, int64_t* out_rows, cudaStream_t st);
 // True when `j` (built) can take segmented input: inner join, unique build keys, no validity.
 bool join_segments_eligible(const igl_join* j);
 int32_t join_probe_segments(igl_join* j, const SegSource& S, igl_dev_col* out, int64_t out_capacity, int64_t* out_rows,
