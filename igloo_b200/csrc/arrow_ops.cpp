@@ -272,7 +272,12 @@ struct OutCol {
     int type = 0; void* data = nullptr; uint8_t* valid = nullptr; int32_t* off = nullptr; int64_t null_count = 0;
     bool alias = false;   // `data` belongs to another column of the same batch (two columns, one host buffer)
 };
-struct OutBatch { int64_t nrows = 0; std::vector<OutCol> cols; };
+struct OutBatch {
+    int64_t nrows = 0;
+    std::vector<OutCol> cols;
+    cudaEvent_t done = nullptr;        // join: recorded behind the batch's device->host copies (download stream)
+    std::vector<void*> dev_free;       // device output blocks, returned to the pool once `done` has passed
+};
 
 struct ExportHolder {
     std::vector<void*> pinned;
@@ -374,6 +379,17 @@ struct igl_op {
     // right key equals its left key bit for bit, so the right key column is not copied back
     // over PCIe — the exported batch's two key columns share one host buffer.
     int alias_right_key = -1, alias_left_key = -1;
+    // Probe chunks are pipelined over three streams: chunk i's upload (s_up), its probe (the context's
+    // stream) and the download of its output (s_down) overlap the host-side staging of chunk i + 1 and
+    // each other across chunks; igl_op_pull hands a batch out once its download has finished.
+    cudaStream_t s_up = nullptr, s_down = nullptr;
+    cudaEvent_t ev_up = nullptr;
+    struct JoinPending {
+        bool active = false;
+        int64_t n = 0, cap = 0;
+        std::vector<igl_dev_col> dev, dout;
+        std::vector<void*> to_free;
+    } jpend;
     std::vector<void*> build_dev;            // grown device columns of the whole build side
     std::vector<size_t> build_cap;
     std::vector<uint8_t*> build_valid;
@@ -531,6 +547,41 @@ int32_t fp_flush(igl_op* op) {
     return fp_begin(op);
 }
 
+// Room for `n` more rows on the device-resident build side (every column grows by doubling; one
+// wait per growth step, after all the copies have been queued).
+int32_t join_build_reserve(igl_op* op, int64_t n) {
+    Staging& S = op->build;
+    igl_ctx* ctx = op->ctx;
+    cudaStream_t st = ctx->stream;
+    if (op->build_rows + n <= op->build_rows_cap) return IGL_OK;
+    const int64_t cap = std::max<int64_t>(op->build_rows + n, op->build_rows_cap * 2);
+    std::vector<void*> old_blocks;
+    for (int c = 0; c < op->n_right; ++c) {
+        const int w = type_width(S.fields[c].type);
+        void* p = nullptr;
+        IGL_TRY(pool_alloc(ctx, pad64((size_t)cap * w), &p));
+        if (op->build_dev[c]) {
+            IGL_CUDA_OK(cudaMemcpyAsync(p, op->build_dev[c], (size_t)op->build_rows * w, cudaMemcpyDeviceToDevice, st));
+            old_blocks.push_back(op->build_dev[c]);
+        }
+        op->build_dev[c] = p;
+        if (S.fields[c].nullable) {
+            void* v = nullptr;
+            IGL_TRY(pool_alloc(ctx, pad64((size_t)(cap + 7) / 8 + 8), &v));
+            IGL_CUDA_OK(cudaMemsetAsync(v, 0, pad64((size_t)(cap + 7) / 8 + 8), st));
+            if (op->build_valid[c]) {
+                IGL_CUDA_OK(cudaMemcpyAsync(v, op->build_valid[c], (size_t)(op->build_rows + 7) / 8, cudaMemcpyDeviceToDevice, st));
+                old_blocks.push_back(op->build_valid[c]);
+            }
+            op->build_valid[c] = (uint8_t*)v;
+        }
+    }
+    if (!old_blocks.empty()) IGL_CUDA_OK(cudaStreamSynchronize(st));
+    for (void* q : old_blocks) pool_free(ctx, q);
+    op->build_rows_cap = cap;
+    return IGL_OK;
+}
+
 // Appends the staged build chunk to the device-resident build side.
 int32_t join_build_flush(igl_op* op) {
     Staging& S = op->build;
@@ -538,32 +589,7 @@ int32_t join_build_flush(igl_op* op) {
     if (n == 0) return IGL_OK;
     igl_ctx* ctx = op->ctx;
     cudaStream_t st = ctx->stream;
-    if (op->build_rows + n > op->build_rows_cap) {   // grow every column (doubling)
-        const int64_t cap = std::max<int64_t>(op->build_rows + n, op->build_rows_cap * 2);
-        for (int c = 0; c < op->n_right; ++c) {
-            const int w = type_width(S.fields[c].type);
-            void* p = nullptr;
-            IGL_TRY(pool_alloc(ctx, pad64((size_t)cap * w), &p));
-            if (op->build_dev[c]) {
-                IGL_CUDA_OK(cudaMemcpyAsync(p, op->build_dev[c], (size_t)op->build_rows * w, cudaMemcpyDeviceToDevice, st));
-                IGL_CUDA_OK(cudaStreamSynchronize(st));
-                pool_free(ctx, op->build_dev[c]);
-            }
-            op->build_dev[c] = p;
-            if (S.fields[c].nullable) {
-                void* v = nullptr;
-                IGL_TRY(pool_alloc(ctx, pad64((size_t)(cap + 7) / 8 + 8), &v));
-                IGL_CUDA_OK(cudaMemsetAsync(v, 0, pad64((size_t)(cap + 7) / 8 + 8), st));
-                if (op->build_valid[c]) {
-                    IGL_CUDA_OK(cudaMemcpyAsync(v, op->build_valid[c], (size_t)(op->build_rows + 7) / 8, cudaMemcpyDeviceToDevice, st));
-                    IGL_CUDA_OK(cudaStreamSynchronize(st));
-                    pool_free(ctx, op->build_valid[c]);
-                }
-                op->build_valid[c] = (uint8_t*)v;
-            }
-        }
-        op->build_rows_cap = cap;
-    }
+    IGL_TRY(join_build_reserve(op, n));
     if ((op->build_rows & 7) != 0) {
         // validity bitmaps are appended bytewise: keep chunk boundaries byte aligned
         for (int c = 0; c < op->n_right; ++c)
@@ -581,41 +607,26 @@ int32_t join_build_flush(igl_op* op) {
     return IGL_OK;
 }
 
-int32_t join_probe_flush(igl_op* op) {
-    Staging& S = op->in;
-    const int64_t n = S.rows;
-    if (n == 0) return IGL_OK;
+// Finishes the probe chunk queued before: waits for its kernels, queues the download of its output
+// on the download stream and appends the batch to `ready` (igl_op_pull waits for the download).
+int32_t join_probe_end_chunk(igl_op* op) {
+    auto& PD = op->jpend;
+    if (!PD.active) return IGL_OK;
+    PD.active = false;
     igl_ctx* ctx = op->ctx;
     cudaStream_t st = ctx->stream;
-    std::vector<igl_dev_col> dev;
-    IGL_TRY(S.upload(st, dev));
-    int64_t cap = n;
-    if (igl_join_has_duplicates(op->join)) IGL_TRY(igl_join_probe_count(op->join, dev.data(), n, &cap, st));
-    const int nc = op->n_left + op->n_right;
-    std::vector<igl_dev_col> dout(nc);
-    std::vector<void*> to_free;
-    auto cleanup = [&]() { for (void* p : to_free) pool_free(ctx, p); };
-    for (int c = 0; c < nc; ++c) {
-        dout[c].type = op->out_fields[c].type;
-        void* p = nullptr;
-        int32_t rc = pool_alloc(ctx, pad64((size_t)std::max<int64_t>(cap, 1) * type_width(dout[c].type)), &p);
-        if (rc < 0) { cleanup(); return rc; }
-        to_free.push_back(p); dout[c].data = p;
-        rc = pool_alloc(ctx, pad64((size_t)(cap + 7) / 8 + 8), &p);
-        if (rc < 0) { cleanup(); return rc; }
-        to_free.push_back(p); dout[c].validity = (uint8_t*)p;
-    }
+    auto cleanup = [&]() { for (void* p : PD.to_free) pool_free(ctx, p); PD.to_free.clear(); };
     int64_t n_out = 0;
-    int32_t rc = igl_join_probe(op->join, dev.data(), n, dout.data(), cap, &n_out, st);
-    S.reset();
-    if (rc < 0) { cleanup(); return rc; }
+    int32_t rc = join_probe_end(op->join, &n_out, st);   // the compute stream is drained here
+    if (rc < 0) { cudaStreamSynchronize(st); cleanup(); return rc; }
     if (n_out == 0) { cleanup(); return IGL_OK; }
+    const int nc = op->n_left + op->n_right;
     OutBatch ob;
     ob.nrows = n_out;
     ob.cols.resize(nc);
     for (int c = 0; c < nc && rc >= 0; ++c) {
-        ob.cols[c].type = dout[c].type;
-        if (op->alias_right_key >= 0 && c == op->n_left + op->alias_right_key && dev[op->alias_left_key].validity == nullptr &&
+        ob.cols[c].type = PD.dout[c].type;
+        if (op->alias_right_key >= 0 && c == op->n_left + op->alias_right_key && PD.dev[op->alias_left_key].validity == nullptr &&
             op->build_valid[op->alias_right_key] == nullptr) {   // no NULL keys on either side in this chunk
             ob.cols[c].data = ob.cols[op->alias_left_key].data;   // left columns come first: already set
             ob.cols[c].alias = true;
@@ -624,18 +635,134 @@ int32_t join_probe_flush(igl_op* op) {
         // igl_join_probe writes a validity bitmap for a left column that has one and
         // for a right column that can be null (source nullable, or null-extended)
         const bool is_left = c < op->n_left;
-        const bool wrote_valid = is_left ? dev[c].validity != nullptr
+        const bool wrote_valid = is_left ? PD.dev[c].validity != nullptr
                                          : (op->left_join || op->build_valid[c - op->n_left] != nullptr);
-        rc = d2h_col(ctx, st, ob.cols[c], dout[c].data, wrote_valid ? dout[c].validity : nullptr, n_out, true);
+        rc = d2h_col(ctx, op->s_down, ob.cols[c], PD.dout[c].data, wrote_valid ? PD.dout[c].validity : nullptr, n_out, true);
     }
-    if (rc >= 0 && cudaStreamSynchronize(st) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "stream synchronise failed");
-    cleanup();
+    if (rc >= 0 && (cudaEventCreateWithFlags(&ob.done, cudaEventDisableTiming) != cudaSuccess || cudaEventRecord(ob.done, op->s_down) != cudaSuccess))
+        rc = fail(IGL_ERR_CUDA, "event for the output download failed");
     if (rc < 0) {
+        cudaStreamSynchronize(op->s_down);
+        cleanup();
+        if (ob.done) cudaEventDestroy(ob.done);
         for (auto& c : ob.cols) { if (!c.alias) pinned_pool().put(c.data); pinned_pool().put(c.valid); }
         return rc;
     }
-    for (auto& c : ob.cols) c.null_count = c.valid ? count_zero_bits(c.valid, n_out) : 0;
+    ob.dev_free.swap(PD.to_free);   // the device output blocks live until the download has passed
     op->ready.push_back(std::move(ob));
+    return IGL_OK;
+}
+
+// Queues the probe of one chunk whose columns are (being) uploaded into `dev`; does not wait for it.
+int32_t join_probe_begin_chunk(igl_op* op, int64_t n, std::vector<igl_dev_col>&& dev) {
+    igl_ctx* ctx = op->ctx;
+    cudaStream_t st = ctx->stream;
+    auto& PD = op->jpend;
+    PD.dev = std::move(dev);
+    PD.dout.clear(); PD.to_free.clear();
+    IGL_CUDA_OK(cudaEventRecord(op->ev_up, op->s_up));
+    IGL_CUDA_OK(cudaStreamWaitEvent(st, op->ev_up, 0));
+    int64_t cap = n;
+    if (igl_join_has_duplicates(op->join)) IGL_TRY(igl_join_probe_count(op->join, PD.dev.data(), n, &cap, st));
+    const int nc = op->n_left + op->n_right;
+    PD.dout.assign(nc, igl_dev_col{});
+    auto cleanup = [&]() { for (void* p : PD.to_free) pool_free(ctx, p); PD.to_free.clear(); };
+    for (int c = 0; c < nc; ++c) {
+        PD.dout[c].type = op->out_fields[c].type;
+        void* p = nullptr;
+        int32_t rc = pool_alloc(ctx, pad64((size_t)std::max<int64_t>(cap, 1) * type_width(PD.dout[c].type)), &p);
+        if (rc < 0) { cleanup(); return rc; }
+        PD.to_free.push_back(p); PD.dout[c].data = p;
+        rc = pool_alloc(ctx, pad64((size_t)(cap + 7) / 8 + 8), &p);
+        if (rc < 0) { cleanup(); return rc; }
+        PD.to_free.push_back(p); PD.dout[c].validity = (uint8_t*)p;
+    }
+    int32_t rc = join_probe_begin(op->join, PD.dev.data(), n, PD.dout.data(), cap, st);
+    if (rc < 0) { cudaStreamSynchronize(st); cleanup(); return rc; }
+    PD.n = n; PD.cap = cap;
+    PD.active = true;
+    return IGL_OK;
+}
+
+// A staged chunk is full (or the input ended): finish the chunk queued before, queue this one.
+int32_t join_probe_flush(igl_op* op) {
+    IGL_TRY(join_probe_end_chunk(op));
+    Staging& S = op->in;
+    const int64_t n = S.rows;
+    if (n == 0) return IGL_OK;
+    std::vector<igl_dev_col> dev;
+    IGL_TRY(S.upload(op->s_up, dev));
+    IGL_TRY(join_probe_begin_chunk(op, n, std::move(dev)));
+    std::swap(op->in, op->in_alt);   // the queued chunk's pinned and device buffers now sit in in_alt
+    op->in.reset();                  // the chunk that used these buffers was finished above
+    return IGL_OK;
+}
+
+// Page-locked host buffers need no staging copy: the DMA engine reads them where they are.
+bool is_pinned_host(const void* p) {
+    cudaPointerAttributes a{};
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { (void)cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
+}
+
+// True when rows of `batch` can be uploaded straight from the caller's buffers: fixed-width
+// columns without nulls in page-locked memory, and enough rows to be worth a chunk of their own.
+bool batch_is_direct(const Staging& S, const ArrowArray* batch) {
+    static const bool enabled = !(getenv("IGL_OP_DIRECT") && getenv("IGL_OP_DIRECT")[0] == '0');
+    if (!enabled || S.rows != 0 || batch->length < (64 << 10) || (size_t)batch->n_children != S.fields.size()) return false;
+    for (size_t j = 0; j < S.fields.size(); ++j) {
+        if (!S.wanted[j]) continue;
+        const int t = S.fields[j].type;
+        const ArrowArray* a = batch->children[j];
+        if (type_width(t) == 0 || a->null_count != 0 || a->n_buffers < 2 || !is_pinned_host(a->buffers[1])) return false;
+    }
+    return true;
+}
+
+// Uploads rows [from, from + n) of a direct batch into the device buffers of `S` on stream `up`.
+int32_t direct_upload(Staging& S, const ArrowArray* batch, int64_t from, int64_t n, cudaStream_t up, std::vector<igl_dev_col>& dev) {
+    igl_ctx* ctx = S.ctx;
+    dev.assign(S.fields.size(), igl_dev_col{});
+    for (size_t j = 0; j < S.fields.size(); ++j) {
+        dev[j].type = S.fields[j].type;
+        if (!S.wanted[j]) continue;
+        StagedCol& c = S.cols[j];
+        const ArrowArray* a = batch->children[j];
+        const int w = type_width(c.type);
+        const size_t bytes = (size_t)n * w;
+        if (pad64(bytes) > c.d_data_cap) {
+            if (c.d_data) pool_free(ctx, c.d_data);
+            c.d_data = nullptr; c.d_data_cap = 0;
+            IGL_TRY(pool_alloc(ctx, pad64(std::max(bytes, (size_t)S.chunk_rows * w)), &c.d_data));
+            c.d_data_cap = pad64(std::max(bytes, (size_t)S.chunk_rows * w));
+        }
+        IGL_CUDA_OK(cudaMemcpyAsync(c.d_data, (const uint8_t*)a->buffers[1] + (size_t)(a->offset + batch->offset + from) * w, bytes,
+                                    cudaMemcpyHostToDevice, up));
+        dev[j].data = c.d_data;
+        if (c.nullable) {   // declared nullable, no nulls in this batch: an all-ones bitmap
+            if (!c.d_valid) { void* p = nullptr; IGL_TRY(pool_alloc(ctx, pad64((size_t)(S.chunk_rows + 7) / 8), &p)); c.d_valid = (uint8_t*)p; }
+            IGL_CUDA_OK(cudaMemsetAsync(c.d_valid, 0xFF, (size_t)(n + 7) / 8, up));
+            dev[j].validity = c.d_valid;
+        }
+    }
+    return IGL_OK;
+}
+
+// Probe rows straight from the caller's page-locked batch, chunk by chunk.  The batch is only
+// borrowed for this call, so each chunk's upload is awaited before the next step — while it
+// travels, the previous chunk's output is on its way down and its successor's probe runs.
+int32_t join_probe_direct(igl_op* op, const ArrowArray* batch) {
+    int64_t done = 0;
+    while (done < batch->length) {
+        const int64_t n = std::min<int64_t>(batch->length - done, op->in.chunk_rows);
+        IGL_TRY(join_probe_end_chunk(op));
+        std::vector<igl_dev_col> dev;
+        IGL_TRY(direct_upload(op->in, batch, done, n, op->s_up, dev));
+        IGL_TRY(join_probe_begin_chunk(op, n, std::move(dev)));
+        IGL_CUDA_OK(cudaEventSynchronize(op->ev_up));   // the caller's buffers are free again
+        std::swap(op->in, op->in_alt);
+        done += n;
+    }
     return IGL_OK;
 }
 
@@ -773,6 +900,13 @@ int32_t igl_op_hash_join_create(igl_ctx* ctx, int32_t join_type, const struct Ar
     op->build_dev.assign(op->n_right, nullptr);
     op->build_cap.assign(op->n_right, 0);
     op->build_valid.assign(op->n_right, nullptr);
+    op->in_alt = op->in;   // second probe chunk buffer of the same shape
+    if (cudaStreamCreateWithFlags(&op->s_up, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&op->s_down, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&op->ev_up, cudaEventDisableTiming) != cudaSuccess) {
+        destroy_partial();
+        return fail(IGL_ERR_CUDA, "igl_op_hash_join_create: stream / event creation failed");
+    }
     *out = op.release();
     return IGL_OK;
 }
@@ -787,6 +921,24 @@ int32_t igl_op_push_build(igl_op* op, const struct ArrowArray* batch) {
     if (!op || !op->is_join) return fail(IGL_ERR_INVALID_ARG, "igl_op_push_build: not a join operator");
     if (op->build_done) return fail(IGL_ERR_INVALID_ARG, "igl_op_push_build: build side already finished");
     DeviceGuard g(op->ctx->device);
+    if (batch && batch_is_direct(op->build, batch) && (op->build_rows & 7) == 0) {
+        // page-locked batch: straight from the caller's buffers to the end of the device columns
+        Staging& S = op->build;
+        const int64_t n = batch->length;
+        IGL_TRY(join_build_reserve(op, n));
+        cudaStream_t st = op->ctx->stream;
+        for (int c = 0; c < op->n_right; ++c) {
+            const ArrowArray* a = batch->children[c];
+            const int w = type_width(S.fields[c].type);
+            IGL_CUDA_OK(cudaMemcpyAsync((uint8_t*)op->build_dev[c] + (size_t)op->build_rows * w,
+                                        (const uint8_t*)a->buffers[1] + (size_t)(a->offset + batch->offset) * w, (size_t)n * w, cudaMemcpyHostToDevice, st));
+            if (S.fields[c].nullable)   // no nulls in a direct batch: all ones (a partial last byte is completed by the next append)
+                IGL_CUDA_OK(cudaMemsetAsync(op->build_valid[c] + (op->build_rows >> 3), 0xFF, (size_t)(n + 7) / 8, st));
+        }
+        IGL_CUDA_OK(cudaStreamSynchronize(st));   // the batch is only borrowed for this call
+        op->build_rows += n;
+        return IGL_OK;
+    }
     return push_rows(op, op->build, batch, join_build_flush);
 }
 
@@ -813,6 +965,7 @@ int32_t igl_op_push(igl_op* op, const struct ArrowArray* batch) {
     DeviceGuard g(op->ctx->device);
     if (op->is_join) {
         if (!op->build_done) return fail(IGL_ERR_INVALID_ARG, "igl_op_push: finish the build side first (hash_join.rs:100-128 drains the right child before probing)");
+        if (batch && batch_is_direct(op->in, batch)) return join_probe_direct(op, batch);
         return push_rows(op, op->in, batch, join_probe_flush);
     }
     return push_rows(op, op->in, batch, fp_flush);
@@ -825,6 +978,7 @@ int32_t igl_op_finish_input(igl_op* op) {
     if (op->is_join) {
         if (!op->build_done) IGL_TRY(igl_op_finish_build(op));
         IGL_TRY(join_probe_flush(op));
+        IGL_TRY(join_probe_end_chunk(op));
     } else {
         IGL_TRY(fp_flush(op));
         IGL_TRY(fp_end(op));
@@ -836,6 +990,20 @@ int32_t igl_op_finish_input(igl_op* op) {
 int32_t igl_op_pull(igl_op* op, struct ArrowArray* out) {
     if (!op || !out) return fail(IGL_ERR_INVALID_ARG, "igl_op_pull: NULL argument");
     if (op->ready.empty()) return op->input_done ? IGL_EOS : IGL_AGAIN;
+    OutBatch& f = op->ready.front();
+    if (f.done) {
+        // still travelling: while input is flowing the caller should push on (the copy overlaps the
+        // next chunk's upload); once the input has ended there is nothing better to do than wait
+        DeviceGuard g(op->ctx->device);
+        if (!op->input_done && cudaEventQuery(f.done) == cudaErrorNotReady) return IGL_AGAIN;
+        (void)cudaGetLastError();
+        if (cudaEventSynchronize(f.done) != cudaSuccess) return fail(IGL_ERR_CUDA, "output download failed: %s", cudaGetErrorString(cudaGetLastError()));
+        cudaEventDestroy(f.done);
+        f.done = nullptr;
+        for (void* p : f.dev_free) pool_free(op->ctx, p);
+        f.dev_free.clear();
+        for (auto& c : f.cols) c.null_count = c.valid ? count_zero_bits(c.valid, f.nrows) : 0;
+    }
     OutBatch b = std::move(op->ready.front());
     op->ready.pop_front();
     export_batch(std::move(b), out);
@@ -845,7 +1013,21 @@ int32_t igl_op_pull(igl_op* op, struct ArrowArray* out) {
 void igl_op_destroy(igl_op* op) {
     if (!op) return;
     DeviceGuard g(op->ctx->device);
-    for (auto& b : op->ready) for (auto& c : b.cols) { pinned_pool().put(c.data); pinned_pool().put(c.valid); pinned_pool().put(c.off); }
+    if (op->s_down) cudaStreamSynchronize(op->s_down);
+    if (op->s_up) cudaStreamSynchronize(op->s_up);
+    if (op->jpend.active) {
+        int64_t dummy = 0;
+        join_probe_end(op->join, &dummy, op->ctx->stream);
+        for (void* p : op->jpend.to_free) pool_free(op->ctx, p);
+    }
+    for (auto& b : op->ready) {
+        if (b.done) cudaEventDestroy(b.done);
+        for (void* p : b.dev_free) pool_free(op->ctx, p);
+        for (auto& c : b.cols) { if (!c.alias) pinned_pool().put(c.data); pinned_pool().put(c.valid); pinned_pool().put(c.off); }
+    }
+    if (op->s_up) cudaStreamDestroy(op->s_up);
+    if (op->s_down) cudaStreamDestroy(op->s_down);
+    if (op->ev_up) cudaEventDestroy(op->ev_up);
     if (op->pend.active) { cudaStreamSynchronize(op->ctx->stream); for (void* p : op->pend.to_free) pool_free(op->ctx, p); }
     op->in.destroy();
     op->in_alt.destroy();
