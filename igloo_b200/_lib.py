@@ -125,6 +125,7 @@ _sig("igl_join_shuffle_phase_ms", _i32, _vp, _P(C.c_double))
 _sig("igl_join_shuffle_stats", _i32, _vp, _P(_i64))
 _sig("igl_join_shuffle_destroy", None, _vp)
 _sig("igl_shuffle_plan", _i32, _i32, _i32, _i32, _P(_i64), _P(_i64), _P(_i32), _P(_i64), _P(_i64), _P(_i64))
+_sig("igl_shuffle_plan_ex", _i32, _i32, _i32, _i32, _i32, _P(_i64), _P(_i64), _P(_i32), _P(_i64), _P(_i64), _P(_i64))
 _sig("igl_gen_column", _i32, _vp, _i32, _u64, _u64, _i64, _i64, _u64, _i32, _vp, _vp, _vp)
 _sig("igl_digest_rows", _i32, _vp, _P(DevCol), _i32, _i64, _P(_u64), _vp)
 _sig("igl_op_filter_project_create", _i32, _vp, _P(ArrowSchema), C.c_char_p, _sz, _P(C.c_char_p), _P(_sz),

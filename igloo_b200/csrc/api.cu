@@ -4,6 +4,7 @@
 // pool" and "pinned-memory batch upload path" BASELINE.json's north_star names.
 #include "internal.h"
 
+#include <chrono>
 #include <cstdlib>
 #include <cstring>
 
@@ -28,6 +29,29 @@ int32_t fail(int32_t code, const char* fmt, ...) {
     va_end(ap);
     g_last_error = buf;
     return code;
+}
+
+// ---- host-time tracing (IGL_TRACE=1) ----------------------------------------------------------
+namespace {
+struct TraceTable {
+    std::mutex mu;
+    std::map<std::string, std::pair<double, long>> acc;
+    ~TraceTable() {
+        if (acc.empty()) return;
+        fprintf(stderr, "[igl trace]");
+        for (auto& kv : acc) fprintf(stderr, " %s=%.2fms/%ld", kv.first.c_str(), kv.second.first * 1e3, kv.second.second);
+        fprintf(stderr, "\n");
+    }
+};
+TraceTable& trace_table() { static TraceTable t; return t; }
+}  // namespace
+bool trace_on() { static const bool on = getenv("IGL_TRACE") && getenv("IGL_TRACE")[0] == '1'; return on; }
+double trace_now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+void trace_add(const char* name, double seconds) {
+    TraceTable& t = trace_table();
+    std::lock_guard<std::mutex> g(t.mu);
+    auto& e = t.acc[name];
+    e.first += seconds; e.second++;
 }
 
 static size_t bucket_of(size_t bytes) {

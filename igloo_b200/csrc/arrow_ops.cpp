@@ -14,6 +14,7 @@
 // boundaries follow the coalescing (one output batch per chunk; a FilterExec
 // chunk that keeps no row emits nothing, filter.rs:59-63).
 #include <algorithm>
+#include <chrono>
 #include <cstring>
 #include <deque>
 #include <memory>
@@ -62,6 +63,21 @@ struct PinnedPool {
 PinnedPool& pinned_pool() { static PinnedPool* p = new PinnedPool(); return *p; }
 
 struct FieldMeta { std::string name; int type; bool nullable; };
+
+// IGL_OP_TRACE=1: host wall-clock spent per step of the streaming operators, printed when an
+// operator is destroyed (where does a chunk's time go: staging, waiting for the GPU, copies?).
+struct OpTrace {
+    bool on = getenv("IGL_OP_TRACE") && getenv("IGL_OP_TRACE")[0] == '1';
+    double t[8] = {};
+    long n[8] = {};
+    static double now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+};
+struct TraceScope {
+    OpTrace& T; int i; double t0;
+    TraceScope(OpTrace& t, int idx) : T(t), i(idx), t0(t.on ? OpTrace::now() : 0.0) {}
+    ~TraceScope() { if (T.on) { T.t[i] += OpTrace::now() - t0; T.n[i]++; } }
+};
+enum { TR_STAGE = 0, TR_END = 1, TR_UPLOAD = 2, TR_BEGIN = 3, TR_WAIT_UP = 4, TR_PULL = 5, TR_BUILD = 6, TR_PUSH = 7 };
 
 int type_of_format(const char* f) {
     if (!f) return 0;
@@ -384,6 +400,7 @@ struct igl_op {
     // each other across chunks; igl_op_pull hands a batch out once its download has finished.
     cudaStream_t s_up = nullptr, s_down = nullptr;
     cudaEvent_t ev_up = nullptr;
+    OpTrace trace;
     struct JoinPending {
         bool active = false;
         int64_t n = 0, cap = 0;
@@ -660,8 +677,12 @@ int32_t join_probe_begin_chunk(igl_op* op, int64_t n, std::vector<igl_dev_col>&&
     auto& PD = op->jpend;
     PD.dev = std::move(dev);
     PD.dout.clear(); PD.to_free.clear();
-    IGL_CUDA_OK(cudaEventRecord(op->ev_up, op->s_up));
-    IGL_CUDA_OK(cudaStreamWaitEvent(st, op->ev_up, 0));
+    {
+        HostTrace tr("op.begin.event");
+        IGL_CUDA_OK(cudaEventRecord(op->ev_up, op->s_up));
+        IGL_CUDA_OK(cudaStreamWaitEvent(st, op->ev_up, 0));
+    }
+    HostTrace tr_alloc("op.begin.alloc+probe");
     int64_t cap = n;
     if (igl_join_has_duplicates(op->join)) IGL_TRY(igl_join_probe_count(op->join, PD.dev.data(), n, &cap, st));
     const int nc = op->n_left + op->n_right;
@@ -677,7 +698,11 @@ int32_t join_probe_begin_chunk(igl_op* op, int64_t n, std::vector<igl_dev_col>&&
         if (rc < 0) { cleanup(); return rc; }
         PD.to_free.push_back(p); PD.dout[c].validity = (uint8_t*)p;
     }
-    int32_t rc = join_probe_begin(op->join, PD.dev.data(), n, PD.dout.data(), cap, st);
+    int32_t rc;
+    {
+        HostTrace tr("op.begin.probe");
+        rc = join_probe_begin(op->join, PD.dev.data(), n, PD.dout.data(), cap, st);
+    }
     if (rc < 0) { cudaStreamSynchronize(st); cleanup(); return rc; }
     PD.n = n; PD.cap = cap;
     PD.active = true;
@@ -686,13 +711,13 @@ int32_t join_probe_begin_chunk(igl_op* op, int64_t n, std::vector<igl_dev_col>&&
 
 // A staged chunk is full (or the input ended): finish the chunk queued before, queue this one.
 int32_t join_probe_flush(igl_op* op) {
-    IGL_TRY(join_probe_end_chunk(op));
+    { TraceScope ts(op->trace, TR_END); IGL_TRY(join_probe_end_chunk(op)); }
     Staging& S = op->in;
     const int64_t n = S.rows;
     if (n == 0) return IGL_OK;
     std::vector<igl_dev_col> dev;
-    IGL_TRY(S.upload(op->s_up, dev));
-    IGL_TRY(join_probe_begin_chunk(op, n, std::move(dev)));
+    { TraceScope ts(op->trace, TR_UPLOAD); IGL_TRY(S.upload(op->s_up, dev)); }
+    { TraceScope ts(op->trace, TR_BEGIN); IGL_TRY(join_probe_begin_chunk(op, n, std::move(dev))); }
     std::swap(op->in, op->in_alt);   // the queued chunk's pinned and device buffers now sit in in_alt
     op->in.reset();                  // the chunk that used these buffers was finished above
     return IGL_OK;
@@ -755,11 +780,11 @@ int32_t join_probe_direct(igl_op* op, const ArrowArray* batch) {
     int64_t done = 0;
     while (done < batch->length) {
         const int64_t n = std::min<int64_t>(batch->length - done, op->in.chunk_rows);
-        IGL_TRY(join_probe_end_chunk(op));
+        { TraceScope ts(op->trace, TR_END); IGL_TRY(join_probe_end_chunk(op)); }
         std::vector<igl_dev_col> dev;
-        IGL_TRY(direct_upload(op->in, batch, done, n, op->s_up, dev));
-        IGL_TRY(join_probe_begin_chunk(op, n, std::move(dev)));
-        IGL_CUDA_OK(cudaEventSynchronize(op->ev_up));   // the caller's buffers are free again
+        { TraceScope ts(op->trace, TR_UPLOAD); IGL_TRY(direct_upload(op->in, batch, done, n, op->s_up, dev)); }
+        { TraceScope ts(op->trace, TR_BEGIN); IGL_TRY(join_probe_begin_chunk(op, n, std::move(dev))); }
+        { TraceScope ts(op->trace, TR_WAIT_UP); IGL_CUDA_OK(cudaEventSynchronize(op->ev_up)); }   // the caller's buffers are free again
         std::swap(op->in, op->in_alt);
         done += n;
     }
@@ -771,7 +796,7 @@ int32_t push_rows(igl_op* op, Staging& S, const ArrowArray* batch, int32_t (*flu
     int64_t done = 0;
     while (done < batch->length) {
         const int64_t take = std::min<int64_t>(batch->length - done, S.chunk_rows - S.rows);
-        IGL_TRY(S.append(batch, done, take));
+        { TraceScope ts(op->trace, TR_STAGE); IGL_TRY(S.append(batch, done, take)); }
         done += take;
         if (S.rows == S.chunk_rows) IGL_TRY(flush(op));
     }
@@ -920,6 +945,7 @@ int32_t igl_op_schema(igl_op* op, struct ArrowSchema* out) {
 int32_t igl_op_push_build(igl_op* op, const struct ArrowArray* batch) {
     if (!op || !op->is_join) return fail(IGL_ERR_INVALID_ARG, "igl_op_push_build: not a join operator");
     if (op->build_done) return fail(IGL_ERR_INVALID_ARG, "igl_op_push_build: build side already finished");
+    TraceScope ts_build(op->trace, TR_BUILD);
     DeviceGuard g(op->ctx->device);
     if (batch && batch_is_direct(op->build, batch) && (op->build_rows & 7) == 0) {
         // page-locked batch: straight from the caller's buffers to the end of the device columns
@@ -961,6 +987,7 @@ int32_t igl_op_finish_build(igl_op* op) {
 
 int32_t igl_op_push(igl_op* op, const struct ArrowArray* batch) {
     if (!op) return fail(IGL_ERR_INVALID_ARG, "igl_op_push: NULL operator");
+    TraceScope ts_push(op->trace, TR_PUSH);
     if (op->input_done) return fail(IGL_ERR_INVALID_ARG, "igl_op_push: input already finished");
     DeviceGuard g(op->ctx->device);
     if (op->is_join) {
@@ -989,6 +1016,7 @@ int32_t igl_op_finish_input(igl_op* op) {
 
 int32_t igl_op_pull(igl_op* op, struct ArrowArray* out) {
     if (!op || !out) return fail(IGL_ERR_INVALID_ARG, "igl_op_pull: NULL argument");
+    TraceScope ts_pull(op->trace, TR_PULL);
     if (op->ready.empty()) return op->input_done ? IGL_EOS : IGL_AGAIN;
     OutBatch& f = op->ready.front();
     if (f.done) {
@@ -1012,6 +1040,12 @@ int32_t igl_op_pull(igl_op* op, struct ArrowArray* out) {
 
 void igl_op_destroy(igl_op* op) {
     if (!op) return;
+    if (op->trace.on) {
+        static const char* nm[8] = {"stage", "end_chunk", "upload", "begin_chunk", "wait_upload", "pull", "push_build", "push"};
+        fprintf(stderr, "[igl_op trace]");
+        for (int i = 0; i < 8; ++i) fprintf(stderr, " %s=%.1fms/%ld", nm[i], op->trace.t[i] * 1e3, op->trace.n[i]);
+        fprintf(stderr, "\n");
+    }
     DeviceGuard g(op->ctx->device);
     if (op->s_down) cudaStreamSynchronize(op->s_down);
     if (op->s_up) cudaStreamSynchronize(op->s_up);

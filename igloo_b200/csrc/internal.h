@@ -76,6 +76,15 @@ struct igl_ctx {
 };
 
 namespace igl {
+// IGL_TRACE=1: host wall-clock per named section, printed at process exit (api.cu).
+void trace_add(const char* name, double seconds);
+bool trace_on();
+double trace_now();
+struct HostTrace {
+    const char* name; double t0;
+    explicit HostTrace(const char* n) : name(n), t0(trace_on() ? trace_now() : 0.0) {}
+    ~HostTrace() { if (trace_on()) trace_add(name, trace_now() - t0); }
+};
 struct DeviceGuard {
     int prev = -1;
     explicit DeviceGuard(int dev) {

@@ -1146,6 +1146,7 @@ int32_t flat_fill_params(igl_join* j, FlatProbeParams& F, igl_dev_col* out, int6
 // First half: scratch, launch, header copy — everything is queued on `st`, nothing waits.
 int32_t flat_probe_launch(igl_join* j, FlatProbeParams& F, bool seg, int64_t nrows, long long nchunks, int64_t out_capacity,
                           cudaStream_t st) {
+    HostTrace tr_all("probe.flat");
     igl_ctx* ctx = j->ctx;
     const int nl = F.n_left, nr = F.n_right;
     // DENSE form (see the kernel): needs room for every probe row and 32-bit row numbers
@@ -1175,9 +1176,13 @@ int32_t flat_probe_launch(igl_join* j, FlatProbeParams& F, bool seg, int64_t nro
     F.miss_counter = &((PipeHeader*)j->scratch)->aux[2];
     const void* kfn = flat_kernel_for(F.key_type, dense, seg);
     const size_t fsmem = (size_t)F.stage_bytes * kFlatStages;
-    IGL_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
     int per_sm = 0;
-    IGL_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, kFlatThreads, fsmem));
+    {
+        HostTrace tr("probe.flat.attr");
+        IGL_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
+        IGL_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, kFlatThreads, fsmem));
+    }
+    HostTrace tr_launch("probe.flat.launch");
     if (const char* e = getenv("IGL_FLAT_CTAS_PER_SM")) per_sm = std::min(per_sm, std::max(1, atoi(e)));   // experiments
     const int grid = (int)std::min<long long>(nchunks, (long long)ctx->sm_count * std::max(per_sm, 1));
     void* kargs[] = {&F};
@@ -1488,6 +1493,7 @@ int32_t join_probe_begin(igl_join* j, const igl_dev_col* left, int64_t nrows, ig
     cudaEventRecord(j->ev[3], st);
     j->ev_probe = false;
     if (j->log2_parts > 0) {   // reorder the probe chunk the same way, so it walks the table region by region
+        HostTrace tr("probe.partition");
         if (radix_partition_supported(left, nl)) {
             if (nrows > j->part_left_rows) {
                 for (void* p : j->part_left) pool_free(ctx, p);

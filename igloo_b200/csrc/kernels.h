@@ -43,18 +43,25 @@ bool radix_partition_supported(const igl_dev_col* cols, int ncols);
 int32_t radix_partition(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int key_col, long long nrows, int log2_parts,
                         void* const* dst, void* scratch, cudaStream_t st);
 
-// (destination x partition) split without host synchronisation (partition.cu; driven by shuffle.cu)
-int32_t radix_histogram_async(igl_ctx* ctx, const igl_dev_col* key, long long nrows, int ndest, int log2_parts,
-                              unsigned long long* dev_hist, cudaStream_t st);
-int32_t radix_scatter_bins_async(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int key_col, long long nrows, int ndest,
-                                 int log2_parts, void* const* dst, const unsigned long long* dev_offsets,
+// (destination x partition) split without host synchronisation (partition.cu; driven by shuffle.cu).
+// HotKeys: a small device-resident set of canonical keys that go to the fixed destination `dest`
+// instead of the one their hash names (table == NULL: none); `ndest` destinations exist, the hash
+// picks among the first `nhash`.
+struct HotKeys { const unsigned long long* table = nullptr; int mask = 0; int dest = 0; };
+int32_t radix_histogram_async(igl_ctx* ctx, const igl_dev_col* key, long long nrows, int ndest, int nhash, int log2_parts,
+                              const HotKeys& hot, unsigned long long* dev_hist, cudaStream_t st);
+int32_t radix_scatter_bins_async(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int key_col, long long nrows, int ndest, int nhash,
+                                 int log2_parts, const HotKeys& hot, void* const* dst, const unsigned long long* dev_offsets,
                                  unsigned long long* dev_cursor, cudaStream_t st);
+// canonical form of every (nrows / nsamples)-th key
+int32_t sample_keys_async(igl_ctx* ctx, const igl_dev_col* key, long long nrows, int nsamples, unsigned long long* dev_out, cudaStream_t st);
 
 // ---- segmented probe input (join.cu; used by the multi-GPU join, shuffle.cu) ---------------------
 // The probe side as a list of contiguous runs that may live in different buffers — the staging
 // buffers of this and the peer GPUs.  Runs are walked in list order; each starts on a 128-row
 // boundary of the (virtual) output, so `chunk0` is its first 128-row chunk.
-constexpr int kSegMaxSrc = 8;
+constexpr int kSegMaxSrc = 16;       // up to 8 ranks' staging buffers + a local prefetched copy of each
+constexpr int kShufMaxRanks = 8;
 constexpr int kSegChunkRows = 128;   // rows per chunk of the flat probe kernel (join.cu asserts it)
 constexpr int kSegAlignRows = 4;     // a run starts on a multiple of this many rows of its source: 16 bytes for 4-byte columns
 struct ProbeSeg {

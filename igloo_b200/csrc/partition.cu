@@ -18,6 +18,7 @@
 // all go to partition 0 (they must meet: NULL == NULL in the reference).
 #include "device_utils.cuh"
 #include "internal.h"
+#include "kernels.h"
 
 namespace igl {
 
@@ -140,29 +141,55 @@ constexpr int kRadixRowsPerThread = 8;
 constexpr int kRadixTile = kRadixThreads * kRadixRowsPerThread;   // 4096 rows per tile: long write runs per partition
 
 // bin = destination * 2^log2_parts + partition: destination from the LOW 32 hash bits (as
-// part_dest), partition from the TOP bits (as the join table).  ndest == 1: partition only.
-__device__ __forceinline__ int radix_bin_of(uint64_t h, int ndest, int log2_parts) {
+// part_dest), partition from the TOP bits (as the join table).  nhash == 1: partition only.
+//
+// Hot keys (skewed probe sides): a few keys carry so many probe rows that the GPU
+// their hash names would receive far more than its share.  Keys listed in `H` are routed to the
+// fixed destination H.dest instead — the probe side keeps them where they are (H.dest = this
+// rank), the build side sends them to one extra "every rank reads this" destination — so the
+// hash decides only the rest.  H.table: open-addressing set of canonical keys, kHotEmpty = free.
+constexpr unsigned long long kHotEmpty = 0xFFFFFFFFFFFFFFFFull;
+__device__ __forceinline__ int radix_bin_of(uint64_t canon, uint64_t h, int nhash, int log2_parts, const HotKeys& H) {
     const int part = log2_parts ? (int)(h >> (64 - log2_parts)) : 0;
-    const int dest = ndest > 1 ? (int)(((h & 0xFFFFFFFFull) * (uint64_t)ndest) >> 32) : 0;
+    int dest = nhash > 1 ? (int)(((h & 0xFFFFFFFFull) * (uint64_t)nhash) >> 32) : 0;
+    if (H.table) {
+        uint32_t s = (uint32_t)(h >> 24) & (uint32_t)H.mask;
+        while (true) {
+            const unsigned long long k = __ldg(H.table + s);
+            if (k == canon) { dest = H.dest; break; }
+            if (k == kHotEmpty) break;
+            s = (s + 1) & (uint32_t)H.mask;
+        }
+    }
     return (dest << log2_parts) | part;
 }
-__device__ __forceinline__ int radix_part(const void* keys, int type, long long i, int ndest, int log2_parts) {
+__device__ __forceinline__ int radix_part(const void* keys, int type, long long i, int nhash, int log2_parts, const HotKeys& H) {
     const uint64_t raw = type == IGL_T_I32 ? (uint64_t)(uint32_t)((const int32_t*)keys)[i] : ((const uint64_t*)keys)[i];
-    return radix_bin_of(mix64(part_canon(type, raw)), ndest, log2_parts);
+    const uint64_t c = part_canon(type, raw);
+    return radix_bin_of(c, mix64(c), nhash, log2_parts, H);
 }
 
-__global__ void __launch_bounds__(512) radix_hist_kernel(const void* __restrict__ keys, int type, long long n, int ndest,
-                                                                   int log2_parts, unsigned long long* hist) {
+__global__ void __launch_bounds__(512) radix_hist_kernel(const void* __restrict__ keys, int type, long long n, int ndest, int nhash,
+                                                                   int log2_parts, unsigned long long* hist, HotKeys H) {
     __shared__ unsigned int s_hist[kRadixMaxParts];
     const int nparts = ndest << log2_parts;
     for (int p = threadIdx.x; p < nparts; p += blockDim.x) s_hist[p] = 0;
     __syncthreads();
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
-        atomicAdd(&s_hist[radix_part(keys, type, i, ndest, log2_parts)], 1u);
+        atomicAdd(&s_hist[radix_part(keys, type, i, nhash, log2_parts, H)], 1u);
     __syncthreads();
     for (int p = threadIdx.x; p < nparts; p += blockDim.x)
         if (s_hist[p]) atomicAdd(&hist[p], (unsigned long long)s_hist[p]);
+}
+
+// Every (n / nsamples)-th key in canonical form: the host counts them to find hot keys.
+__global__ void sample_keys_kernel(const void* __restrict__ keys, int type, long long n, int nsamples, unsigned long long* out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nsamples) return;
+    const long long row = (long long)(((__int128)i * n) / nsamples);
+    const uint64_t raw = type == IGL_T_I32 ? (uint64_t)(uint32_t)((const int32_t*)keys)[row] : ((const uint64_t*)keys)[row];
+    out[i] = part_canon(type, raw);
 }
 
 // offsets[p] = sum of hist[0..p) ; offsets[nparts] = total ; cursor[] zeroed.
@@ -188,6 +215,8 @@ struct RadixParams {
     uint8_t shift[kPartMaxCols];
     uint32_t stage_off[kPartMaxCols];   // byte offset of each column's staging area in dynamic shared memory
     int ncols, key_col, key_type, log2_parts, ndest;
+    int nhash;                          // range of the hashed destination (== ndest unless hot keys add a destination)
+    HotKeys hot;
     long long n;
     const unsigned long long* offsets;  // [bins]: first row of the bin inside its destination's buffer
     unsigned long long* cursor;         // [bins]
@@ -215,7 +244,8 @@ __device__ __forceinline__ void radix_tile(const RadixParams& P, uint8_t* stage,
 #pragma unroll
     for (int r = 0; r < kRadixRowsPerThread; ++r) {
         const bool ok = FULL || (r * kRadixThreads + tid) < rows;
-        part[r] = radix_bin_of(mix64(part_canon(P.key_type, keyraw[r])), P.ndest, P.log2_parts);
+        const uint64_t ck = part_canon(P.key_type, keyraw[r]);
+        part[r] = radix_bin_of(ck, mix64(ck), P.nhash, P.log2_parts, P.hot);
         rank[r] = 0;
         if (ok) rank[r] = atomicAdd(&s_cnt[part[r]], 1u);
         else part[r] = -1;
@@ -385,7 +415,8 @@ __global__ void __launch_bounds__(kRtThreads, 1) radix_scatter_bulk_kernel(const
                 bin[r] = -1;
                 if (i < rows) {
                     const uint64_t raw = P.key_type == IGL_T_I32 ? (uint64_t)((const uint32_t*)kc)[i] : ((const uint64_t*)kc)[i];
-                    bin[r] = radix_bin_of(mix64(part_canon(P.key_type, raw)), P.ndest, P.log2_parts);
+                    const uint64_t ck = part_canon(P.key_type, raw);
+                    bin[r] = radix_bin_of(ck, mix64(ck), P.nhash, P.log2_parts, P.hot);
                     rank[r] = atomicAdd(&cnt[bin[r]], 1u);
                 }
             }
@@ -507,7 +538,7 @@ int32_t radix_partition(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int ke
     unsigned long long* cursor = offsets + (nparts + 1);
     IGL_CUDA_OK(cudaMemsetAsync(hist, 0, sizeof(unsigned long long) * (nparts + 1), st));
     RadixParams P{};
-    P.ncols = ncols; P.key_col = key_col; P.key_type = cols[key_col].type; P.log2_parts = log2_parts; P.ndest = 1; P.n = nrows;
+    P.ncols = ncols; P.key_col = key_col; P.key_type = cols[key_col].type; P.log2_parts = log2_parts; P.ndest = 1; P.nhash = 1; P.n = nrows;
     P.offsets = offsets; P.cursor = cursor;
     uint32_t off = 0;
     for (int c = 0; c < ncols; ++c) {
@@ -521,13 +552,18 @@ int32_t radix_partition(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int ke
     }
     if (!radix_partition_supported(cols, ncols)) return fail(IGL_ERR_UNSUPPORTED, "radix_partition: row too wide (%u bytes of staging)", off);
     if (nrows > 0) {
-        radix_hist_kernel<<<ctx->sm_count * 4, 512, 0, st>>>(cols[key_col].data, P.key_type, nrows, 1, log2_parts, hist);
+        HostTrace tr("partition.hist");
+        radix_hist_kernel<<<ctx->sm_count * 4, 512, 0, st>>>(cols[key_col].data, P.key_type, nrows, 1, 1, log2_parts, hist, HotKeys{});
         IGL_CUDA_OK(cudaGetLastError());
     }
-    radix_scan_kernel<<<1, kRadixMaxParts, 0, st>>>(hist, offsets, cursor, nparts);
-    IGL_CUDA_OK(cudaGetLastError());
+    {
+        HostTrace tr("partition.scan");
+        radix_scan_kernel<<<1, kRadixMaxParts, 0, st>>>(hist, offsets, cursor, nparts);
+        IGL_CUDA_OK(cudaGetLastError());
+    }
     ctx->launches += 2;
     if (nrows > 0) {
+        HostTrace tr("partition.scatter");
         IGL_CUDA_OK(launch_radix_scatter(ctx, P, off, st));
         ctx->launches++;
     }
@@ -537,16 +573,24 @@ int32_t radix_partition(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int ke
 // ---- the two halves of a (destination x partition) split, stream-ordered and without any
 // host synchronisation (shuffle.cu drives them) --------------------------------------------
 // dev_hist[ndest << log2_parts] is zeroed and filled.
-int32_t radix_histogram_async(igl_ctx* ctx, const igl_dev_col* key, long long nrows, int ndest, int log2_parts,
-                              unsigned long long* dev_hist, cudaStream_t st) {
-    if (ndest < 1 || ndest > kPartMaxParts || log2_parts < 0 || (ndest << log2_parts) > kRadixMaxParts)
+int32_t radix_histogram_async(igl_ctx* ctx, const igl_dev_col* key, long long nrows, int ndest, int nhash, int log2_parts,
+                              const HotKeys& hot, unsigned long long* dev_hist, cudaStream_t st) {
+    if (ndest < 1 || ndest > kPartMaxParts || nhash < 1 || nhash > ndest || log2_parts < 0 || (ndest << log2_parts) > kRadixMaxParts)
         return fail(IGL_ERR_UNSUPPORTED, "ndest in [1, %d] and ndest << log2_parts <= %d", kPartMaxParts, kRadixMaxParts);
     if (key->type != IGL_T_I32 && key->type != IGL_T_I64 && key->type != IGL_T_F64)
         return fail(IGL_ERR_UNSUPPORTED, "partition key must be Int32/Int64/Float64");
     if (key->validity) return fail(IGL_ERR_UNSUPPORTED, "nullable join keys are not repartitioned across GPUs");
     IGL_CUDA_OK(cudaMemsetAsync(dev_hist, 0, sizeof(unsigned long long) * ((size_t)ndest << log2_parts), st));
     if (nrows == 0) return IGL_OK;
-    radix_hist_kernel<<<ctx->sm_count * 4, 512, 0, st>>>(key->data, key->type, nrows, ndest, log2_parts, dev_hist);
+    radix_hist_kernel<<<ctx->sm_count * 4, 512, 0, st>>>(key->data, key->type, nrows, ndest, nhash, log2_parts, dev_hist, hot);
+    IGL_CUDA_OK(cudaGetLastError());
+    ctx->launches++;
+    return IGL_OK;
+}
+
+int32_t sample_keys_async(igl_ctx* ctx, const igl_dev_col* key, long long nrows, int nsamples, unsigned long long* dev_out, cudaStream_t st) {
+    if (nrows <= 0 || nsamples <= 0) return IGL_OK;
+    sample_keys_kernel<<<(nsamples + 255) / 256, 256, 0, st>>>(key->data, key->type, nrows, nsamples, dev_out);
     IGL_CUDA_OK(cudaGetLastError());
     ctx->launches++;
     return IGL_OK;
@@ -554,16 +598,16 @@ int32_t radix_histogram_async(igl_ctx* ctx, const igl_dev_col* key, long long nr
 
 // Rows of `cols` are written to dst[c] (one buffer per column, all bins inside it) at
 // dev_offsets[bin] + arrival order; dev_cursor[bins] must be zero.  Bins are destination-major.
-int32_t radix_scatter_bins_async(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int key_col, long long nrows, int ndest,
-                                 int log2_parts, void* const* dst, const unsigned long long* dev_offsets,
+int32_t radix_scatter_bins_async(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int key_col, long long nrows, int ndest, int nhash,
+                                 int log2_parts, const HotKeys& hot, void* const* dst, const unsigned long long* dev_offsets,
                                  unsigned long long* dev_cursor, cudaStream_t st) {
-    if (ndest < 1 || ndest > kPartMaxParts || log2_parts < 0 || (ndest << log2_parts) > kRadixMaxParts)
+    if (ndest < 1 || ndest > kPartMaxParts || nhash < 1 || nhash > ndest || log2_parts < 0 || (ndest << log2_parts) > kRadixMaxParts)
         return fail(IGL_ERR_UNSUPPORTED, "ndest in [1, %d] and ndest << log2_parts <= %d", kPartMaxParts, kRadixMaxParts);
     if (ncols < 1 || ncols > kPartMaxCols || key_col < 0 || key_col >= ncols) return fail(IGL_ERR_INVALID_ARG, "radix_scatter_bins: bad column set");
     if (!radix_partition_supported(cols, ncols)) return fail(IGL_ERR_UNSUPPORTED, "columns cannot be radix-partitioned (nullable, not fixed-width, or too wide)");
     if (nrows == 0) return IGL_OK;
     RadixParams P{};
-    P.ncols = ncols; P.key_col = key_col; P.key_type = cols[key_col].type; P.log2_parts = log2_parts; P.ndest = ndest; P.n = nrows;
+    P.ncols = ncols; P.key_col = key_col; P.key_type = cols[key_col].type; P.log2_parts = log2_parts; P.ndest = ndest; P.nhash = nhash; P.hot = hot; P.n = nrows;
     P.offsets = dev_offsets; P.cursor = dev_cursor;
     uint32_t off = 0;
     for (int c = 0; c < ncols; ++c) {
@@ -660,7 +704,7 @@ int32_t igl_partition_histogram_radix(igl_ctx* ctx, const igl_dev_col* key, int6
     cudaStream_t st = pick_stream(ctx, stream);
     IGL_CUDA_OK(cudaMemsetAsync(dev_hist, 0, sizeof(int64_t) * ((size_t)ndest << log2_parts), st));
     if (nrows == 0) return IGL_OK;
-    radix_hist_kernel<<<ctx->sm_count * 4, 512, 0, st>>>(key->data, key->type, nrows, ndest, log2_parts, (unsigned long long*)dev_hist);
+    radix_hist_kernel<<<ctx->sm_count * 4, 512, 0, st>>>(key->data, key->type, nrows, ndest, ndest, log2_parts, (unsigned long long*)dev_hist, HotKeys{});
     IGL_CUDA_OK(cudaGetLastError());
     ctx->launches++;
     return IGL_OK;
@@ -681,7 +725,7 @@ int32_t igl_partition_scatter_radix(igl_ctx* ctx, const igl_dev_col* cols, int32
     cudaStream_t st = pick_stream(ctx, stream);
     const int bins = ndest << log2_parts;
     RadixParams P{};
-    P.ncols = ncols; P.key_col = key_col; P.key_type = cols[key_col].type; P.log2_parts = log2_parts; P.ndest = ndest; P.n = nrows;
+    P.ncols = ncols; P.key_col = key_col; P.key_type = cols[key_col].type; P.log2_parts = log2_parts; P.ndest = ndest; P.nhash = ndest; P.n = nrows;
     uint32_t off = 0;
     for (int c = 0; c < ncols; ++c) {
         const int t = cols[c].type;

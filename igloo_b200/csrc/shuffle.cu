@@ -42,6 +42,7 @@
 
 #include <algorithm>
 #include <cstring>
+#include <map>
 #include <memory>
 
 namespace igl {
@@ -135,9 +136,15 @@ extern "C" {
 
 int32_t igl_shuffle_plan(int32_t nranks, int32_t rank, int32_t log2_parts, const int64_t* counts, int64_t* src_offsets,
                          int32_t* seg_src, int64_t* seg_row0, int64_t* seg_rows, int64_t* total_rows) {
-    if (nranks < 1 || nranks > 16 || rank < 0 || rank >= nranks || log2_parts < 0 || ((int64_t)nranks << log2_parts) > 1024 || !counts || !src_offsets)
+    return igl_shuffle_plan_ex(nranks, rank, log2_parts, 0, counts, src_offsets, seg_src, seg_row0, seg_rows, total_rows);
+}
+
+int32_t igl_shuffle_plan_ex(int32_t nranks, int32_t rank, int32_t log2_parts, int32_t broadcast, const int64_t* counts,
+                            int64_t* src_offsets, int32_t* seg_src, int64_t* seg_row0, int64_t* seg_rows, int64_t* total_rows) {
+    if (nranks < 1 || nranks > 16 || rank < 0 || rank >= nranks || log2_parts < 0 || broadcast < 0 || broadcast > 1 ||
+        ((int64_t)(nranks + broadcast) << log2_parts) > 1024 || !counts || !src_offsets)
         return fail(IGL_ERR_INVALID_ARG, "igl_shuffle_plan: bad arguments");
-    const int parts = 1 << log2_parts, bins = nranks << log2_parts;
+    const int parts = 1 << log2_parts, bins = (nranks + broadcast) << log2_parts;
     for (int s = 0; s < nranks; ++s) {
         int64_t off = 0;
         for (int b = 0; b < bins; ++b) {
@@ -148,15 +155,17 @@ int32_t igl_shuffle_plan(int32_t nranks, int32_t rank, int32_t log2_parts, const
         }
     }
     int64_t total = 0;
+    const int per_part = nranks * (1 + broadcast);
     for (int p = 0; p < parts; ++p)
-        for (int s = 0; s < nranks; ++s) {
-            const size_t b = (size_t)s * bins + ((size_t)rank << log2_parts) + p;
-            const int i = p * nranks + s;
-            if (seg_src) seg_src[i] = s;
-            if (seg_row0) seg_row0[i] = src_offsets[b];
-            if (seg_rows) seg_rows[i] = counts[b];
-            total += counts[b];
-        }
+        for (int k = 0; k < 1 + broadcast; ++k)        // the rank's own bins, then the "every rank reads this" bins
+            for (int s = 0; s < nranks; ++s) {
+                const size_t b = (size_t)s * bins + ((size_t)(k ? nranks : rank) << log2_parts) + p;
+                const int i = p * per_part + k * nranks + s;
+                if (seg_src) seg_src[i] = s;
+                if (seg_row0) seg_row0[i] = src_offsets[b];
+                if (seg_rows) seg_rows[i] = counts[b];
+                total += counts[b];
+            }
     if (total_rows) *total_rows = total;
     return IGL_OK;
 }
@@ -266,19 +275,88 @@ struct igl_join_shuffle {
     void* h_segs = nullptr;                 // pinned
     size_t segs_bytes = 0;
     int* d_flag = nullptr;
+    // hot keys (skewed probe sides): device set, sample and candidate buffers
+    unsigned long long* d_hot = nullptr;       // [kHotSlots] open-addressing set of canonical keys
+    unsigned long long* d_samples = nullptr;   // [kHotSamples] then [2 * kHotCand] candidates to send, then [nranks][2 * kHotCand] received
+    unsigned long long* h_samples = nullptr;   // pinned mirror of d_samples
     std::vector<void*> out;                 // library-owned output columns (+ validity for a Left/Full join)
     std::vector<void*> out_valid;
     int64_t out_cap = 0;
     int64_t out_rows = 0;
     cudaEvent_t ev[7] = {};
     cudaEvent_t ev_plan = nullptr, ev_wait = nullptr, ev_l[3] = {};   // second stream: probe-side partition start / end / barrier end
-    cudaStream_t stream2 = nullptr;
+    cudaStream_t stream2 = nullptr, stream3 = nullptr;
+    cudaEvent_t ev_copy = nullptr;
+    double last_build_ms = -1.0;            // measured build phase of the previous run: sizes the probe-side prefetch
     bool timed = false;
-    int64_t stats[8] = {};
+    int64_t stats[12] = {};
     int log2_parts = 0;
 };
 
 namespace {
+
+constexpr int kHotSlots = 512;      // device set size (a power of two)
+constexpr int kHotSamples = 16384;  // probe keys sampled per rank
+constexpr int kHotCand = 128;       // (key, count) candidates each rank contributes; also the most keys kept
+
+// Finds the keys that carry an outsized share of the probe rows: every rank samples its probe keys,
+// counts them on the host, contributes its most frequent ones; the lists are all-gathered and merged
+// the same way on every rank (keys whose share of all samples is at least 1/1000, at most kHotCand
+// of them), and the set is uploaded to js->d_hot.  *nhot = 0: nothing stands out.
+int32_t find_hot_keys(igl_join_shuffle* js, const igl_dev_col& key, int64_t nrows, cudaStream_t st, int32_t* nhot) {
+    igl_ctx* ctx = js->ctx;
+    Comm* comm = (Comm*)ctx->comm;
+    const int W = comm->nranks;
+    *nhot = 0;
+    const int ns = (int)std::min<int64_t>(kHotSamples, nrows);
+    unsigned long long* d_cand = js->d_samples + kHotSamples;
+    unsigned long long* d_all = d_cand + 2 * kHotCand;
+    unsigned long long* h_cand = js->h_samples + kHotSamples;
+    unsigned long long* h_all = h_cand + 2 * kHotCand;
+    if (ns > 0) {
+        IGL_TRY(sample_keys_async(ctx, &key, nrows, ns, js->d_samples, st));
+        IGL_CUDA_OK(cudaMemcpyAsync(js->h_samples, js->d_samples, sizeof(unsigned long long) * ns, cudaMemcpyDeviceToHost, st));
+        IGL_CUDA_OK(cudaStreamSynchronize(st));
+    }
+    std::sort(js->h_samples, js->h_samples + ns);
+    std::vector<std::pair<unsigned long long, unsigned long long>> runs;   // (count, key)
+    for (int i = 0; i < ns;) {
+        int j = i;
+        while (j < ns && js->h_samples[j] == js->h_samples[i]) ++j;
+        if (j - i >= 4) runs.push_back({(unsigned long long)(j - i), js->h_samples[i]});
+        i = j;
+    }
+    std::sort(runs.begin(), runs.end(), [](const auto& a, const auto& b) { return a.first != b.first ? a.first > b.first : a.second < b.second; });
+    for (int i = 0; i < kHotCand; ++i) {
+        h_cand[2 * i] = i < (int)runs.size() ? runs[i].second : 0;
+        h_cand[2 * i + 1] = i < (int)runs.size() ? runs[i].first : 0;   // count 0 = no candidate
+    }
+    IGL_CUDA_OK(cudaMemcpyAsync(d_cand, h_cand, sizeof(unsigned long long) * 2 * kHotCand, cudaMemcpyHostToDevice, st));
+    IGL_NCCL_OK(g_nccl.AllGather(d_cand, d_all, sizeof(unsigned long long) * 2 * kHotCand, kNcclUint8, comm->comm, st));
+    IGL_CUDA_OK(cudaMemcpyAsync(h_all, d_all, sizeof(unsigned long long) * 2 * kHotCand * W, cudaMemcpyDeviceToHost, st));
+    IGL_CUDA_OK(cudaStreamSynchronize(st));
+    std::map<unsigned long long, unsigned long long> merged;
+    for (int i = 0; i < W * kHotCand; ++i)
+        if (h_all[2 * i + 1]) merged[h_all[2 * i]] += h_all[2 * i + 1];
+    const unsigned long long floor_count = std::max<unsigned long long>(8, (unsigned long long)W * kHotSamples / 1000);
+    std::vector<std::pair<unsigned long long, unsigned long long>> hotv;
+    for (auto& kv : merged)
+        if (kv.second >= floor_count && kv.first != 0xFFFFFFFFFFFFFFFFull) hotv.push_back({kv.second, kv.first});
+    std::sort(hotv.begin(), hotv.end(), [](const auto& a, const auto& b) { return a.first != b.first ? a.first > b.first : a.second < b.second; });
+    if ((int)hotv.size() > kHotCand) hotv.resize(kHotCand);
+    if (hotv.empty()) return IGL_OK;
+    std::vector<unsigned long long> table(kHotSlots, 0xFFFFFFFFFFFFFFFFull);
+    for (auto& hk : hotv) {
+        uint32_t sl = (uint32_t)(mix64(hk.second) >> 24) & (kHotSlots - 1);
+        while (table[sl] != 0xFFFFFFFFFFFFFFFFull) sl = (sl + 1) & (kHotSlots - 1);
+        table[sl] = hk.second;
+    }
+    memcpy(js->h_samples, table.data(), sizeof(unsigned long long) * kHotSlots);   // pinned staging for the upload
+    IGL_CUDA_OK(cudaMemcpyAsync(js->d_hot, js->h_samples, sizeof(unsigned long long) * kHotSlots, cudaMemcpyHostToDevice, st));
+    IGL_CUDA_OK(cudaStreamSynchronize(st));
+    *nhot = (int32_t)hotv.size();
+    return IGL_OK;
+}
 
 int floor_log2(int v) { int l = 0; while ((2 << l) <= v) ++l; return l; }
 
@@ -321,8 +399,8 @@ int32_t igl_comm_unique_id(uint8_t id_out[128]) {
 }
 
 int32_t igl_comm_init(igl_ctx* ctx, int32_t nranks, int32_t rank, const uint8_t id[128]) {
-    if (!ctx || !id || nranks < 1 || nranks > kSegMaxSrc || rank < 0 || rank >= nranks)
-        return fail(IGL_ERR_INVALID_ARG, "igl_comm_init: bad arguments (1 <= nranks <= %d)", kSegMaxSrc);
+    if (!ctx || !id || nranks < 1 || nranks > kShufMaxRanks || rank < 0 || rank >= nranks)
+        return fail(IGL_ERR_INVALID_ARG, "igl_comm_init: bad arguments (1 <= nranks <= %d)", kShufMaxRanks);
     if (ctx->comm) return fail(IGL_ERR_INVALID_ARG, "igl_comm_init: this context already has a communicator");
     IGL_TRY(nccl_load());
     DeviceGuard g(ctx->device);
@@ -378,11 +456,17 @@ int32_t igl_join_shuffle_create(igl_ctx* ctx, int32_t join_type, const int32_t* 
     if (rc >= 0) { rc = pool_alloc(ctx, sizeof(ShuffleMsg) * W, &p); js->d_recv = (ShuffleMsg*)p; }
     if (rc >= 0) { rc = pool_alloc(ctx, sizeof(unsigned long long) * 4 * kMsgBins, &p); js->d_plan = (unsigned long long*)p; }
     if (rc >= 0) { rc = pool_alloc(ctx, 256, &p); js->d_flag = (int*)p; }
+    const size_t hot_words = (size_t)kHotSamples + 2 * kHotCand * (1 + W);
+    if (rc >= 0) { rc = pool_alloc(ctx, sizeof(unsigned long long) * kHotSlots, &p); js->d_hot = (unsigned long long*)p; }
+    if (rc >= 0) { rc = pool_alloc(ctx, sizeof(unsigned long long) * hot_words, &p); js->d_samples = (unsigned long long*)p; }
+    if (rc >= 0 && cudaHostAlloc((void**)&js->h_samples, sizeof(unsigned long long) * hot_words, cudaHostAllocDefault) != cudaSuccess) rc = fail(IGL_ERR_OOM, "pinned allocation failed");
     if (rc >= 0 && cudaMemset(js->d_flag, 0, 256) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "cudaMemset failed");
     for (auto& ev : js->ev) if (rc >= 0 && cudaEventCreate(&ev) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "cudaEventCreate failed");
     for (auto& ev : js->ev_l) if (rc >= 0 && cudaEventCreate(&ev) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "cudaEventCreate failed");
     if (rc >= 0 && (cudaEventCreate(&js->ev_plan) != cudaSuccess || cudaEventCreate(&js->ev_wait) != cudaSuccess)) rc = fail(IGL_ERR_CUDA, "cudaEventCreate failed");
     if (rc >= 0 && cudaStreamCreateWithFlags(&js->stream2, cudaStreamNonBlocking) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "cudaStreamCreate failed");
+    if (rc >= 0 && cudaStreamCreateWithFlags(&js->stream3, cudaStreamNonBlocking) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "cudaStreamCreate failed");
+    if (rc >= 0 && cudaEventCreateWithFlags(&js->ev_copy, cudaEventDisableTiming) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "cudaEventCreate failed");
     if (rc < 0) { igl_join_shuffle_destroy(js.release()); return rc; }
     *out = js.release();
     return IGL_OK;
@@ -408,8 +492,6 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
         if (!radix_partition_supported(in[sd], S.ncols)) return fail(IGL_ERR_UNSUPPORTED, "%s side cannot be radix-partitioned (fixed-width columns, at most 46 bytes per row)", sd ? "left" : "right");
         if (n_in[sd] >= (1ll << 32)) return fail(IGL_ERR_UNSUPPORTED, "at most 2^32-1 rows per rank and side");
     }
-    const int lp_h = std::min(10, floor_log2(kMsgBins / W));   // the histogram's partition count; the join's is chosen once the totals are known
-    const int bins_h = W << lp_h;
     cudaEventRecord(js->ev[0], st);
     // ---- staging buffers: this rank's rows, bin by bin (grow-only; peers re-map them when `gen` changes)
     for (int sd = 0; sd < 2; ++sd) {
@@ -428,42 +510,83 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
         js->h_send->n_rows[sd] = n_in[sd];
         js->h_send->gen[sd] = S.gen;
     }
-    // ---- 1. histograms, 2. the all-gather
-    IGL_CUDA_OK(cudaMemcpyAsync(js->d_send, js->h_send, offsetof(ShuffleMsg, hist), cudaMemcpyHostToDevice, st));
-    for (int sd = 0; sd < 2; ++sd) {
-        IGL_CUDA_OK(cudaMemsetAsync(js->d_send->hist[sd], 0, sizeof(unsigned long long) * kMsgBins, st));
-        IGL_TRY(radix_histogram_async(ctx, &in[sd][js->side[sd].key], n_in[sd], W, lp_h, js->d_send->hist[sd], st));
-    }
-    IGL_NCCL_OK(g_nccl.AllGather(js->d_send, js->d_recv, sizeof(ShuffleMsg), kNcclUint8, comm->comm, st));
-    IGL_CUDA_OK(cudaMemcpyAsync(js->h_recv, js->d_recv, sizeof(ShuffleMsg) * W, cudaMemcpyDeviceToHost, st));
+    // ---- 1. histograms, 2. the all-gather.  nd[side] destinations (the build side gets one more,
+    // "every rank reads this", when hot keys are in play), lp_h partitions in the histogram; the
+    // join's own partition count is chosen once the totals are known and the counts are folded.
+    int nd[2] = {W, W};
+    HotKeys hot[2];
+    int lp_h = std::min(10, floor_log2(kMsgBins / W));
+    auto exchange_counts = [&]() -> int32_t {
+        IGL_CUDA_OK(cudaMemcpyAsync(js->d_send, js->h_send, offsetof(ShuffleMsg, hist), cudaMemcpyHostToDevice, st));
+        for (int sd = 0; sd < 2; ++sd) {
+            IGL_CUDA_OK(cudaMemsetAsync(js->d_send->hist[sd], 0, sizeof(unsigned long long) * kMsgBins, st));
+            IGL_TRY(radix_histogram_async(ctx, &in[sd][js->side[sd].key], n_in[sd], nd[sd], W, lp_h, hot[sd], js->d_send->hist[sd], st));
+        }
+        IGL_NCCL_OK(g_nccl.AllGather(js->d_send, js->d_recv, sizeof(ShuffleMsg), kNcclUint8, comm->comm, st));
+        IGL_CUDA_OK(cudaMemcpyAsync(js->h_recv, js->d_recv, sizeof(ShuffleMsg) * W, cudaMemcpyDeviceToHost, st));
+        return IGL_OK;
+    };
+    IGL_TRY(exchange_counts());
     cudaEventRecord(js->ev[1], st);
     IGL_CUDA_OK(cudaStreamSynchronize(st));
     // every rank has entered this join, so nobody reads last join's staging any more
     for (int sd = 0; sd < 2; ++sd) { for (void* p : js->side[sd].retired) pool_free(ctx, p); js->side[sd].retired.clear(); }
-    // ---- the plan (identical arithmetic on every rank)
     int64_t total_rows[2] = {0, 0};
     for (int s = 0; s < W; ++s) for (int sd = 0; sd < 2; ++sd) total_rows[sd] += js->h_recv[s].n_rows[sd];
+    // ---- skew: if one GPU would receive far more probe rows than its share, find the keys that
+    // cause it (a sample of every rank's probe keys, merged on every rank alike), keep their probe
+    // rows where they are and send their build rows to every rank; then count again.
+    js->stats[10] = 0;
+    {
+        const char* he = getenv("IGL_SHUFFLE_HOTKEYS");
+        const bool allowed = W > 1 && js->mode == IGL_EXCHANGE_P2P && !(he && he[0] == '0');   // the NCCL mode ships destination ranges only
+        int64_t per_dest[kShufMaxRanks] = {}, most = 0;
+        for (int s = 0; s < W; ++s)
+            for (int b = 0; b < (W << lp_h); ++b) per_dest[b >> lp_h] += (int64_t)js->h_recv[s].hist[1][b];
+        for (int d = 0; d < W; ++d) most = std::max(most, per_dest[d]);
+        if (allowed && total_rows[1] >= (1 << 20) && (double)most > 1.15 * (double)total_rows[1] / W && ((W + 1) << 1) <= kMsgBins) {
+            int32_t nhot = 0;
+            IGL_TRY(find_hot_keys(js, in[1][js->side[1].key], n_in[1], st, &nhot));
+            if (nhot > 0) {
+                nd[0] = W + 1;
+                lp_h = std::min(10, floor_log2(kMsgBins / (W + 1)));
+                hot[0] = HotKeys{js->d_hot, kHotSlots - 1, W};    // build rows of hot keys: the broadcast destination
+                hot[1] = HotKeys{js->d_hot, kHotSlots - 1, me};   // probe rows of hot keys: stay here
+                IGL_TRY(exchange_counts());
+                IGL_CUDA_OK(cudaStreamSynchronize(st));
+                js->stats[10] = nhot;
+            }
+        }
+    }
+    // ---- the plan (identical arithmetic on every rank)
     int lp = std::min(lp_h, (int)igl_join_partition_bits(ctx, std::max<int64_t>(1, total_rows[0] / W)));
     js->log2_parts = lp;
-    const int parts = 1 << lp, bins = W << lp, fold = lp_h - lp;
-    std::vector<int64_t> counts((size_t)2 * W * bins), offs((size_t)2 * W * bins);
-    for (int sd = 0; sd < 2; ++sd)
+    const int parts = 1 << lp, fold = lp_h - lp;
+    const int bins = W << lp;                         // probe side (and build side without hot keys)
+    const int binsS[2] = {nd[0] << lp, nd[1] << lp};
+    std::vector<int64_t> cnt[2], off[2];
+    for (int sd = 0; sd < 2; ++sd) {
+        cnt[sd].assign((size_t)W * binsS[sd], 0);
+        off[sd].assign((size_t)W * binsS[sd], 0);
         for (int s = 0; s < W; ++s) {
-            int64_t* c = &counts[((size_t)sd * W + s) * bins];
-            std::fill(c, c + bins, 0);
-            for (int b = 0; b < bins_h; ++b) {
+            int64_t* c = &cnt[sd][(size_t)s * binsS[sd]];
+            for (int b = 0; b < (nd[sd] << lp_h); ++b) {
                 const int d = b >> lp_h, ph = b & ((1 << lp_h) - 1);
                 c[(d << lp) | (ph >> fold)] += (int64_t)js->h_recv[s].hist[sd][b];
             }
         }
-    std::vector<int32_t> seg_src((size_t)2 * W * parts);
-    std::vector<int64_t> seg_row0((size_t)2 * W * parts), seg_rows((size_t)2 * W * parts);
+    }
+    const int nsegS[2] = {W * parts * (nd[0] > W ? 2 : 1), W * parts};
+    std::vector<int32_t> seg_src[2];
+    std::vector<int64_t> seg_row0[2], seg_rows[2];
     int64_t recv_total[2] = {0, 0};
+    for (int sd = 0; sd < 2; ++sd) {
+        seg_src[sd].assign(nsegS[sd], 0); seg_row0[sd].assign(nsegS[sd], 0); seg_rows[sd].assign(nsegS[sd], 0);
+        IGL_TRY(igl_shuffle_plan_ex(W, me, lp, nd[sd] - W, cnt[sd].data(), off[sd].data(), seg_src[sd].data(), seg_row0[sd].data(),
+                                    seg_rows[sd].data(), &recv_total[sd]));
+    }
     for (int sd = 0; sd < 2; ++sd)
-        IGL_TRY(igl_shuffle_plan(W, me, lp, &counts[(size_t)sd * W * bins], &offs[(size_t)sd * W * bins], &seg_src[(size_t)sd * W * parts],
-                                 &seg_row0[(size_t)sd * W * parts], &seg_rows[(size_t)sd * W * parts], &recv_total[sd]));
-    for (int sd = 0; sd < 2; ++sd)
-        for (int b = 0; b < bins; ++b) js->h_plan[(size_t)sd * kMsgBins + b] = (unsigned long long)offs[((size_t)sd * W + me) * bins + b];
+        for (int b = 0; b < binsS[sd]; ++b) js->h_plan[(size_t)sd * kMsgBins + b] = (unsigned long long)off[sd][(size_t)me * binsS[sd] + b];
     IGL_CUDA_OK(cudaMemcpyAsync(js->d_plan, js->h_plan, sizeof(unsigned long long) * 2 * kMsgBins, cudaMemcpyHostToDevice, st));
     IGL_CUDA_OK(cudaMemsetAsync(js->d_plan + 2 * kMsgBins, 0, sizeof(unsigned long long) * 2 * kMsgBins, st));
     // ---- 3. local radix partition of both sides into the staging buffers.  p2p mode: the probe side
@@ -477,14 +600,17 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
         cudaEventRecord(js->ev_l[0], st_l);
     }
     for (int sd = 0; sd < 2; ++sd)
-        IGL_TRY(radix_scatter_bins_async(ctx, in[sd], js->side[sd].ncols, js->side[sd].key, n_in[sd], W, lp, js->side[sd].staging.data(),
-                                         js->d_plan + (size_t)sd * kMsgBins, js->d_plan + (size_t)(2 + sd) * kMsgBins, sd == 1 ? st_l : st));
+        IGL_TRY(radix_scatter_bins_async(ctx, in[sd], js->side[sd].ncols, js->side[sd].key, n_in[sd], nd[sd], W, lp, hot[sd],
+                                         js->side[sd].staging.data(), js->d_plan + (size_t)sd * kMsgBins,
+                                         js->d_plan + (size_t)(2 + sd) * kMsgBins, sd == 1 ? st_l : st));
     if (overlap) cudaEventRecord(js->ev_l[1], st_l);
     cudaEventRecord(js->ev[2], st);
     // ---- where the runs are read from
     const uint8_t* src_cols[2][kSegMaxSrc][16] = {};
     int64_t src_base[2][kSegMaxSrc] = {};   // row of a source's bin (me, 0) inside src_cols (nccl mode: the receive slab holds only this range)
-    int64_t remote_bytes = 0;
+    int64_t remote_bytes = 0, pref_bytes = 0;
+    int pref_parts = 0;                     // probe-side partitions [0, pref_parts) of every peer are prefetched into local memory
+    bool prefetching = false;
     if (js->mode == IGL_EXCHANGE_P2P) {
         for (int sd = 0; sd < 2; ++sd) {
             ShuffleSide& S = js->side[sd];
@@ -509,14 +635,61 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
             IGL_NCCL_OK(g_nccl.AllReduce(js->d_flag + 8, js->d_flag + 8, 1, kNcclInt32, kNcclSum, comm->comm, st_l));
             cudaEventRecord(js->ev_l[2], st_l);
         }
+        // ---- NVLink is idle while the table is built: the copy engines use that time to bring the
+        // probe rows of the first `pref_parts` partitions over from every peer (each peer's range is
+        // one contiguous copy per column); the probe kernel then finds those runs in local memory
+        // and fetches only the rest across the link itself.  Sized from the previous run's build time.
+        if (overlap && W > 1) {
+            ShuffleSide& S = js->side[1];
+            const char* pe = getenv("IGL_SHUFFLE_PREFETCH");
+            double frac = -1.0;
+            if (pe) frac = atof(pe);
+            int64_t remote_rows = 0;
+            for (int s = 0; s < W; ++s)
+                if (s != me) for (int p = 0; p < parts; ++p) remote_rows += cnt[1][(size_t)s * bins + ((size_t)me << lp) + p];
+            if (frac < 0) {
+                const double build_ms = js->last_build_ms > 0 ? js->last_build_ms : (double)recv_total[0] * 6.5e-8;
+                const double budget = 0.85 * build_ms * 700e6;   // bytes the copy engines move in that time (~700 GB/s)
+                frac = remote_rows > 0 ? std::min(1.0, budget / ((double)remote_rows * S.row_bytes())) : 0.0;
+            }
+            pref_parts = (int)(frac * parts);
+            if (pref_parts > parts) pref_parts = parts;
+            if (pref_parts > 0 && remote_rows > 0) {
+                int64_t rbase = 0;
+                int64_t first[kShufMaxRanks] = {}, len[kShufMaxRanks] = {}, base[kShufMaxRanks] = {};
+                for (int s = 0; s < W; ++s) {
+                    if (s == me) continue;
+                    const int64_t* o = &off[1][(size_t)s * bins];
+                    const int64_t* c = &cnt[1][(size_t)s * bins];
+                    const int b0 = me << lp, b1 = b0 + pref_parts - 1;
+                    first[s] = o[b0]; len[s] = o[b1] + align_rows(c[b1]) - first[s];
+                    base[s] = rbase; rbase += len[s];
+                }
+                IGL_TRY(ensure_cols(ctx, S.recv, S.recv_rows, S, rbase + 64));
+                IGL_CUDA_OK(cudaStreamWaitEvent(js->stream3, js->ev_l[2], 0));
+                for (int s = 0; s < W; ++s) {
+                    if (s == me || len[s] == 0) continue;
+                    for (int c = 0; c < S.ncols; ++c) {
+                        IGL_CUDA_OK(cudaMemcpyAsync((uint8_t*)S.recv[c] + ((size_t)base[s] << S.shift[c]),
+                                                    src_cols[1][s][c] + ((size_t)first[s] << S.shift[c]), (size_t)len[s] << S.shift[c],
+                                                    cudaMemcpyDefault, js->stream3));
+                        src_cols[1][W + s][c] = (const uint8_t*)S.recv[c] + ((size_t)base[s] << S.shift[c]);
+                    }
+                    src_base[1][W + s] = first[s];
+                    pref_bytes += len[s] * S.row_bytes();
+                }
+                IGL_CUDA_OK(cudaEventRecord(js->ev_copy, js->stream3));
+                prefetching = true;
+            } else pref_parts = 0;
+        }
     } else {
         // grouped send/recv of each destination's contiguous staging range (padding included)
         for (int sd = 0; sd < 2; ++sd) {
             ShuffleSide& S = js->side[sd];
             std::vector<int64_t> rbase(W + 1, 0);
             auto range = [&](int src, int dst, int64_t& first, int64_t& len) {   // rows [first, first+len) of src's staging go to dst
-                const int64_t* o = &offs[((size_t)sd * W + src) * bins];
-                const int64_t* c = &counts[((size_t)sd * W + src) * bins];
+                const int64_t* o = &off[sd][(size_t)src * binsS[sd]];
+                const int64_t* c = &cnt[sd][(size_t)src * binsS[sd]];
                 first = o[(size_t)dst << lp];
                 const int last = ((dst + 1) << lp) - 1;
                 len = o[last] + align_rows(c[last]) - first;
@@ -543,7 +716,7 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
     cudaEventRecord(js->ev[3], st);
     // ---- run lists
     const bool seg_probe_possible = !js->left_join;   // decided for good once the build has shown whether keys repeat
-    const int nseg_max = W * parts;
+    const int nseg_max = 2 * W * parts;   // per side (the build side lists broadcast runs too when hot keys are in play)
     const size_t seg_bytes = (size_t)nseg_max * (sizeof(CopySeg) * 2 + sizeof(ProbeSeg)) + 256;
     if (seg_bytes > js->segs_bytes) {
         if (js->d_segs) pool_free(ctx, js->d_segs);
@@ -560,13 +733,13 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
     long long probe_chunks = 0;
     for (int sd = 0; sd < 2; ++sd) {
         int64_t dst = 0;
-        for (int i = 0; i < nseg_max; ++i) {
-            const size_t k = (size_t)sd * nseg_max + i;
-            const int64_t rows = seg_rows[k];
+        for (int i = 0; i < nsegS[sd]; ++i) {
+            const int64_t rows = seg_rows[sd][i];
             if (rows == 0) continue;
-            const int s = seg_src[k];
-            const int64_t row0 = seg_row0[k] - src_base[sd][s];
+            int s = seg_src[sd][i];
             if (s != me) remote_bytes += rows * js->side[sd].row_bytes();
+            if (sd == 1 && prefetching && s != me && i / W < pref_parts) s += W;   // this run has a local copy
+            const int64_t row0 = seg_row0[sd][i] - src_base[sd][s];
             CopySeg& cs = h_copy[sd][ncopy[sd]++];
             cs.src_row0 = (uint64_t)row0; cs.dst_row0 = (uint64_t)dst; cs.rows = (uint32_t)rows; cs.blk0 = copy_blocks[sd]; cs.src = (uint32_t)s; cs.pad = 0;
             copy_blocks[sd] += (uint32_t)((rows + kCopyBlockRows - 1) / kCopyBlockRows);
@@ -595,7 +768,9 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
     cudaEventRecord(js->ev[4], st);
     // ---- 6. probe side
     if (overlap) IGL_CUDA_OK(cudaStreamWaitEvent(st, js->ev_l[2], 0));
+    if (prefetching) IGL_CUDA_OK(cudaStreamWaitEvent(st, js->ev_copy, 0));
     cudaEventRecord(js->ev_wait, st);
+    const int nsrc = prefetching ? 2 * W : W;
     const int ncols_out = L.ncols + R.ncols;
     auto ensure_out = [&](int64_t rows) -> int32_t {
         if (rows <= js->out_cap && !js->out.empty()) return IGL_OK;
@@ -621,15 +796,15 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
     const char* segenv = getenv("IGL_SHUFFLE_FUSED_PROBE");
     if (seg_probe_possible && !(segenv && segenv[0] == '0') && join_segments_eligible(js->join)) {
         SegSource SS{};
-        for (int s = 0; s < W; ++s) for (int c = 0; c < L.ncols; ++c) SS.cols[s][c] = src_cols[1][s][c];
-        SS.nsrc = W; SS.dev_segs = d_probe; SS.nsegs = nprobe; SS.nchunks = probe_chunks; SS.total_rows = recv_total[1];
+        for (int s = 0; s < nsrc; ++s) for (int c = 0; c < L.ncols; ++c) SS.cols[s][c] = src_cols[1][s][c] ? src_cols[1][s][c] : src_cols[1][me][c];
+        SS.nsrc = nsrc; SS.dev_segs = d_probe; SS.nsegs = nprobe; SS.nchunks = probe_chunks; SS.total_rows = recv_total[1];
         IGL_TRY(ensure_out(std::max<int64_t>(recv_total[1], 1)));
         out_cols(oc);
         IGL_TRY(join_probe_segments(js->join, SS, oc.data(), js->out_cap, &n_out, st));
         js->stats[4] = 1;
     } else {
         IGL_TRY(ensure_cols(ctx, L.slab, L.slab_rows, L, recv_total[1] + 64));
-        IGL_TRY(launch_seg_copy(ctx, L, src_cols[1], W, d_copy[1], ncopy[1], copy_blocks[1], L.slab.data(), st));
+        IGL_TRY(launch_seg_copy(ctx, L, src_cols[1], nsrc, d_copy[1], ncopy[1], copy_blocks[1], L.slab.data(), st));
         for (int c = 0; c < L.ncols; ++c) lcols[c] = igl_dev_col{L.types[c], 0, L.slab[c], nullptr, nullptr};
         int64_t need = recv_total[1];
         if (igl_join_has_duplicates(js->join)) IGL_TRY(igl_join_probe_count(js->join, lcols.data(), recv_total[1], &need, st));
@@ -649,6 +824,12 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
     js->out_rows = n_out;
     js->stats[0] = recv_total[0]; js->stats[1] = recv_total[1]; js->stats[2] = remote_bytes; js->stats[3] = lp;
     js->stats[5] = n_out;
+    {
+        float bms = 0.f;
+        if (cudaEventElapsedTime(&bms, js->ev[3], js->ev[4]) == cudaSuccess) js->last_build_ms = bms;
+    }
+    js->stats[2] = remote_bytes;
+    js->stats[8] = pref_bytes; js->stats[9] = pref_parts;
     js->stats[6] = js->stats[7] = -1;   // probe-side partitioning on the second stream (us), and how long the probe waited for it (us)
     if (overlap) {
         float ms = 0.f;
@@ -685,7 +866,7 @@ int32_t igl_join_shuffle_phase_ms(igl_join_shuffle* js, double out[8]) {
     return IGL_OK;
 }
 
-int32_t igl_join_shuffle_stats(igl_join_shuffle* js, int64_t out[8]) {
+int32_t igl_join_shuffle_stats(igl_join_shuffle* js, int64_t out[12]) {
     if (!js || !out) return fail(IGL_ERR_INVALID_ARG, "igl_join_shuffle_stats: NULL argument");
     memcpy(out, js->stats, sizeof js->stats);
     return IGL_OK;
@@ -708,6 +889,8 @@ void igl_join_shuffle_destroy(igl_join_shuffle* js) {
     }
     for (void* p : js->out) pool_free(ctx, p);
     for (void* p : js->out_valid) pool_free(ctx, p);
+    pool_free(ctx, js->d_hot); pool_free(ctx, js->d_samples);
+    if (js->h_samples) cudaFreeHost(js->h_samples);
     pool_free(ctx, js->d_send); pool_free(ctx, js->d_recv); pool_free(ctx, js->d_plan); pool_free(ctx, js->d_segs); pool_free(ctx, js->d_flag);
     if (js->h_send) cudaFreeHost(js->h_send);
     if (js->h_recv) cudaFreeHost(js->h_recv);
@@ -718,6 +901,8 @@ void igl_join_shuffle_destroy(igl_join_shuffle* js) {
     if (js->ev_plan) cudaEventDestroy(js->ev_plan);
     if (js->ev_wait) cudaEventDestroy(js->ev_wait);
     if (js->stream2) cudaStreamDestroy(js->stream2);
+    if (js->stream3) cudaStreamDestroy(js->stream3);
+    if (js->ev_copy) cudaEventDestroy(js->ev_copy);
     igl_join_destroy(js->join);
     delete js;
 }

@@ -26,7 +26,7 @@ EXCHANGE_P2P, EXCHANGE_NCCL = 0, 1
 _MODES = {"p2p": EXCHANGE_P2P, "nccl": EXCHANGE_NCCL}
 PHASES = ("counts", "partition", "exchange", "build", "probe", "closing_barrier", "total", "probe_kernel")
 STATS = ("build_rows_received", "probe_rows_received", "bytes_read_from_peers", "log2_parts", "fused_probe", "output_rows",
-         "probe_partition_us", "probe_wait_us")
+         "probe_partition_us", "probe_wait_us", "prefetched_bytes", "prefetched_parts", "hot_keys")
 
 
 def init_comm(ctx, rank: int, world: int, broadcast=None) -> None:
@@ -47,19 +47,20 @@ def init_comm(ctx, rank: int, world: int, broadcast=None) -> None:
     check(lib.igl_comm_init(ctx._h, world, rank, raw))
 
 
-def shuffle_plan(counts, rank: int, world: int, log2_parts: int):
-    """igl_shuffle_plan (pure host code): `counts[src][dest * parts + part]` -> the padded bin
+def shuffle_plan(counts, rank: int, world: int, log2_parts: int, broadcast: int = 0):
+    """igl_shuffle_plan[_ex] (pure host code): `counts[src][dest * parts + part]` -> the padded bin
     offsets of every source's staging buffer, and for `rank` the runs it reads, in walk order,
-    as (source, first row in the source's staging buffer, rows); plus their total."""
-    parts, bins = 1 << log2_parts, world << log2_parts
+    as (source, first row in the source's staging buffer, rows); plus their total.
+    broadcast=1: one more destination (index `world`) whose bins every rank reads."""
+    parts, bins = 1 << log2_parts, (world + broadcast) << log2_parts
     c = np.ascontiguousarray(np.asarray(counts, dtype=np.int64).reshape(world, bins))
     offs = np.zeros((world, bins), np.int64)
-    nseg = world * parts
+    nseg = world * parts * (1 + broadcast)
     src = np.zeros(nseg, np.int32); row0 = np.zeros(nseg, np.int64); rows = np.zeros(nseg, np.int64)
     total = C.c_int64(0)
-    check(lib.igl_shuffle_plan(world, rank, log2_parts, c.ctypes.data_as(C.POINTER(C.c_int64)),
-                               offs.ctypes.data_as(C.POINTER(C.c_int64)), src.ctypes.data_as(C.POINTER(C.c_int32)),
-                               row0.ctypes.data_as(C.POINTER(C.c_int64)), rows.ctypes.data_as(C.POINTER(C.c_int64)), C.byref(total)))
+    check(lib.igl_shuffle_plan_ex(world, rank, log2_parts, broadcast, c.ctypes.data_as(C.POINTER(C.c_int64)),
+                                  offs.ctypes.data_as(C.POINTER(C.c_int64)), src.ctypes.data_as(C.POINTER(C.c_int32)),
+                                  row0.ctypes.data_as(C.POINTER(C.c_int64)), rows.ctypes.data_as(C.POINTER(C.c_int64)), C.byref(total)))
     return offs, list(zip(src.tolist(), row0.tolist(), rows.tolist())), total.value
 
 
@@ -121,7 +122,7 @@ class PartitionedJoin:
         return {k: round(float(v), 3) for k, v in zip(PHASES, out)}
 
     def stats(self):
-        out = (C.c_int64 * 8)()
+        out = (C.c_int64 * 12)()
         check(lib.igl_join_shuffle_stats(self._h, out))
         return {k: int(v) for k, v in zip(STATS, out)}
 

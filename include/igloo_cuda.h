@@ -297,9 +297,13 @@ int32_t igl_join_shuffle_output(igl_join_shuffle* js, igl_dev_col* out /* [n_lef
  * barrier, [6] total, [7] the probe kernel alone.  stats: [0] build rows received, [1] probe rows
  * received, [2] bytes read from peer GPUs, [3] log2 of the partition count, [4] 1 = fused probe,
  * [5] output rows, [6] probe-side partitioning on the second stream (us, -1 = not overlapped),
- * [7] time the probe waited for it after the build (us). */
+ * [7] time the probe waited for it after the build (us), [8] probe-side bytes the copy engines
+ * prefetched over NVLink while the table was built, [9] partitions prefetched, [10] hot keys:
+ * when one GPU would receive more than 1.15 x its share of the probe rows, the keys behind it
+ * are found from a sample, their probe rows stay on the GPU that holds them and their build rows
+ * go to every GPU (0 = the hash alone decided). */
 int32_t igl_join_shuffle_phase_ms(igl_join_shuffle* js, double out[8]);
-int32_t igl_join_shuffle_stats(igl_join_shuffle* js, int64_t out[8]);
+int32_t igl_join_shuffle_stats(igl_join_shuffle* js, int64_t out[12]);
 void igl_join_shuffle_destroy(igl_join_shuffle* js);
 /* The exchange plan as pure host arithmetic (no GPU needed; igl_join_shuffle_run uses it).
  * counts[nranks][bins], bins = nranks << log2_parts, destination-major: rows of each source per
@@ -310,6 +314,13 @@ void igl_join_shuffle_destroy(igl_join_shuffle* js);
 int32_t igl_shuffle_plan(int32_t nranks, int32_t rank, int32_t log2_parts, const int64_t* counts,
                          int64_t* src_offsets, int32_t* seg_src, int64_t* seg_row0, int64_t* seg_rows,
                          int64_t* total_rows);
+/* The same with one extra destination (broadcast = 1: bins = (nranks + 1) << log2_parts) whose
+ * rows EVERY rank reads — the build rows of hot keys, whose probe rows stay on the GPU that holds
+ * them.  A partition's runs are then the rank's own bins of every source followed by the
+ * broadcast bins of every source: 2 * nranks entries per partition. */
+int32_t igl_shuffle_plan_ex(int32_t nranks, int32_t rank, int32_t log2_parts, int32_t broadcast, const int64_t* counts,
+                            int64_t* src_offsets, int32_t* seg_src, int64_t* seg_row0, int64_t* seg_rows,
+                            int64_t* total_rows);
 
 /* ---- synthetic data + multiset digest (SURVEY.md §8d generator), device side */
 enum igl_gen_kind {

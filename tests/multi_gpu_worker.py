@@ -47,7 +47,8 @@ def main():
             assert bench.fold_digests([g[0] for g in got]) == want, (mode, got, want)
         st = pj.stats()
         if rank == 0:
-            print(f"mode={mode} fused={bool(st['fused_probe'])} log2_parts={st['log2_parts']} rows={tot} OK", flush=True)
+            print(f"mode={mode} fused={bool(st['fused_probe'])} log2_parts={st['log2_parts']} hot={'yes' if st['hot_keys'] else 'no'} "
+                  f"prefetched={st['prefetched_bytes']} rows={tot} OK", flush=True)
         pj.close()
     dist.barrier()
     dist.destroy_process_group()

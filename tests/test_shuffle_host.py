@@ -45,6 +45,30 @@ def test_plan_layout_is_aligned_gap_free_and_partition_major():
         assert sum(p[2] for p in plans) == int(counts.sum())      # every row has exactly one reader
 
 
+def test_plan_with_a_broadcast_destination_hands_hot_build_rows_to_every_rank():
+    """Hot keys: their build rows go to one extra destination that EVERY rank reads (after its own
+    bins, partition by partition); everything else is read by exactly one rank."""
+    rng = np.random.default_rng(5)
+    world, lp = 4, 2
+    parts, bins = 1 << lp, (world + 1) << lp
+    counts = rng.integers(0, 40, (world, bins))
+    plans = [shuffle_plan(counts, r, world, lp, broadcast=1) for r in range(world)]
+    offs = plans[0][0]
+    bcast = int(counts[:, world * parts:].sum())
+    for d in range(world):
+        _, segs, total = plans[d]
+        assert len(segs) == 2 * world * parts
+        i = 0
+        for part in range(parts):
+            for k, dest in ((0, d), (1, world)):
+                for src in range(world):
+                    b = dest * parts + part
+                    assert segs[i] == (src, int(offs[src][b]), int(counts[src][b]))
+                    i += 1
+        assert total == int(counts[:, d * parts:(d + 1) * parts].sum()) + bcast
+    assert sum(p[2] for p in plans) == int(counts[:, :world * parts].sum()) + world * bcast
+
+
 def test_plan_rejects_bad_arguments():
     import pytest
     from igloo_b200._lib import IglooCudaError
