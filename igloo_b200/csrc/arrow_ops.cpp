@@ -133,12 +133,12 @@ size_t pad64(size_t b) { return (b + 63) / 64 * 64 + 64; }
 
 // Host batches are pageable memory: every input byte is copied once into the pinned staging
 // chunk, and one core moves ~10 GB/s while PCIe takes 50.  Copies of 4 MB and more are therefore
-// split over up to 8 threads (IGL_STAGE_THREADS overrides; 1 = plain memcpy).
+// split over up to 16 threads (IGL_STAGE_THREADS overrides; 1 = plain memcpy).
 void staged_copy(uint8_t* dst, const uint8_t* src, size_t bytes) {
     static const unsigned max_threads = [] {
         if (const char* e = getenv("IGL_STAGE_THREADS")) return (unsigned)std::max(1, atoi(e));
         const unsigned hw = std::thread::hardware_concurrency();
-        return std::min(8u, hw ? hw : 1u);
+        return std::min(16u, hw ? hw : 1u);
     }();
     const size_t kMinSlice = (size_t)2 << 20;
     unsigned nt = (unsigned)std::min<size_t>(max_threads, bytes / kMinSlice);
@@ -162,6 +162,7 @@ struct StagedCol {
     uint8_t* h_valid = nullptr;                          // bitmap for chunk_rows (pinned)
     int32_t* h_off = nullptr;                            // utf8 offsets (pinned)
     size_t utf8_used = 0;
+    bool any_null = false;                               // a batch staged into this chunk carried nulls for this column
     void* d_data = nullptr; size_t d_data_cap = 0;
     uint8_t* d_valid = nullptr; int32_t* d_off = nullptr;
 };
@@ -172,6 +173,9 @@ struct Staging {
     std::vector<StagedCol> cols;
     std::vector<uint8_t> wanted;   // which columns are staged at all
     int64_t chunk_rows = 0, rows = 0;
+    // join sides: a nullable column whose chunk holds no null goes to the device without a bitmap, so
+    // the kernels for non-null data serve it (Arrow producers mark almost every field nullable)
+    bool elide_all_valid = false;
 
     int32_t init(igl_ctx* c, const std::vector<FieldMeta>& f, int64_t chunk) {
         ctx = c; fields = f; chunk_rows = chunk; cols.resize(f.size()); wanted.assign(f.size(), 1);
@@ -227,7 +231,7 @@ struct Staging {
                 staged_copy(c.h_data + (size_t)rows * w, (const uint8_t*)a->buffers[1] + (size_t)off * w, (size_t)n * w);
             }
             if (c.nullable) {
-                if (valid && a->null_count != 0) copy_bits(c.h_valid, rows, valid, off, n);
+                if (valid && a->null_count != 0) { copy_bits(c.h_valid, rows, valid, off, n); c.any_null = true; }
                 else { // clear then set: the target bytes may hold stale bits from the previous chunk
                     for (int64_t i = 0; i < n; ++i) c.h_valid[(rows + i) >> 3] |= (uint8_t)(1u << ((rows + i) & 7));
                 }
@@ -254,7 +258,7 @@ struct Staging {
             }
             if (bytes) IGL_CUDA_OK(cudaMemcpyAsync(c.d_data, c.h_data, bytes, cudaMemcpyHostToDevice, st));
             dev[j].data = c.d_data;
-            if (c.nullable) {
+            if (c.nullable && (c.any_null || !elide_all_valid)) {
                 if (!c.d_valid) { void* p = nullptr; IGL_TRY(pool_alloc(ctx, pad64((size_t)(chunk_rows + 7) / 8), &p)); c.d_valid = (uint8_t*)p; }
                 IGL_CUDA_OK(cudaMemcpyAsync(c.d_valid, c.h_valid, (size_t)(rows + 7) / 8, cudaMemcpyHostToDevice, st));
                 dev[j].validity = c.d_valid;
@@ -271,6 +275,7 @@ struct Staging {
         rows = 0;
         for (auto& c : cols) {
             c.utf8_used = 0;
+            c.any_null = false;
             if (c.h_valid) memset(c.h_valid, 0, (size_t)(chunk_rows + 7) / 8);
         }
     }
@@ -410,6 +415,7 @@ struct igl_op {
     std::vector<void*> build_dev;            // grown device columns of the whole build side
     std::vector<size_t> build_cap;
     std::vector<uint8_t*> build_valid;
+    std::vector<uint8_t> build_any_null;     // a build batch carried nulls in this column (else the bitmap is dropped at finish_build)
     int64_t build_rows = 0, build_rows_cap = 0;
 };
 
@@ -620,6 +626,7 @@ int32_t join_build_flush(igl_op* op) {
     }
     IGL_CUDA_OK(cudaStreamSynchronize(st));
     op->build_rows += n;
+    for (int c = 0; c < op->n_right; ++c) if (S.cols[c].any_null) op->build_any_null[c] = 1;
     S.reset();
     return IGL_OK;
 }
@@ -764,7 +771,7 @@ int32_t direct_upload(Staging& S, const ArrowArray* batch, int64_t from, int64_t
         IGL_CUDA_OK(cudaMemcpyAsync(c.d_data, (const uint8_t*)a->buffers[1] + (size_t)(a->offset + batch->offset + from) * w, bytes,
                                     cudaMemcpyHostToDevice, up));
         dev[j].data = c.d_data;
-        if (c.nullable) {   // declared nullable, no nulls in this batch: an all-ones bitmap
+        if (c.nullable && !S.elide_all_valid) {   // declared nullable, no nulls in this batch: an all-ones bitmap
             if (!c.d_valid) { void* p = nullptr; IGL_TRY(pool_alloc(ctx, pad64((size_t)(S.chunk_rows + 7) / 8), &p)); c.d_valid = (uint8_t*)p; }
             IGL_CUDA_OK(cudaMemsetAsync(c.d_valid, 0xFF, (size_t)(n + 7) / 8, up));
             dev[j].validity = c.d_valid;
@@ -925,6 +932,8 @@ int32_t igl_op_hash_join_create(igl_ctx* ctx, int32_t join_type, const struct Ar
     op->build_dev.assign(op->n_right, nullptr);
     op->build_cap.assign(op->n_right, 0);
     op->build_valid.assign(op->n_right, nullptr);
+    op->build_any_null.assign(op->n_right, 0);
+    op->in.elide_all_valid = true;
     op->in_alt = op->in;   // second probe chunk buffer of the same shape
     if (cudaStreamCreateWithFlags(&op->s_up, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&op->s_down, cudaStreamNonBlocking) != cudaSuccess ||
@@ -973,6 +982,8 @@ int32_t igl_op_finish_build(igl_op* op) {
     if (op->build_done) return IGL_OK;
     DeviceGuard g(op->ctx->device);
     IGL_TRY(join_build_flush(op));
+    for (int c = 0; c < op->n_right; ++c)   // a nullable column that never carried a null: no bitmap, non-null kernels
+        if (op->build_valid[c] && !op->build_any_null[c]) { pool_free(op->ctx, op->build_valid[c]); op->build_valid[c] = nullptr; }
     std::vector<igl_dev_col> cols(op->n_right);
     for (int c = 0; c < op->n_right; ++c) {
         cols[c].type = op->build.fields[c].type;

@@ -1403,7 +1403,7 @@ int32_t igl_join_build(igl_join* j, const igl_dev_col* right, int64_t nrows, voi
     const igl_dev_col& kc = right[j->rkey];
     // payload inlining: (key, one non-null fixed-width column), integer key (exact round trip)
     j->payload_col = -1;
-    if (nr == 2 && !j->rn[0] && !j->rn[1] && !right[0].validity && !right[1].validity &&
+    if (nr == 2 && !right[0].validity && !right[1].validity &&   // what is there decides, not the schema's nullable flags
         (j->rt[j->rkey] == IGL_T_I32 || j->rt[j->rkey] == IGL_T_I64))
         j->payload_col = 1 - j->rkey;
     join_init_kernel<<<grid, 256, 0, st>>>((Slot*)j->d_slots, cap, (JoinSide*)j->d_side);
