@@ -787,9 +787,11 @@ int32_t join_probe_direct(igl_op* op, const ArrowArray* batch) {
     int64_t done = 0;
     while (done < batch->length) {
         const int64_t n = std::min<int64_t>(batch->length - done, op->in.chunk_rows);
-        { TraceScope ts(op->trace, TR_END); IGL_TRY(join_probe_end_chunk(op)); }
+        // the upload goes first: it travels while the previous chunk's probe is awaited (that chunk
+        // reads the other pair of device buffers) and its output download is queued
         std::vector<igl_dev_col> dev;
         { TraceScope ts(op->trace, TR_UPLOAD); IGL_TRY(direct_upload(op->in, batch, done, n, op->s_up, dev)); }
+        { TraceScope ts(op->trace, TR_END); IGL_TRY(join_probe_end_chunk(op)); }
         { TraceScope ts(op->trace, TR_BEGIN); IGL_TRY(join_probe_begin_chunk(op, n, std::move(dev))); }
         { TraceScope ts(op->trace, TR_WAIT_UP); IGL_CUDA_OK(cudaEventSynchronize(op->ev_up)); }   // the caller's buffers are free again
         std::swap(op->in, op->in_alt);
