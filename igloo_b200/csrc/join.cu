@@ -337,6 +337,7 @@ template <bool HAS_NULLS>
 __device__ __forceinline__ void emit_row(const JoinProbeParams& P, const uint8_t* stage, int row, long long pos,
                                          bool matched, unsigned long long val, uint64_t raw_key) {
     for (int c = 0; c < P.n_left; ++c) {
+        if (!P.out_data[c]) continue;   // hidden column (a computed / combined key): joined on, not emitted
         const uint8_t* src = stage + P.T.smem_off[c];
         if (P.out_shift[c] == 2) st_cs_u32((uint8_t*)P.out_data[c] + (pos << 2), *reinterpret_cast<const uint32_t*>(src + (row << 2)));
         else st_cs_u64((uint8_t*)P.out_data[c] + (pos << 3), *reinterpret_cast<const uint64_t*>(src + (row << 3)));
@@ -344,6 +345,7 @@ __device__ __forceinline__ void emit_row(const JoinProbeParams& P, const uint8_t
     }
     for (int c = 0; c < P.n_right; ++c) {
         const int oc = P.n_left + c;
+        if (!P.out_data[oc]) continue;
         uint64_t v = 0;
         uint8_t ok = matched ? 1 : 0;
         if (matched) {
@@ -413,6 +415,7 @@ __device__ __forceinline__ void unique_emit(const JoinProbeParams& P, const Uniq
     for (int c = 0; c < P.n_left; ++c) {
         const uint8_t* src = t.stage + P.T.smem_off[c];
         uint8_t* dst = (uint8_t*)P.out_data[c];
+        if (!dst) continue;
         if (P.out_shift[c] == 3) {
 #pragma unroll
             for (int r = 0; r < R; ++r)
@@ -434,6 +437,7 @@ __device__ __forceinline__ void unique_emit(const JoinProbeParams& P, const Uniq
     for (int c = 0; c < P.n_right; ++c) {
         const int oc = P.n_left + c;
         uint8_t* dst = (uint8_t*)P.out_data[oc];
+        if (!dst) continue;
         const int mode = P.payload_col < 0 ? 2 : (c == P.payload_col ? 0 : 1);   // 0 inlined payload, 1 the probe key, 2 gather by row id
 #pragma unroll
         for (int r = 0; r < R; ++r) {
@@ -640,12 +644,14 @@ __global__ void __launch_bounds__(256) join_expand_giant_kernel(const __grid_con
             const long long pos = pos0 + j;
             const uint32_t rid = P.table.rowids[rend - cnt + (uint32_t)j];
             for (int c = 0; c < P.n_left; ++c) {
+                if (!P.out_data[c]) continue;
                 if (P.out_shift[c] == 2) st_cs_u32((uint8_t*)P.out_data[c] + (pos << 2), (uint32_t)lv[c]);
                 else st_cs_u64((uint8_t*)P.out_data[c] + (pos << 3), lv[c]);
                 if (HAS_NULLS && P.out_valid[c]) P.out_valid[c][pos] = lok[c];
             }
             for (int c = 0; c < P.n_right; ++c) {
                 const int oc = P.n_left + c;
+                if (!P.out_data[oc]) continue;
                 const uint64_t v = P.out_shift[oc] == 2 ? (uint64_t)((const uint32_t*)P.right_data[c])[rid] : ((const uint64_t*)P.right_data[c])[rid];
                 if (P.out_shift[oc] == 2) st_cs_u32((uint8_t*)P.out_data[oc] + (pos << 2), (uint32_t)v);
                 else st_cs_u64((uint8_t*)P.out_data[oc] + (pos << 3), v);
@@ -912,6 +918,7 @@ __global__ void __launch_bounds__(kFlatThreads, IGL_FLAT_CTAS) join_probe_flat_k
         // column by column: uniform width test, unconditional (clamped) loads, predicated stores
         for (int c = 0; c < P.n_left; ++c) {
             const bool is_key = c == P.key_col;
+            if (!P.out[c]) continue;   // hidden column (a computed / combined key): joined on, not emitted
             if (P.lshift[c] == 3) {
                 const uint64_t* src = (const uint64_t*)(stage + P.stage_off[c]);
                 uint64_t* dst = (uint64_t*)P.out[c] + obase;
@@ -932,6 +939,7 @@ __global__ void __launch_bounds__(kFlatThreads, IGL_FLAT_CTAS) join_probe_flat_k
         }
         for (int c = 0; c < P.n_right; ++c) {
             const int mode = P.payload_col < 0 ? 2 : (c == P.payload_col ? 0 : 1);   // 0 inlined payload, 1 the key itself, 2 gather by row id
+            if (!P.out[P.n_left + c]) continue;
             if (P.rshift[c] == 3) {
                 const uint64_t* src = (const uint64_t*)P.right_data[c];
                 uint64_t* dst = (uint64_t*)P.out[P.n_left + c] + obase;
@@ -991,6 +999,7 @@ __global__ void __launch_bounds__(256) dense_fix_kernel(const __grid_constant__ 
         } else if (i >= (long long)H && i < P.nrows && bit) {
             const uint32_t dst = P.holes[H - hb - 1];
             for (int col = 0; col < P.ncols; ++col) {
+                if (!P.out[col]) continue;
                 if (P.shift[col] == 3) ((uint64_t*)P.out[col])[dst] = ((const uint64_t*)P.out[col])[i];
                 else ((uint32_t*)P.out[col])[dst] = ((const uint32_t*)P.out[col])[i];
             }
@@ -1041,6 +1050,7 @@ struct igl_join {
     std::vector<uint8_t> ln, rn;
     int lkey = 0, rkey = 0;
     bool never_match = false;
+    std::vector<uint8_t> lhide, rhide;       // hidden columns: joined on (computed or combined keys) but not emitted
     // build state
     bool built = false, csr = false;
     int payload_col = -1;
@@ -1132,11 +1142,13 @@ int32_t flat_fill_params(igl_join* j, FlatProbeParams& F, igl_dev_col* out, int6
     F.right_key_col = j->rkey; F.payload_col = j->payload_col; F.table = j->table; F.nrows = nrows;
     for (int c = 0; c < nl; ++c) {
         F.lshift[c] = j->lt[c] == IGL_T_I32 ? 2 : 3;
+        if (j->lhide[c]) { F.out[c] = nullptr; continue; }
         if (!out[c].data) return fail(IGL_ERR_INVALID_ARG, "output column %d has no data buffer", c);
         F.out[c] = out[c].data;
     }
     for (int c = 0; c < nr; ++c) {
         F.right_data[c] = (const uint8_t*)j->right[c].data; F.rshift[c] = j->rt[c] == IGL_T_I32 ? 2 : 3;
+        if (j->rhide[c]) { F.out[nl + c] = nullptr; continue; }
         if (!out[nl + c].data) return fail(IGL_ERR_INVALID_ARG, "output column %d has no data buffer", nl + c);
         F.out[nl + c] = out[nl + c].data;
     }
@@ -1290,6 +1302,7 @@ int32_t igl_join_create(igl_ctx* ctx, int32_t join_type, const int32_t* left_typ
     j->lt.assign(left_types, left_types + n_left);
     j->rt.assign(right_types, right_types + n_right);
     j->ln.assign(n_left, 0); j->rn.assign(n_right, 0);
+    j->lhide.assign(n_left, 0); j->rhide.assign(n_right, 0);
     if (left_nullable) j->ln.assign(left_nullable, left_nullable + n_left);
     if (right_nullable) j->rn.assign(right_nullable, right_nullable + n_right);
     j->lkey = left_key->nodes[0].col;
@@ -1568,10 +1581,11 @@ int32_t join_probe_begin(igl_join* j, const igl_dev_col* left, int64_t nrows, ig
         const bool is_left = c < nl;
         const int t = is_left ? j->lt[c] : j->rt[c - nl];
         P.out_shift[c] = t == IGL_T_I32 ? 2 : 3;
-        if (!out[c].data) return fail(IGL_ERR_INVALID_ARG, "output column %d has no data buffer", c);
-        P.out_data[c] = out[c].data;
+        const bool hidden = is_left ? j->lhide[c] != 0 : j->rhide[c - nl] != 0;
+        if (!hidden && !out[c].data) return fail(IGL_ERR_INVALID_ARG, "output column %d has no data buffer", c);
+        P.out_data[c] = hidden ? nullptr : out[c].data;
         bool want = is_left ? (left[c].validity != nullptr) : (j->left_join || j->right[c - nl].validity != nullptr);
-        if (!j->has_nulls) want = false;
+        if (!j->has_nulls || hidden) want = false;
         if (want && !out[c].validity) return fail(IGL_ERR_INVALID_ARG, "output column %d can hold nulls but has no validity buffer", c);
         if (want) {
             if (!j->valid_planes[c]) IGL_TRY(pool_alloc(ctx, (size_t)j->plane_rows, &j->valid_planes[c]));

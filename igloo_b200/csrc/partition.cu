@@ -149,10 +149,11 @@ constexpr int kRadixTile = kRadixThreads * kRadixRowsPerThread;   // 4096 rows p
 // rank), the build side sends them to one extra "every rank reads this" destination — so the
 // hash decides only the rest.  H.table: open-addressing set of canonical keys, kHotEmpty = free.
 constexpr unsigned long long kHotEmpty = 0xFFFFFFFFFFFFFFFFull;
+template <bool HOT>
 __device__ __forceinline__ int radix_bin_of(uint64_t canon, uint64_t h, int nhash, int log2_parts, const HotKeys& H) {
     const int part = log2_parts ? (int)(h >> (64 - log2_parts)) : 0;
     int dest = nhash > 1 ? (int)(((h & 0xFFFFFFFFull) * (uint64_t)nhash) >> 32) : 0;
-    if (H.table) {
+    if (HOT) {
         uint32_t s = (uint32_t)(h >> 24) & (uint32_t)H.mask;
         while (true) {
             const unsigned long long k = __ldg(H.table + s);
@@ -163,12 +164,14 @@ __device__ __forceinline__ int radix_bin_of(uint64_t canon, uint64_t h, int nhas
     }
     return (dest << log2_parts) | part;
 }
+template <bool HOT>
 __device__ __forceinline__ int radix_part(const void* keys, int type, long long i, int nhash, int log2_parts, const HotKeys& H) {
     const uint64_t raw = type == IGL_T_I32 ? (uint64_t)(uint32_t)((const int32_t*)keys)[i] : ((const uint64_t*)keys)[i];
     const uint64_t c = part_canon(type, raw);
-    return radix_bin_of(c, mix64(c), nhash, log2_parts, H);
+    return radix_bin_of<HOT>(c, mix64(c), nhash, log2_parts, H);
 }
 
+template <bool HOT>
 __global__ void __launch_bounds__(512) radix_hist_kernel(const void* __restrict__ keys, int type, long long n, int ndest, int nhash,
                                                                    int log2_parts, unsigned long long* hist, HotKeys H) {
     __shared__ unsigned int s_hist[kRadixMaxParts];
@@ -177,7 +180,7 @@ __global__ void __launch_bounds__(512) radix_hist_kernel(const void* __restrict_
     __syncthreads();
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
-        atomicAdd(&s_hist[radix_part(keys, type, i, nhash, log2_parts, H)], 1u);
+        atomicAdd(&s_hist[radix_part<HOT>(keys, type, i, nhash, log2_parts, H)], 1u);
     __syncthreads();
     for (int p = threadIdx.x; p < nparts; p += blockDim.x)
         if (s_hist[p]) atomicAdd(&hist[p], (unsigned long long)s_hist[p]);
@@ -245,7 +248,7 @@ __device__ __forceinline__ void radix_tile(const RadixParams& P, uint8_t* stage,
     for (int r = 0; r < kRadixRowsPerThread; ++r) {
         const bool ok = FULL || (r * kRadixThreads + tid) < rows;
         const uint64_t ck = part_canon(P.key_type, keyraw[r]);
-        part[r] = radix_bin_of(ck, mix64(ck), P.nhash, P.log2_parts, P.hot);
+        part[r] = radix_bin_of<false>(ck, mix64(ck), P.nhash, P.log2_parts, P.hot);
         rank[r] = 0;
         if (ok) rank[r] = atomicAdd(&s_cnt[part[r]], 1u);
         else part[r] = -1;
@@ -364,7 +367,7 @@ constexpr int kRtRows = 4;
 constexpr int kRtTile = kRtThreads * kRtRows;          // 4096 rows
 constexpr unsigned kRtMaxDyn = 190u << 10;   // tile buffers; the two permutation arrays (16 KB) follow them
 
-template <int ROWS>   // rows per thread: 4 (4096-row tiles) or 8 (8192-row tiles: twice the run length per bin, for the exchange)
+template <int ROWS, bool HOT>   // rows per thread: 4 (4096-row tiles) or 8 (8192-row tiles: twice the run length per bin, for the exchange)
 __global__ void __launch_bounds__(kRtThreads, 1) radix_scatter_bulk_kernel(const __grid_constant__ RadixParams P, int n_buf, uint32_t tile_bytes) {
     constexpr int kTile = kRtThreads * ROWS;
     constexpr uint32_t kOffScale = ROWS / kRtRows;   // P.stage_off is laid out for 4096-row tiles
@@ -416,7 +419,7 @@ __global__ void __launch_bounds__(kRtThreads, 1) radix_scatter_bulk_kernel(const
                 if (i < rows) {
                     const uint64_t raw = P.key_type == IGL_T_I32 ? (uint64_t)((const uint32_t*)kc)[i] : ((const uint64_t*)kc)[i];
                     const uint64_t ck = part_canon(P.key_type, raw);
-                    bin[r] = radix_bin_of(ck, mix64(ck), P.nhash, P.log2_parts, P.hot);
+                    bin[r] = radix_bin_of<HOT>(ck, mix64(ck), P.nhash, P.log2_parts, P.hot);
                     rank[r] = atomicAdd(&cnt[bin[r]], 1u);
                 }
             }
@@ -503,20 +506,24 @@ static cudaError_t launch_radix_scatter(igl_ctx* ctx, const RadixParams& P, uint
     bool aligned = true;
     for (int c = 0; c < P.ncols; ++c) if ((uintptr_t)P.src[c] & 15) aligned = false;
     const char* env = getenv("IGL_RADIX_BULK");
-    if (aligned && tile_bytes_4096 <= kRtMaxDyn && (!(env && env[0] == '0') || tile_bytes_4096 > kRadixMaxStage)) {
+    if (P.hot.table && !(aligned && tile_bytes_4096 <= kRtMaxDyn)) return cudaErrorNotSupported;   // only the bulk form routes hot keys
+    if (aligned && tile_bytes_4096 <= kRtMaxDyn && (!(env && env[0] == '0') || tile_bytes_4096 > kRadixMaxStage || P.hot.table)) {
         const int n_buf = 2u * tile_bytes_4096 <= kRtMaxDyn ? 2 : 1;
         const size_t dyn = (size_t)n_buf * tile_bytes_4096;
-        cudaError_t e = cudaFuncSetAttribute((const void*)radix_scatter_bulk_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kRtMaxDyn + 4u * kRtTile));
+        const bool hot = P.hot.table != nullptr;
+        cudaError_t e = cudaFuncSetAttribute(hot ? (const void*)radix_scatter_bulk_kernel<4, true> : (const void*)radix_scatter_bulk_kernel<4, false>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kRtMaxDyn + 4u * kRtTile));
         if (e != cudaSuccess) return e;
         // 8192-row tiles (one buffer) when the caller wants the longest runs and the tile fits beside 48 KB of static arrays
         const char* lenv = getenv("IGL_RADIX_LONG");
         if (long_runs && !(lenv && lenv[0] == '0') && 2u * tile_bytes_4096 <= (176u << 10)) {
-            e = cudaFuncSetAttribute((const void*)radix_scatter_bulk_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((176u << 10) + 8u * kRtTile));
+            e = cudaFuncSetAttribute((const void*)radix_scatter_bulk_kernel<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((176u << 10) + 8u * kRtTile));
             if (e != cudaSuccess) return e;
-            radix_scatter_bulk_kernel<8><<<ctx->sm_count, kRtThreads, 2u * tile_bytes_4096 + 4u * 2u * kRtTile, st>>>(P, 1, 2u * tile_bytes_4096);
+            radix_scatter_bulk_kernel<8, false><<<ctx->sm_count, kRtThreads, 2u * tile_bytes_4096 + 4u * 2u * kRtTile, st>>>(P, 1, 2u * tile_bytes_4096);
             return cudaGetLastError();
         }
-        radix_scatter_bulk_kernel<4><<<ctx->sm_count, kRtThreads, dyn + 4u * kRtTile, st>>>(P, n_buf, tile_bytes_4096);
+        if (hot) radix_scatter_bulk_kernel<4, true><<<ctx->sm_count, kRtThreads, dyn + 4u * kRtTile, st>>>(P, n_buf, tile_bytes_4096);
+        else radix_scatter_bulk_kernel<4, false><<<ctx->sm_count, kRtThreads, dyn + 4u * kRtTile, st>>>(P, n_buf, tile_bytes_4096);
         return cudaGetLastError();
     }
     cudaError_t e = cudaFuncSetAttribute((const void*)radix_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRadixMaxStage);
@@ -553,7 +560,7 @@ int32_t radix_partition(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int ke
     if (!radix_partition_supported(cols, ncols)) return fail(IGL_ERR_UNSUPPORTED, "radix_partition: row too wide (%u bytes of staging)", off);
     if (nrows > 0) {
         HostTrace tr("partition.hist");
-        radix_hist_kernel<<<ctx->sm_count * 4, 512, 0, st>>>(cols[key_col].data, P.key_type, nrows, 1, 1, log2_parts, hist, HotKeys{});
+        radix_hist_kernel<false><<<ctx->sm_count * 4, 512, 0, st>>>(cols[key_col].data, P.key_type, nrows, 1, 1, log2_parts, hist, HotKeys{});
         IGL_CUDA_OK(cudaGetLastError());
     }
     {
@@ -582,7 +589,8 @@ int32_t radix_histogram_async(igl_ctx* ctx, const igl_dev_col* key, long long nr
     if (key->validity) return fail(IGL_ERR_UNSUPPORTED, "nullable join keys are not repartitioned across GPUs");
     IGL_CUDA_OK(cudaMemsetAsync(dev_hist, 0, sizeof(unsigned long long) * ((size_t)ndest << log2_parts), st));
     if (nrows == 0) return IGL_OK;
-    radix_hist_kernel<<<ctx->sm_count * 4, 512, 0, st>>>(key->data, key->type, nrows, ndest, nhash, log2_parts, dev_hist, hot);
+    if (hot.table) radix_hist_kernel<true><<<ctx->sm_count * 4, 512, 0, st>>>(key->data, key->type, nrows, ndest, nhash, log2_parts, dev_hist, hot);
+    else radix_hist_kernel<false><<<ctx->sm_count * 4, 512, 0, st>>>(key->data, key->type, nrows, ndest, nhash, log2_parts, dev_hist, hot);
     IGL_CUDA_OK(cudaGetLastError());
     ctx->launches++;
     return IGL_OK;
@@ -704,7 +712,7 @@ int32_t igl_partition_histogram_radix(igl_ctx* ctx, const igl_dev_col* key, int6
     cudaStream_t st = pick_stream(ctx, stream);
     IGL_CUDA_OK(cudaMemsetAsync(dev_hist, 0, sizeof(int64_t) * ((size_t)ndest << log2_parts), st));
     if (nrows == 0) return IGL_OK;
-    radix_hist_kernel<<<ctx->sm_count * 4, 512, 0, st>>>(key->data, key->type, nrows, ndest, ndest, log2_parts, (unsigned long long*)dev_hist, HotKeys{});
+    radix_hist_kernel<false><<<ctx->sm_count * 4, 512, 0, st>>>(key->data, key->type, nrows, ndest, ndest, log2_parts, (unsigned long long*)dev_hist, HotKeys{});
     IGL_CUDA_OK(cudaGetLastError());
     ctx->launches++;
     return IGL_OK;

@@ -648,9 +648,19 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
             for (int s = 0; s < W; ++s)
                 if (s != me) for (int p = 0; p < parts; ++p) remote_rows += cnt[1][(size_t)s * bins + ((size_t)me << lp) + p];
             if (frac < 0) {
-                const double build_ms = js->last_build_ms > 0 ? js->last_build_ms : (double)recv_total[0] * 6.5e-8;
-                const double budget = 0.85 * build_ms * 700e6;   // bytes the copy engines move in that time (~700 GB/s)
-                frac = remote_rows > 0 ? std::min(1.0, budget / ((double)remote_rows * S.row_bytes())) : 0.0;
+                // Only a probe that the link would hold back is worth it: a probe kernel streams about
+                // 3.3 TB/s of (input + output) bytes from local memory and about 650 GB/s across NVLink;
+                // prefetch what exceeds the link's share of that time, at most what fits under the build.
+                const double remote_bytes_l = (double)remote_rows * S.row_bytes();
+                const double local_ms = (double)recv_total[1] * (2.0 * S.row_bytes() + js->side[0].row_bytes()) / 3.3e9;
+                const double link_ms = remote_bytes_l / 650e6;
+                frac = 0.0;
+                if (remote_rows > 0 && link_ms > 0.9 * local_ms) {
+                    const double build_ms = js->last_build_ms > 0 ? js->last_build_ms : (double)recv_total[0] * 6.5e-8;
+                    const double budget = 0.85 * build_ms * 700e6;   // bytes the copy engines move while the table is built
+                    const double want = remote_bytes_l - 0.85 * local_ms * 650e6;
+                    frac = std::max(0.0, std::min(1.0, std::min(budget, want) / remote_bytes_l));
+                }
             }
             pref_parts = (int)(frac * parts);
             if (pref_parts > parts) pref_parts = parts;

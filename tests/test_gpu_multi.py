@@ -36,6 +36,6 @@ def test_two_gpu_partitioned_join_digest(workload, scale, extra, jt, fused):
     assert "mode=p2p" in r.stdout and "mode=nccl" in r.stdout
     assert f"mode=p2p fused={fused}" in r.stdout, r.stdout[-500:]
     # skewed probe keys must be noticed: their rows stay local, their build rows go to every rank
-    skewed = extra == "skew" or workload == "c5a"
+    skewed = extra == "skew"   # (Zipf(1.1) over two GPUs stays within 1.15 x of an even split: the hash alone serves it)
     p2p_line = [ln for ln in r.stdout.splitlines() if ln.startswith("mode=p2p")][0]
     assert ("hot=yes" in p2p_line) == skewed, p2p_line
