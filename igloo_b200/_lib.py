@@ -99,6 +99,7 @@ _sig("igl_fp_jit_compile_only", _i32, _vp, _P(_i64))
 _sig("igl_jit_selftest", _i32, _P(_i64))
 _sig("igl_fp_run_static", _i32, _vp, _P(DevCol), _i64, _P(DevCol), _P(_i64), _vp)
 _sig("igl_join_create", _i32, _vp, _i32, _P(_i32), C.c_char_p, _i32, _P(_i32), C.c_char_p, _i32, _vp, _vp, _P(_vp))
+_sig("igl_join_create_ex", _i32, _vp, _i32, _P(_i32), C.c_char_p, _i32, _P(_i32), C.c_char_p, _i32, _P(_vp), _P(_vp), _i32, _P(_vp))
 _sig("igl_join_build", _i32, _vp, _P(DevCol), _i64, _vp)
 _sig("igl_join_probe_count", _i32, _vp, _P(DevCol), _i64, _P(_i64), _vp)
 _sig("igl_join_probe", _i32, _vp, _P(DevCol), _i64, _P(DevCol), _i64, _P(_i64), _vp)
@@ -132,6 +133,8 @@ _sig("igl_op_filter_project_create", _i32, _vp, _P(ArrowSchema), C.c_char_p, _sz
      _P(C.c_char_p), _i32, _P(_vp))
 _sig("igl_op_hash_join_create", _i32, _vp, _i32, _P(ArrowSchema), _P(ArrowSchema), C.c_char_p, _sz,
      C.c_char_p, _sz, _P(_vp))
+_sig("igl_op_hash_join_create_ex", _i32, _vp, _i32, _P(ArrowSchema), _P(ArrowSchema), _P(C.c_char_p), _P(_sz),
+     _P(C.c_char_p), _P(_sz), _i32, _P(_vp))
 _sig("igl_op_schema", _i32, _vp, _P(ArrowSchema))
 _sig("igl_op_push_build", _i32, _vp, _P(ArrowArray))
 _sig("igl_op_finish_build", _i32, _vp)

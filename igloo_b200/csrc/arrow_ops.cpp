@@ -393,7 +393,8 @@ struct igl_op {
     // join
     Staging build;
     igl_join* join = nullptr;
-    igl_expr *lkey = nullptr, *rkey = nullptr;
+    igl_expr *lkey = nullptr, *rkey = nullptr;   // the first pair (aliases of lkeys[0] / rkeys[0])
+    std::vector<igl_expr*> lkeys, rkeys;         // owned
     bool build_done = false, left_join = false;
     int n_left = 0, n_right = 0;
     // Inner equi-join on integer keys of one type, neither side nullable: every output row's
@@ -580,11 +581,13 @@ int32_t join_build_reserve(igl_op* op, int64_t n) {
     const int64_t cap = std::max<int64_t>(op->build_rows + n, op->build_rows_cap * 2);
     std::vector<void*> old_blocks;
     for (int c = 0; c < op->n_right; ++c) {
+        const bool bits = S.fields[c].type == IGL_T_BOOL;   // bit-packed: grows bytewise, like a validity bitmap
         const int w = type_width(S.fields[c].type);
         void* p = nullptr;
-        IGL_TRY(pool_alloc(ctx, pad64((size_t)cap * w), &p));
+        IGL_TRY(pool_alloc(ctx, pad64(bits ? (size_t)(cap + 7) / 8 + 8 : (size_t)cap * w), &p));
+        if (bits) IGL_CUDA_OK(cudaMemsetAsync(p, 0, pad64((size_t)(cap + 7) / 8 + 8), st));
         if (op->build_dev[c]) {
-            IGL_CUDA_OK(cudaMemcpyAsync(p, op->build_dev[c], (size_t)op->build_rows * w, cudaMemcpyDeviceToDevice, st));
+            IGL_CUDA_OK(cudaMemcpyAsync(p, op->build_dev[c], bits ? (size_t)(op->build_rows + 7) / 8 : (size_t)op->build_rows * w, cudaMemcpyDeviceToDevice, st));
             old_blocks.push_back(op->build_dev[c]);
         }
         op->build_dev[c] = p;
@@ -614,12 +617,15 @@ int32_t join_build_flush(igl_op* op) {
     cudaStream_t st = ctx->stream;
     IGL_TRY(join_build_reserve(op, n));
     if ((op->build_rows & 7) != 0) {
-        // validity bitmaps are appended bytewise: keep chunk boundaries byte aligned
+        // validity bitmaps and Boolean values are appended bytewise: keep chunk boundaries byte aligned
         for (int c = 0; c < op->n_right; ++c)
-            if (S.fields[c].nullable) return fail(IGL_ERR_UNSUPPORTED, "nullable build columns need coalesce_rows to be a multiple of 8");
+            if (S.fields[c].nullable || S.fields[c].type == IGL_T_BOOL) return fail(IGL_ERR_UNSUPPORTED, "nullable or Boolean build columns need coalesce_rows to be a multiple of 8");
     }
     for (int c = 0; c < op->n_right; ++c) {
         const int w = type_width(S.fields[c].type);
+        if (S.fields[c].type == IGL_T_BOOL)
+            IGL_CUDA_OK(cudaMemcpyAsync((uint8_t*)op->build_dev[c] + (op->build_rows >> 3), S.cols[c].h_data, (size_t)(n + 7) / 8, cudaMemcpyHostToDevice, st));
+        else
         IGL_CUDA_OK(cudaMemcpyAsync((uint8_t*)op->build_dev[c] + (size_t)op->build_rows * w, S.cols[c].h_data, (size_t)n * w, cudaMemcpyHostToDevice, st));
         if (S.fields[c].nullable)
             IGL_CUDA_OK(cudaMemcpyAsync(op->build_valid[c] + (op->build_rows >> 3), S.cols[c].h_valid, (size_t)(n + 7) / 8, cudaMemcpyHostToDevice, st));
@@ -698,7 +704,8 @@ int32_t join_probe_begin_chunk(igl_op* op, int64_t n, std::vector<igl_dev_col>&&
     for (int c = 0; c < nc; ++c) {
         PD.dout[c].type = op->out_fields[c].type;
         void* p = nullptr;
-        int32_t rc = pool_alloc(ctx, pad64((size_t)std::max<int64_t>(cap, 1) * type_width(PD.dout[c].type)), &p);
+        const size_t cap1 = (size_t)std::max<int64_t>(cap, 1);
+        int32_t rc = pool_alloc(ctx, pad64(PD.dout[c].type == IGL_T_BOOL ? (cap1 + 7) / 8 + 8 : cap1 * type_width(PD.dout[c].type)), &p);
         if (rc < 0) { cleanup(); return rc; }
         PD.to_free.push_back(p); PD.dout[c].data = p;
         rc = pool_alloc(ctx, pad64((size_t)(cap + 7) / 8 + 8), &p);
@@ -896,7 +903,15 @@ int32_t igl_op_filter_project_create(igl_ctx* ctx, const struct ArrowSchema* in_
 int32_t igl_op_hash_join_create(igl_ctx* ctx, int32_t join_type, const struct ArrowSchema* left_schema,
                                 const struct ArrowSchema* right_schema, const uint8_t* left_key, size_t left_key_len,
                                 const uint8_t* right_key, size_t right_key_len, igl_op** out) {
-    if (!ctx || !out || !left_key || !right_key) return fail(IGL_ERR_INVALID_ARG, "igl_op_hash_join_create: NULL argument");
+    if (!left_key || !right_key) return fail(IGL_ERR_INVALID_ARG, "igl_op_hash_join_create: NULL argument");
+    return igl_op_hash_join_create_ex(ctx, join_type, left_schema, right_schema, &left_key, &left_key_len, &right_key, &right_key_len, 1, out);
+}
+
+int32_t igl_op_hash_join_create_ex(igl_ctx* ctx, int32_t join_type, const struct ArrowSchema* left_schema,
+                                   const struct ArrowSchema* right_schema, const uint8_t* const* left_keys, const size_t* left_key_lens,
+                                   const uint8_t* const* right_keys, const size_t* right_key_lens, int32_t nkeys, igl_op** out) {
+    if (!ctx || !out || !left_keys || !right_keys || !left_key_lens || !right_key_lens || nkeys < 1)
+        return fail(IGL_ERR_INVALID_ARG, "igl_op_hash_join_create: NULL argument");
     *out = nullptr;
     std::vector<FieldMeta> lf, rf;
     IGL_TRY(import_schema(left_schema, lf));
@@ -911,9 +926,21 @@ int32_t igl_op_hash_join_create(igl_ctx* ctx, int32_t join_type, const struct Ar
     for (auto& f : lf) { lt.push_back(f.type); ln.push_back(f.nullable); }
     for (auto& f : rf) { rt.push_back(f.type); rn.push_back(f.nullable); }
     auto destroy_partial = [&]() { igl_op_destroy(op.release()); };
-    int32_t rc = igl_expr_compile(ctx, left_key, left_key_len, lt.data(), ln.data(), op->n_left, &op->lkey);
-    if (rc >= 0) rc = igl_expr_compile(ctx, right_key, right_key_len, rt.data(), rn.data(), op->n_right, &op->rkey);
-    if (rc >= 0) rc = igl_join_create(ctx, join_type, lt.data(), ln.data(), op->n_left, rt.data(), rn.data(), op->n_right, op->lkey, op->rkey, &op->join);
+    for (auto& f : lf) if (f.type == IGL_T_UTF8) { destroy_partial(); return fail(IGL_ERR_UNSUPPORTED, "Utf8 column \"%s\" on a join side is not supported yet", f.name.c_str()); }
+    for (auto& f : rf) if (f.type == IGL_T_UTF8) { destroy_partial(); return fail(IGL_ERR_UNSUPPORTED, "Utf8 column \"%s\" on a join side is not supported yet", f.name.c_str()); }
+    int32_t rc = IGL_OK;
+    for (int k = 0; k < nkeys && rc >= 0; ++k) {   // one pair per `join.on` entry (physical_planner.rs:106-120)
+        igl_expr *le = nullptr, *re = nullptr;
+        rc = igl_expr_compile(ctx, left_keys[k], left_key_lens[k], lt.data(), ln.data(), op->n_left, &le);
+        if (rc >= 0) rc = igl_expr_compile(ctx, right_keys[k], right_key_lens[k], rt.data(), rn.data(), op->n_right, &re);
+        if (le) op->lkeys.push_back(le);
+        if (re) op->rkeys.push_back(re);
+    }
+    if (rc >= 0) {
+        op->lkey = op->lkeys[0]; op->rkey = op->rkeys[0];
+        rc = igl_join_create_ex(ctx, join_type, lt.data(), ln.data(), op->n_left, rt.data(), rn.data(), op->n_right,
+                                op->lkeys.data(), op->rkeys.data(), nkeys, &op->join);
+    }
     if (rc < 0) { destroy_partial(); return rc; }
     // output schema: hash_join.rs:35-76 (left fields, right fields, clashes renamed right_<name>)
     op->left_join = join_type == IGL_JOIN_LEFT || join_type == IGL_JOIN_FULL;
@@ -927,7 +954,7 @@ int32_t igl_op_hash_join_create(igl_ctx* ctx, int32_t join_type, const struct Ar
         if (op->left_join) o.nullable = true;
         op->out_fields.push_back(o);
     }
-    if (!op->left_join && op->lkey->is_plain_col() && op->rkey->is_plain_col()) {
+    if (!op->left_join && nkeys == 1 && op->lkey->is_plain_col() && op->rkey->is_plain_col()) {
         const int lc = op->lkey->nodes[0].col, rc2 = op->rkey->nodes[0].col;
         if (lt[lc] == rt[rc2] && (lt[lc] == IGL_T_I32 || lt[lc] == IGL_T_I64)) { op->alias_left_key = lc; op->alias_right_key = rc2; }
     }
@@ -1083,7 +1110,8 @@ void igl_op_destroy(igl_op* op) {
     if (op->join) igl_join_destroy(op->join);
     igl_expr_destroy(op->pred);
     for (auto* e : op->proj_exprs) igl_expr_destroy(e);
-    igl_expr_destroy(op->lkey); igl_expr_destroy(op->rkey);
+    for (auto* e : op->lkeys) igl_expr_destroy(e);
+    for (auto* e : op->rkeys) igl_expr_destroy(e);
     for (void* p : op->build_dev) pool_free(op->ctx, p);
     for (uint8_t* p : op->build_valid) pool_free(op->ctx, p);
     delete op;

@@ -1051,6 +1051,7 @@ struct igl_join {
     int lkey = 0, rkey = 0;
     bool never_match = false;
     std::vector<uint8_t> lhide, rhide;       // hidden columns: joined on (computed or combined keys) but not emitted
+    void* ex = nullptr;                      // join_ex.cu: this handle fronts a wider join (several / computed keys, Boolean columns)
     // build state
     bool built = false, csr = false;
     int payload_col = -1;
@@ -1256,6 +1257,14 @@ namespace igl {
 
 bool join_segments_eligible(const igl_join* j) { return j && flat_eligible(j); }
 
+igl_ctx* join_ctx(const igl_join* j) { return j->ctx; }
+void** join_ex_slot(igl_join* j) { return &j->ex; }
+igl_join* join_new_shell(igl_ctx* ctx) { igl_join* j = new igl_join(); j->ctx = ctx; return j; }
+void join_set_hidden(igl_join* j, const uint8_t* lhide, const uint8_t* rhide) {
+    if (lhide) j->lhide.assign(lhide, lhide + j->lt.size());
+    if (rhide) j->rhide.assign(rhide, rhide + j->rt.size());
+}
+
 // The probe of a segmented probe side (kernels.h): this GPU's and its peers' staging buffers,
 // walked run by run.  The output is dense, `out_rows` rows; it needs S.total_rows rows of room.
 int32_t join_probe_segments(igl_join* j, const SegSource& S, igl_dev_col* out, int64_t out_capacity, int64_t* out_rows,
@@ -1354,12 +1363,14 @@ int32_t igl_join_partition_bits(igl_ctx* ctx, int64_t build_rows) {
 
 int32_t igl_join_set_prepartitioned(igl_join* j, int32_t on) {
     if (!j) return fail(IGL_ERR_INVALID_ARG, "igl_join_set_prepartitioned: NULL join");
+    if (j->ex) return igl_join_set_prepartitioned(join_ex_inner(j), on);
     j->prepartitioned = on != 0;
     return IGL_OK;
 }
 
 int32_t igl_join_build(igl_join* j, const igl_dev_col* right, int64_t nrows, void* stream) {
     if (!j || !right || nrows < 0) return fail(IGL_ERR_INVALID_ARG, "igl_join_build: bad arguments");
+    if (j->ex) return join_ex_build(j, right, nrows, stream);
     if (nrows >= (int64_t)kNoRow) return fail(IGL_ERR_UNSUPPORTED, "build side limited to 2^32-2 rows per table");
     igl_ctx* ctx = j->ctx;
     DeviceGuard g(ctx->device);
@@ -1451,10 +1462,14 @@ int32_t igl_join_build(igl_join* j, const igl_dev_col* right, int64_t nrows, voi
     return IGL_OK;
 }
 
-int32_t igl_join_has_duplicates(const igl_join* j) { return j && j->csr ? 1 : 0; }
+int32_t igl_join_has_duplicates(const igl_join* j) {
+    if (j && j->ex) return igl_join_has_duplicates(join_ex_inner(const_cast<igl_join*>(j)));
+    return j && j->csr ? 1 : 0;
+}
 
 int32_t igl_join_probe_count(igl_join* j, const igl_dev_col* left, int64_t nrows, int64_t* out_rows, void* stream) {
     if (!j || !left || !out_rows || nrows < 0) return fail(IGL_ERR_INVALID_ARG, "igl_join_probe_count: bad arguments");
+    if (j->ex) return join_ex_probe_count(j, left, nrows, out_rows, stream);
     if (!j->built) return fail(IGL_ERR_INVALID_ARG, "igl_join_probe_count: build side not finished");
     igl_ctx* ctx = j->ctx;
     DeviceGuard g(ctx->device);
@@ -1486,6 +1501,12 @@ int32_t join_probe_begin(igl_join* j, const igl_dev_col* left, int64_t nrows, ig
                          cudaStream_t st) {
     void* stream = (void*)st;
     if (!j || !left || !out || nrows < 0) return fail(IGL_ERR_INVALID_ARG, "igl_join_probe: bad arguments");
+    if (j->ex) {   // wider joins are not split: the whole probe runs here, `end` only reports
+        int64_t n = 0;
+        IGL_TRY(join_ex_probe(j, left, nrows, out, out_capacity, &n, stream));
+        j->pend_kind = 2; j->pend_rows = n;
+        return IGL_OK;
+    }
     if (!j->built) return fail(IGL_ERR_INVALID_ARG, "igl_join_probe: build side not finished");
     igl_ctx* ctx = j->ctx;
     DeviceGuard g(ctx->device);
@@ -1635,6 +1656,7 @@ extern "C" {
 int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_dev_col* out, int64_t out_capacity,
                        int64_t* out_rows, void* stream) {
     if (!j || !left || !out || nrows < 0) return fail(IGL_ERR_INVALID_ARG, "igl_join_probe: bad arguments");
+    if (j->ex) return join_ex_probe(j, left, nrows, out, out_capacity, out_rows, stream);
     cudaStream_t st = pick_stream(j->ctx, stream);
     IGL_TRY(join_probe_begin(j, left, nrows, out, out_capacity, st));
     return join_probe_end(j, out_rows, st);
@@ -1646,6 +1668,7 @@ int32_t igl_join_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_
 // partitioning, out[3] the probe kernel (fast path only; -1 where nothing was recorded).
 int32_t igl_join_phase_ms(igl_join* j, double out[4]) {
     if (!j || !out) return fail(IGL_ERR_INVALID_ARG, "igl_join_phase_ms: NULL argument");
+    if (j->ex) return igl_join_phase_ms(join_ex_inner(j), out);
     DeviceGuard g(j->ctx->device);
     for (int i = 0; i < 4; ++i) out[i] = -1.0;
     float ms = 0.f;
@@ -1662,6 +1685,7 @@ int32_t igl_join_phase_ms(igl_join* j, double out[4]) {
 
 void igl_join_destroy(igl_join* j) {
     if (!j) return;
+    if (j->ex) { join_ex_destroy(j); delete j; return; }
     DeviceGuard g(j->ctx->device);
     pool_free(j->ctx, j->d_slots);
     pool_free(j->ctx, j->d_side);

@@ -89,4 +89,17 @@ bool join_segments_eligible(const igl_join* j);
 int32_t join_probe_segments(igl_join* j, const SegSource& S, igl_dev_col* out, int64_t out_capacity, int64_t* out_rows,
                             cudaStream_t st);
 
+// ---- wider joins (join_ex.cu): several key expressions, computed keys, Boolean columns — all
+// reduced to the core join over an augmented column set with a hidden key column.
+igl_ctx* join_ctx(const igl_join* j);
+void** join_ex_slot(igl_join* j);
+igl_join* join_new_shell(igl_ctx* ctx);
+void join_set_hidden(igl_join* j, const uint8_t* lhide, const uint8_t* rhide);
+igl_join* join_ex_inner(igl_join* j);
+int32_t join_ex_build(igl_join* j, const igl_dev_col* right, int64_t nrows, void* stream);
+int32_t join_ex_probe_count(igl_join* j, const igl_dev_col* left, int64_t nrows, int64_t* out_rows, void* stream);
+int32_t join_ex_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_dev_col* out, int64_t out_capacity,
+                      int64_t* out_rows, void* stream);
+void join_ex_destroy(igl_join* j);
+
 }  // namespace igl

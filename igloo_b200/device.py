@@ -241,18 +241,25 @@ class HashJoin:
     """igl_join: build from the right child, probe with the left (hash_join.rs:100-213)."""
 
     def __init__(self, ctx: Context, join_type: int, left: Sequence[Field], right: Sequence[Field],
-                 left_key: Expr, right_key: Expr):
+                 left_key, right_key):
+        """left_key / right_key: one expression or a list of them, pairwise (HashJoinExec::new takes
+        vectors, hash_join.rs:38-39); anything beyond one plain column goes through igl_join_create_ex."""
         self.ctx, self.join_type = ctx, join_type
         self.left, self.right = list(left), list(right)
-        self._lk = ctx.compile(left_key, left)
-        self._rk = ctx.compile(right_key, right)
+        lks = list(left_key) if isinstance(left_key, (list, tuple)) else [left_key]
+        rks = list(right_key) if isinstance(right_key, (list, tuple)) else [right_key]
+        assert len(lks) == len(rks) and lks, "join keys come in pairs"
+        self._lks = [ctx.compile(e, left) for e in lks]
+        self._rks = [ctx.compile(e, right) for e in rks]
+        self._lk, self._rk = self._lks[0], self._rks[0]
         lt = (C.c_int32 * len(left))(*[f.type for f in left])
         rt = (C.c_int32 * len(right))(*[f.type for f in right])
         ln = bytes(1 if f.nullable else 0 for f in left)
         rn = bytes(1 if f.nullable else 0 for f in right)
         h = C.c_void_p()
-        check(lib.igl_join_create(ctx._h, join_type, lt, ln, len(left), rt, rn, len(right),
-                                  self._lk._h, self._rk._h, C.byref(h)))
+        la = (C.c_void_p * len(lks))(*[k._h for k in self._lks])
+        ra = (C.c_void_p * len(rks))(*[k._h for k in self._rks])
+        check(lib.igl_join_create_ex(ctx._h, join_type, lt, ln, len(left), rt, rn, len(right), la, ra, len(lks), C.byref(h)))
         self._h = h
         self.out_fields = join_output_fields(left, right, join_type)
         self._right_cols = None

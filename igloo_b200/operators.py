@@ -206,8 +206,8 @@ class HashJoinExec(ExecutionPlan):
 
     def __init__(self, left: ExecutionPlan, right: ExecutionPlan, left_keys: Sequence[Expr], right_keys: Sequence[Expr],
                  join_type: int, ctx=None):
-        if len(left_keys) != 1 or len(right_keys) != 1:
-            raise NotImplementedError("igloo-cuda joins on one key column (multi-column keys: SURVEY.md §8 f4)")
+        if len(left_keys) != len(right_keys) or not left_keys:
+            raise ValueError("join keys come in pairs (physical_planner.rs:106-120)")
         self.left, self.right, self.left_keys, self.right_keys = left, right, list(left_keys), list(right_keys)
         self.join_type, self.ctx = join_type, ctx
         lf, rf = fields_of(left.schema()), fields_of(right.schema())
@@ -225,13 +225,15 @@ class HashJoinExec(ExecutionPlan):
     def execute(self):
         ctx = self.ctx or default_context()
         lf, rf = fields_of(self.left.schema()), fields_of(self.right.schema())
-        lk = lower(self.left_keys[0], lf)[0]
-        rk = lower(self.right_keys[0], rf)[0]
+        lks = [lower(e, lf)[0] for e in self.left_keys]
+        rks = [lower(e, rf)[0] for e in self.right_keys]
+        nk = len(lks)
         ls, rs = _export_schema(self.left.schema()), _export_schema(self.right.schema())
         h = C.c_void_p()
         try:
-            check(lib.igl_op_hash_join_create(ctx._h, self.join_type, C.byref(ls), C.byref(rs), lk, len(lk), rk, len(rk),
-                                              C.byref(h)))
+            check(lib.igl_op_hash_join_create_ex(ctx._h, self.join_type, C.byref(ls), C.byref(rs),
+                                                 (C.c_char_p * nk)(*lks), (C.c_size_t * nk)(*[len(b) for b in lks]),
+                                                 (C.c_char_p * nk)(*rks), (C.c_size_t * nk)(*[len(b) for b in rks]), nk, C.byref(h)))
         finally:
             _release_schema(ls)
             _release_schema(rs)

@@ -200,6 +200,22 @@ int32_t igl_join_create(igl_ctx* ctx, int32_t join_type,
                         const int32_t* left_types, const uint8_t* left_nullable, int32_t n_left,
                         const int32_t* right_types, const uint8_t* right_nullable, int32_t n_right,
                         const igl_expr* left_key, const igl_expr* right_key, igl_join** out);
+/* HashJoinExec::new with everything it accepts (hash_join.rs:35-41: `left_keys` / `right_keys` are
+ * vectors of expressions; physical_planner.rs:106-120 pushes one pair per `join.on` entry; the
+ * key of a row is the printed form of ALL its key values, hash_join.rs:117-122): 1 to 4 key
+ * pairs, each any expression of the side's columns (evaluated by the projection kernel; their
+ * errors — division by zero, casts — surface from build / probe), and Boolean columns on either
+ * side.  A pair whose types differ never matches.  Two Int32 keys that cannot be NULL are packed
+ * into one exact 64-bit key; other key lists are hashed to 64 bits and the joined rows are then
+ * filtered by the real, null-safe condition (Inner / Right only; plain-column keys only).
+ * Utf8 columns are carried by the streaming operator (igl_op_hash_join_create), not here.
+ * igl_join_probe_count on a hashed key list is an upper bound.  One plain key over fixed-width
+ * columns is exactly igl_join_create. */
+int32_t igl_join_create_ex(igl_ctx* ctx, int32_t join_type,
+                           const int32_t* left_types, const uint8_t* left_nullable, int32_t n_left,
+                           const int32_t* right_types, const uint8_t* right_nullable, int32_t n_right,
+                           const igl_expr* const* left_keys, const igl_expr* const* right_keys, int32_t nkeys,
+                           igl_join** out);
 /* Build from the complete right side.  The columns are borrowed until
  * igl_join_destroy (right payload is gathered from them by row id). */
 int32_t igl_join_build(igl_join* j, const igl_dev_col* right, int64_t nrows, void* stream);
@@ -360,6 +376,13 @@ int32_t igl_op_hash_join_create(igl_ctx* ctx, int32_t join_type,
                                 const struct ArrowSchema* left_schema, const struct ArrowSchema* right_schema,
                                 const uint8_t* left_key, size_t left_key_len,
                                 const uint8_t* right_key, size_t right_key_len, igl_op** out);
+/* The same with every key pair of `join.on` (physical_planner.rs:106-120): nkeys bytecodes per side,
+ * any expressions of the side's columns; Boolean columns may ride along (igl_join_create_ex). */
+int32_t igl_op_hash_join_create_ex(igl_ctx* ctx, int32_t join_type,
+                                   const struct ArrowSchema* left_schema, const struct ArrowSchema* right_schema,
+                                   const uint8_t* const* left_keys, const size_t* left_key_lens,
+                                   const uint8_t* const* right_keys, const size_t* right_key_lens, int32_t nkeys,
+                                   igl_op** out);
 /* ExecutionPlan::schema (physical_plan.rs:16). */
 int32_t igl_op_schema(igl_op* op, struct ArrowSchema* out);
 /* Join only: right (build) child batches, then finish_build (hash_join.rs:100-128). */

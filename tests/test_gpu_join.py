@@ -20,12 +20,18 @@ def ctx():
     c.close()
 
 
+def _keys(k):
+    """A column name, an expression, or a list of either -> list of expressions."""
+    ks = k if isinstance(k, (list, tuple)) else [k]
+    return [col(x) if isinstance(x, str) else x for x in ks]
+
+
 def gpu_join(ctx, left, right, lk, rk, jt=0):
     from igloo_b200.device import DeviceColumn, HashJoin
     lf, rf = tight_fields(left), tight_fields(right)
     lc = [DeviceColumn.from_arrow(left.column(i), ctx.device) for i in range(left.num_columns)]
     rc = [DeviceColumn.from_arrow(right.column(i), ctx.device) for i in range(right.num_columns)]
-    j = HashJoin(ctx, jt, lf, rf, col(lk), col(rk))
+    j = HashJoin(ctx, jt, lf, rf, _keys(lk), _keys(rk))
     j.build(rc, right.num_rows)
     want_n = j.probe_count(lc, left.num_rows)
     out, n = j.probe(lc, left.num_rows)
@@ -40,7 +46,7 @@ def oracle_join(left, right, lk, rk, jt=0, mode=1):
     lf, rf = tight_fields(left), tight_fields(right)
     L = orc.Table.scan(arrow_to_columns(left))
     R = orc.Table.scan(arrow_to_columns(right))
-    J = L.hash_join(R, [lower(col(lk), lf)[0]], [lower(col(rk), rf)[0]], jt, mode, 4)
+    J = L.hash_join(R, [lower(e, lf)[0] for e in _keys(lk)], [lower(e, rf)[0] for e in _keys(rk)], jt, mode, 4)
     t = columns_to_arrow(J.columns())
     return t.cast(pa.schema([pa.field(f.name, f.type, True) for f in t.schema]))
 
@@ -265,3 +271,74 @@ def test_bench_workloads_small_join_vs_definition_and_oracle(ctx, workload, scal
     R = orc.Table.scan([orc.Column(nm, c.type, c.data[:nr].cpu().numpy()) for nm, c in zip(names_r, right)])
     J = L.hash_join(R, [lower(col(names_l[wl.lkey]), wl.lf)[0]], [lower(col(names_r[wl.rkey]), wl.rf)[0]], 0, 1, 4)
     assert J.nrows == n and J.digest() == got
+
+
+# ---- igl_join_create_ex: several keys, computed keys, Boolean columns (hash_join.rs:35-41, 109-122) ----
+def test_two_int32_keys_are_packed_exactly_all_join_types(ctx):
+    rng = np.random.default_rng(31)
+    nb, nl = 20_000, 70_000
+    right = pa.table({"a": rng.integers(-50, 50, nb).astype(np.int32), "b": rng.integers(0, 40, nb).astype(np.int32),
+                      "v": rng.integers(0, 1 << 40, nb)})
+    left = pa.table({"a": rng.integers(-60, 60, nl).astype(np.int32), "b": rng.integers(0, 45, nl).astype(np.int32),
+                     "w": rng.random(nl)})
+    for jt in (0, 1, 2, 3):
+        got, j = check(ctx, left, right, ["a", "b"], ["a", "b"], jt)
+        assert got.schema.names == ["a", "b", "w", "right_a", "right_b", "v"]
+    # unique build side: the packed key takes the flat fast path
+    uq = pa.table({"a": (np.arange(nb) // 200).astype(np.int32), "b": (np.arange(nb) % 200).astype(np.int32), "v": rng.integers(0, 9, nb)})
+    got, j = check(ctx, left, uq, ["a", "b"], ["a", "b"], 0)
+    assert not j.has_duplicates
+
+
+def test_hashed_key_lists_are_verified_by_the_real_condition(ctx):
+    rng = np.random.default_rng(32)
+    nb, nl = 30_000, 90_000
+    right = pa.table({"k1": rng.integers(0, 300, nb), "k2": pa.array(rng.integers(0, 20, nb).astype(np.float64), pa.float64(), mask=rng.random(nb) < 0.05),
+                      "k3": rng.integers(0, 3, nb).astype(np.int32), "v": rng.integers(0, 1 << 40, nb)})
+    left = pa.table({"k1": rng.integers(0, 320, nl), "k2": pa.array(rng.integers(0, 22, nl).astype(np.float64), pa.float64(), mask=rng.random(nl) < 0.05),
+                     "k3": rng.integers(0, 3, nl).astype(np.int32), "w": rng.integers(0, 99, nl).astype(np.int32)})
+    got, j = check(ctx, left, right, ["k1", "k2", "k3"], ["k1", "k2", "k3"], 0)     # NULL == NULL inside the key list too
+    assert got.num_rows > 0 and j.has_duplicates
+    check(ctx, left, right, ["k1", "k2"], ["k1", "k2"], 2)                          # Right == Inner
+    # a Left join on such a key list is refused, not approximated
+    from igloo_b200._lib import IglooCudaError
+    with pytest.raises(IglooCudaError) as e:
+        gpu_join(ctx, left, right, ["k1", "k2", "k3"], ["k1", "k2", "k3"], 1)
+    assert e.value.code == -2
+    # one pair of differing types: nothing can match (the printed key carries the type)
+    r2 = pa.table({"k1": right.column("k1"), "k3": right.column("k3").cast(pa.int64()), "v": right.column("v")})
+    got, _ = check(ctx, left.select(["k1", "k3", "w"]), r2, ["k1", "k3"], ["k1", "k3"], 0)
+    assert got.num_rows == 0
+    got, _ = check(ctx, left.select(["k1", "k3", "w"]), r2, ["k1", "k3"], ["k1", "k3"], 1)
+    assert got.num_rows == nl and got.column("v").null_count == nl
+
+
+def test_computed_join_keys_are_evaluated_on_the_device(ctx):
+    rng = np.random.default_rng(33)
+    nb, nl = 10_000, 50_000
+    right = pa.table({"j": np.arange(nb, dtype=np.int64) * 2, "v": rng.random(nb)})
+    left = pa.table({"a": rng.integers(0, nb, nl), "b": pa.array(rng.integers(0, nb, nl), pa.int64(), mask=rng.random(nl) < 0.1),
+                     "w": rng.integers(0, 9, nl).astype(np.int32)})
+    for jt in (0, 1):
+        got, j = check(ctx, left, right, col("a") + col("b"), "j", jt)              # nullable computed key: NULL keys find no NULL here
+        assert got.schema.names == ["a", "b", "w", "j", "v"]
+    check(ctx, left, right, col("a") * 2, col("j") + 0, 0)                           # computed on both sides
+    # a key expression that fails fails the probe (hash_join.rs:151-160 forwards the error)
+    from igloo_b200._lib import IglooCudaError
+    with pytest.raises(IglooCudaError) as e:
+        gpu_join(ctx, left, right, col("a") / (col("w") - col("w")), "j", 0)
+    assert e.value.code == -6
+
+
+def test_boolean_columns_ride_along_and_can_be_the_key(ctx):
+    rng = np.random.default_rng(34)
+    nb, nl = 5_000, 20_000
+    right = pa.table({"k": rng.integers(0, 6000, nb), "flag": pa.array(rng.random(nb) < 0.3, pa.bool_(), mask=rng.random(nb) < 0.1),
+                      "v": rng.integers(0, 99, nb).astype(np.int32)})
+    left = pa.table({"k": rng.integers(0, 6000, nl), "on": pa.array(rng.random(nl) < 0.5, pa.bool_()), "w": rng.random(nl)})
+    for jt in (0, 1):
+        got, _ = check(ctx, left, right, "k", "k", jt)
+        assert got.schema.names == ["k", "on", "w", "right_k", "flag", "v"]
+    small_r = pa.table({"flag": pa.array([True, False], pa.bool_()), "name_id": pa.array([1, 0], pa.int64())})
+    got, _ = check(ctx, left, small_r, "on", "flag", 0)                               # Boolean key
+    assert got.num_rows == nl

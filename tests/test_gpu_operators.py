@@ -167,3 +167,32 @@ def test_golden_scan_fixture_through_filter_exec(ctx):
     tbl = pacsv.read_csv(io.BytesIO(g["csv"].encode()))
     got, _ = collect(FilterExec(MemoryScanExec(tbl), col("col_a") > lit(1, T_I64), ctx))
     assert got.to_pydict() == {"col_a": [2], "col_b": ["bar"]}
+
+
+def test_hash_join_exec_key_lists_computed_keys_and_boolean_columns(ctx):
+    """HashJoinExec::new takes key VECTORS of arbitrary expressions (hash_join.rs:35-41, 109-122) and
+    carries every column type of its children: two key pairs (one computed), a Boolean payload column
+    on each side, streamed in small batches; Inner and Left against the oracle."""
+    from igloo_b200.operators import HashJoinExec, MemoryScanExec
+    rng = np.random.default_rng(12)
+    nb, nl = 6_000, 25_000
+    right = pa.table({"a": rng.integers(0, 80, nb).astype(np.int32), "b": rng.integers(0, 60, nb).astype(np.int32),
+                      "ok": pa.array(rng.random(nb) < 0.4, pa.bool_()), "v": rng.integers(0, 1 << 40, nb)},
+                     schema=pa.schema([pa.field("a", pa.int32(), False), pa.field("b", pa.int32(), False),
+                                       pa.field("ok", pa.bool_(), False), pa.field("v", pa.int64(), False)]))
+    left = pa.table({"a": rng.integers(0, 90, nl).astype(np.int32), "c": rng.integers(0, 30, nl).astype(np.int32),
+                     "hot": pa.array(rng.random(nl) < 0.5, pa.bool_()), "w": rng.random(nl)},
+                    schema=pa.schema([pa.field("a", pa.int32(), False), pa.field("c", pa.int32(), False),
+                                      pa.field("hot", pa.bool_(), False), pa.field("w", pa.float64(), False)]))
+    lf = [Field("a", T_I32), Field("c", T_I32), Field("hot", 1), Field("w", 4)]
+    rf = [Field("a", T_I32), Field("b", T_I32), Field("ok", 1), Field("v", T_I64)]
+    lkeys, rkeys = [col("a"), col("c") * 2], [col("a"), col("b")]
+    for jt in (0, 1):
+        j = HashJoinExec(MemoryScanExec(left, 4096), MemoryScanExec(right, 4096), lkeys, rkeys, jt, ctx)
+        assert j.schema().names == ["a", "c", "hot", "w", "right_a", "b", "ok", "v"]
+        got, _ = collect(j)
+        L = orc.Table.scan(arrow_to_columns(left)); R = orc.Table.scan(arrow_to_columns(right))
+        want = columns_to_arrow(L.hash_join(R, [lower(e, lf)[0] for e in lkeys], [lower(e, rf)[0] for e in rkeys], jt, 1, 2).columns())
+        assert got.num_rows == want.num_rows > 0
+        assert_same_multiset(got.cast(pa.schema([pa.field(f.name, f.type, True) for f in got.schema])),
+                             want.cast(pa.schema([pa.field(f.name, f.type, True) for f in want.schema])))
