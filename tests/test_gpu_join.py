@@ -46,6 +46,8 @@ def oracle_join(left, right, lk, rk, jt=0, mode=1):
     lf, rf = tight_fields(left), tight_fields(right)
     L = orc.Table.scan(arrow_to_columns(left))
     R = orc.Table.scan(arrow_to_columns(right))
+    if len(_keys(lk)) > 1:
+        mode = 0                      # the oracle's typed fast join takes one key; key lists go through the faithful printed-key join
     J = L.hash_join(R, [lower(e, lf)[0] for e in _keys(lk)], [lower(e, rf)[0] for e in _keys(rk)], jt, mode, 4)
     t = columns_to_arrow(J.columns())
     return t.cast(pa.schema([pa.field(f.name, f.type, True) for f in t.schema]))

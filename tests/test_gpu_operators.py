@@ -192,7 +192,7 @@ def test_hash_join_exec_key_lists_computed_keys_and_boolean_columns(ctx):
         assert j.schema().names == ["a", "c", "hot", "w", "right_a", "b", "ok", "v"]
         got, _ = collect(j)
         L = orc.Table.scan(arrow_to_columns(left)); R = orc.Table.scan(arrow_to_columns(right))
-        want = columns_to_arrow(L.hash_join(R, [lower(e, lf)[0] for e in lkeys], [lower(e, rf)[0] for e in rkeys], jt, 1, 2).columns())
+        want = columns_to_arrow(L.hash_join(R, [lower(e, lf)[0] for e in lkeys], [lower(e, rf)[0] for e in rkeys], jt, 0, 1).columns())
         assert got.num_rows == want.num_rows > 0
         assert_same_multiset(got.cast(pa.schema([pa.field(f.name, f.type, True) for f in got.schema])),
                              want.cast(pa.schema([pa.field(f.name, f.type, True) for f in want.schema])))
