@@ -686,6 +686,9 @@ struct FlatProbeParams {
     const uint8_t* seg_left[kSegMaxSrc][kJoinMaxCols];
 };
 
+#ifndef IGL_FLAT_COMPACT
+#define IGL_FLAT_COMPACT 1
+#endif
 constexpr int kFlatStages = 3;   // chunks in flight per CTA: the one being probed + two on their way from HBM
 
 // The left columns of every chunk reach shared memory through a ring of bulk async
@@ -824,6 +827,49 @@ __global__ void __launch_bounds__(kFlatThreads, IGL_FLAT_CTAS) join_probe_flat_k
                     if (((special & live) >> r) & 1u) { hit |= 1u << r; val[r] = P.table.side->val[1]; }
             }
         }
+#if IGL_FLAT_COMPACT
+        // About one row in ten is not decided by its home bucket (load factor 0.5, two slots per
+        // bucket), so nearly every 128-row chunk has some — on average a dozen, spread over the
+        // lanes.  Walking them where they sit costs every lane the predicated code of all four of
+        // its rows per round (a third of this kernel's instructions, measured); instead the
+        // undecided keys of the whole warp are gathered into a dense list in shared memory, each
+        // lane walks ONE of them to its end, and the owners read the answers back.
+        if (__any_sync(0xffffffffu, pend != 0)) {
+            static_assert(kFlatThreads == 32, "the walk list is per warp");
+            __shared__ unsigned long long s_walk[kFlatChunk];   // key in, value out
+            __shared__ unsigned char s_walk_hit[kFlatChunk];
+            int pos[kFlatRows], total = 0;
+#pragma unroll
+            for (int r = 0; r < kFlatRows; ++r) {
+                const uint32_t pb = __ballot_sync(0xffffffffu, (pend >> r) & 1u);
+                pos[r] = total + __popc(pb & lt_mask);
+                total += __popc(pb);
+                if ((pend >> r) & 1u) s_walk[pos[r]] = k[r];
+            }
+            __syncwarp();
+            for (int i = lane; i < total; i += 32) {
+                const uint64_t key = s_walk[i];
+                uint64_t b = ((mix64(key) >> tshift) + 1) & bmask;
+                unsigned long long v = 0;
+                bool found = false;
+                while (true) {
+                    const ulonglong4 qq = ld_nc_u64x4(slots + 2 * b);
+                    if (qq.x == key) { v = qq.y; found = true; break; }
+                    if (qq.x == kEmptyKey) break;
+                    if (qq.z == key) { v = qq.w; found = true; break; }
+                    if (qq.z == kEmptyKey) break;
+                    b = (b + 1) & bmask;
+                }
+                s_walk[i] = v;
+                s_walk_hit[i] = found ? 1 : 0;
+            }
+            __syncwarp();
+#pragma unroll
+            for (int r = 0; r < kFlatRows; ++r)
+                if (((pend >> r) & 1u) && s_walk_hit[pos[r]]) { hit |= 1u << r; val[r] = s_walk[pos[r]]; }
+            pend = 0;
+        }
+#else
         if (pend) {
             // About one row in ten is not decided by its home bucket (load factor 0.5, two
             // slots per bucket), so nearly every warp comes here: fetch the next bucket of
@@ -860,6 +906,7 @@ __global__ void __launch_bounds__(kFlatThreads, IGL_FLAT_CTAS) join_probe_flat_k
                 }
             }
         }
+#endif
         uint32_t hb[kFlatRows];
         unsigned int wcnt = 0;
 #pragma unroll

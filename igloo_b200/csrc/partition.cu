@@ -367,16 +367,18 @@ constexpr int kRtRows = 4;
 constexpr int kRtTile = kRtThreads * kRtRows;          // 4096 rows
 constexpr unsigned kRtMaxDyn = 190u << 10;   // tile buffers; the two permutation arrays (16 KB) follow them
 
-template <int ROWS, bool HOT>   // rows per thread: 4 (4096-row tiles) or 8 (8192-row tiles: twice the run length per bin, for the exchange)
-__global__ void __launch_bounds__(kRtThreads, 1) radix_scatter_bulk_kernel(const __grid_constant__ RadixParams P, int n_buf, uint32_t tile_bytes) {
-    constexpr int kTile = kRtThreads * ROWS;
-    constexpr uint32_t kOffScale = ROWS / kRtRows;   // P.stage_off is laid out for 4096-row tiles
+template <int ROWS, bool HOT, int THREADS>   // ROWS rows per thread; tile = THREADS * ROWS rows (4096, or 8192 for the long-run form)
+__global__ void __launch_bounds__(THREADS, THREADS >= 1024 ? 1 : 2) radix_scatter_bulk_kernel(const __grid_constant__ RadixParams P, int n_buf, uint32_t tile_bytes) {
+    constexpr int kTile = THREADS * ROWS;
+    constexpr uint32_t kOffScale = kTile / kRtTile;   // P.stage_off is laid out for 4096-row tiles
+    constexpr int BPT = kRadixMaxParts / THREADS;     // bins per thread in the scan
+    static_assert(kTile % kRtTile == 0 && kRadixMaxParts % THREADS == 0, "tile and bin layout");
     extern __shared__ __align__(128) uint8_t in_tiles[];
     __shared__ unsigned int s_cnt[2][kRadixMaxParts];      // by tile parity: count, then exclusive start
     __shared__ unsigned long long s_gbase[kRadixMaxParts];
     unsigned short* s_perm = reinterpret_cast<unsigned short*>(in_tiles + (size_t)n_buf * tile_bytes);   // slot -> row of the tile
     unsigned short* s_part = s_perm + kTile;                                                               // slot -> bin
-    __shared__ unsigned int s_warp_tot[kRtThreads / 32];
+    __shared__ unsigned int s_warp_tot[THREADS / 32];
     __shared__ uint64_t s_full[2];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nbins = P.ndest << P.log2_parts;
@@ -397,7 +399,8 @@ __global__ void __launch_bounds__(kRtThreads, 1) radix_scatter_bulk_kernel(const
         mbar_fence_init();
         for (int b = 0; b < n_buf; ++b) issue((long long)blockIdx.x + (long long)b * gridDim.x, b);
     }
-    s_cnt[0][tid] = 0; s_cnt[1][tid] = 0;
+#pragma unroll
+    for (int q = 0; q < BPT; ++q) { s_cnt[0][tid * BPT + q] = 0; s_cnt[1][tid * BPT + q] = 0; }
     __syncthreads();
     int it = 0;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
@@ -414,7 +417,7 @@ __global__ void __launch_bounds__(kRtThreads, 1) radix_scatter_bulk_kernel(const
             const uint8_t* kc = in + P.stage_off[P.key_col] * kOffScale;
 #pragma unroll
             for (int r = 0; r < ROWS; ++r) {
-                const int i = r * kRtThreads + tid;
+                const int i = r * THREADS + tid;
                 bin[r] = -1;
                 if (i < rows) {
                     const uint64_t raw = P.key_type == IGL_T_I32 ? (uint64_t)((const uint32_t*)kc)[i] : ((const uint64_t*)kc)[i];
@@ -424,11 +427,14 @@ __global__ void __launch_bounds__(kRtThreads, 1) radix_scatter_bulk_kernel(const
                 }
             }
         }
-        s_cnt[(it + 1) & 1][tid] = 0;   // the other parity's counters: last read before the previous tile's final barrier
+#pragma unroll
+        for (int q = 0; q < BPT; ++q) s_cnt[(it + 1) & 1][tid * BPT + q] = 0;   // the other parity's counters: last read before the previous tile's final barrier
         __syncthreads();
-        {   // exclusive scan of the bin counts (one bin per thread) + global reservation
-            const unsigned int c = tid < nbins ? cnt[tid] : 0;
-            unsigned int inc = c;
+        {   // exclusive scan of the bin counts (BPT bins per thread) + global reservation
+            unsigned int c[BPT], sum = 0;
+#pragma unroll
+            for (int q = 0; q < BPT; ++q) { c[q] = tid * BPT + q < nbins ? cnt[tid * BPT + q] : 0; sum += c[q]; }
+            unsigned int inc = sum;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 const unsigned int t = __shfl_up_sync(0xffffffffu, inc, o);
@@ -436,11 +442,16 @@ __global__ void __launch_bounds__(kRtThreads, 1) radix_scatter_bulk_kernel(const
             }
             if (lane == 31) s_warp_tot[warp] = inc;
             __syncthreads();
-            unsigned int ex = inc - c;
+            unsigned int ex = inc - sum;
             for (int w = 0; w < warp; ++w) ex += s_warp_tot[w];
-            if (tid < nbins) {
-                cnt[tid] = ex;
-                s_gbase[tid] = c ? P.offsets[tid] + atomicAdd(&P.cursor[tid], (unsigned long long)c) : 0ull;
+#pragma unroll
+            for (int q = 0; q < BPT; ++q) {
+                const int bq = tid * BPT + q;
+                if (bq < nbins) {
+                    cnt[bq] = ex;
+                    s_gbase[bq] = c[q] ? P.offsets[bq] + atomicAdd(&P.cursor[bq], (unsigned long long)c[q]) : 0ull;
+                }
+                ex += c[q];
             }
         }
         __syncthreads();
@@ -448,7 +459,7 @@ __global__ void __launch_bounds__(kRtThreads, 1) radix_scatter_bulk_kernel(const
         for (int r = 0; r < ROWS; ++r) {
             if (bin[r] >= 0) {
                 const unsigned int slot = cnt[bin[r]] + rank[r];
-                s_perm[slot] = (unsigned short)(r * kRtThreads + tid);
+                s_perm[slot] = (unsigned short)(r * THREADS + tid);
                 s_part[slot] = (unsigned short)bin[r];
             }
         }
@@ -458,7 +469,7 @@ __global__ void __launch_bounds__(kRtThreads, 1) radix_scatter_bulk_kernel(const
         int src_row[ROWS], dq[ROWS];
 #pragma unroll
         for (int r = 0; r < ROWS; ++r) {
-            const int sl = r * kRtThreads + tid;
+            const int sl = r * THREADS + tid;
             d[r] = 0; src_row[r] = 0; dq[r] = 0;
             if (sl < rows) {
                 const int p = s_part[sl];
@@ -472,12 +483,12 @@ __global__ void __launch_bounds__(kRtThreads, 1) radix_scatter_bulk_kernel(const
                 const uint64_t* sc = reinterpret_cast<const uint64_t*>(in + P.stage_off[c] * kOffScale);
 #pragma unroll
                 for (int r = 0; r < ROWS; ++r)
-                    if (r * kRtThreads + tid < rows) reinterpret_cast<uint64_t*>(P.dst[dq[r]][c])[d[r]] = sc[src_row[r]];
+                    if (r * THREADS + tid < rows) reinterpret_cast<uint64_t*>(P.dst[dq[r]][c])[d[r]] = sc[src_row[r]];
             } else {
                 const uint32_t* sc = reinterpret_cast<const uint32_t*>(in + P.stage_off[c] * kOffScale);
 #pragma unroll
                 for (int r = 0; r < ROWS; ++r)
-                    if (r * kRtThreads + tid < rows) reinterpret_cast<uint32_t*>(P.dst[dq[r]][c])[d[r]] = sc[src_row[r]];
+                    if (r * THREADS + tid < rows) reinterpret_cast<uint32_t*>(P.dst[dq[r]][c])[d[r]] = sc[src_row[r]];
             }
         }
         __syncthreads();   // the tile buffer, s_perm, s_part and s_gbase are free again
@@ -506,24 +517,37 @@ static cudaError_t launch_radix_scatter(igl_ctx* ctx, const RadixParams& P, uint
     bool aligned = true;
     for (int c = 0; c < P.ncols; ++c) if ((uintptr_t)P.src[c] & 15) aligned = false;
     const char* env = getenv("IGL_RADIX_BULK");
-    if (P.hot.table && !(aligned && tile_bytes_4096 <= kRtMaxDyn)) return cudaErrorNotSupported;   // only the bulk form routes hot keys
-    if (aligned && tile_bytes_4096 <= kRtMaxDyn && (!(env && env[0] == '0') || tile_bytes_4096 > kRadixMaxStage || P.hot.table)) {
-        const int n_buf = 2u * tile_bytes_4096 <= kRtMaxDyn ? 2 : 1;
-        const size_t dyn = (size_t)n_buf * tile_bytes_4096;
-        const bool hot = P.hot.table != nullptr;
-        cudaError_t e = cudaFuncSetAttribute(hot ? (const void*)radix_scatter_bulk_kernel<4, true> : (const void*)radix_scatter_bulk_kernel<4, false>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kRtMaxDyn + 4u * kRtTile));
-        if (e != cudaSuccess) return e;
+    const bool hot = P.hot.table != nullptr;
+    if (hot && !(aligned && tile_bytes_4096 <= kRtMaxDyn)) return cudaErrorNotSupported;   // only the bulk form routes hot keys
+    if (aligned && tile_bytes_4096 <= kRtMaxDyn && (!(env && env[0] == '0') || tile_bytes_4096 > kRadixMaxStage || hot)) {
         // 8192-row tiles (one buffer) when the caller wants the longest runs and the tile fits beside 48 KB of static arrays
         const char* lenv = getenv("IGL_RADIX_LONG");
-        if (long_runs && !(lenv && lenv[0] == '0') && 2u * tile_bytes_4096 <= (176u << 10)) {
-            e = cudaFuncSetAttribute((const void*)radix_scatter_bulk_kernel<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((176u << 10) + 8u * kRtTile));
+        if (long_runs && !hot && !(lenv && lenv[0] == '0') && 2u * tile_bytes_4096 <= (176u << 10)) {
+            cudaError_t e = cudaFuncSetAttribute((const void*)radix_scatter_bulk_kernel<8, false, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((176u << 10) + 8u * kRtTile));
             if (e != cudaSuccess) return e;
-            radix_scatter_bulk_kernel<8, false><<<ctx->sm_count, kRtThreads, 2u * tile_bytes_4096 + 4u * 2u * kRtTile, st>>>(P, 1, 2u * tile_bytes_4096);
+            radix_scatter_bulk_kernel<8, false, 1024><<<ctx->sm_count, kRtThreads, 2u * tile_bytes_4096 + 4u * 2u * kRtTile, st>>>(P, 1, 2u * tile_bytes_4096);
             return cudaGetLastError();
         }
-        if (hot) radix_scatter_bulk_kernel<4, true><<<ctx->sm_count, kRtThreads, dyn + 4u * kRtTile, st>>>(P, n_buf, tile_bytes_4096);
-        else radix_scatter_bulk_kernel<4, false><<<ctx->sm_count, kRtThreads, dyn + 4u * kRtTile, st>>>(P, n_buf, tile_bytes_4096);
+        // Two 512-thread CTAs per SM, each sorting its own 4096-row tile in one buffer: while one waits at
+        // a barrier or for its next tile, the other runs (IGL_RADIX_CTAS2=0: one 1024-thread CTA, two buffers).
+        const char* cenv = getenv("IGL_RADIX_CTAS2");
+        const bool two = !(cenv && cenv[0] == '0') && tile_bytes_4096 + 4u * kRtTile <= (92u << 10);
+        if (two) {
+            const size_t dyn = (size_t)tile_bytes_4096 + 4u * kRtTile;
+            const void* k = hot ? (const void*)radix_scatter_bulk_kernel<8, true, 512> : (const void*)radix_scatter_bulk_kernel<8, false, 512>;
+            cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+            if (e != cudaSuccess) return e;
+            if (hot) radix_scatter_bulk_kernel<8, true, 512><<<ctx->sm_count * 2, 512, dyn, st>>>(P, 1, tile_bytes_4096);
+            else radix_scatter_bulk_kernel<8, false, 512><<<ctx->sm_count * 2, 512, dyn, st>>>(P, 1, tile_bytes_4096);
+            return cudaGetLastError();
+        }
+        const int n_buf = 2u * tile_bytes_4096 <= kRtMaxDyn ? 2 : 1;
+        const size_t dyn = (size_t)n_buf * tile_bytes_4096;
+        cudaError_t e = cudaFuncSetAttribute(hot ? (const void*)radix_scatter_bulk_kernel<4, true, 1024> : (const void*)radix_scatter_bulk_kernel<4, false, 1024>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kRtMaxDyn + 4u * kRtTile));
+        if (e != cudaSuccess) return e;
+        if (hot) radix_scatter_bulk_kernel<4, true, 1024><<<ctx->sm_count, kRtThreads, dyn + 4u * kRtTile, st>>>(P, n_buf, tile_bytes_4096);
+        else radix_scatter_bulk_kernel<4, false, 1024><<<ctx->sm_count, kRtThreads, dyn + 4u * kRtTile, st>>>(P, n_buf, tile_bytes_4096);
         return cudaGetLastError();
     }
     cudaError_t e = cudaFuncSetAttribute((const void*)radix_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRadixMaxStage);

@@ -286,7 +286,7 @@ struct igl_join_shuffle {
     cudaEvent_t ev[7] = {};
     cudaEvent_t ev_plan = nullptr, ev_wait = nullptr, ev_l[3] = {};   // second stream: probe-side partition start / end / barrier end
     cudaStream_t stream2 = nullptr, stream3 = nullptr;
-    cudaEvent_t ev_copy = nullptr;
+    cudaEvent_t ev_copy = nullptr, ev_segs = nullptr;
     double last_build_ms = -1.0;            // measured build phase of the previous run: sizes the probe-side prefetch
     bool timed = false;
     int64_t stats[12] = {};
@@ -296,7 +296,7 @@ struct igl_join_shuffle {
 namespace {
 
 constexpr int kHotSlots = 512;      // device set size (a power of two)
-constexpr int kHotSamples = 16384;  // probe keys sampled per rank
+constexpr int kHotSamples = 4096;   // probe keys sampled per rank
 constexpr int kHotCand = 128;       // (key, count) candidates each rank contributes; also the most keys kept
 
 // Finds the keys that carry an outsized share of the probe rows: every rank samples its probe keys,
@@ -467,6 +467,7 @@ int32_t igl_join_shuffle_create(igl_ctx* ctx, int32_t join_type, const int32_t* 
     if (rc >= 0 && cudaStreamCreateWithFlags(&js->stream2, cudaStreamNonBlocking) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "cudaStreamCreate failed");
     if (rc >= 0 && cudaStreamCreateWithFlags(&js->stream3, cudaStreamNonBlocking) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "cudaStreamCreate failed");
     if (rc >= 0 && cudaEventCreateWithFlags(&js->ev_copy, cudaEventDisableTiming) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "cudaEventCreate failed");
+    if (rc >= 0 && cudaEventCreateWithFlags(&js->ev_segs, cudaEventDisableTiming) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "cudaEventCreate failed");
     if (rc < 0) { igl_join_shuffle_destroy(js.release()); return rc; }
     *out = js.release();
     return IGL_OK;
@@ -607,10 +608,19 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
     cudaEventRecord(js->ev[2], st);
     // ---- where the runs are read from
     const uint8_t* src_cols[2][kSegMaxSrc][16] = {};
-    int64_t src_base[2][kSegMaxSrc] = {};   // row of a source's bin (me, 0) inside src_cols (nccl mode: the receive slab holds only this range)
+    int64_t src_base[2][kSegMaxSrc] = {};   // row of src_cols[..][s] inside source s's staging buffer (0 when it IS the staging buffer)
     int64_t remote_bytes = 0, pref_bytes = 0;
     int pref_parts = 0;                     // probe-side partitions [0, pref_parts) of every peer are prefetched into local memory
     bool prefetching = false;
+    auto range = [&](int sd, int src, int dst, int np, int64_t& first, int64_t& len) {   // rows of src's staging that hold dst's partitions [0, np)
+        const int64_t* o = &off[sd][(size_t)src * binsS[sd]];
+        const int64_t* c = &cnt[sd][(size_t)src * binsS[sd]];
+        first = o[(size_t)dst << lp];
+        const int last = (dst << lp) + np - 1;
+        len = o[last] + align_rows(c[last]) - first;
+    };
+    int64_t pf_first[kShufMaxRanks] = {}, pf_len[kShufMaxRanks] = {}, pf_base[kShufMaxRanks] = {};
+    int64_t rbase[2][kShufMaxRanks + 1] = {};
     if (js->mode == IGL_EXCHANGE_P2P) {
         for (int sd = 0; sd < 2; ++sd) {
             ShuffleSide& S = js->side[sd];
@@ -628,106 +638,63 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
                 for (int c = 0; c < S.ncols; ++c) src_cols[sd][s][c] = (const uint8_t*)P.ptrs[c];
             }
         }
-        // ---- 4. every rank's staging is complete: the build side's (on this stream) first, then the
-        // probe side's (on its own stream when overlapped) — the same order on every rank
-        IGL_NCCL_OK(g_nccl.AllReduce(js->d_flag, js->d_flag, 1, kNcclInt32, kNcclSum, comm->comm, st));
-        if (overlap) {
-            IGL_NCCL_OK(g_nccl.AllReduce(js->d_flag + 8, js->d_flag + 8, 1, kNcclInt32, kNcclSum, comm->comm, st_l));
-            cudaEventRecord(js->ev_l[2], st_l);
-        }
-        // ---- NVLink is idle while the table is built: the copy engines use that time to bring the
-        // probe rows of the first `pref_parts` partitions over from every peer (each peer's range is
-        // one contiguous copy per column); the probe kernel then finds those runs in local memory
-        // and fetches only the rest across the link itself.  Sized from the previous run's build time.
-        if (overlap && W > 1) {
+        // ---- NVLink is idle while the table is built: a copy kernel on its own stream uses that time to
+        // bring the probe rows of the first `pref_parts` partitions over from every peer (each peer's range
+        // is one contiguous run per column); the probe kernel then finds those runs in local memory and
+        // fetches only the rest across the link itself.  Only a probe that the link would hold back is
+        // worth it, and only as much as fits under the build (sized from the previous run's build time).
+        const char* pe = getenv("IGL_SHUFFLE_PREFETCH");
+        if (overlap && W > 1 && !(pe && pe[0] == '0' && pe[1] == 0)) {
             ShuffleSide& S = js->side[1];
-            const char* pe = getenv("IGL_SHUFFLE_PREFETCH");
-            double frac = -1.0;
-            if (pe) frac = atof(pe);
+            double frac = pe ? atof(pe) : -1.0;
             int64_t remote_rows = 0;
             for (int s = 0; s < W; ++s)
                 if (s != me) for (int p = 0; p < parts; ++p) remote_rows += cnt[1][(size_t)s * bins + ((size_t)me << lp) + p];
             if (frac < 0) {
-                // Only a probe that the link would hold back is worth it: a probe kernel streams about
-                // 3.3 TB/s of (input + output) bytes from local memory and about 650 GB/s across NVLink;
-                // prefetch what exceeds the link's share of that time, at most what fits under the build.
+                // a probe kernel streams about 3.3 TB/s of (input + output) bytes from local memory and
+                // about 650 GB/s across NVLink
                 const double remote_bytes_l = (double)remote_rows * S.row_bytes();
                 const double local_ms = (double)recv_total[1] * (2.0 * S.row_bytes() + js->side[0].row_bytes()) / 3.3e9;
                 const double link_ms = remote_bytes_l / 650e6;
                 frac = 0.0;
                 if (remote_rows > 0 && link_ms > 0.9 * local_ms) {
                     const double build_ms = js->last_build_ms > 0 ? js->last_build_ms : (double)recv_total[0] * 6.5e-8;
-                    const double budget = 0.85 * build_ms * 700e6;   // bytes the copy engines move while the table is built
+                    const double budget = 0.8 * build_ms * 600e6;
                     const double want = remote_bytes_l - 0.85 * local_ms * 650e6;
                     frac = std::max(0.0, std::min(1.0, std::min(budget, want) / remote_bytes_l));
                 }
             }
-            pref_parts = (int)(frac * parts);
-            if (pref_parts > parts) pref_parts = parts;
+            pref_parts = std::min(parts, (int)(frac * parts));
             if (pref_parts > 0 && remote_rows > 0) {
-                int64_t rbase = 0;
-                int64_t first[kShufMaxRanks] = {}, len[kShufMaxRanks] = {}, base[kShufMaxRanks] = {};
+                int64_t rb = 0;
                 for (int s = 0; s < W; ++s) {
                     if (s == me) continue;
-                    const int64_t* o = &off[1][(size_t)s * bins];
-                    const int64_t* c = &cnt[1][(size_t)s * bins];
-                    const int b0 = me << lp, b1 = b0 + pref_parts - 1;
-                    first[s] = o[b0]; len[s] = o[b1] + align_rows(c[b1]) - first[s];
-                    base[s] = rbase; rbase += len[s];
+                    range(1, s, me, pref_parts, pf_first[s], pf_len[s]);
+                    pf_base[s] = rb; rb += pf_len[s];
                 }
-                IGL_TRY(ensure_cols(ctx, S.recv, S.recv_rows, S, rbase + 64));
-                IGL_CUDA_OK(cudaStreamWaitEvent(js->stream3, js->ev_l[2], 0));
+                IGL_TRY(ensure_cols(ctx, S.recv, S.recv_rows, S, rb + 64));
                 for (int s = 0; s < W; ++s) {
-                    if (s == me || len[s] == 0) continue;
-                    for (int c = 0; c < S.ncols; ++c) {
-                        IGL_CUDA_OK(cudaMemcpyAsync((uint8_t*)S.recv[c] + ((size_t)base[s] << S.shift[c]),
-                                                    src_cols[1][s][c] + ((size_t)first[s] << S.shift[c]), (size_t)len[s] << S.shift[c],
-                                                    cudaMemcpyDefault, js->stream3));
-                        src_cols[1][W + s][c] = (const uint8_t*)S.recv[c] + ((size_t)base[s] << S.shift[c]);
-                    }
-                    src_base[1][W + s] = first[s];
-                    pref_bytes += len[s] * S.row_bytes();
+                    if (s == me || pf_len[s] == 0) continue;
+                    for (int c = 0; c < S.ncols; ++c) src_cols[1][W + s][c] = (const uint8_t*)S.recv[c] + ((size_t)pf_base[s] << S.shift[c]);
+                    src_base[1][W + s] = pf_first[s];
+                    pref_bytes += pf_len[s] * S.row_bytes();
                 }
-                IGL_CUDA_OK(cudaEventRecord(js->ev_copy, js->stream3));
                 prefetching = true;
             } else pref_parts = 0;
         }
     } else {
-        // grouped send/recv of each destination's contiguous staging range (padding included)
+        // NCCL mode: every source's range for this rank lands in a local receive slab, source by source
         for (int sd = 0; sd < 2; ++sd) {
             ShuffleSide& S = js->side[sd];
-            std::vector<int64_t> rbase(W + 1, 0);
-            auto range = [&](int src, int dst, int64_t& first, int64_t& len) {   // rows [first, first+len) of src's staging go to dst
-                const int64_t* o = &off[sd][(size_t)src * binsS[sd]];
-                const int64_t* c = &cnt[sd][(size_t)src * binsS[sd]];
-                first = o[(size_t)dst << lp];
-                const int last = ((dst + 1) << lp) - 1;
-                len = o[last] + align_rows(c[last]) - first;
-            };
-            for (int s = 0; s < W; ++s) { int64_t f, l; range(s, me, f, l); rbase[s + 1] = rbase[s] + l; }
-            IGL_TRY(ensure_cols(ctx, S.recv, S.recv_rows, S, rbase[W] + 64));
-            IGL_NCCL_OK(g_nccl.GroupStart());
-            for (int c = 0; c < S.ncols; ++c)
-                for (int p = 0; p < W; ++p) {
-                    int64_t f, l;
-                    range(me, p, f, l);
-                    if (l) IGL_NCCL_OK(g_nccl.Send((const uint8_t*)S.staging[c] + ((size_t)f << S.shift[c]), (size_t)l << S.shift[c], kNcclUint8, p, comm->comm, st));
-                    range(p, me, f, l);
-                    if (l) IGL_NCCL_OK(g_nccl.Recv((uint8_t*)S.recv[c] + ((size_t)rbase[p] << S.shift[c]), (size_t)l << S.shift[c], kNcclUint8, p, comm->comm, st));
-                }
-            IGL_NCCL_OK(g_nccl.GroupEnd());
-            for (int s = 0; s < W; ++s) {
-                int64_t f, l; range(s, me, f, l);
-                src_base[sd][s] = f;
-                for (int c = 0; c < S.ncols; ++c) src_cols[sd][s][c] = (const uint8_t*)S.recv[c] + ((size_t)rbase[s] << S.shift[c]);
-            }
+            for (int s = 0; s < W; ++s) { int64_t f, l; range(sd, s, me, parts, f, l); rbase[sd][s + 1] = rbase[sd][s] + l; src_base[sd][s] = f; }
+            IGL_TRY(ensure_cols(ctx, S.recv, S.recv_rows, S, rbase[sd][W] + 64));
+            for (int s = 0; s < W; ++s)
+                for (int c = 0; c < S.ncols; ++c) src_cols[sd][s][c] = (const uint8_t*)S.recv[c] + ((size_t)rbase[sd][s] << S.shift[c]);
         }
     }
-    cudaEventRecord(js->ev[3], st);
-    // ---- run lists
-    const bool seg_probe_possible = !js->left_join;   // decided for good once the build has shown whether keys repeat
+    // ---- run lists (one upload): what the build pull, the probe and the prefetch walk
     const int nseg_max = 2 * W * parts;   // per side (the build side lists broadcast runs too when hot keys are in play)
-    const size_t seg_bytes = (size_t)nseg_max * (sizeof(CopySeg) * 2 + sizeof(ProbeSeg)) + 256;
+    const size_t seg_bytes = (size_t)nseg_max * (sizeof(CopySeg) * 2 + sizeof(ProbeSeg)) + sizeof(CopySeg) * kShufMaxRanks + 256;
     if (seg_bytes > js->segs_bytes) {
         if (js->d_segs) pool_free(ctx, js->d_segs);
         if (js->h_segs) cudaFreeHost(js->h_segs);
@@ -738,8 +705,9 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
     }
     CopySeg* h_copy[2] = {(CopySeg*)js->h_segs, (CopySeg*)js->h_segs + nseg_max};
     ProbeSeg* h_probe = (ProbeSeg*)((CopySeg*)js->h_segs + 2 * nseg_max);
-    int ncopy[2] = {0, 0}, nprobe = 0;
-    uint32_t copy_blocks[2] = {0, 0};
+    CopySeg* h_pref = (CopySeg*)(h_probe + nseg_max);
+    int ncopy[2] = {0, 0}, nprobe = 0, npref = 0;
+    uint32_t copy_blocks[2] = {0, 0}, pref_blocks = 0;
     long long probe_chunks = 0;
     for (int sd = 0; sd < 2; ++sd) {
         int64_t dst = 0;
@@ -763,9 +731,50 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
             }
         }
     }
+    if (prefetching)
+        for (int s = 0; s < W; ++s) {
+            if (s == me || pf_len[s] == 0) continue;
+            CopySeg& cs = h_pref[npref++];
+            cs.src_row0 = (uint64_t)pf_first[s]; cs.dst_row0 = (uint64_t)pf_base[s]; cs.rows = (uint32_t)pf_len[s]; cs.blk0 = pref_blocks; cs.src = (uint32_t)s; cs.pad = 0;
+            pref_blocks += (uint32_t)((pf_len[s] + kCopyBlockRows - 1) / kCopyBlockRows);
+        }
     IGL_CUDA_OK(cudaMemcpyAsync(js->d_segs, js->h_segs, seg_bytes - 256, cudaMemcpyHostToDevice, st));
     const CopySeg* d_copy[2] = {(const CopySeg*)js->d_segs, (const CopySeg*)js->d_segs + nseg_max};
     const ProbeSeg* d_probe = (const ProbeSeg*)((const CopySeg*)js->d_segs + 2 * nseg_max);
+    const CopySeg* d_pref = (const CopySeg*)(d_probe + nseg_max);
+    cudaEventRecord(js->ev_segs, st);
+    // ---- 4. every rank's staging is complete (p2p), or the rows travel now (nccl)
+    if (js->mode == IGL_EXCHANGE_P2P) {
+        // the build side's barrier (on this stream) first, then the probe side's (on its own stream when
+        // overlapped) — the same order on every rank
+        IGL_NCCL_OK(g_nccl.AllReduce(js->d_flag, js->d_flag, 1, kNcclInt32, kNcclSum, comm->comm, st));
+        if (overlap) {
+            IGL_NCCL_OK(g_nccl.AllReduce(js->d_flag + 8, js->d_flag + 8, 1, kNcclInt32, kNcclSum, comm->comm, st_l));
+            cudaEventRecord(js->ev_l[2], st_l);
+        }
+        if (prefetching) {
+            IGL_CUDA_OK(cudaStreamWaitEvent(js->stream3, js->ev_l[2], 0));
+            IGL_CUDA_OK(cudaStreamWaitEvent(js->stream3, js->ev_segs, 0));
+            IGL_TRY(launch_seg_copy(ctx, js->side[1], src_cols[1], W, d_pref, npref, pref_blocks, js->side[1].recv.data(), js->stream3));
+            IGL_CUDA_OK(cudaEventRecord(js->ev_copy, js->stream3));
+        }
+    } else {
+        // grouped send/recv of each destination's contiguous staging range (padding included)
+        for (int sd = 0; sd < 2; ++sd) {
+            ShuffleSide& S = js->side[sd];
+            IGL_NCCL_OK(g_nccl.GroupStart());
+            for (int c = 0; c < S.ncols; ++c)
+                for (int p = 0; p < W; ++p) {
+                    int64_t f, l;
+                    range(sd, me, p, parts, f, l);
+                    if (l) IGL_NCCL_OK(g_nccl.Send((const uint8_t*)S.staging[c] + ((size_t)f << S.shift[c]), (size_t)l << S.shift[c], kNcclUint8, p, comm->comm, st));
+                    range(sd, p, me, parts, f, l);
+                    if (l) IGL_NCCL_OK(g_nccl.Recv((uint8_t*)S.recv[c] + ((size_t)rbase[sd][p] << S.shift[c]), (size_t)l << S.shift[c], kNcclUint8, p, comm->comm, st));
+                }
+            IGL_NCCL_OK(g_nccl.GroupEnd());
+        }
+    }
+    cudaEventRecord(js->ev[3], st);
     // ---- 5. build side: pull, build
     ShuffleSide& R = js->side[0];
     ShuffleSide& L = js->side[1];
@@ -804,7 +813,7 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
     std::vector<igl_dev_col> oc;
     int64_t n_out = 0;
     const char* segenv = getenv("IGL_SHUFFLE_FUSED_PROBE");
-    if (seg_probe_possible && !(segenv && segenv[0] == '0') && join_segments_eligible(js->join)) {
+    if (!js->left_join && !(segenv && segenv[0] == '0') && join_segments_eligible(js->join)) {
         SegSource SS{};
         for (int s = 0; s < nsrc; ++s) for (int c = 0; c < L.ncols; ++c) SS.cols[s][c] = src_cols[1][s][c] ? src_cols[1][s][c] : src_cols[1][me][c];
         SS.nsrc = nsrc; SS.dev_segs = d_probe; SS.nsegs = nprobe; SS.nchunks = probe_chunks; SS.total_rows = recv_total[1];
@@ -913,6 +922,7 @@ void igl_join_shuffle_destroy(igl_join_shuffle* js) {
     if (js->stream2) cudaStreamDestroy(js->stream2);
     if (js->stream3) cudaStreamDestroy(js->stream3);
     if (js->ev_copy) cudaEventDestroy(js->ev_copy);
+    if (js->ev_segs) cudaEventDestroy(js->ev_segs);
     igl_join_destroy(js->join);
     delete js;
 }
