@@ -103,6 +103,18 @@ __global__ void join_init_kernel(Slot* slots, uint64_t capacity, JoinSide* side)
     }
 }
 
+#ifndef IGL_BUILD_CAS128
+#define IGL_BUILD_CAS128 1
+#endif
+// 128-bit compare-and-swap on a 16-byte-aligned slot (SASS ATOMG.E.CAS.128); returns the old value.
+__device__ __forceinline__ void cas_u128(void* addr, unsigned long long c0, unsigned long long c1, unsigned long long s0,
+                                         unsigned long long s1, unsigned long long& o0, unsigned long long& o1) {
+    asm volatile(
+        "{\n\t.reg .b128 cmp, swp, old;\n\tmov.b128 cmp, {%2, %3};\n\tmov.b128 swp, {%4, %5};\n\t"
+        "atom.global.cas.b128 old, [%6], cmp, swp;\n\tmov.b128 {%0, %1}, old;\n\t}"
+        : "=l"(o0), "=l"(o1) : "l"(c0), "l"(c1), "l"(s0), "l"(s1), "l"(addr) : "memory");
+}
+
 // ---- K5 build, unique layout ---------------------------------------------------------
 // payload_shift: 2 / 3 = width of the inlined payload column, 0xFF = store the row id.
 constexpr int kBuildThreads = 256;
@@ -153,6 +165,23 @@ __global__ void __launch_bounds__(kBuildThreads) join_build_unique_kernel(const 
         }
         while (pend) {
             unsigned long long prev[U];
+#if IGL_BUILD_CAS128
+            // one 128-bit compare-and-swap claims the slot and writes the payload: an empty slot is
+            // always {kEmptyKey, 0} (join_init_kernel), so the swap succeeds exactly on empty slots —
+            // one L2 atomic per insert instead of a CAS followed by a dependent store to the same sector
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                unsigned long long pv;
+                if ((pend >> u) & 1u) cas_u128(&t.slots[h[u]], (unsigned long long)kEmptyKey, 0ull, (unsigned long long)k[u], val[u], prev[u], pv);
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (!((pend >> u) & 1u)) continue;
+                if (prev[u] == kEmptyKey) pend &= ~(1u << u);
+                else if (prev[u] == k[u]) { t.side->dup_flag = 1; pend &= ~(1u << u); }
+                else h[u] = (h[u] + 1) & t.mask;
+            }
+#else
 #pragma unroll
             for (int u = 0; u < U; ++u)
                 if ((pend >> u) & 1u) prev[u] = atomicCAS(&t.slots[h[u]].key, (unsigned long long)kEmptyKey, (unsigned long long)k[u]);
@@ -163,6 +192,7 @@ __global__ void __launch_bounds__(kBuildThreads) join_build_unique_kernel(const 
                 else if (prev[u] == k[u]) { t.side->dup_flag = 1; pend &= ~(1u << u); }
                 else h[u] = (h[u] + 1) & t.mask;
             }
+#endif
         }
         __syncthreads();   // s_chunk[(it + 1) & 1] is written; s_chunk[it & 1] may be overwritten next round
     }
@@ -1126,6 +1156,8 @@ struct igl_join {
     // device-timeline marks of the last build / probe (igl_join_phase_ms): [0] build start, [1] after its
     // partitioning, [2] build end, [3] probe start, [4] after its partitioning, [5] probe kernel end
     cudaEvent_t ev[6] = {};
+    cudaStream_t aux_stream = nullptr;       // table clearing runs here, beside the build side's partitioning
+    cudaEvent_t ev_aux = nullptr;
     bool ev_build = false, ev_probe = false;
     // a probe that has been queued but not finished (join_probe_begin / join_probe_end)
     int pend_kind = 0;                       // 0 none, 1 flat kernel queued, 2 already complete (pend_rows)
@@ -1443,6 +1475,17 @@ int32_t igl_join_build(igl_join* j, const igl_dev_col* right, int64_t nrows, voi
     j->table.rowids = nullptr;
     const int grid = ctx->sm_count * 8;
     cudaEventRecord(j->ev[0], st);
+    // The table is cleared on a side stream while the build side is partitioned on this one (both are
+    // plain streaming passes; together they take little more than the longer of the two).
+    if (!j->aux_stream) {
+        IGL_CUDA_OK(cudaStreamCreateWithFlags(&j->aux_stream, cudaStreamNonBlocking));
+        IGL_CUDA_OK(cudaEventCreateWithFlags(&j->ev_aux, cudaEventDisableTiming));
+    }
+    IGL_CUDA_OK(cudaStreamWaitEvent(j->aux_stream, j->ev[0], 0));   // whatever used the table before is done
+    join_init_kernel<<<grid, 256, 0, j->aux_stream>>>((Slot*)j->d_slots, cap, (JoinSide*)j->d_side);
+    IGL_CUDA_OK(cudaGetLastError());
+    IGL_CUDA_OK(cudaEventRecord(j->ev_aux, j->aux_stream));
+    ctx->launches++;
     // Large tables: reorder the build side by the top hash bits (partition.cu).
     for (void* p : j->part_right) pool_free(ctx, p);
     j->part_right.clear();
@@ -1477,9 +1520,7 @@ int32_t igl_join_build(igl_join* j, const igl_dev_col* right, int64_t nrows, voi
     if (nr == 2 && !right[0].validity && !right[1].validity &&   // what is there decides, not the schema's nullable flags
         (j->rt[j->rkey] == IGL_T_I32 || j->rt[j->rkey] == IGL_T_I64))
         j->payload_col = 1 - j->rkey;
-    join_init_kernel<<<grid, 256, 0, st>>>((Slot*)j->d_slots, cap, (JoinSide*)j->d_side);
-    IGL_CUDA_OK(cudaGetLastError());
-    ctx->launches++;
+    IGL_CUDA_OK(cudaStreamWaitEvent(st, j->ev_aux, 0));   // the table is clear
     if (nrows > 0) {
         const void* payload = j->payload_col >= 0 ? right[j->payload_col].data : nullptr;
         const int pshift = j->payload_col >= 0 ? (j->rt[j->payload_col] == IGL_T_I32 ? 2 : 3) : 0xFF;
@@ -1745,6 +1786,8 @@ void igl_join_destroy(igl_join* j) {
     if (j->host_hdr) cudaFreeHost(j->host_hdr);
     if (j->host_side) cudaFreeHost(j->host_side);
     for (auto& e : j->ev) if (e) cudaEventDestroy(e);
+    if (j->aux_stream) { cudaStreamSynchronize(j->aux_stream); cudaStreamDestroy(j->aux_stream); }
+    if (j->ev_aux) cudaEventDestroy(j->ev_aux);
     delete j;
 }
 
