@@ -95,6 +95,7 @@ _sig("igl_fp_launch", _i32, _vp, _P(DevCol), _i64, _P(DevCol), _vp)
 _sig("igl_fp_finish", _i32, _vp, _P(_i64), _vp)
 _sig("igl_fp_destroy", None, _vp)
 _sig("igl_fp_is_specialised", _i32, _vp)
+_sig("igl_fp_prepare", _i32, _vp)
 _sig("igl_fp_jit_compile_only", _i32, _vp, _P(_i64))
 _sig("igl_jit_selftest", _i32, _P(_i64))
 _sig("igl_fp_run_static", _i32, _vp, _P(DevCol), _i64, _P(DevCol), _P(_i64), _vp)

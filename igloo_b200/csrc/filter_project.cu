@@ -613,6 +613,29 @@ int32_t igl_fp_jit_compile_only(igl_fp* fp, int64_t* cubin_bytes) {
     return IGL_OK;
 }
 
+// Ahead-of-time specialisation: compiles and loads the plan's kernels now (while the query is being
+// planned, say), so that no later launch pays the ~1 s compile.  IGL_OK with igl_fp_is_specialised
+// still 0 means NVRTC is not available: the interpreter stays in use, nothing else changes.
+int32_t igl_fp_prepare(igl_fp* fp) {
+    if (!fp) return fail(IGL_ERR_INVALID_ARG, "igl_fp_prepare: NULL plan");
+    DeviceGuard g(fp->ctx->device);
+    std::vector<FpProgram*> progs{&fp->one};
+    if (fp->two_pass_ok) { progs.push_back(&fp->mask); progs.push_back(&fp->apply); }
+    for (FpProgram* p : progs) {
+        if (p->jit_state != 0) continue;
+        void* k = nullptr;
+        if (fp_jit_build(jit_spec(*p, fp->has_nulls), &k) >= 0 &&
+            cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem_bytes) == cudaSuccess) {
+            p->jit_kernel = k;
+            p->jit_state = 1;
+        } else {
+            cudaGetLastError();
+            p->jit_state = -1;
+        }
+    }
+    return IGL_OK;
+}
+
 int32_t igl_fp_finish(igl_fp* fp, int64_t* out_rows, void* stream) {
     if (!fp || !fp->launched) return fail(IGL_ERR_INVALID_ARG, "igl_fp_finish: nothing launched");
     igl_ctx* ctx = fp->ctx;

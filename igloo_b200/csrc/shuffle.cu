@@ -287,6 +287,8 @@ struct igl_join_shuffle {
     cudaEvent_t ev_plan = nullptr, ev_wait = nullptr, ev_l[3] = {};   // second stream: probe-side partition start / end / barrier end
     cudaStream_t stream2 = nullptr, stream3 = nullptr;
     cudaEvent_t ev_copy = nullptr, ev_segs = nullptr;
+    cudaStream_t peer_stream[kShufMaxRanks] = {};   // copy-engine prefetch: one stream per peer
+    cudaEvent_t peer_ev[kShufMaxRanks] = {};
     double last_build_ms = -1.0;            // measured build phase of the previous run: sizes the probe-side prefetch
     bool timed = false;
     int64_t stats[12] = {};
@@ -643,10 +645,17 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
         // is one contiguous run per column); the probe kernel then finds those runs in local memory and
         // fetches only the rest across the link itself.  Only a probe that the link would hold back is
         // worth it, and only as much as fits under the build (sized from the previous run's build time).
+        // Measured at C3 on 8 GPUs (5.69 ms per join without): one copy-engine stream moved the
+        // 0.71 GB at only ~245 GB/s and the probe waited for it (8.44 ms); a copy kernel took the build
+        // kernel's SMs and memory system (build 1.1 -> 3.4 ms; 7.80 ms).  Off unless IGL_SHUFFLE_PREFETCH
+        // names a mode: "ce" = one copy-engine stream per peer, "sm" = copy kernel; IGL_SHUFFLE_PREFETCH_FRAC
+        // overrides the share of partitions.
         const char* pe = getenv("IGL_SHUFFLE_PREFETCH");
-        if (overlap && W > 1 && !(pe && pe[0] == '0' && pe[1] == 0)) {
+        const bool pref_ce = pe && pe[0] == 'c', pref_sm = pe && pe[0] == 's';
+        if (overlap && W > 1 && (pref_ce || pref_sm)) {
             ShuffleSide& S = js->side[1];
-            double frac = pe ? atof(pe) : -1.0;
+            const char* fe = getenv("IGL_SHUFFLE_PREFETCH_FRAC");
+            double frac = fe ? atof(fe) : -1.0;
             int64_t remote_rows = 0;
             for (int s = 0; s < W; ++s)
                 if (s != me) for (int p = 0; p < parts; ++p) remote_rows += cnt[1][(size_t)s * bins + ((size_t)me << lp) + p];
@@ -753,9 +762,28 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
             cudaEventRecord(js->ev_l[2], st_l);
         }
         if (prefetching) {
-            IGL_CUDA_OK(cudaStreamWaitEvent(js->stream3, js->ev_l[2], 0));
-            IGL_CUDA_OK(cudaStreamWaitEvent(js->stream3, js->ev_segs, 0));
-            IGL_TRY(launch_seg_copy(ctx, js->side[1], src_cols[1], W, d_pref, npref, pref_blocks, js->side[1].recv.data(), js->stream3));
+            const char* pm = getenv("IGL_SHUFFLE_PREFETCH");
+            if (pm && pm[0] == 'c') {   // copy engines, one stream per peer so the engines work side by side
+                ShuffleSide& S = js->side[1];
+                for (int s = 0; s < W; ++s) {
+                    if (s == me || pf_len[s] == 0) continue;
+                    if (!js->peer_stream[s]) {
+                        IGL_CUDA_OK(cudaStreamCreateWithFlags(&js->peer_stream[s], cudaStreamNonBlocking));
+                        IGL_CUDA_OK(cudaEventCreateWithFlags(&js->peer_ev[s], cudaEventDisableTiming));
+                    }
+                    IGL_CUDA_OK(cudaStreamWaitEvent(js->peer_stream[s], js->ev_l[2], 0));
+                    for (int c = 0; c < S.ncols; ++c)
+                        IGL_CUDA_OK(cudaMemcpyAsync((uint8_t*)S.recv[c] + ((size_t)pf_base[s] << S.shift[c]),
+                                                    src_cols[1][s][c] + ((size_t)pf_first[s] << S.shift[c]), (size_t)pf_len[s] << S.shift[c],
+                                                    cudaMemcpyDefault, js->peer_stream[s]));
+                    IGL_CUDA_OK(cudaEventRecord(js->peer_ev[s], js->peer_stream[s]));
+                    IGL_CUDA_OK(cudaStreamWaitEvent(js->stream3, js->peer_ev[s], 0));
+                }
+            } else {
+                IGL_CUDA_OK(cudaStreamWaitEvent(js->stream3, js->ev_l[2], 0));
+                IGL_CUDA_OK(cudaStreamWaitEvent(js->stream3, js->ev_segs, 0));
+                IGL_TRY(launch_seg_copy(ctx, js->side[1], src_cols[1], W, d_pref, npref, pref_blocks, js->side[1].recv.data(), js->stream3));
+            }
             IGL_CUDA_OK(cudaEventRecord(js->ev_copy, js->stream3));
         }
     } else {
@@ -921,6 +949,8 @@ void igl_join_shuffle_destroy(igl_join_shuffle* js) {
     if (js->ev_wait) cudaEventDestroy(js->ev_wait);
     if (js->stream2) cudaStreamDestroy(js->stream2);
     if (js->stream3) cudaStreamDestroy(js->stream3);
+    for (auto& q : js->peer_stream) if (q) cudaStreamDestroy(q);
+    for (auto& q : js->peer_ev) if (q) cudaEventDestroy(q);
     if (js->ev_copy) cudaEventDestroy(js->ev_copy);
     if (js->ev_segs) cudaEventDestroy(js->ev_segs);
     igl_join_destroy(js->join);

@@ -198,6 +198,11 @@ class FilterProject:
         """True once the plan runs on kernels compiled for it at run time (igl_fp_is_specialised)."""
         return bool(lib.igl_fp_is_specialised(self._h))
 
+    def prepare(self) -> bool:
+        """igl_fp_prepare: compile the plan's specialised kernels now; True when they are in use."""
+        check(lib.igl_fp_prepare(self._h))
+        return self.is_specialised
+
     def alloc_outputs(self, nrows: int) -> List[DeviceColumn]:
         return [DeviceColumn.empty(f.type, nrows, self.ctx.device, nullable=f.nullable) for f in self.out_fields]
 

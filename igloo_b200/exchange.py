@@ -126,3 +126,52 @@ def deserialize_batch(message: RecordBatchMessage) -> pa.RecordBatch:
     if batch.num_rows != message.num_rows:
         raise ValueError(f"RecordBatchMessage says {message.num_rows} rows, the batch holds {batch.num_rows}")
     return batch
+
+
+# ---- fragments on the receiving side -------------------------------------------------------------
+class WireScanExec:
+    """ExecutionPlan over RecordBatchMessage wire bytes: what a fragment that depends on a remote
+    fragment reads (distributed_executor.rs:105-166 collects the replies; :209-222 is the stub this
+    fills).  Feeds any operator of igloo_b200.operators, e.g. the probe side of a HashJoinExec."""
+
+    def __init__(self, messages, schema: pa.Schema):
+        self._messages, self._schema = messages, schema
+
+    def execute(self):
+        for raw in self._messages:
+            yield deserialize_batch(RecordBatchMessage.from_wire(raw))
+
+    def schema(self):
+        return self._schema
+
+
+@dataclass
+class ShuffleJoinSpec:
+    """The plan a FragmentType.Shuffle fragment carries: a hash join whose two inputs are sharded over
+    the worker's GPUs and must be repartitioned by key (the step the reference declares in
+    fragment.rs:8-13 and never builds).  Executed by igl_join_shuffle_* (csrc/shuffle.cu)."""
+    left_fields: list
+    right_fields: list
+    left_key: int
+    right_key: int
+    join_type: int = 0
+    mode: str = "p2p"
+
+
+def execute_fragment(fragment: QueryFragment, ctx=None, rank: int = 0, world: int = 1, shards=None):
+    """The worker-side half of DistributedExecutor::execute_fragments (distributed_executor.rs:36-193)
+    for one fragment.  Scan / Compute / Join fragments run their operator tree and reply with
+    RecordBatchMessage wire bytes (one per batch); a Shuffle fragment runs the multi-GPU join on this
+    rank's device-resident shards (`shards` = (right cols, n_right, left cols, n_left)) and returns
+    (output columns, rows) — its rows never leave the GPUs."""
+    if fragment.fragment_type is FragmentType.Shuffle:
+        from .shuffle import PartitionedJoin
+        spec = fragment.physical_plan
+        if not isinstance(spec, ShuffleJoinSpec):
+            raise TypeError("a Shuffle fragment carries a ShuffleJoinSpec")
+        pj = PartitionedJoin(ctx, rank, world, spec.left_fields, spec.right_fields, spec.left_key, spec.right_key,
+                             join_type=spec.join_type, mode=spec.mode)
+        pj.prepare(*shards)
+        n = pj.run()
+        return pj, n
+    return [serialize_batch(b).to_wire() for b in fragment.physical_plan.execute()]

@@ -168,6 +168,9 @@ void igl_fp_destroy(igl_fp* fp);
  * igl_fp_is_specialised: 1 when the plan's kernels are the specialised ones.
  * igl_fp_jit_compile_only / igl_jit_selftest: compile without loading (diagnostics). */
 int32_t igl_fp_is_specialised(const igl_fp* fp);
+/* Compile and load the plan's specialised kernels NOW (e.g. while the query is planned) instead of
+ * inside the launch that crosses the row threshold; without NVRTC it does nothing and returns OK. */
+int32_t igl_fp_prepare(igl_fp* fp);
 int32_t igl_fp_jit_compile_only(igl_fp* fp, int64_t* cubin_bytes);
 int32_t igl_jit_selftest(int64_t* cubin_bytes);
 /* No counterpart in the reference.  igl_fp_run for callers that must not

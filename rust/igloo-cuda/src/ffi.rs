@@ -32,6 +32,14 @@ extern "C" {
         left_key: *const u8, left_key_len: usize, right_key: *const u8, right_key_len: usize,
         out: *mut *mut IglOp,
     ) -> i32;
+    pub fn igl_op_hash_join_create_ex(
+        ctx: *mut IglCtx, join_type: i32, left: *const FFI_ArrowSchema, right: *const FFI_ArrowSchema,
+        left_keys: *const *const u8, left_key_lens: *const usize, right_keys: *const *const u8, right_key_lens: *const usize,
+        nkeys: i32, out: *mut *mut IglOp,
+    ) -> i32;
+    // multi-GPU join of one worker per GPU: communicator and the collective join
+    pub fn igl_comm_unique_id(id_out: *mut u8) -> i32;
+    pub fn igl_comm_init(ctx: *mut IglCtx, nranks: i32, rank: i32, id: *const u8) -> i32;
     pub fn igl_op_schema(op: *mut IglOp, out: *mut FFI_ArrowSchema) -> i32;
     pub fn igl_op_push_build(op: *mut IglOp, batch: *const FFI_ArrowArray) -> i32;
     pub fn igl_op_finish_build(op: *mut IglOp) -> i32;

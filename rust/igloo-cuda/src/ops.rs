@@ -175,23 +175,24 @@ pub struct GpuHashJoinExec {
     ctx: Arc<GpuContext>,
     left: Arc<dyn ExecutionPlan>,
     right: Arc<dyn ExecutionPlan>,
-    left_key: Arc<dyn PhysicalExpr>,
-    right_key: Arc<dyn PhysicalExpr>,
+    left_keys: Vec<Arc<dyn PhysicalExpr>>,
+    right_keys: Vec<Arc<dyn PhysicalExpr>>,
     join_type: JoinType,
     schema: Arc<Schema>,
 }
 
 impl GpuHashJoinExec {
-    /// Same arguments as `HashJoinExec::new` (hash_join.rs:35-41).  One key pair per side today;
-    /// several pairs return `NotImplemented` and the planner keeps the CPU join.
+    /// Same arguments as `HashJoinExec::new` (hash_join.rs:35-41): one (left, right) key pair per
+    /// `join.on` entry, any expressions (igl_op_hash_join_create_ex).  What the library cannot
+    /// take (Utf8 columns on a join side, Left joins on wide key lists) comes back as
+    /// `NotImplemented` and the planner keeps the CPU join.
     pub fn try_new(ctx: Arc<GpuContext>, left: Arc<dyn ExecutionPlan>, right: Arc<dyn ExecutionPlan>,
                    left_keys: Vec<Arc<dyn PhysicalExpr>>, right_keys: Vec<Arc<dyn PhysicalExpr>>,
                    join_type: JoinType) -> DataFusionResult<Self> {
-        if left_keys.len() != 1 || right_keys.len() != 1 {
-            return Err(DataFusionError::NotImplemented("igloo-cuda: multi-column join keys".into()));
+        if left_keys.is_empty() || left_keys.len() != right_keys.len() {
+            return Err(DataFusionError::Plan("join keys come in pairs".into()));
         }
-        let me = Self { ctx, left, right, left_key: left_keys[0].clone(), right_key: right_keys[0].clone(), join_type,
-                        schema: Arc::new(Schema::empty()) };
+        let me = Self { ctx, left, right, left_keys, right_keys, join_type, schema: Arc::new(Schema::empty()) };
         // the library derives the output schema (left fields, right fields, `right_` prefix on a
         // name clash: hash_join.rs:54-63); creating the operator once here validates keys and types
         let op = me.new_op()?;
@@ -201,10 +202,15 @@ impl GpuHashJoinExec {
     fn new_op(&self) -> DataFusionResult<OpHandle> {
         let l = FFI_ArrowSchema::try_from(self.left.schema().as_ref())?;
         let r = FFI_ArrowSchema::try_from(self.right.schema().as_ref())?;
-        let (lk, rk) = (to_bytecode(&self.left_key)?, to_bytecode(&self.right_key)?);
+        let lk: Vec<Vec<u8>> = self.left_keys.iter().map(to_bytecode).collect::<DataFusionResult<_>>()?;
+        let rk: Vec<Vec<u8>> = self.right_keys.iter().map(to_bytecode).collect::<DataFusionResult<_>>()?;
+        let (lp, rp): (Vec<*const u8>, Vec<*const u8>) = (lk.iter().map(|v| v.as_ptr()).collect(), rk.iter().map(|v| v.as_ptr()).collect());
+        let (ll, rl): (Vec<usize>, Vec<usize>) = (lk.iter().map(|v| v.len()).collect(), rk.iter().map(|v| v.len()).collect());
         let jt = match self.join_type { JoinType::Inner => 0, JoinType::Left => 1, JoinType::Right => 2, JoinType::Full => 3 };
         let mut op = std::ptr::null_mut();
-        check(unsafe { igl_op_hash_join_create(self.ctx.0, jt, &l, &r, lk.as_ptr(), lk.len(), rk.as_ptr(), rk.len(), &mut op) })?;
+        check(unsafe {
+            igl_op_hash_join_create_ex(self.ctx.0, jt, &l, &r, lp.as_ptr(), ll.as_ptr(), rp.as_ptr(), rl.as_ptr(), lk.len() as i32, &mut op)
+        })?;
         Ok(OpHandle(op))
     }
 }

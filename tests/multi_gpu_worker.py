@@ -50,6 +50,17 @@ def main():
             print(f"mode={mode} fused={bool(st['fused_probe'])} log2_parts={st['log2_parts']} hot={'yes' if st['hot_keys'] else 'no'} "
                   f"prefetched={st['prefetched_bytes']} rows={tot} OK", flush=True)
         pj.close()
+    # the same join as a FragmentType.Shuffle fragment (exchange.py: the plan node the reference declares
+    # in fragment.rs:8-13 and never builds), executed by the worker-side fragment executor
+    from igloo_b200.exchange import FragmentType, QueryFragment, ShuffleJoinSpec, execute_fragment
+    frag = QueryFragment("shuffle-join", FragmentType.Shuffle, ShuffleJoinSpec(wl.lf, wl.rf, wl.lkey, wl.rkey, jt), f"worker-{rank}")
+    pj, n = execute_fragment(frag, ctx, rank, world, (right, nr, left, nl))
+    got = [None] * world
+    dist.all_gather_object(got, (ctx.digest(pj.out, n), n))
+    assert sum(g[1] for g in got) == want_rows and bench.fold_digests([g[0] for g in got]) == want
+    pj.close()
+    if rank == 0:
+        print("shuffle fragment OK", flush=True)
     dist.barrier()
     dist.destroy_process_group()
 

@@ -222,6 +222,12 @@ def test_run_time_specialised_kernels_match_the_interpreter_and_the_oracle(ctx, 
         seen.append((fp.is_specialised, n, out[0].data[:n].cpu().numpy().copy()))
     assert [x[0] for x in seen] == [False, False, True, True]       # 100 003 rows per call, threshold 250 000
     assert all(x[1] == seen[0][1] and np.array_equal(x[2], seen[0][2]) for x in seen)
+    # igl_fp_prepare: the same specialisation ahead of time, before the plan has seen a single row
+    fp2 = FilterProject(ctx, _fields(t), col("a") < 250, [(col("b") + col("a")).alias("s")])
+    assert not fp2.is_specialised
+    assert fp2.prepare() and fp2.is_specialised
+    out, n = fp2.run(cols, t.num_rows)
+    assert n == seen[0][1] and np.array_equal(out[0].data[:n].cpu().numpy(), seen[0][2])
 
 
 def test_predicate_must_be_boolean(ctx):

@@ -33,7 +33,7 @@ def test_two_gpu_partitioned_join_digest(workload, scale, extra, jt, fused):
                         "--master-port", "29533", os.path.join(ROOT, "tests", "multi_gpu_worker.py"), workload, str(scale)] + ([extra] if extra else []),
                        capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
-    assert "mode=p2p" in r.stdout and "mode=nccl" in r.stdout
+    assert "mode=p2p" in r.stdout and "mode=nccl" in r.stdout and "shuffle fragment OK" in r.stdout
     assert f"mode=p2p fused={fused}" in r.stdout, r.stdout[-500:]
     # skewed probe keys must be noticed: their rows stay local, their build rows go to every rank
     skewed = extra == "skew"   # (Zipf(1.1) over two GPUs stays within 1.15 x of an even split: the hash alone serves it)

@@ -196,3 +196,30 @@ def test_hash_join_exec_key_lists_computed_keys_and_boolean_columns(ctx):
         assert got.num_rows == want.num_rows > 0
         assert_same_multiset(got.cast(pa.schema([pa.field(f.name, f.type, True) for f in got.schema])),
                              want.cast(pa.schema([pa.field(f.name, f.type, True) for f in want.schema])))
+
+
+def test_fragment_exchange_wire_format_carries_gpu_operator_output(ctx):
+    """a Compute fragment's FilterExec output travels as RecordBatchMessage wire bytes
+    (distributed.proto:53-57; the stubs at distributed_executor.rs:203-222) and feeds the probe side
+    of a HashJoinExec in the dependent Join fragment."""
+    from igloo_b200.exchange import (FragmentType, QueryFragment, RecordBatchMessage, WireScanExec, deserialize_batch,
+                                     execute_fragment)
+    from igloo_b200.operators import FilterExec, HashJoinExec, MemoryScanExec
+    rng = np.random.default_rng(21)
+    nb, nl = 3_000, 40_000
+    orders = pa.table({"o_key": np.arange(nb, dtype=np.int64), "o_total": rng.random(nb)},
+                      schema=pa.schema([pa.field("o_key", pa.int64(), False), pa.field("o_total", pa.float64(), False)]))
+    items = pa.table({"l_key": rng.integers(0, 2 * nb, nl), "l_qty": rng.integers(1, 50, nl).astype(np.int32)},
+                     schema=pa.schema([pa.field("l_key", pa.int64(), False), pa.field("l_qty", pa.int32(), False)]))
+    compute = QueryFragment("f1", FragmentType.Compute, FilterExec(MemoryScanExec(items, 8192), col("l_qty") > 40, ctx), "worker-0")
+    wire = execute_fragment(compute)
+    assert wire and all(isinstance(w, bytes) for w in wire)
+    assert sum(RecordBatchMessage.from_wire(w).num_rows for w in wire) == int((items.column("l_qty").to_numpy() > 40).sum())
+    join = QueryFragment("f2", FragmentType.Join,
+                         HashJoinExec(WireScanExec(wire, items.schema), MemoryScanExec(orders), [col("l_key")], [col("o_key")], 0, ctx),
+                         "coordinator", dependencies=["f1"])
+    got = pa.Table.from_batches([deserialize_batch(RecordBatchMessage.from_wire(w)) for w in execute_fragment(join)])
+    m = (items.column("l_qty").to_numpy() > 40) & (items.column("l_key").to_numpy() < nb)
+    assert got.num_rows == int(m.sum()) and got.schema.names == ["l_key", "l_qty", "o_key", "o_total"]
+    assert np.array_equal(np.sort(got.column("l_key").to_numpy()), np.sort(items.column("l_key").to_numpy()[m]))
+    assert np.array_equal(got.column("o_total").to_numpy(), orders.column("o_total").to_numpy()[got.column("o_key").to_numpy()])
