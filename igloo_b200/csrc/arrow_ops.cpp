@@ -417,6 +417,16 @@ struct igl_op {
     std::vector<size_t> build_cap;
     std::vector<uint8_t*> build_valid;
     std::vector<uint8_t> build_any_null;     // a build batch carried nulls in this column (else the bitmap is dropped at finish_build)
+    // Utf8 columns ride along by row id: the device join sees an Int32 row-id column in a string
+    // column's place (the probe chunk's row number / the build side's row number) and the strings are
+    // gathered by the ids it emits (utf8.cu), as filter_record_batch's compaction does for Filter.
+    std::vector<uint8_t> l_utf8, r_utf8;     // per column: 1 = Utf8
+    bool any_utf8 = false;
+    void* d_iota = nullptr;                  // 0 .. max(chunk_rows, build rows) - 1
+    int64_t iota_rows = 0;
+    std::vector<void*> build_str;            // per Utf8 build column: all its bytes on the device
+    std::vector<size_t> build_str_cap, build_str_used;
+    std::vector<void*> build_off;            // per Utf8 build column: build_rows + 1 offsets
     int64_t build_rows = 0, build_rows_cap = 0;
 };
 
@@ -571,6 +581,21 @@ int32_t fp_flush(igl_op* op) {
     return fp_begin(op);
 }
 
+// 0, 1, 2, ... on the device: the row-id column that stands in for string columns inside the join.
+int32_t ensure_iota(igl_op* op, int64_t rows) {
+    if (rows <= op->iota_rows && op->d_iota) return IGL_OK;
+    if (rows >= ((int64_t)1 << 31)) return fail(IGL_ERR_UNSUPPORTED, "a join side with Utf8 columns is limited to 2^31 rows");
+    igl_ctx* ctx = op->ctx;
+    IGL_CUDA_OK(cudaStreamSynchronize(ctx->stream));   // nothing still reads the old one
+    if (op->d_iota) pool_free(ctx, op->d_iota);
+    op->d_iota = nullptr; op->iota_rows = 0;
+    const int64_t cap = rows + rows / 4 + 1024;
+    IGL_TRY(pool_alloc(ctx, pad64((size_t)cap * 4), &op->d_iota));
+    IGL_TRY(launch_iota_i32(ctx, (int32_t*)op->d_iota, cap, ctx->stream));
+    op->iota_rows = cap;
+    return IGL_OK;
+}
+
 // Room for `n` more rows on the device-resident build side (every column grows by doubling; one
 // wait per growth step, after all the copies have been queued).
 int32_t join_build_reserve(igl_op* op, int64_t n) {
@@ -602,9 +627,45 @@ int32_t join_build_reserve(igl_op* op, int64_t n) {
             op->build_valid[c] = (uint8_t*)v;
         }
     }
+    for (int c = 0; c < op->n_right; ++c) {
+        if (!op->r_utf8[c]) continue;
+        void* p = nullptr;
+        IGL_TRY(pool_alloc(ctx, pad64((size_t)(cap + 1) * 4), &p));
+        if (op->build_off[c]) {
+            IGL_CUDA_OK(cudaMemcpyAsync(p, op->build_off[c], (size_t)(op->build_rows + 1) * 4, cudaMemcpyDeviceToDevice, st));
+            old_blocks.push_back(op->build_off[c]);
+        }
+        op->build_off[c] = p;
+    }
     if (!old_blocks.empty()) IGL_CUDA_OK(cudaStreamSynchronize(st));
     for (void* q : old_blocks) pool_free(ctx, q);
     op->build_rows_cap = cap;
+    return IGL_OK;
+}
+
+// Appends one staged chunk of a Utf8 build column: its bytes behind the column's bytes so far, its
+// offsets shifted by that amount behind the offsets so far.
+int32_t join_build_append_utf8(igl_op* op, int c, StagedCol& sc, int64_t n, cudaStream_t st) {
+    igl_ctx* ctx = op->ctx;
+    const size_t used = op->build_str_used[c], add = sc.utf8_used;
+    if (used + add >= ((size_t)1 << 31)) return fail(IGL_ERR_UNSUPPORTED, "a Utf8 build column is limited to 2 GiB of string bytes");
+    if (used + add > op->build_str_cap[c]) {
+        const size_t cap = std::max(used + add, op->build_str_cap[c] * 2);
+        void* p = nullptr;
+        IGL_TRY(pool_alloc(ctx, pad64(cap), &p));
+        if (op->build_str[c]) {
+            IGL_CUDA_OK(cudaMemcpyAsync(p, op->build_str[c], used, cudaMemcpyDeviceToDevice, st));
+            IGL_CUDA_OK(cudaStreamSynchronize(st));
+            pool_free(ctx, op->build_str[c]);
+        }
+        op->build_str[c] = p; op->build_str_cap[c] = cap;
+    }
+    if (add) IGL_CUDA_OK(cudaMemcpyAsync((uint8_t*)op->build_str[c] + used, sc.h_data, add, cudaMemcpyHostToDevice, st));
+    for (int64_t i = 0; i <= n; ++i) sc.h_off[i] += (int32_t)used;   // chunk-relative -> column-relative (undone below)
+    IGL_CUDA_OK(cudaMemcpyAsync((int32_t*)op->build_off[c] + op->build_rows, sc.h_off, (size_t)(n + 1) * 4, cudaMemcpyHostToDevice, st));
+    IGL_CUDA_OK(cudaStreamSynchronize(st));
+    for (int64_t i = 0; i <= n; ++i) sc.h_off[i] -= (int32_t)used;
+    op->build_str_used[c] = used + add;
     return IGL_OK;
 }
 
@@ -623,7 +684,9 @@ int32_t join_build_flush(igl_op* op) {
     }
     for (int c = 0; c < op->n_right; ++c) {
         const int w = type_width(S.fields[c].type);
-        if (S.fields[c].type == IGL_T_BOOL)
+        if (S.fields[c].type == IGL_T_UTF8)
+            IGL_TRY(join_build_append_utf8(op, c, S.cols[c], n, st));
+        else if (S.fields[c].type == IGL_T_BOOL)
             IGL_CUDA_OK(cudaMemcpyAsync((uint8_t*)op->build_dev[c] + (op->build_rows >> 3), S.cols[c].h_data, (size_t)(n + 7) / 8, cudaMemcpyHostToDevice, st));
         else
         IGL_CUDA_OK(cudaMemcpyAsync((uint8_t*)op->build_dev[c] + (size_t)op->build_rows * w, S.cols[c].h_data, (size_t)n * w, cudaMemcpyHostToDevice, st));
@@ -634,6 +697,53 @@ int32_t join_build_flush(igl_op* op) {
     op->build_rows += n;
     for (int c = 0; c < op->n_right; ++c) if (S.cols[c].any_null) op->build_any_null[c] = 1;
     S.reset();
+    return IGL_OK;
+}
+
+// One Utf8 output column of a finished probe chunk: the join emitted row ids in its place (probe chunk
+// rows for a left column, build rows for a right one; the null-extended rows of a Left join carry an
+// unset validity bit); the strings are gathered by them — lengths, scan, bytes (utf8.cu) — and copied
+// down on the download stream.
+int32_t join_gather_utf8(igl_op* op, int c, int64_t n_out, OutCol& oc, std::vector<void*>& dev_free) {
+    igl_ctx* ctx = op->ctx;
+    cudaStream_t st = ctx->stream;
+    auto& PD = op->jpend;
+    const bool is_left = c < op->n_left;
+    const int sc = is_left ? c : c - op->n_left;
+    int32_t* rowid = (int32_t*)PD.dout[c].data;
+    const int32_t* src_off = is_left ? PD.dev[c].offsets : (const int32_t*)op->build_off[sc];
+    const uint8_t* src_bytes = is_left ? (const uint8_t*)PD.dev[c].data : (const uint8_t*)op->build_str[sc];
+    const uint8_t* src_valid = is_left ? PD.dev[c].validity : op->build_valid[sc];
+    const bool null_rows = !is_left && op->left_join;
+    if (null_rows) IGL_TRY(launch_mask_rowids(ctx, rowid, PD.dout[c].validity, n_out, st));
+    const bool want_valid = src_valid != nullptr || null_rows;
+    void *d_off = nullptr, *scratch = nullptr, *vbytes = nullptr, *d_bytes = nullptr, *d_bits = nullptr;
+    const size_t sbytes = 256 + ((size_t)n_out / 2048 + 8) * 8 + 64;
+    IGL_TRY(pool_alloc(ctx, pad64((size_t)(n_out + 1) * 4), &d_off)); dev_free.push_back(d_off);
+    IGL_TRY(pool_alloc(ctx, sbytes, &scratch)); dev_free.push_back(scratch);
+    if (want_valid) { IGL_TRY(pool_alloc(ctx, pad64((size_t)n_out + 1), &vbytes)); dev_free.push_back(vbytes); }
+    IGL_TRY(utf8_gather_offsets(ctx, src_off, src_valid, rowid, n_out, (int32_t*)d_off, (uint8_t*)vbytes, scratch, sbytes, st));
+    oc.off = (int32_t*)pinned_pool().get(pad64((size_t)(n_out + 1) * 4));
+    if (!oc.off) return fail(IGL_ERR_OOM, "pinned output allocation failed");
+    IGL_CUDA_OK(cudaMemcpyAsync(oc.off, d_off, (size_t)(n_out + 1) * 4, cudaMemcpyDeviceToHost, st));
+    IGL_CUDA_OK(cudaStreamSynchronize(st));   // the byte total decides the size of what follows
+    const size_t total = (size_t)oc.off[n_out];
+    IGL_TRY(pool_alloc(ctx, pad64(total), &d_bytes)); dev_free.push_back(d_bytes);
+    IGL_TRY(utf8_gather_bytes(ctx, src_off, src_bytes, rowid, n_out, (const int32_t*)d_off, (uint8_t*)d_bytes, st));
+    if (want_valid) {
+        IGL_TRY(pool_alloc(ctx, pad64((size_t)(n_out + 7) / 8 + 4), &d_bits)); dev_free.push_back(d_bits);
+        if (launch_pack_bits((const uint8_t*)vbytes, (uint32_t*)d_bits, nullptr, n_out, n_out, ctx->sm_count, st) != cudaSuccess) return fail(IGL_ERR_CUDA, "validity pack failed");
+        ctx->launches++;
+    }
+    IGL_CUDA_OK(cudaStreamSynchronize(st));   // the download stream may start
+    oc.data = pinned_pool().get(pad64(total));
+    if (!oc.data) return fail(IGL_ERR_OOM, "pinned output allocation failed");
+    if (total) IGL_CUDA_OK(cudaMemcpyAsync(oc.data, d_bytes, total, cudaMemcpyDeviceToHost, op->s_down));
+    if (want_valid) {
+        oc.valid = (uint8_t*)pinned_pool().get(pad64((size_t)(n_out + 7) / 8 + 4));
+        if (!oc.valid) return fail(IGL_ERR_OOM, "pinned output allocation failed");
+        IGL_CUDA_OK(cudaMemcpyAsync(oc.valid, d_bits, (size_t)(n_out + 7) / 8, cudaMemcpyDeviceToHost, op->s_down));
+    }
     return IGL_OK;
 }
 
@@ -655,7 +765,8 @@ int32_t join_probe_end_chunk(igl_op* op) {
     ob.nrows = n_out;
     ob.cols.resize(nc);
     for (int c = 0; c < nc && rc >= 0; ++c) {
-        ob.cols[c].type = PD.dout[c].type;
+        ob.cols[c].type = op->out_fields[c].type;
+        if (op->out_fields[c].type == IGL_T_UTF8) { rc = join_gather_utf8(op, c, n_out, ob.cols[c], ob.dev_free); continue; }
         if (op->alias_right_key >= 0 && c == op->n_left + op->alias_right_key && PD.dev[op->alias_left_key].validity == nullptr &&
             op->build_valid[op->alias_right_key] == nullptr) {   // no NULL keys on either side in this chunk
             ob.cols[c].data = ob.cols[op->alias_left_key].data;   // left columns come first: already set
@@ -673,12 +784,15 @@ int32_t join_probe_end_chunk(igl_op* op) {
         rc = fail(IGL_ERR_CUDA, "event for the output download failed");
     if (rc < 0) {
         cudaStreamSynchronize(op->s_down);
+        cudaStreamSynchronize(st);
         cleanup();
+        for (void* p : ob.dev_free) pool_free(ctx, p);
         if (ob.done) cudaEventDestroy(ob.done);
-        for (auto& c : ob.cols) { if (!c.alias) pinned_pool().put(c.data); pinned_pool().put(c.valid); }
+        for (auto& c : ob.cols) { if (!c.alias) pinned_pool().put(c.data); pinned_pool().put(c.valid); pinned_pool().put(c.off); }
         return rc;
     }
-    ob.dev_free.swap(PD.to_free);   // the device output blocks live until the download has passed
+    ob.dev_free.insert(ob.dev_free.end(), PD.to_free.begin(), PD.to_free.end());   // the device output blocks live until the download has passed
+    PD.to_free.clear();
     op->ready.push_back(std::move(ob));
     return IGL_OK;
 }
@@ -697,12 +811,20 @@ int32_t join_probe_begin_chunk(igl_op* op, int64_t n, std::vector<igl_dev_col>&&
     }
     HostTrace tr_alloc("op.begin.alloc+probe");
     int64_t cap = n;
-    if (igl_join_has_duplicates(op->join)) IGL_TRY(igl_join_probe_count(op->join, PD.dev.data(), n, &cap, st));
+    if (igl_join_has_duplicates(op->join)) {
+        std::vector<igl_dev_col> cdev = PD.dev;
+        for (int c = 0; c < op->n_left; ++c)
+            if (op->l_utf8[c]) cdev[c] = igl_dev_col{IGL_T_I32, 0, op->d_iota, nullptr, nullptr};
+        IGL_TRY(igl_join_probe_count(op->join, cdev.data(), n, &cap, st));
+    }
     const int nc = op->n_left + op->n_right;
     PD.dout.assign(nc, igl_dev_col{});
     auto cleanup = [&]() { for (void* p : PD.to_free) pool_free(ctx, p); PD.to_free.clear(); };
+    std::vector<igl_dev_col> jdev = PD.dev;   // what the device join reads: row ids where the strings are
+    for (int c = 0; c < op->n_left; ++c)
+        if (op->l_utf8[c]) jdev[c] = igl_dev_col{IGL_T_I32, 0, op->d_iota, nullptr, nullptr};
     for (int c = 0; c < nc; ++c) {
-        PD.dout[c].type = op->out_fields[c].type;
+        PD.dout[c].type = op->out_fields[c].type == IGL_T_UTF8 ? IGL_T_I32 : op->out_fields[c].type;
         void* p = nullptr;
         const size_t cap1 = (size_t)std::max<int64_t>(cap, 1);
         int32_t rc = pool_alloc(ctx, pad64(PD.dout[c].type == IGL_T_BOOL ? (cap1 + 7) / 8 + 8 : cap1 * type_width(PD.dout[c].type)), &p);
@@ -715,7 +837,7 @@ int32_t join_probe_begin_chunk(igl_op* op, int64_t n, std::vector<igl_dev_col>&&
     int32_t rc;
     {
         HostTrace tr("op.begin.probe");
-        rc = join_probe_begin(op->join, PD.dev.data(), n, PD.dout.data(), cap, st);
+        rc = join_probe_begin(op->join, jdev.data(), n, PD.dout.data(), cap, st);
     }
     if (rc < 0) { cudaStreamSynchronize(st); cleanup(); return rc; }
     PD.n = n; PD.cap = cap;
@@ -729,6 +851,7 @@ int32_t join_probe_flush(igl_op* op) {
     Staging& S = op->in;
     const int64_t n = S.rows;
     if (n == 0) return IGL_OK;
+    if (op->any_utf8) IGL_TRY(ensure_iota(op, std::max<int64_t>(n, S.chunk_rows)));
     std::vector<igl_dev_col> dev;
     { TraceScope ts(op->trace, TR_UPLOAD); IGL_TRY(S.upload(op->s_up, dev)); }
     { TraceScope ts(op->trace, TR_BEGIN); IGL_TRY(join_probe_begin_chunk(op, n, std::move(dev))); }
@@ -926,8 +1049,11 @@ int32_t igl_op_hash_join_create_ex(igl_ctx* ctx, int32_t join_type, const struct
     for (auto& f : lf) { lt.push_back(f.type); ln.push_back(f.nullable); }
     for (auto& f : rf) { rt.push_back(f.type); rn.push_back(f.nullable); }
     auto destroy_partial = [&]() { igl_op_destroy(op.release()); };
-    for (auto& f : lf) if (f.type == IGL_T_UTF8) { destroy_partial(); return fail(IGL_ERR_UNSUPPORTED, "Utf8 column \"%s\" on a join side is not supported yet", f.name.c_str()); }
-    for (auto& f : rf) if (f.type == IGL_T_UTF8) { destroy_partial(); return fail(IGL_ERR_UNSUPPORTED, "Utf8 column \"%s\" on a join side is not supported yet", f.name.c_str()); }
+    // Utf8 columns: the device join gets an Int32 row-id column in their place (never NULL itself; the
+    // string's own validity is applied when the strings are gathered)
+    op->l_utf8.assign(op->n_left, 0); op->r_utf8.assign(op->n_right, 0);
+    for (int c = 0; c < op->n_left; ++c) if (lt[c] == IGL_T_UTF8) { op->l_utf8[c] = 1; op->any_utf8 = true; lt[c] = IGL_T_I32; ln[c] = 0; }
+    for (int c = 0; c < op->n_right; ++c) if (rt[c] == IGL_T_UTF8) { op->r_utf8[c] = 1; op->any_utf8 = true; rt[c] = IGL_T_I32; rn[c] = 0; }
     int32_t rc = IGL_OK;
     for (int k = 0; k < nkeys && rc >= 0; ++k) {   // one pair per `join.on` entry (physical_planner.rs:106-120)
         igl_expr *le = nullptr, *re = nullptr;
@@ -935,6 +1061,10 @@ int32_t igl_op_hash_join_create_ex(igl_ctx* ctx, int32_t join_type, const struct
         if (rc >= 0) rc = igl_expr_compile(ctx, right_keys[k], right_key_lens[k], rt.data(), rn.data(), op->n_right, &re);
         if (le) op->lkeys.push_back(le);
         if (re) op->rkeys.push_back(re);
+        if (rc >= 0) {   // a key must not read a string column (it would see the row ids)
+            for (auto& nd : le->nodes) if (nd.op == IGL_OP_COL && op->l_utf8[nd.col]) rc = fail(IGL_ERR_UNSUPPORTED, "Utf8 join keys are not supported on the GPU (left key %d)", k);
+            for (auto& nd : re->nodes) if (nd.op == IGL_OP_COL && op->r_utf8[nd.col]) rc = fail(IGL_ERR_UNSUPPORTED, "Utf8 join keys are not supported on the GPU (right key %d)", k);
+        }
     }
     if (rc >= 0) {
         op->lkey = op->lkeys[0]; op->rkey = op->rkeys[0];
@@ -962,6 +1092,8 @@ int32_t igl_op_hash_join_create_ex(igl_ctx* ctx, int32_t join_type, const struct
     op->build_cap.assign(op->n_right, 0);
     op->build_valid.assign(op->n_right, nullptr);
     op->build_any_null.assign(op->n_right, 0);
+    op->build_str.assign(op->n_right, nullptr); op->build_off.assign(op->n_right, nullptr);
+    op->build_str_cap.assign(op->n_right, 0); op->build_str_used.assign(op->n_right, 0);
     op->in.elide_all_valid = true;
     op->in_alt = op->in;   // second probe chunk buffer of the same shape
     if (cudaStreamCreateWithFlags(&op->s_up, cudaStreamNonBlocking) != cudaSuccess ||
@@ -1013,9 +1145,18 @@ int32_t igl_op_finish_build(igl_op* op) {
     IGL_TRY(join_build_flush(op));
     for (int c = 0; c < op->n_right; ++c)   // a nullable column that never carried a null: no bitmap, non-null kernels
         if (op->build_valid[c] && !op->build_any_null[c]) { pool_free(op->ctx, op->build_valid[c]); op->build_valid[c] = nullptr; }
+    if (op->any_utf8) IGL_TRY(ensure_iota(op, std::max<int64_t>(op->build_rows, op->in.chunk_rows)));
     std::vector<igl_dev_col> cols(op->n_right);
     for (int c = 0; c < op->n_right; ++c) {
         cols[c].type = op->build.fields[c].type;
+        if (op->r_utf8[c]) {   // the join carries the build row number; the strings follow it after the probe
+            cols[c] = igl_dev_col{IGL_T_I32, 0, op->d_iota, nullptr, nullptr};
+            if (!op->build_off[c]) {   // an empty build side still needs a valid offsets array
+                void* p = nullptr; IGL_TRY(pool_alloc(op->ctx, 256, &p)); op->build_off[c] = p;
+                IGL_CUDA_OK(cudaMemsetAsync(p, 0, 256, op->ctx->stream));
+            }
+            continue;
+        }
         if (!op->build_dev[c]) { void* p = nullptr; IGL_TRY(pool_alloc(op->ctx, 256, &p)); op->build_dev[c] = p; }
         cols[c].data = op->build_dev[c];
         cols[c].validity = op->build_valid[c];
@@ -1113,6 +1254,9 @@ void igl_op_destroy(igl_op* op) {
     for (auto* e : op->lkeys) igl_expr_destroy(e);
     for (auto* e : op->rkeys) igl_expr_destroy(e);
     for (void* p : op->build_dev) pool_free(op->ctx, p);
+    for (void* p : op->build_str) pool_free(op->ctx, p);
+    for (void* p : op->build_off) pool_free(op->ctx, p);
+    pool_free(op->ctx, op->d_iota);
     for (uint8_t* p : op->build_valid) pool_free(op->ctx, p);
     delete op;
 }

@@ -37,6 +37,9 @@ int32_t utf8_gather_offsets(igl_ctx* ctx, const int32_t* src_off, const uint8_t*
 int32_t utf8_gather_bytes(igl_ctx* ctx, const int32_t* src_off, const uint8_t* src_bytes, const int32_t* rowid,
                           long long n, const int32_t* out_off, uint8_t* out_bytes, cudaStream_t st);
 
+int32_t launch_iota_i32(igl_ctx* ctx, int32_t* out, long long n, cudaStream_t st);
+int32_t launch_mask_rowids(igl_ctx* ctx, int32_t* rowid, const uint8_t* valid_bits, long long n, cudaStream_t st);
+
 // Radix partition of a column set by the top bits of the join hash (partition.cu).
 // dst[c]: device buffers of nrows rows; scratch: 3 * ((1 << log2_parts) + 1) * 8 bytes.
 bool radix_partition_supported(const igl_dev_col* cols, int ncols);

@@ -17,6 +17,11 @@ __global__ void utf8_lengths_kernel(const int32_t* __restrict__ src_off, const u
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const int32_t r = rowid ? rowid[i] : (int32_t)i;
+        if (r < 0) {   // no source row (the null-extended side of a Left join): an empty, NULL string
+            out_off[i + 1] = 0;
+            if (out_valid_bytes) out_valid_bytes[i] = 0;
+            continue;
+        }
         out_off[i + 1] = src_off[r + 1] - src_off[r];
         if (out_valid_bytes) out_valid_bytes[i] = src_valid ? ((src_valid[r >> 3] >> (r & 7)) & 1) : 1;
     }
@@ -90,9 +95,35 @@ __global__ void utf8_gather_kernel(const int32_t* __restrict__ src_off, const ui
     const long long warps = ((long long)gridDim.x * blockDim.x) >> 5;
     for (long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < n; i += warps) {
         const int32_t r = rowid ? rowid[i] : (int32_t)i;
+        if (r < 0) continue;
         const int32_t s = src_off[r], len = src_off[r + 1] - s, d = out_off[i];
         for (int32_t b = lane; b < len; b += 32) out_bytes[d + b] = src_bytes[s + b];
     }
+}
+
+__global__ void iota_i32_kernel(int32_t* out, long long n) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = (int32_t)i;
+}
+__global__ void mask_rowids_kernel(int32_t* rowid, const uint8_t* __restrict__ valid_bits, long long n) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+        if (!((valid_bits[i >> 3] >> (i & 7)) & 1)) rowid[i] = -1;
+}
+int32_t launch_iota_i32(igl_ctx* ctx, int32_t* out, long long n, cudaStream_t st) {
+    if (n <= 0) return IGL_OK;
+    iota_i32_kernel<<<(int)std::min<long long>((n + 255) / 256, (long long)ctx->sm_count * 8), 256, 0, st>>>(out, n);
+    IGL_CUDA_OK(cudaGetLastError());
+    ctx->launches++;
+    return IGL_OK;
+}
+// rowid[i] = -1 wherever bit i of `valid_bits` is clear (row ids of null-extended join rows)
+int32_t launch_mask_rowids(igl_ctx* ctx, int32_t* rowid, const uint8_t* valid_bits, long long n, cudaStream_t st) {
+    if (n <= 0) return IGL_OK;
+    mask_rowids_kernel<<<(int)std::min<long long>((n + 255) / 256, (long long)ctx->sm_count * 8), 256, 0, st>>>(rowid, valid_bits, n);
+    IGL_CUDA_OK(cudaGetLastError());
+    ctx->launches++;
+    return IGL_OK;
 }
 
 // Gathers a Utf8 column by row ids.  out_off must hold n+1 entries, scratch

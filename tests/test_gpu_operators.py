@@ -223,3 +223,38 @@ def test_fragment_exchange_wire_format_carries_gpu_operator_output(ctx):
     assert got.num_rows == int(m.sum()) and got.schema.names == ["l_key", "l_qty", "o_key", "o_total"]
     assert np.array_equal(np.sort(got.column("l_key").to_numpy()), np.sort(items.column("l_key").to_numpy()[m]))
     assert np.array_equal(got.column("o_total").to_numpy(), orders.column("o_total").to_numpy()[got.column("o_key").to_numpy()])
+
+
+@pytest.mark.parametrize("jt", [0, 1])
+def test_hash_join_exec_carries_utf8_columns_on_both_sides(ctx, jt):
+    """The reference's own fixture shape, users(id, name, age) (integration_test.rs:21-29), joined with
+    an orders table that carries a nullable string as well: HashJoinExec stores and emits whole rows
+    (hash_join.rs:125, 229-236), so string columns ride along on either side.  On the GPU the join sees
+    row ids in their place and the strings are gathered afterwards."""
+    from igloo_b200.operators import HashJoinExec, MemoryScanExec
+    rng = np.random.default_rng(77)
+    names = GOLD["rows"]["name"] if "rows" in GOLD and "name" in GOLD["rows"] else ["Alice", "Bob", "Charlie", "Diana", "Eve"]
+    nu, no = 3_000, 20_000
+    users = pa.table({"id": pa.array(np.arange(1, nu + 1), pa.int32()),
+                      "name": pa.array([f"{names[i % len(names)]}-{i}" for i in range(nu)], pa.string()),
+                      "age": pa.array(rng.integers(18, 80, nu), pa.int32())},
+                     schema=pa.schema([pa.field("id", pa.int32(), False), pa.field("name", pa.string(), False), pa.field("age", pa.int32(), False)]))
+    notes = [None if rng.random() < 0.2 else ("n" * int(rng.integers(0, 12))) + str(i) for i in range(no)]
+    orders = pa.table({"user_id": pa.array(rng.integers(1, nu + 500, no), pa.int32()), "amount": rng.random(no),
+                       "note": pa.array(notes, pa.string())})
+    # orders probe, users build (strings on both sides); then the other way round
+    for left, right, lk, rk in ((orders, users, "user_id", "id"), (users, orders, "id", "user_id")):
+        j = HashJoinExec(MemoryScanExec(left, 2048), MemoryScanExec(right, 1000), [col(lk)], [col(rk)], jt, ctx)
+        got, _ = collect(j)
+        L = orc.Table.scan(arrow_to_columns(left)); R = orc.Table.scan(arrow_to_columns(right))
+        from tests.util import tight_fields
+        lf, rf = tight_fields(left), tight_fields(right)
+        want = columns_to_arrow(L.hash_join(R, [lower(col(lk), lf)[0]], [lower(col(rk), rf)[0]], jt, 0, 1).columns())
+        assert got.schema.names == want.schema.names and got.num_rows == want.num_rows > 0
+        assert_same_multiset(got.cast(pa.schema([pa.field(f.name, f.type, True) for f in got.schema])),
+                             want.cast(pa.schema([pa.field(f.name, f.type, True) for f in want.schema])))
+    # a string key is refused (the planner keeps the CPU join)
+    from igloo_b200._lib import IglooCudaError
+    with pytest.raises(IglooCudaError) as e:
+        collect(HashJoinExec(MemoryScanExec(users), MemoryScanExec(users), [col("name")], [col("name")], 0, ctx))
+    assert e.value.code == -2
