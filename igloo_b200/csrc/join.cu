@@ -143,6 +143,9 @@ __global__ void __launch_bounds__(kBuildThreads) join_build_unique_kernel(const 
     for (int it = 0;; ++it) {
         const long long chunk = s_chunk[it & 1];
         if (chunk >= nchunks) break;
+        // a duplicate has been seen: the build will be redone as CSR runs, so stop here — every further
+        // insert of a heavy key would be one more atomic on the same slot (C5b: 29 M of them)
+        if (*reinterpret_cast<volatile unsigned int*>(&t.side->dup_flag)) break;
         if (threadIdx.x == 0) s_chunk[(it + 1) & 1] = (long long)atomicAdd(ticket, 1u);
         const long long i0 = chunk * kBuildChunk + threadIdx.x;
         uint64_t k[U], h[U];
@@ -274,6 +277,23 @@ __global__ void join_build_fill_kernel(const void* __restrict__ keys, int key_ty
         if (in && !normal) pos = atomicAdd(&t.side->run_end[valid ? 1 : 0], 1u);
         if (in) rowids[pos] = (uint32_t)i;   // after this pass the low word / run_end is the END of the run
     }
+}
+
+// The build columns in CSR order: dst[pos] = src[rowids[pos]].  Afterwards the row ids are the
+// identity, so a probe row's matches (one run) are read from consecutive rows of the build columns
+// instead of one random 8-byte gather per output row and column.
+__global__ void gather_rows_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, const uint32_t* __restrict__ rowids,
+                                   long long n, int shift) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const uint32_t r = rowids[i];
+        if (shift == 2) ((uint32_t*)dst)[i] = ((const uint32_t*)src)[r];
+        else ((uint64_t*)dst)[i] = ((const uint64_t*)src)[r];
+    }
+}
+__global__ void iota_u32_kernel(uint32_t* out, long long n) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = (uint32_t)i;
 }
 
 // ---- probe ---------------------------------------------------------------------------------
@@ -1145,6 +1165,7 @@ struct igl_join {
     int log2_parts = 0;
     bool prepartitioned = false;             // both sides arrive ordered by the top hash bits: skip the radix passes
     std::vector<void*> part_right;           // partitioned build columns (owned)
+    std::vector<void*> csr_right;            // duplicate layout: the build columns in CSR order (owned)
     std::vector<void*> part_left;            // partitioned probe columns (owned, grow-only)
     int64_t part_left_rows = 0;
     void* part_scratch = nullptr;
@@ -1477,6 +1498,8 @@ int32_t igl_join_build(igl_join* j, const igl_dev_col* right, int64_t nrows, voi
     // Large tables: reorder the build side by the top hash bits (partition.cu).
     for (void* p : j->part_right) pool_free(ctx, p);
     j->part_right.clear();
+    for (void* p : j->csr_right) pool_free(ctx, p);
+    j->csr_right.clear();
     j->log2_parts = 0;
     {
         // IGL_JOIN_PARTITION=0 switches it off (A/B measurements in profiles/README.md).
@@ -1536,6 +1559,25 @@ int32_t igl_join_build(igl_join* j, const igl_dev_col* right, int64_t nrows, voi
         IGL_CUDA_OK(cudaGetLastError());
         ctx->launches += 4;
         j->table.rowids = (const uint32_t*)j->d_rowids;
+        // Heavy buckets: put the build columns themselves into CSR order (one gather pass over the build
+        // side), so that expanding a run reads consecutive rows.  Columns with a validity bitmap keep
+        // the row-id indirection.
+        bool reorder = nrows > 0 && !(getenv("IGL_JOIN_CSR_REORDER") && getenv("IGL_JOIN_CSR_REORDER")[0] == '0');
+        for (int c = 0; c < nr && reorder; ++c) if (right[c].validity) reorder = false;
+        for (void* p : j->csr_right) pool_free(ctx, p);
+        j->csr_right.clear();
+        if (reorder) {
+            for (int c = 0; c < nr; ++c) {
+                void* p = nullptr;
+                IGL_TRY(pool_alloc(ctx, (size_t)nrows * (j->rt[c] == IGL_T_I32 ? 4 : 8) + 256, &p));
+                j->csr_right.push_back(p);
+                gather_rows_kernel<<<grid, 256, 0, st>>>((const uint8_t*)right[c].data, (uint8_t*)p, (const uint32_t*)j->d_rowids, nrows, j->rt[c] == IGL_T_I32 ? 2 : 3);
+            }
+            iota_u32_kernel<<<grid, 256, 0, st>>>((uint32_t*)j->d_rowids, nrows);
+            IGL_CUDA_OK(cudaGetLastError());
+            ctx->launches += nr + 1;
+            for (int c = 0; c < nr; ++c) j->right[c].data = j->csr_right[c];
+        }
         IGL_CUDA_OK(cudaStreamSynchronize(st));
     }
     j->built = true;
@@ -1773,6 +1815,7 @@ void igl_join_destroy(igl_join* j) {
     pool_free(j->ctx, j->scratch);
     pool_free(j->ctx, j->part_scratch);
     for (void* p : j->part_right) pool_free(j->ctx, p);
+    for (void* p : j->csr_right) pool_free(j->ctx, p);
     for (void* p : j->part_left) pool_free(j->ctx, p);
     for (void* p : j->valid_planes) pool_free(j->ctx, p);
     if (j->host_hdr) cudaFreeHost(j->host_hdr);
