@@ -143,10 +143,14 @@ __global__ void __launch_bounds__(kBuildThreads) join_build_unique_kernel(const 
     for (int it = 0;; ++it) {
         const long long chunk = s_chunk[it & 1];
         if (chunk >= nchunks) break;
-        // a duplicate has been seen: the build will be redone as CSR runs, so stop here — every further
-        // insert of a heavy key would be one more atomic on the same slot (C5b: 29 M of them)
-        if (*reinterpret_cast<volatile unsigned int*>(&t.side->dup_flag)) break;
-        if (threadIdx.x == 0) s_chunk[(it + 1) & 1] = (long long)atomicAdd(ticket, 1u);
+        if (threadIdx.x == 0) {
+            long long nxt = (long long)atomicAdd(ticket, 1u);
+            // a duplicate has been seen: the build will be redone as CSR runs, so stop claiming work —
+            // every further insert of a heavy key would be one more atomic on the same slot (C5b: 29 M
+            // of them).  Read beside the ticket, one chunk ahead: its latency hides behind the inserts.
+            if (*reinterpret_cast<volatile unsigned int*>(&t.side->dup_flag)) nxt = nchunks;
+            s_chunk[(it + 1) & 1] = nxt;
+        }
         const long long i0 = chunk * kBuildChunk + threadIdx.x;
         uint64_t k[U], h[U];
         unsigned long long val[U];
@@ -311,15 +315,23 @@ struct JoinProbeParams {
     uint8_t out_shift[2 * kJoinMaxCols];
     const uint8_t* right_data[kJoinMaxCols];
     const uint8_t* right_valid[kJoinMaxCols];
-    // duplicate layout: runs longer than kGiantRun are not walked by the probing warp (one warp
+    // duplicate layout: runs longer than kListRun are not walked by the probing warp (one warp
     // would emit millions of rows alone) but listed here as {left row, run end, count, output
     // position} and expanded afterwards by the whole grid (join_expand_giant_kernel)
-    unsigned long long* giant_list;
+    unsigned long long* giant_list;   // runs of kListRun+1 .. kHugeRun rows: expanded one CTA per run
     unsigned long long* giant_count;
     unsigned int giant_cap;
+    unsigned long long* huge_list;    // runs longer than kHugeRun: expanded by the whole grid, one after another
+    unsigned long long* huge_count;
+    unsigned int huge_cap;
 };
 
-constexpr uint32_t kGiantRun = 8192;
+// A probing warp walks a run of up to kListRun rows itself (32 rows per step).  Longer runs would hold
+// its tile — and, through the ordered output scan, every tile behind it — for as long as one warp
+// needs to write them (measured at C5b/8: 120 ms per join with an 8192-row limit), so they are listed
+// and expanded after the probe kernel: a CTA per listed run, the whole grid per run beyond kHugeRun.
+constexpr uint32_t kListRun = 256;
+constexpr uint32_t kHugeRun = 65536;
 
 struct Match {
     unsigned long long val;   // unique: payload or row id;  duplicate: {count, run end}
@@ -605,13 +617,14 @@ __device__ __forceinline__ void multi_emit(const JoinProbeParams& P, const Multi
             const uint32_t he = __shfl_sync(0xffffffffu, t.rend[r], src);
             const long long hp = __shfl_sync(0xffffffffu, pos, src);
             const int hrow = row - lane + src;
-            if (hc > kGiantRun && P.giant_list) {   // warp-uniform
+            if (hc > kListRun && P.giant_list) {   // warp-uniform
+                const bool huge = hc > kHugeRun;
                 unsigned long long slot = 0;
-                if (lane == 0) slot = atomicAdd(P.giant_count, 1ull);
+                if (lane == 0) slot = atomicAdd(huge ? P.huge_count : P.giant_count, 1ull);
                 slot = __shfl_sync(0xffffffffu, slot, 0);
-                if (slot < P.giant_cap) {
+                if (slot < (huge ? P.huge_cap : P.giant_cap)) {
                     if (lane == 0) {
-                        unsigned long long* e = P.giant_list + 4 * slot;
+                        unsigned long long* e = (huge ? P.huge_list : P.giant_list) + 4 * slot;
                         e[0] = (unsigned long long)(t.row_begin + hrow); e[1] = he; e[2] = hc; e[3] = (unsigned long long)hp;
                     }
                     continue;
@@ -674,42 +687,49 @@ constexpr int kFlatChunk = kFlatThreads * kFlatRows;   // 1024 rows per CTA iter
 constexpr int kFlatClaim = 4;                          // consecutive chunks claimed per ticket
 static_assert(kFlatChunk == kSegChunkRows, "ProbeSeg::chunk0 counts chunks of the flat probe kernel");
 
-// Expands the listed giant runs: every CTA takes a slice of every run.  The left row's values
-// are read once per thread from the (global) left columns; right columns are gathered by row id.
+// Expands the listed runs.  The left row's values are read once per thread from the (global) left
+// columns; right columns are gathered by row id (the identity when the build columns were put into
+// CSR order).  `first`/`step` select the rows of the run this thread writes.
 template <bool HAS_NULLS>
-__global__ void __launch_bounds__(256) join_expand_giant_kernel(const __grid_constant__ JoinProbeParams P) {
-    const unsigned long long n = min(*P.giant_count, (unsigned long long)P.giant_cap);
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    for (unsigned long long e = 0; e < n; ++e) {
-        const unsigned long long* ent = P.giant_list + 4 * e;
-        const long long lrow = (long long)ent[0];
-        const uint32_t rend = (uint32_t)ent[1], cnt = (uint32_t)ent[2];
-        const long long pos0 = (long long)ent[3];
-        uint64_t lv[kJoinMaxCols];
-        uint8_t lok[kJoinMaxCols];
+__device__ __forceinline__ void expand_run(const JoinProbeParams& P, const unsigned long long* ent, long long first, long long step) {
+    const long long lrow = (long long)ent[0];
+    const uint32_t rend = (uint32_t)ent[1], cnt = (uint32_t)ent[2];
+    const long long pos0 = (long long)ent[3];
+    uint64_t lv[kJoinMaxCols];
+    uint8_t lok[kJoinMaxCols];
+    for (int c = 0; c < P.n_left; ++c) {
+        lv[c] = P.out_shift[c] == 2 ? (uint64_t)((const uint32_t*)P.T.data[c])[lrow] : ((const uint64_t*)P.T.data[c])[lrow];
+        lok[c] = (HAS_NULLS && P.T.valid[c]) ? (uint8_t)bit_at(P.T.valid[c], lrow) : (uint8_t)1;
+    }
+    for (long long j = first; j < (long long)cnt; j += step) {
+        const long long pos = pos0 + j;
+        const uint32_t rid = P.table.rowids[rend - cnt + (uint32_t)j];
         for (int c = 0; c < P.n_left; ++c) {
-            lv[c] = P.out_shift[c] == 2 ? (uint64_t)((const uint32_t*)P.T.data[c])[lrow] : ((const uint64_t*)P.T.data[c])[lrow];
-            lok[c] = (HAS_NULLS && P.T.valid[c]) ? (uint8_t)bit_at(P.T.valid[c], lrow) : (uint8_t)1;
+            if (!P.out_data[c]) continue;
+            if (P.out_shift[c] == 2) st_cs_u32((uint8_t*)P.out_data[c] + (pos << 2), (uint32_t)lv[c]);
+            else st_cs_u64((uint8_t*)P.out_data[c] + (pos << 3), lv[c]);
+            if (HAS_NULLS && P.out_valid[c]) P.out_valid[c][pos] = lok[c];
         }
-        for (long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x; j < (long long)cnt; j += stride) {
-            const long long pos = pos0 + j;
-            const uint32_t rid = P.table.rowids[rend - cnt + (uint32_t)j];
-            for (int c = 0; c < P.n_left; ++c) {
-                if (!P.out_data[c]) continue;
-                if (P.out_shift[c] == 2) st_cs_u32((uint8_t*)P.out_data[c] + (pos << 2), (uint32_t)lv[c]);
-                else st_cs_u64((uint8_t*)P.out_data[c] + (pos << 3), lv[c]);
-                if (HAS_NULLS && P.out_valid[c]) P.out_valid[c][pos] = lok[c];
-            }
-            for (int c = 0; c < P.n_right; ++c) {
-                const int oc = P.n_left + c;
-                if (!P.out_data[oc]) continue;
-                const uint64_t v = P.out_shift[oc] == 2 ? (uint64_t)((const uint32_t*)P.right_data[c])[rid] : ((const uint64_t*)P.right_data[c])[rid];
-                if (P.out_shift[oc] == 2) st_cs_u32((uint8_t*)P.out_data[oc] + (pos << 2), (uint32_t)v);
-                else st_cs_u64((uint8_t*)P.out_data[oc] + (pos << 3), v);
-                if (HAS_NULLS && P.out_valid[oc]) P.out_valid[oc][pos] = P.right_valid[c] ? (uint8_t)bit_at(P.right_valid[c], rid) : (uint8_t)1;
-            }
+        for (int c = 0; c < P.n_right; ++c) {
+            const int oc = P.n_left + c;
+            if (!P.out_data[oc]) continue;
+            const uint64_t v = P.out_shift[oc] == 2 ? (uint64_t)((const uint32_t*)P.right_data[c])[rid] : ((const uint64_t*)P.right_data[c])[rid];
+            if (P.out_shift[oc] == 2) st_cs_u32((uint8_t*)P.out_data[oc] + (pos << 2), (uint32_t)v);
+            else st_cs_u64((uint8_t*)P.out_data[oc] + (pos << 3), v);
+            if (HAS_NULLS && P.out_valid[oc]) P.out_valid[oc][pos] = P.right_valid[c] ? (uint8_t)bit_at(P.right_valid[c], rid) : (uint8_t)1;
         }
     }
+}
+
+template <bool HAS_NULLS>
+__global__ void __launch_bounds__(256) join_expand_giant_kernel(const __grid_constant__ JoinProbeParams P) {
+    // listed runs: one CTA per run
+    const unsigned long long nm = min(*P.giant_count, (unsigned long long)P.giant_cap);
+    for (unsigned long long e = blockIdx.x; e < nm; e += gridDim.x) expand_run<HAS_NULLS>(P, P.giant_list + 4 * e, threadIdx.x, blockDim.x);
+    // huge runs: every CTA takes a slice of every run
+    const unsigned long long nh = min(*P.huge_count, (unsigned long long)P.huge_cap);
+    for (unsigned long long e = 0; e < nh; ++e)
+        expand_run<HAS_NULLS>(P, P.huge_list + 4 * e, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
 }
 
 struct FlatProbeParams {
@@ -1688,9 +1708,9 @@ int32_t join_probe_begin(igl_join* j, const igl_dev_col* left, int64_t nrows, ig
         P.T.data[c] = (const uint8_t*)left[c].data;
         P.T.valid[c] = j->has_nulls ? left[c].validity : nullptr;
     }
-    constexpr unsigned int kGiantCap = 4096;   // listed giant runs per probe call; more are walked in place
+    constexpr unsigned int kGiantCap = 1u << 18, kHugeCap = 4096;   // listed runs per probe call; more are walked in place
     const size_t scan_part = (256 + (size_t)scan_scratch_words(P.T.ntiles) * 8 + 255) & ~(size_t)255;
-    size_t need = scan_part + (j->csr ? (size_t)kGiantCap * 32 : 0);
+    size_t need = scan_part + (j->csr ? ((size_t)kGiantCap + kHugeCap) * 32 : 0);
     if (need > j->scratch_bytes) {
         if (j->scratch) pool_free(ctx, j->scratch);
         j->scratch = nullptr; j->scratch_bytes = 0;
@@ -1704,6 +1724,9 @@ int32_t join_probe_begin(igl_join* j, const igl_dev_col* left, int64_t nrows, ig
         P.giant_list = (unsigned long long*)((uint8_t*)j->scratch + scan_part);
         P.giant_count = &P.T.hdr->aux[3];
         P.giant_cap = kGiantCap;
+        P.huge_list = P.giant_list + 4ull * kGiantCap;
+        P.huge_count = &P.T.hdr->aux[2];
+        P.huge_cap = kHugeCap;
     }
     P.table = j->table;
     P.key_slot = j->lkey;

@@ -430,20 +430,11 @@ __global__ void __launch_bounds__(THREADS, THREADS >= 1024 ? 1 : 2) radix_scatte
 #pragma unroll
         for (int q = 0; q < BPT; ++q) s_cnt[(it + 1) & 1][tid * BPT + q] = 0;   // the other parity's counters: last read before the previous tile's final barrier
         __syncthreads();
-        // exclusive scan of the bin counts (BPT bins per thread) + global reservation.  The reserved
-        // positions are first needed by the write-out: the atomics' round trip to L2 runs under the
-        // permutation phase, their results are stored only after it.
-        unsigned int c[BPT];
-        unsigned long long gb[BPT];
-        {
-            unsigned int sum = 0;
+        {   // exclusive scan of the bin counts (BPT bins per thread) + global reservation
+            // (keeping the reservation atomics in flight across the permutation phase was measured: no gain)
+            unsigned int c[BPT], sum = 0;
 #pragma unroll
             for (int q = 0; q < BPT; ++q) { c[q] = tid * BPT + q < nbins ? cnt[tid * BPT + q] : 0; sum += c[q]; }
-#pragma unroll
-            for (int q = 0; q < BPT; ++q) {
-                const int bq = tid * BPT + q;
-                gb[q] = c[q] ? P.offsets[bq] + atomicAdd(&P.cursor[bq], (unsigned long long)c[q]) : 0ull;
-            }
             unsigned int inc = sum;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -457,7 +448,10 @@ __global__ void __launch_bounds__(THREADS, THREADS >= 1024 ? 1 : 2) radix_scatte
 #pragma unroll
             for (int q = 0; q < BPT; ++q) {
                 const int bq = tid * BPT + q;
-                if (bq < nbins) cnt[bq] = ex;
+                if (bq < nbins) {
+                    cnt[bq] = ex;
+                    s_gbase[bq] = c[q] ? P.offsets[bq] + atomicAdd(&P.cursor[bq], (unsigned long long)c[q]) : 0ull;
+                }
                 ex += c[q];
             }
         }
@@ -470,8 +464,6 @@ __global__ void __launch_bounds__(THREADS, THREADS >= 1024 ? 1 : 2) radix_scatte
                 s_part[slot] = (unsigned short)bin[r];
             }
         }
-#pragma unroll
-        for (int q = 0; q < BPT; ++q) if (tid * BPT + q < nbins) s_gbase[tid * BPT + q] = gb[q];
         __syncthreads();
         // write-out: consecutive threads -> consecutive slots -> runs of consecutive destination rows
         unsigned long long d[ROWS];

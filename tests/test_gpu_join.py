@@ -344,3 +344,23 @@ def test_boolean_columns_ride_along_and_can_be_the_key(ctx):
     small_r = pa.table({"flag": pa.array([True, False], pa.bool_()), "name_id": pa.array([1, 0], pa.int64())})
     got, _ = check(ctx, left, small_r, "on", "flag", 0)                               # Boolean key
     assert got.num_rows == nl
+
+
+def test_runs_beyond_the_huge_limit_are_expanded_by_the_whole_grid(ctx):
+    """Three tiers of duplicate runs in one probe call: up to 256 rows walked by the probing warp,
+    up to 65536 rows expanded one CTA per run, longer ones by the whole grid (C5b's heaviest keys)."""
+    rng = np.random.default_rng(41)
+    nb, nl = 160_000, 3_000
+    rk = rng.integers(100, 4000, nb)
+    rk[:80_000] = 7            # huge
+    rk[80_000:90_000] = 8      # listed
+    rk[90_000:90_200] = 9      # walked in place
+    right = pa.table({"k": rk.astype(np.int64), "v": rng.integers(0, 1 << 50, nb), "z": rng.integers(0, 99, nb).astype(np.int32)})
+    lk = rng.integers(100, 5000, nl)
+    lk[[3, 999, 2500]] = 7
+    lk[[10, 20]] = 8
+    lk[[30, 40, 50]] = 9
+    left = pa.table({"k": lk.astype(np.int64), "w": rng.random(nl)})
+    got, j = check(ctx, left, right, "k", "k", 0)
+    assert j.has_duplicates and got.num_rows > 3 * 80_000 + 2 * 10_000
+    check(ctx, left, right, "k", "k", 1)
