@@ -592,32 +592,42 @@ __device__ __forceinline__ void multi_lookup(const JoinProbeParams& P, MultiTile
     t.count = (long long)running;
 }
 
+// Per-warp scratch of the duplicate-layout probe: one entry per probe row of the warp's group.
+struct MultiWarpScratch {
+    uint32_t eexcl[32 * 4];   // exclusive prefix of the rows this warp writes itself (listed runs count 0)
+    uint32_t excl[32 * 4];    // exclusive prefix of ALL output rows (where a probe row's matches start)
+    uint32_t rend[32 * 4];    // end of the probe row's run in the CSR
+    uint32_t cnt[32 * 4];     // bit 31: the row matched (else a null-extended Left-join row)
+};
+
+// Writes the warp's output rows.  Runs longer than kListRun are listed for the expansion kernel (a
+// run of millions of rows must not hang on one warp).  Everything else is expanded load-balanced:
+// the warp's output rows are numbered consecutively, lane l writes rows l, l + 32, ... and finds the
+// probe row each belongs to by bisecting the prefix sums — whatever the mix of run lengths, all 32
+// lanes write (a per-lane loop over its own row's matches leaves 31 lanes waiting for the longest).
 template <int R, bool HAS_NULLS>
-__device__ __forceinline__ void multi_emit(const JoinProbeParams& P, const MultiTile<R>& t, long long wbase, int warp, int lane) {
+__device__ __forceinline__ void multi_emit(const JoinProbeParams& P, const MultiTile<R>& t, long long wbase, int warp, int lane,
+                                           MultiWarpScratch& S) {
     if (t.count == 0) return;
+    static_assert(R <= 4, "MultiWarpScratch holds 4 rows per lane");
     const int row0 = warp * (32 * R) + lane;
+    uint32_t ec[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         const int row = row0 + r * 32;
         const uint32_t c = t.cnt[r];
-        const bool hit = (t.hitb[r] >> lane) & 1u;
+        ec[r] = c;
         const long long pos = wbase + t.excl[r];
-        const bool heavy = c > 32;
-        if (c && !heavy) {
-            if (!hit) emit_row<HAS_NULLS>(P, t.stage, row, pos, false, 0, 0);
-            else
-                for (uint32_t j = 0; j < c; ++j)
-                    emit_row<HAS_NULLS>(P, t.stage, row, pos + j, true, P.table.rowids[t.rend[r] - c + j], 0);
-        }
-        uint32_t hv = __ballot_sync(0xffffffffu, heavy);
-        while (hv) {   // warp-cooperative walk of one long run
+        uint32_t hv = __ballot_sync(0xffffffffu, c > kListRun);
+        while (hv) {   // list one long run (warp-uniform)
             const int src = __ffs(hv) - 1;
             hv &= hv - 1;
             const uint32_t hc = __shfl_sync(0xffffffffu, c, src);
             const uint32_t he = __shfl_sync(0xffffffffu, t.rend[r], src);
             const long long hp = __shfl_sync(0xffffffffu, pos, src);
             const int hrow = row - lane + src;
-            if (hc > kListRun && P.giant_list) {   // warp-uniform
+            bool listed = false;
+            if (P.giant_list) {
                 const bool huge = hc > kHugeRun;
                 unsigned long long slot = 0;
                 if (lane == 0) slot = atomicAdd(huge ? P.huge_count : P.giant_count, 1ull);
@@ -627,19 +637,54 @@ __device__ __forceinline__ void multi_emit(const JoinProbeParams& P, const Multi
                         unsigned long long* e = (huge ? P.huge_list : P.giant_list) + 4 * slot;
                         e[0] = (unsigned long long)(t.row_begin + hrow); e[1] = he; e[2] = hc; e[3] = (unsigned long long)hp;
                     }
-                    continue;
+                    listed = true;
                 }
             }
-            for (uint32_t j = lane; j < hc; j += 32)
-                emit_row<HAS_NULLS>(P, t.stage, hrow, hp + j, true, P.table.rowids[he - hc + j], 0);
+            if (!listed)   // the list is full: the warp walks the run itself
+                for (uint32_t j = lane; j < hc; j += 32)
+                    emit_row<HAS_NULLS>(P, t.stage, hrow, hp + j, true, P.table.rowids[he - hc + j], 0);
+            if (lane == src) ec[r] = 0;
         }
     }
+    // prefix sums over the rows the warp writes itself, in the order of the output (r, then lane)
+    uint32_t run = 0;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        uint32_t inc = ec[r];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t nb = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += nb;
+        }
+        const int idx = r * 32 + lane;
+        S.eexcl[idx] = run + inc - ec[r];
+        S.excl[idx] = t.excl[r];
+        S.rend[idx] = t.rend[r];
+        S.cnt[idx] = t.cnt[r] | (((t.hitb[r] >> lane) & 1u) << 31);
+        run += __shfl_sync(0xffffffffu, inc, 31);
+    }
+    __syncwarp();
+    const uint32_t total = run;   // warp-uniform
+    for (uint32_t o = lane; o < total; o += 32) {
+        int lo = 0, hi = 32 * R - 1;   // last idx with eexcl[idx] <= o
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (S.eexcl[mid] <= o) lo = mid; else hi = mid - 1;
+        }
+        const uint32_t j = o - S.eexcl[lo];
+        const uint32_t cw = S.cnt[lo], c = cw & 0x7FFFFFFFu;
+        const bool hit = cw >> 31;
+        const int row = warp * (32 * R) + (lo & 31) + (lo >> 5) * 32;
+        emit_row<HAS_NULLS>(P, t.stage, row, wbase + S.excl[lo] + j, hit, hit ? P.table.rowids[S.rend[lo] - c + j] : 0u, 0);
+    }
+    __syncwarp();   // the scratch is rewritten by the next tile
 }
 
 template <int R, bool HAS_NULLS>
 __global__ void __launch_bounds__(kPipeThreads, kPipeMinCtas) join_probe_multi_kernel(const __grid_constant__ JoinProbeParams P) {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ PipeShared sh;
+    __shared__ MultiWarpScratch wscratch[kPipeComputeWarps];
     TilePipe<true, HAS_NULLS> pipe(P.T, sh, smem);
     pipe.init();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -656,7 +701,7 @@ __global__ void __launch_bounds__(kPipeThreads, kPipeMinCtas) join_probe_multi_k
             pipe.post_count(it + 1, warp, nxt.count);
         }
         const long long wbase = pipe.wait_base(it, warp);
-        multi_emit<R, HAS_NULLS>(P, cur, wbase, warp, lane);
+        multi_emit<R, HAS_NULLS>(P, cur, wbase, warp, lane, wscratch[warp]);
         pipe.release(it);
         if (!has_next) break;
         cur = nxt;
@@ -1200,6 +1245,9 @@ struct igl_join {
     cudaEvent_t ev[6] = {};
     bool ev_build = false, ev_probe = false;
     // a probe that has been queued but not finished (join_probe_begin / join_probe_end)
+    // the last igl_join_probe_count (a caller sizes its output with it; igl_join_probe then needs the same number)
+    const void* counted_keys = nullptr;
+    int64_t counted_nrows = -1, counted_rows = 0;
     int pend_kind = 0;                       // 0 none, 1 flat kernel queued, 2 already complete (pend_rows)
     int64_t pend_rows = 0, pend_nrows = 0;
     bool pend_dense = false;
@@ -1499,6 +1547,7 @@ int32_t igl_join_build(igl_join* j, const igl_dev_col* right, int64_t nrows, voi
         if (right[c].type != j->rt[c]) return fail(IGL_ERR_INVALID_ARG, "right column %d has type %d, join expects %d", c, right[c].type, j->rt[c]);
     j->right.assign(right, right + nr);
     j->n_right_rows = nrows;
+    j->counted_keys = nullptr;
     // capacity: power of two >= rows / load factor
     uint64_t cap = 1024;
     while ((double)cap * ctx->cfg.hash_load_factor < (double)nrows) cap <<= 1;
@@ -1628,6 +1677,7 @@ int32_t igl_join_probe_count(igl_join* j, const igl_dev_col* left, int64_t nrows
     IGL_CUDA_OK(cudaMemcpyAsync(j->host_hdr, j->scratch, sizeof(PipeHeader), cudaMemcpyDeviceToHost, st));
     IGL_CUDA_OK(cudaStreamSynchronize(st));
     *out_rows = (int64_t)j->host_hdr->aux[0];
+    j->counted_keys = kc.data; j->counted_nrows = nrows; j->counted_rows = *out_rows;
     return IGL_OK;
 }
 
@@ -1662,7 +1712,10 @@ int32_t join_probe_begin(igl_join* j, const igl_dev_col* left, int64_t nrows, ig
         if (out_capacity < need) return fail(IGL_ERR_INVALID_ARG, "output capacity %lld < %lld rows", (long long)out_capacity, (long long)need);
     } else if (j->csr) {
         int64_t need = 0;
-        IGL_TRY(igl_join_probe_count(j, left, nrows, &need, stream));
+        // the caller has usually just asked (to size `out`): same key column, same rows, same table
+        if (j->counted_keys == left[j->lkey].data && j->counted_nrows == nrows) need = j->counted_rows;
+        else IGL_TRY(igl_join_probe_count(j, left, nrows, &need, stream));
+        j->counted_keys = nullptr;
         if (out_capacity < need) return fail(IGL_ERR_INVALID_ARG, "output capacity %lld < %lld rows", (long long)out_capacity, (long long)need);
     }
     std::vector<igl_dev_col> pleft;
