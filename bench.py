@@ -657,7 +657,14 @@ def run_e2e(ctx, wl, pinned, steps):
         last = None
         for b in op.execute():
             rows += b.num_rows
-            d2h += b.nbytes
+            # bytes that crossed PCIe: two columns of a batch may share one host buffer (an inner equi-join's
+            # right key equals its left key bit for bit, so the operator copies it down once)
+            seen = set()
+            for c in b.columns:
+                for buf in c.buffers():
+                    if buf is not None and buf.address not in seen:
+                        seen.add(buf.address)
+                        d2h += min(buf.size, (b.num_rows * c.type.bit_width + 7) // 8 if buf.size > b.num_rows else buf.size)
             last = b
         dt = time.perf_counter() - t0
         if s > 0:

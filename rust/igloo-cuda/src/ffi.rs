@@ -13,6 +13,17 @@ pub struct IglConfig {
 }
 pub enum IglCtx {}
 pub enum IglOp {}
+pub enum IglExpr {}
+pub enum IglJoinShuffle {}
+/// `igl_dev_col`: a device-resident Arrow column (values, validity bitmap, Utf8 offsets).
+#[repr(C)]
+pub struct IglDevCol {
+    pub type_: i32,
+    pub reserved: i32,
+    pub data: *mut std::ffi::c_void,
+    pub validity: *mut u8,
+    pub offsets: *mut i32,
+}
 
 pub const IGL_OK: i32 = 0;
 pub const IGL_AGAIN: i32 = 1;
@@ -40,6 +51,17 @@ extern "C" {
     // multi-GPU join of one worker per GPU: communicator and the collective join
     pub fn igl_comm_unique_id(id_out: *mut u8) -> i32;
     pub fn igl_comm_init(ctx: *mut IglCtx, nranks: i32, rank: i32, id: *const u8) -> i32;
+    pub fn igl_join_shuffle_create(
+        ctx: *mut IglCtx, join_type: i32, left_types: *const i32, left_nullable: *const u8, n_left: i32,
+        right_types: *const i32, right_nullable: *const u8, n_right: i32, left_key: *const IglExpr, right_key: *const IglExpr,
+        mode: i32, out: *mut *mut IglJoinShuffle,
+    ) -> i32;
+    pub fn igl_join_shuffle_run(
+        js: *mut IglJoinShuffle, right: *const IglDevCol, n_right: i64, left: *const IglDevCol, n_left: i64,
+        out_rows: *mut i64, stream: *mut std::ffi::c_void,
+    ) -> i32;
+    pub fn igl_join_shuffle_output(js: *mut IglJoinShuffle, out: *mut IglDevCol, rows: *mut i64) -> i32;
+    pub fn igl_join_shuffle_destroy(js: *mut IglJoinShuffle);
     pub fn igl_op_schema(op: *mut IglOp, out: *mut FFI_ArrowSchema) -> i32;
     pub fn igl_op_push_build(op: *mut IglOp, batch: *const FFI_ArrowArray) -> i32;
     pub fn igl_op_finish_build(op: *mut IglOp) -> i32;

@@ -4,6 +4,8 @@ import subprocess
 import sys
 
 rep = sys.argv[1]
+json_out = sys.argv[sys.argv.index("--json") + 1] if "--json" in sys.argv else None   # also write {kernel: dram bytes per launch}
+traffic = {}
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(raw.splitlines()))
 hdr, units = rows[0], rows[1]
@@ -21,3 +23,16 @@ for r in rows[2:]:
             print(f"{k:70s} {d[k]} {units[hdr.index(k)]}")
     st = sorted(((float(d[h] or 0), h.replace("smsp__average_warps_issue_stalled_", "").replace("_per_issue_active.ratio", "")) for h in stall), reverse=True)
     print("stalls per issue:", ", ".join(f"{n}={v:.2f}" for v, n in st[:7]))
+
+    def _bytes(key):
+        v, u = float(d[key].replace(",", "")), units[hdr.index(key)].lower()
+        return v * {"byte": 1, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9, "tbyte": 1e12}.get(u, 1)
+    b = _bytes("dram__bytes_read.sum") + _bytes("dram__bytes_write.sum")
+    name = d["Kernel Name"]
+    if name not in traffic or b > traffic[name]["dram_bytes"]:   # the largest launch of a kernel = the full-size one
+        traffic[name] = {"dram_bytes": int(b), "ms": float(d["gpu__time_duration.sum"].replace(",", "")) * ({"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(units[hdr.index("gpu__time_duration.sum")], 1.0))}
+if json_out:
+    import json
+    import os
+    json.dump({"source": os.path.basename(rep) + " (ncu --set full, one launch per kernel at the size the bench times)", "kernels": traffic},
+              open(json_out, "w"), indent=1)
