@@ -300,6 +300,25 @@ __global__ void iota_u32_kernel(uint32_t* out, long long n) {
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = (uint32_t)i;
 }
 
+// Build rows as records: column c of row i at out + i * stride + off[c].
+struct PackRowsParams {
+    const uint8_t* src[kJoinMaxCols];
+    uint8_t off[kJoinMaxCols], shift[kJoinMaxCols];
+    int ncols, stride;
+    long long n;
+    uint8_t* out;
+};
+__global__ void pack_rows_kernel(const __grid_constant__ PackRowsParams P) {
+    const long long strideg = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < P.n; i += strideg) {
+        uint8_t* rec = P.out + (size_t)i * P.stride;
+        for (int c = 0; c < P.ncols; ++c) {
+            if (P.shift[c] == 3) *reinterpret_cast<uint64_t*>(rec + P.off[c]) = ((const uint64_t*)P.src[c])[i];
+            else *reinterpret_cast<uint32_t*>(rec + P.off[c]) = ((const uint32_t*)P.src[c])[i];
+        }
+    }
+}
+
 // ---- probe ---------------------------------------------------------------------------------
 struct JoinProbeParams {
     PipeCols T;                       // every left column, staged
@@ -793,6 +812,11 @@ struct FlatProbeParams {
     // DENSE form: matched rows keep their input position, the warps leave a hit bitmap
     uint32_t* hit_words;                // bit i = probe row i matched; padded to whole 1024-row tiles, zero-filled
     unsigned long long* miss_counter;
+    // Build rows as packed records (unique layout with row-id payload, rows of at most 32 bytes): one
+    // 16- or 32-byte load per match fetches every right column, instead of one random sector per column.
+    const uint8_t* packed;
+    int packed_stride;                  // 0 = none, else 16 or 32
+    uint8_t pk_off[kJoinMaxCols];       // byte offset of each right column inside a record
     // SEG form (multi-GPU join): the probe rows are a list of runs spread over several source
     // buffers — this GPU's staging buffer and the peers', read over NVLink by the same bulk
     // copies.  `nrows` is the total over all runs.
@@ -1100,6 +1124,30 @@ __global__ void __launch_bounds__(kFlatThreads, IGL_FLAT_CTAS) join_probe_flat_k
                 for (int r = 0; r < kFlatRows; ++r) if ((hit >> r) & 1u) st_cs_u32(dst + p[r], v[r]);
             }
         }
+        if (P.packed_stride) {
+            // row-id payload, packed records: all four record loads first, then every column from registers
+            ulonglong4 rec[kFlatRows];
+#pragma unroll
+            for (int r = 0; r < kFlatRows; ++r) {
+                rec[r] = ulonglong4{0, 0, 0, 0};
+                if ((hit >> r) & 1u) {
+                    const uint8_t* a = P.packed + (size_t)(uint32_t)val[r] * (size_t)P.packed_stride;
+                    if (P.packed_stride == 32) rec[r] = ld_nc_u64x4(a);
+                    else { const ulonglong2 h = ld_nc_u64x2(a); rec[r].x = h.x; rec[r].y = h.y; }
+                }
+            }
+            for (int c = 0; c < P.n_right; ++c) {
+                if (!P.out[P.n_left + c]) continue;
+                const int wi = P.pk_off[c] >> 3, sh = (P.pk_off[c] & 4) * 8;
+#pragma unroll
+                for (int r = 0; r < kFlatRows; ++r) {
+                    if (!((hit >> r) & 1u)) continue;
+                    const unsigned long long w = wi == 0 ? rec[r].x : wi == 1 ? rec[r].y : wi == 2 ? rec[r].z : rec[r].w;
+                    if (P.rshift[c] == 3) st_cs_u64((uint64_t*)P.out[P.n_left + c] + obase + p[r], w);
+                    else st_cs_u32((uint32_t*)P.out[P.n_left + c] + obase + p[r], (uint32_t)(w >> sh));
+                }
+            }
+        } else
         for (int c = 0; c < P.n_right; ++c) {
             const int mode = P.payload_col < 0 ? 2 : (c == P.payload_col ? 0 : 1);   // 0 inlined payload, 1 the key itself, 2 gather by row id
             if (!P.out[P.n_left + c]) continue;
@@ -1231,6 +1279,9 @@ struct igl_join {
     bool prepartitioned = false;             // both sides arrive ordered by the top hash bits: skip the radix passes
     std::vector<void*> part_right;           // partitioned build columns (owned)
     std::vector<void*> csr_right;            // duplicate layout: the build columns in CSR order (owned)
+    void* packed = nullptr;                  // unique layout with row-id payload: the build rows as 16/32-byte records (owned)
+    int packed_stride = 0;
+    uint8_t pk_off[kJoinMaxCols] = {};
     std::vector<void*> part_left;            // partitioned probe columns (owned, grow-only)
     int64_t part_left_rows = 0;
     void* part_scratch = nullptr;
@@ -1308,6 +1359,8 @@ int32_t flat_fill_params(igl_join* j, FlatProbeParams& F, igl_dev_col* out, int6
     for (uint32_t c = 0, off = 0; c < (uint32_t)nl; ++c) { F.stage_off[c] = off; off += (uint32_t)kFlatChunk << (j->lt[c] == IGL_T_I32 ? 2 : 3); }
     F.n_left = nl; F.n_right = nr; F.key_col = j->lkey; F.key_type = j->lt[j->lkey];
     F.right_key_col = j->rkey; F.payload_col = j->payload_col; F.table = j->table; F.nrows = nrows;
+    F.packed = (const uint8_t*)j->packed; F.packed_stride = j->packed_stride;
+    memcpy(F.pk_off, j->pk_off, sizeof F.pk_off);
     for (int c = 0; c < nl; ++c) {
         F.lshift[c] = j->lt[c] == IGL_T_I32 ? 2 : 3;
         if (j->lhide[c]) { F.out[c] = nullptr; continue; }
@@ -1618,6 +1671,34 @@ int32_t igl_join_build(igl_join* j, const igl_dev_col* right, int64_t nrows, voi
     IGL_CUDA_OK(cudaMemcpyAsync(j->host_side, j->d_side, sizeof(JoinSide), cudaMemcpyDeviceToHost, st));
     IGL_CUDA_OK(cudaStreamSynchronize(st));
     j->csr = j->host_side->dup_flag != 0;
+    if (j->packed) { pool_free(ctx, j->packed); j->packed = nullptr; }
+    j->packed_stride = 0;
+    if (!j->csr && j->payload_col < 0 && nrows > 0 && !(getenv("IGL_JOIN_PACKED") && getenv("IGL_JOIN_PACKED")[0] == '0')) {
+        // Row-id payload: the probe would gather every right column of a match from its own array — one
+        // random 32-byte sector per column (C4: four per output row).  Rows of up to 32 bytes are packed
+        // into records, 8-byte columns first, so one aligned load brings the whole row.
+        bool ok = true;
+        int bytes = 0;
+        PackRowsParams K{};
+        for (int c = 0; c < nr; ++c) if (right[c].validity) ok = false;
+        for (int pass = 0; pass < 2 && ok; ++pass)
+            for (int c = 0; c < nr; ++c) {
+                const int sh = j->rt[c] == IGL_T_I32 ? 2 : 3;
+                if ((pass == 0) != (sh == 3)) continue;
+                K.off[c] = (uint8_t)bytes; K.shift[c] = (uint8_t)sh; K.src[c] = (const uint8_t*)right[c].data;
+                bytes += 1 << sh;
+            }
+        if (ok && bytes <= 32) {
+            const int stride = bytes <= 16 ? 16 : 32;
+            IGL_TRY(pool_alloc(ctx, (size_t)nrows * stride + 256, &j->packed));
+            K.ncols = nr; K.stride = stride; K.n = nrows; K.out = (uint8_t*)j->packed;
+            pack_rows_kernel<<<grid, 256, 0, st>>>(K);
+            IGL_CUDA_OK(cudaGetLastError());
+            ctx->launches++;
+            j->packed_stride = stride;
+            memcpy(j->pk_off, K.off, sizeof j->pk_off);
+        }
+    }
     if (j->csr) {   // duplicates: rebuild as CSR runs
         j->payload_col = -1;
         IGL_TRY(pool_alloc(ctx, (size_t)nrows * 4, &j->d_rowids));
@@ -1761,7 +1842,9 @@ int32_t join_probe_begin(igl_join* j, const igl_dev_col* left, int64_t nrows, ig
         P.T.data[c] = (const uint8_t*)left[c].data;
         P.T.valid[c] = j->has_nulls ? left[c].validity : nullptr;
     }
-    constexpr unsigned int kGiantCap = 1u << 18, kHugeCap = 4096;   // listed runs per probe call; more are walked in place
+    // listed runs per probe call (more are walked in place): sized with the call — a skewed build side lists
+    // a run for every probe row that hits one of its heavy keys
+    const unsigned int kGiantCap = (unsigned int)std::min<int64_t>(4 << 20, std::max<int64_t>(64 << 10, nrows / 256)), kHugeCap = 4096;
     const size_t scan_part = (256 + (size_t)scan_scratch_words(P.T.ntiles) * 8 + 255) & ~(size_t)255;
     size_t need = scan_part + (j->csr ? ((size_t)kGiantCap + kHugeCap) * 32 : 0);
     if (need > j->scratch_bytes) {
@@ -1892,6 +1975,7 @@ void igl_join_destroy(igl_join* j) {
     pool_free(j->ctx, j->part_scratch);
     for (void* p : j->part_right) pool_free(j->ctx, p);
     for (void* p : j->csr_right) pool_free(j->ctx, p);
+    pool_free(j->ctx, j->packed);
     for (void* p : j->part_left) pool_free(j->ctx, p);
     for (void* p : j->valid_planes) pool_free(j->ctx, p);
     if (j->host_hdr) cudaFreeHost(j->host_hdr);
