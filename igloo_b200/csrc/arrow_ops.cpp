@@ -428,6 +428,18 @@ struct igl_op {
     std::vector<size_t> build_str_cap, build_str_used;
     std::vector<void*> build_off;            // per Utf8 build column: build_rows + 1 offsets
     int64_t build_rows = 0, build_rows_cap = 0;
+    // Utf8 join keys (hash_join.rs:117-122 joins on the printed string): the device join is given a
+    // 64-bit hash of the string as an Int64 key column on each side (NULL where the string is NULL, so
+    // NULL == NULL as in the reference), and every joined pair is then compared byte for byte through
+    // the row ids both sides carry.  Differing pairs (a hash collision) are filtered out of an Inner /
+    // Right join's output on the device; a Left / Full join reports the collision instead.
+    struct Utf8Key { int lcol, rcol; };
+    std::vector<Utf8Key> utf8_keys;
+    std::vector<void*> build_hash;           // per string key: the build side's hash column
+    igl_fp* collide_fp = nullptr;            // output columns + keep flag -> output columns where keep != 0
+    int utf8_hash_bits = 64;                 // IGL_UTF8_KEY_HASH_BITS: fewer bits force collisions (tests)
+    unsigned long long* h_mismatch = nullptr;   // pinned
+    unsigned long long* d_mismatch = nullptr;
 };
 
 namespace {
@@ -747,6 +759,55 @@ int32_t join_gather_utf8(igl_op* op, int c, int64_t n_out, OutCol& oc, std::vect
     return IGL_OK;
 }
 
+// String keys: every joined pair's strings are compared through the row ids the join emitted; pairs
+// that differ (their 64-bit hashes collided) are filtered out of the chunk's output columns.
+int32_t join_verify_utf8_keys(igl_op* op, int64_t* n_out) {
+    igl_ctx* ctx = op->ctx;
+    cudaStream_t st = ctx->stream;
+    auto& PD = op->jpend;
+    const int64_t n = *n_out;
+    const int nc = op->n_left + op->n_right;
+    void* keep = nullptr;
+    IGL_TRY(pool_alloc(ctx, pad64((size_t)n * 4), &keep));
+    PD.to_free.push_back(keep);
+    IGL_TRY(launch_fill_i32(ctx, (int32_t*)keep, n, 1, st));
+    IGL_CUDA_OK(cudaMemsetAsync(op->d_mismatch, 0, sizeof(unsigned long long), st));
+    for (auto& k : op->utf8_keys) {
+        const int oc = op->n_left + k.rcol;
+        IGL_TRY(utf8_verify_keys(ctx, (const int32_t*)PD.dout[k.lcol].data, (const int32_t*)PD.dout[oc].data,
+                                 op->left_join ? PD.dout[oc].validity : nullptr, n,
+                                 PD.dev[k.lcol].offsets, (const uint8_t*)PD.dev[k.lcol].data, PD.dev[k.lcol].validity,
+                                 (const int32_t*)op->build_off[k.rcol], (const uint8_t*)op->build_str[k.rcol], op->build_valid[k.rcol],
+                                 (int32_t*)keep, op->d_mismatch, st));
+    }
+    IGL_CUDA_OK(cudaMemcpyAsync(op->h_mismatch, op->d_mismatch, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    IGL_CUDA_OK(cudaStreamSynchronize(st));
+    if (*op->h_mismatch == 0) return IGL_OK;
+    if (op->left_join)
+        return fail(IGL_ERR_UNSUPPORTED, "Left/Full join on a Utf8 key: %llu joined pairs have equal 64-bit hashes and different strings; "
+                    "whether their left rows have a true match is not tracked on the device", *op->h_mismatch);
+    // the same columns once more, without the differing pairs
+    std::vector<igl_dev_col> mid(nc + 1), fin(nc);
+    for (int c = 0; c < nc; ++c) {
+        mid[c] = PD.dout[c];
+        const bool is_left = c < op->n_left;
+        const bool wrote_valid = is_left ? PD.dev[c].validity != nullptr : op->build_valid[c - op->n_left] != nullptr;
+        if (!wrote_valid || (is_left ? op->l_utf8[c] : op->r_utf8[c - op->n_left])) mid[c].validity = nullptr;
+        fin[c] = igl_dev_col{mid[c].type, 0, nullptr, nullptr, nullptr};
+        void* p = nullptr;
+        IGL_TRY(pool_alloc(ctx, pad64(mid[c].type == IGL_T_BOOL ? (size_t)(n + 7) / 8 + 8 : (size_t)n * type_width(mid[c].type)), &p));
+        PD.to_free.push_back(p); fin[c].data = p;
+        IGL_TRY(pool_alloc(ctx, pad64((size_t)(n + 7) / 8 + 8), &p));
+        PD.to_free.push_back(p); fin[c].validity = (uint8_t*)p;
+    }
+    mid[nc] = igl_dev_col{IGL_T_I32, 0, keep, nullptr, nullptr};
+    int64_t kept = 0;
+    IGL_TRY(igl_fp_run(op->collide_fp, mid.data(), n, fin.data(), &kept, (void*)st));
+    for (int c = 0; c < nc; ++c) PD.dout[c] = fin[c];
+    *n_out = kept;
+    return IGL_OK;
+}
+
 // Finishes the probe chunk queued before: waits for its kernels, queues the download of its output
 // on the download stream and appends the batch to `ready` (igl_op_pull waits for the download).
 int32_t join_probe_end_chunk(igl_op* op) {
@@ -761,6 +822,11 @@ int32_t join_probe_end_chunk(igl_op* op) {
     if (rc < 0) { cudaStreamSynchronize(st); cleanup(); return rc; }
     if (n_out == 0) { cleanup(); return IGL_OK; }
     const int nc = op->n_left + op->n_right;
+    if (!op->utf8_keys.empty()) {
+        rc = join_verify_utf8_keys(op, &n_out);
+        if (rc < 0) { cudaStreamSynchronize(st); cleanup(); return rc; }
+        if (n_out == 0) { cleanup(); return IGL_OK; }
+    }
     OutBatch ob;
     ob.nrows = n_out;
     ob.cols.resize(nc);
@@ -811,18 +877,27 @@ int32_t join_probe_begin_chunk(igl_op* op, int64_t n, std::vector<igl_dev_col>&&
     }
     HostTrace tr_alloc("op.begin.alloc+probe");
     int64_t cap = n;
+    auto cleanup = [&]() { for (void* p : PD.to_free) pool_free(ctx, p); PD.to_free.clear(); };
+    const int nu = (int)op->utf8_keys.size();
+    std::vector<igl_dev_col> jdev = PD.dev;   // what the device join reads: row ids where the strings are,
+    for (int c = 0; c < op->n_left; ++c)      // and behind them one hash column per string key
+        if (op->l_utf8[c]) jdev[c] = igl_dev_col{IGL_T_I32, 0, op->d_iota, nullptr, nullptr};
+    for (int i = 0; i < nu; ++i) {
+        const int lc = op->utf8_keys[i].lcol;
+        void* p = nullptr;
+        int32_t rc = pool_alloc(ctx, pad64((size_t)std::max<int64_t>(n, 1) * 8), &p);
+        if (rc < 0) { cleanup(); return rc; }
+        PD.to_free.push_back(p);
+        rc = utf8_hash_keys(ctx, PD.dev[lc].offsets, (const uint8_t*)PD.dev[lc].data, n, op->utf8_hash_bits, (int64_t*)p, st);
+        if (rc < 0) { cleanup(); return rc; }
+        jdev.push_back(igl_dev_col{IGL_T_I64, 0, p, PD.dev[lc].validity, nullptr});
+    }
     if (igl_join_has_duplicates(op->join)) {
-        std::vector<igl_dev_col> cdev = PD.dev;
-        for (int c = 0; c < op->n_left; ++c)
-            if (op->l_utf8[c]) cdev[c] = igl_dev_col{IGL_T_I32, 0, op->d_iota, nullptr, nullptr};
-        IGL_TRY(igl_join_probe_count(op->join, cdev.data(), n, &cap, st));
+        int32_t rc = igl_join_probe_count(op->join, jdev.data(), n, &cap, st);
+        if (rc < 0) { cleanup(); return rc; }
     }
     const int nc = op->n_left + op->n_right;
     PD.dout.assign(nc, igl_dev_col{});
-    auto cleanup = [&]() { for (void* p : PD.to_free) pool_free(ctx, p); PD.to_free.clear(); };
-    std::vector<igl_dev_col> jdev = PD.dev;   // what the device join reads: row ids where the strings are
-    for (int c = 0; c < op->n_left; ++c)
-        if (op->l_utf8[c]) jdev[c] = igl_dev_col{IGL_T_I32, 0, op->d_iota, nullptr, nullptr};
     for (int c = 0; c < nc; ++c) {
         PD.dout[c].type = op->out_fields[c].type == IGL_T_UTF8 ? IGL_T_I32 : op->out_fields[c].type;
         void* p = nullptr;
@@ -834,10 +909,26 @@ int32_t join_probe_begin_chunk(igl_op* op, int64_t n, std::vector<igl_dev_col>&&
         if (rc < 0) { cleanup(); return rc; }
         PD.to_free.push_back(p); PD.dout[c].validity = (uint8_t*)p;
     }
+    // the device join's own column order: left columns, left hash columns, right columns, right hash columns
+    std::vector<igl_dev_col> jout(PD.dout.begin(), PD.dout.begin() + op->n_left);
+    for (int side = 0; side < 2; ++side) {
+        for (int i = 0; i < nu; ++i) {
+            void* p = nullptr;
+            int32_t rc2 = pool_alloc(ctx, pad64((size_t)std::max<int64_t>(cap, 1) * 8), &p);
+            if (rc2 < 0) { cleanup(); return rc2; }
+            PD.to_free.push_back(p);
+            void* v = nullptr;
+            rc2 = pool_alloc(ctx, pad64((size_t)(cap + 7) / 8 + 8), &v);
+            if (rc2 < 0) { cleanup(); return rc2; }
+            PD.to_free.push_back(v);
+            jout.push_back(igl_dev_col{IGL_T_I64, 0, p, (uint8_t*)v, nullptr});
+        }
+        if (side == 0) jout.insert(jout.end(), PD.dout.begin() + op->n_left, PD.dout.end());
+    }
     int32_t rc;
     {
         HostTrace tr("op.begin.probe");
-        rc = join_probe_begin(op->join, jdev.data(), n, PD.dout.data(), cap, st);
+        rc = join_probe_begin(op->join, jdev.data(), n, jout.data(), cap, st);
     }
     if (rc < 0) { cudaStreamSynchronize(st); cleanup(); return rc; }
     PD.n = n; PD.cap = cap;
@@ -1055,21 +1146,70 @@ int32_t igl_op_hash_join_create_ex(igl_ctx* ctx, int32_t join_type, const struct
     for (int c = 0; c < op->n_left; ++c) if (lt[c] == IGL_T_UTF8) { op->l_utf8[c] = 1; op->any_utf8 = true; lt[c] = IGL_T_I32; ln[c] = 0; }
     for (int c = 0; c < op->n_right; ++c) if (rt[c] == IGL_T_UTF8) { op->r_utf8[c] = 1; op->any_utf8 = true; rt[c] = IGL_T_I32; rn[c] = 0; }
     int32_t rc = IGL_OK;
+    // string keys first, against the real schema: a bare Utf8 column on both sides of a pair
+    std::vector<int> key_utf8(nkeys, -1);
+    {
+        std::vector<int32_t> lt0, rt0; std::vector<uint8_t> ln0, rn0;
+        for (auto& f : lf) { lt0.push_back(f.type); ln0.push_back(f.nullable); }
+        for (auto& f : rf) { rt0.push_back(f.type); rn0.push_back(f.nullable); }
+        for (int k = 0; k < nkeys && rc >= 0; ++k) {
+            igl_expr *le = nullptr, *re = nullptr;
+            rc = igl_expr_compile(ctx, left_keys[k], left_key_lens[k], lt0.data(), ln0.data(), op->n_left, &le);
+            if (rc >= 0) rc = igl_expr_compile(ctx, right_keys[k], right_key_lens[k], rt0.data(), rn0.data(), op->n_right, &re);
+            if (rc >= 0 && (le->type == IGL_T_UTF8) != (re->type == IGL_T_UTF8))
+                rc = fail(IGL_ERR_UNSUPPORTED, "join key %d pairs a Utf8 key with a key of another type (such a pair never matches: hash_join.rs:120 prints the type); not supported on the GPU", k);
+            if (rc >= 0 && le->type == IGL_T_UTF8) {
+                if (!le->is_plain_col() || !re->is_plain_col()) rc = fail(IGL_ERR_UNSUPPORTED, "Utf8 join key %d must be a bare column", k);
+                else { key_utf8[k] = (int)op->utf8_keys.size(); op->utf8_keys.push_back({le->nodes[0].col, re->nodes[0].col}); }
+            }
+            igl_expr_destroy(le); igl_expr_destroy(re);
+        }
+        if (rc < 0) { destroy_partial(); return rc; }
+    }
+    const int nu = (int)op->utf8_keys.size();
+    for (int i = 0; i < nu; ++i) {   // the hash columns follow each side's own columns
+        lt.push_back(IGL_T_I64); ln.push_back(lf[op->utf8_keys[i].lcol].nullable);
+        rt.push_back(IGL_T_I64); rn.push_back(rf[op->utf8_keys[i].rcol].nullable);
+    }
+    if (const char* e = getenv("IGL_UTF8_KEY_HASH_BITS")) op->utf8_hash_bits = std::min(64, std::max(1, atoi(e)));
     for (int k = 0; k < nkeys && rc >= 0; ++k) {   // one pair per `join.on` entry (physical_planner.rs:106-120)
         igl_expr *le = nullptr, *re = nullptr;
-        rc = igl_expr_compile(ctx, left_keys[k], left_key_lens[k], lt.data(), ln.data(), op->n_left, &le);
-        if (rc >= 0) rc = igl_expr_compile(ctx, right_keys[k], right_key_lens[k], rt.data(), rn.data(), op->n_right, &re);
+        if (key_utf8[k] >= 0) {
+            const int lc = op->n_left + key_utf8[k], rc2 = op->n_right + key_utf8[k];
+            const uint8_t lb[3] = {IGL_OP_COL, (uint8_t)(lc & 0xFF), (uint8_t)(lc >> 8)}, rb[3] = {IGL_OP_COL, (uint8_t)(rc2 & 0xFF), (uint8_t)(rc2 >> 8)};
+            rc = igl_expr_compile(ctx, lb, 3, lt.data(), ln.data(), op->n_left + nu, &le);
+            if (rc >= 0) rc = igl_expr_compile(ctx, rb, 3, rt.data(), rn.data(), op->n_right + nu, &re);
+        } else {
+            rc = igl_expr_compile(ctx, left_keys[k], left_key_lens[k], lt.data(), ln.data(), op->n_left + nu, &le);
+            if (rc >= 0) rc = igl_expr_compile(ctx, right_keys[k], right_key_lens[k], rt.data(), rn.data(), op->n_right + nu, &re);
+        }
         if (le) op->lkeys.push_back(le);
         if (re) op->rkeys.push_back(re);
-        if (rc >= 0) {   // a key must not read a string column (it would see the row ids)
-            for (auto& nd : le->nodes) if (nd.op == IGL_OP_COL && op->l_utf8[nd.col]) rc = fail(IGL_ERR_UNSUPPORTED, "Utf8 join keys are not supported on the GPU (left key %d)", k);
-            for (auto& nd : re->nodes) if (nd.op == IGL_OP_COL && op->r_utf8[nd.col]) rc = fail(IGL_ERR_UNSUPPORTED, "Utf8 join keys are not supported on the GPU (right key %d)", k);
-        }
     }
     if (rc >= 0) {
         op->lkey = op->lkeys[0]; op->rkey = op->rkeys[0];
-        rc = igl_join_create_ex(ctx, join_type, lt.data(), ln.data(), op->n_left, rt.data(), rn.data(), op->n_right,
+        rc = igl_join_create_ex(ctx, join_type, lt.data(), ln.data(), op->n_left + nu, rt.data(), rn.data(), op->n_right + nu,
                                 op->lkeys.data(), op->rkeys.data(), nkeys, &op->join);
+    }
+    if (rc >= 0 && nu > 0) {
+        // what removes a colliding pair from the output: the output columns as the device join writes them
+        // (row ids where the strings are) plus one Int32 keep flag; keeps rows with flag != 0
+        std::vector<int32_t> ot(lt.begin(), lt.begin() + op->n_left);
+        ot.insert(ot.end(), rt.begin(), rt.begin() + op->n_right);
+        std::vector<uint8_t> on(ln.begin(), ln.begin() + op->n_left);
+        on.insert(on.end(), rn.begin(), rn.begin() + op->n_right);
+        const int kc = (int)ot.size();
+        ot.push_back(IGL_T_I32); on.push_back(0);
+        std::vector<uint8_t> skip(ot.size(), 0);
+        skip[kc] = 1;
+        const uint8_t bc[9] = {IGL_OP_COL, (uint8_t)(kc & 0xFF), (uint8_t)(kc >> 8), IGL_OP_LIT_I32, 0, 0, 0, 0, IGL_OP_NE};
+        igl_expr* pred = nullptr;
+        rc = igl_expr_compile(ctx, bc, sizeof bc, ot.data(), on.data(), (int32_t)ot.size(), &pred);
+        if (rc >= 0) rc = fp_create_ex(ctx, ot.data(), on.data(), (int32_t)ot.size(), pred, nullptr, 0, skip.data(), false, &op->collide_fp);
+        igl_expr_destroy(pred);
+        if (rc >= 0 && cudaHostAlloc((void**)&op->h_mismatch, sizeof(unsigned long long), cudaHostAllocDefault) != cudaSuccess) rc = fail(IGL_ERR_OOM, "pinned allocation failed");
+        if (rc >= 0) { void* p = nullptr; rc = pool_alloc(ctx, 256, &p); op->d_mismatch = (unsigned long long*)p; }
+        op->build_hash.assign(nu, nullptr);
     }
     if (rc < 0) { destroy_partial(); return rc; }
     // output schema: hash_join.rs:35-76 (left fields, right fields, clashes renamed right_<name>)
@@ -1084,7 +1224,7 @@ int32_t igl_op_hash_join_create_ex(igl_ctx* ctx, int32_t join_type, const struct
         if (op->left_join) o.nullable = true;
         op->out_fields.push_back(o);
     }
-    if (!op->left_join && nkeys == 1 && op->lkey->is_plain_col() && op->rkey->is_plain_col()) {
+    if (!op->left_join && nkeys == 1 && nu == 0 && op->lkey->is_plain_col() && op->rkey->is_plain_col()) {
         const int lc = op->lkey->nodes[0].col, rc2 = op->rkey->nodes[0].col;
         if (lt[lc] == rt[rc2] && (lt[lc] == IGL_T_I32 || lt[lc] == IGL_T_I64)) { op->alias_left_key = lc; op->alias_right_key = rc2; }
     }
@@ -1160,6 +1300,13 @@ int32_t igl_op_finish_build(igl_op* op) {
         if (!op->build_dev[c]) { void* p = nullptr; IGL_TRY(pool_alloc(op->ctx, 256, &p)); op->build_dev[c] = p; }
         cols[c].data = op->build_dev[c];
         cols[c].validity = op->build_valid[c];
+    }
+    for (size_t i = 0; i < op->utf8_keys.size(); ++i) {   // string keys: the build side's hash columns, kept with the table
+        const int c = op->utf8_keys[i].rcol;
+        if (!op->build_hash[i]) IGL_TRY(pool_alloc(op->ctx, pad64((size_t)std::max<int64_t>(op->build_rows, 1) * 8), &op->build_hash[i]));
+        IGL_TRY(utf8_hash_keys(op->ctx, (const int32_t*)op->build_off[c], (const uint8_t*)op->build_str[c], op->build_rows, op->utf8_hash_bits,
+                               (int64_t*)op->build_hash[i], op->ctx->stream));
+        cols.push_back(igl_dev_col{IGL_T_I64, 0, op->build_hash[i], op->build_valid[c], nullptr});
     }
     IGL_TRY(igl_join_build(op->join, cols.data(), op->build_rows, op->ctx->stream));
     op->build_done = true;
@@ -1256,6 +1403,10 @@ void igl_op_destroy(igl_op* op) {
     for (void* p : op->build_dev) pool_free(op->ctx, p);
     for (void* p : op->build_str) pool_free(op->ctx, p);
     for (void* p : op->build_off) pool_free(op->ctx, p);
+    for (void* p : op->build_hash) pool_free(op->ctx, p);
+    if (op->collide_fp) igl_fp_destroy(op->collide_fp);
+    if (op->h_mismatch) cudaFreeHost(op->h_mismatch);
+    pool_free(op->ctx, op->d_mismatch);
     pool_free(op->ctx, op->d_iota);
     for (uint8_t* p : op->build_valid) pool_free(op->ctx, p);
     delete op;

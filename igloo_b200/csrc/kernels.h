@@ -39,6 +39,13 @@ int32_t utf8_gather_bytes(igl_ctx* ctx, const int32_t* src_off, const uint8_t* s
 
 int32_t launch_iota_i32(igl_ctx* ctx, int32_t* out, long long n, cudaStream_t st);
 int32_t launch_mask_rowids(igl_ctx* ctx, int32_t* rowid, const uint8_t* valid_bits, long long n, cudaStream_t st);
+// Utf8 join keys: hash of each row's bytes as an Int64 key column; byte-for-byte check of the joined pairs
+int32_t utf8_hash_keys(igl_ctx* ctx, const int32_t* off, const uint8_t* bytes, long long n, int bits, int64_t* out, cudaStream_t st);
+int32_t utf8_verify_keys(igl_ctx* ctx, const int32_t* lrow, const int32_t* rrow, const uint8_t* r_out_valid, long long n,
+                         const int32_t* loff, const uint8_t* lbytes, const uint8_t* lvalid,
+                         const int32_t* roff, const uint8_t* rbytes, const uint8_t* rvalid,
+                         int32_t* keep, unsigned long long* mismatches, cudaStream_t st);
+int32_t launch_fill_i32(igl_ctx* ctx, int32_t* out, long long n, int32_t v, cudaStream_t st);
 
 // Radix partition of a column set by the top bits of the join hash (partition.cu).
 // dst[c]: device buffers of nrows rows; scratch: 3 * ((1 << log2_parts) + 1) * 8 bytes.

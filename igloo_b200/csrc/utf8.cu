@@ -126,6 +126,83 @@ int32_t launch_mask_rowids(igl_ctx* ctx, int32_t* rowid, const uint8_t* valid_bi
     return IGL_OK;
 }
 
+// ---- Utf8 join keys (hash_join.rs:117-122: the key is the printed string; here: a 64-bit hash of
+// the bytes joined on as an Int64 key, every joined pair then checked byte for byte) ----
+
+// out[i] = hash of row i's bytes (FNV-1a over the bytes, length folded in, finished with splitmix64).
+// `bits` < 64 keeps only that many low bits: a test switch that makes different strings collide.
+__global__ void utf8_hash_kernel(const int32_t* __restrict__ off, const uint8_t* __restrict__ bytes, long long n, int bits,
+                                 int64_t* __restrict__ out) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const uint64_t mask = bits >= 64 ? ~0ull : ((1ull << bits) - 1);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const int32_t s = off[i], e = off[i + 1];
+        uint64_t h = 0xCBF29CE484222325ull ^ ((uint64_t)(uint32_t)(e - s) * 0x9E3779B97F4A7C15ull);
+        for (int32_t b = s; b < e; ++b) h = (h ^ bytes[b]) * 0x100000001B3ull;
+        out[i] = (int64_t)(splitmix64(h) & mask);
+    }
+}
+
+// keep[i] &= (left string of joined row i == right string of joined row i), NULL == NULL
+// (hash_join.rs:120 prints NULL as "null" on both sides); null-extended rows of a Left join
+// (bit i of r_out_valid clear) are kept.  *mismatches counts the rows cleared.
+__global__ void utf8_verify_kernel(const int32_t* __restrict__ lrow, const int32_t* __restrict__ rrow,
+                                   const uint8_t* __restrict__ r_out_valid, long long n,
+                                   const int32_t* __restrict__ loff, const uint8_t* __restrict__ lbytes, const uint8_t* __restrict__ lvalid,
+                                   const int32_t* __restrict__ roff, const uint8_t* __restrict__ rbytes, const uint8_t* __restrict__ rvalid,
+                                   int32_t* __restrict__ keep, unsigned long long* __restrict__ mismatches) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    unsigned long long bad = 0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        if (r_out_valid && !((r_out_valid[i >> 3] >> (i & 7)) & 1)) continue;
+        const int32_t l = lrow[i], r = rrow[i];
+        const bool lnull = lvalid && !((lvalid[l >> 3] >> (l & 7)) & 1);
+        const bool rnull = rvalid && !((rvalid[r >> 3] >> (r & 7)) & 1);
+        bool same;
+        if (lnull || rnull) same = lnull && rnull;
+        else {
+            const int32_t ls = loff[l], len = loff[l + 1] - ls, rs = roff[r];
+            same = len == roff[r + 1] - rs;
+            for (int32_t b = 0; same && b < len; ++b) same = lbytes[ls + b] == rbytes[rs + b];
+        }
+        if (!same && keep[i]) { keep[i] = 0; ++bad; }
+    }
+    if (bad) atomicAdd(mismatches, bad);
+}
+
+__global__ void fill_i32_kernel(int32_t* out, long long n, int32_t v) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = v;
+}
+
+int32_t utf8_hash_keys(igl_ctx* ctx, const int32_t* off, const uint8_t* bytes, long long n, int bits, int64_t* out, cudaStream_t st) {
+    if (n <= 0) return IGL_OK;
+    utf8_hash_kernel<<<(int)std::min<long long>((n + 255) / 256, (long long)ctx->sm_count * 8), 256, 0, st>>>(off, bytes, n, bits, out);
+    IGL_CUDA_OK(cudaGetLastError());
+    ctx->launches++;
+    return IGL_OK;
+}
+
+int32_t launch_fill_i32(igl_ctx* ctx, int32_t* out, long long n, int32_t v, cudaStream_t st) {
+    if (n <= 0) return IGL_OK;
+    fill_i32_kernel<<<(int)std::min<long long>((n + 255) / 256, (long long)ctx->sm_count * 8), 256, 0, st>>>(out, n, v);
+    IGL_CUDA_OK(cudaGetLastError());
+    ctx->launches++;
+    return IGL_OK;
+}
+
+int32_t utf8_verify_keys(igl_ctx* ctx, const int32_t* lrow, const int32_t* rrow, const uint8_t* r_out_valid, long long n,
+                         const int32_t* loff, const uint8_t* lbytes, const uint8_t* lvalid,
+                         const int32_t* roff, const uint8_t* rbytes, const uint8_t* rvalid,
+                         int32_t* keep, unsigned long long* mismatches, cudaStream_t st) {
+    if (n <= 0) return IGL_OK;
+    utf8_verify_kernel<<<(int)std::min<long long>((n + 255) / 256, (long long)ctx->sm_count * 8), 256, 0, st>>>(
+        lrow, rrow, r_out_valid, n, loff, lbytes, lvalid, roff, rbytes, rvalid, keep, mismatches);
+    IGL_CUDA_OK(cudaGetLastError());
+    ctx->launches++;
+    return IGL_OK;
+}
+
 // Gathers a Utf8 column by row ids.  out_off must hold n+1 entries, scratch
 // 8 * ceil(n / 2048) + 256 bytes (zeroed here).  Returns after enqueueing; the
 // total byte count is out_off[n] on the device.

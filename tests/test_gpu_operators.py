@@ -253,8 +253,71 @@ def test_hash_join_exec_carries_utf8_columns_on_both_sides(ctx, jt):
         assert got.schema.names == want.schema.names and got.num_rows == want.num_rows > 0
         assert_same_multiset(got.cast(pa.schema([pa.field(f.name, f.type, True) for f in got.schema])),
                              want.cast(pa.schema([pa.field(f.name, f.type, True) for f in want.schema])))
-    # a string key is refused (the planner keeps the CPU join)
+
+
+def _string_key_tables(seed, nl, nr, nkeys_distinct):
+    rng = np.random.default_rng(seed)
+    def names(n):
+        out = []
+        for _ in range(n):
+            u = rng.random()
+            k = int(rng.integers(0, nkeys_distinct))
+            out.append(None if u < 0.05 else "null" if u < 0.07 else "" if u < 0.09 else f"user-{k}" + "x" * (k % 7))
+        return out
+    left = pa.table({"name": pa.array(names(nl), pa.string()), "v": pa.array(rng.integers(0, 1000, nl), pa.int32()),
+                     "grp": pa.array(rng.integers(0, 3, nl), pa.int64())})
+    right = pa.table({"tag": pa.array(rng.integers(0, 3, nr), pa.int64()), "name": pa.array(names(nr), pa.string()), "w": rng.random(nr)})
+    return left, right
+
+
+def _check_join(ctx, left, right, lkeys, rkeys, jt):
+    from igloo_b200.operators import HashJoinExec, MemoryScanExec
+    from tests.util import tight_fields
+    j = HashJoinExec(MemoryScanExec(left, 1500), MemoryScanExec(right, 700), [col(k) for k in lkeys], [col(k) for k in rkeys], jt, ctx)
+    got, _ = collect(j)
+    L = orc.Table.scan(arrow_to_columns(left)); R = orc.Table.scan(arrow_to_columns(right))
+    lf, rf = tight_fields(left), tight_fields(right)
+    want = columns_to_arrow(L.hash_join(R, [lower(col(k), lf)[0] for k in lkeys], [lower(col(k), rf)[0] for k in rkeys], jt, 0, 1).columns())
+    assert got.schema.names == want.schema.names and got.num_rows == want.num_rows > 0
+    assert_same_multiset(got.cast(pa.schema([pa.field(f.name, f.type, True) for f in got.schema])),
+                         want.cast(pa.schema([pa.field(f.name, f.type, True) for f in want.schema])))
+    return got.num_rows
+
+
+@pytest.mark.parametrize("jt", [0, 1])
+def test_hash_join_exec_on_a_string_key(ctx, jt):
+    """hash_join.rs:117-122 joins on the printed key, so a Utf8 key is a key like any other: NULL == NULL,
+    the string "null" is not NULL, the empty string is a value.  On the GPU: a 64-bit hash of the bytes as
+    the device key, every joined pair compared byte for byte afterwards.  Unique and duplicated build keys."""
+    left, right = _string_key_tables(5, 9_000, 2_500, 4_000)      # duplicates on both sides (NULL, "null", "" and repeats)
+    _check_join(ctx, left, right, ["name"], ["name"], jt)
+    uniq = pa.table({"name": pa.array([f"user-{k}" + "x" * (k % 7) for k in range(3_000)], pa.string()), "w": np.arange(3_000) * 0.5},
+                    schema=pa.schema([pa.field("name", pa.string(), False), pa.field("w", pa.float64(), False)]))
+    _check_join(ctx, left, uniq, ["name"], ["name"], jt)            # unique build keys, no NULLs on the build side
+
+
+def test_hash_join_exec_on_a_string_key_and_an_integer_key(ctx):
+    left, right = _string_key_tables(6, 8_000, 3_000, 500)
+    _check_join(ctx, left, right, ["name", "grp"], ["name", "tag"], 0)
+
+
+def test_string_key_hash_collisions_are_filtered_out(ctx, monkeypatch):
+    """With the hash cut to 6 bits nearly every bucket mixes different strings: the byte-for-byte check
+    must remove exactly the false pairs from an Inner join, and a Left join must refuse rather than guess."""
     from igloo_b200._lib import IglooCudaError
+    from igloo_b200.operators import HashJoinExec, MemoryScanExec
+    monkeypatch.setenv("IGL_UTF8_KEY_HASH_BITS", "6")
+    left, right = _string_key_tables(7, 5_000, 1_200, 900)
+    _check_join(ctx, left, right, ["name"], ["name"], 0)
     with pytest.raises(IglooCudaError) as e:
-        collect(HashJoinExec(MemoryScanExec(users), MemoryScanExec(users), [col("name")], [col("name")], 0, ctx))
+        collect(HashJoinExec(MemoryScanExec(left), MemoryScanExec(right), [col("name")], [col("name")], 1, ctx))
+    assert e.value.code == -2 and "different strings" in str(e.value)
+
+
+def test_string_key_paired_with_an_integer_key_is_refused(ctx):
+    from igloo_b200._lib import IglooCudaError
+    from igloo_b200.operators import HashJoinExec, MemoryScanExec
+    left, right = _string_key_tables(8, 100, 100, 10)
+    with pytest.raises(IglooCudaError) as e:
+        collect(HashJoinExec(MemoryScanExec(left), MemoryScanExec(right), [col("name")], [col("tag")], 0, ctx))
     assert e.value.code == -2
