@@ -62,7 +62,7 @@ int32_t radix_histogram_async(igl_ctx* ctx, const igl_dev_col* key, long long nr
                               const HotKeys& hot, unsigned long long* dev_hist, cudaStream_t st);
 int32_t radix_scatter_bins_async(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int key_col, long long nrows, int ndest, int nhash,
                                  int log2_parts, const HotKeys& hot, void* const* dst, const unsigned long long* dev_offsets,
-                                 unsigned long long* dev_cursor, cudaStream_t st);
+                                 unsigned long long* dev_cursor, cudaStream_t st, bool yielding = false);
 // canonical form of every (nrows / nsamples)-th key
 int32_t sample_keys_async(igl_ctx* ctx, const igl_dev_col* key, long long nrows, int nsamples, unsigned long long* dev_out, cudaStream_t st);
 

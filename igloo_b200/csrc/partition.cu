@@ -514,7 +514,10 @@ bool radix_partition_supported(const igl_dev_col* cols, int ncols) {
 }
 
 // Launches the scatter pass for `P` (offsets and cursor already set): bulk-copy form when it applies.
-static cudaError_t launch_radix_scatter(igl_ctx* ctx, const RadixParams& P, uint32_t tile_bytes_4096, cudaStream_t st, bool long_runs = false) {
+// `yielding`: one CTA per tile instead of a persistent grid, so that kernels of a higher-priority stream
+// get onto the SMs between tiles (the two-CTA form only: it holds no state across tiles anyway).
+static cudaError_t launch_radix_scatter(igl_ctx* ctx, const RadixParams& P, uint32_t tile_bytes_4096, cudaStream_t st, bool long_runs = false,
+                                        bool yielding = false) {
     bool aligned = true;
     for (int c = 0; c < P.ncols; ++c) if ((uintptr_t)P.src[c] & 15) aligned = false;
     const char* env = getenv("IGL_RADIX_BULK");
@@ -538,8 +541,10 @@ static cudaError_t launch_radix_scatter(igl_ctx* ctx, const RadixParams& P, uint
             const void* k = hot ? (const void*)radix_scatter_bulk_kernel<8, true, 512> : (const void*)radix_scatter_bulk_kernel<8, false, 512>;
             cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
             if (e != cudaSuccess) return e;
-            if (hot) radix_scatter_bulk_kernel<8, true, 512><<<ctx->sm_count * 2, 512, dyn, st>>>(P, 1, tile_bytes_4096);
-            else radix_scatter_bulk_kernel<8, false, 512><<<ctx->sm_count * 2, 512, dyn, st>>>(P, 1, tile_bytes_4096);
+            const long long ntiles = (P.n + kRtTile - 1) / kRtTile;
+            const int grid = yielding ? (int)std::min<long long>(ntiles, 1ll << 30) : ctx->sm_count * 2;
+            if (hot) radix_scatter_bulk_kernel<8, true, 512><<<grid, 512, dyn, st>>>(P, 1, tile_bytes_4096);
+            else radix_scatter_bulk_kernel<8, false, 512><<<grid, 512, dyn, st>>>(P, 1, tile_bytes_4096);
             return cudaGetLastError();
         }
         const int n_buf = 2u * tile_bytes_4096 <= kRtMaxDyn ? 2 : 1;
@@ -633,7 +638,7 @@ int32_t sample_keys_async(igl_ctx* ctx, const igl_dev_col* key, long long nrows,
 // dev_offsets[bin] + arrival order; dev_cursor[bins] must be zero.  Bins are destination-major.
 int32_t radix_scatter_bins_async(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int key_col, long long nrows, int ndest, int nhash,
                                  int log2_parts, const HotKeys& hot, void* const* dst, const unsigned long long* dev_offsets,
-                                 unsigned long long* dev_cursor, cudaStream_t st) {
+                                 unsigned long long* dev_cursor, cudaStream_t st, bool yielding) {
     if (ndest < 1 || ndest > kPartMaxParts || nhash < 1 || nhash > ndest || log2_parts < 0 || (ndest << log2_parts) > kRadixMaxParts)
         return fail(IGL_ERR_UNSUPPORTED, "ndest in [1, %d] and ndest << log2_parts <= %d", kPartMaxParts, kRadixMaxParts);
     if (ncols < 1 || ncols > kPartMaxCols || key_col < 0 || key_col >= ncols) return fail(IGL_ERR_INVALID_ARG, "radix_scatter_bins: bad column set");
@@ -650,7 +655,7 @@ int32_t radix_scatter_bins_async(igl_ctx* ctx, const igl_dev_col* cols, int ncol
         off += (uint32_t)kRadixTile << P.shift[c];
         for (int d = 0; d < ndest; ++d) P.dst[d][c] = (uint8_t*)dst[c];
     }
-    IGL_CUDA_OK(launch_radix_scatter(ctx, P, off, st));
+    IGL_CUDA_OK(launch_radix_scatter(ctx, P, off, st, false, yielding));
     ctx->launches++;
     return IGL_OK;
 }

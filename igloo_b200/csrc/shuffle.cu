@@ -229,6 +229,67 @@ __global__ void __launch_bounds__(kCopyThreads) seg_copy_kernel(const __grid_con
     }
 }
 
+// ---- a few CTAs acting as copy engines ------------------------------------------------------------
+// Moves contiguous byte ranges (peer staging -> local receive slab) with bulk async copies only: one
+// thread per CTA keeps kDmaAhead 16 KB loads in flight into a shared-memory ring and writes each
+// piece out with a bulk store as it lands.  No registers, no issue slots to speak of: the kernel
+// takes the shared memory of the few SMs it sits on and leaves the rest of the GPU to whatever
+// else is running (the table build).  TMA multicast loads here read only this GPU's memory, since
+// on B200 a TMA multicast load from another GPU's memory hung the GPU — these are plain bulk copies.
+constexpr uint32_t kDmaPiece = 16u << 10;
+constexpr int kDmaSlots = 12, kDmaAhead = 8;
+constexpr int kDmaMaxRuns = 64;
+struct DmaParams {
+    const uint8_t* src[kDmaMaxRuns];
+    uint8_t* dst[kDmaMaxRuns];
+    uint64_t bytes[kDmaMaxRuns];
+    uint32_t piece0[kDmaMaxRuns + 1];
+    int nruns;
+};
+
+__device__ __forceinline__ void bulk_s2g(void* gmem_dst, const void* smem_src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem_dst), "r"(smem_u32(smem_src)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+
+__global__ void __launch_bounds__(32) dma_copy_kernel(const __grid_constant__ DmaParams P) {
+    extern __shared__ __align__(128) uint8_t ring[];
+    __shared__ uint64_t s_full[kDmaSlots];
+    if (threadIdx.x != 0) return;
+    for (int k = 0; k < kDmaSlots; ++k) mbar_init(&s_full[k], 1);
+    mbar_fence_init();
+    const uint32_t npieces = P.piece0[P.nruns];
+    const uint32_t mine = blockIdx.x < npieces ? (npieces - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;   // pieces blockIdx.x, + gridDim.x, ...
+    int run = 0;
+    auto load = [&](uint32_t t) {   // t-th piece of this CTA -> slot t % kDmaSlots (pieces are visited in rising order: `run` only moves forward)
+        const uint32_t piece = blockIdx.x + t * gridDim.x;
+        while (P.piece0[run + 1] <= piece) ++run;
+        const uint64_t off = (uint64_t)(piece - P.piece0[run]) * kDmaPiece;
+        const uint32_t n = (uint32_t)min((uint64_t)kDmaPiece, P.bytes[run] - off);
+        uint64_t* bar = &s_full[t % kDmaSlots];
+        mbar_arrive_expect_tx(bar, n);
+        bulk_g2s(ring + (size_t)(t % kDmaSlots) * kDmaPiece, P.src[run] + off, n, bar);
+    };
+    for (uint32_t t = 0; t < mine && t < (uint32_t)kDmaAhead; ++t) load(t);
+    int srun = 0;
+    for (uint32_t t = 0; t < mine; ++t) {
+        const uint32_t piece = blockIdx.x + t * gridDim.x;
+        while (P.piece0[srun + 1] <= piece) ++srun;
+        const uint64_t off = (uint64_t)(piece - P.piece0[srun]) * kDmaPiece;
+        const uint32_t n = (uint32_t)min((uint64_t)kDmaPiece, P.bytes[srun] - off);
+        mbar_wait(&s_full[t % kDmaSlots], (t / kDmaSlots) & 1u);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        bulk_s2g(P.dst[srun] + off, ring + (size_t)(t % kDmaSlots) * kDmaPiece, n);
+        if (t + kDmaAhead < mine) {
+            // the slot of piece t + kDmaAhead was last read by the store of piece t + kDmaAhead - kDmaSlots:
+            // kDmaSlots - kDmaAhead stores have been committed after that one
+            asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kDmaSlots - kDmaAhead) : "memory");
+            load(t + kDmaAhead);
+        }
+    }
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
 constexpr int kMsgBins = 1024;
 constexpr int kShufMaxCols = 16;
 
@@ -285,7 +346,7 @@ struct igl_join_shuffle {
     int64_t out_rows = 0;
     cudaEvent_t ev[7] = {};
     cudaEvent_t ev_plan = nullptr, ev_wait = nullptr, ev_l[3] = {};   // second stream: probe-side partition start / end / barrier end
-    cudaStream_t stream2 = nullptr, stream3 = nullptr;
+    cudaStream_t stream2 = nullptr, stream3 = nullptr, stream_hi = nullptr;   // stream_hi: highest priority (the build side's barrier, pull and table build)
     cudaEvent_t ev_copy = nullptr, ev_segs = nullptr;
     cudaStream_t peer_stream[kShufMaxRanks] = {};   // copy-engine prefetch: one stream per peer
     cudaEvent_t peer_ev[kShufMaxRanks] = {};
@@ -467,7 +528,12 @@ int32_t igl_join_shuffle_create(igl_ctx* ctx, int32_t join_type, const int32_t* 
     for (auto& ev : js->ev_l) if (rc >= 0 && cudaEventCreate(&ev) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "cudaEventCreate failed");
     if (rc >= 0 && (cudaEventCreate(&js->ev_plan) != cudaSuccess || cudaEventCreate(&js->ev_wait) != cudaSuccess)) rc = fail(IGL_ERR_CUDA, "cudaEventCreate failed");
     if (rc >= 0 && cudaStreamCreateWithFlags(&js->stream2, cudaStreamNonBlocking) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "cudaStreamCreate failed");
-    if (rc >= 0 && cudaStreamCreateWithFlags(&js->stream3, cudaStreamNonBlocking) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "cudaStreamCreate failed");
+    if (rc >= 0) {   // the prefetch stream and the build-chain stream: highest priority, their CTAs go first when an SM has room
+        int lo = 0, hi = 0;
+        cudaDeviceGetStreamPriorityRange(&lo, &hi);
+        if (cudaStreamCreateWithPriority(&js->stream3, cudaStreamNonBlocking, hi) != cudaSuccess ||
+            cudaStreamCreateWithPriority(&js->stream_hi, cudaStreamNonBlocking, hi) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "cudaStreamCreate failed");
+    }
     if (rc >= 0 && cudaEventCreateWithFlags(&js->ev_copy, cudaEventDisableTiming) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "cudaEventCreate failed");
     if (rc >= 0 && cudaEventCreateWithFlags(&js->ev_segs, cudaEventDisableTiming) != cudaSuccess) rc = fail(IGL_ERR_CUDA, "cudaEventCreate failed");
     if (rc < 0) { igl_join_shuffle_destroy(js.release()); return rc; }
@@ -597,6 +663,14 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
     // pull and table build; the probe kernel waits for it (and for every peer's) below.
     const bool overlap = js->mode == IGL_EXCHANGE_P2P && !(getenv("IGL_SHUFFLE_OVERLAP") && getenv("IGL_SHUFFLE_OVERLAP")[0] == '0');
     cudaStream_t st_l = overlap ? js->stream2 : st;
+    // The probe side's partition kernel, launched as one persistent grid, holds every SM until it is done, and
+    // the build side's pull and table build wait behind it although they need other resources (NVLink, L2
+    // atomics).  Yielding form: one CTA per tile for the probe side's partitioning, and the build side's chain
+    // on a stream of the highest priority — its CTAs get onto the SMs between tiles.  Measured (C3): the two then
+    // do run side by side and finish no earlier — 16.43 against 16.48 ms on 2 GPUs, 5.78 against 5.59 ms on 8 —
+    // so it stays off unless IGL_SHUFFLE_YIELD=1.
+    const bool yield = overlap && W > 1 && getenv("IGL_SHUFFLE_YIELD") && getenv("IGL_SHUFFLE_YIELD")[0] == '1';
+    cudaStream_t st_b = yield ? js->stream_hi : st;
     if (overlap) {
         cudaEventRecord(js->ev_plan, st);
         IGL_CUDA_OK(cudaStreamWaitEvent(st_l, js->ev_plan, 0));
@@ -605,7 +679,7 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
     for (int sd = 0; sd < 2; ++sd)
         IGL_TRY(radix_scatter_bins_async(ctx, in[sd], js->side[sd].ncols, js->side[sd].key, n_in[sd], nd[sd], W, lp, hot[sd],
                                          js->side[sd].staging.data(), js->d_plan + (size_t)sd * kMsgBins,
-                                         js->d_plan + (size_t)(2 + sd) * kMsgBins, sd == 1 ? st_l : st));
+                                         js->d_plan + (size_t)(2 + sd) * kMsgBins, sd == 1 ? st_l : st, sd == 1 && yield));
     if (overlap) cudaEventRecord(js->ev_l[1], st_l);
     cudaEventRecord(js->ev[2], st);
     // ---- where the runs are read from
@@ -645,14 +719,17 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
         // is one contiguous run per column); the probe kernel then finds those runs in local memory and
         // fetches only the rest across the link itself.  Only a probe that the link would hold back is
         // worth it, and only as much as fits under the build (sized from the previous run's build time).
-        // Measured at C3 on 8 GPUs (5.69 ms per join without): one copy-engine stream moved the
-        // 0.71 GB at only ~245 GB/s and the probe waited for it (8.44 ms); a copy kernel took the build
-        // kernel's SMs and memory system (build 1.1 -> 3.4 ms; 7.80 ms).  Off unless IGL_SHUFFLE_PREFETCH
-        // names a mode: "ce" = one copy-engine stream per peer, "sm" = copy kernel; IGL_SHUFFLE_PREFETCH_FRAC
-        // overrides the share of partitions.
+        // Measured at C3 on 8 GPUs (5.6-5.7 ms per join without), every variant slower: one copy-engine
+        // stream moved the 0.71 GB at only ~245 GB/s and the probe waited for it (8.44 ms); one copy-engine
+        // stream per peer 6.97 ms (8.87 ms at 60 % of the partitions); a copy kernel over all SMs took the
+        // build kernel's SMs and memory system (build 1.1 -> 3.4 ms; 7.80 ms); 24 CTAs working as copy engines
+        // (dma_copy_kernel, 20 % of the partitions) 6.33 ms: the probe kernel gained 0.19 ms (2.74 -> 2.55: its
+        // time does not fall in proportion to the rows made local), the build lost 0.2-0.9 ms.  Off unless
+        // IGL_SHUFFLE_PREFETCH names a mode: "ce" = one copy-engine stream per peer, "sm" = copy kernel,
+        // "dma" = dma_copy_kernel; IGL_SHUFFLE_PREFETCH_FRAC sets the share of partitions.
         const char* pe = getenv("IGL_SHUFFLE_PREFETCH");
-        const bool pref_ce = pe && pe[0] == 'c', pref_sm = pe && pe[0] == 's';
-        if (overlap && W > 1 && (pref_ce || pref_sm)) {
+        const bool pref_ce = pe && pe[0] == 'c', pref_sm = pe && pe[0] == 's', pref_dma = pe && pe[0] == 'd';
+        if (overlap && W > 1 && (pref_ce || pref_sm || (pref_dma && (W - 1) * js->side[1].ncols <= kDmaMaxRuns))) {
             ShuffleSide& S = js->side[1];
             const char* fe = getenv("IGL_SHUFFLE_PREFETCH_FRAC");
             double frac = fe ? atof(fe) : -1.0;
@@ -756,7 +833,8 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
     if (js->mode == IGL_EXCHANGE_P2P) {
         // the build side's barrier (on this stream) first, then the probe side's (on its own stream when
         // overlapped) — the same order on every rank
-        IGL_NCCL_OK(g_nccl.AllReduce(js->d_flag, js->d_flag, 1, kNcclInt32, kNcclSum, comm->comm, st));
+        if (yield) IGL_CUDA_OK(cudaStreamWaitEvent(st_b, js->ev_segs, 0));
+        IGL_NCCL_OK(g_nccl.AllReduce(js->d_flag, js->d_flag, 1, kNcclInt32, kNcclSum, comm->comm, st_b));
         if (overlap) {
             IGL_NCCL_OK(g_nccl.AllReduce(js->d_flag + 8, js->d_flag + 8, 1, kNcclInt32, kNcclSum, comm->comm, st_l));
             cudaEventRecord(js->ev_l[2], st_l);
@@ -778,6 +856,35 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
                                                     cudaMemcpyDefault, js->peer_stream[s]));
                     IGL_CUDA_OK(cudaEventRecord(js->peer_ev[s], js->peer_stream[s]));
                     IGL_CUDA_OK(cudaStreamWaitEvent(js->stream3, js->peer_ev[s], 0));
+                }
+            } else if (pm && pm[0] == 'd') {   // a few CTAs as copy engines (dma_copy_kernel)
+                ShuffleSide& S = js->side[1];
+                DmaParams D{};
+                uint32_t piece = 0;
+                for (int s = 0; s < W; ++s) {
+                    if (s == me || pf_len[s] == 0) continue;
+                    for (int c = 0; c < S.ncols; ++c) {
+                        D.src[D.nruns] = src_cols[1][s][c] + ((size_t)pf_first[s] << S.shift[c]);
+                        D.dst[D.nruns] = (uint8_t*)S.recv[c] + ((size_t)pf_base[s] << S.shift[c]);
+                        D.bytes[D.nruns] = (uint64_t)pf_len[s] << S.shift[c];
+                        D.piece0[D.nruns] = piece;
+                        piece += (uint32_t)((D.bytes[D.nruns] + kDmaPiece - 1) / kDmaPiece);
+                        ++D.nruns;
+                    }
+                }
+                D.piece0[D.nruns] = piece;
+                const char* ce = getenv("IGL_SHUFFLE_PREFETCH_CTAS");
+                const int ctas = std::max(1, std::min(ctx->sm_count, ce ? atoi(ce) : 24));
+                static bool attr_set = false;
+                if (!attr_set) {
+                    IGL_CUDA_OK(cudaFuncSetAttribute((const void*)dma_copy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kDmaSlots * kDmaPiece)));
+                    attr_set = true;
+                }
+                IGL_CUDA_OK(cudaStreamWaitEvent(js->stream3, js->ev_l[2], 0));
+                if (piece) {
+                    dma_copy_kernel<<<ctas, 32, kDmaSlots * kDmaPiece, js->stream3>>>(D);
+                    IGL_CUDA_OK(cudaGetLastError());
+                    ctx->launches++;
                 }
             } else {
                 IGL_CUDA_OK(cudaStreamWaitEvent(js->stream3, js->ev_l[2], 0));
@@ -802,17 +909,18 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
             IGL_NCCL_OK(g_nccl.GroupEnd());
         }
     }
-    cudaEventRecord(js->ev[3], st);
+    cudaEventRecord(js->ev[3], st_b);
     // ---- 5. build side: pull, build
     ShuffleSide& R = js->side[0];
     ShuffleSide& L = js->side[1];
     IGL_TRY(ensure_cols(ctx, R.slab, R.slab_rows, R, recv_total[0] + 64));
-    IGL_TRY(launch_seg_copy(ctx, R, src_cols[0], W, d_copy[0], ncopy[0], copy_blocks[0], R.slab.data(), st));
+    IGL_TRY(launch_seg_copy(ctx, R, src_cols[0], W, d_copy[0], ncopy[0], copy_blocks[0], R.slab.data(), st_b));
     std::vector<igl_dev_col> rcols(R.ncols), lcols(L.ncols);
     for (int c = 0; c < R.ncols; ++c) rcols[c] = igl_dev_col{R.types[c], 0, R.slab[c], nullptr, nullptr};
     IGL_TRY(igl_join_set_prepartitioned(js->join, lp > 0 ? 1 : 0));
-    IGL_TRY(igl_join_build(js->join, rcols.data(), recv_total[0], st));
-    cudaEventRecord(js->ev[4], st);
+    IGL_TRY(igl_join_build(js->join, rcols.data(), recv_total[0], st_b));
+    cudaEventRecord(js->ev[4], st_b);
+    if (yield) IGL_CUDA_OK(cudaStreamWaitEvent(st, js->ev[4], 0));
     // ---- 6. probe side
     if (overlap) IGL_CUDA_OK(cudaStreamWaitEvent(st, js->ev_l[2], 0));
     if (prefetching) IGL_CUDA_OK(cudaStreamWaitEvent(st, js->ev_copy, 0));
@@ -949,6 +1057,7 @@ void igl_join_shuffle_destroy(igl_join_shuffle* js) {
     if (js->ev_wait) cudaEventDestroy(js->ev_wait);
     if (js->stream2) cudaStreamDestroy(js->stream2);
     if (js->stream3) cudaStreamDestroy(js->stream3);
+    if (js->stream_hi) cudaStreamDestroy(js->stream_hi);
     for (auto& q : js->peer_stream) if (q) cudaStreamDestroy(q);
     for (auto& q : js->peer_ev) if (q) cudaEventDestroy(q);
     if (js->ev_copy) cudaEventDestroy(js->ev_copy);
