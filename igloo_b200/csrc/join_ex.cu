@@ -18,9 +18,11 @@
 //   other key lists     a 64-bit hash of the canonical key values (type tags and NULL markers
 //                       included) is the hidden key; since a hash can collide, the joined rows are
 //                       then filtered by the real condition, key by key and null-safe
-//                       (a = b OR (a IS NULL AND b IS NULL)) with the fused filter kernel.  Inner /
-//                       Right joins only: a Left join would need to know that ALL matches of a row
-//                       were false ones.
+//                       (a = b OR (a IS NULL AND b IS NULL)) with the fused filter kernel.  A Left /
+//                       Full join must also know when ALL matches of a probe row were false ones:
+//                       both sides then carry a row-number column through the join, true matches are
+//                       counted per probe row, and the first false pair of a row without any true
+//                       match is turned into its null-extended row (the others are dropped).
 //   Boolean columns     widened to Int32 on the way in, packed back to bits on the way out
 //   key types differ    the printed key carries the Arrow type: such a pair never matches (the core
 //                       join's own rule, so one mismatching pair is handed to it as the key)
@@ -69,8 +71,9 @@ struct HashKeyCols {
 
 // Canonical value per key (join.cu canon_key: Int32 sign-extended, every NaN one NaN, Boolean 0/1),
 // a marker for NULL, the type and the position folded in; equal key lists give equal hashes.
-__global__ void hash_keys_kernel(const __grid_constant__ HashKeyCols K, long long n, int64_t* __restrict__ out) {
+__global__ void hash_keys_kernel(const __grid_constant__ HashKeyCols K, long long n, int bits, int64_t* __restrict__ out) {
     const long long stride = (long long)gridDim.x * blockDim.x;
+    const uint64_t mask = bits >= 64 ? ~0ull : ((1ull << bits) - 1);   // IGL_JOIN_KEY_HASH_BITS: a test switch that forces collisions
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         uint64_t h = 0x9E3779B97F4A7C15ull;
         for (int k = 0; k < K.n; ++k) {
@@ -89,7 +92,45 @@ __global__ void hash_keys_kernel(const __grid_constant__ HashKeyCols K, long lon
             }
             h = splitmix64(h ^ (v + (uint64_t)(K.type[k] * 16 + k + (ok ? 0 : 8)) * 0xD6E8FEB86659FD93ull));
         }
-        out[i] = (int64_t)h;
+        out[i] = (int64_t)(h & mask);
+    }
+}
+
+// ---- Left / Full join on a hashed key list: which joined pairs survive the real condition ----
+__device__ __forceinline__ bool bit_at(const uint8_t* b, long long i) { return (b[i >> 3] >> (i & 7)) & 1; }
+
+__global__ void lj_count_true_kernel(const int32_t* __restrict__ lrow, const uint8_t* __restrict__ matched, const uint8_t* __restrict__ ok_bits,
+                                     const uint8_t* __restrict__ ok_valid, long long n, int32_t* __restrict__ true_cnt) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+        if (bit_at(matched, i) && bit_at(ok_bits, i) && (!ok_valid || bit_at(ok_valid, i))) atomicAdd(&true_cnt[lrow[i]], 1);
+}
+
+// keep[i]: the row stays.  nullify[i]: it stays as the null-extended row of its probe row (the first false pair of a
+// probe row none of whose matches was a true one).
+__global__ void lj_decide_kernel(const int32_t* __restrict__ lrow, const uint8_t* __restrict__ matched, const uint8_t* __restrict__ ok_bits,
+                                 const uint8_t* __restrict__ ok_valid, long long n, const int32_t* __restrict__ true_cnt,
+                                 int32_t* __restrict__ claimed, int32_t* __restrict__ keep, uint8_t* __restrict__ nullify) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        int k = 1, z = 0;
+        if (bit_at(matched, i) && !(bit_at(ok_bits, i) && (!ok_valid || bit_at(ok_valid, i)))) {
+            const int32_t l = lrow[i];
+            if (true_cnt[l] == 0 && atomicExch(&claimed[l], 1) == 0) z = 1; else k = 0;
+        }
+        keep[i] = k; nullify[i] = (uint8_t)z;
+    }
+}
+
+// one thread per 32-row word of a validity bitmap: clears the bits of the rows to null-extend
+__global__ void lj_nullify_kernel(const uint8_t* __restrict__ nullify, long long n, uint32_t* __restrict__ valid_words) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const long long nwords = (n + 31) >> 5;
+    for (long long w = (long long)blockIdx.x * blockDim.x + threadIdx.x; w < nwords; w += stride) {
+        uint32_t m = 0;
+        const long long base = w << 5;
+        for (int b = 0; b < 32 && base + b < n; ++b) m |= (uint32_t)(nullify[base + b] & 1) << b;
+        if (m) valid_words[w] &= ~m;
     }
 }
 
@@ -112,6 +153,10 @@ struct JoinEx {
     int key_type = IGL_T_I64;                  // type of the hidden key column
     igl_join* inner = nullptr;
     igl_fp* verify = nullptr;                  // EX_HASHED: the real join condition over the output schema
+    bool track = false;                        // EX_HASHED Left / Full: both sides carry an emitted row-number column
+    igl_fp* verify_ok = nullptr;               // then: the condition as a Boolean output column,
+    igl_fp* compact = nullptr;                 //       and (output columns, keep flag) -> output columns where keep != 0
+    int hash_bits = 64;
     std::vector<void*> rtemp;                  // build-side temporaries (widened booleans, key column): live as long as the table
     std::vector<uint8_t> r_has_valid;          // which build columns came with a validity bitmap
     int64_t build_rows = 0;
@@ -175,7 +220,7 @@ static int32_t hidden_key_column(JoinEx* E, const std::vector<igl_dev_col>& kv, 
         HashKeyCols K{};
         K.n = E->nkeys;
         for (int k = 0; k < E->nkeys; ++k) { K.data[k] = (const uint8_t*)kv[k].data; K.valid[k] = kv[k].validity; K.type[k] = kv[k].type; }
-        hash_keys_kernel<<<grid_for(ctx, n), 256, 0, st>>>(K, n, (int64_t*)p);
+        hash_keys_kernel<<<grid_for(ctx, n), 256, 0, st>>>(K, n, E->hash_bits, (int64_t*)p);
     }
     IGL_CUDA_OK(cudaGetLastError());
     ctx->launches++;
@@ -208,6 +253,14 @@ static int32_t augment(JoinEx* E, bool left, const igl_dev_col* cols, int64_t n,
         igl_dev_col hk{};
         IGL_TRY(hidden_key_column(E, kv, n, st, hk, temps));
         aug.push_back(hk);
+    }
+    if (E->track) {   // this side's row numbers, carried through the join
+        if (n >= ((int64_t)1 << 31)) return fail(IGL_ERR_UNSUPPORTED, "a Left/Full join on a hashed key list is limited to 2^31 rows per side and call");
+        void* p = nullptr;
+        IGL_TRY(pool_alloc(ctx, pad_bytes((size_t)n * 4), &p));
+        temps.push_back(p);
+        IGL_TRY(launch_iota_i32(ctx, (int32_t*)p, n, st));
+        aug.push_back(igl_dev_col{IGL_T_I32, 0, p, nullptr, nullptr});
     }
     IGL_CUDA_OK(cudaGetLastError());
     return IGL_OK;
@@ -292,6 +345,14 @@ int32_t join_ex_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_d
             iout.push_back(o);
         }
         if (E->hidden_key) iout.push_back(igl_dev_col{E->key_type, 0, nullptr, nullptr, nullptr});
+        if (E->track) {
+            void *p = nullptr, *v = nullptr;
+            IGL_TRY(pool_alloc(ctx, pad_bytes((size_t)cap * 4), &p));
+            temps.push_back(p);
+            IGL_TRY(pool_alloc(ctx, pad_bytes((size_t)(cap + 7) / 8), &v));
+            temps.push_back(v);
+            iout.push_back(igl_dev_col{IGL_T_I32, 0, p, (uint8_t*)v, nullptr});
+        }
         return IGL_OK;
     };
     rc = push_side(0, E->nl);
@@ -302,13 +363,46 @@ int32_t join_ex_probe(igl_join* j, const igl_dev_col* left, int64_t nrows, igl_d
     if (rc < 0) return done(rc);
     // Booleans back to bits
     for (int c = 0, ic = 0; c < nu; ++c, ++ic) {
-        if (c == E->nl && E->hidden_key) ++ic;
+        if (c == E->nl) ic += (E->hidden_key ? 1 : 0) + (E->track ? 1 : 0);
         if (out_type(c) != IGL_T_BOOL || n == 0) continue;
         i32_to_bool_kernel<<<grid_for(ctx, (n + 31) / 32), 256, 0, st>>>((const int32_t*)iout[ic].data, n, (uint32_t*)mid[c].data);
         ctx->launches++;
     }
     if (cudaGetLastError() != cudaSuccess) return done(fail(IGL_ERR_CUDA, "boolean repack failed"));
-    if (staged && n > 0) {
+    if (staged && n > 0 && E->track) {
+        // Left / Full: the condition as a column, true matches counted per probe row, false pairs dropped —
+        // except the first one of a probe row without any true match, which becomes its null-extended row
+        const int extra = (E->hidden_key ? 1 : 0) + 1;
+        const int32_t* lrow = (const int32_t*)iout[E->nl + extra - 1].data;
+        const uint8_t* matched = iout[E->nl + extra + E->nr + extra - 1].validity;   // the right row number is valid = the pair is a match
+        int32_t okt = 0, oknl = 0;
+        igl_fp_output_type(E->verify_ok, 0, &okt, &oknl);
+        void *ok_bits = nullptr, *ok_valid = nullptr, *true_cnt = nullptr, *claimed = nullptr, *keep = nullptr, *nullify = nullptr;
+        auto get = [&](size_t bytes, void** p) -> int32_t { int32_t r = pool_alloc(ctx, pad_bytes(bytes), p); if (r >= 0) temps.push_back(*p); return r; };
+        if ((rc = get((size_t)(n + 7) / 8, &ok_bits)) < 0 || (oknl && (rc = get((size_t)(n + 7) / 8, &ok_valid)) < 0) ||
+            (rc = get((size_t)std::max<int64_t>(nrows, 1) * 4, &true_cnt)) < 0 || (rc = get((size_t)std::max<int64_t>(nrows, 1) * 4, &claimed)) < 0 ||
+            (rc = get((size_t)n * 4, &keep)) < 0 || (rc = get((size_t)n, &nullify)) < 0) return done(rc);
+        igl_dev_col okcol{IGL_T_BOOL, 0, ok_bits, (uint8_t*)ok_valid, nullptr};
+        int64_t rows = 0;
+        rc = igl_fp_run(E->verify_ok, mid.data(), n, &okcol, &rows, (void*)st);
+        if (rc < 0) return done(rc);
+        if (cudaMemsetAsync(true_cnt, 0, (size_t)std::max<int64_t>(nrows, 1) * 4, st) != cudaSuccess ||
+            cudaMemsetAsync(claimed, 0, (size_t)std::max<int64_t>(nrows, 1) * 4, st) != cudaSuccess) return done(fail(IGL_ERR_CUDA, "memset failed"));
+        lj_count_true_kernel<<<grid_for(ctx, n), 256, 0, st>>>(lrow, matched, (const uint8_t*)ok_bits, (const uint8_t*)ok_valid, n, (int32_t*)true_cnt);
+        lj_decide_kernel<<<grid_for(ctx, n), 256, 0, st>>>(lrow, matched, (const uint8_t*)ok_bits, (const uint8_t*)ok_valid, n, (const int32_t*)true_cnt,
+                                                          (int32_t*)claimed, (int32_t*)keep, (uint8_t*)nullify);
+        for (int c = E->nl; c < nu; ++c)
+            lj_nullify_kernel<<<grid_for(ctx, (n + 31) / 32), 256, 0, st>>>((const uint8_t*)nullify, n, (uint32_t*)mid[c].validity);
+        ctx->launches += 2 + E->nr;
+        if (cudaGetLastError() != cudaSuccess) return done(fail(IGL_ERR_CUDA, "left-join verification failed to launch"));
+        std::vector<igl_dev_col> in2(mid), fin(nu);
+        in2.push_back(igl_dev_col{IGL_T_I32, 0, keep, nullptr, nullptr});
+        for (int c = 0; c < nu; ++c) { fin[c] = out[c]; fin[c].type = out_type(c); }
+        int64_t kept = 0;
+        rc = igl_fp_run(E->compact, in2.data(), n, fin.data(), &kept, (void*)st);
+        if (rc < 0) return done(rc);
+        n = kept;
+    } else if (staged && n > 0) {
         // the real join condition, key by key: drops rows whose 64-bit key hashes collided
         std::vector<igl_dev_col> fin(nu);
         for (int c = 0; c < nu; ++c) { fin[c] = out[c]; fin[c].type = out_type(c); }
@@ -330,6 +424,8 @@ void join_ex_destroy(igl_join* j) {
     if (E->lfp) igl_fp_destroy(E->lfp);
     if (E->rfp) igl_fp_destroy(E->rfp);
     if (E->verify) igl_fp_destroy(E->verify);
+    if (E->verify_ok) igl_fp_destroy(E->verify_ok);
+    if (E->compact) igl_fp_destroy(E->compact);
     for (void* p : E->rtemp) pool_free(E->ctx, p);
     delete E;
     *join_ex_slot(j) = nullptr;
@@ -395,7 +491,7 @@ extern "C" int32_t igl_join_create_ex(igl_ctx* ctx, int32_t join_type, const int
     if (right_nullable) E->rn.assign(right_nullable, right_nullable + n_right);
     for (int k = 0; k < nkeys; ++k) { E->lkeys.push_back(*left_keys[k]); E->rkeys.push_back(*right_keys[k]); }
     DeviceGuard g(ctx->device);
-    struct Cleanup { JoinEx* e; ~Cleanup() { if (e) { if (e->inner) igl_join_destroy(e->inner); if (e->lfp) igl_fp_destroy(e->lfp); if (e->rfp) igl_fp_destroy(e->rfp); if (e->verify) igl_fp_destroy(e->verify); } } } guard{E.get()};
+    struct Cleanup { JoinEx* e; ~Cleanup() { if (e) { if (e->inner) igl_join_destroy(e->inner); if (e->lfp) igl_fp_destroy(e->lfp); if (e->rfp) igl_fp_destroy(e->rfp); if (e->verify) igl_fp_destroy(e->verify); if (e->verify_ok) igl_fp_destroy(e->verify_ok); if (e->compact) igl_fp_destroy(e->compact); } } } guard{E.get()};
 
     // a pair whose types differ can never match (the printed key names its Arrow type): hand that pair
     // to the core join as the one key — its own rule then yields no match / all null-extended rows
@@ -421,7 +517,8 @@ extern "C" int32_t igl_join_create_ex(igl_ctx* ctx, int32_t join_type, const int
         E->mode = EX_PACKED; E->hidden_key = true; E->key_type = IGL_T_I64;
     } else {
         E->mode = EX_HASHED; E->hidden_key = true; E->key_type = IGL_T_I64;
-        if (E->left_join) return fail(IGL_ERR_UNSUPPORTED, "Left/Full joins on key lists wider than two Int32 columns are not supported on the device");
+        E->track = E->left_join;
+        if (const char* hb = getenv("IGL_JOIN_KEY_HASH_BITS")) E->hash_bits = std::min(64, std::max(1, atoi(hb)));
         if (!all_plain) return fail(IGL_ERR_UNSUPPORTED, "computed keys in a join on a hashed key list are not supported; project them first");
     }
     // projections for the computed keys
@@ -451,6 +548,11 @@ extern "C" int32_t igl_join_create_ex(igl_ctx* ctx, int32_t join_type, const int
         irn.push_back(E->mode == EX_SINGLE && E->rkeys[0].nullable ? 1 : 0);
         lhide.push_back(1); rhide.push_back(1);
     }
+    if (E->track) {   // row numbers of both sides: emitted, never NULL on their own side
+        ilt.push_back(IGL_T_I32); irt.push_back(IGL_T_I32);
+        iln.push_back(0); irn.push_back(0);
+        lhide.push_back(0); rhide.push_back(0);
+    }
     std::vector<int> ilt_i(ilt.begin(), ilt.end()), irt_i(irt.begin(), irt.end());
     igl_expr lk = plain_col_expr(ilkey, ilt[ilkey], iln[ilkey] != 0, ilt_i, iln);
     igl_expr rk = plain_col_expr(irkey, irt[irkey], irn[irkey] != 0, irt_i, irn);
@@ -462,6 +564,7 @@ extern "C" int32_t igl_join_create_ex(igl_ctx* ctx, int32_t join_type, const int
         ot.insert(ot.end(), E->rt.begin(), E->rt.end());
         std::vector<uint8_t> on(E->ln);
         on.insert(on.end(), E->rn.begin(), E->rn.end());
+        if (E->left_join) for (int c = n_left; c < n_left + n_right; ++c) on[c] = 1;   // null-extended rows
         std::vector<uint8_t> bc;
         for (int k = 0; k < E->nkeys; ++k) {
             const int a = E->lkeys[k].nodes[0].col, b = n_left + E->rkeys[k].nodes[0].col;
@@ -472,9 +575,26 @@ extern "C" int32_t igl_join_create_ex(igl_ctx* ctx, int32_t join_type, const int
         }
         igl_expr* pred = nullptr;
         IGL_TRY(igl_expr_compile(ctx, bc.data(), bc.size(), ot.data(), on.data(), (int32_t)ot.size(), &pred));
-        const int32_t rc = fp_create_ex(ctx, ot.data(), on.data(), (int32_t)ot.size(), pred, nullptr, 0, nullptr, false, &E->verify);
+        int32_t rc;
+        if (!E->track) rc = fp_create_ex(ctx, ot.data(), on.data(), (int32_t)ot.size(), pred, nullptr, 0, nullptr, false, &E->verify);
+        else {
+            const igl_expr* pe[1] = {pred};
+            rc = fp_create_ex(ctx, ot.data(), on.data(), (int32_t)ot.size(), nullptr, pe, 1, nullptr, false, &E->verify_ok);
+        }
         igl_expr_destroy(pred);
         IGL_TRY(rc);
+        if (E->track) {
+            const int kc = (int)ot.size();
+            ot.push_back(IGL_T_I32); on.push_back(0);
+            std::vector<uint8_t> skip(ot.size(), 0);
+            skip[kc] = 1;
+            const uint8_t kb[9] = {IGL_OP_COL, (uint8_t)(kc & 0xFF), (uint8_t)(kc >> 8), IGL_OP_LIT_I32, 0, 0, 0, 0, IGL_OP_NE};
+            igl_expr* kp = nullptr;
+            IGL_TRY(igl_expr_compile(ctx, kb, sizeof kb, ot.data(), on.data(), (int32_t)ot.size(), &kp));
+            rc = fp_create_ex(ctx, ot.data(), on.data(), (int32_t)ot.size(), kp, nullptr, 0, skip.data(), false, &E->compact);
+            igl_expr_destroy(kp);
+            IGL_TRY(rc);
+        }
     }
     igl_join* shell = join_new_shell(ctx);
     guard.e = nullptr;
