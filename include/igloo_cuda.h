@@ -210,7 +210,8 @@ int32_t igl_join_create(igl_ctx* ctx, int32_t join_type,
  * errors — division by zero, casts — surface from build / probe), and Boolean columns on either
  * side.  A pair whose types differ never matches.  Two Int32 keys that cannot be NULL are packed
  * into one exact 64-bit key; other key lists are hashed to 64 bits and the joined rows are then
- * filtered by the real, null-safe condition (Inner / Right only; plain-column keys only).
+ * filtered by the real, null-safe condition (plain-column keys only; a Left / Full join counts
+ * the true matches per probe row and null-extends the rows left without one).
  * Utf8 columns are carried by the streaming operator (igl_op_hash_join_create), not here.
  * igl_join_probe_count on a hashed key list is an upper bound.  One plain key over fixed-width
  * columns is exactly igl_join_create. */
@@ -380,7 +381,10 @@ int32_t igl_op_hash_join_create(igl_ctx* ctx, int32_t join_type,
                                 const uint8_t* left_key, size_t left_key_len,
                                 const uint8_t* right_key, size_t right_key_len, igl_op** out);
 /* The same with every key pair of `join.on` (physical_planner.rs:106-120): nkeys bytecodes per side,
- * any expressions of the side's columns; Boolean columns may ride along (igl_join_create_ex). */
+ * any expressions of the side's columns; Boolean and Utf8 columns may ride along (igl_join_create_ex;
+ * strings by row id), and a bare Utf8 column may be a key on both sides of a pair (hash_join.rs:120
+ * prints any Arrow type): the device joins on a 64-bit hash of the bytes and every joined pair is then
+ * compared byte for byte; NULL == NULL as for every key. */
 int32_t igl_op_hash_join_create_ex(igl_ctx* ctx, int32_t join_type,
                                    const struct ArrowSchema* left_schema, const struct ArrowSchema* right_schema,
                                    const uint8_t* const* left_keys, const size_t* left_key_lens,
