@@ -60,6 +60,7 @@ struct JoinSide {          // side entries: [0] NULL key, [1] key == kEmptyKey
     unsigned long long cursor;   // CSR run allocator
     unsigned int ticket;         // build kernels: chunk claims
     unsigned int pad2;
+    unsigned long long ovf_count;   // shared-memory build: rows that ran past their sub-region's end
 };
 
 struct JoinTable {
@@ -99,7 +100,87 @@ __global__ void join_init_kernel(Slot* slots, uint64_t capacity, JoinSide* side)
         *reinterpret_cast<ulonglong2*>(slots + i) = e;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         side->count[0] = side->count[1] = 0; side->run_end[0] = side->run_end[1] = 0;
-        side->val[0] = side->val[1] = 0; side->dup_flag = 0; side->cursor = 0; side->ticket = 0;
+        side->val[0] = side->val[1] = 0; side->dup_flag = 0; side->cursor = 0; side->ticket = 0; side->ovf_count = 0;
+    }
+}
+
+// ---- build in shared memory -------------------------------------------------------------------------
+// Random 16-byte writes into an L2-resident table region — atomic or not — run at 28-37 G/s on B200
+// (tools/micro/atomic_bench.cu: CAS 36.8, CAS + payload store 29.5, plain 16-byte stores 27.8 G/s), which
+// is what join_build_unique_kernel gets (34 G inserts/s).  So for large unique build sides the rows are
+// ordered once more (partition.cu, radix_partition_fine) down to sub-regions of kFineSlots slots, and one
+// CTA builds each sub-region in shared memory and writes it out as 64 KB of consecutive stores — which
+// also clears the empty slots, so no init pass.  A row whose walk runs past the sub-region's end (rare)
+// goes to a short list and is inserted with global atomics afterwards.
+constexpr int kFineSlotsLog2 = 12;
+constexpr int kFineSlots = 1 << kFineSlotsLog2;   // 64 KB of table per CTA, three CTAs per SM
+constexpr int kFineThreads = 1024;
+constexpr int kFineU = 2;
+
+__global__ void __launch_bounds__(kFineThreads, 2) join_build_fine_kernel(const void* __restrict__ keys, int key_type, const void* __restrict__ payload,
+                                                                       int payload_shift, const unsigned long long* __restrict__ bin_offsets,
+                                                                       JoinTable t, Slot* __restrict__ ovf, unsigned long long ovf_cap) {
+    extern __shared__ __align__(16) uint8_t fine_smem[];
+    Slot* tab = reinterpret_cast<Slot*>(fine_smem);
+    const unsigned long long slot0 = (unsigned long long)blockIdx.x << kFineSlotsLog2;
+    {
+        ulonglong2 e; e.x = kEmptyKey; e.y = 0;
+        for (int q = threadIdx.x; q < kFineSlots; q += kFineThreads) reinterpret_cast<ulonglong2*>(tab)[q] = e;
+    }
+    __syncthreads();
+    const long long r0 = (long long)bin_offsets[blockIdx.x], r1 = (long long)bin_offsets[blockIdx.x + 1];
+    for (long long base = r0; base < r1; base += kFineThreads * kFineU) {
+        uint64_t k[kFineU];
+        unsigned long long val[kFineU];
+#pragma unroll
+        for (int u = 0; u < kFineU; ++u) {   // all loads first
+            const long long i = base + u * kFineThreads + threadIdx.x;
+            k[u] = kEmptyKey; val[u] = 0;
+            if (i < r1) {
+                val[u] = payload_shift == 0xFF ? (unsigned long long)i
+                         : payload_shift == 2 ? (unsigned long long)((const uint32_t*)payload)[i]
+                                              : ((const unsigned long long*)payload)[i];
+                k[u] = canon_key(key_type, load_key_global(keys, key_type, i));
+                if (k[u] == kEmptyKey) {   // the one key equal to the empty-slot sentinel lives in a side entry
+                    if (atomicAdd(&t.side->count[1], 1u) == 0) t.side->val[1] = val[u];
+                    else t.side->dup_flag = 1;
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kFineU; ++u) {
+            if (k[u] == kEmptyKey) continue;
+            unsigned long long h = ((mix64(k[u]) >> t.shift) & ~1ull) - slot0;   // < kFineSlots: that is what the fine order means
+            bool placed = false;
+            for (; h < (unsigned long long)kFineSlots; ++h) {
+                const unsigned long long prev = atomicCAS(reinterpret_cast<unsigned long long*>(&tab[h].key), (unsigned long long)kEmptyKey, (unsigned long long)k[u]);
+                if (prev == kEmptyKey) { tab[h].val = val[u]; placed = true; break; }
+                if (prev == k[u]) { t.side->dup_flag = 1; placed = true; break; }
+            }
+            if (!placed) {
+                const unsigned long long q = atomicAdd(&t.side->ovf_count, 1ull);
+                if (q < ovf_cap) { ovf[q].key = k[u]; ovf[q].val = val[u]; }
+            }
+        }
+    }
+    __syncthreads();
+    ulonglong2* g = reinterpret_cast<ulonglong2*>(t.slots + slot0);
+    for (int q = threadIdx.x; q < kFineSlots; q += kFineThreads) g[q] = reinterpret_cast<const ulonglong2*>(tab)[q];
+}
+
+// the rows join_build_fine_kernel could not place: ordinary linear probing over the finished table
+__global__ void join_build_overflow_kernel(const Slot* __restrict__ ovf, unsigned long long ovf_cap, JoinTable t) {
+    const unsigned long long n = min(t.side->ovf_count, ovf_cap);
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const unsigned long long k = ovf[i].key;
+        uint64_t h = (mix64(k) >> t.shift) & ~1ull;
+        while (true) {
+            const unsigned long long prev = atomicCAS(&t.slots[h].key, (unsigned long long)kEmptyKey, k);
+            if (prev == kEmptyKey) { t.slots[h].val = ovf[i].val; break; }
+            if (prev == k) { t.side->dup_flag = 1; break; }
+            h = (h + 1) & t.mask;
+        }
     }
 }
 
@@ -1284,6 +1365,12 @@ struct igl_join {
     // bits of the hash so each 16 MB table region is built and probed while L2-resident
     int log2_parts = 0;
     bool prepartitioned = false;             // both sides arrive ordered by the top hash bits: skip the radix passes
+    int prepart_bits = 0;                    // then: by how many bits (0 / 1 = not told)
+    void* fine_scratch = nullptr;            // shared-memory build: counts / offsets / cursors of the fine bins
+    size_t fine_scratch_bytes = 0;
+    void* fine_ovf = nullptr;                // rows that ran past their sub-region
+    size_t fine_ovf_cap = 0;
+    bool fine_built = false;                 // the last build went through join_build_fine_kernel
     std::vector<void*> part_right;           // partitioned build columns (owned)
     std::vector<void*> csr_right;            // duplicate layout: the build columns in CSR order (owned)
     void* packed = nullptr;                  // unique layout with row-id payload: the build rows as 16/32-byte records (owned)
@@ -1592,6 +1679,7 @@ int32_t igl_join_set_prepartitioned(igl_join* j, int32_t on) {
     if (!j) return fail(IGL_ERR_INVALID_ARG, "igl_join_set_prepartitioned: NULL join");
     if (j->ex) return igl_join_set_prepartitioned(join_ex_inner(j), on);
     j->prepartitioned = on != 0;
+    j->prepart_bits = on;
     return IGL_OK;
 }
 
@@ -1652,6 +1740,36 @@ int32_t igl_join_build(igl_join* j, const igl_dev_col* right, int64_t nrows, voi
             j->log2_parts = lp;
         }
     }
+    // Large unique build sides are built in shared memory, sub-region by sub-region (join_build_fine_kernel):
+    // the rows, ordered by their first hash bits above (or by the exchange), are first ordered down to sub-regions.
+    bool fine = false;
+    std::vector<void*> level1;   // the first-level copies: not needed once the fine order exists (freed after the stream has drained)
+    {
+        const int lp1 = j->log2_parts > 0 ? j->log2_parts : (j->prepartitioned && j->prepart_bits >= 2 ? j->prepart_bits : 0);
+        const int fine_bits = lg - kFineSlotsLog2;
+        const char* fenv = getenv("IGL_JOIN_FINE");
+        if (!(fenv && fenv[0] == '0') && lp1 > 0 && nrows > 0 && fine_bits > lp1 && fine_bits - lp1 <= 10 && fine_bits <= 20 &&
+            radix_partition_fine_supported(j->right.data(), nr)) {
+            const size_t need = 3 * ((size_t(1) << fine_bits) + 1) * 8;
+            if (need > j->fine_scratch_bytes) {
+                if (j->fine_scratch) pool_free(ctx, j->fine_scratch);
+                j->fine_scratch = nullptr; j->fine_scratch_bytes = 0;
+                IGL_TRY(pool_alloc(ctx, need, &j->fine_scratch));
+                j->fine_scratch_bytes = need;
+            }
+            std::vector<void*> dst(nr, nullptr);
+            level1 = j->part_right;
+            j->part_right.clear();
+            for (int c = 0; c < nr; ++c) {
+                IGL_TRY(pool_alloc(ctx, (size_t)nrows * (j->rt[c] == IGL_T_I32 ? 4 : 8) + 256, &dst[c]));
+                j->part_right.push_back(dst[c]);
+            }
+            IGL_TRY(radix_partition_fine(ctx, j->right.data(), nr, j->rkey, nrows, fine_bits, fine_bits - lp1, dst.data(), j->fine_scratch, st));
+            for (int c = 0; c < nr; ++c) j->right[c].data = dst[c];
+            fine = true;
+        }
+    }
+    j->fine_built = fine;
     right = j->right.data();
     cudaEventRecord(j->ev[1], st);
     const igl_dev_col& kc = right[j->rkey];
@@ -1662,21 +1780,57 @@ int32_t igl_join_build(igl_join* j, const igl_dev_col* right, int64_t nrows, voi
         j->payload_col = 1 - j->rkey;
     // (clearing the table on a side stream under the build side's partitioning was measured: both are
     // streaming passes over HBM, the sum of the two phases did not change — 5.87 vs 5.83 ms at C3)
-    join_init_kernel<<<grid, 256, 0, st>>>((Slot*)j->d_slots, cap, (JoinSide*)j->d_side);
-    IGL_CUDA_OK(cudaGetLastError());
-    ctx->launches++;
-    if (nrows > 0) {
-        const void* payload = j->payload_col >= 0 ? right[j->payload_col].data : nullptr;
-        const int pshift = j->payload_col >= 0 ? (j->rt[j->payload_col] == IGL_T_I32 ? 2 : 3) : 0xFF;
-        join_build_unique_kernel<<<grid, kBuildThreads, 0, st>>>(kc.data, j->rt[j->rkey], kc.validity, payload, pshift, nrows, j->table,
-                                                                  &((JoinSide*)j->d_side)->ticket);
+    const void* payload = j->payload_col >= 0 ? right[j->payload_col].data : nullptr;
+    const int pshift = j->payload_col >= 0 ? (j->rt[j->payload_col] == IGL_T_I32 ? 2 : 3) : 0xFF;
+    auto plain_build = [&]() -> int32_t {
+        join_init_kernel<<<grid, 256, 0, st>>>((Slot*)j->d_slots, cap, (JoinSide*)j->d_side);
         IGL_CUDA_OK(cudaGetLastError());
         ctx->launches++;
+        if (nrows > 0) {
+            join_build_unique_kernel<<<grid, kBuildThreads, 0, st>>>(kc.data, j->rt[j->rkey], kc.validity, payload, pshift, nrows, j->table,
+                                                                      &((JoinSide*)j->d_side)->ticket);
+            IGL_CUDA_OK(cudaGetLastError());
+            ctx->launches++;
+        }
+        return IGL_OK;
+    };
+    if (fine) {
+        const size_t ovf_cap = (size_t)std::max<int64_t>(4096, nrows / 32);
+        if (ovf_cap > j->fine_ovf_cap) {
+            if (j->fine_ovf) pool_free(ctx, j->fine_ovf);
+            j->fine_ovf = nullptr; j->fine_ovf_cap = 0;
+            IGL_TRY(pool_alloc(ctx, ovf_cap * sizeof(Slot), &j->fine_ovf));
+            j->fine_ovf_cap = ovf_cap;
+        }
+        static bool attr_set = false;
+        if (!attr_set) {
+            IGL_CUDA_OK(cudaFuncSetAttribute((const void*)join_build_fine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kFineSlots * sizeof(Slot))));
+            attr_set = true;
+        }
+        IGL_CUDA_OK(cudaMemsetAsync(j->d_side, 0, sizeof(JoinSide), st));
+        const unsigned long long* bin_offsets = (const unsigned long long*)j->fine_scratch + ((size_t(1) << (lg - kFineSlotsLog2)) + 1);
+        join_build_fine_kernel<<<(unsigned)(cap >> kFineSlotsLog2), kFineThreads, kFineSlots * sizeof(Slot), st>>>(
+            kc.data, j->rt[j->rkey], payload, pshift, bin_offsets, j->table, (Slot*)j->fine_ovf, (unsigned long long)j->fine_ovf_cap);
+        join_build_overflow_kernel<<<ctx->sm_count, 256, 0, st>>>((const Slot*)j->fine_ovf, (unsigned long long)j->fine_ovf_cap, j->table);
+        IGL_CUDA_OK(cudaGetLastError());
+        ctx->launches += 2;
+    } else {
+        IGL_TRY(plain_build());
     }
     cudaEventRecord(j->ev[2], st);
     j->ev_build = true;
     IGL_CUDA_OK(cudaMemcpyAsync(j->host_side, j->d_side, sizeof(JoinSide), cudaMemcpyDeviceToHost, st));
     IGL_CUDA_OK(cudaStreamSynchronize(st));
+    if (fine && j->host_side->ovf_count > (unsigned long long)j->fine_ovf_cap) {
+        // more rows ran past their sub-regions than the list holds (a pathological key set): the plain build, over the same rows
+        IGL_TRY(plain_build());
+        cudaEventRecord(j->ev[2], st);
+        IGL_CUDA_OK(cudaMemcpyAsync(j->host_side, j->d_side, sizeof(JoinSide), cudaMemcpyDeviceToHost, st));
+        IGL_CUDA_OK(cudaStreamSynchronize(st));
+        j->fine_built = false;
+    }
+    for (void* p : level1) pool_free(ctx, p);
+    level1.clear();
     j->csr = j->host_side->dup_flag != 0;
     if (j->packed) { pool_free(ctx, j->packed); j->packed = nullptr; }
     j->packed_stride = 0;
@@ -1980,6 +2134,8 @@ void igl_join_destroy(igl_join* j) {
     pool_free(j->ctx, j->d_rowids);
     pool_free(j->ctx, j->scratch);
     pool_free(j->ctx, j->part_scratch);
+    pool_free(j->ctx, j->fine_scratch);
+    pool_free(j->ctx, j->fine_ovf);
     for (void* p : j->part_right) pool_free(j->ctx, p);
     for (void* p : j->csr_right) pool_free(j->ctx, p);
     pool_free(j->ctx, j->packed);

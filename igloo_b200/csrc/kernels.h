@@ -60,6 +60,9 @@ int32_t radix_partition(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int ke
 struct HotKeys { const unsigned long long* table = nullptr; int mask = 0; int dest = 0; };
 int32_t radix_histogram_async(igl_ctx* ctx, const igl_dev_col* key, long long nrows, int ndest, int nhash, int log2_parts,
                               const HotKeys& hot, unsigned long long* dev_hist, cudaStream_t st);
+bool radix_partition_fine_supported(const igl_dev_col* cols, int ncols);
+int32_t radix_partition_fine(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int key_col, long long nrows, int fine_bits, int fine_lp2,
+                             void* const* dst, void* scratch, cudaStream_t st);
 int32_t radix_scatter_bins_async(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int key_col, long long nrows, int ndest, int nhash,
                                  int log2_parts, const HotKeys& hot, void* const* dst, const unsigned long long* dev_offsets,
                                  unsigned long long* dev_cursor, cudaStream_t st, bool yielding = false);

@@ -223,6 +223,11 @@ struct RadixParams {
     long long n;
     const unsigned long long* offsets;  // [bins]: first row of the bin inside its destination's buffer
     unsigned long long* cursor;         // [bins]
+    // second-level ("fine") pass over rows already ordered by the first `log2_parts` hash bits: the bin of a row is
+    // mix64 >> fine_shift (fine_bins of them — far more than a tile can rank), a tile ranks the 1024 bins that
+    // start at its first row's first-level partition and places the odd row beyond them one by one
+    int fine_shift, fine_lp2;
+    long long fine_bins;
 };
 
 // One tile.  FULL = every one of the 4096 rows exists (all tiles but the last):
@@ -367,7 +372,7 @@ constexpr int kRtRows = 4;
 constexpr int kRtTile = kRtThreads * kRtRows;          // 4096 rows
 constexpr unsigned kRtMaxDyn = 190u << 10;   // tile buffers; the two permutation arrays (16 KB) follow them
 
-template <int ROWS, bool HOT, int THREADS>   // ROWS rows per thread; tile = THREADS * ROWS rows (4096, or 8192 for the long-run form)
+template <int ROWS, bool HOT, int THREADS, bool FINE = false>   // ROWS rows per thread; tile = THREADS * ROWS rows (4096, or 8192 for the long-run form)
 __global__ void __launch_bounds__(THREADS, THREADS >= 1024 ? 1 : 2) radix_scatter_bulk_kernel(const __grid_constant__ RadixParams P, int n_buf, uint32_t tile_bytes) {
     constexpr int kTile = THREADS * ROWS;
     constexpr uint32_t kOffScale = kTile / kRtTile;   // P.stage_off is laid out for 4096-row tiles
@@ -380,8 +385,9 @@ __global__ void __launch_bounds__(THREADS, THREADS >= 1024 ? 1 : 2) radix_scatte
     unsigned short* s_part = s_perm + kTile;                                                               // slot -> bin
     __shared__ unsigned int s_warp_tot[THREADS / 32];
     __shared__ uint64_t s_full[2];
+    __shared__ int s_total;   // FINE: rows of the tile that were ranked (the others were placed one by one)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int nbins = P.ndest << P.log2_parts;
+    const int nbins = FINE ? kRadixMaxParts : P.ndest << P.log2_parts;
     const long long ntiles = (P.n + kTile - 1) / kTile;
     auto issue = [&](long long tile, int buf) {   // thread 0
         if (tile >= ntiles) return;
@@ -413,8 +419,13 @@ __global__ void __launch_bounds__(THREADS, THREADS >= 1024 ? 1 : 2) radix_scatte
         mbar_wait(&s_full[buf], phase);
         int bin[ROWS];
         unsigned int rank[ROWS];
+        long long fbase = 0;   // FINE: first bin of the window this tile ranks
         {
             const uint8_t* kc = in + P.stage_off[P.key_col] * kOffScale;
+            if constexpr (FINE) {   // the tile's first row sits in its lowest first-level partition: the window starts there
+                const uint64_t raw0 = P.key_type == IGL_T_I32 ? (uint64_t)((const uint32_t*)kc)[0] : ((const uint64_t*)kc)[0];
+                fbase = (long long)((mix64(part_canon(P.key_type, raw0)) >> P.fine_shift) >> P.fine_lp2) << P.fine_lp2;
+            }
 #pragma unroll
             for (int r = 0; r < ROWS; ++r) {
                 const int i = r * THREADS + tid;
@@ -422,8 +433,24 @@ __global__ void __launch_bounds__(THREADS, THREADS >= 1024 ? 1 : 2) radix_scatte
                 if (i < rows) {
                     const uint64_t raw = P.key_type == IGL_T_I32 ? (uint64_t)((const uint32_t*)kc)[i] : ((const uint64_t*)kc)[i];
                     const uint64_t ck = part_canon(P.key_type, raw);
-                    bin[r] = radix_bin_of<HOT>(ck, mix64(ck), P.nhash, P.log2_parts, P.hot);
-                    rank[r] = atomicAdd(&cnt[bin[r]], 1u);
+                    if constexpr (FINE) {
+                        const long long f = (long long)(mix64(ck) >> P.fine_shift) - fbase;
+                        if (f >= 0 && f < kRadixMaxParts) {
+                            bin[r] = (int)f;
+                            rank[r] = atomicAdd(&cnt[bin[r]], 1u);
+                        } else {   // beyond the window (tiny first-level partitions): this row is placed on its own
+                            const long long fb = f + fbase;
+                            const unsigned long long pos = P.offsets[fb] + atomicAdd(&P.cursor[fb], 1ull);
+                            for (int c = 0; c < P.ncols; ++c) {
+                                const uint8_t* sc = in + P.stage_off[c] * kOffScale;
+                                if (P.shift[c] == 3) reinterpret_cast<uint64_t*>(P.dst[0][c])[pos] = ((const uint64_t*)sc)[i];
+                                else reinterpret_cast<uint32_t*>(P.dst[0][c])[pos] = ((const uint32_t*)sc)[i];
+                            }
+                        }
+                    } else {
+                        bin[r] = radix_bin_of<HOT>(ck, mix64(ck), P.nhash, P.log2_parts, P.hot);
+                        rank[r] = atomicAdd(&cnt[bin[r]], 1u);
+                    }
                 }
             }
         }
@@ -450,10 +477,11 @@ __global__ void __launch_bounds__(THREADS, THREADS >= 1024 ? 1 : 2) radix_scatte
                 const int bq = tid * BPT + q;
                 if (bq < nbins) {
                     cnt[bq] = ex;
-                    s_gbase[bq] = c[q] ? P.offsets[bq] + atomicAdd(&P.cursor[bq], (unsigned long long)c[q]) : 0ull;
+                    s_gbase[bq] = c[q] ? P.offsets[fbase + bq] + atomicAdd(&P.cursor[fbase + bq], (unsigned long long)c[q]) : 0ull;
                 }
                 ex += c[q];
             }
+            if (FINE && tid == THREADS - 1) s_total = (int)ex;
         }
         __syncthreads();
 #pragma unroll
@@ -468,15 +496,16 @@ __global__ void __launch_bounds__(THREADS, THREADS >= 1024 ? 1 : 2) radix_scatte
         // write-out: consecutive threads -> consecutive slots -> runs of consecutive destination rows
         unsigned long long d[ROWS];
         int src_row[ROWS], dq[ROWS];
+        const int nslots = FINE ? s_total : rows;
 #pragma unroll
         for (int r = 0; r < ROWS; ++r) {
             const int sl = r * THREADS + tid;
             d[r] = 0; src_row[r] = 0; dq[r] = 0;
-            if (sl < rows) {
+            if (sl < nslots) {
                 const int p = s_part[sl];
                 d[r] = s_gbase[p] + (unsigned)(sl - cnt[p]);
                 src_row[r] = s_perm[sl];
-                dq[r] = p >> P.log2_parts;
+                dq[r] = FINE ? 0 : p >> P.log2_parts;
             }
         }
         for (int c = 0; c < P.ncols; ++c) {
@@ -484,12 +513,12 @@ __global__ void __launch_bounds__(THREADS, THREADS >= 1024 ? 1 : 2) radix_scatte
                 const uint64_t* sc = reinterpret_cast<const uint64_t*>(in + P.stage_off[c] * kOffScale);
 #pragma unroll
                 for (int r = 0; r < ROWS; ++r)
-                    if (r * THREADS + tid < rows) reinterpret_cast<uint64_t*>(P.dst[dq[r]][c])[d[r]] = sc[src_row[r]];
+                    if (r * THREADS + tid < nslots) reinterpret_cast<uint64_t*>(P.dst[dq[r]][c])[d[r]] = sc[src_row[r]];
             } else {
                 const uint32_t* sc = reinterpret_cast<const uint32_t*>(in + P.stage_off[c] * kOffScale);
 #pragma unroll
                 for (int r = 0; r < ROWS; ++r)
-                    if (r * THREADS + tid < rows) reinterpret_cast<uint32_t*>(P.dst[dq[r]][c])[d[r]] = sc[src_row[r]];
+                    if (r * THREADS + tid < nslots) reinterpret_cast<uint32_t*>(P.dst[dq[r]][c])[d[r]] = sc[src_row[r]];
             }
         }
         __syncthreads();   // the tile buffer, s_perm, s_part and s_gbase are free again
@@ -602,6 +631,107 @@ int32_t radix_partition(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int ke
     if (nrows > 0) {
         HostTrace tr("partition.scatter");
         IGL_CUDA_OK(launch_radix_scatter(ctx, P, off, st));
+        ctx->launches++;
+    }
+    return IGL_OK;
+}
+
+// ---- second-level ("fine") partition: rows already ordered by their first hash bits are ordered by more of
+// them, down to the table sub-region a single CTA can build in shared memory (join.cu, join_build_fine_kernel).
+__global__ void __launch_bounds__(512) radix_hist_fine_kernel(const void* __restrict__ keys, int type, long long n, int fine_shift, int fine_lp2,
+                                                              unsigned long long* hist) {
+    __shared__ unsigned int s_hist[kRadixMaxParts];
+    const long long ntiles = (n + kRtTile - 1) / kRtTile;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        for (int p = threadIdx.x; p < kRadixMaxParts; p += 512) s_hist[p] = 0;
+        __syncthreads();
+        const long long row0 = tile * kRtTile;
+        const uint64_t raw0 = type == IGL_T_I32 ? (uint64_t)(uint32_t)((const int32_t*)keys)[row0] : ((const uint64_t*)keys)[row0];
+        const long long fbase = (long long)((mix64(part_canon(type, raw0)) >> fine_shift) >> fine_lp2) << fine_lp2;
+#pragma unroll
+        for (int r = 0; r < kRtTile / 512; ++r) {
+            const long long i = row0 + r * 512 + threadIdx.x;
+            if (i < n) {
+                const uint64_t raw = type == IGL_T_I32 ? (uint64_t)(uint32_t)((const int32_t*)keys)[i] : ((const uint64_t*)keys)[i];
+                const long long f = (long long)(mix64(part_canon(type, raw)) >> fine_shift) - fbase;
+                if (f >= 0 && f < kRadixMaxParts) atomicAdd(&s_hist[f], 1u);
+                else atomicAdd(&hist[f + fbase], 1ull);
+            }
+        }
+        __syncthreads();
+        for (int p = threadIdx.x; p < kRadixMaxParts; p += 512)
+            if (s_hist[p]) atomicAdd(&hist[fbase + p], (unsigned long long)s_hist[p]);
+        __syncthreads();
+    }
+}
+
+// exclusive scan of up to 2^20 counters by one CTA: offsets[nbins] = total, cursor zeroed
+__global__ void __launch_bounds__(1024) radix_scan_fine_kernel(const unsigned long long* __restrict__ hist, unsigned long long* __restrict__ offsets,
+                                                               unsigned long long* __restrict__ cursor, long long nbins) {
+    __shared__ unsigned long long s_warp[32];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const long long per = (nbins + 1023) / 1024, b0 = (long long)t * per, b1 = min(nbins, b0 + per);
+    unsigned long long sum = 0;
+    for (long long b = b0; b < b1; ++b) sum += hist[b];
+    unsigned long long inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += v;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    unsigned long long ex = inc - sum;
+    for (int w = 0; w < warp; ++w) ex += s_warp[w];
+    for (long long b = b0; b < b1; ++b) { offsets[b] = ex; cursor[b] = 0; ex += hist[b]; }
+    if (t == 1023) offsets[nbins] = ex;
+}
+
+bool radix_partition_fine_supported(const igl_dev_col* cols, int ncols) {
+    if (!radix_partition_supported(cols, ncols)) return false;
+    uint32_t off = 0;
+    for (int c = 0; c < ncols; ++c) {
+        if ((uintptr_t)cols[c].data & 15) return false;
+        off += (uint32_t)kRtTile << (cols[c].type == IGL_T_I32 ? 2 : 3);
+    }
+    return off + 4u * kRtTile <= (92u << 10);   // the two-CTA scatter form
+}
+
+// Orders `cols` (already ordered by the top `fine_bits - fine_lp2` bits of the join hash) by its top `fine_bits`
+// bits into dst[c].  `scratch` holds 3 * (2^fine_bits + 1) u64: counts, offsets (kept: offsets[b] .. offsets[b + 1]
+// are bin b's rows), cursors.
+int32_t radix_partition_fine(igl_ctx* ctx, const igl_dev_col* cols, int ncols, int key_col, long long nrows, int fine_bits, int fine_lp2,
+                             void* const* dst, void* scratch, cudaStream_t st) {
+    if (fine_bits < 1 || fine_bits > 20 || fine_lp2 < 0 || fine_lp2 > fine_bits || !radix_partition_fine_supported(cols, ncols))
+        return fail(IGL_ERR_INVALID_ARG, "radix_partition_fine: bad arguments");
+    const long long nbins = 1ll << fine_bits;
+    unsigned long long* hist = (unsigned long long*)scratch;
+    unsigned long long* offsets = hist + (nbins + 1);
+    unsigned long long* cursor = offsets + (nbins + 1);
+    IGL_CUDA_OK(cudaMemsetAsync(hist, 0, sizeof(unsigned long long) * (nbins + 1), st));
+    RadixParams P{};
+    P.ncols = ncols; P.key_col = key_col; P.key_type = cols[key_col].type; P.log2_parts = 0; P.ndest = 1; P.nhash = 1; P.n = nrows;
+    P.offsets = offsets; P.cursor = cursor;
+    P.fine_shift = 64 - fine_bits; P.fine_lp2 = fine_lp2; P.fine_bins = nbins;
+    uint32_t off = 0;
+    for (int c = 0; c < ncols; ++c) {
+        P.src[c] = (const uint8_t*)cols[c].data; P.dst[0][c] = (uint8_t*)dst[c];
+        P.shift[c] = cols[c].type == IGL_T_I32 ? 2 : 3;
+        P.stage_off[c] = off;
+        off += (uint32_t)kRadixTile << P.shift[c];
+    }
+    if (nrows > 0) {
+        radix_hist_fine_kernel<<<ctx->sm_count * 4, 512, 0, st>>>(cols[key_col].data, P.key_type, nrows, P.fine_shift, fine_lp2, hist);
+        IGL_CUDA_OK(cudaGetLastError());
+    }
+    radix_scan_fine_kernel<<<1, 1024, 0, st>>>(hist, offsets, cursor, nbins);
+    IGL_CUDA_OK(cudaGetLastError());
+    ctx->launches += 2;
+    if (nrows > 0) {
+        const size_t dyn = (size_t)off + 4u * kRtTile;
+        IGL_CUDA_OK(cudaFuncSetAttribute((const void*)radix_scatter_bulk_kernel<8, false, 512, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+        radix_scatter_bulk_kernel<8, false, 512, true><<<ctx->sm_count * 2, 512, dyn, st>>>(P, 1, off);
+        IGL_CUDA_OK(cudaGetLastError());
         ctx->launches++;
     }
     return IGL_OK;

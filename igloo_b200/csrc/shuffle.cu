@@ -917,7 +917,7 @@ int32_t igl_join_shuffle_run(igl_join_shuffle* js, const igl_dev_col* right, int
     IGL_TRY(launch_seg_copy(ctx, R, src_cols[0], W, d_copy[0], ncopy[0], copy_blocks[0], R.slab.data(), st_b));
     std::vector<igl_dev_col> rcols(R.ncols), lcols(L.ncols);
     for (int c = 0; c < R.ncols; ++c) rcols[c] = igl_dev_col{R.types[c], 0, R.slab[c], nullptr, nullptr};
-    IGL_TRY(igl_join_set_prepartitioned(js->join, lp > 0 ? 1 : 0));
+    IGL_TRY(igl_join_set_prepartitioned(js->join, lp));   // by how many hash bits the slab is ordered
     IGL_TRY(igl_join_build(js->join, rcols.data(), recv_total[0], st_b));
     cudaEventRecord(js->ev[4], st_b);
     if (yield) IGL_CUDA_OK(cudaStreamWaitEvent(st, js->ev[4], 0));

@@ -236,7 +236,10 @@ int32_t igl_join_has_duplicates(const igl_join* j);
  * probed while it is L2-resident.  igl_join_partition_bits: log2 of the fan-out
  * igl_join_build would use for `build_rows` rows (0 = none).  A caller whose rows already
  * arrive in that order (igl_partition_scatter_radix) switches the join's own reordering
- * off with igl_join_set_prepartitioned(j, 1).  No counterpart in the reference. */
+ * off with igl_join_set_prepartitioned(j, bits): bits = the number of leading hash bits the rows
+ * are ordered by (1 = ordered, not told by how many; 0 = back to the join's own reordering).
+ * A large unique build side is then ordered once more, down to 64 KB table sub-regions that one
+ * CTA each builds in shared memory.  No counterpart in the reference. */
 int32_t igl_join_partition_bits(igl_ctx* ctx, int64_t build_rows);
 int32_t igl_join_set_prepartitioned(igl_join* j, int32_t on);
 /* Device time (ms, CUDA events on the call's stream) of the last build and probe of `j`:

@@ -211,6 +211,34 @@ def test_full_scale_property_c3_digest(ctx):
     assert np.array_equal(out[3].data[:m].cpu().numpy(), hv)
 
 
+def test_large_unique_build_sides_are_built_in_shared_memory(ctx):
+    """Build sides whose table exceeds 64 MB are ordered down to 64 KB table sub-regions and built by one CTA
+    each in shared memory (join_build_fine_kernel); rows whose walk leaves their sub-region are inserted
+    afterwards.  Against the oracle: row-id payload over narrow rows (Inner and Left), the key equal to the
+    empty-slot sentinel, Int32 keys with an inlined payload, and duplicate keys (the build falls back to CSR)."""
+    rng = np.random.default_rng(41)
+    nb, nl = 2_200_000, 3_000_000
+    keys = rng.permutation(np.arange(-1_500_000, 3_000_000, dtype=np.int64))[:nb].copy()
+    keys[7] = np.iinfo(np.int64).min                                  # kEmptyKey: lives in a side entry
+    right = pa.table({"k": keys, "a": rng.integers(0, 1 << 30, nb).astype(np.int32), "b": rng.integers(-5, 5, nb).astype(np.int32)})
+    lk = rng.integers(-2_000_000, 3_500_000, nl)
+    lk[::1000] = np.iinfo(np.int64).min
+    left = pa.table({"k": lk, "w": rng.integers(0, 99, nl).astype(np.int32)})
+    for jt in (0, 1):
+        got, j = check(ctx, left, right, "k", "k", jt)
+        assert not j.has_duplicates and got.num_rows > nl // 3
+    # Int32 keys, payload inlined into the table
+    k32 = rng.permutation(np.arange(-(1 << 22), 1 << 22, dtype=np.int32))[:nb]
+    right32 = pa.table({"k": k32, "v": rng.integers(0, 1 << 50, nb)})
+    left32 = pa.table({"k": rng.integers(-(1 << 22), 1 << 22, nl).astype(np.int32), "w": rng.integers(0, 1 << 40, nl)})
+    got, j = check(ctx, left32, right32, "k", "k", 0)
+    assert not j.has_duplicates
+    # every key twice: the shared-memory build sees the duplicates and the table is rebuilt as CSR runs
+    dup = pa.table({"k": np.concatenate([keys[: nb // 2], keys[: nb // 2]]), "a": right.column("a"), "b": right.column("b")})
+    got, j = check(ctx, left.slice(0, 500_000), dup, "k", "k", 0)
+    assert j.has_duplicates
+
+
 def test_partitioned_row_id_gather_c4_shape_digest(ctx):
     """C4 shape at 1/18 scale on the device generator: a build side wider than (key, payload) is
     joined through row ids, and at 2^23 rows its 256 MB table is radix-partitioned, so the row ids
