@@ -26,11 +26,17 @@
 // NULL keys and the one key value that equals the empty-slot sentinel live in
 // two side entries.
 //
-// Probe kernels reuse the tile pipeline (tile_pipe.cuh): left column tiles are
-// staged by bulk async copies, each lane looks up 4 keys with all first-slot
-// loads in flight together, output offsets come from the ordered look-back scan,
-// and output rows (left columns from shared memory ++ right payload) are written
-// once, to their final place.
+// Large build sides are ordered by the top bits of the join hash (partition.cu) so that
+// the table is touched region by region while L2-resident; large UNIQUE ones are ordered
+// once more and built in shared memory, one CTA per 64 KB of table (join_build_fine_kernel).
+//
+// Probe kernels.  General path (nulls, Left/Full, duplicate keys): the tile pipeline
+// (tile_pipe.cuh) — left column tiles staged by bulk async copies, each lane looks up 4 keys
+// with all first-slot loads in flight together, output offsets from the ordered look-back
+// scan, output rows (left columns from shared memory ++ right payload) written once, to
+// their final place.  Fast path (inner, unique keys, no nulls): join_probe_flat_kernel, one
+// warp per CTA, matched rows written at their input position; its SEG form reads the probe
+// rows from runs that may sit in other GPUs' memory (shuffle.cu).
 #include "internal.h"
 #include "kernels.h"
 #include "tile_pipe.cuh"
