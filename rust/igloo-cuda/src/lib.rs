@@ -2,6 +2,7 @@
 //! and HashJoin physical operators behind the engine's own `ExecutionPlan` trait.
 //! UNBUILT in this repository's environment (no Rust toolchain) — see README.md.
 pub mod expr;
+pub mod device;
 pub mod ffi;
 pub mod ops;
 

@@ -34,6 +34,29 @@ def test_library_exports_every_declared_symbol(lib):
     assert not missing, missing
 
 
+def test_rust_shim_binds_only_what_the_header_declares_and_each_function_once():
+    """rust/igloo-cuda cannot be built here (no toolchain), so at least its extern blocks are held against
+    the header: every `fn igl_*` it declares exists in include/igloo_cuda.h, with the same number of
+    parameters, and no function is declared twice across the crate's modules."""
+    hdr = open(os.path.join(ROOT, "include", "igloo_cuda.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    c_params = {}
+    for name, params in re.findall(r"\b(igl_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", hdr, flags=re.S):
+        params = params.strip()
+        c_params[name] = 0 if params in ("", "void") else params.count(",") + 1
+    seen = {}
+    for fn in ("ffi.rs", "device.rs"):
+        src = open(os.path.join(ROOT, "rust", "igloo-cuda", "src", fn)).read()
+        src = re.sub(r"//[^\n]*", "", src)
+        for name, params in re.findall(r"\bfn\s+(igl_[a-z0-9_]+)\s*\(([^)]*)\)", src, flags=re.S):
+            assert name not in seen, f"{name} declared in {seen[name]} and {fn}"
+            seen[name] = fn
+            assert name in c_params, f"{fn}: {name} is not in the header"
+            n = len([q for q in params.split(",") if q.strip()])
+            assert n == c_params[name], f"{fn}: {name} takes {n} parameters, the header says {c_params[name]}"
+    assert {"igl_op_push", "igl_op_pull", "igl_join_shuffle_run", "igl_join_create_ex", "igl_fp_run_static"} <= set(seen)
+
+
 def test_no_device_means_loud_failure_not_fallback(lib):
     """Without a GPU, igl_ctx_create must fail with a message (this box has none;
     on the GPU box the call succeeds and the handle is destroyed again)."""

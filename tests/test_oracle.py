@@ -231,6 +231,23 @@ def test_join_utf8_key_and_payload_faithful():
     assert out.to_pydict() == {"name": ["Bob", "Eve"], "age": [30, 32], "right_name": ["Bob", "Eve"], "city": ["Rome", "Oslo"]}
 
 
+def test_join_utf8_key_null_the_string_null_and_the_empty_string():
+    """The printed key (hash_join.rs:120, arrow-array's Debug) writes a NULL as `null` and the string "null" as
+    `"null"` with its quotes, so they differ; NULL == NULL like every key; "" is a value of its own; and a Utf8 key
+    never meets a key of another type (`StringArray` is in the printed form).  What the GPU string-key tests
+    (tests/test_gpu_operators.py) are held against."""
+    left = pa.table({"name": pa.array(["null", None, "", "a", "a"], pa.string()), "w": pa.array([1, 2, 3, 4, 5], pa.int32())})
+    right = pa.table({"name": pa.array([None, "null", "a", "", None], pa.string()), "v": pa.array([10, 20, 30, 40, 50], pa.int32())})
+    _, out = _join(left, right, "name", "name")
+    got = sorted(zip(out.column("w").to_pylist(), out.column("v").to_pylist()))
+    assert got == [(1, 20), (2, 10), (2, 50), (3, 40), (4, 30), (5, 30)]
+    _, lo = _join(pa.table({"name": pa.array(["zz"], pa.string()), "w": pa.array([9], pa.int32())}), right, "name", "name", orc.JOIN_LEFT)
+    assert lo.to_pydict() == {"name": ["zz"], "w": [9], "right_name": [None], "v": [None]}
+    ints = pa.table({"name": pa.array([1, 2], pa.int64()), "v": pa.array([1, 2], pa.int32())})
+    _, none = _join(pa.table({"name": pa.array(["1", "2"], pa.string())}), ints, "name", "name")
+    assert none.num_rows == 0
+
+
 def test_join_fast_equals_faithful_random():
     rng = np.random.default_rng(3)
     nl, nr = 5000, 700
