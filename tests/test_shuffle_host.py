@@ -69,6 +69,44 @@ def test_plan_with_a_broadcast_destination_hands_hot_build_rows_to_every_rank():
     assert sum(p[2] for p in plans) == int(counts[:, :world * parts].sum()) + world * bcast
 
 
+def test_plan_properties_on_random_inputs():
+    """Whatever the counts: every rank derives the same layout, bins never overlap, every ordinary row is read by
+    exactly one rank and every broadcast row by all of them, and a rank's runs come partition by partition."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=60, deadline=None)
+    @given(st.integers(1, 8), st.integers(0, 4), st.integers(0, 1), st.integers(0, 2 ** 31), st.sampled_from([0, 1, 7, 300, 70000]))
+    def prop(world, lp, broadcast, seed, hi):
+        rng = np.random.default_rng(seed)
+        parts, ndest = 1 << lp, world + broadcast
+        bins = ndest << lp
+        counts = rng.integers(0, hi + 1, (world, bins))
+        plans = [shuffle_plan(counts, r, world, lp, broadcast=broadcast) for r in range(world)]
+        offs = plans[0][0]
+        readers = np.zeros((world, bins), np.int64)
+        for r, (o, segs, total) in enumerate(plans):
+            assert np.array_equal(o, offs)
+            assert len(segs) == (1 + broadcast) * world * parts
+            assert total == sum(n for _, _, n in segs)
+            last_part = -1
+            for i, (src, row0, n) in enumerate(segs):
+                part = i // ((1 + broadcast) * world)
+                assert part >= last_part
+                last_part = part
+                k = (i // world) % (1 + broadcast)
+                b = ((world if k else r) << lp) + part
+                assert (src, row0, n) == (i % world, int(offs[i % world][b]), int(counts[i % world][b]))
+                readers[src][b] += 1
+        for s in range(world):
+            ends = offs[s] + (counts[s] + 3) // 4 * 4
+            assert (offs[s][1:] == ends[:-1]).all() and offs[s][0] == 0 and (offs[s] % 4 == 0).all()
+        assert (readers[:, : world << lp] == 1).all()
+        if broadcast:
+            assert (readers[:, world << lp:] == world).all()
+
+    prop()
+
+
 def test_plan_rejects_bad_arguments():
     import pytest
     from igloo_b200._lib import IglooCudaError
