@@ -243,7 +243,8 @@ int32_t igl_join_has_duplicates(const igl_join* j);
 int32_t igl_join_partition_bits(igl_ctx* ctx, int64_t build_rows);
 int32_t igl_join_set_prepartitioned(igl_join* j, int32_t on);
 /* Device time (ms, CUDA events on the call's stream) of the last build and probe of `j`:
- * out[0] build-side partitioning, out[1] table init + build kernels, out[2] probe-side
+ * out[0] build-side partitioning (both levels when the table is built in shared memory), out[1]
+ * the table build (init + global-atomic build, or the shared-memory build), out[2] probe-side
  * partitioning, out[3] the probe kernel (-1 where nothing was recorded).  Measurement aid. */
 int32_t igl_join_phase_ms(igl_join* j, double out[4]);
 void igl_join_destroy(igl_join* j);
